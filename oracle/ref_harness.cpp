@@ -1,0 +1,357 @@
+// oracle/ref_harness.cpp — TEST INFRASTRUCTURE ONLY (never shipped, never linked into libstage_gpu.so).
+//
+// Our own C-API harness over the UNMODIFIED reference library (compiled by oracle/Makefile.ref
+// from the sources where they lie under /root/reference into oracle/_ref/libstage_ref.so).
+// It drives the reference's real code path for the hot path:
+//   * table construction   : BTree::Insert + BTree::FinalizeInsert, like LoadYCSBRows
+//                            (/root/reference/benchmark/ycsb/ycsb_loader.cpp:93-173)
+//   * point probe          : BTree::Read (src/vstore/b_tree.cpp:2066-2129) + the visibility rule of
+//                            IndexScanExecutor (include/execute/executor.h:383-446)
+//   * range scan           : BTree::RangeScanBySize -> Iterator::GetNext (include/vstore/b_tree.h:830-941)
+//                            + executor loop (executor.h:459-535 MVCC, :626-638 table scan)
+// The two executor chain-walk branches are undefined behaviour at HEAD, so the
+// harness applies the same visibility rule itself: "emit the matching version once, then stop".
+//
+// Used by tests/ (as the checker) and by bench.py's cpu_baseline / --impl reference legs only.
+
+#include <cstdint>
+#include <cstring>
+#include <vector>
+#include <thread>
+#include <chrono>
+#include <atomic>
+#include <limits>
+
+#include "vstore/b_tree.h"
+#include "vstore/valen_buffer.h"
+#include "vstore/version_store.h"
+#include "common/catalog.h"
+#include "common/ephemeral_pool.h"
+
+using namespace mvstore;
+
+struct ref_table {
+    BTree *tree = nullptr;
+    Catalog *catalog = nullptr;
+    DramBlockPool *leaf_pool = nullptr;
+    InnerNodeBuffer *inner_pool = nullptr;
+    EphemeralPool *undo_pool = nullptr;
+    uint32_t payload_size = 0;
+    uint32_t leaf_node_size = 0;
+    // version-chain storage created by ref_commit_update (TupleHeader + slot bytes)
+    std::vector<char *> chain_allocs;
+};
+
+extern "C" {
+
+// ---------------------------------------------------------------------------------------------
+// construction
+// ---------------------------------------------------------------------------------------------
+ref_table *ref_table_create(uint32_t catalog_key_len, uint32_t payload_size, uint32_t split_threshold,
+                            uint32_t merge_threshold, uint32_t leaf_node_size, uint64_t leaf_pool_blocks) {
+    auto *t = new ref_table();
+    t->payload_size = payload_size;
+    t->leaf_node_size = leaf_node_size;
+    t->catalog = new Catalog();
+    uint8_t *bitmap = new uint8_t[2];
+    bitmap[0] = 1;
+    bitmap[1] = 0;
+    t->catalog->init("table0", 2, bitmap, catalog_key_len, 1, false);
+    t->catalog->add_col("Key", catalog_key_len, "VARCHAR");
+    t->catalog->add_col("payload", payload_size, "VARCHAR");
+    ParameterSet param(split_threshold, merge_threshold, leaf_node_size, payload_size);
+    t->leaf_pool = new DramBlockPool(leaf_pool_blocks, leaf_pool_blocks);
+    RecordBufferPool *p1 = new RecordBufferPool(5000000, 5000000);
+    t->inner_pool = new InnerNodeBuffer(p1);
+    RecordBufferPool *p2 = new RecordBufferPool(5000000, 5000000);
+    UndoBuffer *undo = new UndoBuffer(p2);
+    t->undo_pool = new EphemeralPool(undo);
+    t->tree = new BTree(param, *t->catalog, t->leaf_pool, t->inner_pool, t->undo_pool);
+    return t;
+}
+
+// Insert n (key, payload) pairs in order and finalize each with commit_id, exactly like the loaders do.
+// Returns number of rows actually inserted (duplicates are skipped like the loader's KeyExists branch).
+int64_t ref_insert(ref_table *t, const void *keys, uint32_t key_size, const void *payloads, uint64_t n,
+                   uint32_t commit_id) {
+    const char *k = static_cast<const char *>(keys);
+    const char *p = static_cast<const char *>(payloads);
+    int64_t ok = 0;
+    for (uint64_t i = 0; i < n; ++i) {
+        RecordMeta meta;
+        ReturnCode rc = t->tree->Insert(k + i * key_size, (uint16_t) key_size, p + i * (uint64_t) t->payload_size,
+                                        &meta, commit_id);
+        if (!rc.IsOk()) continue;
+        RecordMetadata *meta_ptr =
+                reinterpret_cast<RecordMetadata *>(meta.GetMetaData().GetLocationPtr()->record_meta_ptr);
+        t->tree->FinalizeInsert(meta_ptr, commit_id);
+        t->tree->IncreaseTupleCount(1);
+        ++ok;
+    }
+    return ok;
+}
+
+// Variable-length keys (reference test fixture uses std::to_string(i) keys): key i occupies
+// keys[off[i] .. off[i+1]).
+int64_t ref_insert_varlen(ref_table *t, const void *keys, const uint32_t *off, const void *payloads, uint64_t n,
+                          uint32_t commit_id) {
+    const char *k = static_cast<const char *>(keys);
+    const char *p = static_cast<const char *>(payloads);
+    int64_t ok = 0;
+    for (uint64_t i = 0; i < n; ++i) {
+        RecordMeta meta;
+        ReturnCode rc = t->tree->Insert(k + off[i], (uint16_t) (off[i + 1] - off[i]),
+                                        p + i * (uint64_t) t->payload_size, &meta, commit_id);
+        if (!rc.IsOk()) continue;
+        RecordMetadata *meta_ptr =
+                reinterpret_cast<RecordMetadata *>(meta.GetMetaData().GetLocationPtr()->record_meta_ptr);
+        t->tree->FinalizeInsert(meta_ptr, commit_id);
+        ++ok;
+    }
+    return ok;
+}
+
+// YCSB int loader body (ycsb_loader.cpp:144-172): key = 4 LE bytes of rowid, payload = 1000 x (uint8)rowid.
+int64_t ref_load_ycsb_int(ref_table *t, uint64_t begin_rowid, uint64_t end_rowid) {
+    std::vector<char> payload(t->payload_size);
+    int64_t ok = 0;
+    for (uint64_t rowid = begin_rowid; rowid < end_rowid; ++rowid) {
+        memset(payload.data(), (int) rowid, payload.size());
+        uint32_t k_ = (uint32_t) rowid;
+        RecordMeta meta;
+        ReturnCode rc = t->tree->Insert(reinterpret_cast<const char *>(&k_), sizeof(uint32_t), payload.data(),
+                                        &meta, INVALID_CID);
+        if (!rc.IsOk()) continue;
+        RecordMetadata *meta_ptr =
+                reinterpret_cast<RecordMetadata *>(meta.GetMetaData().GetLocationPtr()->record_meta_ptr);
+        t->tree->FinalizeInsert(meta_ptr, INVALID_CID);
+        t->tree->IncreaseTupleCount(1);
+        ++ok;
+    }
+    return ok;
+}
+
+// Delete via BTree::Delete (is_for_update=true path zeroes the slot meta immediately,
+// src/vstore/b_tree.cpp:1210-1221) — used to create leaves whose max key is not the separator (Q6).
+int ref_delete(ref_table *t, const void *key, uint32_t key_size) {
+    RecordMeta meta;
+    TupleHeader hdr;
+    ReturnCode rc = t->tree->Delete(static_cast<const char *>(key), (uint16_t) key_size, &meta, &hdr, true, 0);
+    return rc.IsOk() ? 0 : -(int) rc.rc;
+}
+
+// Post-commit state of a committed single-row update, constructed with the reference's own types
+// exactly as SSNTransactionManager::CommitTransaction installs it
+// (src/concurrency/transaction_manager.cpp:610-676): the old version [key][payload] goes into a
+// TupleHeader slot with begin_id_ = old cstamp, comm_id_ = committer stamp, next_ = previous chain
+// head; the leaf record is overwritten in place, its meta takes the new commit id and next_ptr
+// points at the new TupleHeader. (Going through the full Index-SSN machinery is out of scope and
+// nondeterministic because of its GC thread; the bytes the read path sees are these.)
+int ref_commit_update(ref_table *t, const void *key, uint32_t key_size, const void *new_payload,
+                      uint32_t commit_id) {
+    LeafNode *leaf = t->tree->TraverseToLeaf(nullptr, static_cast<const char *>(key), (uint16_t) key_size);
+    if (!leaf) return -1;
+    RecordMetadata *meta_ptr = nullptr;
+    ReturnCode rc = leaf->Read(static_cast<const char *>(key), (uint16_t) key_size, t->payload_size, &meta_ptr,
+                               false);
+    if (!rc.IsOk() || !meta_ptr) return -2;
+    char *rec_key = nullptr, *rec_payload = nullptr;
+    leaf->GetRawRecord(*meta_ptr, &rec_key, &rec_payload);
+    uint32_t klen = meta_ptr->GetKeyLength();
+    char *mem = new char[sizeof(TupleHeader) + klen + t->payload_size];
+    t->chain_allocs.push_back(mem);
+    TupleHeader *hd = new (mem) TupleHeader();
+    char *slot = mem + sizeof(TupleHeader);
+    hd->init(hd, reinterpret_cast<uint64_t>(slot), (oid_t) t->chain_allocs.size());
+    memcpy(slot, rec_key, klen);
+    memcpy(slot + klen, rec_payload, t->payload_size);
+    hd->SetBeginId(meta_ptr->GetTxnCommitId());
+    hd->SetCommitId(commit_id);
+    hd->SetNextHeaderPointer(meta_ptr->GetNextPointer());
+    memcpy(rec_payload, new_payload, t->payload_size);
+    meta_ptr->FinalizeForUpdate(commit_id);
+    meta_ptr->SetNextPointer(reinterpret_cast<uint64_t>(hd));
+    return 0;
+}
+
+const void *ref_root(ref_table *t) { return t->tree->GetRootNodeSafe(); }
+uint64_t ref_tuple_count(ref_table *t) { return t->tree->GetTupleCount(); }
+
+// ---------------------------------------------------------------------------------------------
+// reads
+// ---------------------------------------------------------------------------------------------
+// returns 1 if a visible version was found; writes commit id, key (key_size bytes), payload.
+static inline int visible_version(Record *rec, uint32_t key_size, uint32_t payload_size, uint32_t read_ts,
+                                  uint32_t *ts_out, char *key_out, char *payload_out) {
+    uint32_t cid = rec->meta.meta_data.GetTxnCommitId();
+    if (read_ts >= cid) {                                   // executor.h:385 / :469
+        if (ts_out) *ts_out = cid;
+        if (key_out) memcpy(key_out, rec->GetKey(), key_size);
+        if (payload_out) memcpy(payload_out, rec->GetPayload(), payload_size);
+        return 1;
+    }
+    uint64_t next = rec->meta.meta_data.GetNextPointer();   // == RecordMeta.next_tuple_ptr (b_tree.cpp:2116)
+    while (next != 0 && next != std::numeric_limits<uint64_t>::max()) {
+        TupleHeader *hd = reinterpret_cast<TupleHeader *>(next);
+        cid_t begn = hd->GetBeginId(), comm = hd->GetEndCommitId();
+        // executor.h:418/:502 stop on INVALID_CID (==0). NB a loader-created version has begin 0, so
+        // the reference can never return the original (commit id 0) version through a chain.
+        if (begn == INVALID_CID || comm == INVALID_CID) return 0;
+        if (read_ts >= begn && read_ts <= comm) {           // executor.h:422 / :505
+            const char *slot = reinterpret_cast<const char *>(hd->GetTupleSlot());
+            if (ts_out) *ts_out = begn;
+            if (key_out) memcpy(key_out, slot, key_size);
+            if (payload_out) memcpy(payload_out, slot + key_size, payload_size);
+            return 1;
+        }
+        next = hd->GetNextHeaderPointer();
+    }
+    return 0;
+}
+
+int ref_probe(ref_table *t, const void *keys, uint32_t key_size, uint64_t n, uint32_t read_ts, uint8_t *found,
+              uint32_t *ts, void *key_out, void *payload_out) {
+    const char *k = static_cast<const char *>(keys);
+    const uint32_t P = t->payload_size;
+    for (uint64_t i = 0; i < n; ++i) {
+        std::unique_ptr<Record> rec = t->tree->Read(k + i * key_size, (uint16_t) key_size, read_ts, false);
+        int f = 0;
+        if (rec != nullptr) {
+            f = visible_version(rec.get(), key_size, P, read_ts, ts ? ts + i : nullptr,
+                                key_out ? static_cast<char *>(key_out) + i * key_size : nullptr,
+                                payload_out ? static_cast<char *>(payload_out) + i * (uint64_t) P : nullptr);
+            delete[] reinterpret_cast<char *>(rec.release());
+        }
+        if (found) found[i] = (uint8_t) f;
+        if (!f) {
+            if (ts) ts[i] = 0;
+            if (key_out) memset(static_cast<char *>(key_out) + i * key_size, 0, key_size);
+            if (payload_out) memset(static_cast<char *>(payload_out) + i * (uint64_t) P, 0, P);
+        }
+    }
+    return 0;
+}
+
+// One scan: executor loop over Iterator::GetNext. Rows go to out row index base .. base+count.
+static inline uint32_t scan_one(ref_table *t, const char *start_key, uint32_t key_size, uint32_t scan_size,
+                                uint32_t read_ts, int apply_visibility, uint32_t *ts_out, char *key_out,
+                                char *payload_out) {
+    const uint32_t P = t->payload_size;
+    auto iter = t->tree->RangeScanBySize(start_key, (uint16_t) key_size, scan_size);
+    uint32_t cnt = 0;
+    for (uint32_t scanned = 0; scanned < scan_size; ++scanned) {
+        std::unique_ptr<Record> rec = iter->GetNext();
+        if (rec == nullptr) continue;                        // executor.h:461 / :629
+        int f;
+        if (apply_visibility) {
+            f = visible_version(rec.get(), key_size, P, read_ts, ts_out ? ts_out + cnt : nullptr,
+                                key_out ? key_out + (uint64_t) cnt * key_size : nullptr,
+                                payload_out ? payload_out + (uint64_t) cnt * P : nullptr);
+        } else {                                             // TableScanExecutor: no visibility test
+            if (ts_out) ts_out[cnt] = rec->meta.meta_data.GetTxnCommitId();
+            if (key_out) memcpy(key_out + (uint64_t) cnt * key_size, rec->GetKey(), key_size);
+            if (payload_out) memcpy(payload_out + (uint64_t) cnt * P, rec->GetPayload(), P);
+            f = 1;
+        }
+        cnt += (uint32_t) f;
+        delete[] reinterpret_cast<char *>(rec.release());
+    }
+    return cnt;
+}
+
+int ref_scan(ref_table *t, const void *start_keys, uint32_t key_size, const uint32_t *scan_sizes, uint64_t n,
+             uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts, void *key_out,
+             uint32_t *ts_out, void *payload_out) {
+    const char *k = static_cast<const char *>(start_keys);
+    const uint32_t P = t->payload_size;
+    for (uint64_t i = 0; i < n; ++i) {
+        uint64_t base = i * (uint64_t) out_stride;
+        row_counts[i] = scan_one(t, k + i * key_size, key_size, scan_sizes[i], read_ts, apply_visibility,
+                                 ts_out ? ts_out + base : nullptr,
+                                 key_out ? static_cast<char *>(key_out) + base * key_size : nullptr,
+                                 payload_out ? static_cast<char *>(payload_out) + base * P : nullptr);
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// timing legs (CPU baseline): T threads, each over its slice of the same key stream, results copied
+// into per-thread scratch (the reference allocates a Record per row; that cost is part of its path).
+// Returns elapsed seconds; *rows_out = total rows returned.
+// ---------------------------------------------------------------------------------------------
+static void pin_to_core(int c) {
+    cpu_set_t set;
+    CPU_ZERO(&set);
+    CPU_SET(c, &set);
+    pthread_setaffinity_np(pthread_self(), sizeof(set), &set);   // like PinToCore, ycsb_workload.cpp:41-46
+}
+
+double ref_time_probe(ref_table *t, const void *keys, uint32_t key_size, uint64_t n, uint32_t read_ts,
+                      int threads, int pin, uint64_t *hits_out) {
+    std::vector<std::thread> th;
+    std::vector<uint64_t> hits(threads, 0);
+    std::atomic<int> ready{0};
+    std::atomic<bool> go{false};
+    const char *k = static_cast<const char *>(keys);
+    for (int w = 0; w < threads; ++w) {
+        th.emplace_back([&, w] {
+            if (pin) pin_to_core(w);
+            std::vector<char> pay(t->payload_size), key(key_size);
+            uint64_t b = n * w / threads, e = n * (w + 1) / threads, h = 0;
+            ready++;
+            while (!go.load()) {}
+            for (uint64_t i = b; i < e; ++i) {
+                std::unique_ptr<Record> rec = t->tree->Read(k + i * key_size, (uint16_t) key_size, read_ts, false);
+                if (rec != nullptr) {
+                    uint32_t ts;
+                    h += visible_version(rec.get(), key_size, t->payload_size, read_ts, &ts, key.data(), pay.data());
+                    delete[] reinterpret_cast<char *>(rec.release());
+                }
+            }
+            hits[w] = h;
+        });
+    }
+    while (ready.load() < threads) {}
+    auto t0 = std::chrono::steady_clock::now();
+    go.store(true);
+    for (auto &x : th) x.join();
+    auto t1 = std::chrono::steady_clock::now();
+    uint64_t tot = 0;
+    for (auto h : hits) tot += h;
+    if (hits_out) *hits_out = tot;
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
+double ref_time_scan(ref_table *t, const void *start_keys, uint32_t key_size, uint32_t scan_size, uint64_t n,
+                     uint32_t read_ts, int apply_visibility, int threads, int pin, uint64_t *rows_out) {
+    std::vector<std::thread> th;
+    std::vector<uint64_t> rows(threads, 0);
+    std::atomic<int> ready{0};
+    std::atomic<bool> go{false};
+    const char *k = static_cast<const char *>(start_keys);
+    for (int w = 0; w < threads; ++w) {
+        th.emplace_back([&, w] {
+            if (pin) pin_to_core(w);
+            std::vector<char> pay((uint64_t) t->payload_size * scan_size), key((uint64_t) key_size * scan_size);
+            std::vector<uint32_t> ts(scan_size);
+            uint64_t b = n * w / threads, e = n * (w + 1) / threads, r = 0;
+            ready++;
+            while (!go.load()) {}
+            for (uint64_t i = b; i < e; ++i)
+                r += scan_one(t, k + i * key_size, key_size, scan_size, read_ts, apply_visibility, ts.data(),
+                              key.data(), pay.data());
+            rows[w] = r;
+        });
+    }
+    while (ready.load() < threads) {}
+    auto t0 = std::chrono::steady_clock::now();
+    go.store(true);
+    for (auto &x : th) x.join();
+    auto t1 = std::chrono::steady_clock::now();
+    uint64_t tot = 0;
+    for (auto r : rows) tot += r;
+    if (rows_out) *rows_out = tot;
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
+}  // extern "C"

@@ -1,0 +1,167 @@
+/* stage_gpu.h — C ABI of libstage_gpu.so: the B200-native index-organized read path for Stage.
+ *
+ * This is the drop-in boundary. The reference has no FFI layer: its read interface
+ * is in-process C++ (paths relative to the reference repository):
+ *
+ *   std::unique_ptr<Record>   BTree::Read(const char *key, uint16_t key_size, cid_t commit_id,
+ *                                         bool is_for_update)            include/vstore/b_tree.h:812-813
+ *   std::unique_ptr<Iterator> BTree::RangeScanBySize(const char *key1, uint16_t size1,
+ *                                         uint32_t scan_size)            include/vstore/b_tree.h:830-835
+ *   std::unique_ptr<Record>   Iterator::GetNext()                        include/vstore/b_tree.h:899-941
+ *   IndexScanExecutor<Key,T>::Execute / GetResults / GetRecord           include/execute/executor.h:342-570
+ *   TableScanExecutor<Key,T>::Execute / GetResults / GetFailNum          include/execute/executor.h:572-661
+ *
+ * The entry points below are what a cgo-style binding of that interface would bind: plain
+ * pointers and sizes, no C++ types, no exceptions, caller-allocated outputs. The header-only C++
+ * adapters in include/stage_gpu_executors.h put the reference's own class shapes back on top.
+ *
+ * All functions return 0 on success or a negative stage_status code; stage_gpu_strerror() names it.
+ * A snapshot is immutable once sealed; *_batch calls on one snapshot are serialised on the
+ * snapshot's CUDA stream.
+ */
+#ifndef STAGE_GPU_H_
+#define STAGE_GPU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct stage_snapshot stage_snapshot_t;
+
+enum stage_status {
+    STAGE_OK = 0,
+    STAGE_ERR_ARG = -1,          /* bad argument / unsupported schema */
+    STAGE_ERR_CUDA = -2,         /* CUDA runtime error (text via stage_gpu_last_error) */
+    STAGE_ERR_NOT_QUIESCED = -3, /* tree has a frozen node or an in-flight (IsInserting) record */
+    STAGE_ERR_STATE = -4,        /* call order (e.g. probe before seal) */
+    STAGE_ERR_NOMEM = -5,
+    STAGE_ERR_LAYOUT = -6        /* node bytes do not look like a Stage BzTree node */
+};
+
+/* key_kind: how BaseNode::KeyCompare orders keys of this table (include/vstore/b_tree.h:116-134) */
+enum stage_key_kind {
+    STAGE_KEY_AUTO = 0,         /* key_size < 16 -> signed bytes, else memcmp */
+    STAGE_KEY_SIGNED_BYTES = 1, /* my_memcmp: signed char difference, byte 0 first (b_tree.h:99-106) */
+    STAGE_KEY_MEMCMP = 2        /* libc memcmp: unsigned bytes */
+};
+
+/* Table schema = the part of ParameterSet (include/vstore/b_tree.h:23-40) and Catalog
+ * (include/common/catalog.h:69) the read path depends on. Keys are fixed-length per table, as in
+ * every driver table (YCSB int 4 B, YCSB string 16 B, TPC-C 8/16/32 B). */
+typedef struct stage_schema {
+    uint32_t key_size;       /* bytes of key actually passed to Read/Insert (YCSB int: 4) */
+    uint32_t payload_size;   /* ParameterSet.payload_size */
+    uint32_t leaf_node_size; /* ParameterSet.leaf_node_size (64 KiB in both drivers) */
+    uint32_t key_kind;       /* enum stage_key_kind */
+} stage_schema_t;
+
+/* One retired version = one TupleHeader (include/vstore/version_store.h:28-46) in index form. */
+typedef struct stage_version {
+    uint32_t begin_id;  /* TupleHeader.begin_id_  */
+    uint32_t commit_id; /* TupleHeader.comm_id_   */
+    uint32_t next;      /* 1-based index of the next older version in this snapshot, 0 = end of chain */
+    uint32_t reserved;
+} stage_version_t;
+
+typedef struct stage_snapshot_info {
+    uint64_t n_rows;        /* visible records flattened */
+    uint64_t n_leaves;
+    uint64_t n_versions;
+    uint64_t device_bytes;  /* HBM held by the snapshot */
+    uint32_t key_words;     /* 32-bit words per sortable key */
+    uint32_t n_levels;      /* sampled search levels above the key column */
+    uint32_t max_leaf_rows;
+    uint32_t device;        /* CUDA device ordinal */
+} stage_snapshot_info_t;
+
+/* flags for *_batch */
+enum {
+    STAGE_IO_HOST = 0,   /* all in/out pointers are host memory (pinned or pageable) */
+    STAGE_IO_DEVICE = 1  /* all in/out pointers are device memory on the snapshot's GPU */
+};
+
+/* ---- lifecycle --------------------------------------------------------------------------- */
+
+/* Bind the calling process to a CUDA device (one process per GPU). Optional; default device 0. */
+int stage_gpu_init(int device);
+
+/* Flatten a live, quiesced reference tree. `root` is BTree::GetRootNodeSafe() (b_tree.h:872-875).
+ * Walks inner nodes in tree order (the order TableScanExecutor::ScanInnerNode uses,
+ * executor.h:592-609), stages the leaf images and the TupleHeader chains hanging off
+ * RecordMetadata.next_ptr, and runs the record-layout transform kernel. Replaces the pointer
+ * chasing of BTree::TraverseToLeaf (src/vstore/b_tree.cpp:1804-1846) for all later reads. */
+int stage_gpu_snapshot_from_tree(const void *root, const stage_schema_t *schema, stage_snapshot_t **out);
+
+/* Streaming construction for callers that own the walk (same result as from_tree):
+ *   begin -> add_versions* -> add_leaves* -> seal.
+ * leaf_images[i] points at leaf_node_size bytes of an unmodified LeafNode, leaves in tree order.
+ * upper_fences holds n keys of key_size bytes: the separator the parent stores to the RIGHT of
+ * each leaf (ignored for the last leaf of the tree; pass has_upper_fence[i] = 0 there).
+ * chain_heads: for every leaf, an array of record_count 1-based version indices (0 = no chain)
+ * replacing the host pointers in RecordMetadata.next_ptr; may be NULL if the tree has no chains. */
+int stage_gpu_snapshot_begin(const stage_schema_t *schema, uint64_t n_leaves_hint, uint64_t n_rows_hint,
+                             stage_snapshot_t **out);
+int stage_gpu_snapshot_add_versions(stage_snapshot_t *s, const stage_version_t *versions,
+                                    const void *payloads /* n x payload_size */, uint64_t n);
+int stage_gpu_snapshot_add_leaves(stage_snapshot_t *s, const void *const *leaf_images, const void *upper_fences,
+                                  const uint8_t *has_upper_fence, const uint32_t *const *chain_heads, uint64_t n);
+int stage_gpu_snapshot_seal(stage_snapshot_t *s);
+
+/* Build the YCSB int table (benchmark/ycsb/ycsb_loader.cpp:144-159: key = uint32 rowid as 4 raw
+ * bytes, payload = payload_size x (uint8)rowid, commit id 0) directly on the device in consolidated
+ * form: rows [first_rank, first_rank + n_local) of the table of n_rows_total keys in reference key
+ * order, rows_per_leaf records per leaf (every leaf sorted, separator = its largest key).
+ * Used where the host tree cannot be materialised. */
+int stage_gpu_snapshot_generate_ycsb(const stage_schema_t *schema, uint64_t n_rows_total, uint64_t first_rank,
+                                     uint64_t n_local, uint32_t rows_per_leaf, stage_snapshot_t **out);
+
+int stage_gpu_snapshot_info(const stage_snapshot_t *s, stage_snapshot_info_t *info);
+int stage_gpu_snapshot_destroy(stage_snapshot_t *s);
+
+/* The CUDA stream (cudaStream_t) the snapshot launches on; set it to share a caller's stream. */
+int stage_gpu_snapshot_set_stream(stage_snapshot_t *s, void *cuda_stream);
+void *stage_gpu_snapshot_get_stream(const stage_snapshot_t *s);
+
+/* ---- reads -------------------------------------------------------------------------------- */
+
+/* Batched BTree::Read + IndexScanExecutor point branch (b_tree.cpp:2066-2129, executor.h:374-454).
+ * keys: n x key_size bytes. For probe i:
+ *   found[i]   1 if a version visible at read_ts exists (latest in-leaf version if
+ *              read_ts >= its commit id, else the first chain version with begin <= read_ts <= commit)
+ *   ts[i]      commit id of the version returned (in-leaf: meta & 0xFFFFFFFF; chain: begin_id_)
+ *   key_out    n x key_size, payload_out n x payload_size: written only where found[i] == 1
+ * Any output pointer may be NULL. */
+int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
+                          uint32_t *ts, void *key_out, void *payload_out, int flags);
+
+/* Batched BTree::RangeScanBySize + the executor loop over Iterator::GetNext
+ * (b_tree.h:830-941, b_tree.cpp:1261-1315; executor.h:455-535 with apply_visibility = 1,
+ * executor.h:620-638 with apply_visibility = 0). Scan i starts at start_keys[i] (inclusive) and asks
+ * for scan_sizes[i] rows; its rows are written, in the reference's order, to row slots
+ * [i*out_stride, i*out_stride + row_counts[i]) of key_out / ts_out / payload_out
+ * (out_stride >= max scan size). Reproduces the iterator's slot-order truncation and
+ * leaf-hop termination rules exactly. */
+int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
+                         uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts,
+                         void *key_out, uint32_t *ts_out, void *payload_out, int flags);
+
+/* Range partitioning across GPUs (one process per GPU): splitters = the largest key of every shard
+ * but the last, in reference key order. owner[i] = shard that owns keys[i]. Host pointers. */
+int stage_gpu_route(const stage_schema_t *schema, const void *splitters, uint32_t n_shards, const void *keys,
+                    uint64_t n, uint32_t *owner);
+
+/* ---- utilities ---------------------------------------------------------------------------- */
+void *stage_gpu_host_alloc(size_t bytes); /* pinned host memory for STAGE_IO_HOST batches */
+void stage_gpu_host_free(void *p);
+/* Kernels launched by this library since process start (for bench.py's gpu_launches). */
+uint64_t stage_gpu_launch_count(void);
+const char *stage_gpu_strerror(int status);
+const char *stage_gpu_last_error(void); /* text of the last CUDA error seen on this thread */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STAGE_GPU_H_ */

@@ -1,0 +1,272 @@
+"""stage_indexorganized_b200 — Python host mirror of the C ABI in include/stage_gpu.h.
+
+The product is ``libstage_gpu.so`` (hand-written sm_100a CUDA behind a C ABI, see csrc/). This module
+only binds it with ctypes so that tests, ``bench.py`` and Python callers drive exactly the entry
+points a C++/cgo caller would. There is NO CPU fallback: if the library is missing or no CUDA device
+is usable the calls raise.
+
+Reference interface mirrored (paths relative to the reference repository):
+  BTree::Read                      include/vstore/b_tree.h:812-813   -> Snapshot.probe
+  BTree::RangeScanBySize/GetNext   include/vstore/b_tree.h:830-941   -> Snapshot.scan
+  IndexScanExecutor / TableScanExecutor  include/execute/executor.h:342-661 (visibility on/off)
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libstage_gpu.so")
+
+IO_HOST, IO_DEVICE = 0, 1
+KEY_AUTO, KEY_SIGNED_BYTES, KEY_MEMCMP = 0, 1, 2
+
+_vp, _u32, _u64, _i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int
+
+
+class StageError(RuntimeError):
+    pass
+
+
+class Schema(C.Structure):
+    _fields_ = [("key_size", _u32), ("payload_size", _u32), ("leaf_node_size", _u32), ("key_kind", _u32)]
+
+
+class Version(C.Structure):
+    _fields_ = [("begin_id", _u32), ("commit_id", _u32), ("next", _u32), ("reserved", _u32)]
+
+
+class SnapshotInfo(C.Structure):
+    _fields_ = [("n_rows", _u64), ("n_leaves", _u64), ("n_versions", _u64), ("device_bytes", _u64),
+                ("key_words", _u32), ("n_levels", _u32), ("max_leaf_rows", _u32), ("device", _u32)]
+
+
+# every symbol include/stage_gpu.h declares: (restype, argtypes)
+SYMBOLS = {
+    "stage_gpu_init": (_i32, [_i32]),
+    "stage_gpu_snapshot_from_tree": (_i32, [_vp, C.POINTER(Schema), C.POINTER(_vp)]),
+    "stage_gpu_snapshot_begin": (_i32, [C.POINTER(Schema), _u64, _u64, C.POINTER(_vp)]),
+    "stage_gpu_snapshot_add_versions": (_i32, [_vp, _vp, _vp, _u64]),
+    "stage_gpu_snapshot_add_leaves": (_i32, [_vp, _vp, _vp, _vp, _vp, _u64]),
+    "stage_gpu_snapshot_seal": (_i32, [_vp]),
+    "stage_gpu_snapshot_generate_ycsb": (_i32, [C.POINTER(Schema), _u64, _u64, _u64, _u32, C.POINTER(_vp)]),
+    "stage_gpu_snapshot_info": (_i32, [_vp, C.POINTER(SnapshotInfo)]),
+    "stage_gpu_snapshot_destroy": (_i32, [_vp]),
+    "stage_gpu_snapshot_set_stream": (_i32, [_vp, _vp]),
+    "stage_gpu_snapshot_get_stream": (_vp, [_vp]),
+    "stage_gpu_probe_batch": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp, _vp, _vp, _i32]),
+    "stage_gpu_scan_batch": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _vp, _vp, _i32]),
+    "stage_gpu_route": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp]),
+    "stage_gpu_host_alloc": (_vp, [C.c_size_t]),
+    "stage_gpu_host_free": (None, [_vp]),
+    "stage_gpu_launch_count": (_u64, []),
+    "stage_gpu_strerror": (C.c_char_p, [_i32]),
+    "stage_gpu_last_error": (C.c_char_p, []),
+}
+
+_lib = None
+
+
+def build(verbose=False):
+    """Compile csrc/ into libstage_gpu.so (nvcc, sm_100a). Raises on failure."""
+    r = subprocess.run(["make", "-C", os.path.join(_HERE, "csrc")], capture_output=not verbose, text=True)
+    if r.returncode != 0:
+        raise StageError("building libstage_gpu.so failed:\n" + (r.stdout or "") + (r.stderr or ""))
+
+
+def lib():
+    """The loaded C-ABI library; raises loudly if it is not built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise StageError(f"{LIB_PATH} is missing: run __graft_entry__.build() / make -C "
+                             f"{os.path.join(_HERE, 'csrc')} (there is no CPU fallback)")
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            f = getattr(l, name)
+            f.restype, f.argtypes = res, args
+        _lib = l
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        l = lib()
+        raise StageError(f"stage_gpu error {rc}: {l.stage_gpu_strerror(rc).decode()} "
+                         f"[{l.stage_gpu_last_error().decode()}]")
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data_as(_vp)
+    if hasattr(a, "data_ptr"):          # torch tensor on the snapshot's device
+        return _vp(a.data_ptr())
+    return _vp(int(a))
+
+
+def init(device=0):
+    _check(lib().stage_gpu_init(device))
+
+
+def launch_count():
+    return int(lib().stage_gpu_launch_count())
+
+
+class PinnedArray:
+    """numpy view over pinned host memory from stage_gpu_host_alloc."""
+
+    def __init__(self, shape, dtype):
+        self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self.ptr = lib().stage_gpu_host_alloc(max(self.nbytes, 1))
+        if not self.ptr:
+            raise StageError("stage_gpu_host_alloc failed")
+        buf = (C.c_uint8 * max(self.nbytes, 1)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            lib().stage_gpu_host_free(self.ptr)
+            self.ptr = None
+
+
+class Snapshot:
+    """GPU-resident flattened copy of one index-organized table (immutable once built)."""
+
+    def __init__(self, handle, schema):
+        self.h = handle
+        self.schema = schema
+
+    # -- construction --------------------------------------------------------------------------
+    @classmethod
+    def from_tree(cls, root, key_size, payload_size, leaf_node_size=65536, key_kind=KEY_AUTO):
+        sc = Schema(key_size, payload_size, leaf_node_size, key_kind)
+        h = _vp()
+        _check(lib().stage_gpu_snapshot_from_tree(_vp(int(root)), C.byref(sc), C.byref(h)))
+        return cls(h, sc)
+
+    @classmethod
+    def generate_ycsb(cls, n_rows_total, payload_size=1000, rows_per_leaf=61, first_rank=0, n_local=None,
+                      leaf_node_size=65536):
+        sc = Schema(4, payload_size, leaf_node_size, KEY_AUTO)
+        h = _vp()
+        if n_local is None:
+            n_local = n_rows_total - first_rank
+        _check(lib().stage_gpu_snapshot_generate_ycsb(C.byref(sc), n_rows_total, first_rank, n_local, rows_per_leaf,
+                                                      C.byref(h)))
+        return cls(h, sc)
+
+    @classmethod
+    def from_leaves(cls, leaf_ptrs, fences, has_fence, key_size, payload_size, leaf_node_size=65536,
+                    key_kind=KEY_AUTO, versions=None, version_payloads=None, chain_heads=None, rows_hint=None):
+        """Streaming construction: begin -> add_versions -> add_leaves -> seal."""
+        sc = Schema(key_size, payload_size, leaf_node_size, key_kind)
+        h = _vp()
+        n = len(leaf_ptrs)
+        if rows_hint is None:
+            rows_hint = n * (leaf_node_size // 24)
+        _check(lib().stage_gpu_snapshot_begin(C.byref(sc), n, rows_hint, C.byref(h)))
+        self = cls(h, sc)
+        if versions is not None and len(versions):
+            varr = (Version * len(versions))(*versions)
+            vp = np.ascontiguousarray(version_payloads, np.uint8)
+            _check(lib().stage_gpu_snapshot_add_versions(h, C.cast(varr, _vp), _ptr(vp), len(versions)))
+        ptrs = (C.c_void_p * n)(*[int(p) for p in leaf_ptrs])
+        fences = np.ascontiguousarray(fences, np.uint8)
+        has_fence = np.ascontiguousarray(has_fence, np.uint8)
+        heads_ptrs = None
+        keep = []
+        if chain_heads is not None:
+            hp = []
+            for ch in chain_heads:
+                if ch is None:
+                    hp.append(None)
+                else:
+                    a = np.ascontiguousarray(ch, np.uint32)
+                    keep.append(a)
+                    hp.append(a.ctypes.data)
+            heads_ptrs = (C.c_void_p * n)(*hp)
+        _check(lib().stage_gpu_snapshot_add_leaves(h, C.cast(ptrs, _vp), _ptr(fences), _ptr(has_fence),
+                                                   C.cast(heads_ptrs, _vp) if heads_ptrs is not None else None, n))
+        _check(lib().stage_gpu_snapshot_seal(h))
+        return self
+
+    def info(self):
+        i = SnapshotInfo()
+        _check(lib().stage_gpu_snapshot_info(self.h, C.byref(i)))
+        return i
+
+    def set_stream(self, cuda_stream):
+        _check(lib().stage_gpu_snapshot_set_stream(self.h, _vp(int(cuda_stream))))
+
+    def close(self):
+        if self.h:
+            _check(lib().stage_gpu_snapshot_destroy(self.h))
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -- reads: host buffers (the call a user of the reference's API makes) ---------------------
+    def probe(self, keys, read_ts, want_payload=True, out=None):
+        """Batched BTree::Read + point visibility. keys: (n, key_size) uint8 host array.
+        Returns (found u8[n], ts u32[n], key_out u8[n,K], payload u8[n,P])."""
+        keys = np.ascontiguousarray(keys, np.uint8)
+        n = keys.shape[0]
+        K, P = self.schema.key_size, self.schema.payload_size
+        assert keys.shape == (n, K)
+        if out is None:
+            found = np.zeros(n, np.uint8)
+            ts = np.zeros(n, np.uint32)
+            key_out = np.zeros((n, K), np.uint8)
+            pay = np.zeros((n, P), np.uint8) if want_payload else None
+        else:
+            found, ts, key_out, pay = out
+        _check(lib().stage_gpu_probe_batch(self.h, _ptr(keys), n, read_ts, _ptr(found), _ptr(ts), _ptr(key_out),
+                                           _ptr(pay), IO_HOST))
+        return found, ts, key_out, pay
+
+    def scan(self, start_keys, scan_sizes, read_ts, apply_visibility, want_payload=True, out_stride=None):
+        """Batched RangeScanBySize + executor loop. Returns (row_counts u32[n], key_out u8[n,S,K],
+        ts u32[n,S], payload u8[n,S,P])."""
+        start_keys = np.ascontiguousarray(start_keys, np.uint8)
+        n = start_keys.shape[0]
+        K, P = self.schema.key_size, self.schema.payload_size
+        scan_sizes = np.ascontiguousarray(np.broadcast_to(np.asarray(scan_sizes, np.uint32), (n,)))
+        stride = int(out_stride if out_stride is not None else (scan_sizes.max() if n else 0))
+        counts = np.zeros(n, np.uint32)
+        key_out = np.zeros((n, stride, K), np.uint8)
+        ts = np.zeros((n, stride), np.uint32)
+        pay = np.zeros((n, stride, P), np.uint8) if want_payload else None
+        _check(lib().stage_gpu_scan_batch(self.h, _ptr(start_keys), _ptr(scan_sizes), n, stride, read_ts,
+                                          int(apply_visibility), _ptr(counts), _ptr(key_out), _ptr(ts), _ptr(pay),
+                                          IO_HOST))
+        return counts, key_out, ts, pay
+
+    # -- reads: device buffers (torch tensors or raw device pointers) ---------------------------
+    def probe_device(self, keys, n, read_ts, found=None, ts=None, key_out=None, payload_out=None):
+        _check(lib().stage_gpu_probe_batch(self.h, _ptr(keys), n, read_ts, _ptr(found), _ptr(ts), _ptr(key_out),
+                                           _ptr(payload_out), IO_DEVICE))
+
+    def scan_device(self, start_keys, scan_sizes, n, out_stride, read_ts, apply_visibility, row_counts,
+                    key_out=None, ts_out=None, payload_out=None):
+        _check(lib().stage_gpu_scan_batch(self.h, _ptr(start_keys), _ptr(scan_sizes), n, out_stride, read_ts,
+                                          int(apply_visibility), _ptr(row_counts), _ptr(key_out), _ptr(ts_out),
+                                          _ptr(payload_out), IO_DEVICE))
+
+
+def route(keys, splitters, key_size, key_kind=KEY_AUTO):
+    """owner[i] = index of the range shard owning keys[i] (splitters = largest key of each shard but the last)."""
+    keys = np.ascontiguousarray(keys, np.uint8)
+    splitters = np.ascontiguousarray(splitters, np.uint8).reshape(-1, key_size)
+    sc = Schema(key_size, 1, 65536, key_kind)
+    owner = np.zeros(keys.shape[0], np.uint32)
+    _check(lib().stage_gpu_route(C.byref(sc), _ptr(splitters), splitters.shape[0] + 1, _ptr(keys), keys.shape[0],
+                                 _ptr(owner)))
+    return owner

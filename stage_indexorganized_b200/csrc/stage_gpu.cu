@@ -1,0 +1,900 @@
+// stage_gpu.cu — host side of libstage_gpu.so: snapshot construction (tree walker, staging,
+// transform launch), batch entry points, C ABI (include/stage_gpu.h).
+//
+// Reference anchors (paths relative to the reference repository):
+//   tree walk order        include/execute/executor.h:592-609 (ScanInnerNode), b_tree.h:336-345
+//   leaf / meta decoding   include/vstore/record_meta.h:66-93, version_store.h:176-217
+//   version chains         include/vstore/version_store.h:28-46, src/concurrency/transaction_manager.cpp:610-676
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <atomic>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/stage_gpu.h"
+#include "keys.cuh"
+#include "node_layout.h"
+#include "probe.cuh"
+#include "scan.cuh"
+#include "transform.cuh"
+#include "generate.cuh"
+
+using namespace stage;
+
+// ------------------------------------------------------------------------------------------------
+// error plumbing
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+static std::atomic<uint64_t> g_launches{0};
+static int g_device = 0;
+
+#define CUDA_TRY(expr)                                                                       \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess) {                                                             \
+            g_last_error = std::string(#expr) + ": " + cudaGetErrorString(_e);               \
+            return STAGE_ERR_CUDA;                                                           \
+        }                                                                                    \
+    } while (0)
+
+#define LAUNCH_CHECK()                                                                       \
+    do {                                                                                     \
+        g_launches.fetch_add(1, std::memory_order_relaxed);                                  \
+        CUDA_TRY(cudaGetLastError());                                                        \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// snapshot
+// ------------------------------------------------------------------------------------------------
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes) {
+        if (bytes <= cap) return STAGE_OK;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        CUDA_TRY(cudaMalloc(&p, want));
+        cap = want;
+        return STAGE_OK;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+struct stage_snapshot {
+    stage_schema_t schema{};
+    int nw = 1;
+    uint32_t xormask = 0;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    bool sealed = false;
+    std::mutex mu;
+
+    uint64_t n_rows = 0, n_leaves = 0, n_versions = 0;
+    uint64_t cap_rows = 0, cap_leaves = 0;
+    uint32_t max_leaf_rows = 0;
+    size_t device_bytes = 0;
+
+    // columns
+    uint32_t *d_skey = nullptr;
+    uint16_t *d_slot = nullptr;
+    uint32_t *d_ts = nullptr, *d_chain = nullptr;
+    uint8_t *d_payload = nullptr;
+    uint32_t *d_leaf_off = nullptr, *d_sep = nullptr;
+    uint8_t *d_cont = nullptr, *d_has_sep = nullptr;
+    uint32_t *d_levels = nullptr;
+    uint32_t *d_ver_begin = nullptr, *d_ver_commit = nullptr, *d_ver_next = nullptr;
+    uint8_t *d_ver_payload = nullptr;
+    uint32_t *d_err = nullptr;
+
+    // streaming build state
+    std::vector<uint32_t> h_leaf_off;           // [n_leaves+1]
+    std::vector<uint32_t> h_sep;                // sortable, n_leaves * nw
+    std::vector<uint8_t> h_has_sep;
+    std::vector<stage_version_t> h_versions;
+    std::vector<uint8_t> h_ver_payload;
+    uint8_t *h_stage[2] = {nullptr, nullptr};   // pinned
+    uint8_t *d_stage[2] = {nullptr, nullptr};
+    cudaEvent_t stage_ev[2] = {nullptr, nullptr};
+    uint32_t chunk_leaves = 0;
+    uint32_t stage_fill = 0, stage_cur = 0, stage_maxcount = 0;
+    uint64_t staged_base_leaf = 0;              // first leaf index of the chunk being filled
+    uint64_t rows_staged = 0;
+
+    SnapshotView view{};
+
+    // scratch for STAGE_IO_HOST batches
+    DevBuf sc_keys, sc_found, sc_ts, sc_keyout, sc_payload, sc_sizes, sc_counts;
+};
+
+template <typename T>
+static int dev_alloc(stage_snapshot *s, T **p, size_t n) {
+    size_t bytes = std::max<size_t>(n, 1) * sizeof(T);
+    bytes = (bytes + 255) & ~size_t(255);
+    CUDA_TRY(cudaMalloc((void **) p, bytes + 256));   // +256: vector loads may touch the padding
+    s->device_bytes += bytes + 256;
+    return STAGE_OK;
+}
+
+static int key_words(uint32_t key_size) {
+    uint32_t w = (key_size + 3) / 4;
+    if (w <= 1) return 1;
+    if (w <= 2) return 2;
+    if (w <= 4) return 4;
+    if (w <= 8) return 8;
+    return 0;
+}
+
+static int schema_check(const stage_schema_t *sc, int *nw, uint32_t *xormask) {
+    if (!sc || sc->key_size == 0 || sc->payload_size == 0 || sc->leaf_node_size < 64 ||
+        sc->leaf_node_size > 65536 || (sc->leaf_node_size & 7))
+        return STAGE_ERR_ARG;
+    *nw = key_words(sc->key_size);
+    if (*nw == 0) return STAGE_ERR_ARG;
+    uint32_t kind = sc->key_kind;
+    if (kind == STAGE_KEY_AUTO) kind = sc->key_size < 16 ? STAGE_KEY_SIGNED_BYTES : STAGE_KEY_MEMCMP;
+    if (kind != STAGE_KEY_SIGNED_BYTES && kind != STAGE_KEY_MEMCMP) return STAGE_ERR_ARG;
+    *xormask = kind == STAGE_KEY_SIGNED_BYTES ? 0x80808080u : 0u;
+    return STAGE_OK;
+}
+
+template <int NW>
+static void host_sortable(const uint8_t *key, uint32_t K, uint32_t xormask, uint32_t *out) {
+    SKey<NW> k = to_sortable<NW>(key, K, xormask);
+    for (int i = 0; i < NW; ++i) out[i] = k.w[i];
+}
+static void host_sortable_nw(int nw, const uint8_t *key, uint32_t K, uint32_t xormask, uint32_t *out) {
+    switch (nw) {
+        case 1: host_sortable<1>(key, K, xormask, out); break;
+        case 2: host_sortable<2>(key, K, xormask, out); break;
+        case 4: host_sortable<4>(key, K, xormask, out); break;
+        default: host_sortable<8>(key, K, xormask, out); break;
+    }
+}
+
+static void snapshot_free(stage_snapshot *s) {
+    cudaSetDevice(s->device);
+    void *ptrs[] = {s->d_skey, s->d_slot, s->d_ts, s->d_chain, s->d_payload, s->d_leaf_off, s->d_sep, s->d_cont,
+                    s->d_has_sep, s->d_levels, s->d_ver_begin, s->d_ver_commit, s->d_ver_next, s->d_ver_payload,
+                    s->d_err, s->d_stage[0], s->d_stage[1]};
+    for (void *p : ptrs)
+        if (p) cudaFree(p);
+    for (int i = 0; i < 2; ++i) {
+        if (s->h_stage[i]) cudaFreeHost(s->h_stage[i]);
+        if (s->stage_ev[i]) cudaEventDestroy(s->stage_ev[i]);
+    }
+    s->sc_keys.release(); s->sc_found.release(); s->sc_ts.release(); s->sc_keyout.release();
+    s->sc_payload.release(); s->sc_sizes.release(); s->sc_counts.release();
+    if (s->own_stream && s->stream) cudaStreamDestroy(s->stream);
+    delete s;
+}
+
+// ------------------------------------------------------------------------------------------------
+// build: begin / add_versions / add_leaves / seal
+// ------------------------------------------------------------------------------------------------
+static int snapshot_new(const stage_schema_t *schema, stage_snapshot **out) {
+    int nw;
+    uint32_t xm;
+    int rc = schema_check(schema, &nw, &xm);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(g_device));
+    auto *s = new stage_snapshot();
+    s->schema = *schema;
+    s->nw = nw;
+    s->xormask = xm;
+    s->device = g_device;
+    cudaError_t e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        g_last_error = cudaGetErrorString(e);
+        delete s;
+        return STAGE_ERR_CUDA;
+    }
+    s->own_stream = true;
+    *out = s;
+    return STAGE_OK;
+}
+
+static int alloc_columns(stage_snapshot *s, uint64_t cap_leaves, uint64_t cap_rows) {
+    if (cap_rows >= 0xFFFFFFF0ull) return STAGE_ERR_ARG;
+    s->cap_leaves = cap_leaves;
+    s->cap_rows = cap_rows;
+    int rc;
+    if ((rc = dev_alloc(s, &s->d_skey, cap_rows * s->nw))) return rc;
+    if ((rc = dev_alloc(s, &s->d_slot, cap_rows))) return rc;
+    if ((rc = dev_alloc(s, &s->d_ts, cap_rows))) return rc;
+    if ((rc = dev_alloc(s, &s->d_chain, cap_rows))) return rc;
+    if ((rc = dev_alloc(s, &s->d_payload, cap_rows * (uint64_t) s->schema.payload_size))) return rc;
+    if ((rc = dev_alloc(s, &s->d_leaf_off, cap_leaves + 1))) return rc;
+    if ((rc = dev_alloc(s, &s->d_sep, (cap_leaves + 1) * s->nw))) return rc;
+    if ((rc = dev_alloc(s, &s->d_cont, cap_leaves + 1))) return rc;
+    if ((rc = dev_alloc(s, &s->d_has_sep, cap_leaves + 1))) return rc;
+    if ((rc = dev_alloc(s, &s->d_err, 1))) return rc;
+    CUDA_TRY(cudaMemsetAsync(s->d_err, 0, 4, s->stream));
+    return STAGE_OK;
+}
+
+static int alloc_staging(stage_snapshot *s) {
+    const uint32_t ls = s->schema.leaf_node_size;
+    s->chunk_leaves = std::max<uint32_t>(1, (32u << 20) / ls);       // 32 MiB per staging buffer
+    for (int i = 0; i < 2; ++i) {
+        CUDA_TRY(cudaHostAlloc((void **) &s->h_stage[i], (size_t) s->chunk_leaves * ls, cudaHostAllocDefault));
+        CUDA_TRY(cudaMalloc((void **) &s->d_stage[i], (size_t) s->chunk_leaves * ls));
+        CUDA_TRY(cudaEventCreateWithFlags(&s->stage_ev[i], cudaEventDisableTiming));
+    }
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_begin(const stage_schema_t *schema, uint64_t n_leaves_hint, uint64_t n_rows_hint,
+                                        stage_snapshot_t **out) {
+    if (!out) return STAGE_ERR_ARG;
+    stage_snapshot *s = nullptr;
+    int rc = snapshot_new(schema, &s);
+    if (rc) return rc;
+    if ((rc = alloc_columns(s, std::max<uint64_t>(n_leaves_hint, 1), n_rows_hint)) || (rc = alloc_staging(s))) {
+        snapshot_free(s);
+        return rc;
+    }
+    s->h_leaf_off.push_back(0);
+    *out = s;
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_add_versions(stage_snapshot_t *s, const stage_version_t *versions,
+                                               const void *payloads, uint64_t n) {
+    if (!s || s->sealed || (n && (!versions || !payloads))) return STAGE_ERR_ARG;
+    s->h_versions.insert(s->h_versions.end(), versions, versions + n);
+    const uint8_t *p = static_cast<const uint8_t *>(payloads);
+    s->h_ver_payload.insert(s->h_ver_payload.end(), p, p + n * (uint64_t) s->schema.payload_size);
+    return STAGE_OK;
+}
+
+template <int NW>
+static int launch_transform(stage_snapshot *s, int buf, uint32_t n_chunk, uint64_t base_leaf, uint32_t maxcount) {
+    TransformArgs a{};
+    a.leaves = s->d_stage[buf];
+    a.n_chunk_leaves = n_chunk;
+    a.leaf_size = s->schema.leaf_node_size;
+    a.base_leaf = base_leaf;
+    a.leaf_off = s->d_leaf_off;
+    a.sep = s->d_sep;
+    a.has_sep = s->d_has_sep;
+    a.key_size = s->schema.key_size;
+    a.payload_size = s->schema.payload_size;
+    a.xormask = s->xormask;
+    uint32_t cap = 32;
+    while (cap < maxcount) cap <<= 1;
+    a.sort_cap = cap;
+    a.skey = s->d_skey; a.slot = s->d_slot; a.ts = s->d_ts; a.chain = s->d_chain; a.payload = s->d_payload;
+    a.cont = s->d_cont;
+    a.err = s->d_err;
+    size_t smem = (size_t) cap * (NW * 4 + 2);
+    if (smem > 48 * 1024)
+        CUDA_TRY(cudaFuncSetAttribute(leaf_transform_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    leaf_transform_kernel<NW><<<n_chunk, 128, smem, s->stream>>>(a);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
+// push the chunk being filled: upload its fences/offsets, H2D the images, run the transform
+static int flush_chunk(stage_snapshot *s) {
+    const uint32_t n = s->stage_fill;
+    if (n == 0) return STAGE_OK;
+    const int buf = s->stage_cur;
+    const uint64_t base = s->staged_base_leaf;
+    const uint32_t ls = s->schema.leaf_node_size;
+    CUDA_TRY(cudaMemcpyAsync(s->d_leaf_off + base, s->h_leaf_off.data() + base, (n + 1) * sizeof(uint32_t),
+                             cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(s->d_sep + base * s->nw, s->h_sep.data() + base * s->nw, (size_t) n * s->nw * 4,
+                             cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(s->d_has_sep + base, s->h_has_sep.data() + base, n, cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(s->d_stage[buf], s->h_stage[buf], (size_t) n * ls, cudaMemcpyHostToDevice, s->stream));
+    int rc;
+    switch (s->nw) {
+        case 1: rc = launch_transform<1>(s, buf, n, base, s->stage_maxcount); break;
+        case 2: rc = launch_transform<2>(s, buf, n, base, s->stage_maxcount); break;
+        case 4: rc = launch_transform<4>(s, buf, n, base, s->stage_maxcount); break;
+        default: rc = launch_transform<8>(s, buf, n, base, s->stage_maxcount); break;
+    }
+    if (rc) return rc;
+    CUDA_TRY(cudaEventRecord(s->stage_ev[buf], s->stream));
+    s->stage_cur ^= 1;
+    s->stage_fill = 0;
+    s->stage_maxcount = 0;
+    s->staged_base_leaf = base + n;
+    // the other buffer may still be in flight from two chunks ago
+    CUDA_TRY(cudaEventSynchronize(s->stage_ev[s->stage_cur]));
+    return STAGE_OK;
+}
+
+// stage one leaf image: copy to pinned memory, count visible records, patch chain heads
+static int stage_one_leaf(stage_snapshot *s, const uint8_t *leaf, const uint8_t *fence, bool has_fence,
+                          const uint32_t *chain_heads) {
+    const uint32_t ls = s->schema.leaf_node_size;
+    if (s->n_leaves >= s->cap_leaves) return STAGE_ERR_ARG;
+    if (!leaf[kOffIsLeaf]) return STAGE_ERR_LAYOUT;
+    uint64_t status;
+    memcpy(&status, leaf + kOffStatus, 8);
+    if (status & kStatusFrozen) return STAGE_ERR_NOT_QUIESCED;
+    const uint32_t count = status_record_count(status);
+    if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize > ls) return STAGE_ERR_LAYOUT;
+    uint8_t *dst = s->h_stage[s->stage_cur] + (size_t) s->stage_fill * ls;
+    memcpy(dst, leaf, ls);
+    uint32_t vis = 0;
+    for (uint32_t i = 0; i < count; ++i) {
+        uint8_t *mp = dst + kOffMeta + (size_t) i * kMetaSize;
+        uint64_t m;
+        memcpy(&m, mp, 8);
+        uint64_t head = 0;
+        if (meta_visible(m)) {
+            if (m & kMetaControl) return STAGE_ERR_NOT_QUIESCED;
+            if (meta_offset(m) + pad_key_len(meta_key_len(m)) + s->schema.payload_size > ls) return STAGE_ERR_LAYOUT;
+            ++vis;
+            if (chain_heads) head = chain_heads[i];
+        }
+        memcpy(mp + kMetaNextPtr, &head, 8);   // pointer translation: host TupleHeader* -> version index
+    }
+    if (s->rows_staged + vis > s->cap_rows) return STAGE_ERR_ARG;
+    s->rows_staged += vis;
+    s->h_leaf_off.push_back((uint32_t) s->rows_staged);
+    s->h_sep.resize((s->n_leaves + 1) * s->nw, 0xFFFFFFFFu);
+    if (has_fence) host_sortable_nw(s->nw, fence, s->schema.key_size, s->xormask, s->h_sep.data() + s->n_leaves * s->nw);
+    s->h_has_sep.push_back(has_fence ? 1 : 0);
+    s->n_leaves++;
+    s->stage_fill++;
+    s->stage_maxcount = std::max(s->stage_maxcount, count);
+    s->max_leaf_rows = std::max(s->max_leaf_rows, vis);
+    if (s->stage_fill == s->chunk_leaves) return flush_chunk(s);
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_add_leaves(stage_snapshot_t *s, const void *const *leaf_images,
+                                             const void *upper_fences, const uint8_t *has_upper_fence,
+                                             const uint32_t *const *chain_heads, uint64_t n) {
+    if (!s || s->sealed || (n && !leaf_images)) return STAGE_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(s->device));
+    const uint8_t *f = static_cast<const uint8_t *>(upper_fences);
+    for (uint64_t i = 0; i < n; ++i) {
+        bool hf = f && (!has_upper_fence || has_upper_fence[i]);
+        int rc = stage_one_leaf(s, static_cast<const uint8_t *>(leaf_images[i]),
+                                hf ? f + i * s->schema.key_size : nullptr, hf, chain_heads ? chain_heads[i] : nullptr);
+        if (rc) return rc;
+    }
+    return STAGE_OK;
+}
+
+template <int NW>
+static int build_levels(stage_snapshot *s) {
+    // level sizes
+    uint64_t n = s->n_rows;
+    std::vector<uint64_t> sizes{n};
+    while (sizes.back() > kFan) sizes.push_back(sizes.back() / kFan);
+    if ((int) sizes.size() > kMaxLevels) return STAGE_ERR_ARG;
+    uint64_t total = 0;
+    for (size_t l = 1; l < sizes.size(); ++l) total += sizes[l];
+    int rc = dev_alloc(s, &s->d_levels, total * NW);
+    if (rc) return rc;
+    SnapshotView &v = s->view;
+    v.n_levels = (int) sizes.size();
+    v.level[0] = s->d_skey;
+    v.level_n[0] = (uint32_t) sizes[0];
+    uint64_t off = 0;
+    for (size_t l = 1; l < sizes.size(); ++l) {
+        uint32_t *dst = s->d_levels + off * NW;
+        const uint64_t nd = sizes[l];
+        sample_level_kernel<NW><<<(unsigned) ((nd + 255) / 256), 256, 0, s->stream>>>(v.level[l - 1], dst, nd);
+        LAUNCH_CHECK();
+        v.level[l] = dst;
+        v.level_n[l] = (uint32_t) nd;
+        off += nd;
+    }
+    // top levels cached in shared memory: as many as fit in 32 KiB
+    v.smem_levels = 0;
+    v.smem_words = 0;
+    for (int l = v.n_levels - 1; l >= 1; --l) {     // never stage the key column itself
+        uint64_t words = (uint64_t) v.level_n[l] * NW;
+        if ((v.smem_words + words) * 4 > 32 * 1024) break;
+        v.smem_words += (uint32_t) words;
+        v.smem_levels++;
+    }
+    return STAGE_OK;
+}
+
+static void fill_view(stage_snapshot *s) {
+    SnapshotView &v = s->view;
+    v.slot = s->d_slot; v.ts = s->d_ts; v.chain = s->d_chain; v.payload = s->d_payload;
+    v.leaf_off = s->d_leaf_off; v.sep = s->d_sep; v.cont = s->d_cont;
+    v.ver_begin = s->d_ver_begin; v.ver_commit = s->d_ver_commit; v.ver_next = s->d_ver_next;
+    v.ver_payload = s->d_ver_payload;
+    v.n_rows = s->n_rows; v.n_leaves = s->n_leaves;
+    v.key_size = s->schema.key_size; v.payload_size = s->schema.payload_size; v.xormask = s->xormask;
+    v.max_leaf_rows = s->max_leaf_rows;
+}
+
+static int finish_seal(stage_snapshot *s) {
+    int rc;
+    switch (s->nw) {
+        case 1: rc = build_levels<1>(s); break;
+        case 2: rc = build_levels<2>(s); break;
+        case 4: rc = build_levels<4>(s); break;
+        default: rc = build_levels<8>(s); break;
+    }
+    if (rc) return rc;
+    fill_view(s);
+    uint32_t err = 0;
+    CUDA_TRY(cudaMemcpyAsync(&err, s->d_err, 4, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    if (err == 1) return STAGE_ERR_NOT_QUIESCED;
+    if (err) return STAGE_ERR_LAYOUT;
+    s->sealed = true;
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_seal(stage_snapshot_t *s) {
+    if (!s || s->sealed) return STAGE_ERR_STATE;
+    CUDA_TRY(cudaSetDevice(s->device));
+    int rc = flush_chunk(s);
+    if (rc) return rc;
+    s->n_rows = s->rows_staged;
+    // versions
+    s->n_versions = s->h_versions.size();
+    if (s->n_versions) {
+        const uint64_t V = s->n_versions;
+        if ((rc = dev_alloc(s, &s->d_ver_begin, V)) || (rc = dev_alloc(s, &s->d_ver_commit, V)) ||
+            (rc = dev_alloc(s, &s->d_ver_next, V)) ||
+            (rc = dev_alloc(s, &s->d_ver_payload, V * (uint64_t) s->schema.payload_size)))
+            return rc;
+        std::vector<uint32_t> b(V), c(V), nx(V);
+        for (uint64_t i = 0; i < V; ++i) {
+            b[i] = s->h_versions[i].begin_id; c[i] = s->h_versions[i].commit_id; nx[i] = s->h_versions[i].next;
+            if (nx[i] > V) return STAGE_ERR_ARG;
+        }
+        CUDA_TRY(cudaMemcpyAsync(s->d_ver_begin, b.data(), V * 4, cudaMemcpyHostToDevice, s->stream));
+        CUDA_TRY(cudaMemcpyAsync(s->d_ver_commit, c.data(), V * 4, cudaMemcpyHostToDevice, s->stream));
+        CUDA_TRY(cudaMemcpyAsync(s->d_ver_next, nx.data(), V * 4, cudaMemcpyHostToDevice, s->stream));
+        CUDA_TRY(cudaMemcpyAsync(s->d_ver_payload, s->h_ver_payload.data(), s->h_ver_payload.size(),
+                                 cudaMemcpyHostToDevice, s->stream));
+        CUDA_TRY(cudaStreamSynchronize(s->stream));
+    }
+    rc = finish_seal(s);
+    // staging no longer needed
+    for (int i = 0; i < 2; ++i) {
+        if (s->h_stage[i]) { cudaFreeHost(s->h_stage[i]); s->h_stage[i] = nullptr; }
+        if (s->d_stage[i]) { cudaFree(s->d_stage[i]); s->d_stage[i] = nullptr; }
+    }
+    std::vector<uint8_t>().swap(s->h_ver_payload);
+    std::vector<stage_version_t>().swap(s->h_versions);
+    return rc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host tree walker: root -> leaves in tree order, fences, version chains
+// ------------------------------------------------------------------------------------------------
+struct WalkOut {
+    std::vector<const uint8_t *> leaves;
+    std::vector<const uint8_t *> fences;   // fence[i] = separator to the right of leaf i (nullptr for the last)
+    uint64_t rows_upper = 0;
+};
+
+static int walk(const uint8_t *node, uint32_t key_size, WalkOut &w, int depth) {
+    if (!node || depth > 32) return STAGE_ERR_LAYOUT;
+    if (node[kOffIsLeaf]) {
+        uint64_t status;
+        memcpy(&status, node + kOffStatus, 8);
+        w.rows_upper += status_record_count(status);
+        w.leaves.push_back(node);
+        w.fences.push_back(nullptr);
+        return STAGE_OK;
+    }
+    uint32_t sorted;
+    memcpy(&sorted, node + kOffSortedCount, 4);
+    for (uint32_t i = 0; i < sorted; ++i) {
+        uint64_t m;
+        memcpy(&m, node + kOffMeta + (size_t) i * kMetaSize, 8);
+        const uint8_t *rec = node + meta_offset(m);
+        if (i > 0) {
+            // separator i sits between child i-1 and child i: upper fence of the last leaf emitted
+            if (meta_key_len(m) != key_size || w.leaves.empty()) return STAGE_ERR_LAYOUT;
+            w.fences.back() = rec;
+        }
+        uint64_t child;
+        memcpy(&child, rec + pad_key_len(meta_key_len(m)), 8);      // GetChildByMetaIndex, b_tree.h:336-345
+        int rc = walk(reinterpret_cast<const uint8_t *>(child), key_size, w, depth + 1);
+        if (rc) return rc;
+    }
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema_t *schema, stage_snapshot_t **out) {
+    if (!root || !out) return STAGE_ERR_ARG;
+    WalkOut w;
+    int nw;
+    uint32_t xm;
+    int rc = schema_check(schema, &nw, &xm);
+    if (rc) return rc;
+    if ((rc = walk(static_cast<const uint8_t *>(root), schema->key_size, w, 0))) return rc;
+
+    stage_snapshot *s = nullptr;
+    if ((rc = stage_gpu_snapshot_begin(schema, w.leaves.size(), w.rows_upper, &s))) return rc;
+
+    // version chains: RecordMetadata.next_ptr -> TupleHeader (version_store.h:28-46), slot = [key][payload]
+    const uint32_t K = schema->key_size, P = schema->payload_size;
+    std::unordered_map<uint64_t, uint32_t> seen;   // TupleHeader* -> 1-based version index
+    std::vector<uint32_t> heads;
+    std::vector<stage_version_t> vers;
+    std::vector<uint8_t> vpay;
+    std::vector<uint64_t> path;
+    auto add_chain = [&](uint64_t head) -> uint32_t {
+        path.clear();
+        uint32_t tail = 0;
+        const uint32_t first = (uint32_t) vers.size() + 1;
+        for (uint64_t cur = head; cur != 0 && cur != UINT64_MAX;) {
+            auto it = seen.find(cur);
+            if (it != seen.end()) { tail = it->second; break; }      // joins a chain already staged (or a cycle)
+            seen.emplace(cur, first + (uint32_t) path.size());
+            path.push_back(cur);
+            memcpy(&cur, reinterpret_cast<const uint8_t *>(cur) + kThNext, 8);
+        }
+        for (size_t k = 0; k < path.size(); ++k) {
+            const uint8_t *hd = reinterpret_cast<const uint8_t *>(path[k]);
+            stage_version_t ver{};
+            uint64_t slot;
+            memcpy(&ver.begin_id, hd + kThBegin, 4);
+            memcpy(&ver.commit_id, hd + kThCommit, 4);
+            memcpy(&slot, hd + kThSlot, 8);
+            ver.next = k + 1 < path.size() ? first + (uint32_t) k + 1 : tail;
+            vers.push_back(ver);
+            const size_t at = vpay.size();
+            vpay.resize(at + P, 0);
+            if (slot != 0 && slot != UINT64_MAX) memcpy(vpay.data() + at, reinterpret_cast<const uint8_t *>(slot) + K, P);
+        }
+        return path.empty() ? tail : first;
+    };
+    for (size_t li = 0; li < w.leaves.size() && !rc; ++li) {
+        const uint8_t *leaf = w.leaves[li];
+        uint64_t status;
+        memcpy(&status, leaf + kOffStatus, 8);
+        const uint32_t count = status_record_count(status);
+        heads.assign(count, 0);
+        bool any = false;
+        for (uint32_t i = 0; i < count; ++i) {
+            uint64_t m, nx;
+            memcpy(&m, leaf + kOffMeta + (size_t) i * kMetaSize, 8);
+            memcpy(&nx, leaf + kOffMeta + (size_t) i * kMetaSize + kMetaNextPtr, 8);
+            if (!meta_visible(m) || nx == 0 || nx == UINT64_MAX) continue;
+            heads[i] = add_chain(nx);
+            any = true;
+        }
+        rc = stage_one_leaf(s, leaf, w.fences[li], w.fences[li] != nullptr, any ? heads.data() : nullptr);
+    }
+    if (!rc && !vers.empty()) rc = stage_gpu_snapshot_add_versions(s, vers.data(), vpay.data(), vers.size());
+    if (!rc) rc = stage_gpu_snapshot_seal(s);
+    if (rc) {
+        snapshot_free(s);
+        return rc;
+    }
+    *out = s;
+    return STAGE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// on-device YCSB table generation (consolidated leaves)
+// ------------------------------------------------------------------------------------------------
+extern "C" int stage_gpu_snapshot_generate_ycsb(const stage_schema_t *schema, uint64_t n_rows_total, uint64_t first_rank,
+                                                uint64_t n_local, uint32_t rows_per_leaf, stage_snapshot_t **out) {
+    if (!out || !schema || schema->key_size != 4 || rows_per_leaf == 0 || first_rank + n_local > n_rows_total ||
+        n_rows_total > 0xFFFFFFFFull)
+        return STAGE_ERR_ARG;
+    stage_snapshot *s = nullptr;
+    int rc = snapshot_new(schema, &s);
+    if (rc) return rc;
+    const uint64_t L = (n_local + rows_per_leaf - 1) / rows_per_leaf;
+    if ((rc = alloc_columns(s, std::max<uint64_t>(L, 1), n_local))) { snapshot_free(s); return rc; }
+    s->n_rows = n_local;
+    s->n_leaves = std::max<uint64_t>(L, 1);
+    s->max_leaf_rows = (uint32_t) std::min<uint64_t>(rows_per_leaf, n_local);
+    GenArgs g{};
+    g.n_total = n_rows_total; g.first_rank = first_rank; g.n_local = n_local; g.rows_per_leaf = rows_per_leaf;
+    g.n_leaves = s->n_leaves; g.payload_size = schema->payload_size;
+    g.skey = s->d_skey; g.slot = s->d_slot; g.ts = s->d_ts; g.chain = s->d_chain; g.payload = s->d_payload;
+    g.leaf_off = s->d_leaf_off; g.sep = s->d_sep; g.cont = s->d_cont;
+    auto fail = [&](int code) { snapshot_free(s); return code; };
+    {
+        const unsigned blocks = (unsigned) std::min<uint64_t>((n_local + 255) / 256 + 1, 148ull * 32);
+        generate_ycsb_meta_kernel<<<blocks, 256, 0, s->stream>>>(g);
+        g_launches++;
+        if (cudaGetLastError() != cudaSuccess) return fail(STAGE_ERR_CUDA);
+        generate_ycsb_payload_kernel<<<148 * 8, 256, 0, s->stream>>>(g);
+        g_launches++;
+        if (cudaGetLastError() != cudaSuccess) return fail(STAGE_ERR_CUDA);
+    }
+    if ((rc = finish_seal(s))) return fail(rc);
+    *out = s;
+    return STAGE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// info / lifecycle
+// ------------------------------------------------------------------------------------------------
+extern "C" int stage_gpu_init(int device) {
+    int n = 0;
+    CUDA_TRY(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return STAGE_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(device));
+    g_device = device;
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_info(const stage_snapshot_t *s, stage_snapshot_info_t *info) {
+    if (!s || !info) return STAGE_ERR_ARG;
+    info->n_rows = s->n_rows;
+    info->n_leaves = s->n_leaves;
+    info->n_versions = s->n_versions;
+    info->device_bytes = s->device_bytes;
+    info->key_words = (uint32_t) s->nw;
+    info->n_levels = (uint32_t) s->view.n_levels;
+    info->max_leaf_rows = s->max_leaf_rows;
+    info->device = (uint32_t) s->device;
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_destroy(stage_snapshot_t *s) {
+    if (!s) return STAGE_ERR_ARG;
+    cudaSetDevice(s->device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    snapshot_free(s);
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_set_stream(stage_snapshot_t *s, void *cuda_stream) {
+    if (!s) return STAGE_ERR_ARG;
+    if (s->own_stream && s->stream) {
+        cudaStreamSynchronize(s->stream);
+        cudaStreamDestroy(s->stream);
+    }
+    s->stream = static_cast<cudaStream_t>(cuda_stream);
+    s->own_stream = false;
+    return STAGE_OK;
+}
+extern "C" void *stage_gpu_snapshot_get_stream(const stage_snapshot_t *s) { return s ? (void *) s->stream : nullptr; }
+
+// ------------------------------------------------------------------------------------------------
+// reads
+// ------------------------------------------------------------------------------------------------
+static int g_sm_count = 0;
+static int sm_count() {
+    if (!g_sm_count) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+        if (g_sm_count <= 0) g_sm_count = 148;
+    }
+    return g_sm_count;
+}
+
+template <int NW>
+static int launch_probe(stage_snapshot *s, const ProbeArgs &a) {
+    if (a.n == 0) return STAGE_OK;
+    const size_t smem = (size_t) s->view.smem_words * 4;
+    const uint64_t tiles = (a.n + 31) / 32;
+    const uint64_t want_blocks = (tiles + 7) / 8;
+    const unsigned blocks = (unsigned) std::min<uint64_t>(want_blocks, (uint64_t) sm_count() * 8);
+    probe_kernel<NW, 4><<<blocks, 256, smem, s->stream>>>(s->view, a);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
+static int probe_device(stage_snapshot *s, const ProbeArgs &a) {
+    switch (s->nw) {
+        case 1: return launch_probe<1>(s, a);
+        case 2: return launch_probe<2>(s, a);
+        case 4: return launch_probe<4>(s, a);
+        default: return launch_probe<8>(s, a);
+    }
+}
+
+extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
+                                     uint32_t *ts, void *key_out, void *payload_out, int flags) {
+    if (!s || (n && !keys)) return STAGE_ERR_ARG;
+    if (!s->sealed) return STAGE_ERR_STATE;
+    std::lock_guard<std::mutex> lock(s->mu);
+    CUDA_TRY(cudaSetDevice(s->device));
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    ProbeArgs a{};
+    a.n = n;
+    a.read_ts = read_ts;
+    if (flags & STAGE_IO_DEVICE) {
+        a.keys = static_cast<const uint8_t *>(keys);
+        a.found = found; a.ts_out = ts;
+        a.key_out = static_cast<uint8_t *>(key_out);
+        a.payload_out = static_cast<uint8_t *>(payload_out);
+        return probe_device(s, a);
+    }
+    // host I/O: chunked so the device scratch stays bounded (<= 256 Ki probes per chunk)
+    const uint64_t chunk = 1ull << 18;
+    int rc;
+    if ((rc = s->sc_keys.ensure(std::min(n, chunk) * K))) return rc;
+    if (found && (rc = s->sc_found.ensure(std::min(n, chunk)))) return rc;
+    if (ts && (rc = s->sc_ts.ensure(std::min(n, chunk) * 4))) return rc;
+    if (key_out && (rc = s->sc_keyout.ensure(std::min(n, chunk) * K))) return rc;
+    if (payload_out && (rc = s->sc_payload.ensure(std::min(n, chunk) * (uint64_t) P))) return rc;
+    for (uint64_t b = 0; b < n; b += chunk) {
+        const uint64_t m = std::min(chunk, n - b);
+        CUDA_TRY(cudaMemcpyAsync(s->sc_keys.p, static_cast<const uint8_t *>(keys) + b * K, m * K, cudaMemcpyHostToDevice,
+                                 s->stream));
+        // rows of missed probes are left untouched in the caller's buffer: start from its content
+        if (key_out) CUDA_TRY(cudaMemsetAsync(s->sc_keyout.p, 0, m * K, s->stream));
+        a.keys = static_cast<const uint8_t *>(s->sc_keys.p);
+        a.n = m;
+        a.found = found ? static_cast<uint8_t *>(s->sc_found.p) : nullptr;
+        a.ts_out = ts ? static_cast<uint32_t *>(s->sc_ts.p) : nullptr;
+        a.key_out = key_out ? static_cast<uint8_t *>(s->sc_keyout.p) : nullptr;
+        a.payload_out = payload_out ? static_cast<uint8_t *>(s->sc_payload.p) : nullptr;
+        if (payload_out) CUDA_TRY(cudaMemsetAsync(s->sc_payload.p, 0, m * (uint64_t) P, s->stream));
+        if ((rc = probe_device(s, a))) return rc;
+        if (found) CUDA_TRY(cudaMemcpyAsync(found + b, s->sc_found.p, m, cudaMemcpyDeviceToHost, s->stream));
+        if (ts) CUDA_TRY(cudaMemcpyAsync(ts + b, s->sc_ts.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
+        if (key_out)
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(key_out) + b * K, s->sc_keyout.p, m * K, cudaMemcpyDeviceToHost,
+                                     s->stream));
+        if (payload_out)
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(payload_out) + b * (uint64_t) P, s->sc_payload.p,
+                                     m * (uint64_t) P, cudaMemcpyDeviceToHost, s->stream));
+        CUDA_TRY(cudaStreamSynchronize(s->stream));
+    }
+    return STAGE_OK;
+}
+
+template <int NW>
+static int launch_scan(stage_snapshot *s, const ScanArgs &a) {
+    if (a.n == 0) return STAGE_OK;
+    const size_t smem = (size_t) std::max<uint32_t>(s->view.max_leaf_rows, 1) * 2;
+    if (smem > 48 * 1024)
+        CUDA_TRY(cudaFuncSetAttribute(scan_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    const unsigned blocks = (unsigned) std::min<uint64_t>(a.n, (uint64_t) sm_count() * 64);
+    scan_kernel<NW><<<blocks, kScanThreads, smem, s->stream>>>(s->view, a);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
+static int scan_device(stage_snapshot *s, const ScanArgs &a) {
+    switch (s->nw) {
+        case 1: return launch_scan<1>(s, a);
+        case 2: return launch_scan<2>(s, a);
+        case 4: return launch_scan<4>(s, a);
+        default: return launch_scan<8>(s, a);
+    }
+}
+
+extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
+                                    uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts,
+                                    void *key_out, uint32_t *ts_out, void *payload_out, int flags) {
+    if (!s || (n && (!start_keys || !scan_sizes || !row_counts))) return STAGE_ERR_ARG;
+    if (!s->sealed) return STAGE_ERR_STATE;
+    std::lock_guard<std::mutex> lock(s->mu);
+    CUDA_TRY(cudaSetDevice(s->device));
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    ScanArgs a{};
+    a.out_stride = out_stride;
+    a.read_ts = read_ts;
+    a.apply_visibility = apply_visibility;
+    if (flags & STAGE_IO_DEVICE) {
+        a.start_keys = static_cast<const uint8_t *>(start_keys);
+        a.scan_sizes = scan_sizes;
+        a.n = n;
+        a.row_counts = row_counts;
+        a.key_out = static_cast<uint8_t *>(key_out);
+        a.ts_out = ts_out;
+        a.payload_out = static_cast<uint8_t *>(payload_out);
+        return scan_device(s, a);
+    }
+    for (uint64_t i = 0; i < n; ++i)
+        if (scan_sizes[i] > out_stride) return STAGE_ERR_ARG;
+    // host I/O: chunks of scans so that the result scratch stays <= ~1 GiB
+    const uint64_t row_bytes = (uint64_t) P + K + 4;
+    uint64_t chunk = std::max<uint64_t>(1, (1ull << 30) / std::max<uint64_t>(1, row_bytes * out_stride));
+    chunk = std::min<uint64_t>(chunk, std::max<uint64_t>(n, 1));
+    int rc;
+    if ((rc = s->sc_keys.ensure(chunk * K)) || (rc = s->sc_sizes.ensure(chunk * 4)) || (rc = s->sc_counts.ensure(chunk * 4)))
+        return rc;
+    if (key_out && (rc = s->sc_keyout.ensure(chunk * out_stride * K))) return rc;
+    if (ts_out && (rc = s->sc_ts.ensure(chunk * out_stride * 4))) return rc;
+    if (payload_out && (rc = s->sc_payload.ensure(chunk * out_stride * (uint64_t) P))) return rc;
+    for (uint64_t b = 0; b < n; b += chunk) {
+        const uint64_t m = std::min(chunk, n - b);
+        const uint64_t rows = m * out_stride;
+        CUDA_TRY(cudaMemcpyAsync(s->sc_keys.p, static_cast<const uint8_t *>(start_keys) + b * K, m * K,
+                                 cudaMemcpyHostToDevice, s->stream));
+        CUDA_TRY(cudaMemcpyAsync(s->sc_sizes.p, scan_sizes + b, m * 4, cudaMemcpyHostToDevice, s->stream));
+        if (key_out) CUDA_TRY(cudaMemsetAsync(s->sc_keyout.p, 0, rows * K, s->stream));
+        if (ts_out) CUDA_TRY(cudaMemsetAsync(s->sc_ts.p, 0, rows * 4, s->stream));
+        if (payload_out) CUDA_TRY(cudaMemsetAsync(s->sc_payload.p, 0, rows * (uint64_t) P, s->stream));
+        a.start_keys = static_cast<const uint8_t *>(s->sc_keys.p);
+        a.scan_sizes = static_cast<const uint32_t *>(s->sc_sizes.p);
+        a.n = m;
+        a.row_counts = static_cast<uint32_t *>(s->sc_counts.p);
+        a.key_out = key_out ? static_cast<uint8_t *>(s->sc_keyout.p) : nullptr;
+        a.ts_out = ts_out ? static_cast<uint32_t *>(s->sc_ts.p) : nullptr;
+        a.payload_out = payload_out ? static_cast<uint8_t *>(s->sc_payload.p) : nullptr;
+        if ((rc = scan_device(s, a))) return rc;
+        CUDA_TRY(cudaMemcpyAsync(row_counts + b, s->sc_counts.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
+        const uint64_t rb = b * out_stride;
+        if (key_out)
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(key_out) + rb * K, s->sc_keyout.p, rows * K,
+                                     cudaMemcpyDeviceToHost, s->stream));
+        if (ts_out) CUDA_TRY(cudaMemcpyAsync(ts_out + rb, s->sc_ts.p, rows * 4, cudaMemcpyDeviceToHost, s->stream));
+        if (payload_out)
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(payload_out) + rb * (uint64_t) P, s->sc_payload.p,
+                                     rows * (uint64_t) P, cudaMemcpyDeviceToHost, s->stream));
+        CUDA_TRY(cudaStreamSynchronize(s->stream));
+    }
+    return STAGE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// routing (host): owner = number of splitters < key, in reference key order
+// ------------------------------------------------------------------------------------------------
+extern "C" int stage_gpu_route(const stage_schema_t *schema, const void *splitters, uint32_t n_shards, const void *keys,
+                               uint64_t n, uint32_t *owner) {
+    int nw;
+    uint32_t xm;
+    int rc = schema_check(schema, &nw, &xm);
+    if (rc) return rc;
+    if (n_shards == 0 || (n && (!keys || !owner)) || (n_shards > 1 && !splitters)) return STAGE_ERR_ARG;
+    const uint32_t K = schema->key_size;
+    std::vector<uint32_t> sp((size_t) (n_shards - 1) * nw);
+    for (uint32_t i = 0; i + 1 < n_shards; ++i)
+        host_sortable_nw(nw, static_cast<const uint8_t *>(splitters) + (size_t) i * K, K, xm, sp.data() + (size_t) i * nw);
+    std::vector<uint32_t> k(nw);
+    for (uint64_t i = 0; i < n; ++i) {
+        host_sortable_nw(nw, static_cast<const uint8_t *>(keys) + i * K, K, xm, k.data());
+        uint32_t lo = 0, hi = n_shards - 1;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            const uint32_t *sm = sp.data() + (size_t) mid * nw;
+            bool less = false;                       // splitter[mid] < key ?
+            for (int w = 0; w < nw; ++w)
+                if (sm[w] != k[w]) { less = sm[w] < k[w]; break; }
+            if (less) lo = mid + 1; else hi = mid;
+        }
+        owner[i] = lo;
+    }
+    return STAGE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// utilities
+// ------------------------------------------------------------------------------------------------
+extern "C" void *stage_gpu_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+    return p;
+}
+extern "C" void stage_gpu_host_free(void *p) {
+    if (p) cudaFreeHost(p);
+}
+extern "C" uint64_t stage_gpu_launch_count(void) { return g_launches.load(); }
+extern "C" const char *stage_gpu_strerror(int status) {
+    switch (status) {
+        case STAGE_OK: return "ok";
+        case STAGE_ERR_ARG: return "bad argument or unsupported schema";
+        case STAGE_ERR_CUDA: return "CUDA error";
+        case STAGE_ERR_NOT_QUIESCED: return "tree not quiesced (frozen node or in-flight record)";
+        case STAGE_ERR_STATE: return "call order";
+        case STAGE_ERR_NOMEM: return "out of memory";
+        case STAGE_ERR_LAYOUT: return "node bytes are not a Stage BzTree node";
+        default: return "unknown";
+    }
+}
+extern "C" const char *stage_gpu_last_error(void) { return g_last_error.c_str(); }

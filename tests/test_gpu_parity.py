@@ -1,0 +1,143 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU checker on identical tables and
+key streams. Bit-exact: found flags, commit ids, key bytes, payload bytes, scan row order and counts."""
+import numpy as np
+import pytest
+
+import stage_indexorganized_b200 as sg
+from helpers import assert_probe_equal, assert_scan_equal, random_table, u32_keys, ycsb_int_table
+from oracle import pyoracle
+
+pytestmark = pytest.mark.gpu
+
+
+def checker_classes():
+    cls = [pyoracle.OracleTable]
+    if pyoracle.have_ref():
+        cls.append(pyoracle.RefTable)      # the unmodified reference, when its prebuilt library travelled
+    return cls
+
+
+@pytest.fixture(scope="module", params=checker_classes(), ids=lambda c: c.__name__)
+def ycsb10k(request):
+    t = ycsb_int_table(request.param, 10000)
+    snap = sg.Snapshot.from_tree(t.root, 4, 1000)
+    yield t, snap
+    snap.close()
+
+
+def test_snapshot_shape(ycsb10k):
+    t, snap = ycsb10k
+    info = snap.info()
+    assert info.n_rows == 10000
+    leaves, _, _ = pyoracle.walk_tree(t.root)
+    assert info.n_leaves == len(leaves)
+    assert info.n_versions == 0
+
+
+def test_probe_config1_uniform(ycsb10k):
+    """BASELINE config #1 key stream: uniform 1..N (key N misses), read_ts = 1."""
+    t, snap = ycsb10k
+    keys = u32_keys(pyoracle.uniform_keys(10000, 1 << 16, seed=1))
+    assert_probe_equal(snap.probe(keys, 1), t.probe(keys, 1), "uniform")
+
+
+def test_probe_zipf_and_misses(ycsb10k):
+    t, snap = ycsb10k
+    z = pyoracle.Zipf(9999, 0.2, seed=1).draw(20000).astype(np.uint32)
+    miss = np.array([10000, 10001, 0xFFFFFFFF, 0x80808080, 70000], np.uint32)
+    keys = u32_keys(np.concatenate([z, miss, np.arange(0, 300, dtype=np.uint32)]))
+    got, want = snap.probe(keys, 1), t.probe(keys, 1)
+    assert_probe_equal(got, want, "zipf+miss")
+    assert got[0][20000:20005].sum() == 0
+
+
+def test_probe_empty_and_ragged_batches(ycsb10k):
+    t, snap = ycsb10k
+    for n in (0, 1, 31, 33, 255):
+        keys = u32_keys(np.arange(n, dtype=np.uint32) * 7)
+        assert_probe_equal(snap.probe(keys, 0), t.probe(keys, 0), f"n={n}")
+
+
+@pytest.mark.parametrize("scan_size", [1, 10, 100, 1000])
+@pytest.mark.parametrize("vis", [0, 1])
+def test_scan_ycsb(ycsb10k, scan_size, vis):
+    t, snap = ycsb10k
+    n = 256 if scan_size < 1000 else 64
+    sk = u32_keys(pyoracle.uniform_keys(10000, n, seed=3))
+    assert_scan_equal(snap.scan(sk, scan_size, 1, vis), t.scan(sk, scan_size, 1, vis), f"S={scan_size}")
+
+
+def test_scan_edges(ycsb10k):
+    """start keys below the smallest / above the largest key, absent keys, ragged sizes."""
+    t, snap = ycsb10k
+    sk = u32_keys(np.array([32896, 0x80808080, 0x7F7F7F7F, 9999, 10000, 98175, 0, 5, 123456], np.uint32))
+    sizes = np.array([5, 1000, 7, 3, 50, 9, 1, 64, 33], np.uint32)
+    assert_scan_equal(snap.scan(sk, sizes, 1, 0), t.scan(sk, sizes, 1, 0), "edges")
+    assert_scan_equal(snap.scan(sk, sizes, 1, 1), t.scan(sk, sizes, 1, 1), "edges/vis")
+
+
+@pytest.mark.parametrize("cls", checker_classes(), ids=lambda c: c.__name__)
+@pytest.mark.parametrize("key_size,payload", [(16, 400), (32, 64), (8, 96), (16, 1000)])
+def test_other_key_shapes(cls, key_size, payload):
+    """memcmp-ordered 16/32-byte keys (YCSB string, TPC-C stock / order_line) and 8-byte signed keys."""
+    t, keys, pay = random_table(cls, 3000, key_size, payload, seed=key_size + payload)
+    with sg.Snapshot.from_tree(t.root, key_size, payload) as snap:
+        rng = np.random.default_rng(5)
+        probe = np.concatenate([keys[rng.integers(0, len(keys), 4000)],
+                                rng.integers(0, 256, size=(500, key_size), dtype=np.uint8)])
+        assert_probe_equal(snap.probe(probe, 1), t.probe(probe, 1), "probe")
+        sk = probe[:200]
+        for S in (10, 150):
+            assert_scan_equal(snap.scan(sk, S, 1, 0), t.scan(sk, S, 1, 0), f"scan S={S}")
+
+
+@pytest.mark.parametrize("cls", checker_classes(), ids=lambda c: c.__name__)
+def test_mvcc_chains_and_deletes(cls):
+    """Committed updates create TupleHeader chains; deletes leave leaves whose max key is not the
+    separator (iterator stops early). Reads at timestamps straddling the commit ids."""
+    N, P = 6000, 1000
+    t = ycsb_int_table(cls, N, P)
+    rng = np.random.default_rng(11)
+    cid = 10
+    for k in rng.integers(0, N, 1500):
+        newp = np.full(P, cid % 251, np.uint8)
+        assert t.commit_update(u32_keys([k])[0], newp, cid) == 0
+        cid += 1
+    for k in rng.choice(N, 300, replace=False):
+        t.delete(u32_keys([k])[0])
+    with sg.Snapshot.from_tree(t.root, 4, P) as snap:
+        assert snap.info().n_versions >= 1500
+        keys = u32_keys(rng.integers(0, N + 10, 8000))
+        sk = u32_keys(rng.integers(0, N, 200))
+        for read_ts in (0, 1, 9, 10, 500, 760, 1509, 1510, 4000):
+            assert_probe_equal(snap.probe(keys, read_ts), t.probe(keys, read_ts), f"ts={read_ts}")
+            for S in (10, 200):
+                for vis in (0, 1):
+                    assert_scan_equal(snap.scan(sk, S, read_ts, vis), t.scan(sk, S, read_ts, vis),
+                                      f"ts={read_ts} S={S} vis={vis}")
+
+
+def test_generated_ycsb_matches_row_function():
+    """On-device table generation (stage_gpu_snapshot_generate_ycsb): probes must agree with a tree the
+    checker loads normally (probe results do not depend on the tree shape)."""
+    N = 50000
+    t = ycsb_int_table(pyoracle.OracleTable, N)
+    with sg.Snapshot.generate_ycsb(N, 1000, rows_per_leaf=61) as snap:
+        assert snap.info().n_rows == N
+        keys = u32_keys(pyoracle.uniform_keys(N, 30000, seed=9))
+        assert_probe_equal(snap.probe(keys, 1), t.probe(keys, 1), "generated")
+        # consolidated leaves: a scan is the next S keys in reference order
+        k = np.arange(N, dtype=np.uint32)
+        order = k[np.argsort(k.byteswap() ^ np.uint32(0x80808080), kind="stable")]
+        pos = {int(v): i for i, v in enumerate(order)}
+        sk = keys[:64]
+        counts, key_out, ts, pay = snap.scan(sk, 100, 1, 1)
+        for i in range(64):
+            p = pos[int(sk[i].view(np.uint32)[0])] if int(sk[i].view(np.uint32)[0]) < N else None
+            if p is None:
+                continue
+            want = order[p:p + 100]
+            assert counts[i] == len(want)
+            assert np.array_equal(key_out[i, :counts[i]].view(np.uint32).ravel(), want)
+            assert np.array_equal(pay[i, :counts[i], 0], (want & 0xFF).astype(np.uint8))
+            assert np.array_equal(pay[i, :counts[i], 999], (want & 0xFF).astype(np.uint8))

@@ -1,0 +1,397 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the index-organized read path on B200.
+
+Workload (BASELINE.json configs[1]): YCSB int table (4-byte keys, 1000-byte payload), 10 M tuples per
+GPU, 10 % of rows overwritten by committed updates (version chains), scan_mode range scans of 1000
+rows with the MVCC visibility filter (IndexScanExecutor range semantics) at a read timestamp in the
+middle of the update commit ids. A "step" = one batch of `--scans` scans through the scan kernel.
+Secondary leg in the same JSON line ("probe"): batches of 2^20 uniform point probes on the same table.
+
+  value     rows/s, whole job (all ranks), inputs and outputs resident in HBM, CUDA-event timed
+  e2e       the same metric through the host-buffer C ABI call (pinned host start keys in, pinned host
+            rows out; the H2D/D2H copies are inside the timed region)
+  roofline  algorithmic bytes of the scan kernel / its CUDA-event duration vs the measured HBM copy peak
+  cpu_baseline  the reference's own CPU path (oracle/_ref when its prebuilt library is present, else
+            the C port) on this box's host cores over a bounded sample of the same scans
+
+`--impl reference` times that CPU path alone, with every host thread, on the same metric/config.
+
+N > 1 (torchrun, one rank per GPU): the table is range-partitioned in reference key order; every rank
+holds 10 M tuples (weak scaling) built on the device by stage_gpu_snapshot_generate_ycsb plus a halo of
+the next shard's first rows, scans run shard-local (no data-path collective), probes are routed to
+their owning shard with an NCCL all-to-all (keys out, results back).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+K_BYTES, P_BYTES = 4, 1000
+ROW_ALGO_BYTES = 2 * (K_BYTES + P_BYTES + 4)       # record read + result write per emitted row
+PROBE_HIT_BYTES = K_BYTES + 2 * (K_BYTES + P_BYTES + 4)
+PROBE_MISS_BYTES = K_BYTES + 1
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=10_000_000, help="tuples per GPU")
+    ap.add_argument("--scans", type=int, default=4096, help="scans per step per GPU")
+    ap.add_argument("--scan-size", type=int, default=1000)
+    ap.add_argument("--probes", type=int, default=1 << 20, help="probes per probe step per GPU")
+    ap.add_argument("--e2e-scans", type=int, default=1024)
+    ap.add_argument("--cpu-scans", type=int, default=0, help="scans in the CPU-baseline sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--generated", action="store_true", help="force the on-device table generator at N=1")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ----------------------------------------------------------------------------------------------
+# clocks sampling during the timed region
+# ----------------------------------------------------------------------------------------------
+class ClockSampler:
+    def __init__(self, index):
+        self.samples, self.reasons, self.stop = [], set(), False
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+        self.t = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                 "hw_power_brake": 0x80}
+        while not self.stop:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(
+                    nv, "nvmlDeviceGetCurrentClocksEventReasons") else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def __enter__(self):
+        if self.nv:
+            self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        if self.nv:
+            self.t.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+# ----------------------------------------------------------------------------------------------
+# input table (host tree in the reference's byte format) and CPU baseline — the only users of oracle/
+# ----------------------------------------------------------------------------------------------
+def build_host_table(rows, updates):
+    """The YCSB table exactly as the reference's loader builds it (single loader thread), then
+    `updates` committed single-row updates with commit ids 10..10+updates-1 (keys uniform, seed 2)."""
+    from oracle import pyoracle
+    pyoracle.build_oracle()
+    if pyoracle.have_ref():
+        t, kind = pyoracle.RefTable(P_BYTES, leaf_pool_blocks=max(rows // 20, 4096)), "reference"
+    else:
+        t, kind = pyoracle.OracleTable(P_BYTES), "port"
+    assert t.load_ycsb_int(0, rows) == rows
+    if updates:
+        uk = pyoracle.uniform_keys(rows, updates, seed=2) - 1         # existing keys 0..rows-1
+        uk = uk.astype(np.uint32).view(np.uint8).reshape(-1, 4)
+        assert t.commit_update_batch(uk, 10) == updates
+    return t, kind
+
+
+def cpu_scan_sample(table, start_keys, scan_size, read_ts, threads):
+    sec, rows = table.time_scan(start_keys, scan_size, read_ts, 1, threads, pin=True)
+    return rows / sec, rows, sec
+
+
+def scan_start_keys(rows, n, seed):
+    from oracle import pyoracle
+    return (pyoracle.uniform_keys(rows, n, seed=seed) - 1).astype(np.uint32)
+
+
+# ----------------------------------------------------------------------------------------------
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU path, all host threads, bounded sample per step."""
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    rows = args.rows
+    updates = rows // 10
+    read_ts = 10 + updates // 2
+    table, kind = build_host_table(rows, updates)
+    n = args.cpu_scans or max(threads * 64, 512)
+    times, total_rows = [], 0
+    for step in range(args.warmup + args.steps):
+        sk = scan_start_keys(rows, n, seed=100 + step).view(np.uint8).reshape(-1, 4)
+        rps, r, sec = cpu_scan_sample(table, sk, args.scan_size, read_ts, threads)
+        if step >= args.warmup:
+            times.append(sec)
+            total_rows += r
+    value = total_rows / sum(times)
+    line = {
+        "impl": "reference", "metric": "YCSB scan rows/s (1000-row MVCC range scans, 10M-tuple int table)",
+        "value": value, "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": workload_config(args, world=1, table="reference loader (host tree)"),
+        "cpu_baseline": {"value": value, "unit": "rows/s", "cores": threads, "kind": kind,
+                         "sample": f"{n} scans x {args.scan_size} rows per step, {args.steps} steps, {threads} pinned threads"},
+        "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, world, table):
+    return {"workload": "BASELINE configs[1]: YCSB scan_mode (-n) range scan with MVCC visibility, int keys, "
+                        f"{args.rows} tuples per GPU, scan_size {args.scan_size}",
+            "rows_per_gpu": args.rows, "payload_bytes": P_BYTES, "key_bytes": K_BYTES,
+            "scans_per_step_per_gpu": args.scans, "scan_size": args.scan_size,
+            "probes_per_step_per_gpu": args.probes, "updates_per_gpu": args.rows // 10,
+            "read_ts": "middle of the update commit ids", "table": table,
+            "partitioning": f"range x{world}" if world > 1 else "single shard",
+            "l2": "inputs larger than L2 (table >= 10 GB, 4 GB of rows written per step); no explicit flush"}
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import stage_indexorganized_b200 as sg
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    sg.init(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        dist.init_process_group("nccl", device_id=dev)
+
+    rows, S, n_scans, n_probes = args.rows, args.scan_size, args.scans, args.probes
+    updates = rows // 10
+    use_generated = world > 1 or args.generated
+    host_table, table_kind = None, None
+    t_build0 = time.time()
+    if use_generated:
+        halo = 2 * S + 128
+        total = rows * world
+        first = rank * rows
+        n_local = min(rows + (halo if rank + 1 < world else 0), total - first)
+        snap = sg.Snapshot.generate_ycsb(total, P_BYTES, rows_per_leaf=61, first_rank=first, n_local=n_local)
+        read_ts = 1
+        table_desc = "generated on device (consolidated leaves, 61 rows/leaf, no version chains)"
+    else:
+        host_table, table_kind = build_host_table(rows, updates)
+        snap = sg.Snapshot.from_tree(host_table.root, K_BYTES, P_BYTES)
+        read_ts = 10 + updates // 2
+        table_desc = f"host tree built by the reference loader ({table_kind}), flattened by the transform kernel"
+    t_build = time.time() - t_build0
+    info = snap.info()
+    stream = torch.cuda.current_stream()
+    snap.set_stream(stream.cuda_stream)
+
+    # ---- device-resident inputs / outputs -------------------------------------------------------
+    n_batches = args.warmup + args.steps
+    if use_generated:
+        from stage_indexorganized_b200.ycsb import rank_to_key
+        rng = np.random.default_rng(1000 + rank)
+        sk_all = rank_to_key(rows * world, rank * rows + rng.integers(0, rows, size=(n_batches, n_scans)))
+        pk_all = rng.integers(0, rows * world + 1, size=(n_batches, n_probes)).astype(np.uint32)
+    else:
+        from oracle import pyoracle  # input key streams come from the reference's generators (FastRandom)
+        sk_all = np.stack([scan_start_keys(rows, n_scans, seed=100 + b) for b in range(n_batches)])
+        pk_all = np.stack([pyoracle.uniform_keys(rows, n_probes, seed=200 + b) for b in range(n_batches)])
+    d_sk = torch.from_numpy(sk_all.astype(np.uint32).view(np.int32)).to(dev)
+    d_sizes = torch.full((n_scans,), S, dtype=torch.int32, device=dev)
+    d_counts = torch.zeros((n_batches, n_scans), dtype=torch.int32, device=dev)
+    d_keyout = torch.empty((n_scans * S,), dtype=torch.int32, device=dev)
+    d_tsout = torch.empty((n_scans * S,), dtype=torch.int32, device=dev)
+    d_payout = torch.empty((n_scans * S * P_BYTES,), dtype=torch.uint8, device=dev)
+
+    def scan_step(b):
+        snap.scan_device(d_sk[b], d_sizes, n_scans, S, read_ts, 1, d_counts[b], d_keyout, d_tsout, d_payout)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for b in range(args.warmup):
+        scan_step(b)
+    barrier()
+    launches0 = sg.launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    with ClockSampler(local_rank) as clk:
+        ev[0].record(stream)
+        for i in range(args.steps):
+            scan_step(args.warmup + i)
+            ev[i + 1].record(stream)
+        barrier()
+    launches = sg.launch_count() - launches0
+    step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    total_ms = ev[0].elapsed_time(ev[-1])
+    rows_emitted = int(d_counts[args.warmup:].sum().item())
+
+    # ---- probe leg (device resident) ------------------------------------------------------------
+    probe = None
+    if world == 1:
+        d_pk = torch.from_numpy(pk_all.view(np.int32)).to(dev)
+        d_found = torch.zeros((n_batches, n_probes), dtype=torch.uint8, device=dev)
+        d_pts = torch.empty((n_probes,), dtype=torch.int32, device=dev)
+        d_pkey = torch.empty((n_probes,), dtype=torch.int32, device=dev)
+        d_ppay = d_payout[: n_probes * P_BYTES] if n_probes <= n_scans * S else torch.empty(
+            (n_probes * P_BYTES,), dtype=torch.uint8, device=dev)
+        for b in range(args.warmup):
+            snap.probe_device(d_pk[b], n_probes, read_ts, d_found[b], d_pts, d_pkey, d_ppay)
+        torch.cuda.synchronize()
+        pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        pe0.record(stream)
+        for i in range(args.steps):
+            b = args.warmup + i
+            snap.probe_device(d_pk[b], n_probes, read_ts, d_found[b], d_pts, d_pkey, d_ppay)
+        pe1.record(stream)
+        torch.cuda.synchronize()
+        pms = pe0.elapsed_time(pe1)
+        hits = int(d_found[args.warmup:].sum().item())
+        nprobe = args.steps * n_probes
+        peak, peak_src = peaks()
+        pbytes = hits * PROBE_HIT_BYTES + (nprobe - hits) * PROBE_MISS_BYTES
+        probe = {"value": nprobe / (pms * 1e-3), "unit": "probes/s", "ms_per_step": pms / args.steps,
+                 "hit_rate": hits / nprobe,
+                 "roofline": {"bound": "hbm", "achieved": pbytes / (pms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                              "frac": pbytes / (pms * 1e-3) / 1e9 / peak, "traffic": None}}
+
+    # ---- max over ranks, whole-job aggregate ----------------------------------------------------
+    t_ms = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    r_sum = torch.tensor([rows_emitted], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(r_sum, op=dist.ReduceOp.SUM)
+    total_ms_max = float(t_ms.item())
+    rows_all = float(r_sum.item())
+    value = rows_all / (total_ms_max * 1e-3)
+
+    # ---- e2e: host buffers through the C ABI ----------------------------------------------------
+    ne = min(args.e2e_scans, n_scans)
+    h_sk = sg.PinnedArray((n_batches, ne, K_BYTES), np.uint8)
+    h_sk.array[:] = sk_all[:, :ne].astype(np.uint32).view(np.uint8).reshape(n_batches, ne, K_BYTES)
+    h_sizes = np.full(ne, S, np.uint32)
+    h_counts = sg.PinnedArray((ne,), np.uint32)
+    h_key = sg.PinnedArray((ne * S, K_BYTES), np.uint8)
+    h_ts = sg.PinnedArray((ne * S,), np.uint32)
+    h_pay = sg.PinnedArray((ne * S, P_BYTES), np.uint8)
+
+    def e2e_step(b):
+        sg._check(sg.lib().stage_gpu_scan_batch(snap.h, h_sk.array[b].ctypes.data, h_sizes.ctypes.data, ne, S, read_ts,
+                                                1, h_counts.ptr, h_key.ptr, h_ts.ptr, h_pay.ptr, sg.IO_HOST))
+        return int(h_counts.array.sum())
+
+    for b in range(min(args.warmup, 2)):
+        e2e_step(b)
+    barrier()
+    t0 = time.perf_counter()
+    e_rows = 0
+    for i in range(args.steps):
+        e_rows += e2e_step(args.warmup + i)
+    torch.cuda.synchronize()
+    e_sec = time.perf_counter() - t0
+    e_t = torch.tensor([e_sec], dtype=torch.float64, device=dev)
+    e_r = torch.tensor([e_rows], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(e_t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(e_r, op=dist.ReduceOp.SUM)
+    e2e = {"value": float(e_r.item()) / float(e_t.item()), "unit": "rows/s",
+           "h2d_bytes_per_step": ne * (K_BYTES + 4),
+           "d2h_bytes_per_step": ne * 4 + ne * S * (K_BYTES + 4 + P_BYTES),
+           "scans_per_step": ne}
+
+    # ---- CPU baseline (rank 0, N = 1) -----------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        if host_table is None:
+            host_table, table_kind = build_host_table(rows, updates)
+            cpu_ts = 10 + updates // 2
+        else:
+            cpu_ts = read_ts
+        threads = os.cpu_count() or 1
+        n_cpu = args.cpu_scans or max(threads * 256, 2048)
+        sk = scan_start_keys(rows, n_cpu, seed=100 + args.warmup).view(np.uint8).reshape(-1, 4)
+        rps, r, sec = cpu_scan_sample(host_table, sk, S, cpu_ts, threads)
+        cpu = {"value": rps, "unit": "rows/s", "cores": threads, "kind": table_kind,
+               "sample": f"{n_cpu} scans x {S} rows ({r} rows, {sec:.1f} s), {threads} pinned threads, same table"}
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        algo_bytes = rows_emitted * ROW_ALGO_BYTES + args.steps * n_scans * (K_BYTES + 8)
+        kern_ms = sum(step_ms)
+        achieved = algo_bytes / (kern_ms * 1e-3) / 1e9
+        line = {
+            "metric": "YCSB scan rows/s (1000-row MVCC range scans, 10M-tuple int table)",
+            "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": workload_config(args, world, table_desc),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src, "kernel": "stage::scan_kernel<1>",
+                         "algorithmic_bytes_per_launch": algo_bytes / args.steps,
+                         "launch_ms": kern_ms / args.steps},
+            "cpu_baseline": cpu,
+            "e2e": e2e,
+            "gpu_launches": int(launches),
+            "clocks": clk.summary(),
+            "probe": probe,
+            "snapshot": {"rows": int(info.n_rows), "leaves": int(info.n_leaves), "versions": int(info.n_versions),
+                         "hbm_bytes": int(info.device_bytes), "build_s": t_build},
+        }
+        print(json.dumps(line), flush=True)
+    snap.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -53,6 +53,7 @@ class _Table:
         self._load_int = self._fn("load_ycsb_int", C.c_int64, [_vp, _u64, _u64])
         self._delete = self._fn("delete", _i32, [_vp, _vp, _u32])
         self._commit_update = self._fn("commit_update", _i32, [_vp, _vp, _u32, _vp, _u32])
+        self._commit_update_batch = self._fn("commit_update_batch", C.c_int64, [_vp, _vp, _u32, _u64, _u32])
         self._root = self._fn("root", _vp, [_vp])
         self._probe = self._fn("probe", _i32, [_vp, _vp, _u32, _u64, _u32, _vp, _vp, _vp, _vp])
         self._scan = self._fn("scan", _i32, [_vp, _vp, _u32, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _vp, _vp])
@@ -87,6 +88,12 @@ class _Table:
         new_payload = np.ascontiguousarray(new_payload, np.uint8)
         assert new_payload.size == self.payload_size
         return self._commit_update(self.h, _ptr(key), key.size, _ptr(new_payload), commit_id)
+
+    def commit_update_batch(self, keys, first_commit_id):
+        """n committed YCSB-style updates (column 1 <- (uint8) commit id), commit ids first..first+n-1."""
+        keys = np.ascontiguousarray(keys, np.uint8)
+        n, ks = keys.shape
+        return self._commit_update_batch(self.h, _ptr(keys), ks, n, first_commit_id)
 
     @property
     def root(self):

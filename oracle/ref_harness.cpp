@@ -174,6 +174,29 @@ int ref_commit_update(ref_table *t, const void *key, uint32_t key_size, const vo
     return 0;
 }
 
+// n committed single-row updates: update i rewrites payload bytes [100,200) with (uint8)(first_cid+i) and
+// commits with id first_cid+i (the shape of the YCSB update transaction, ycsb_mixed.cpp:38-80, after commit).
+int64_t ref_commit_update_batch(ref_table *t, const void *keys, uint32_t key_size, uint64_t n, uint32_t first_cid) {
+    const char *k = static_cast<const char *>(keys);
+    const uint32_t P = t->payload_size;
+    std::vector<char> np_(P);
+    int64_t ok = 0;
+    for (uint64_t i = 0; i < n; ++i) {
+        LeafNode *leaf = t->tree->TraverseToLeaf(nullptr, k + i * key_size, (uint16_t) key_size);
+        if (!leaf) continue;
+        RecordMetadata *meta_ptr = nullptr;
+        ReturnCode rc = leaf->Read(k + i * key_size, (uint16_t) key_size, P, &meta_ptr, false);
+        if (!rc.IsOk() || !meta_ptr) continue;
+        char *rk = nullptr, *rp = nullptr;
+        leaf->GetRawRecord(*meta_ptr, &rk, &rp);
+        memcpy(np_.data(), rp, P);
+        uint32_t lo = P > 100 ? 100 : 0, hi = P > 200 ? 200 : P;
+        memset(np_.data() + lo, (int) ((first_cid + i) & 0xFF), hi - lo);
+        ok += ref_commit_update(t, k + i * key_size, key_size, np_.data(), first_cid + (uint32_t) i) == 0;
+    }
+    return ok;
+}
+
 const void *ref_root(ref_table *t) { return t->tree->GetRootNodeSafe(); }
 uint64_t ref_tuple_count(ref_table *t) { return t->tree->GetTupleCount(); }
 

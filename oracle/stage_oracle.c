@@ -499,6 +499,28 @@ int so_commit_update(so_tree *t, const void *key, uint32_t ks, const void *new_p
     return 0;
 }
 
+/* n committed single-row updates in a row: update i rewrites column 1 (payload bytes [100,200) clipped to
+ * the payload) with (uint8)(first_cid + i) and commits with id first_cid + i — the shape of the YCSB
+ * update transaction (benchmark/ycsb/ycsb_mixed.cpp:38-80) after commit. Returns updates applied. */
+int64_t so_commit_update_batch(so_tree *t, const void *keys, uint32_t ks, uint64_t n, uint32_t first_cid) {
+    const u8 *k = (const u8 *) keys;
+    uint32_t P = t->payload_size;
+    u8 *np_ = (u8 *) malloc(P);
+    int64_t ok = 0;
+    for (uint64_t i = 0; i < n; i++) {
+        u8 *leaf = traverse_to_leaf(t, NULL, k + i * ks, ks, 1);
+        int64_t s = leaf ? search_record_meta(leaf, k + i * ks, ks) : -1;
+        if (s < 0) continue;
+        uint64_t m = meta_at(leaf, (uint32_t) s)[0];
+        memcpy(np_, leaf + m_offset(m) + m_padlen(m), P);
+        uint32_t lo = P > 100 ? 100 : 0, hi = P > 200 ? 200 : P;
+        memset(np_ + lo, (int) ((first_cid + i) & 0xFF), hi - lo);
+        ok += so_commit_update(t, k + i * ks, ks, np_, first_cid + (uint32_t) i) == 0;
+    }
+    free(np_);
+    return ok;
+}
+
 /* ------------------------------------------------------------------------------------------ */
 /* a10: visibility rule + version chain (include/execute/executor.h:383-446, 465-534)          */
 /* UB branches at HEAD are given defined behaviour: emit the hit once.       */

@@ -106,7 +106,7 @@ def test_mvcc_chains_and_deletes(cls):
     for k in rng.choice(N, 300, replace=False):
         t.delete(u32_keys([k])[0])
     with sg.Snapshot.from_tree(t.root, 4, P) as snap:
-        assert snap.info().n_versions >= 1500
+        assert snap.info().n_versions >= 1000      # chains of deleted rows are not staged
         keys = u32_keys(rng.integers(0, N + 10, 8000))
         sk = u32_keys(rng.integers(0, N, 200))
         for read_ts in (0, 1, 9, 10, 500, 760, 1509, 1510, 4000):

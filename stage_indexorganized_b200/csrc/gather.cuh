@@ -1,0 +1,76 @@
+// gather.cuh — payload row gather: the kernel that moves >98 % of the bytes of both read operators.
+//
+// Replaces the per-row heap allocation + two memcpys of Record::New (include/vstore/b_tree.h:407-428)
+// and the executors' sizeof(T) copies (include/execute/executor.h:397, 476, 637): output row slot o
+// receives the payload row named by src_row[o] (a row of the flattened table, or — top bit set — a row
+// of the staged version table; kNoRow = nothing to copy, e.g. a missed probe or the unused tail of a
+// scan's output slab).
+//
+// HBM-bound streaming copy. One CTA handles kGatherRows consecutive output slots; each warp copies
+// kU rows at a time, issuing every load of the batch before the first store so that ~4 KB per warp
+// (32 KB per CTA, ~200 KB per SM) is in flight. Loads/stores are as wide as the row alignment allows
+// (YCSB rows are 1000 B => 8-byte aligned => 64-bit accesses, 256 B contiguous per warp instruction).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace stage {
+
+constexpr uint32_t kNoRow = 0xFFFFFFFFu;
+constexpr uint32_t kVersionRowFlag = 0x80000000u;   // src_row refers to ver_payload
+constexpr int kGatherRows = 64;                     // output slots per CTA
+constexpr int kGatherThreads = 256;
+
+struct GatherArgs {
+    const uint32_t *src_row;     // [n_slots]
+    uint64_t n_slots;
+    const uint8_t *payload;      // flattened table rows
+    const uint8_t *ver_payload;  // staged version rows
+    uint8_t *dst;                // [n_slots][P]
+    uint32_t payload_size;
+};
+
+template <typename V, int U>
+__global__ void __launch_bounds__(kGatherThreads) gather_rows_kernel(GatherArgs a) {
+    __shared__ uint32_t s_row[kGatherRows];
+    const uint64_t slot0 = (uint64_t) blockIdx.x * kGatherRows;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int kWarps = kGatherThreads / 32;
+    if (tid < kGatherRows) {
+        const uint64_t o = slot0 + tid;
+        s_row[tid] = o < a.n_slots ? __ldg(a.src_row + o) : kNoRow;
+    }
+    __syncthreads();
+    const uint32_t P = a.payload_size;
+    const uint32_t nvec = P / (uint32_t) sizeof(V);
+    // warp w takes rows w*U .. w*U+U-1, then (w+kWarps)*U ..., so that one warp's U rows are adjacent
+    for (int r0 = warp * U; r0 < kGatherRows; r0 += kWarps * U) {
+        const V *src[U];
+        V *dst[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint32_t row = s_row[r0 + u];
+            const uint8_t *base = (row & kVersionRowFlag) ? a.ver_payload : a.payload;
+            src[u] = row == kNoRow ? nullptr
+                                   : reinterpret_cast<const V *>(base + (uint64_t) (row & ~kVersionRowFlag) * P);
+            dst[u] = reinterpret_cast<V *>(a.dst + (slot0 + r0 + u) * P);
+        }
+        // 4 x U loads per lane are issued before the first store (K = 4 covers a 1000-byte row at 8 B/lane)
+        constexpr int K = 4;
+        for (uint32_t c0 = lane; c0 < nvec; c0 += 32 * K) {
+            V v[U][K];
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int k = 0; k < K; ++k)
+                    if (src[u] && c0 + 32 * k < nvec) v[u][k] = __ldcs(src[u] + c0 + 32 * k);
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int k = 0; k < K; ++k)
+                    if (src[u] && c0 + 32 * k < nvec) __stcs(dst[u] + c0 + 32 * k, v[u][k]);
+        }
+    }
+}
+
+}  // namespace stage

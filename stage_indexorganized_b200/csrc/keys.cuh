@@ -53,6 +53,12 @@ STAGE_HD SKey<NW> to_sortable(const uint8_t *key, uint32_t key_size, uint32_t xo
 // inverse: write the original key bytes
 template <int NW>
 STAGE_HD void from_sortable(const SKey<NW> &s, uint8_t *key, uint32_t key_size, uint32_t xormask) {
+    if (key_size == (uint32_t) NW * 4 && ((uintptr_t) key & 3u) == 0) {
+        uint32_t *k32 = reinterpret_cast<uint32_t *>(key);
+#pragma unroll
+        for (int i = 0; i < NW; ++i) k32[i] = bswap32(s.w[i] ^ xormask);
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < NW; ++i) {
         uint32_t v = s.w[i] ^ xormask;

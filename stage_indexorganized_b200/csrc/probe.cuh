@@ -8,12 +8,14 @@
 // route to" is exactly "the equal key in the globally sorted key column". The flattened column is
 // searched with a warp-cooperative 32-ary descent over sampled levels (level l+1 holds every 32nd
 // key of level l): each step is one coalesced 32-key load + ballot/popc. The top levels live in
-// shared memory; 4 probes are in flight per warp to overlap the L2/HBM latency of the lower levels.
-// Then the MVCC rule (executor.h:383-446) picks the in-leaf version or walks the staged chain, and
-// the warp copies the 1 KB payload rows with coalesced vector loads/stores.
+// shared memory; G probes are in flight per warp to overlap the L2/HBM latency of the lower levels.
+// Then the MVCC rule (executor.h:383-446) picks the in-leaf version or walks the staged chain. The
+// kernel emits found / commit id / key and the source row of every probe; gather_rows_kernel
+// (gather.cuh) then streams the payload rows.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "gather.cuh"
 #include "keys.cuh"
 
 namespace stage {
@@ -47,44 +49,29 @@ struct ProbeArgs {
     uint8_t *found;
     uint32_t *ts_out;
     uint8_t *key_out;
-    uint8_t *payload_out;
+    uint32_t *src_row;   // [n] row to gather (gather.cuh encoding), kNoRow on a miss
 };
 
-// MVCC visibility (executor.h:383-446): returns the payload row to read (or nullptr) and its stamp.
-__device__ __forceinline__ const uint8_t *visible_version(const SnapshotView &v, uint32_t row, uint32_t read_ts,
-                                                          uint32_t *stamp) {
-    const uint32_t t = __ldg(v.ts + row);
+// MVCC visibility (executor.h:383-446): the version of `row` visible at read_ts, in gather.cuh's
+// source-row encoding (kNoRow if none), and its stamp. `t` = commit id of the in-leaf version.
+__device__ __forceinline__ uint32_t visible_version(const SnapshotView &v, uint32_t row, uint32_t t, uint32_t read_ts,
+                                                    uint32_t *stamp) {
     if (read_ts >= t) {
         *stamp = t;
-        return v.payload + (uint64_t) row * v.payload_size;
+        return row;
     }
     uint32_t c = __ldg(v.chain + row);            // 1-based index into the staged version table
     while (c != 0) {
         const uint32_t b = __ldg(v.ver_begin + (c - 1)), e = __ldg(v.ver_commit + (c - 1));
-        if (b == 0 || e == 0) return nullptr;     // INVALID_CID stops the walk (executor.h:418)
+        if (b == 0 || e == 0) return kNoRow;      // INVALID_CID stops the walk (executor.h:418)
         if (read_ts >= b && read_ts <= e) {
             *stamp = b;
-            return v.ver_payload + (uint64_t) (c - 1) * v.payload_size;
+            return (c - 1) | kVersionRowFlag;
         }
         c = __ldg(v.ver_next + (c - 1));
     }
-    return nullptr;
-}
-
-// copy `nbytes` from each of U source rows to U destination rows, all loads issued before the stores
-template <typename V, int U>
-__device__ __forceinline__ void warp_copy_rows(const uint8_t *const (&src)[U], uint8_t *const (&dst)[U],
-                                               uint32_t nbytes, int lane) {
-    const uint32_t nvec = nbytes / (uint32_t) sizeof(V);
-    for (uint32_t c = lane; c < nvec; c += 32) {
-        V r[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u)
-            if (src[u]) r[u] = __ldcs(reinterpret_cast<const V *>(src[u]) + c);
-#pragma unroll
-        for (int u = 0; u < U; ++u)
-            if (src[u]) __stcs(reinterpret_cast<V *>(dst[u]) + c, r[u]);
-    }
+    *stamp = 0;
+    return kNoRow;
 }
 
 template <int NW, int G>
@@ -112,7 +99,7 @@ __global__ void __launch_bounds__(256) probe_kernel(SnapshotView v, ProbeArgs a)
     const uint64_t warp_global = (uint64_t) blockIdx.x * warps_per_block + (threadIdx.x >> 5);
     const uint64_t n_warps = (uint64_t) gridDim.x * warps_per_block;
     const uint64_t n_tiles = (a.n + 31) / 32;
-    const uint32_t K = v.key_size, P = v.payload_size;
+    const uint32_t K = v.key_size;
     const int first_smem = v.n_levels - v.smem_levels;
 
     for (uint64_t tile = warp_global; tile < n_tiles; tile += n_warps) {
@@ -158,34 +145,15 @@ __global__ void __launch_bounds__(256) probe_kernel(SnapshotView v, ProbeArgs a)
         }
 
         // MVCC: one lane per probe
-        const uint8_t *src = nullptr;
-        uint32_t stamp = 0;
-        if (active && myhit) src = visible_version(v, mypos, a.read_ts, &stamp);
         if (active) {
-            if (a.found) a.found[gi] = src ? 1 : 0;
+            uint32_t src = kNoRow, stamp = 0;
+            if (myhit) src = visible_version(v, mypos, __ldg(v.ts + mypos), a.read_ts, &stamp);
+            if (a.found) a.found[gi] = src != kNoRow ? 1 : 0;
             if (a.ts_out) a.ts_out[gi] = stamp;
-            if (a.key_out && src) {
+            if (a.key_out && src != kNoRow) {
                 for (uint32_t b = 0; b < K; ++b) a.key_out[gi * K + b] = a.keys[gi * K + b];
             }
-        }
-
-        // payload rows: the warp copies 4 rows at a time
-        if (a.payload_out) {
-            const uintptr_t align = (uintptr_t) v.payload | (uintptr_t) v.ver_payload | (uintptr_t) a.payload_out | P;
-            constexpr int U = 4;
-            for (int p0 = 0; p0 < 32; p0 += U) {
-                const uint8_t *s[U];
-                uint8_t *d[U];
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    s[u] = reinterpret_cast<const uint8_t *>(__shfl_sync(0xFFFFFFFFu, (unsigned long long) src, p0 + u));
-                    d[u] = a.payload_out + (tile * 32 + p0 + u) * P;
-                }
-                if ((align & 15) == 0) warp_copy_rows<uint4, U>(s, d, P, lane);
-                else if ((align & 7) == 0) warp_copy_rows<uint2, U>(s, d, P, lane);
-                else if ((align & 3) == 0) warp_copy_rows<uint32_t, U>(s, d, P, lane);
-                else warp_copy_rows<uint8_t, U>(s, d, P, lane);
-            }
+            if (a.src_row) a.src_row[gi] = src;
         }
     }
 }

@@ -10,14 +10,20 @@
 //     to_scan+1 lowest-slot qualifying rows;
 //   * the iterator moves to the next leaf only when its buffer runs down to one row with budget left,
 //     by re-descending with le_child=false from that row's key (b_tree.h:913-926): it reaches the right
-//     sibling iff that key equals the leaf's upper fence, otherwise it lands in the same leaf, sees the
-//     same record first and ends the scan (b_tree.h:930-938). An empty leaf ends the scan too.
-// One CTA per scan walks the flattened leaves from the start leaf: per leaf it evaluates the qualify /
-// slot-rank / MVCC predicates one row per thread, compacts with ballot + prefix sums, and the warps copy
-// the selected payload rows (coalesced vector loads/stores) into the scan's output slab.
+//     sibling iff that key equals the leaf's upper fence (cont[leaf]), otherwise it lands in the same
+//     leaf, sees the same record first and ends the scan (b_tree.h:930-938). An empty leaf ends it too.
+//
+// Because the flattened leaves are contiguous in key order, those rules collapse to: the scan emits the
+// contiguous row window [q0, q0+S) of the table, cut at the end of the first leaf whose cont flag is 0,
+// with the slot-order selection applied only inside the leaf where the budget runs out. One CTA plans
+// one scan: it stages the window's commit-id / chain-head columns in shared memory with TMA bulk copies
+// (cp.async.bulk + mbarrier), evaluates the MVCC predicate one row per thread, compacts with
+// ballot/prefix sums and writes the scan's source-row list, keys and commit ids; gather_rows_kernel
+// (gather.cuh) then streams the payload rows of all scans at once, perfectly load-balanced.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "gather.cuh"
 #include "keys.cuh"
 #include "probe.cuh"
 
@@ -33,146 +39,205 @@ struct ScanArgs {
     uint32_t *row_counts;
     uint8_t *key_out;
     uint32_t *ts_out;
-    uint8_t *payload_out;
+    uint32_t *src_row;          // [n][out_stride] rows to gather, kNoRow beyond row_counts[i]
 };
 
 constexpr int kScanThreads = 256;
+constexpr int kScanRowsPerThread = 4;
+constexpr int kScanTile = kScanThreads * kScanRowsPerThread;     // rows staged per TMA tile
 
-// block-wide exclusive prefix sum of a 0/1 flag; returns this thread's prefix, *total = block sum
-__device__ __forceinline__ uint32_t block_prefix(bool flag, uint32_t *s_warp, uint32_t *total) {
+// ---- mbarrier / TMA bulk copy (PTX) -----------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy (TMA, SASS UBLKCP); 16-byte aligned addresses, size multiple of 16
+__device__ __forceinline__ void tma_load_1d(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// block-wide exclusive prefix sum of small per-thread counts; *total = block sum
+__device__ __forceinline__ uint32_t block_exclusive_sum(uint32_t x, uint32_t *s_warp, uint32_t *total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t m = __ballot_sync(0xFFFFFFFFu, flag);
-    const uint32_t within = __popc(m & ((1u << lane) - 1u));
-    __syncthreads();                       // protect s_warp reuse
-    if (lane == 0) s_warp[warp] = __popc(m);
+    uint32_t incl = x;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= d) incl += y;
+    }
+    __syncthreads();                       // s_warp may still be read by the previous call
+    if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
     uint32_t base = 0, tot = 0;
-    const int nw = blockDim.x >> 5;
-    for (int w = 0; w < nw; ++w) {
-        const uint32_t x = s_warp[w];
-        if (w < warp) base += x;
-        tot += x;
+#pragma unroll
+    for (int w = 0; w < kScanThreads / 32; ++w) {
+        const uint32_t s = s_warp[w];
+        if (w < warp) base += s;
+        tot += s;
     }
     *total = tot;
-    return base + within;
+    return base + incl - x;
 }
 
 template <int NW>
-__global__ void __launch_bounds__(kScanThreads) scan_kernel(SnapshotView v, ScanArgs a) {
+__global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v, ScanArgs a) {
+    __shared__ __align__(16) uint32_t s_ts[kScanTile + 8];
+    __shared__ __align__(16) uint32_t s_chain[kScanTile + 8];
+    __shared__ __align__(8) uint64_t s_bar;
     __shared__ uint32_t s_warp[kScanThreads / 32];
-    __shared__ uint32_t s_leaf;
-    __shared__ const uint8_t *s_src[kScanThreads];
-    extern __shared__ __align__(16) uint16_t s_slots[];          // [max_leaf_rows] for the slot-rank quirk
+    __shared__ uint32_t s_leaf, s_min;
+    extern __shared__ __align__(16) uint16_t s_slots[];          // [max_leaf_rows] for the slot-rank rule
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
-    const uint32_t K = v.key_size, P = v.payload_size;
-    const uintptr_t align = (uintptr_t) v.payload | (uintptr_t) v.ver_payload | (uintptr_t) a.payload_out | P;
+    const int tid = threadIdx.x;
+    const uint32_t K = v.key_size;
+    const uint32_t L = (uint32_t) v.n_leaves;
+    uint32_t parity = 0;
+    if (tid == 0) mbar_init(&s_bar, 1);
+    __syncthreads();
 
     for (uint64_t sid = blockIdx.x; sid < a.n; sid += gridDim.x) {
         const uint32_t S = a.scan_sizes[sid];
         const SKey<NW> begin = to_sortable<NW>(a.start_keys + sid * K, K, v.xormask);
         const uint64_t out_base = sid * (uint64_t) a.out_stride;
+        uint32_t cnt = 0;
 
-        // locate the start leaf: number of upper fences < begin (fences of leaves 0..L-2)
-        if (tid == 0) {
-            uint64_t lo = 0, hi = v.n_leaves ? v.n_leaves - 1 : 0;
-            while (lo < hi) {
-                const uint64_t mid = (lo + hi) >> 1;
-                if (skey_less<NW>(load_skey<NW>(v.sep, mid), begin)) lo = mid + 1; else hi = mid;
-            }
-            s_leaf = (uint32_t) lo;
-        }
-        __syncthreads();
-        uint32_t j = s_leaf;
-        uint32_t remaining = S, cnt = 0;
-        bool first = true;
+        // emits one row (already selected) at output position `pos` of this scan
+        auto emit = [&](uint32_t row, uint32_t src, uint32_t stamp, uint32_t pos) {
+            const uint64_t o = out_base + pos;
+            a.src_row[o] = src;
+            if (a.ts_out) a.ts_out[o] = stamp;
+            if (a.key_out) from_sortable<NW>(load_skey<NW>(v.level[0], row), a.key_out + o * K, K, v.xormask);
+        };
 
-        while (remaining > 0 && j < v.n_leaves) {
-            const uint32_t lo = v.leaf_off[j], hi = v.leaf_off[j + 1];
-            const uint32_t nleaf = hi - lo;
-            // rows of this leaf with key >= bound. Later leaves: every key is > the previous leaf's keys.
-            uint32_t q = 0;
-            if (first) {
-                uint32_t below = 0;
-                for (uint32_t base = 0; base < nleaf; base += blockDim.x) {
-                    const uint32_t i = base + tid;
-                    const bool lt = i < nleaf && skey_less<NW>(load_skey<NW>(v.level[0], (uint64_t) lo + i), begin);
-                    below += __syncthreads_count(lt);
+        if (S > 0 && L > 0) {
+            // ---- start leaf: number of upper fences < begin (fences of leaves 0..L-2) ------------------
+            if (tid == 0) {
+                uint32_t lo = 0, hi = L - 1;
+                while (lo < hi) {
+                    const uint32_t mid = (lo + hi) >> 1;
+                    if (skey_less<NW>(load_skey<NW>(v.sep, mid), begin)) lo = mid + 1; else hi = mid;
                 }
-                q = below;
+                s_leaf = lo;
+                s_min = 0xFFFFFFFFu;
             }
-            const uint32_t q0 = lo + q, nq = hi - q0, T = remaining;
-            if (nq == 0) break;                                   // empty buffer: every later GetNext is null
-            const uint32_t take = nq < T ? nq : T;
-            const bool quirk = nq > T + 1;                        // slot-order early break bites
-
-            if (quirk) {
-                for (uint32_t i = tid; i < nq; i += blockDim.x) s_slots[i] = v.slot[q0 + i];
-                __syncthreads();
-            }
-            // emit `take` rows in key order, one row per thread per pass
-            uint32_t emitted_sel = 0;                              // selected rows seen so far (quirk path)
-            for (uint32_t base = 0; base < nq; base += blockDim.x) {
+            __syncthreads();
+            const uint32_t j0 = s_leaf;
+            const uint32_t lo0 = v.leaf_off[j0], hi0 = v.leaf_off[j0 + 1];
+            uint32_t below = 0;                                   // rows of the start leaf with key < begin
+            for (uint32_t base = 0; base < hi0 - lo0; base += kScanThreads) {
                 const uint32_t i = base + tid;
-                bool sel = i < nq;
-                if (quirk) {
-                    if (sel) {
-                        const uint16_t me = s_slots[i];
-                        uint32_t rank = 0;
-                        for (uint32_t x = 0; x < nq; ++x) rank += s_slots[x] < me;
-                        sel = rank < T + 1;                        // among the T+1 lowest-slot qualifying rows
+                const bool lt = i < hi0 - lo0 && skey_less<NW>(load_skey<NW>(v.level[0], (uint64_t) lo0 + i), begin);
+                below += __syncthreads_count(lt);
+            }
+            const uint32_t q0 = lo0 + below;
+            if (hi0 > q0) {                                       // an empty first buffer ends the scan at once
+                // ---- last leaf touched: first j >= j0 that stops the hop chain or exhausts the budget --
+                const uint64_t need_end = (uint64_t) q0 + S;
+                for (uint32_t base = j0;; base += kScanThreads) {
+                    const uint32_t j = base + tid;
+                    if (j < L && (!v.cont[j] || (uint64_t) v.leaf_off[j + 1] >= need_end || j == L - 1)) atomicMin(&s_min, j);
+                    __syncthreads();
+                    const uint32_t m = s_min;
+                    __syncthreads();
+                    if (m != 0xFFFFFFFFu) break;                 // leaf L-1 always qualifies, so this terminates
+                }
+                const uint32_t jl = s_min;
+                const uint32_t row_end = v.leaf_off[jl + 1];
+                const uint32_t total = (uint64_t) row_end >= need_end ? S : row_end - q0;
+                const uint32_t start_l = max(q0, v.leaf_off[jl]);
+                const uint32_t T = S - (start_l - q0);            // budget left when the iterator reaches leaf jl
+                const uint32_t nql = row_end - start_l;           // qualifying rows of leaf jl
+                const bool quirk = nql > T + 1;                   // slot-order early break bites (Q5)
+                const uint32_t main_n = quirk ? start_l - q0 : total;
+
+                // ---- rows [q0, q0 + main_n): straight window, TMA-staged commit ids / chain heads -------
+                for (uint32_t off = 0; off < main_n; off += kScanTile) {
+                    const uint32_t r0 = q0 + off;
+                    const uint32_t n = min((uint32_t) kScanTile, main_n - off);
+                    const uint32_t a0 = r0 & ~3u;                 // 16-byte aligned start of the staged window
+                    const uint32_t bytes = ((r0 + n - a0) * 4u + 15u) & ~15u;
+                    if (tid == 0) {
+                        mbar_expect_tx(&s_bar, a.apply_visibility ? 2 * bytes : bytes);
+                        tma_load_1d(s_ts, v.ts + a0, bytes, &s_bar);
+                        if (a.apply_visibility) tma_load_1d(s_chain, v.chain + a0, bytes, &s_bar);
+                    }
+                    mbar_wait(&s_bar, parity);
+                    parity ^= 1;
+                    uint32_t src[kScanRowsPerThread], stamp[kScanRowsPerThread], mine = 0;
+#pragma unroll
+                    for (int k = 0; k < kScanRowsPerThread; ++k) {
+                        const uint32_t i = tid * kScanRowsPerThread + k;
+                        src[k] = kNoRow;
+                        stamp[k] = 0;
+                        if (i < n) {
+                            const uint32_t row = r0 + i, t = s_ts[row - a0];
+                            if (!a.apply_visibility) { src[k] = row; stamp[k] = t; }
+                            else if (a.read_ts >= t) { src[k] = row; stamp[k] = t; }
+                            else if (s_chain[row - a0] != 0) src[k] = visible_version(v, row, t, a.read_ts, &stamp[k]);
+                            mine += src[k] != kNoRow;
+                        }
                     }
                     uint32_t tot;
-                    const uint32_t pre = block_prefix(sel, s_warp, &tot);
-                    sel = sel && (emitted_sel + pre) < T;          // first T of them in key order
-                    emitted_sel += tot;
-                } else {
-                    sel = sel && i < take;
+                    uint32_t pos = cnt + block_exclusive_sum(mine, s_warp, &tot);
+#pragma unroll
+                    for (int k = 0; k < kScanRowsPerThread; ++k)
+                        if (src[k] != kNoRow) emit(r0 + tid * kScanRowsPerThread + k, src[k], stamp[k], pos++);
+                    cnt += tot;
+                    __syncthreads();                              // tile fully consumed before it is overwritten
                 }
-                // MVCC per selected row
-                const uint8_t *src = nullptr;
-                uint32_t stamp = 0;
-                const uint32_t row = q0 + i;
-                if (sel) {
-                    if (a.apply_visibility) {
-                        src = visible_version(v, row, a.read_ts, &stamp);
-                    } else {
-                        stamp = __ldg(v.ts + row);
-                        src = v.payload + (uint64_t) row * P;
+
+                // ---- the leaf where the budget runs out, when the slot-order rule changes the result -----
+                if (quirk) {
+                    for (uint32_t i = tid; i < nql; i += kScanThreads) s_slots[i] = v.slot[start_l + i];
+                    __syncthreads();
+                    uint32_t sel_before = 0;
+                    for (uint32_t base = 0; base < nql; base += kScanThreads) {
+                        const uint32_t i = base + tid;
+                        bool sel = false;
+                        if (i < nql) {
+                            const uint16_t me = s_slots[i];
+                            uint32_t rank = 0;
+                            for (uint32_t x = 0; x < nql; ++x) rank += s_slots[x] < me;
+                            sel = rank < T + 1;                   // among the T+1 lowest-slot qualifying rows
+                        }
+                        uint32_t tot;
+                        const uint32_t pre = block_exclusive_sum(sel ? 1u : 0u, s_warp, &tot);
+                        sel = sel && sel_before + pre < T;        // first T of them in key order
+                        sel_before += tot;
+                        uint32_t src = kNoRow, stamp = 0;
+                        const uint32_t row = start_l + i;
+                        if (sel) {
+                            const uint32_t t = __ldg(v.ts + row);
+                            if (a.apply_visibility) src = visible_version(v, row, t, a.read_ts, &stamp);
+                            else { src = row; stamp = t; }
+                        }
+                        const uint32_t p2 = block_exclusive_sum(src != kNoRow ? 1u : 0u, s_warp, &tot);
+                        if (src != kNoRow) emit(row, src, stamp, cnt + p2);
+                        cnt += tot;
                     }
                 }
-                uint32_t tot;
-                const uint32_t pre = block_prefix(src != nullptr, s_warp, &tot);
-                if (src) {
-                    const uint64_t o = out_base + cnt + pre;
-                    if (a.ts_out) a.ts_out[o] = stamp;
-                    if (a.key_out) {
-                        const SKey<NW> kk = load_skey<NW>(v.level[0], row);
-                        from_sortable<NW>(kk, a.key_out + o * K, K, v.xormask);
-                    }
-                    s_src[pre] = src;
-                }
-                __syncthreads();
-                if (a.payload_out) {
-                    for (uint32_t r = warp; r < tot; r += nwarps) {
-                        const uint8_t *s1[1] = { s_src[r] };
-                        uint8_t *d1[1] = { a.payload_out + (out_base + cnt + r) * P };
-                        if ((align & 15) == 0) warp_copy_rows<uint4, 1>(s1, d1, P, lane);
-                        else if ((align & 7) == 0) warp_copy_rows<uint2, 1>(s1, d1, P, lane);
-                        else if ((align & 3) == 0) warp_copy_rows<uint32_t, 1>(s1, d1, P, lane);
-                        else warp_copy_rows<uint8_t, 1>(s1, d1, P, lane);
-                    }
-                }
-                cnt += tot;
-                __syncthreads();
-                if (!quirk && base + blockDim.x >= take) break;
             }
-            remaining -= take;
-            // hop: only if the whole leaf was consumed and its max visible key is the parent separator
-            if (take < nq || !v.cont[j]) break;
-            ++j;
-            first = false;
         }
+        // unused tail of the scan's slab: nothing to gather
+        for (uint32_t i = cnt + tid; i < a.out_stride; i += kScanThreads) a.src_row[out_base + i] = kNoRow;
         if (tid == 0) a.row_counts[sid] = cnt;
         __syncthreads();
     }

@@ -23,6 +23,7 @@
 #include "probe.cuh"
 #include "scan.cuh"
 #include "transform.cuh"
+#include "gather.cuh"
 #include "generate.cuh"
 
 using namespace stage;
@@ -117,6 +118,7 @@ struct stage_snapshot {
 
     // scratch for STAGE_IO_HOST batches
     DevBuf sc_keys, sc_found, sc_ts, sc_keyout, sc_payload, sc_sizes, sc_counts;
+    DevBuf sc_srcrow;                           // source-row lists handed from the plan kernels to the gather
 };
 
 template <typename T>
@@ -176,7 +178,7 @@ static void snapshot_free(stage_snapshot *s) {
         if (s->stage_ev[i]) cudaEventDestroy(s->stage_ev[i]);
     }
     s->sc_keys.release(); s->sc_found.release(); s->sc_ts.release(); s->sc_keyout.release();
-    s->sc_payload.release(); s->sc_sizes.release(); s->sc_counts.release();
+    s->sc_payload.release(); s->sc_sizes.release(); s->sc_counts.release(); s->sc_srcrow.release();
     if (s->own_stream && s->stream) cudaStreamDestroy(s->stream);
     delete s;
 }
@@ -683,25 +685,59 @@ static int sm_count() {
     return g_sm_count;
 }
 
+template <typename V>
+static int launch_gather_v(stage_snapshot *s, const GatherArgs &g) {
+    const unsigned blocks = (unsigned) ((g.n_slots + kGatherRows - 1) / kGatherRows);
+    gather_rows_kernel<V, 4><<<blocks, kGatherThreads, 0, s->stream>>>(g);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
+// payload rows named by src_row[0..n_slots) -> dst[n_slots][P]
+static int launch_gather(stage_snapshot *s, const uint32_t *src_row, uint64_t n_slots, uint8_t *dst) {
+    if (n_slots == 0 || !dst) return STAGE_OK;
+    if ((n_slots + kGatherRows - 1) / kGatherRows > 0x7FFFFFFFull) return STAGE_ERR_ARG;
+    GatherArgs g{};
+    g.src_row = src_row;
+    g.n_slots = n_slots;
+    g.payload = s->d_payload;
+    g.ver_payload = s->d_ver_payload;
+    g.dst = dst;
+    g.payload_size = s->schema.payload_size;
+    const uintptr_t align = (uintptr_t) g.payload | (uintptr_t) g.ver_payload | (uintptr_t) dst | g.payload_size;
+    if ((align & 15) == 0) return launch_gather_v<uint4>(s, g);
+    if ((align & 7) == 0) return launch_gather_v<uint2>(s, g);
+    if ((align & 3) == 0) return launch_gather_v<uint32_t>(s, g);
+    return launch_gather_v<uint8_t>(s, g);
+}
+
 template <int NW>
 static int launch_probe(stage_snapshot *s, const ProbeArgs &a) {
-    if (a.n == 0) return STAGE_OK;
     const size_t smem = (size_t) s->view.smem_words * 4;
     const uint64_t tiles = (a.n + 31) / 32;
     const uint64_t want_blocks = (tiles + 7) / 8;
-    const unsigned blocks = (unsigned) std::min<uint64_t>(want_blocks, (uint64_t) sm_count() * 8);
+    const unsigned blocks = (unsigned) std::min<uint64_t>(want_blocks, (uint64_t) sm_count() * 16);
     probe_kernel<NW, 4><<<blocks, 256, smem, s->stream>>>(s->view, a);
     LAUNCH_CHECK();
     return STAGE_OK;
 }
 
-static int probe_device(stage_snapshot *s, const ProbeArgs &a) {
-    switch (s->nw) {
-        case 1: return launch_probe<1>(s, a);
-        case 2: return launch_probe<2>(s, a);
-        case 4: return launch_probe<4>(s, a);
-        default: return launch_probe<8>(s, a);
+// search + MVCC (probe_kernel) then payload gather; all pointers are device pointers
+static int probe_device(stage_snapshot *s, ProbeArgs a, uint8_t *payload_out) {
+    if (a.n == 0) return STAGE_OK;
+    int rc;
+    if (payload_out) {
+        if ((rc = s->sc_srcrow.ensure(a.n * 4))) return rc;
+        a.src_row = static_cast<uint32_t *>(s->sc_srcrow.p);
     }
+    switch (s->nw) {
+        case 1: rc = launch_probe<1>(s, a); break;
+        case 2: rc = launch_probe<2>(s, a); break;
+        case 4: rc = launch_probe<4>(s, a); break;
+        default: rc = launch_probe<8>(s, a); break;
+    }
+    if (rc) return rc;
+    return launch_gather(s, a.src_row, a.n, payload_out);
 }
 
 extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
@@ -718,8 +754,7 @@ extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint
         a.keys = static_cast<const uint8_t *>(keys);
         a.found = found; a.ts_out = ts;
         a.key_out = static_cast<uint8_t *>(key_out);
-        a.payload_out = static_cast<uint8_t *>(payload_out);
-        return probe_device(s, a);
+        return probe_device(s, a, static_cast<uint8_t *>(payload_out));
     }
     // host I/O: chunked so the device scratch stays bounded (<= 256 Ki probes per chunk)
     const uint64_t chunk = 1ull << 18;
@@ -740,9 +775,8 @@ extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint
         a.found = found ? static_cast<uint8_t *>(s->sc_found.p) : nullptr;
         a.ts_out = ts ? static_cast<uint32_t *>(s->sc_ts.p) : nullptr;
         a.key_out = key_out ? static_cast<uint8_t *>(s->sc_keyout.p) : nullptr;
-        a.payload_out = payload_out ? static_cast<uint8_t *>(s->sc_payload.p) : nullptr;
         if (payload_out) CUDA_TRY(cudaMemsetAsync(s->sc_payload.p, 0, m * (uint64_t) P, s->stream));
-        if ((rc = probe_device(s, a))) return rc;
+        if ((rc = probe_device(s, a, payload_out ? static_cast<uint8_t *>(s->sc_payload.p) : nullptr))) return rc;
         if (found) CUDA_TRY(cudaMemcpyAsync(found + b, s->sc_found.p, m, cudaMemcpyDeviceToHost, s->stream));
         if (ts) CUDA_TRY(cudaMemcpyAsync(ts + b, s->sc_ts.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
         if (key_out)
@@ -758,23 +792,28 @@ extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint
 
 template <int NW>
 static int launch_scan(stage_snapshot *s, const ScanArgs &a) {
-    if (a.n == 0) return STAGE_OK;
-    const size_t smem = (size_t) std::max<uint32_t>(s->view.max_leaf_rows, 1) * 2;
-    if (smem > 48 * 1024)
-        CUDA_TRY(cudaFuncSetAttribute(scan_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    const size_t smem = (size_t) std::max<uint32_t>(s->view.max_leaf_rows, 8) * 2;
     const unsigned blocks = (unsigned) std::min<uint64_t>(a.n, (uint64_t) sm_count() * 64);
-    scan_kernel<NW><<<blocks, kScanThreads, smem, s->stream>>>(s->view, a);
+    scan_plan_kernel<NW><<<blocks, kScanThreads, smem, s->stream>>>(s->view, a);
     LAUNCH_CHECK();
     return STAGE_OK;
 }
 
-static int scan_device(stage_snapshot *s, const ScanArgs &a) {
+// plan (scan_plan_kernel) then payload gather; all pointers are device pointers
+static int scan_device(stage_snapshot *s, ScanArgs a, uint8_t *payload_out) {
+    if (a.n == 0) return STAGE_OK;
+    const uint64_t slots = a.n * (uint64_t) a.out_stride;
+    int rc;
+    if ((rc = s->sc_srcrow.ensure(std::max<uint64_t>(slots, 1) * 4))) return rc;
+    a.src_row = static_cast<uint32_t *>(s->sc_srcrow.p);
     switch (s->nw) {
-        case 1: return launch_scan<1>(s, a);
-        case 2: return launch_scan<2>(s, a);
-        case 4: return launch_scan<4>(s, a);
-        default: return launch_scan<8>(s, a);
+        case 1: rc = launch_scan<1>(s, a); break;
+        case 2: rc = launch_scan<2>(s, a); break;
+        case 4: rc = launch_scan<4>(s, a); break;
+        default: rc = launch_scan<8>(s, a); break;
     }
+    if (rc) return rc;
+    return launch_gather(s, a.src_row, slots, payload_out);
 }
 
 extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
@@ -796,8 +835,7 @@ extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys,
         a.row_counts = row_counts;
         a.key_out = static_cast<uint8_t *>(key_out);
         a.ts_out = ts_out;
-        a.payload_out = static_cast<uint8_t *>(payload_out);
-        return scan_device(s, a);
+        return scan_device(s, a, static_cast<uint8_t *>(payload_out));
     }
     for (uint64_t i = 0; i < n; ++i)
         if (scan_sizes[i] > out_stride) return STAGE_ERR_ARG;
@@ -826,8 +864,7 @@ extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys,
         a.row_counts = static_cast<uint32_t *>(s->sc_counts.p);
         a.key_out = key_out ? static_cast<uint8_t *>(s->sc_keyout.p) : nullptr;
         a.ts_out = ts_out ? static_cast<uint32_t *>(s->sc_ts.p) : nullptr;
-        a.payload_out = payload_out ? static_cast<uint8_t *>(s->sc_payload.p) : nullptr;
-        if ((rc = scan_device(s, a))) return rc;
+        if ((rc = scan_device(s, a, payload_out ? static_cast<uint8_t *>(s->sc_payload.p) : nullptr))) return rc;
         CUDA_TRY(cudaMemcpyAsync(row_counts + b, s->sc_counts.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
         const uint64_t rb = b * out_stride;
         if (key_out)

@@ -37,6 +37,9 @@ K_BYTES, P_BYTES = 4, 1000
 ROW_ALGO_BYTES = 2 * (K_BYTES + P_BYTES + 4)       # record read + result write per emitted row
 PROBE_HIT_BYTES = K_BYTES + 2 * (K_BYTES + P_BYTES + 4)
 PROBE_MISS_BYTES = K_BYTES + 1
+# dram__bytes_read.sum + dram__bytes_write.sum of one gather_rows_kernel launch of the default workload, from the
+# committed `ncu --set full` capture (profiles/); None until a capture of the current kernel exists.
+NCU_TRAFFIC_PER_LAUNCH = 7.79e9   # profiles/r1_v2_ncu_summary_scan.txt: 3.939 GB read + 3.851 GB written
 
 
 def parse_args():
@@ -140,6 +143,14 @@ def cpu_scan_sample(table, start_keys, scan_size, read_ts, threads):
     return rows / sec, rows, sec
 
 
+def calibrated_scan_count(table, rows, scan_size, read_ts, threads, target_s):
+    """Number of scans that keeps one CPU sample near target_s seconds (pilot run of 64 scans/thread)."""
+    pilot = scan_start_keys(rows, 64 * threads, seed=7).view(np.uint8).reshape(-1, 4)
+    sec, _ = table.time_scan(pilot, scan_size, read_ts, 1, threads, pin=True)
+    per_scan = max(sec / len(pilot), 1e-9)
+    return int(min(max(target_s / per_scan, 64 * threads), 4_000_000))
+
+
 def scan_start_keys(rows, n, seed):
     from oracle import pyoracle
     return (pyoracle.uniform_keys(rows, n, seed=seed) - 1).astype(np.uint32)
@@ -155,7 +166,8 @@ def run_reference(args, rank, world):
     updates = rows // 10
     read_ts = 10 + updates // 2
     table, kind = build_host_table(rows, updates)
-    n = args.cpu_scans or max(threads * 64, 512)
+    # each step is a bounded sample: ~4 s of work on all host threads
+    n = args.cpu_scans or calibrated_scan_count(table, rows, args.scan_size, read_ts, threads, 4.0)
     times, total_rows = [], 0
     for step in range(args.warmup + args.steps):
         sk = scan_start_keys(rows, n, seed=100 + step).view(np.uint8).reshape(-1, 4)
@@ -275,6 +287,15 @@ def main():
     step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
     total_ms = ev[0].elapsed_time(ev[-1])
     rows_emitted = int(d_counts[args.warmup:].sum().item())
+    # per-kernel durations of the same K steps (CUDA events recorded by the library around each launch)
+    snap.enable_timing(True)
+    plan_ms, gather_ms = [], []
+    for i in range(args.steps):
+        scan_step(args.warmup + i)
+        p_, g_ = snap.last_timing()
+        plan_ms.append(p_)
+        gather_ms.append(g_)
+    snap.enable_timing(False)
 
     # ---- probe leg (device resident) ------------------------------------------------------------
     probe = None
@@ -296,14 +317,26 @@ def main():
         pe1.record(stream)
         torch.cuda.synchronize()
         pms = pe0.elapsed_time(pe1)
+        snap.enable_timing(True)
+        pp, pg = [], []
+        for i in range(args.steps):
+            b = args.warmup + i
+            snap.probe_device(d_pk[b], n_probes, read_ts, d_found[b], d_pts, d_pkey, d_ppay)
+            p_, g_ = snap.last_timing()
+            pp.append(p_)
+            pg.append(g_)
+        snap.enable_timing(False)
         hits = int(d_found[args.warmup:].sum().item())
         nprobe = args.steps * n_probes
         peak, peak_src = peaks()
         pbytes = hits * PROBE_HIT_BYTES + (nprobe - hits) * PROBE_MISS_BYTES
+        g_ach = hits * 2 * P_BYTES / (sum(pg) * 1e-3) / 1e9
         probe = {"value": nprobe / (pms * 1e-3), "unit": "probes/s", "ms_per_step": pms / args.steps,
-                 "hit_rate": hits / nprobe,
-                 "roofline": {"bound": "hbm", "achieved": pbytes / (pms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                              "frac": pbytes / (pms * 1e-3) / 1e9 / peak, "traffic": None}}
+                 "hit_rate": hits / nprobe, "plan_ms": sum(pp) / len(pp), "gather_ms": sum(pg) / len(pg),
+                 "roofline": {"bound": "hbm", "kernel": "stage::gather_rows_kernel", "achieved": g_ach, "peak": peak,
+                              "unit": "GB/s", "frac": g_ach / peak, "traffic": None,
+                              "step_achieved": pbytes / (pms * 1e-3) / 1e9,
+                              "step_frac": pbytes / (pms * 1e-3) / 1e9 / peak}}
 
     # ---- max over ranks, whole-job aggregate ----------------------------------------------------
     t_ms = torch.tensor([total_ms], dtype=torch.float64, device=dev)
@@ -358,7 +391,7 @@ def main():
         else:
             cpu_ts = read_ts
         threads = os.cpu_count() or 1
-        n_cpu = args.cpu_scans or max(threads * 256, 2048)
+        n_cpu = args.cpu_scans or calibrated_scan_count(host_table, rows, S, cpu_ts, threads, 15.0)
         sk = scan_start_keys(rows, n_cpu, seed=100 + args.warmup).view(np.uint8).reshape(-1, 4)
         rps, r, sec = cpu_scan_sample(host_table, sk, S, cpu_ts, threads)
         cpu = {"value": rps, "unit": "rows/s", "cores": threads, "kind": table_kind,
@@ -368,7 +401,9 @@ def main():
         peak, peak_src = peaks()
         algo_bytes = rows_emitted * ROW_ALGO_BYTES + args.steps * n_scans * (K_BYTES + 8)
         kern_ms = sum(step_ms)
-        achieved = algo_bytes / (kern_ms * 1e-3) / 1e9
+        step_achieved = algo_bytes / (kern_ms * 1e-3) / 1e9
+        gather_bytes = rows_emitted * 2 * P_BYTES            # the gather kernel moves the payload rows only
+        achieved = gather_bytes / (sum(gather_ms) * 1e-3) / 1e9
         line = {
             "metric": "YCSB scan rows/s (1000-row MVCC range scans, 10M-tuple int table)",
             "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -376,9 +411,13 @@ def main():
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": workload_config(args, world, table_desc),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel": "stage::scan_kernel<1>",
-                         "algorithmic_bytes_per_launch": algo_bytes / args.steps,
-                         "launch_ms": kern_ms / args.steps},
+                         "traffic": NCU_TRAFFIC_PER_LAUNCH, "peak_source": peak_src,
+                         "kernel": "stage::gather_rows_kernel<uint2,4> (payload rows; dominant kernel of the step)",
+                         "algorithmic_bytes_per_launch": gather_bytes / args.steps,
+                         "launch_ms": sum(gather_ms) / args.steps,
+                         "plan_kernel_ms": sum(plan_ms) / args.steps,
+                         "step_algorithmic_bytes": algo_bytes / args.steps,
+                         "step_achieved": step_achieved, "step_frac": step_achieved / peak},
             "cpu_baseline": cpu,
             "e2e": e2e,
             "gpu_launches": int(launches),

@@ -125,6 +125,12 @@ int stage_gpu_snapshot_destroy(stage_snapshot_t *s);
 int stage_gpu_snapshot_set_stream(stage_snapshot_t *s, void *cuda_stream);
 void *stage_gpu_snapshot_get_stream(const stage_snapshot_t *s);
 
+/* Per-call kernel timing with CUDA events recorded on the snapshot's stream around the two launches of
+ * a *_batch call with STAGE_IO_DEVICE (plan kernel: search / scan planning + MVCC; gather kernel: payload
+ * rows). last_timing() waits for the last call and returns its two durations in milliseconds. */
+int stage_gpu_snapshot_enable_timing(stage_snapshot_t *s, int on);
+int stage_gpu_snapshot_last_timing(stage_snapshot_t *s, float *plan_ms, float *gather_ms);
+
 /* ---- reads -------------------------------------------------------------------------------- */
 
 /* Batched BTree::Read + IndexScanExecutor point branch (b_tree.cpp:2066-2129, executor.h:374-454).

@@ -55,6 +55,8 @@ SYMBOLS = {
     "stage_gpu_snapshot_destroy": (_i32, [_vp]),
     "stage_gpu_snapshot_set_stream": (_i32, [_vp, _vp]),
     "stage_gpu_snapshot_get_stream": (_vp, [_vp]),
+    "stage_gpu_snapshot_enable_timing": (_i32, [_vp, _i32]),
+    "stage_gpu_snapshot_last_timing": (_i32, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "stage_gpu_probe_batch": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp, _vp, _vp, _i32]),
     "stage_gpu_scan_batch": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _vp, _vp, _i32]),
     "stage_gpu_route": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp]),
@@ -201,6 +203,15 @@ class Snapshot:
 
     def set_stream(self, cuda_stream):
         _check(lib().stage_gpu_snapshot_set_stream(self.h, _vp(int(cuda_stream))))
+
+    def enable_timing(self, on=True):
+        _check(lib().stage_gpu_snapshot_enable_timing(self.h, int(on)))
+
+    def last_timing(self):
+        """(plan_ms, gather_ms) of the last device-I/O batch call (CUDA events on the snapshot stream)."""
+        p, g = C.c_float(0), C.c_float(0)
+        _check(lib().stage_gpu_snapshot_last_timing(self.h, C.byref(p), C.byref(g)))
+        return p.value, g.value
 
     def close(self):
         if self.h:

@@ -5,10 +5,14 @@
 // b_tree.cpp:664-702) and then scans the leaf's slots linearly (BaseNode::SearchRecordMeta,
 // b_tree.cpp:18-122). Keys are unique (LeafNode::CheckUnique, b_tree.cpp:1395-1417) and every leaf's
 // keys lie inside its fence range, so "the first visible slot with an equal key in the leaf the fences
-// route to" is exactly "the equal key in the globally sorted key column". The flattened column is
-// searched with a warp-cooperative 32-ary descent over sampled levels (level l+1 holds every 32nd
-// key of level l): each step is one coalesced 32-key load + ballot/popc. The top levels live in
-// shared memory; G probes are in flight per warp to overlap the L2/HBM latency of the lower levels.
+// route to" is exactly "the equal key in the globally sorted key column".
+//
+// Search structure = implicit 4-ary fence levels over the key column: level l+1 holds every 4th key of
+// level l (the last key of each group), down to a top level small enough for shared memory. One lane
+// per probe: the top level is binary-searched in shared memory (the warp's 32 probes proceed
+// together, no global traffic), then every lower level costs ONE 16-byte load — the 4 keys of the
+// group the level above selected — and 4 compares. (A warp-cooperative 32-ary descent was measured
+// first: it is issue-bound, ~130 warp instructions per probe, 0.19 ms per 2^20 probes; profiles/.)
 // Then the MVCC rule (executor.h:383-446) picks the in-leaf version or walks the staged chain. The
 // kernel emits found / commit id / key and the source row of every probe; gather_rows_kernel
 // (gather.cuh) then streams the payload rows.
@@ -20,15 +24,14 @@
 
 namespace stage {
 
-constexpr int kMaxLevels = 8;
-constexpr int kFan = 32;
+constexpr int kMaxLevels = 16;
+constexpr int kFan = 4;             // keys per fence group: 4 x 4-byte keys = one 16-byte load
 
 struct SnapshotView {
-    const uint32_t *level[kMaxLevels];   // level[0] = key column; level[l+1][i] = level[l][32(i+1)-1]
+    const uint32_t *level[kMaxLevels];   // level[0] = key column; level[l+1][i] = level[l][kFan*(i+1)-1]
     uint32_t level_n[kMaxLevels];
-    int n_levels;
-    int smem_levels;                     // how many of the top levels are cached in shared memory
-    uint32_t smem_words;                 // total 32-bit words of those levels
+    int n_levels;                        // level[n_levels-1] is the top level (cached in shared memory)
+    uint32_t smem_words;                 // 32-bit words of the top level
     const uint16_t *slot;
     const uint32_t *ts;
     const uint32_t *chain;
@@ -74,85 +77,91 @@ __device__ __forceinline__ uint32_t visible_version(const SnapshotView &v, uint3
     return kNoRow;
 }
 
-template <int NW, int G>
-__global__ void __launch_bounds__(256) probe_kernel(SnapshotView v, ProbeArgs a) {
-    extern __shared__ __align__(16) uint32_t s_levels[];
-    // stage the top levels in shared memory
-    const uint32_t *lvl[kMaxLevels];
-    {
-        uint32_t off = 0;
-        for (int l = v.n_levels - 1; l >= 0; --l) {
-            if (l >= v.n_levels - v.smem_levels) {
-                const uint32_t words = v.level_n[l] * NW;
-                for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) s_levels[off + i] = v.level[l][i];
-                lvl[l] = s_levels + off;
-                off += words;
-            } else {
-                lvl[l] = v.level[l];
+// number of keys < k among the kFan keys of group `grp` of a level (keys past the level's end do not count);
+// *eq = one of them equals k
+template <int NW>
+__device__ __forceinline__ uint32_t group_count_less(const uint32_t *lvl, uint32_t n, uint32_t grp, const SKey<NW> &k,
+                                                     bool *eq) {
+    const uint64_t base = (uint64_t) grp * kFan;
+    uint32_t cnt = 0;
+    bool e = false;
+    if constexpr (NW == 1) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4 *>(lvl) + grp);     // arrays are padded: safe past n
+        const uint32_t x[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const bool ok = base + i < n;
+            cnt += ok && x[i] < k.w[0];
+            e = e || (ok && x[i] == k.w[0]);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < kFan; ++i) {
+            if (base + i < n) {
+                const SKey<NW> x = load_skey<NW>(lvl, base + i);
+                cnt += skey_less<NW>(x, k);
+                e = e || skey_equal<NW>(x, k);
             }
         }
     }
+    *eq = e;
+    return cnt;
+}
+
+constexpr int kProbeThreads = 256;
+constexpr int kProbePerLane = 2;     // independent probes per lane (memory-level parallelism)
+
+template <int NW>
+__global__ void __launch_bounds__(kProbeThreads) probe_kernel(SnapshotView v, ProbeArgs a) {
+    extern __shared__ __align__(16) uint32_t s_top[];
+    const int top = v.n_levels - 1;
+    const uint32_t n_top = v.level_n[top];
+    for (uint32_t i = threadIdx.x; i < n_top * NW; i += blockDim.x) s_top[i] = v.level[top][i];
     __syncthreads();
 
-    const int lane = threadIdx.x & 31;
-    const uint32_t warps_per_block = blockDim.x >> 5;
-    const uint64_t warp_global = (uint64_t) blockIdx.x * warps_per_block + (threadIdx.x >> 5);
-    const uint64_t n_warps = (uint64_t) gridDim.x * warps_per_block;
-    const uint64_t n_tiles = (a.n + 31) / 32;
     const uint32_t K = v.key_size;
-    const int first_smem = v.n_levels - v.smem_levels;
-
-    for (uint64_t tile = warp_global; tile < n_tiles; tile += n_warps) {
-        const uint64_t gi = tile * 32 + lane;
-        const bool active = gi < a.n;
-        SKey<NW> myk = skey_inf<NW>();
-        if (active) myk = to_sortable<NW>(a.keys + gi * K, K, v.xormask);
-
-        uint32_t mypos = 0;
-        bool myhit = false;
-        for (int g = 0; g < 32; g += G) {
-            SKey<NW> kq[G];
-            uint32_t c[G];
-            bool hit[G];
+    const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+    const uint64_t per_iter = stride * kProbePerLane;
+    for (uint64_t g0 = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; g0 < a.n; g0 += per_iter) {
+        SKey<NW> k[kProbePerLane];
+        uint32_t c[kProbePerLane];
+        bool hit[kProbePerLane], active[kProbePerLane];
 #pragma unroll
-            for (int q = 0; q < G; ++q) {
-#pragma unroll
-                for (int w = 0; w < NW; ++w) kq[q].w[w] = __shfl_sync(0xFFFFFFFFu, myk.w[w], g + q);
-                c[q] = 0;
-                hit[q] = false;
+        for (int p = 0; p < kProbePerLane; ++p) {
+            const uint64_t gi = g0 + p * stride;
+            active[p] = gi < a.n;
+            k[p] = active[p] ? to_sortable<NW>(a.keys + gi * K, K, v.xormask) : skey_inf<NW>();
+            // top level, in shared memory: c = number of keys < k
+            uint32_t lo = 0, hi = n_top;
+            while (lo < hi) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (skey_less<NW>(load_skey_generic<NW>(s_top, mid), k[p])) lo = mid + 1; else hi = mid;
             }
-            for (int l = v.n_levels - 1; l >= 0; --l) {
-                const uint32_t nl = v.level_n[l];
-                SKey<NW> e[G];
-                bool valid[G];
-#pragma unroll
-                for (int q = 0; q < G; ++q) {
-                    const uint64_t idx = (uint64_t) c[q] * kFan + lane;
-                    valid[q] = idx < nl;
-                    if (valid[q]) e[q] = (l >= first_smem) ? load_skey_generic<NW>(lvl[l], idx) : load_skey<NW>(lvl[l], idx);
-                }
-#pragma unroll
-                for (int q = 0; q < G; ++q) {
-                    const bool lt = valid[q] && skey_less<NW>(e[q], kq[q]);
-                    const uint32_t m = __ballot_sync(0xFFFFFFFFu, lt);
-                    if (l == 0) hit[q] = __ballot_sync(0xFFFFFFFFu, valid[q] && skey_equal<NW>(e[q], kq[q])) != 0;
-                    c[q] = c[q] * kFan + __popc(m);
-                }
-            }
-#pragma unroll
-            for (int q = 0; q < G; ++q)
-                if (lane == g + q) { mypos = c[q]; myhit = hit[q]; }
+            c[p] = lo;
+            hit[p] = false;
+            if (top == 0) hit[p] = lo < n_top && skey_equal<NW>(load_skey_generic<NW>(s_top, lo), k[p]);
         }
-
-        // MVCC: one lane per probe
-        if (active) {
+        for (int l = top - 1; l >= 0; --l) {
+            const uint32_t *lvl = v.level[l];
+            const uint32_t nl = v.level_n[l];
+#pragma unroll
+            for (int p = 0; p < kProbePerLane; ++p) {
+                bool eq;
+                const uint32_t cnt = group_count_less<NW>(lvl, nl, c[p], k[p], &eq);
+                c[p] = c[p] * kFan + cnt;
+                if (l == 0) hit[p] = eq;
+            }
+        }
+        // MVCC + outputs
+#pragma unroll
+        for (int p = 0; p < kProbePerLane; ++p) {
+            if (!active[p]) continue;
+            const uint64_t gi = g0 + p * stride;
             uint32_t src = kNoRow, stamp = 0;
-            if (myhit) src = visible_version(v, mypos, __ldg(v.ts + mypos), a.read_ts, &stamp);
+            if (hit[p]) src = visible_version(v, c[p], __ldg(v.ts + c[p]), a.read_ts, &stamp);
             if (a.found) a.found[gi] = src != kNoRow ? 1 : 0;
             if (a.ts_out) a.ts_out[gi] = stamp;
-            if (a.key_out && src != kNoRow) {
-                for (uint32_t b = 0; b < K; ++b) a.key_out[gi * K + b] = a.keys[gi * K + b];
-            }
+            if (a.key_out && src != kNoRow) from_sortable<NW>(k[p], a.key_out + gi * K, K, v.xormask);
             if (a.src_row) a.src_row[gi] = src;
         }
     }

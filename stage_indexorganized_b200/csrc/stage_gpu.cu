@@ -116,6 +116,10 @@ struct stage_snapshot {
 
     SnapshotView view{};
 
+    // per-call kernel timing (CUDA events on the snapshot stream): [0] before plan, [1] between, [2] after gather
+    cudaEvent_t tev[3] = {nullptr, nullptr, nullptr};
+    bool timing = false, timed_gather = false;
+
     // scratch for STAGE_IO_HOST batches
     DevBuf sc_keys, sc_found, sc_ts, sc_keyout, sc_payload, sc_sizes, sc_counts;
     DevBuf sc_srcrow;                           // source-row lists handed from the plan kernels to the gather
@@ -179,6 +183,8 @@ static void snapshot_free(stage_snapshot *s) {
     }
     s->sc_keys.release(); s->sc_found.release(); s->sc_ts.release(); s->sc_keyout.release();
     s->sc_payload.release(); s->sc_sizes.release(); s->sc_counts.release(); s->sc_srcrow.release();
+    for (int i = 0; i < 3; ++i)
+        if (s->tev[i]) cudaEventDestroy(s->tev[i]);
     if (s->own_stream && s->stream) cudaStreamDestroy(s->stream);
     delete s;
 }
@@ -378,13 +384,13 @@ extern "C" int stage_gpu_snapshot_add_leaves(stage_snapshot_t *s, const void *co
 
 template <int NW>
 static int build_levels(stage_snapshot *s) {
-    // level sizes
-    uint64_t n = s->n_rows;
-    std::vector<uint64_t> sizes{n};
-    while (sizes.back() > kFan) sizes.push_back(sizes.back() / kFan);
+    // implicit kFan-ary fence levels over the key column; the top level must fit in shared memory
+    const uint64_t top_max = (44 * 1024) / (NW * 4);
+    std::vector<uint64_t> sizes{s->n_rows};
+    while (sizes.back() > top_max) sizes.push_back(sizes.back() / kFan);
     if ((int) sizes.size() > kMaxLevels) return STAGE_ERR_ARG;
     uint64_t total = 0;
-    for (size_t l = 1; l < sizes.size(); ++l) total += sizes[l];
+    for (size_t l = 1; l < sizes.size(); ++l) total += (sizes[l] + 3) & ~uint64_t(3);   // keep every level 16 B aligned
     int rc = dev_alloc(s, &s->d_levels, total * NW);
     if (rc) return rc;
     SnapshotView &v = s->view;
@@ -395,21 +401,15 @@ static int build_levels(stage_snapshot *s) {
     for (size_t l = 1; l < sizes.size(); ++l) {
         uint32_t *dst = s->d_levels + off * NW;
         const uint64_t nd = sizes[l];
-        sample_level_kernel<NW><<<(unsigned) ((nd + 255) / 256), 256, 0, s->stream>>>(v.level[l - 1], dst, nd);
-        LAUNCH_CHECK();
+        if (nd) {
+            sample_level_kernel<NW><<<(unsigned) ((nd + 255) / 256), 256, 0, s->stream>>>(v.level[l - 1], dst, nd);
+            LAUNCH_CHECK();
+        }
         v.level[l] = dst;
         v.level_n[l] = (uint32_t) nd;
-        off += nd;
+        off += (nd + 3) & ~uint64_t(3);
     }
-    // top levels cached in shared memory: as many as fit in 32 KiB
-    v.smem_levels = 0;
-    v.smem_words = 0;
-    for (int l = v.n_levels - 1; l >= 1; --l) {     // never stage the key column itself
-        uint64_t words = (uint64_t) v.level_n[l] * NW;
-        if ((v.smem_words + words) * 4 > 32 * 1024) break;
-        v.smem_words += (uint32_t) words;
-        v.smem_levels++;
-    }
+    v.smem_words = (uint32_t) (sizes.back() * NW);
     return STAGE_OK;
 }
 
@@ -669,6 +669,24 @@ extern "C" int stage_gpu_snapshot_set_stream(stage_snapshot_t *s, void *cuda_str
     s->own_stream = false;
     return STAGE_OK;
 }
+extern "C" int stage_gpu_snapshot_enable_timing(stage_snapshot_t *s, int on) {
+    if (!s) return STAGE_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(s->device));
+    if (on && !s->tev[0])
+        for (int i = 0; i < 3; ++i) CUDA_TRY(cudaEventCreate(&s->tev[i]));
+    s->timing = on != 0;
+    return STAGE_OK;
+}
+extern "C" int stage_gpu_snapshot_last_timing(stage_snapshot_t *s, float *plan_ms, float *gather_ms) {
+    if (!s || !s->timing || !s->tev[0]) return STAGE_ERR_STATE;
+    CUDA_TRY(cudaEventSynchronize(s->tev[2]));
+    float p = 0.f, g = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&p, s->tev[0], s->tev[1]));
+    CUDA_TRY(cudaEventElapsedTime(&g, s->tev[1], s->tev[2]));
+    if (plan_ms) *plan_ms = p;
+    if (gather_ms) *gather_ms = s->timed_gather ? g : 0.f;
+    return STAGE_OK;
+}
 extern "C" void *stage_gpu_snapshot_get_stream(const stage_snapshot_t *s) { return s ? (void *) s->stream : nullptr; }
 
 // ------------------------------------------------------------------------------------------------
@@ -713,11 +731,17 @@ static int launch_gather(stage_snapshot *s, const uint32_t *src_row, uint64_t n_
 
 template <int NW>
 static int launch_probe(stage_snapshot *s, const ProbeArgs &a) {
-    const size_t smem = (size_t) s->view.smem_words * 4;
-    const uint64_t tiles = (a.n + 31) / 32;
-    const uint64_t want_blocks = (tiles + 7) / 8;
-    const unsigned blocks = (unsigned) std::min<uint64_t>(want_blocks, (uint64_t) sm_count() * 16);
-    probe_kernel<NW, 4><<<blocks, 256, smem, s->stream>>>(s->view, a);
+    const size_t smem = (size_t) std::max<uint32_t>(s->view.smem_words, 4) * 4;
+    // persistent grid: the CTAs that are resident at once; threads stride over the probes
+    static int occ[9] = {0};
+    if (!occ[NW]) {
+        int o = 0;
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, probe_kernel<NW>, kProbeThreads, 44 * 1024));
+        occ[NW] = std::max(o, 1);
+    }
+    const uint64_t want_blocks = (a.n + kProbeThreads * kProbePerLane - 1) / (kProbeThreads * kProbePerLane);
+    const unsigned blocks = (unsigned) std::min<uint64_t>(want_blocks, (uint64_t) sm_count() * occ[NW]);
+    probe_kernel<NW><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a);
     LAUNCH_CHECK();
     return STAGE_OK;
 }
@@ -730,6 +754,7 @@ static int probe_device(stage_snapshot *s, ProbeArgs a, uint8_t *payload_out) {
         if ((rc = s->sc_srcrow.ensure(a.n * 4))) return rc;
         a.src_row = static_cast<uint32_t *>(s->sc_srcrow.p);
     }
+    if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[0], s->stream));
     switch (s->nw) {
         case 1: rc = launch_probe<1>(s, a); break;
         case 2: rc = launch_probe<2>(s, a); break;
@@ -737,7 +762,11 @@ static int probe_device(stage_snapshot *s, ProbeArgs a, uint8_t *payload_out) {
         default: rc = launch_probe<8>(s, a); break;
     }
     if (rc) return rc;
-    return launch_gather(s, a.src_row, a.n, payload_out);
+    if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[1], s->stream));
+    rc = launch_gather(s, a.src_row, a.n, payload_out);
+    if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[2], s->stream));
+    s->timed_gather = payload_out != nullptr;
+    return rc;
 }
 
 extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
@@ -806,6 +835,7 @@ static int scan_device(stage_snapshot *s, ScanArgs a, uint8_t *payload_out) {
     int rc;
     if ((rc = s->sc_srcrow.ensure(std::max<uint64_t>(slots, 1) * 4))) return rc;
     a.src_row = static_cast<uint32_t *>(s->sc_srcrow.p);
+    if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[0], s->stream));
     switch (s->nw) {
         case 1: rc = launch_scan<1>(s, a); break;
         case 2: rc = launch_scan<2>(s, a); break;
@@ -813,7 +843,11 @@ static int scan_device(stage_snapshot *s, ScanArgs a, uint8_t *payload_out) {
         default: rc = launch_scan<8>(s, a); break;
     }
     if (rc) return rc;
-    return launch_gather(s, a.src_row, slots, payload_out);
+    if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[1], s->stream));
+    rc = launch_gather(s, a.src_row, slots, payload_out);
+    if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[2], s->stream));
+    s->timed_gather = payload_out != nullptr;
+    return rc;
 }
 
 extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,

@@ -26,6 +26,7 @@ namespace stage {
 
 constexpr int kMaxLevels = 16;
 constexpr int kFan = 4;             // keys per fence group: 4 x 4-byte keys = one 16-byte load
+constexpr int kProbeTopBytes = 12 * 1024;   // top fence level kept in shared memory (8 CTAs/SM stay resident)
 
 struct SnapshotView {
     const uint32_t *level[kMaxLevels];   // level[0] = key column; level[l+1][i] = level[l][kFan*(i+1)-1]
@@ -77,88 +78,96 @@ __device__ __forceinline__ uint32_t visible_version(const SnapshotView &v, uint3
     return kNoRow;
 }
 
-// number of keys < k among the kFan keys of group `grp` of a level (keys past the level's end do not count);
-// *eq = one of them equals k
+// One fence group: the kFan keys [grp*kFan, grp*kFan+kFan) of a level. Levels (and the key column) are
+// padded with all-ones keys, so no bounds checks are needed: cnt = keys < k, eq = some key == k.
 template <int NW>
-__device__ __forceinline__ uint32_t group_count_less(const uint32_t *lvl, uint32_t n, uint32_t grp, const SKey<NW> &k,
-                                                     bool *eq) {
-    const uint64_t base = (uint64_t) grp * kFan;
-    uint32_t cnt = 0;
-    bool e = false;
+__device__ __forceinline__ uint32_t group_count_less(const uint32_t *lvl, uint32_t grp, const SKey<NW> &k, bool *eq) {
+    uint32_t cnt;
     if constexpr (NW == 1) {
-        const uint4 q = __ldg(reinterpret_cast<const uint4 *>(lvl) + grp);     // arrays are padded: safe past n
-        const uint32_t x[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const bool ok = base + i < n;
-            cnt += ok && x[i] < k.w[0];
-            e = e || (ok && x[i] == k.w[0]);
-        }
+        const uint4 q = __ldg(reinterpret_cast<const uint4 *>(lvl) + grp);
+        const uint32_t kk = k.w[0];
+        cnt = (q.x < kk) + (q.y < kk) + (q.z < kk) + (q.w < kk);
+        *eq = (q.x == kk) | (q.y == kk) | (q.z == kk) | (q.w == kk);
     } else {
+        cnt = 0;
+        bool e = false;
 #pragma unroll
         for (int i = 0; i < kFan; ++i) {
-            if (base + i < n) {
-                const SKey<NW> x = load_skey<NW>(lvl, base + i);
-                cnt += skey_less<NW>(x, k);
-                e = e || skey_equal<NW>(x, k);
-            }
+            const SKey<NW> x = load_skey<NW>(lvl, (uint64_t) grp * kFan + i);
+            cnt += skey_less<NW>(x, k);
+            e = e || skey_equal<NW>(x, k);
         }
+        *eq = e;
     }
-    *eq = e;
     return cnt;
 }
 
 constexpr int kProbeThreads = 256;
-constexpr int kProbePerLane = 2;     // independent probes per lane (memory-level parallelism)
 
-template <int NW>
+// kProbePerLane independent probes per lane: their searches are interleaved step by step (ILP)
+template <int NW, int kProbePerLane>
 __global__ void __launch_bounds__(kProbeThreads) probe_kernel(SnapshotView v, ProbeArgs a) {
     extern __shared__ __align__(16) uint32_t s_top[];
     const int top = v.n_levels - 1;
     const uint32_t n_top = v.level_n[top];
-    for (uint32_t i = threadIdx.x; i < n_top * NW; i += blockDim.x) s_top[i] = v.level[top][i];
+    for (uint32_t i = threadIdx.x; i < n_top * NW; i += blockDim.x) s_top[i] = __ldg(v.level[top] + i);
     __syncthreads();
 
     const uint32_t K = v.key_size;
+    const uint32_t n_rows = (uint32_t) v.n_rows;
     const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
     const uint64_t per_iter = stride * kProbePerLane;
     for (uint64_t g0 = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; g0 < a.n; g0 += per_iter) {
         SKey<NW> k[kProbePerLane];
         uint32_t c[kProbePerLane];
-        bool hit[kProbePerLane], active[kProbePerLane];
+        bool hit[kProbePerLane];
 #pragma unroll
         for (int p = 0; p < kProbePerLane; ++p) {
             const uint64_t gi = g0 + p * stride;
-            active[p] = gi < a.n;
-            k[p] = active[p] ? to_sortable<NW>(a.keys + gi * K, K, v.xormask) : skey_inf<NW>();
-            // top level, in shared memory: c = number of keys < k
-            uint32_t lo = 0, hi = n_top;
-            while (lo < hi) {
-                const uint32_t mid = (lo + hi) >> 1;
-                if (skey_less<NW>(load_skey_generic<NW>(s_top, mid), k[p])) lo = mid + 1; else hi = mid;
-            }
-            c[p] = lo;
+            k[p] = gi < a.n ? to_sortable<NW>(a.keys + gi * K, K, v.xormask) : skey_inf<NW>();
+            c[p] = 0;
             hit[p] = false;
-            if (top == 0) hit[p] = lo < n_top && skey_equal<NW>(load_skey_generic<NW>(s_top, lo), k[p]);
+        }
+        // top level, in shared memory: branch-free lower bound, c = number of keys < k
+        if (n_top > 0) {
+            uint32_t n = n_top;
+            while (n > 1) {
+                const uint32_t half = n >> 1;
+#pragma unroll
+                for (int p = 0; p < kProbePerLane; ++p)
+                    if (skey_less<NW>(load_skey_generic<NW>(s_top, c[p] + half - 1), k[p])) c[p] += half;
+                n -= half;
+            }
+#pragma unroll
+            for (int p = 0; p < kProbePerLane; ++p) {
+                const SKey<NW> x = load_skey_generic<NW>(s_top, c[p]);
+                if (top == 0) hit[p] = skey_equal<NW>(x, k[p]);
+                c[p] += skey_less<NW>(x, k[p]);
+            }
         }
         for (int l = top - 1; l >= 0; --l) {
             const uint32_t *lvl = v.level[l];
-            const uint32_t nl = v.level_n[l];
 #pragma unroll
             for (int p = 0; p < kProbePerLane; ++p) {
                 bool eq;
-                const uint32_t cnt = group_count_less<NW>(lvl, nl, c[p], k[p], &eq);
+                const uint32_t cnt = group_count_less<NW>(lvl, c[p], k[p], &eq);
                 c[p] = c[p] * kFan + cnt;
-                if (l == 0) hit[p] = eq;
+                hit[p] = eq;
             }
         }
         // MVCC + outputs
+        uint32_t t[kProbePerLane];
 #pragma unroll
         for (int p = 0; p < kProbePerLane; ++p) {
-            if (!active[p]) continue;
+            hit[p] = hit[p] && c[p] < n_rows;                 // an equal PAD key is not a row
+            t[p] = hit[p] ? __ldg(v.ts + c[p]) : 0u;
+        }
+#pragma unroll
+        for (int p = 0; p < kProbePerLane; ++p) {
             const uint64_t gi = g0 + p * stride;
+            if (gi >= a.n) continue;
             uint32_t src = kNoRow, stamp = 0;
-            if (hit[p]) src = visible_version(v, c[p], __ldg(v.ts + c[p]), a.read_ts, &stamp);
+            if (hit[p]) src = visible_version(v, c[p], t[p], a.read_ts, &stamp);
             if (a.found) a.found[gi] = src != kNoRow ? 1 : 0;
             if (a.ts_out) a.ts_out[gi] = stamp;
             if (a.key_out && src != kNoRow) from_sortable<NW>(k[p], a.key_out + gi * K, K, v.xormask);

@@ -9,6 +9,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 
 #include <algorithm>
 #include <atomic>
@@ -95,7 +96,8 @@ struct stage_snapshot {
     uint8_t *d_payload = nullptr;
     uint32_t *d_leaf_off = nullptr, *d_sep = nullptr;
     uint8_t *d_cont = nullptr, *d_has_sep = nullptr;
-    uint32_t *d_levels = nullptr;
+    uint32_t *d_levels = nullptr;               // inside the d_skey allocation
+    size_t key_blob_bytes = 0;
     uint32_t *d_ver_begin = nullptr, *d_ver_commit = nullptr, *d_ver_next = nullptr;
     uint8_t *d_ver_payload = nullptr;
     uint32_t *d_err = nullptr;
@@ -173,7 +175,7 @@ static void host_sortable_nw(int nw, const uint8_t *key, uint32_t K, uint32_t xo
 static void snapshot_free(stage_snapshot *s) {
     cudaSetDevice(s->device);
     void *ptrs[] = {s->d_skey, s->d_slot, s->d_ts, s->d_chain, s->d_payload, s->d_leaf_off, s->d_sep, s->d_cont,
-                    s->d_has_sep, s->d_levels, s->d_ver_begin, s->d_ver_commit, s->d_ver_next, s->d_ver_payload,
+                    s->d_has_sep, s->d_ver_begin, s->d_ver_commit, s->d_ver_next, s->d_ver_payload,
                     s->d_err, s->d_stage[0], s->d_stage[1]};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -219,7 +221,15 @@ static int alloc_columns(stage_snapshot *s, uint64_t cap_leaves, uint64_t cap_ro
     s->cap_leaves = cap_leaves;
     s->cap_rows = cap_rows;
     int rc;
-    if ((rc = dev_alloc(s, &s->d_skey, cap_rows * s->nw))) return rc;
+    // key column and its fence levels share one allocation (the search structure is one address range)
+    {
+        const uint64_t key_words = (((cap_rows + 8) * s->nw + 63) & ~uint64_t(63));       // + pad keys
+        uint64_t lvl_words = 64;
+        for (uint64_t n = cap_rows / kFan; n > 0; n /= kFan) lvl_words += ((n + 8) & ~uint64_t(3)) * s->nw;
+        if ((rc = dev_alloc(s, &s->d_skey, key_words + lvl_words))) return rc;
+        s->d_levels = s->d_skey + key_words;
+        s->key_blob_bytes = (key_words + lvl_words) * 4;
+    }
     if ((rc = dev_alloc(s, &s->d_slot, cap_rows))) return rc;
     if ((rc = dev_alloc(s, &s->d_ts, cap_rows))) return rc;
     if ((rc = dev_alloc(s, &s->d_chain, cap_rows))) return rc;
@@ -384,30 +394,27 @@ extern "C" int stage_gpu_snapshot_add_leaves(stage_snapshot_t *s, const void *co
 
 template <int NW>
 static int build_levels(stage_snapshot *s) {
-    // implicit kFan-ary fence levels over the key column; the top level must fit in shared memory
-    const uint64_t top_max = (44 * 1024) / (NW * 4);
+    // implicit kFan-ary fence levels over the key column; the top level must fit in shared memory.
+    // Every level (and the key column) is followed by >= kFan all-ones pad keys: fence groups never
+    // need bounds checks.
+    const uint64_t top_max = (kProbeTopBytes) / (NW * 4);
     std::vector<uint64_t> sizes{s->n_rows};
     while (sizes.back() > top_max) sizes.push_back(sizes.back() / kFan);
     if ((int) sizes.size() > kMaxLevels) return STAGE_ERR_ARG;
-    uint64_t total = 0;
-    for (size_t l = 1; l < sizes.size(); ++l) total += (sizes[l] + 3) & ~uint64_t(3);   // keep every level 16 B aligned
-    int rc = dev_alloc(s, &s->d_levels, total * NW);
-    if (rc) return rc;
     SnapshotView &v = s->view;
     v.n_levels = (int) sizes.size();
     v.level[0] = s->d_skey;
     v.level_n[0] = (uint32_t) sizes[0];
+    CUDA_TRY(cudaMemsetAsync(s->d_skey + s->n_rows * NW, 0xFF, 8 * NW * 4, s->stream));   // key-column pad
     uint64_t off = 0;
     for (size_t l = 1; l < sizes.size(); ++l) {
         uint32_t *dst = s->d_levels + off * NW;
-        const uint64_t nd = sizes[l];
-        if (nd) {
-            sample_level_kernel<NW><<<(unsigned) ((nd + 255) / 256), 256, 0, s->stream>>>(v.level[l - 1], dst, nd);
-            LAUNCH_CHECK();
-        }
+        const uint64_t nd = sizes[l], npad = (nd + 8) & ~uint64_t(3);
+        sample_level_kernel<NW><<<(unsigned) ((npad + 255) / 256), 256, 0, s->stream>>>(v.level[l - 1], dst, nd, npad);
+        LAUNCH_CHECK();
         v.level[l] = dst;
         v.level_n[l] = (uint32_t) nd;
-        off += (nd + 3) & ~uint64_t(3);
+        off += npad;
     }
     v.smem_words = (uint32_t) (sizes.back() * NW);
     return STAGE_OK;
@@ -736,12 +743,15 @@ static int launch_probe(stage_snapshot *s, const ProbeArgs &a) {
     static int occ[9] = {0};
     if (!occ[NW]) {
         int o = 0;
-        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, probe_kernel<NW>, kProbeThreads, 44 * 1024));
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, probe_kernel<NW, 4>, kProbeThreads, kProbeTopBytes));
         occ[NW] = std::max(o, 1);
     }
-    const uint64_t want_blocks = (a.n + kProbeThreads * kProbePerLane - 1) / (kProbeThreads * kProbePerLane);
+    static const int ppl = getenv("STAGE_PROBE_PPL") ? atoi(getenv("STAGE_PROBE_PPL")) : 4;
+    const uint64_t want_blocks = (a.n + kProbeThreads * ppl - 1) / (kProbeThreads * ppl);
     const unsigned blocks = (unsigned) std::min<uint64_t>(want_blocks, (uint64_t) sm_count() * occ[NW]);
-    probe_kernel<NW><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a);
+    if (ppl == 8) probe_kernel<NW, 8><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a);
+    else if (ppl == 4) probe_kernel<NW, 4><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a);
+    else probe_kernel<NW, 2><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a);
     LAUNCH_CHECK();
     return STAGE_OK;
 }

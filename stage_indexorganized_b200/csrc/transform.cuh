@@ -152,14 +152,16 @@ __global__ void __launch_bounds__(128) leaf_transform_kernel(TransformArgs a) {
     }
 }
 
-// sampled fence level: dst[i] = src[(i+1)*kFan - 1]  (kFan = 4, probe.cuh)
+// sampled fence level: dst[i] = src[(i+1)*kFan - 1] for i < n_dst, all-ones pad keys for n_dst <= i < n_pad
+// (kFan = 4, probe.cuh)
 template <int NW>
-__global__ void sample_level_kernel(const uint32_t *__restrict__ src, uint32_t *__restrict__ dst, uint64_t n_dst) {
+__global__ void sample_level_kernel(const uint32_t *__restrict__ src, uint32_t *__restrict__ dst, uint64_t n_dst,
+                                    uint64_t n_pad) {
     uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_dst) return;
+    if (i >= n_pad) return;
     uint64_t s = (i + 1) * 4 - 1;
 #pragma unroll
-    for (int w = 0; w < NW; ++w) dst[i * NW + w] = src[s * NW + w];
+    for (int w = 0; w < NW; ++w) dst[i * NW + w] = i < n_dst ? src[s * NW + w] : 0xFFFFFFFFu;
 }
 
 }  // namespace stage

@@ -338,6 +338,49 @@ def main():
                               "step_achieved": pbytes / (pms * 1e-3) / 1e9,
                               "step_frac": pbytes / (pms * 1e-3) / 1e9 / peak}}
 
+    # ---- probe leg at N > 1: range-routed probes, NCCL all-to-all of keys out and results back ------
+    if world > 1:
+        from stage_indexorganized_b200 import sharded
+        split = sharded.ycsb_splitters(rows * world, world)
+        d_pk = torch.from_numpy(pk_all.astype(np.uint32).view(np.uint8).reshape(n_batches, n_probes, K_BYTES)).to(dev)
+        d_owner = torch.empty((n_probes,), dtype=torch.int32, device=dev)
+
+        def local_probe(kin):
+            m = kin.shape[0]
+            f = torch.zeros((m,), dtype=torch.uint8, device=dev)
+            t = torch.zeros((m,), dtype=torch.int32, device=dev)
+            pay = torch.empty((m, P_BYTES), dtype=torch.uint8, device=dev)
+            if m:
+                snap.probe_device(kin, m, read_ts, f, t, None, pay)
+            return f, t, pay
+
+        def routed_step(b):
+            sg.route_device(d_pk[b], n_probes, split, d_owner, K_BYTES, stream.cuda_stream)
+            return sharded.routed_probe(d_pk[b], d_owner, local_probe, P_BYTES)
+
+        for b in range(args.warmup):
+            routed_step(b)
+        barrier()
+        pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        pe0.record(stream)
+        hits = 0
+        founds = []
+        for i in range(args.steps):
+            f, _, _ = routed_step(args.warmup + i)
+            founds.append(f)
+        pe1.record(stream)
+        barrier()
+        pms_t = torch.tensor([pe0.elapsed_time(pe1)], dtype=torch.float64, device=dev)
+        hit_t = torch.tensor([float(sum(int(f.sum().item()) for f in founds))], dtype=torch.float64, device=dev)
+        dist.all_reduce(pms_t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(hit_t, op=dist.ReduceOp.SUM)
+        nprobe = args.steps * n_probes * world
+        pms = float(pms_t.item())
+        probe = {"value": nprobe / (pms * 1e-3), "unit": "probes/s", "ms_per_step": pms / args.steps,
+                 "hit_rate": float(hit_t.item()) / nprobe, "routing": "stage_gpu_route_device + NCCL all-to-all "
+                 "(keys out, found/ts/payload back), results restored to request order",
+                 "nvlink_bytes_per_probe": (world - 1) / world * (2 * K_BYTES + 5 + P_BYTES)}
+
     # ---- max over ranks, whole-job aggregate ----------------------------------------------------
     t_ms = torch.tensor([total_ms], dtype=torch.float64, device=dev)
     r_sum = torch.tensor([rows_emitted], dtype=torch.float64, device=dev)

@@ -159,6 +159,11 @@ int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys, const uint
 int stage_gpu_route(const stage_schema_t *schema, const void *splitters, uint32_t n_shards, const void *keys,
                     uint64_t n, uint32_t *owner);
 
+/* Same on the device: keys_dev / owner_dev are device pointers, splitters stay on the host (n_shards <= 64).
+ * Launches on cuda_stream (cudaStream_t, may be NULL = default stream). */
+int stage_gpu_route_device(const stage_schema_t *schema, const void *splitters, uint32_t n_shards, const void *keys_dev,
+                           uint64_t n, uint32_t *owner_dev, void *cuda_stream);
+
 /* ---- utilities ---------------------------------------------------------------------------- */
 void *stage_gpu_host_alloc(size_t bytes); /* pinned host memory for STAGE_IO_HOST batches */
 void stage_gpu_host_free(void *p);

@@ -60,6 +60,7 @@ SYMBOLS = {
     "stage_gpu_probe_batch": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp, _vp, _vp, _i32]),
     "stage_gpu_scan_batch": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _vp, _vp, _i32]),
     "stage_gpu_route": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp]),
+    "stage_gpu_route_device": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp, _vp]),
     "stage_gpu_host_alloc": (_vp, [C.c_size_t]),
     "stage_gpu_host_free": (None, [_vp]),
     "stage_gpu_launch_count": (_u64, []),
@@ -281,3 +282,11 @@ def route(keys, splitters, key_size, key_kind=KEY_AUTO):
     _check(lib().stage_gpu_route(C.byref(sc), _ptr(splitters), splitters.shape[0] + 1, _ptr(keys), keys.shape[0],
                                  _ptr(owner)))
     return owner
+
+
+def route_device(keys_dev, n, splitters, owner_dev, key_size, cuda_stream=0, key_kind=KEY_AUTO):
+    """Device-side routing: owner_dev[i] = shard owning keys_dev[i] (torch tensors / device pointers)."""
+    splitters = np.ascontiguousarray(splitters, np.uint8).reshape(-1, key_size)
+    sc = Schema(key_size, 1, 65536, key_kind)
+    _check(lib().stage_gpu_route_device(C.byref(sc), _ptr(splitters), splitters.shape[0] + 1, _ptr(keys_dev), n,
+                                        _ptr(owner_dev), _vp(int(cuda_stream))))

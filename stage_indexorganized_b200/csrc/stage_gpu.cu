@@ -954,6 +954,55 @@ extern "C" int stage_gpu_route(const stage_schema_t *schema, const void *splitte
     return STAGE_OK;
 }
 
+// device-side routing: one thread per key, splitters (<= 63) passed by value in sortable form
+struct RouteArgs {
+    uint32_t split[64 * 8];
+    uint32_t n_split;
+};
+template <int NW>
+__global__ void route_kernel(RouteArgs r, const uint8_t *keys, uint64_t n, uint32_t key_size, uint32_t xormask,
+                             uint32_t *owner) {
+    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const SKey<NW> k = to_sortable<NW>(keys + i * key_size, key_size, xormask);
+    uint32_t lo = 0, hi = r.n_split;                 // owner = number of splitters < key
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        SKey<NW> sp;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) sp.w[w] = r.split[mid * NW + w];
+        if (skey_less<NW>(sp, k)) lo = mid + 1; else hi = mid;
+    }
+    owner[i] = lo;
+}
+
+extern "C" int stage_gpu_route_device(const stage_schema_t *schema, const void *splitters, uint32_t n_shards,
+                                      const void *keys_dev, uint64_t n, uint32_t *owner_dev, void *cuda_stream) {
+    int nw;
+    uint32_t xm;
+    int rc = schema_check(schema, &nw, &xm);
+    if (rc) return rc;
+    if (n_shards == 0 || n_shards > 64 || (n && (!keys_dev || !owner_dev)) || (n_shards > 1 && !splitters))
+        return STAGE_ERR_ARG;
+    if (n == 0) return STAGE_OK;
+    RouteArgs r{};
+    r.n_split = n_shards - 1;
+    for (uint32_t i = 0; i + 1 < n_shards; ++i)
+        host_sortable_nw(nw, static_cast<const uint8_t *>(splitters) + (size_t) i * schema->key_size, schema->key_size, xm,
+                         r.split + (size_t) i * nw);
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    const unsigned blocks = (unsigned) ((n + 255) / 256);
+    const uint8_t *k = static_cast<const uint8_t *>(keys_dev);
+    switch (nw) {
+        case 1: route_kernel<1><<<blocks, 256, 0, st>>>(r, k, n, schema->key_size, xm, owner_dev); break;
+        case 2: route_kernel<2><<<blocks, 256, 0, st>>>(r, k, n, schema->key_size, xm, owner_dev); break;
+        case 4: route_kernel<4><<<blocks, 256, 0, st>>>(r, k, n, schema->key_size, xm, owner_dev); break;
+        default: route_kernel<8><<<blocks, 256, 0, st>>>(r, k, n, schema->key_size, xm, owner_dev); break;
+    }
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 // utilities
 // ------------------------------------------------------------------------------------------------

@@ -1,0 +1,100 @@
+"""Range-partitioned table across the GPUs of one box: one process per GPU, torch.distributed for plumbing.
+
+Partitioning: shard g owns a contiguous range of the table in REFERENCE key order
+(include/vstore/b_tree.h:99-134 of the reference); ``splitters[g]`` = largest key of shard g (g < G-1).
+  * scans run shard-local on the shard that owns the start key (every shard also holds a halo of the next
+    shard's first rows, so a scan that starts in the shard completes there bit-exactly) — no data-path
+    collective, only the requests are routed;
+  * probes: owner = #splitters < key (``stage_gpu_route``), the batch is bucketed by owner, keys travel with
+    one all-to-all, every shard probes locally (probe_kernel + gather_rows_kernel), results travel back with
+    a second all-to-all and are restored to request order.
+
+The exchange logic is backend-agnostic (NCCL on GPUs, gloo in the CPU tests); the local lookup is injected.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def bucket_by_owner(owner, world):
+    """Stable bucketing: returns (perm, counts) with owner[perm] sorted ascending."""
+    owner = owner.to(torch.int64)
+    perm = torch.argsort(owner, stable=True)
+    counts = torch.bincount(owner, minlength=world)[:world]
+    return perm, counts
+
+
+def exchange_counts(counts, group=None):
+    """send counts [world] -> recv counts [world] (recv[j] = what rank j sends to me)."""
+    recv = torch.empty_like(counts)
+    dist.all_to_all_single(recv, counts, group=group)
+    return recv
+
+
+def all_to_all_rows(rows, send_counts, recv_counts, group=None):
+    """rows: [n_send, ...] grouped by destination rank. Returns [n_recv, ...] grouped by source rank."""
+    n_recv = int(recv_counts.sum().item())
+    out = torch.empty((n_recv,) + tuple(rows.shape[1:]), dtype=rows.dtype, device=rows.device)
+    dist.all_to_all_single(out, rows.contiguous(), output_split_sizes=[int(x) for x in recv_counts.tolist()],
+                           input_split_sizes=[int(x) for x in send_counts.tolist()], group=group)
+    return out
+
+
+def routed_probe(keys, owner, local_probe, payload_size, group=None):
+    """Distributed batched point probe.
+
+    keys  : [n, K] uint8 tensor (this rank's requests), owner: [n] shard index per key.
+    local_probe(keys_local [m, K]) -> (found u8 [m], ts i32 [m], payload u8 [m, P]) on the same device.
+    Returns (found [n], ts [n], payload [n, P]) in request order.
+    """
+    world = dist.get_world_size(group)
+    perm, send_counts = bucket_by_owner(owner, world)
+    recv_counts = exchange_counts(send_counts, group)
+    keys_sorted = keys.index_select(0, perm)
+    keys_in = all_to_all_rows(keys_sorted, send_counts, recv_counts, group)            # requests I own
+    found_l, ts_l, pay_l = local_probe(keys_in)
+    # results travel back along the reverse routes
+    found_b = all_to_all_rows(found_l, recv_counts, send_counts, group)
+    ts_b = all_to_all_rows(ts_l, recv_counts, send_counts, group)
+    pay_b = all_to_all_rows(pay_l, recv_counts, send_counts, group)
+    n = keys.shape[0]
+    found = torch.empty(n, dtype=found_b.dtype, device=keys.device)
+    ts = torch.empty(n, dtype=ts_b.dtype, device=keys.device)
+    pay = torch.empty((n, payload_size), dtype=torch.uint8, device=keys.device)
+    found.index_copy_(0, perm, found_b)
+    ts.index_copy_(0, perm, ts_b)
+    pay.index_copy_(0, perm, pay_b)
+    return found, ts, pay
+
+
+def routed_scan_requests(start_keys, sizes, owner, group=None):
+    """Route scan requests to the shard owning each start key. Returns (keys_in, sizes_in, perm, send_counts,
+    recv_counts): the requests this rank must run, plus what is needed to send row counts back."""
+    world = dist.get_world_size(group)
+    perm, send_counts = bucket_by_owner(owner, world)
+    recv_counts = exchange_counts(send_counts, group)
+    keys_in = all_to_all_rows(start_keys.index_select(0, perm), send_counts, recv_counts, group)
+    sizes_in = all_to_all_rows(sizes.index_select(0, perm), send_counts, recv_counts, group)
+    return keys_in, sizes_in, perm, send_counts, recv_counts
+
+
+def gather_scan_counts(row_counts_local, perm, send_counts, recv_counts, group=None):
+    """The 'gather' that follows shard-local scans: per-scan row counts back to the requesters, request order."""
+    back = all_to_all_rows(row_counts_local, recv_counts, send_counts, group)
+    out = torch.empty_like(back)
+    out.index_copy_(0, perm, back)
+    return out
+
+
+def shard_bounds(n_rows_total, world):
+    """Equal-size range shards over ranks of the key order: [first_rank, end_rank) per shard."""
+    per = (n_rows_total + world - 1) // world
+    return [(min(g * per, n_rows_total), min((g + 1) * per, n_rows_total)) for g in range(world)]
+
+
+def ycsb_splitters(n_rows_total, world):
+    """Splitter keys (uint8 [world-1, 4]) of equal-size shards of the YCSB int table 0..N-1."""
+    from .ycsb import rank_to_key
+    b = shard_bounds(n_rows_total, world)
+    last = np.array([b[g][1] - 1 for g in range(world - 1)], np.int64)
+    return rank_to_key(n_rows_total, last).astype(np.uint32).view(np.uint8).reshape(-1, 4)

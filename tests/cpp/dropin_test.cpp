@@ -1,0 +1,250 @@
+// tests/cpp/dropin_test.cpp — drop-in test of the C++ adapters (include/stage_gpu_executors.h) against the
+// UNMODIFIED reference classes, in one process, on one tree.
+//
+// The table is built with the reference's own BTree exactly as its loaders do (Insert + FinalizeInsert,
+// benchmark/ycsb/ycsb_loader.cpp:93-173). Then, with a real SSNTransactionManager / TransactionContext:
+//   * mvstore::IndexScanExecutor<const char*, T>  (point_lookup)   vs  stage_gpu::GpuIndexScanExecutor
+//   * mvstore::TableScanExecutor<const char*, T>  (range, by value) vs  stage_gpu::GpuTableScanExecutor
+//   * mvstore::BTree::Read / RangeScanBySize / Iterator::GetNext    vs  stage_gpu::GpuTreeView / GpuIterator
+// are run on the same key streams (the drivers' FastRandom / ZipfDistribution generators,
+// benchmark/benchmark_common.h:12-105) and every returned struct is compared byte for byte. The
+// reference's *range* IndexScanExecutor keeps pointers into Records it has already freed
+// (include/execute/executor.h:476-484), so its by-value sibling TableScanExecutor is the range checker.
+//
+// Built only where /root/reference exists (oracle/Makefile.ref -> oracle/_ref/dropin_test, which travels to
+// the GPU box); run by tests/test_gpu_dropin_cpp.py. `--ref-only` runs the reference half alone (no GPU).
+// TEST CODE: the reference here is the checker, never the product.
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "execute/executor.h"
+#include "benchmark_common.h"
+#include "../../include/stage_gpu_executors.h"
+
+using namespace mvstore;
+
+// the tuple shapes the YCSB driver instantiates the executors with (benchmark/ycsb/ycsb_configuration.h:22-58)
+struct TupleInt {
+    uint32_t key;
+    char cols[10][100];
+};
+struct TupleStr {
+    char key[16];
+    char cols[10][100];
+};
+// TPC-C stock shape: 16-byte key, 400-byte payload region (benchmark/tpcc/tpcc_record.h:417-510)
+struct TupleStock {
+    char key[16];
+    char body[400];
+};
+
+static int g_fail = 0;
+#define EXPECT(cond, ...)                                   \
+    do {                                                    \
+        if (!(cond)) {                                      \
+            if (g_fail < 20) { printf("FAIL %s:%d: ", __FILE__, __LINE__); printf(__VA_ARGS__); printf("\n"); } \
+            ++g_fail;                                       \
+        }                                                   \
+    } while (0)
+
+struct Table {
+    BTree *tree;
+    Catalog *catalog;
+    uint32_t K, P;
+};
+
+static Table make_table(uint32_t K, uint32_t P, uint32_t split, uint64_t blocks) {
+    Table t{};
+    t.K = K;
+    t.P = P;
+    t.catalog = new Catalog();
+    uint8_t *bitmap = new uint8_t[2]{1, 0};
+    t.catalog->init("table0", 2, bitmap, K, 1, false);
+    t.catalog->add_col("Key", K, "VARCHAR");
+    t.catalog->add_col("payload", P, "VARCHAR");
+    ParameterSet param(split, 32 * 1024, 64 * 1024, P);
+    auto *leaf_pool = new DramBlockPool(blocks, blocks);
+    auto *inner = new InnerNodeBuffer(new RecordBufferPool(5000000, 5000000));
+    auto *undo = new EphemeralPool(new UndoBuffer(new RecordBufferPool(5000000, 5000000)));
+    SSNTransactionManager::GetInstance()->Init(undo);
+    t.tree = new BTree(param, *t.catalog, leaf_pool, inner, undo);
+    return t;
+}
+
+static void insert_row(Table &t, const char *key, const char *payload) {
+    RecordMeta meta;
+    ReturnCode rc = t.tree->Insert(key, (uint16_t) t.K, payload, &meta, INVALID_CID);
+    if (!rc.IsOk()) return;
+    auto *mp = reinterpret_cast<RecordMetadata *>(meta.GetMetaData().GetLocationPtr()->record_meta_ptr);
+    t.tree->FinalizeInsert(mp, INVALID_CID);
+    t.tree->IncreaseTupleCount(1);
+}
+
+template <class T>
+static int run_checks(Table &t, const std::vector<std::string> &probe_keys, const std::vector<std::string> &scan_keys,
+                      uint32_t scan_size, bool ref_only, const char *what) {
+    auto *mgr = SSNTransactionManager::GetInstance();
+    std::unique_ptr<stage_gpu::GpuTreeView> view;
+    if (!ref_only) view.reset(new stage_gpu::GpuTreeView(t.tree->GetRootNodeSafe(), t.K, t.P));
+    uint64_t hits = 0, rows = 0, crc = 0;
+    const int fail0 = g_fail;
+
+    // --- point lookups through the executors ------------------------------------------------------------
+    for (const std::string &k : probe_keys) {
+        TransactionContext *txn = mgr->BeginTransaction(0, IsolationLevelType::SERIALIZABLE);
+        txn->SetReadOnly();
+        IndexScanExecutor<const char *, T> ref(t.tree, (uint16_t) t.K, k.data(), 1, true, nullptr, false, txn, nullptr);
+        EXPECT(ref.Execute(), "reference Execute");
+        const T *want = ref.GetRecord();
+        if (want) { ++hits; for (size_t i = 0; i < sizeof(T); i += 97) crc = crc * 131 + ((const uint8_t *) want)[i]; }
+        if (!ref_only) {
+            stage_gpu::GpuIndexScanExecutor<const char *, T, TransactionContext> gpu(view.get(), (uint16_t) t.K, k.data(), 1, true,
+                                                                                    nullptr, false, txn, nullptr);
+            EXPECT(gpu.Execute(), "gpu Execute");
+            const T *got = gpu.GetRecord();
+            EXPECT((got == nullptr) == (want == nullptr), "%s point: found mismatch", what);
+            if (got && want) EXPECT(memcmp(got, want, sizeof(T)) == 0, "%s point: tuple bytes differ", what);
+            // tree-level shape: BTree::Read vs GpuTreeView::Read (latest in-leaf version, cstamp = reader id)
+            std::unique_ptr<Record> r = t.tree->Read(k.data(), (uint16_t) t.K, txn->GetReadId(), false);
+            std::unique_ptr<stage_gpu::Record> g = view->Read(k.data(), (uint16_t) t.K, txn->GetReadId(), false);
+            EXPECT((r == nullptr) == (g == nullptr), "%s Read: found mismatch", what);
+            if (r && g) {
+                EXPECT(memcmp(r->GetData(), g->GetData(), r->GetKeyPaddedLength() + t.P) == 0, "%s Read: data differs", what);
+                EXPECT(r->GetCstamp() == g->GetCstamp(), "%s Read: cstamp", what);
+                EXPECT(r->meta.meta_data.GetTxnCommitId() == g->commit_id, "%s Read: commit id", what);
+                EXPECT(r->GetKeyPaddedLength() == g->GetKeyPaddedLength(), "%s Read: padded key length", what);
+            }
+            if (r) delete[] reinterpret_cast<char *>(r.release());
+        }
+        delete want;
+        mgr->CommitTransaction(txn);
+    }
+
+    // --- range scans through the executors and the iterator ------------------------------------------------
+    for (const std::string &k : scan_keys) {
+        TransactionContext *txn = mgr->BeginTransaction(0, IsolationLevelType::SERIALIZABLE);
+        txn->SetReadOnly();
+        TableScanExecutor<const char *, T> ref(t.tree, k.data(), t.K, scan_size, txn, nullptr);
+        EXPECT(ref.Execute(), "reference scan Execute");
+        std::vector<T> &want = ref.GetResults();
+        rows += want.size();
+        if (!ref_only) {
+            stage_gpu::GpuTableScanExecutor<const char *, T, TransactionContext> gpu(view.get(), k.data(), t.K, scan_size, txn,
+                                                                                    nullptr);
+            EXPECT(gpu.Execute(), "gpu scan Execute");
+            std::vector<T> &got = gpu.GetResults();
+            EXPECT(got.size() == want.size(), "%s scan: %zu rows, reference %zu", what, got.size(), want.size());
+            EXPECT(gpu.GetFailNum() == ref.GetFailNum(), "%s scan: fail_num %u vs %u", what, gpu.GetFailNum(), ref.GetFailNum());
+            if (got.size() == want.size())
+                for (size_t i = 0; i < got.size(); ++i)
+                    EXPECT(memcmp(&got[i], &want[i], sizeof(T)) == 0, "%s scan: row %zu differs", what, i);
+            // IndexScanExecutor range shape with a predicate (called once per visible row, result ignored)
+            uint32_t pred_calls = 0;
+            stage_gpu::GpuIndexScanExecutor<const char *, T, TransactionContext> gi(
+                view.get(), (uint16_t) t.K, k.data(), scan_size, false,
+                [&](const T *, bool &) { ++pred_calls; return true; }, false, txn, nullptr);
+            EXPECT(gi.Execute(), "gpu index range Execute");
+            EXPECT(gi.GetResults().size() == want.size() && pred_calls == want.size(), "%s index range: row count", what);
+            for (size_t i = 0; i < gi.GetResults().size() && i < want.size(); ++i)
+                EXPECT(memcmp(gi.GetResults()[i], &want[i], sizeof(T)) == 0, "%s index range: row %zu differs", what, i);
+            // iterator shape
+            auto it_ref = t.tree->RangeScanBySize(k.data(), (uint16_t) t.K, scan_size);
+            auto it_gpu = view->RangeScanBySize(k.data(), (uint16_t) t.K, scan_size);
+            for (uint32_t s = 0; s < scan_size; ++s) {
+                std::unique_ptr<Record> r = it_ref->GetNext();
+                if (!r) continue;                                      // executor.h:629-632: a null GetNext is skipped
+                std::unique_ptr<stage_gpu::Record> g = it_gpu->GetNext();
+                EXPECT(g != nullptr, "%s iterator: gpu ran out at step %u", what, s);
+                if (g) EXPECT(memcmp(r->GetData(), g->GetData(), r->GetKeyPaddedLength() + t.P) == 0, "%s iterator: row differs", what);
+                delete[] reinterpret_cast<char *>(r.release());
+            }
+            EXPECT(it_gpu->GetNext() == nullptr, "%s iterator: gpu has extra rows", what);
+        }
+        mgr->CommitTransaction(txn);
+    }
+    printf("%-12s probes %zu (hits %lu) scans %zu x %u (rows %lu) crc %016lx : %s\n", what, probe_keys.size(), hits,
+           scan_keys.size(), scan_size, rows, crc, g_fail == fail0 ? "OK" : "FAILED");
+    return g_fail - fail0;
+}
+
+int main(int argc, char **argv) {
+    bool ref_only = false;
+    uint32_t n_rows = 20000, n_probe = 2000, n_scan = 60;
+    for (int i = 1; i < argc; ++i) {
+        if (!strcmp(argv[i], "--ref-only")) ref_only = true;
+        else if (!strcmp(argv[i], "--rows") && i + 1 < argc) n_rows = (uint32_t) atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--probes") && i + 1 < argc) n_probe = (uint32_t) atoi(argv[++i]);
+    }
+    if (!ref_only) stage_gpu::check(stage_gpu_init(0), "stage_gpu_init");
+
+    // ---- YCSB int table (ycsb_loader.cpp:144-172) and the driver's key streams ---------------------------------
+    {
+        Table t = make_table(4, 1000, 16 * 1024, n_rows / 16 + 4096);
+        std::vector<char> payload(1000);
+        for (uint32_t rowid = 0; rowid < n_rows; ++rowid) {
+            memset(payload.data(), (int) rowid, payload.size());
+            insert_row(t, reinterpret_cast<const char *>(&rowid), payload.data());
+        }
+        benchmark::FastRandom rng(1);
+        benchmark::ZipfDistribution zipf(n_rows - 1, 0.2);
+        std::vector<std::string> probes, scans;
+        for (uint32_t i = 0; i < n_probe; ++i) {
+            uint32_t k = i % 2 ? (uint32_t) (1 + rng.next() % n_rows) : (uint32_t) zipf.GetNextNumber();   // 1..N: key N misses
+            probes.emplace_back(reinterpret_cast<const char *>(&k), 4);
+        }
+        for (uint32_t extra : {0u, n_rows, n_rows + 7, 0xFFFFFFFFu, 0x80808080u})
+            probes.emplace_back(reinterpret_cast<const char *>(&extra), 4);
+        for (uint32_t i = 0; i < n_scan; ++i) {
+            uint32_t k = (uint32_t) (rng.next() % n_rows);
+            scans.emplace_back(reinterpret_cast<const char *>(&k), 4);
+        }
+        run_checks<TupleInt>(t, probes, scans, 1000, ref_only, "ycsb-int");
+        run_checks<TupleInt>(t, {}, scans, 10, ref_only, "ycsb-int/10");
+    }
+    // ---- YCSB string table (ycsb_loader.cpp:107-143): 16 random bytes per key, payload 1000 x 'a' ---------------
+    {
+        const uint32_t n = n_rows / 2;
+        Table t = make_table(16, 1000, 16 * 1024, n / 16 + 4096);
+        benchmark::FastRandom krng(1804289383);
+        std::vector<std::string> keys;
+        std::vector<char> payload(1000, 'a');
+        for (uint32_t i = 0; i < n; ++i) {
+            keys.push_back(krng.next_string(16));
+            insert_row(t, keys.back().data(), payload.data());
+        }
+        benchmark::FastRandom rng(1);
+        benchmark::ZipfDistribution zipf(n - 1, 0.9);
+        std::vector<std::string> probes, scans;
+        for (uint32_t i = 0; i < n_probe; ++i) probes.push_back(keys[zipf.GetNextNumber() % n]);
+        for (uint32_t i = 0; i < 50; ++i) probes.push_back(rng.next_string(16));                // misses
+        for (uint32_t i = 0; i < n_scan; ++i) scans.push_back(i % 4 ? keys[rng.next() % n] : rng.next_string(16));
+        run_checks<TupleStr>(t, probes, scans, 1000, ref_only, "ycsb-string");
+    }
+    // ---- stock-shaped table: 16-byte memcmp keys, 400-byte rows, TPC-C ParameterSet (tpcc.cpp:78) ----------------
+    {
+        const uint32_t n = n_rows / 2;
+        Table t = make_table(16, 400, 64 * 1024, n / 64 + 4096);
+        std::vector<std::string> keys;
+        std::vector<char> payload(400);
+        for (uint32_t i = 0; i < n; ++i) {
+            // {s_w_id, s_i_id} as two 8-byte integers, the shape of Stock::StockKey (tpcc_record.h:417-430)
+            uint64_t kk[2] = {i % 30, i / 30};
+            std::string k(reinterpret_cast<const char *>(kk), 16);
+            for (uint32_t b = 0; b < 400; ++b) payload[b] = (char) ((i * 7 + b) & 0xFF);
+            memcpy(payload.data(), k.data(), 16);
+            keys.push_back(k);
+            insert_row(t, k.data(), payload.data());
+        }
+        benchmark::FastRandom rng(7);
+        std::vector<std::string> probes, scans;
+        for (uint32_t i = 0; i < n_probe; ++i) probes.push_back(keys[rng.next() % n]);
+        for (uint32_t i = 0; i < n_scan; ++i) scans.push_back(keys[rng.next() % n]);
+        run_checks<TupleStock>(t, probes, scans, 10, ref_only, "stock");       // stock-level scans 10 rows
+    }
+    printf("%s: %d failure(s)\n", ref_only ? "reference half only" : "drop-in parity", g_fail);
+    return g_fail ? 1 : 0;
+}

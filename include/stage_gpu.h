@@ -164,6 +164,43 @@ int stage_gpu_route(const stage_schema_t *schema, const void *splitters, uint32_
 int stage_gpu_route_device(const stage_schema_t *schema, const void *splitters, uint32_t n_shards, const void *keys_dev,
                            uint64_t n, uint32_t *owner_dev, void *cuda_stream);
 
+/* ---- routed probes over peer memory (N GPUs, one process per GPU) ----------------------------- */
+
+/* The probe exchange: every rank owns an "arena" in its HBM — an inbox per source rank and the
+ * result slab of its own requests — that all other ranks map (CUDA IPC over NVLink / NVSwitch). A routed batch is
+ *   post   : route this rank's keys and store (key, request index) straight into the owners' inboxes
+ *   serve  : search + MVCC over this rank's inboxes on its shard, payload rows written straight into the
+ *            requesters' result slabs at the row of the original request (request order, no return collective).
+ * Hand-offs: with STAGE_XCHG_DEVICE_SYNC the kernels signal / wait through epoch flags in the arenas (every rank
+ * must call post, serve and wait once per batch, in that order, on one stream); without it the caller places a
+ * barrier across ranks between post and serve and another after serve (e.g. a stream-ordered NCCL all-reduce).
+ * capacity = the largest batch (probes per rank per call). world <= 16. */
+typedef struct stage_exchange stage_exchange_t;
+enum { STAGE_IPC_HANDLE_BYTES = 64, STAGE_XCHG_DEVICE_SYNC = 1 };
+
+int stage_gpu_exchange_create(uint32_t world, uint32_t rank, uint64_t capacity, const stage_schema_t *schema,
+                              stage_exchange_t **out);
+/* 64-byte CUDA IPC handle of this rank's arena, to be all-gathered by the caller's control plane. */
+int stage_gpu_exchange_ipc_handle(stage_exchange_t *x, void *handle_out);
+/* handles: world x STAGE_IPC_HANDLE_BYTES, indexed by rank (the own entry is ignored). */
+int stage_gpu_exchange_attach_ipc(stage_exchange_t *x, const void *handles);
+/* Same-process peers (several ranks driven by one process, peer access already enabled): arena pointers by rank. */
+int stage_gpu_exchange_attach_ptrs(stage_exchange_t *x, void *const *arenas);
+void *stage_gpu_exchange_arena(stage_exchange_t *x);
+/* splitters: (world-1) x key_size host bytes, the largest key of every shard but the last (as stage_gpu_route).
+ * keys_dev: n x key_size device bytes, n <= capacity. cuda_stream: cudaStream_t (NULL = default stream). */
+int stage_gpu_exchange_post(stage_exchange_t *x, const void *splitters, const void *keys_dev, uint64_t n, int flags,
+                            void *cuda_stream);
+int stage_gpu_exchange_serve(stage_exchange_t *x, stage_snapshot_t *shard, uint32_t read_ts, int flags, void *cuda_stream);
+/* STAGE_XCHG_DEVICE_SYNC only: stream-ordered wait until every owner has served this rank's batch. */
+int stage_gpu_exchange_wait(stage_exchange_t *x, void *cuda_stream);
+/* Device pointers (local) of this rank's result slab, rows in request order: found u8[capacity], ts u32[capacity],
+ * payload u8[capacity][payload_size]. Rows of missed probes keep their previous content. */
+int stage_gpu_exchange_results(stage_exchange_t *x, void **found, void **ts, void **payload);
+/* Sticky device-side error of the exchange: 0 ok, 1 inbox overflow, 2 device-sync timeout. Synchronises the stream. */
+int stage_gpu_exchange_error(stage_exchange_t *x, void *cuda_stream, uint32_t *err_out);
+int stage_gpu_exchange_destroy(stage_exchange_t *x);
+
 /* ---- utilities ---------------------------------------------------------------------------- */
 void *stage_gpu_host_alloc(size_t bytes); /* pinned host memory for STAGE_IO_HOST batches */
 void stage_gpu_host_free(void *p);

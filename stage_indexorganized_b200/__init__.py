@@ -20,6 +20,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libstage_gpu.so")
 
 IO_HOST, IO_DEVICE = 0, 1
+XCHG_DEVICE_SYNC = 1
+IPC_HANDLE_BYTES = 64
 KEY_AUTO, KEY_SIGNED_BYTES, KEY_MEMCMP = 0, 1, 2
 
 _vp, _u32, _u64, _i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int
@@ -61,6 +63,17 @@ SYMBOLS = {
     "stage_gpu_scan_batch": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _vp, _vp, _i32]),
     "stage_gpu_route": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp]),
     "stage_gpu_route_device": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp, _vp]),
+    "stage_gpu_exchange_create": (_i32, [_u32, _u32, _u64, C.POINTER(Schema), C.POINTER(_vp)]),
+    "stage_gpu_exchange_ipc_handle": (_i32, [_vp, _vp]),
+    "stage_gpu_exchange_attach_ipc": (_i32, [_vp, _vp]),
+    "stage_gpu_exchange_attach_ptrs": (_i32, [_vp, _vp]),
+    "stage_gpu_exchange_arena": (_vp, [_vp]),
+    "stage_gpu_exchange_post": (_i32, [_vp, _vp, _vp, _u64, _i32, _vp]),
+    "stage_gpu_exchange_serve": (_i32, [_vp, _vp, _u32, _i32, _vp]),
+    "stage_gpu_exchange_wait": (_i32, [_vp, _vp]),
+    "stage_gpu_exchange_results": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)]),
+    "stage_gpu_exchange_error": (_i32, [_vp, _vp, C.POINTER(_u32)]),
+    "stage_gpu_exchange_destroy": (_i32, [_vp]),
     "stage_gpu_host_alloc": (_vp, [C.c_size_t]),
     "stage_gpu_host_free": (None, [_vp]),
     "stage_gpu_launch_count": (_u64, []),
@@ -290,3 +303,80 @@ def route_device(keys_dev, n, splitters, owner_dev, key_size, cuda_stream=0, key
     sc = Schema(key_size, 1, 65536, key_kind)
     _check(lib().stage_gpu_route_device(C.byref(sc), _ptr(splitters), splitters.shape[0] + 1, _ptr(keys_dev), n,
                                         _ptr(owner_dev), _vp(int(cuda_stream))))
+
+
+class _DeviceView:
+    """Minimal __cuda_array_interface__ carrier so torch.as_tensor can wrap library-owned device memory."""
+
+    def __init__(self, ptr, shape, typestr, owner):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+        self._owner = owner
+
+
+class ProbeExchange:
+    """Routed point probes over peer memory (include/stage_gpu.h, "routed probes over peer memory"): this rank's
+    arena (inboxes + result slab) and the mappings of every peer's arena. One instance per rank."""
+
+    def __init__(self, world, rank, capacity, key_size, payload_size, key_kind=KEY_AUTO):
+        self.world, self.rank, self.capacity = world, rank, capacity
+        self.schema = Schema(key_size, payload_size, 65536, key_kind)
+        self.h = _vp()
+        _check(lib().stage_gpu_exchange_create(world, rank, capacity, C.byref(self.schema), C.byref(self.h)))
+
+    def ipc_handle(self):
+        buf = (C.c_uint8 * IPC_HANDLE_BYTES)()
+        _check(lib().stage_gpu_exchange_ipc_handle(self.h, C.cast(buf, _vp)))
+        return bytes(buf)
+
+    def attach_ipc(self, handles):
+        """handles: list of `world` 64-byte IPC handles indexed by rank."""
+        blob = b"".join(handles)
+        assert len(blob) == self.world * IPC_HANDLE_BYTES
+        _check(lib().stage_gpu_exchange_attach_ipc(self.h, C.cast(C.c_char_p(blob), _vp)))
+
+    def attach_ptrs(self, arenas):
+        arr = (C.c_void_p * self.world)(*[int(a) if a else None for a in arenas])
+        _check(lib().stage_gpu_exchange_attach_ptrs(self.h, C.cast(arr, _vp)))
+
+    def arena(self):
+        return int(lib().stage_gpu_exchange_arena(self.h))
+
+    def post(self, splitters, keys_dev, n, flags=0, cuda_stream=0):
+        sp = None
+        if self.world > 1:
+            sp = np.ascontiguousarray(splitters, np.uint8).reshape(self.world - 1, self.schema.key_size)
+        _check(lib().stage_gpu_exchange_post(self.h, _ptr(sp), _ptr(keys_dev), n, flags, _vp(int(cuda_stream))))
+
+    def serve(self, shard, read_ts, flags=0, cuda_stream=0):
+        _check(lib().stage_gpu_exchange_serve(self.h, shard.h, read_ts, flags, _vp(int(cuda_stream))))
+
+    def wait(self, cuda_stream=0):
+        _check(lib().stage_gpu_exchange_wait(self.h, _vp(int(cuda_stream))))
+
+    def error(self, cuda_stream=0):
+        e = _u32(0)
+        _check(lib().stage_gpu_exchange_error(self.h, _vp(int(cuda_stream)), C.byref(e)))
+        return int(e.value)
+
+    def result_ptrs(self):
+        f, t, p = _vp(), _vp(), _vp()
+        _check(lib().stage_gpu_exchange_results(self.h, C.byref(f), C.byref(t), C.byref(p)))
+        return int(f.value), int(t.value), int(p.value)
+
+    def results_torch(self, n=None):
+        """(found u8[n], ts i32[n], payload u8[n,P]) torch views of the result slab (no copy)."""
+        import torch
+        n = self.capacity if n is None else n
+        f, t, p = self.result_ptrs()
+        P = self.schema.payload_size
+        dev = torch.device("cuda", torch.cuda.current_device())
+        found = torch.as_tensor(_DeviceView(f, (n,), "|u1", self), device=dev)
+        ts = torch.as_tensor(_DeviceView(t, (n,), "<i4", self), device=dev)
+        pay = torch.as_tensor(_DeviceView(p, (n, P), "|u1", self), device=dev)
+        return found, ts, pay
+
+    def close(self):
+        if self.h:
+            _check(lib().stage_gpu_exchange_destroy(self.h))
+            self.h = None

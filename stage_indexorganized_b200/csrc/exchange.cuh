@@ -1,0 +1,295 @@
+// exchange.cuh — routed point probes over peer memory: the probe kernels fused with their exchange.
+//
+// Range partitioning: shard g owns a contiguous range of the table in reference key order;
+// a probe must run on the GPU that owns its key. Instead of all-to-all collectives around the local kernels
+// (keys out, results back, then a permutation back into request order), every GPU maps every other GPU's
+// exchange arena (NVLink 5 / NVSwitch peer memory) and the kernels address it directly:
+//
+//   post   (requester)  route each key (owner = #splitters < key), claim a slot of the owner's inbox and store
+//                       the key and the request index there                        -- peer stores, 8 B / probe
+//   serve  (owner)      search + MVCC over its inboxes (fence_search, probe.cuh), then stream every found
+//                       payload row from local HBM straight into the REQUESTER's result slab at the row of
+//                       the original request                                       -- peer stores, P B / hit
+//
+// Results therefore land in request order with no return collective and no restore-order pass. The two
+// hand-offs (posts visible before serving, rows visible before the requester reads them) are either a
+// caller-side barrier or — STAGE_XCHG_DEVICE_SYNC — epoch flags written into the peers' arenas with
+// system-scope release stores and polled locally with acquire loads (bounded spin, sticky error flag).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "gather.cuh"
+#include "keys.cuh"
+#include "probe.cuh"
+
+namespace stage {
+
+constexpr int kMaxExchangeRanks = 16;
+constexpr uint32_t kDstRankShift = 28;                 // dst_slot = (requester rank << 28) | request index
+constexpr uint32_t kDstIndexMask = (1u << kDstRankShift) - 1;
+
+// Offsets inside one rank's arena; the layout is identical on every rank.
+struct ExchangeLayout {
+    uint64_t off_count;     // u32 [world]           requests posted by each source rank (this batch)
+    uint64_t off_posted;    // u32 [world]           epoch flag: source rank's posts are complete
+    uint64_t off_served;    // u32 [world]           epoch flag: owner rank has written all my rows
+    uint64_t off_keys;      // u8  [world][cap][kpad] inbox: keys
+    uint64_t off_req;       // u32 [world][cap]       inbox: request index at the source
+    uint64_t off_found;     // u8  [cap]              result slab of THIS rank's requests
+    uint64_t off_ts;        // u32 [cap]
+    uint64_t off_payload;   // u8  [cap][P]
+    uint64_t bytes;
+    uint32_t cap, kpad;
+};
+
+struct ExchangeView {
+    uint8_t *arena[kMaxExchangeRanks];   // arena of every rank as mapped in this process (arena[rank] = local)
+    ExchangeLayout lay;
+    uint32_t world, rank;
+    uint32_t *local_cnt;                 // [world] slots claimed per owner while posting (local scratch)
+    uint32_t *err;                       // sticky: 1 inbox overflow, 2 device-sync timeout
+};
+
+struct ExchangeSplit {
+    uint32_t w[(kMaxExchangeRanks - 1) * 8];   // splitters in sortable form, NW words each
+};
+
+// ---- system-scope flag helpers ------------------------------------------------------------------------
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint64_t global_ns() {
+    uint64_t t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// Thread 0 of the CTA waits until flags[0..world) all carry `epoch`; everyone leaves through the barrier.
+__device__ __forceinline__ void cta_wait_flags(const uint32_t *flags, uint32_t world, uint32_t epoch, uint32_t *err) {
+    if (threadIdx.x == 0) {
+        const uint64_t t0 = global_ns();
+        for (uint32_t s = 0; s < world; ++s) {
+            while (ld_acquire_sys(flags + s) != epoch) {
+                if (global_ns() - t0 > 4000000000ull) {          // 4 s: a peer died; fail loudly, do not hang the box
+                    atomicExch(err, 2u);
+                    break;
+                }
+                __nanosleep(200);
+            }
+        }
+    }
+    __syncthreads();
+}
+
+// ---- post ---------------------------------------------------------------------------------------------
+// One tile of 256 keys per iteration: owner of every key, slot claim (shared-memory counters, then one
+// atomic per owner per tile on the local running counters), peer store of key + request index.
+template <int NW>
+__global__ void __launch_bounds__(256) exchange_post_kernel(ExchangeView x, ExchangeSplit sp, const uint8_t *keys, uint64_t n,
+                                                            uint32_t key_size, uint32_t xormask) {
+    __shared__ uint32_t s_cnt[kMaxExchangeRanks], s_base[kMaxExchangeRanks];
+    const int tid = threadIdx.x;
+    const uint64_t tiles = (n + 255) / 256;
+    for (uint64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        if (tid < kMaxExchangeRanks) s_cnt[tid] = 0;
+        __syncthreads();
+        const uint64_t i = tile * 256 + tid;
+        uint32_t owner = 0, pos = 0;
+        if (i < n) {
+            const SKey<NW> k = to_sortable<NW>(keys + i * key_size, key_size, xormask);
+            uint32_t lo = 0, hi = x.world - 1;                   // owner = number of splitters < key
+            while (lo < hi) {
+                const uint32_t mid = (lo + hi) >> 1;
+                SKey<NW> s;
+#pragma unroll
+                for (int w = 0; w < NW; ++w) s.w[w] = sp.w[mid * NW + w];
+                if (skey_less<NW>(s, k)) lo = mid + 1; else hi = mid;
+            }
+            owner = lo;
+            pos = atomicAdd(&s_cnt[owner], 1u);
+        }
+        __syncthreads();
+        if (tid < (int) x.world && s_cnt[tid]) s_base[tid] = atomicAdd(x.local_cnt + tid, s_cnt[tid]);
+        __syncthreads();
+        if (i < n) {
+            const uint32_t p = s_base[owner] + pos;
+            if (p < x.lay.cap) {
+                uint8_t *inbox = x.arena[owner];
+                const uint64_t slot = (uint64_t) x.rank * x.lay.cap + p;
+                uint8_t *kd = inbox + x.lay.off_keys + slot * x.lay.kpad;
+                const uint8_t *ks = keys + i * key_size;
+                if ((key_size & 3u) == 0 && ((uintptr_t) ks & 3u) == 0) {
+                    for (uint32_t b = 0; b < key_size; b += 4)
+                        *reinterpret_cast<uint32_t *>(kd + b) = *reinterpret_cast<const uint32_t *>(ks + b);
+                } else {
+                    for (uint32_t b = 0; b < key_size; ++b) kd[b] = ks[b];
+                }
+                reinterpret_cast<uint32_t *>(inbox + x.lay.off_req)[slot] = (uint32_t) i;
+            } else {
+                atomicExch(x.err, 1u);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// After the posts (same stream): publish the per-owner counts in the owners' arenas, reset the local counters
+// for the next batch and — device sync — raise this rank's "posted" flag everywhere.
+__global__ void exchange_post_finish_kernel(ExchangeView x, uint32_t epoch, int device_sync) {
+    const uint32_t t = threadIdx.x;
+    if (t < x.world) {
+        const uint32_t c = min(x.local_cnt[t], x.lay.cap);
+        x.local_cnt[t] = 0;
+        uint8_t *peer = x.arena[t];
+        reinterpret_cast<uint32_t *>(peer + x.lay.off_count)[x.rank] = c;
+        if (device_sync) {
+            __threadfence_system();
+            st_release_sys(reinterpret_cast<uint32_t *>(peer + x.lay.off_posted) + x.rank, epoch);
+        }
+    }
+}
+
+// ---- serve --------------------------------------------------------------------------------------------
+struct ServeArgs {
+    uint32_t read_ts;
+    uint32_t epoch;
+    int device_sync;
+    uint32_t *src_row;      // [world*cap] local scratch: row to gather per inbox entry (compact over sources)
+    uint32_t *dst_slot;     // [world*cap] (requester << 28) | request index
+};
+
+// prefix offsets of the per-source inbox counts, into shared memory (ends with a barrier)
+__device__ __forceinline__ void load_segments(const ExchangeView &x, uint32_t *s_off) {
+    if (threadIdx.x == 0) {
+        const uint32_t *cnt = reinterpret_cast<const uint32_t *>(x.arena[x.rank] + x.lay.off_count);
+        uint32_t acc = 0;
+        for (int s = 0; s < kMaxExchangeRanks; ++s) {
+            s_off[s] = acc;
+            if (s < (int) x.world) acc += min(__ldcg(cnt + s), x.lay.cap);
+        }
+        s_off[kMaxExchangeRanks] = acc;
+    }
+    __syncthreads();
+}
+
+// Search + MVCC over everything posted to this rank. found / commit id go straight to the requester's slab;
+// the payload row to move and its destination are handed to exchange_gather_kernel.
+template <int NW, int kProbePerLane>
+__global__ void __launch_bounds__(kProbeThreads) exchange_serve_kernel(SnapshotView v, ExchangeView x, ServeArgs a) {
+    extern __shared__ __align__(16) uint32_t s_top[];
+    load_top_level(v, s_top, NW);
+    if (a.device_sync)
+        cta_wait_flags(reinterpret_cast<const uint32_t *>(x.arena[x.rank] + x.lay.off_posted), x.world, a.epoch, x.err);
+    __shared__ uint32_t off[kMaxExchangeRanks + 1];
+    load_segments(x, off);
+    const uint32_t total = off[kMaxExchangeRanks];
+    const uint8_t *inbox = x.arena[x.rank];
+    const uint32_t *req = reinterpret_cast<const uint32_t *>(inbox + x.lay.off_req);
+
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t g0 = blockIdx.x * blockDim.x + threadIdx.x; g0 < total; g0 += stride * kProbePerLane) {
+        SKey<NW> k[kProbePerLane];
+        uint32_t c[kProbePerLane], dst[kProbePerLane];
+        bool hit[kProbePerLane];
+#pragma unroll
+        for (int p = 0; p < kProbePerLane; ++p) {
+            const uint32_t g = g0 + p * stride;
+            k[p] = skey_inf<NW>();
+            dst[p] = 0;
+            if (g < total) {
+                uint32_t s = 0;
+                for (uint32_t q = 1; q < x.world; ++q) s += g >= off[q] ? 1u : 0u;
+                const uint64_t slot = (uint64_t) s * x.lay.cap + (g - off[s]);
+                k[p] = to_sortable<NW>(inbox + x.lay.off_keys + slot * x.lay.kpad, v.key_size, v.xormask);
+                dst[p] = (s << kDstRankShift) | (req[slot] & kDstIndexMask);
+            }
+        }
+        fence_search<NW, kProbePerLane>(v, s_top, k, c, hit);
+        uint32_t t[kProbePerLane];
+#pragma unroll
+        for (int p = 0; p < kProbePerLane; ++p) t[p] = hit[p] ? __ldg(v.ts + c[p]) : 0u;
+#pragma unroll
+        for (int p = 0; p < kProbePerLane; ++p) {
+            const uint32_t g = g0 + p * stride;
+            if (g >= total) continue;
+            uint32_t src = kNoRow, stamp = 0;
+            if (hit[p]) src = visible_version(v, c[p], t[p], a.read_ts, &stamp);
+            uint8_t *peer = x.arena[dst[p] >> kDstRankShift];
+            const uint32_t r = dst[p] & kDstIndexMask;
+            (peer + x.lay.off_found)[r] = src != kNoRow ? 1 : 0;
+            reinterpret_cast<uint32_t *>(peer + x.lay.off_ts)[r] = stamp;
+            a.src_row[g] = src;
+            a.dst_slot[g] = dst[p];
+        }
+    }
+}
+
+// Payload rows: local HBM -> the requesters' result slabs (peer stores over NVLink for remote requesters).
+// Persistent CTAs over tiles of kGatherRows inbox entries; same in-flight structure as gather_rows_kernel.
+template <typename V, int U>
+__global__ void __launch_bounds__(kGatherThreads) exchange_gather_kernel(ExchangeView x, ServeArgs a, const uint8_t *payload,
+                                                                        const uint8_t *ver_payload, uint32_t P) {
+    __shared__ uint32_t s_row[kGatherRows], s_dst[kGatherRows];
+    __shared__ uint32_t off[kMaxExchangeRanks + 1];
+    load_segments(x, off);
+    const uint32_t total = off[kMaxExchangeRanks];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int kWarps = kGatherThreads / 32;
+    const uint32_t nvec = P / (uint32_t) sizeof(V);
+    const uint32_t tiles = (total + kGatherRows - 1) / kGatherRows;
+    for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const uint32_t g0 = tile * kGatherRows;
+        __syncthreads();
+        if (tid < kGatherRows) {
+            const uint32_t g = g0 + tid;
+            s_row[tid] = g < total ? a.src_row[g] : kNoRow;
+            s_dst[tid] = g < total ? a.dst_slot[g] : 0u;
+        }
+        __syncthreads();
+        for (int r0 = warp * U; r0 < kGatherRows; r0 += kWarps * U) {
+            const V *src[U];
+            V *dst[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint32_t row = s_row[r0 + u], d = s_dst[r0 + u];
+                const uint8_t *base = (row & kVersionRowFlag) ? ver_payload : payload;
+                src[u] = row == kNoRow ? nullptr : reinterpret_cast<const V *>(base + (uint64_t) (row & ~kVersionRowFlag) * P);
+                dst[u] = reinterpret_cast<V *>(x.arena[d >> kDstRankShift] + x.lay.off_payload +
+                                               (uint64_t) (d & kDstIndexMask) * P);
+            }
+            constexpr int K = 4;
+            for (uint32_t c0 = lane; c0 < nvec; c0 += 32 * K) {
+                V val[U][K];
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+#pragma unroll
+                    for (int k = 0; k < K; ++k)
+                        if (src[u] && c0 + 32 * k < nvec) val[u][k] = __ldcs(src[u] + c0 + 32 * k);
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+#pragma unroll
+                    for (int k = 0; k < K; ++k)
+                        if (src[u] && c0 + 32 * k < nvec) dst[u][c0 + 32 * k] = val[u][k];
+            }
+        }
+    }
+}
+
+// Device sync, owner side: all rows of this batch are written -> raise "served" at every requester.
+__global__ void exchange_serve_finish_kernel(ExchangeView x, uint32_t epoch) {
+    const uint32_t t = threadIdx.x;
+    if (t < x.world) {
+        __threadfence_system();
+        st_release_sys(reinterpret_cast<uint32_t *>(x.arena[t] + x.lay.off_served) + x.rank, epoch);
+    }
+}
+// Device sync, requester side: every owner has served this batch -> the result slab is complete.
+__global__ void exchange_wait_served_kernel(ExchangeView x, uint32_t epoch) {
+    cta_wait_flags(reinterpret_cast<const uint32_t *>(x.arena[x.rank] + x.lay.off_served), x.world, epoch, x.err);
+}
+
+}  // namespace stage

@@ -104,17 +104,67 @@ __device__ __forceinline__ uint32_t group_count_less(const uint32_t *lvl, uint32
 
 constexpr int kProbeThreads = 256;
 
-// kProbePerLane independent probes per lane: their searches are interleaved step by step (ILP)
+// Copies the top fence level into shared memory (all threads of the CTA; ends with a barrier).
+__device__ __forceinline__ void load_top_level(const SnapshotView &v, uint32_t *s_top, int nw) {
+    const int top = v.n_levels - 1;
+    const uint32_t words = v.level_n[top] * (uint32_t) nw;
+    for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) s_top[i] = __ldg(v.level[top] + i);
+    __syncthreads();
+}
+
+// The search proper, for kProbePerLane independent probes of one lane, interleaved step by step (ILP):
+// on return c[p] = number of keys of the key column < k[p] (the row an equal key would occupy) and
+// hit[p] = an equal key sits there (pad keys excluded).
+template <int NW, int kProbePerLane>
+__device__ __forceinline__ void fence_search(const SnapshotView &v, const uint32_t *s_top,
+                                             const SKey<NW> (&k)[kProbePerLane], uint32_t (&c)[kProbePerLane],
+                                             bool (&hit)[kProbePerLane]) {
+    const int top = v.n_levels - 1;
+    const uint32_t n_top = v.level_n[top];
+#pragma unroll
+    for (int p = 0; p < kProbePerLane; ++p) {
+        c[p] = 0;
+        hit[p] = false;
+    }
+    // top level, in shared memory: branch-free lower bound, c = number of keys < k
+    if (n_top > 0) {
+        uint32_t n = n_top;
+        while (n > 1) {
+            const uint32_t half = n >> 1;
+#pragma unroll
+            for (int p = 0; p < kProbePerLane; ++p)
+                if (skey_less<NW>(load_skey_generic<NW>(s_top, c[p] + half - 1), k[p])) c[p] += half;
+            n -= half;
+        }
+#pragma unroll
+        for (int p = 0; p < kProbePerLane; ++p) {
+            const SKey<NW> x = load_skey_generic<NW>(s_top, c[p]);
+            if (top == 0) hit[p] = skey_equal<NW>(x, k[p]);
+            c[p] += skey_less<NW>(x, k[p]);
+        }
+    }
+    for (int l = top - 1; l >= 0; --l) {
+        const uint32_t *lvl = v.level[l];
+#pragma unroll
+        for (int p = 0; p < kProbePerLane; ++p) {
+            bool eq;
+            const uint32_t cnt = group_count_less<NW>(lvl, c[p], k[p], &eq);
+            c[p] = c[p] * kFan + cnt;
+            hit[p] = eq;
+        }
+    }
+    const uint32_t n_rows = (uint32_t) v.n_rows;
+#pragma unroll
+    for (int p = 0; p < kProbePerLane; ++p) hit[p] = hit[p] && c[p] < n_rows;      // an equal PAD key is not a row
+}
+
+// kProbePerLane independent probes per lane
 template <int NW, int kProbePerLane>
 __global__ void __launch_bounds__(kProbeThreads) probe_kernel(SnapshotView v, ProbeArgs a) {
     extern __shared__ __align__(16) uint32_t s_top[];
-    const int top = v.n_levels - 1;
-    const uint32_t n_top = v.level_n[top];
-    for (uint32_t i = threadIdx.x; i < n_top * NW; i += blockDim.x) s_top[i] = __ldg(v.level[top] + i);
-    __syncthreads();
+    load_top_level(v, s_top, NW);
 
     const uint32_t K = v.key_size;
-    const uint32_t n_rows = (uint32_t) v.n_rows;
     const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
     const uint64_t per_iter = stride * kProbePerLane;
     for (uint64_t g0 = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; g0 < a.n; g0 += per_iter) {
@@ -125,43 +175,12 @@ __global__ void __launch_bounds__(kProbeThreads) probe_kernel(SnapshotView v, Pr
         for (int p = 0; p < kProbePerLane; ++p) {
             const uint64_t gi = g0 + p * stride;
             k[p] = gi < a.n ? to_sortable<NW>(a.keys + gi * K, K, v.xormask) : skey_inf<NW>();
-            c[p] = 0;
-            hit[p] = false;
         }
-        // top level, in shared memory: branch-free lower bound, c = number of keys < k
-        if (n_top > 0) {
-            uint32_t n = n_top;
-            while (n > 1) {
-                const uint32_t half = n >> 1;
-#pragma unroll
-                for (int p = 0; p < kProbePerLane; ++p)
-                    if (skey_less<NW>(load_skey_generic<NW>(s_top, c[p] + half - 1), k[p])) c[p] += half;
-                n -= half;
-            }
-#pragma unroll
-            for (int p = 0; p < kProbePerLane; ++p) {
-                const SKey<NW> x = load_skey_generic<NW>(s_top, c[p]);
-                if (top == 0) hit[p] = skey_equal<NW>(x, k[p]);
-                c[p] += skey_less<NW>(x, k[p]);
-            }
-        }
-        for (int l = top - 1; l >= 0; --l) {
-            const uint32_t *lvl = v.level[l];
-#pragma unroll
-            for (int p = 0; p < kProbePerLane; ++p) {
-                bool eq;
-                const uint32_t cnt = group_count_less<NW>(lvl, c[p], k[p], &eq);
-                c[p] = c[p] * kFan + cnt;
-                hit[p] = eq;
-            }
-        }
+        fence_search<NW, kProbePerLane>(v, s_top, k, c, hit);
         // MVCC + outputs
         uint32_t t[kProbePerLane];
 #pragma unroll
-        for (int p = 0; p < kProbePerLane; ++p) {
-            hit[p] = hit[p] && c[p] < n_rows;                 // an equal PAD key is not a row
-            t[p] = hit[p] ? __ldg(v.ts + c[p]) : 0u;
-        }
+        for (int p = 0; p < kProbePerLane; ++p) t[p] = hit[p] ? __ldg(v.ts + c[p]) : 0u;
 #pragma unroll
         for (int p = 0; p < kProbePerLane; ++p) {
             const uint64_t gi = g0 + p * stride;

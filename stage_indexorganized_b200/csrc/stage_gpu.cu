@@ -26,6 +26,7 @@
 #include "transform.cuh"
 #include "gather.cuh"
 #include "generate.cuh"
+#include "exchange.cuh"
 
 using namespace stage;
 
@@ -1000,6 +1001,244 @@ extern "C" int stage_gpu_route_device(const stage_schema_t *schema, const void *
         default: route_kernel<8><<<blocks, 256, 0, st>>>(r, k, n, schema->key_size, xm, owner_dev); break;
     }
     LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// routed probes over peer memory (exchange.cuh)
+// ------------------------------------------------------------------------------------------------
+struct stage_exchange {
+    ExchangeView view{};
+    stage_schema_t schema{};
+    int nw = 1;
+    uint32_t xormask = 0;
+    int device = 0;
+    uint8_t *arena = nullptr;
+    bool opened[kMaxExchangeRanks] = {false};
+    uint32_t *d_local_cnt = nullptr, *d_err = nullptr;
+    uint32_t *d_src_row = nullptr, *d_dst_slot = nullptr;
+    uint32_t epoch_post = 0, epoch_serve = 0, epoch_wait = 0;
+    bool attached = false;
+};
+
+static uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
+
+extern "C" int stage_gpu_exchange_create(uint32_t world, uint32_t rank, uint64_t capacity, const stage_schema_t *schema,
+                                         stage_exchange_t **out) {
+    if (!out || world == 0 || world > (uint32_t) kMaxExchangeRanks || rank >= world || capacity == 0 ||
+        capacity > kDstIndexMask)
+        return STAGE_ERR_ARG;
+    int nw;
+    uint32_t xm;
+    int rc = schema_check(schema, &nw, &xm);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(g_device));
+    auto *x = new stage_exchange();
+    x->schema = *schema;
+    x->nw = nw;
+    x->xormask = xm;
+    x->device = g_device;
+    ExchangeLayout &l = x->view.lay;
+    l.cap = (uint32_t) capacity;
+    l.kpad = (schema->key_size + 3u) & ~3u;
+    uint64_t off = 0;
+    l.off_count = off;   off = align_up(off + 4ull * world, 256);
+    l.off_posted = off;  off = align_up(off + 4ull * world, 256);
+    l.off_served = off;  off = align_up(off + 4ull * world, 256);
+    l.off_keys = off;    off = align_up(off + (uint64_t) world * capacity * l.kpad, 256);
+    l.off_req = off;     off = align_up(off + (uint64_t) world * capacity * 4, 256);
+    l.off_found = off;   off = align_up(off + capacity, 256);
+    l.off_ts = off;      off = align_up(off + capacity * 4, 256);
+    l.off_payload = off; off = align_up(off + capacity * (uint64_t) schema->payload_size + 256, 256);
+    l.bytes = off;
+    x->view.world = world;
+    x->view.rank = rank;
+    auto fail = [&](int code) { stage_gpu_exchange_destroy(x); return code; };
+    if (cudaMalloc((void **) &x->arena, l.bytes) != cudaSuccess || cudaMemset(x->arena, 0, l.bytes) != cudaSuccess ||
+        cudaMalloc((void **) &x->d_local_cnt, 4 * kMaxExchangeRanks) != cudaSuccess ||
+        cudaMemset(x->d_local_cnt, 0, 4 * kMaxExchangeRanks) != cudaSuccess ||
+        cudaMalloc((void **) &x->d_err, 4) != cudaSuccess || cudaMemset(x->d_err, 0, 4) != cudaSuccess ||
+        cudaMalloc((void **) &x->d_src_row, (uint64_t) world * capacity * 4) != cudaSuccess ||
+        cudaMalloc((void **) &x->d_dst_slot, (uint64_t) world * capacity * 4) != cudaSuccess) {
+        g_last_error = std::string("exchange allocation: ") + cudaGetErrorString(cudaGetLastError());
+        return fail(STAGE_ERR_NOMEM);
+    }
+    CUDA_TRY(cudaDeviceSynchronize());
+    x->view.arena[rank] = x->arena;
+    x->view.local_cnt = x->d_local_cnt;
+    x->view.err = x->d_err;
+    x->attached = world == 1;
+    *out = x;
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_ipc_handle(stage_exchange_t *x, void *handle_out) {
+    if (!x || !handle_out) return STAGE_ERR_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == STAGE_IPC_HANDLE_BYTES, "IPC handle size");
+    CUDA_TRY(cudaSetDevice(x->device));
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, x->arena));
+    memcpy(handle_out, &h, sizeof(h));
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_attach_ipc(stage_exchange_t *x, const void *handles) {
+    if (!x || !handles) return STAGE_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(x->device));
+    for (uint32_t r = 0; r < x->view.world; ++r) {
+        if (r == x->view.rank) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, static_cast<const uint8_t *>(handles) + (size_t) r * STAGE_IPC_HANDLE_BYTES, sizeof(h));
+        void *p = nullptr;
+        CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        x->view.arena[r] = static_cast<uint8_t *>(p);
+        x->opened[r] = true;
+    }
+    x->attached = true;
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_attach_ptrs(stage_exchange_t *x, void *const *arenas) {
+    if (!x || !arenas) return STAGE_ERR_ARG;
+    for (uint32_t r = 0; r < x->view.world; ++r)
+        if (r != x->view.rank) {
+            if (!arenas[r]) return STAGE_ERR_ARG;
+            x->view.arena[r] = static_cast<uint8_t *>(arenas[r]);
+        }
+    x->attached = true;
+    return STAGE_OK;
+}
+
+extern "C" void *stage_gpu_exchange_arena(stage_exchange_t *x) { return x ? x->arena : nullptr; }
+
+extern "C" int stage_gpu_exchange_post(stage_exchange_t *x, const void *splitters, const void *keys_dev, uint64_t n,
+                                       int flags, void *cuda_stream) {
+    if (!x || (n && !keys_dev) || (x->view.world > 1 && !splitters) || n > x->view.lay.cap) return STAGE_ERR_ARG;
+    if (!x->attached) return STAGE_ERR_STATE;
+    CUDA_TRY(cudaSetDevice(x->device));
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    ExchangeSplit sp{};
+    for (uint32_t i = 0; i + 1 < x->view.world; ++i)
+        host_sortable_nw(x->nw, static_cast<const uint8_t *>(splitters) + (size_t) i * x->schema.key_size,
+                         x->schema.key_size, x->xormask, sp.w + (size_t) i * x->nw);
+    if (n) {
+        const unsigned blocks = (unsigned) std::min<uint64_t>((n + 255) / 256, (uint64_t) sm_count() * 8);
+        const uint8_t *k = static_cast<const uint8_t *>(keys_dev);
+        switch (x->nw) {
+            case 1: exchange_post_kernel<1><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask); break;
+            case 2: exchange_post_kernel<2><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask); break;
+            case 4: exchange_post_kernel<4><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask); break;
+            default: exchange_post_kernel<8><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask); break;
+        }
+        LAUNCH_CHECK();
+    }
+    ++x->epoch_post;
+    exchange_post_finish_kernel<<<1, 32, 0, st>>>(x->view, x->epoch_post, flags & STAGE_XCHG_DEVICE_SYNC ? 1 : 0);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
+template <int NW>
+static int launch_serve(stage_exchange *x, stage_snapshot *s, const ServeArgs &a, cudaStream_t st) {
+    const size_t smem = (size_t) std::max<uint32_t>(s->view.smem_words, 4) * 4;
+    static int occ[9] = {0};
+    if (!occ[NW]) {
+        int o = 0;
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, exchange_serve_kernel<NW, 4>, kProbeThreads, kProbeTopBytes));
+        occ[NW] = std::max(o, 1);
+    }
+    // persistent grid: the inbox sizes are only known on the device
+    exchange_serve_kernel<NW, 4><<<sm_count() * occ[NW], kProbeThreads, smem, st>>>(s->view, x->view, a);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
+template <typename V>
+static int launch_exchange_gather(stage_exchange *x, stage_snapshot *s, const ServeArgs &a, cudaStream_t st) {
+    static int occ = 0;
+    if (!occ) {
+        int o = 0;
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, exchange_gather_kernel<V, 4>, kGatherThreads, 0));
+        occ = std::max(o, 1);
+    }
+    exchange_gather_kernel<V, 4><<<sm_count() * occ, kGatherThreads, 0, st>>>(x->view, a, s->d_payload, s->d_ver_payload,
+                                                                             s->schema.payload_size);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_serve(stage_exchange_t *x, stage_snapshot_t *s, uint32_t read_ts, int flags,
+                                        void *cuda_stream) {
+    if (!x || !s) return STAGE_ERR_ARG;
+    if (!x->attached || !s->sealed) return STAGE_ERR_STATE;
+    if (s->schema.key_size != x->schema.key_size || s->schema.payload_size != x->schema.payload_size || s->nw != x->nw ||
+        s->device != x->device)
+        return STAGE_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(x->device));
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    ServeArgs a{};
+    a.read_ts = read_ts;
+    a.epoch = ++x->epoch_serve;
+    a.device_sync = flags & STAGE_XCHG_DEVICE_SYNC ? 1 : 0;
+    a.src_row = x->d_src_row;
+    a.dst_slot = x->d_dst_slot;
+    int rc;
+    switch (x->nw) {
+        case 1: rc = launch_serve<1>(x, s, a, st); break;
+        case 2: rc = launch_serve<2>(x, s, a, st); break;
+        case 4: rc = launch_serve<4>(x, s, a, st); break;
+        default: rc = launch_serve<8>(x, s, a, st); break;
+    }
+    if (rc) return rc;
+    // vector width: every arena and the payload offset are 256-byte aligned, so the row stride decides
+    const uintptr_t align = (uintptr_t) s->d_payload | (uintptr_t) s->d_ver_payload | s->schema.payload_size;
+    if ((align & 15) == 0) rc = launch_exchange_gather<uint4>(x, s, a, st);
+    else if ((align & 7) == 0) rc = launch_exchange_gather<uint2>(x, s, a, st);
+    else if ((align & 3) == 0) rc = launch_exchange_gather<uint32_t>(x, s, a, st);
+    else rc = launch_exchange_gather<uint8_t>(x, s, a, st);
+    if (rc) return rc;
+    if (a.device_sync) {
+        exchange_serve_finish_kernel<<<1, 32, 0, st>>>(x->view, a.epoch);
+        LAUNCH_CHECK();
+    }
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_wait(stage_exchange_t *x, void *cuda_stream) {
+    if (!x) return STAGE_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(x->device));
+    exchange_wait_served_kernel<<<1, 32, 0, static_cast<cudaStream_t>(cuda_stream)>>>(x->view, ++x->epoch_wait);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_results(stage_exchange_t *x, void **found, void **ts, void **payload) {
+    if (!x) return STAGE_ERR_ARG;
+    if (found) *found = x->arena + x->view.lay.off_found;
+    if (ts) *ts = x->arena + x->view.lay.off_ts;
+    if (payload) *payload = x->arena + x->view.lay.off_payload;
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_error(stage_exchange_t *x, void *cuda_stream, uint32_t *err_out) {
+    if (!x || !err_out) return STAGE_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(x->device));
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    CUDA_TRY(cudaMemcpyAsync(err_out, x->d_err, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_destroy(stage_exchange_t *x) {
+    if (!x) return STAGE_ERR_ARG;
+    cudaSetDevice(x->device);
+    cudaDeviceSynchronize();
+    for (uint32_t r = 0; r < x->view.world; ++r)
+        if (x->opened[r] && x->view.arena[r]) cudaIpcCloseMemHandle(x->view.arena[r]);
+    void *ptrs[] = {x->arena, x->d_local_cnt, x->d_err, x->d_src_row, x->d_dst_slot};
+    for (void *p : ptrs)
+        if (p) cudaFree(p);
+    delete x;
     return STAGE_OK;
 }
 

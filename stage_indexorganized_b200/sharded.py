@@ -98,3 +98,45 @@ def ycsb_splitters(n_rows_total, world):
     b = shard_bounds(n_rows_total, world)
     last = np.array([b[g][1] - 1 for g in range(world - 1)], np.int64)
     return rank_to_key(n_rows_total, last).astype(np.uint32).view(np.uint8).reshape(-1, 4)
+
+
+class PeerProbe:
+    """Routed probes with the exchange fused into the kernels (csrc/exchange.cuh): keys are stored straight into the
+    owners' inboxes and payload rows straight into the requesters' result slabs over NVLink peer memory; results
+    arrive in request order. torch.distributed only carries the control plane (the one-time all-gather of the CUDA
+    IPC handles, and — without device_sync — two stream-ordered barriers per batch)."""
+
+    def __init__(self, shard, splitters, capacity, device_sync=True, group=None):
+        import stage_indexorganized_b200 as sg
+        self.sg, self.shard, self.group = sg, shard, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.splitters = splitters
+        self.flags = sg.XCHG_DEVICE_SYNC if device_sync else 0
+        self.x = sg.ProbeExchange(self.world, self.rank, capacity, shard.schema.key_size, shard.schema.payload_size)
+        handles = [None] * self.world
+        dist.all_gather_object(handles, self.x.ipc_handle(), group=group)
+        if self.world > 1:
+            self.x.attach_ipc(handles)
+        self._tok = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", torch.cuda.current_device()))
+        dist.barrier(group)          # every arena is mapped everywhere before the first post
+
+    def _barrier(self):
+        dist.all_reduce(self._tok, group=self.group)      # stream-ordered; no host synchronisation
+
+    def probe(self, keys_dev, n, read_ts):
+        """keys_dev: [n, K] uint8 CUDA tensor. Returns (found, ts, payload) views of this rank's result slab."""
+        st = torch.cuda.current_stream().cuda_stream
+        self.x.post(self.splitters, keys_dev, n, self.flags, st)
+        if not self.flags:
+            self._barrier()
+        self.x.serve(self.shard, read_ts, self.flags, st)
+        if self.flags:
+            self.x.wait(st)
+        else:
+            self._barrier()
+        return self.x.results_torch(n)
+
+    def close(self):
+        torch.cuda.synchronize()
+        dist.barrier(self.group)     # nobody unmaps an arena a peer may still be writing
+        self.x.close()

@@ -1,0 +1,122 @@
+"""GPU: routed probes over peer memory (csrc/exchange.cuh) — post / serve kernels, request-order result slabs.
+
+One process drives every rank of a small world on ONE device (arenas attached by pointer), so the whole routing
+path — owner computation in reference key order, inbox slot claims, per-source segments, MVCC on the owner,
+payload rows written into the requester's slab — is checked bit-exactly against the single-table CPU checker
+without needing several GPUs. The multi-process / NVLink form is tests/test_gpu_multi.py."""
+import numpy as np
+import pytest
+import torch
+
+import stage_indexorganized_b200 as sg
+from stage_indexorganized_b200 import sharded
+from stage_indexorganized_b200.ycsb import rank_to_key
+from helpers import u32_keys
+from oracle import pyoracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _run_world(world, shards, split, key_batches, read_ts, K, P, flags):
+    cap = max(len(k) for k in key_batches)
+    xs = [sg.ProbeExchange(world, r, cap, K, P) for r in range(world)]
+    try:
+        arenas = [x.arena() for x in xs]
+        for x in xs:
+            x.attach_ptrs(arenas)
+        dkeys = [torch.from_numpy(np.ascontiguousarray(k)).cuda() for k in key_batches]
+        out = []
+        for rep in range(2):                     # two batches: epochs, counter reset, slab reuse
+            for r in range(world):
+                xs[r].post(split, dkeys[r], len(key_batches[r]), flags)
+            for r in range(world):
+                xs[r].serve(shards[r], read_ts, flags)
+            for r in range(world):
+                if flags:
+                    xs[r].wait()
+            torch.cuda.synchronize()
+            out = []
+            for r in range(world):
+                assert xs[r].error() == 0
+                f, t, p = xs[r].results_torch(len(key_batches[r]))
+                out.append((f.cpu().numpy().copy(), t.cpu().numpy().view(np.uint32).copy(), p.cpu().numpy().copy()))
+        return out
+    finally:
+        for x in xs:
+            x.close()
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+@pytest.mark.parametrize("flags", [0, sg.XCHG_DEVICE_SYNC])
+def test_routed_probe_generated_shards(world, flags):
+    N, P = 40000, 1000
+    sg.init(0)
+    full = pyoracle.OracleTable(P)
+    assert full.load_ycsb_int(0, N) == N
+    bounds = sharded.shard_bounds(N, world)
+    split = sharded.ycsb_splitters(N, world) if world > 1 else None
+    shards = [sg.Snapshot.generate_ycsb(N, P, rows_per_leaf=61, first_rank=lo, n_local=hi - lo) for lo, hi in bounds]
+    try:
+        rng = np.random.default_rng(world)
+        batches = [u32_keys(rng.integers(0, N + 40, 5000 + 17 * r)) for r in range(world)]
+        got = _run_world(world, shards, split, batches, 1, 4, P, flags)
+        for r in range(world):
+            wf, wt, _, wp = full.probe(batches[r], 1)
+            f, t, p = got[r]
+            assert np.array_equal(f, wf), f"rank {r} found"
+            assert np.array_equal(t[wf == 1], wt[wf == 1])
+            assert np.array_equal(p[wf == 1], wp[wf == 1]), f"rank {r} payload"
+    finally:
+        for s in shards:
+            s.close()
+
+
+def test_routed_probe_mvcc_shards_from_trees():
+    """Shards flattened from checker-built trees with committed updates (version chains on the owners)."""
+    N, P, world = 6000, 64, 2
+    sg.init(0)
+    full = pyoracle.OracleTable(P)
+    full.load_ycsb_int(0, N)
+    rng = np.random.default_rng(3)
+    upd = u32_keys(rng.integers(0, N, 1500))
+    assert full.commit_update_batch(upd, 10) == 1500
+    bounds = sharded.shard_bounds(N, world)
+    split = sharded.ycsb_splitters(N, world)
+    order = rank_to_key(N, np.arange(N)).astype(np.uint32)
+    owner_of = {int(k): (0 if i < bounds[0][1] else 1) for i, k in enumerate(order)}
+    tables, shards = [], []
+    for lo, hi in bounds:
+        t = pyoracle.OracleTable(P)
+        mine = order[lo:hi]
+        pay = np.empty((len(mine), P), np.uint8)
+        pay[:] = (mine & 0xFF).astype(np.uint8)[:, None]
+        t.insert(u32_keys(mine), pay, 0)
+        tables.append(t)
+    for i, k in enumerate(upd.view(np.uint32).ravel()):       # same updates, same commit ids, on the owning shard
+        assert tables[owner_of[int(k)]].commit_update_batch(upd[i:i + 1], 10 + i) == 1
+    shards = [sg.Snapshot.from_tree(t.root, 4, P) for t in tables]
+    try:
+        batches = [u32_keys(rng.integers(0, N + 10, 3000)) for _ in range(world)]
+        for read_ts in (0, 9, 700, 1509, 4000):
+            got = _run_world(world, shards, split, batches, read_ts, 4, P, sg.XCHG_DEVICE_SYNC)
+            for r in range(world):
+                wf, wt, _, wp = full.probe(batches[r], read_ts)
+                f, t, p = got[r]
+                assert np.array_equal(f, wf), f"ts={read_ts} rank {r} found"
+                assert np.array_equal(t[wf == 1], wt[wf == 1]), f"ts={read_ts} stamps"
+                assert np.array_equal(p[wf == 1], wp[wf == 1]), f"ts={read_ts} payload"
+    finally:
+        for s in shards:
+            s.close()
+
+
+def test_exchange_overflow_is_reported():
+    sg.init(0)
+    with sg.Snapshot.generate_ycsb(1000, 64) as shard:
+        x = sg.ProbeExchange(1, 0, 100, 4, 64)
+        try:
+            keys = torch.zeros((200, 4), dtype=torch.uint8, device="cuda")
+            with pytest.raises(sg.StageError):
+                x.post(None, keys, 200)          # n > capacity is refused on the host
+        finally:
+            x.close()

@@ -17,9 +17,11 @@ Secondary leg in the same JSON line ("probe"): batches of 2^20 uniform point pro
 `--impl reference` times that CPU path alone, with every host thread, on the same metric/config.
 
 N > 1 (torchrun, one rank per GPU): the table is range-partitioned in reference key order; every rank
-holds 10 M tuples (weak scaling) built on the device by stage_gpu_snapshot_generate_ycsb plus a halo of
-the next shard's first rows, scans run shard-local (no data-path collective), probes are routed to
-their owning shard with an NCCL all-to-all (keys out, results back).
+holds --rows-multi tuples (default 125 M = BASELINE configs[4], 1 B tuples over 8 GPUs; weak scaling: the
+per-GPU step is the same 4096 x 1000-row scans) built on the device by stage_gpu_snapshot_generate_ycsb
+plus a halo of the next shard's first rows; scans run shard-local (no data-path collective); probes are
+routed to their owning shard by kernels that store keys / result rows straight into the peers' memory over
+NVLink (csrc/exchange.cuh), with the NCCL all-to-all form timed beside it.
 """
 import argparse
 import json
@@ -48,7 +50,10 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--rows", type=int, default=10_000_000, help="tuples per GPU")
+    ap.add_argument("--rows", type=int, default=10_000_000, help="tuples per GPU at N = 1 (BASELINE configs[1])")
+    ap.add_argument("--rows-multi", type=int, default=125_000_000,
+                    help="tuples per GPU at N > 1 (BASELINE configs[4]: 1 B tuples over 8 GPUs)")
+    ap.add_argument("--a2a-steps", type=int, default=2, help="steps of the NCCL all-to-all comparison leg (N > 1)")
     ap.add_argument("--scans", type=int, default=4096, help="scans per step per GPU")
     ap.add_argument("--scan-size", type=int, default=1000)
     ap.add_argument("--probes", type=int, default=1 << 20, help="probes per probe step per GPU")
@@ -223,6 +228,8 @@ def main():
         dist = dist_
         dist.init_process_group("nccl", device_id=dev)
 
+    if world > 1:
+        args.rows = args.rows_multi
     rows, S, n_scans, n_probes = args.rows, args.scan_size, args.scans, args.probes
     updates = rows // 10
     use_generated = world > 1 or args.generated
@@ -338,11 +345,65 @@ def main():
                               "step_achieved": pbytes / (pms * 1e-3) / 1e9,
                               "step_frac": pbytes / (pms * 1e-3) / 1e9 / peak}}
 
-    # ---- probe leg at N > 1: range-routed probes, NCCL all-to-all of keys out and results back ------
+    # ---- probe leg at N > 1: range-routed probes, exchange fused into the kernels (peer memory over NVLink) ----
     if world > 1:
         from stage_indexorganized_b200 import sharded
         split = sharded.ycsb_splitters(rows * world, world)
         d_pk = torch.from_numpy(pk_all.astype(np.uint32).view(np.uint8).reshape(n_batches, n_probes, K_BYTES)).to(dev)
+        pp = sharded.PeerProbe(snap, split, n_probes, device_sync=True)
+
+        def timed(fn, steps):
+            for b in range(args.warmup):
+                fn(b)
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            hits_ = []
+            for i in range(steps):
+                f = fn(args.warmup + i)[0]
+                hits_.append(f.sum())          # device-side reduction of this step's found flags (slab is reused)
+            e1.record(stream)
+            barrier()
+            t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+            h = torch.stack(hits_).sum().to(torch.float64).reshape(1)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(h, op=dist.ReduceOp.SUM)
+            return float(t.item()), float(h.item())
+
+        l0 = sg.launch_count()
+        pms, hit_sum = timed(lambda b: pp.probe(d_pk[b], n_probes, read_ts), args.steps)
+        probe_launches = sg.launch_count() - l0
+        if pp.x.error() != 0:
+            raise SystemExit(f"probe exchange error {pp.x.error()} on rank {rank}")
+        nprobe = args.steps * n_probes * world
+        hit_rate = hit_sum / nprobe
+        remote = (world - 1) / world
+        # per GPU per step: HBM = local algorithmic bytes; NVLink (out direction) = rows served to remote requesters
+        hbm_bytes = n_probes * (hit_rate * PROBE_HIT_BYTES + (1 - hit_rate) * PROBE_MISS_BYTES)
+        nvl_bytes = n_probes * remote * (hit_rate * P_BYTES + 5 + K_BYTES + 4)
+        peak, _ = peaks()
+        nvl_peak = 770.0                                           # GB/s per direction per GPU, measured peer copy (B200_PROFILING.md)
+        t_hbm, t_nvl = hbm_bytes / (peak * 1e9), nvl_bytes / (nvl_peak * 1e9)
+        step_s = pms * 1e-3 / args.steps
+        probe = {"value": nprobe / (pms * 1e-3), "unit": "probes/s", "ms_per_step": pms / args.steps,
+                 "hit_rate": hit_rate, "launches_per_step": probe_launches // (args.steps + args.warmup),
+                 "routing": "exchange fused into the kernels (csrc/exchange.cuh): keys stored into the owners' inboxes, "
+                            "payload rows stored into the requesters' result slabs over NVLink peer memory (CUDA IPC), "
+                            "device-side epoch flags, results in request order",
+                 "nvlink_bytes_per_probe": nvl_bytes / n_probes,
+                 "roofline": {"bound": "nvlink" if t_nvl > t_hbm else "hbm",
+                              "target_ms": 1e3 * max(t_hbm, t_nvl), "frac": max(t_hbm, t_nvl) / step_s,
+                              "nvlink_achieved": nvl_bytes / step_s / 1e9, "nvlink_peak": nvl_peak,
+                              "hbm_achieved": hbm_bytes / step_s / 1e9, "hbm_peak": peak, "unit": "GB/s"}}
+        pp.x.enable_timing(True)
+        phases = []
+        for i in range(args.steps):
+            pp.probe(d_pk[args.warmup + i], n_probes, read_ts)
+            phases.append(pp.x.last_timing())
+        pp.x.enable_timing(False)
+        probe["phase_ms_rank0"] = dict(zip(("post", "search_incl_wait_for_posts", "rows", "wait_for_owners"),
+                                           [float(np.mean(c)) for c in zip(*phases)]))
+        # comparison: the same probes with NCCL all-to-all collectives around the local kernels
         d_owner = torch.empty((n_probes,), dtype=torch.int32, device=dev)
 
         def local_probe(kin):
@@ -354,32 +415,15 @@ def main():
                 snap.probe_device(kin, m, read_ts, f, t, None, pay)
             return f, t, pay
 
-        def routed_step(b):
+        def a2a_step(b):
             sg.route_device(d_pk[b], n_probes, split, d_owner, K_BYTES, stream.cuda_stream)
             return sharded.routed_probe(d_pk[b], d_owner, local_probe, P_BYTES)
 
-        for b in range(args.warmup):
-            routed_step(b)
-        barrier()
-        pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        pe0.record(stream)
-        hits = 0
-        founds = []
-        for i in range(args.steps):
-            f, _, _ = routed_step(args.warmup + i)
-            founds.append(f)
-        pe1.record(stream)
-        barrier()
-        pms_t = torch.tensor([pe0.elapsed_time(pe1)], dtype=torch.float64, device=dev)
-        hit_t = torch.tensor([float(sum(int(f.sum().item()) for f in founds))], dtype=torch.float64, device=dev)
-        dist.all_reduce(pms_t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(hit_t, op=dist.ReduceOp.SUM)
-        nprobe = args.steps * n_probes * world
-        pms = float(pms_t.item())
-        probe = {"value": nprobe / (pms * 1e-3), "unit": "probes/s", "ms_per_step": pms / args.steps,
-                 "hit_rate": float(hit_t.item()) / nprobe, "routing": "stage_gpu_route_device + NCCL all-to-all "
-                 "(keys out, found/ts/payload back), results restored to request order",
-                 "nvlink_bytes_per_probe": (world - 1) / world * (2 * K_BYTES + 5 + P_BYTES)}
+        if args.a2a_steps > 0:
+            ams, _ = timed(a2a_step, args.a2a_steps)
+            probe["nccl_all_to_all"] = {"value": args.a2a_steps * n_probes * world / (ams * 1e-3), "unit": "probes/s",
+                                        "ms_per_step": ams / args.a2a_steps}
+        pp.close()
 
     # ---- max over ranks, whole-job aggregate ----------------------------------------------------
     t_ms = torch.tensor([total_ms], dtype=torch.float64, device=dev)

@@ -195,10 +195,16 @@ int stage_gpu_exchange_serve(stage_exchange_t *x, stage_snapshot_t *shard, uint3
 /* STAGE_XCHG_DEVICE_SYNC only: stream-ordered wait until every owner has served this rank's batch. */
 int stage_gpu_exchange_wait(stage_exchange_t *x, void *cuda_stream);
 /* Device pointers (local) of this rank's result slab, rows in request order: found u8[capacity], ts u32[capacity],
- * payload u8[capacity][payload_size]. Rows of missed probes keep their previous content. */
-int stage_gpu_exchange_results(stage_exchange_t *x, void **found, void **ts, void **payload);
+ * payload rows of payload_size bytes every *payload_stride bytes (payload_size rounded up to 128, so that the
+ * owners' peer stores are line-aligned). Rows of missed probes keep their previous content. */
+int stage_gpu_exchange_results(stage_exchange_t *x, void **found, void **ts, void **payload, uint32_t *payload_stride);
 /* Sticky device-side error of the exchange: 0 ok, 1 inbox overflow, 2 device-sync timeout. Synchronises the stream. */
 int stage_gpu_exchange_error(stage_exchange_t *x, void *cuda_stream, uint32_t *err_out);
+/* Per-phase timing of the last post/serve/wait sequence (STAGE_XCHG_DEVICE_SYNC), CUDA events on the caller's stream:
+ * ms4 = { post (route + inbox stores), serve search (incl. waiting for the peers' posts), payload rows (local +
+ * peer stores), wait for the owners }. */
+int stage_gpu_exchange_enable_timing(stage_exchange_t *x, int on);
+int stage_gpu_exchange_last_timing(stage_exchange_t *x, float *ms4);
 int stage_gpu_exchange_destroy(stage_exchange_t *x);
 
 /* ---- utilities ---------------------------------------------------------------------------- */

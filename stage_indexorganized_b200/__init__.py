@@ -71,8 +71,10 @@ SYMBOLS = {
     "stage_gpu_exchange_post": (_i32, [_vp, _vp, _vp, _u64, _i32, _vp]),
     "stage_gpu_exchange_serve": (_i32, [_vp, _vp, _u32, _i32, _vp]),
     "stage_gpu_exchange_wait": (_i32, [_vp, _vp]),
-    "stage_gpu_exchange_results": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)]),
+    "stage_gpu_exchange_results": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_u32)]),
     "stage_gpu_exchange_error": (_i32, [_vp, _vp, C.POINTER(_u32)]),
+    "stage_gpu_exchange_enable_timing": (_i32, [_vp, _i32]),
+    "stage_gpu_exchange_last_timing": (_i32, [_vp, C.POINTER(C.c_float)]),
     "stage_gpu_exchange_destroy": (_i32, [_vp]),
     "stage_gpu_host_alloc": (_vp, [C.c_size_t]),
     "stage_gpu_host_free": (None, [_vp]),
@@ -308,9 +310,9 @@ def route_device(keys_dev, n, splitters, owner_dev, key_size, cuda_stream=0, key
 class _DeviceView:
     """Minimal __cuda_array_interface__ carrier so torch.as_tensor can wrap library-owned device memory."""
 
-    def __init__(self, ptr, shape, typestr, owner):
+    def __init__(self, ptr, shape, typestr, owner, strides=None):
         self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
-                                         "version": 2, "strides": None}
+                                         "version": 2, "strides": strides}
         self._owner = owner
 
 
@@ -359,21 +361,31 @@ class ProbeExchange:
         _check(lib().stage_gpu_exchange_error(self.h, _vp(int(cuda_stream)), C.byref(e)))
         return int(e.value)
 
+    def enable_timing(self, on=True):
+        _check(lib().stage_gpu_exchange_enable_timing(self.h, int(on)))
+
+    def last_timing(self):
+        """(post_ms, search_ms, rows_ms, wait_ms) of the last post/serve/wait sequence."""
+        ms = (C.c_float * 4)()
+        _check(lib().stage_gpu_exchange_last_timing(self.h, ms))
+        return tuple(float(v) for v in ms)
+
     def result_ptrs(self):
-        f, t, p = _vp(), _vp(), _vp()
-        _check(lib().stage_gpu_exchange_results(self.h, C.byref(f), C.byref(t), C.byref(p)))
-        return int(f.value), int(t.value), int(p.value)
+        f, t, p, st = _vp(), _vp(), _vp(), _u32(0)
+        _check(lib().stage_gpu_exchange_results(self.h, C.byref(f), C.byref(t), C.byref(p), C.byref(st)))
+        return int(f.value), int(t.value), int(p.value), int(st.value)
 
     def results_torch(self, n=None):
-        """(found u8[n], ts i32[n], payload u8[n,P]) torch views of the result slab (no copy)."""
+        """(found u8[n], ts i32[n], payload u8[n,P]) torch views of the result slab (no copy; payload rows are
+        strided by the slab's padded row stride)."""
         import torch
         n = self.capacity if n is None else n
-        f, t, p = self.result_ptrs()
+        f, t, p, stride = self.result_ptrs()
         P = self.schema.payload_size
         dev = torch.device("cuda", torch.cuda.current_device())
         found = torch.as_tensor(_DeviceView(f, (n,), "|u1", self), device=dev)
         ts = torch.as_tensor(_DeviceView(t, (n,), "<i4", self), device=dev)
-        pay = torch.as_tensor(_DeviceView(p, (n, P), "|u1", self), device=dev)
+        pay = torch.as_tensor(_DeviceView(p, (n, stride), "|u1", self), device=dev)[:, :P]
         return found, ts, pay
 
     def close(self):

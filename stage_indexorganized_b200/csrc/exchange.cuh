@@ -37,9 +37,9 @@ struct ExchangeLayout {
     uint64_t off_req;       // u32 [world][cap]       inbox: request index at the source
     uint64_t off_found;     // u8  [cap]              result slab of THIS rank's requests
     uint64_t off_ts;        // u32 [cap]
-    uint64_t off_payload;   // u8  [cap][P]
+    uint64_t off_payload;   // u8  [cap][pstride]     rows padded to 128 B so that peer stores are line-aligned
     uint64_t bytes;
-    uint32_t cap, kpad;
+    uint32_t cap, kpad, pstride;
 };
 
 struct ExchangeView {
@@ -228,6 +228,18 @@ __global__ void __launch_bounds__(kProbeThreads) exchange_serve_kernel(SnapshotV
     }
 }
 
+// Inbox entries are grouped by requester, so walking the tiles in order would first move all rows of requester 0,
+// then requester 1, ...: the local (HBM-bound) and the remote (NVLink-bound) rows would be serialised. Tiles are
+// therefore visited in the order t -> t * mul mod tiles (mul coprime with tiles: a bijection), which spreads every
+// requester's tiles over the whole kernel so both paths stay busy at once.
+__device__ __forceinline__ uint32_t tile_multiplier(uint32_t tiles) {
+    const uint32_t primes[4] = {7919u, 7927u, 7933u, 7937u};
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        if (tiles % primes[i] != 0) return primes[i];
+    return 1u;
+}
+
 // Payload rows: local HBM -> the requesters' result slabs (peer stores over NVLink for remote requesters).
 // Persistent CTAs over tiles of kGatherRows inbox entries; same in-flight structure as gather_rows_kernel.
 template <typename V, int U>
@@ -241,8 +253,9 @@ __global__ void __launch_bounds__(kGatherThreads) exchange_gather_kernel(Exchang
     constexpr int kWarps = kGatherThreads / 32;
     const uint32_t nvec = P / (uint32_t) sizeof(V);
     const uint32_t tiles = (total + kGatherRows - 1) / kGatherRows;
-    for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-        const uint32_t g0 = tile * kGatherRows;
+    const uint32_t mul = tile_multiplier(tiles);
+    for (uint32_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const uint32_t g0 = (uint32_t) (((uint64_t) t * mul) % tiles) * kGatherRows;
         __syncthreads();
         if (tid < kGatherRows) {
             const uint32_t g = g0 + tid;
@@ -259,7 +272,7 @@ __global__ void __launch_bounds__(kGatherThreads) exchange_gather_kernel(Exchang
                 const uint8_t *base = (row & kVersionRowFlag) ? ver_payload : payload;
                 src[u] = row == kNoRow ? nullptr : reinterpret_cast<const V *>(base + (uint64_t) (row & ~kVersionRowFlag) * P);
                 dst[u] = reinterpret_cast<V *>(x.arena[d >> kDstRankShift] + x.lay.off_payload +
-                                               (uint64_t) (d & kDstIndexMask) * P);
+                                               (uint64_t) (d & kDstIndexMask) * x.lay.pstride);
             }
             constexpr int K = 4;
             for (uint32_t c0 = lane; c0 < nvec; c0 += 32 * K) {
@@ -274,6 +287,66 @@ __global__ void __launch_bounds__(kGatherThreads) exchange_gather_kernel(Exchang
 #pragma unroll
                     for (int k = 0; k < K; ++k)
                         if (src[u] && c0 + 32 * k < nvec) dst[u][c0 + 32 * k] = val[u][k];
+            }
+        }
+    }
+}
+
+// Same, for rows whose size is a multiple of 8 (8-byte aligned sources, e.g. the 1000-byte YCSB rows): each lane
+// moves 16-byte chunks — two 8-byte loads, ONE 16-byte store — so a warp store instruction covers 512 contiguous,
+// 128-byte-aligned bytes of the destination row (the slab rows are padded to 128 B): full NVLink write packets.
+template <int U>
+__global__ void __launch_bounds__(kGatherThreads) exchange_gather16_kernel(ExchangeView x, ServeArgs a, const uint8_t *payload,
+                                                                          const uint8_t *ver_payload, uint32_t P) {
+    __shared__ uint32_t s_row[kGatherRows], s_dst[kGatherRows];
+    __shared__ uint32_t off[kMaxExchangeRanks + 1];
+    load_segments(x, off);
+    const uint32_t total = off[kMaxExchangeRanks];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int kWarps = kGatherThreads / 32;
+    const uint32_t nfull = P / 16, tail8 = (P & 15u) >> 3;       // 16-byte chunks, then one optional 8-byte chunk
+    const uint32_t tiles = (total + kGatherRows - 1) / kGatherRows;
+    const uint32_t mul = tile_multiplier(tiles);
+    for (uint32_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const uint32_t g0 = (uint32_t) (((uint64_t) t * mul) % tiles) * kGatherRows;
+        __syncthreads();
+        if (tid < kGatherRows) {
+            const uint32_t g = g0 + tid;
+            s_row[tid] = g < total ? a.src_row[g] : kNoRow;
+            s_dst[tid] = g < total ? a.dst_slot[g] : 0u;
+        }
+        __syncthreads();
+        for (int r0 = warp * U; r0 < kGatherRows; r0 += kWarps * U) {
+            const uint2 *src[U];
+            uint8_t *dst[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint32_t row = s_row[r0 + u], d = s_dst[r0 + u];
+                const uint8_t *base = (row & kVersionRowFlag) ? ver_payload : payload;
+                src[u] = row == kNoRow ? nullptr : reinterpret_cast<const uint2 *>(base + (uint64_t) (row & ~kVersionRowFlag) * P);
+                dst[u] = x.arena[d >> kDstRankShift] + x.lay.off_payload + (uint64_t) (d & kDstIndexMask) * x.lay.pstride;
+            }
+            constexpr int K = 2;
+            for (uint32_t c0 = lane; c0 < nfull + tail8; c0 += 32 * K) {
+                uint2 lo[U][K], hi[U][K];
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+#pragma unroll
+                    for (int k = 0; k < K; ++k) {
+                        const uint32_t c = c0 + 32 * k;
+                        if (src[u] && c < nfull + tail8) lo[u][k] = __ldcs(src[u] + 2 * c);
+                        if (src[u] && c < nfull) hi[u][k] = __ldcs(src[u] + 2 * c + 1);
+                    }
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+#pragma unroll
+                    for (int k = 0; k < K; ++k) {
+                        const uint32_t c = c0 + 32 * k;
+                        if (src[u] && c < nfull)
+                            *reinterpret_cast<uint4 *>(dst[u] + 16 * c) = make_uint4(lo[u][k].x, lo[u][k].y, hi[u][k].x, hi[u][k].y);
+                        else if (src[u] && c < nfull + tail8)
+                            *reinterpret_cast<uint2 *>(dst[u] + 16 * c) = lo[u][k];
+                    }
             }
         }
     }

@@ -1019,7 +1019,12 @@ struct stage_exchange {
     uint32_t *d_src_row = nullptr, *d_dst_slot = nullptr;
     uint32_t epoch_post = 0, epoch_serve = 0, epoch_wait = 0;
     bool attached = false;
+    // per-phase CUDA events: [0] before post, [1] after post, [2] after the serve search, [3] after the row gather,
+    // [4] after the wait kernel
+    cudaEvent_t tev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool timing = false;
 };
+#define XCHG_MARK(x, i, st) do { if ((x)->timing) CUDA_TRY(cudaEventRecord((x)->tev[i], st)); } while (0)
 
 static uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 
@@ -1049,7 +1054,8 @@ extern "C" int stage_gpu_exchange_create(uint32_t world, uint32_t rank, uint64_t
     l.off_req = off;     off = align_up(off + (uint64_t) world * capacity * 4, 256);
     l.off_found = off;   off = align_up(off + capacity, 256);
     l.off_ts = off;      off = align_up(off + capacity * 4, 256);
-    l.off_payload = off; off = align_up(off + capacity * (uint64_t) schema->payload_size + 256, 256);
+    l.pstride = (uint32_t) align_up(schema->payload_size, 128);
+    l.off_payload = off; off = align_up(off + capacity * (uint64_t) l.pstride + 256, 256);
     l.bytes = off;
     x->view.world = world;
     x->view.rank = rank;
@@ -1118,6 +1124,7 @@ extern "C" int stage_gpu_exchange_post(stage_exchange_t *x, const void *splitter
     CUDA_TRY(cudaSetDevice(x->device));
     cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
     ExchangeSplit sp{};
+    XCHG_MARK(x, 0, st);
     for (uint32_t i = 0; i + 1 < x->view.world; ++i)
         host_sortable_nw(x->nw, static_cast<const uint8_t *>(splitters) + (size_t) i * x->schema.key_size,
                          x->schema.key_size, x->xormask, sp.w + (size_t) i * x->nw);
@@ -1135,6 +1142,7 @@ extern "C" int stage_gpu_exchange_post(stage_exchange_t *x, const void *splitter
     ++x->epoch_post;
     exchange_post_finish_kernel<<<1, 32, 0, st>>>(x->view, x->epoch_post, flags & STAGE_XCHG_DEVICE_SYNC ? 1 : 0);
     LAUNCH_CHECK();
+    XCHG_MARK(x, 1, st);
     return STAGE_OK;
 }
 
@@ -1190,9 +1198,22 @@ extern "C" int stage_gpu_exchange_serve(stage_exchange_t *x, stage_snapshot_t *s
         default: rc = launch_serve<8>(x, s, a, st); break;
     }
     if (rc) return rc;
+    XCHG_MARK(x, 2, st);
     // vector width: every arena and the payload offset are 256-byte aligned, so the row stride decides
     const uintptr_t align = (uintptr_t) s->d_payload | (uintptr_t) s->d_ver_payload | s->schema.payload_size;
+    static const bool no16 = getenv("STAGE_XCHG_NO16") != nullptr;
     if ((align & 15) == 0) rc = launch_exchange_gather<uint4>(x, s, a, st);
+    else if ((align & 7) == 0 && !no16) {
+        static int occ16 = 0;
+        if (!occ16) {
+            int o = 0;
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, exchange_gather16_kernel<4>, kGatherThreads, 0));
+            occ16 = std::max(o, 1);
+        }
+        exchange_gather16_kernel<4><<<sm_count() * occ16, kGatherThreads, 0, st>>>(x->view, a, s->d_payload, s->d_ver_payload,
+                                                                                 s->schema.payload_size);
+        LAUNCH_CHECK();
+    }
     else if ((align & 7) == 0) rc = launch_exchange_gather<uint2>(x, s, a, st);
     else if ((align & 3) == 0) rc = launch_exchange_gather<uint32_t>(x, s, a, st);
     else rc = launch_exchange_gather<uint8_t>(x, s, a, st);
@@ -1201,6 +1222,7 @@ extern "C" int stage_gpu_exchange_serve(stage_exchange_t *x, stage_snapshot_t *s
         exchange_serve_finish_kernel<<<1, 32, 0, st>>>(x->view, a.epoch);
         LAUNCH_CHECK();
     }
+    XCHG_MARK(x, 3, st);
     return STAGE_OK;
 }
 
@@ -1209,11 +1231,14 @@ extern "C" int stage_gpu_exchange_wait(stage_exchange_t *x, void *cuda_stream) {
     CUDA_TRY(cudaSetDevice(x->device));
     exchange_wait_served_kernel<<<1, 32, 0, static_cast<cudaStream_t>(cuda_stream)>>>(x->view, ++x->epoch_wait);
     LAUNCH_CHECK();
+    XCHG_MARK(x, 4, static_cast<cudaStream_t>(cuda_stream));
     return STAGE_OK;
 }
 
-extern "C" int stage_gpu_exchange_results(stage_exchange_t *x, void **found, void **ts, void **payload) {
+extern "C" int stage_gpu_exchange_results(stage_exchange_t *x, void **found, void **ts, void **payload,
+                                          uint32_t *payload_stride) {
     if (!x) return STAGE_ERR_ARG;
+    if (payload_stride) *payload_stride = x->view.lay.pstride;
     if (found) *found = x->arena + x->view.lay.off_found;
     if (ts) *ts = x->arena + x->view.lay.off_ts;
     if (payload) *payload = x->arena + x->view.lay.off_payload;
@@ -1229,10 +1254,28 @@ extern "C" int stage_gpu_exchange_error(stage_exchange_t *x, void *cuda_stream, 
     return STAGE_OK;
 }
 
+extern "C" int stage_gpu_exchange_enable_timing(stage_exchange_t *x, int on) {
+    if (!x) return STAGE_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(x->device));
+    if (on && !x->tev[0])
+        for (int i = 0; i < 5; ++i) CUDA_TRY(cudaEventCreate(&x->tev[i]));
+    x->timing = on != 0;
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_last_timing(stage_exchange_t *x, float *ms4) {
+    if (!x || !ms4 || !x->timing) return STAGE_ERR_STATE;
+    CUDA_TRY(cudaEventSynchronize(x->tev[4]));
+    for (int i = 0; i < 4; ++i) CUDA_TRY(cudaEventElapsedTime(ms4 + i, x->tev[i], x->tev[i + 1]));
+    return STAGE_OK;
+}
+
 extern "C" int stage_gpu_exchange_destroy(stage_exchange_t *x) {
     if (!x) return STAGE_ERR_ARG;
     cudaSetDevice(x->device);
     cudaDeviceSynchronize();
+    for (int i = 0; i < 5; ++i)
+        if (x->tev[i]) cudaEventDestroy(x->tev[i]);
     for (uint32_t r = 0; r < x->view.world; ++r)
         if (x->opened[r] && x->view.arena[r]) cudaIpcCloseMemHandle(x->view.arena[r]);
     void *ptrs[] = {x->arena, x->d_local_cnt, x->d_err, x->d_src_row, x->d_dst_slot};

@@ -118,6 +118,30 @@ int stage_gpu_snapshot_seal(stage_snapshot_t *s);
 int stage_gpu_snapshot_generate_ycsb(const stage_schema_t *schema, uint64_t n_rows_total, uint64_t first_rank,
                                      uint64_t n_local, uint32_t rows_per_leaf, stage_snapshot_t **out);
 
+/* Bulk load from device-resident columns (tables whose host tree cannot be materialised, or that are produced
+ * on the GPU): alloc_sorted allocates the snapshot's own columns and hands out device pointers to fill —
+ * raw_keys n_rows x key_size bytes, payload n_rows x payload_size bytes, ts n_rows commit ids (zero-initialised) —
+ * with rows in REFERENCE key order (BaseNode::KeyCompare, b_tree.h:116-134); seal_sorted converts the keys to the
+ * sortable form, verifies they are strictly ascending (STAGE_ERR_ARG otherwise), lays out consolidated leaves of
+ * rows_per_leaf records (every leaf sorted, separator = its largest key, as after the reference's consolidation)
+ * and builds the search levels. No version chains. */
+int stage_gpu_snapshot_alloc_sorted(const stage_schema_t *schema, uint64_t n_rows, uint32_t rows_per_leaf,
+                                    stage_snapshot_t **out, void **raw_keys_dev, void **payload_dev, uint32_t **ts_dev);
+int stage_gpu_snapshot_seal_sorted(stage_snapshot_t *s);
+
+/* Incremental refresh: apply n committed single-row updates, in batch order, to a sealed
+ * snapshot. Update i overwrites payload bytes [patch_off, patch_off + patch_len) of the row with key keys[i] by
+ * patches[i] (patch_len bytes each; the whole row when patch_off = 0 and patch_len = payload_size) and commits with
+ * commit_ids[i]. The state installed is the one SSNTransactionManager::CommitTransaction leaves
+ * (src/concurrency/transaction_manager.cpp:610-676): the old version is retired into the version table with
+ * begin = old commit id, commit = commit_ids[i], next = previous chain head; the row takes commit id
+ * commit_ids[i] and the new chain head. Updates of absent keys are ignored (*applied_out counts the rest).
+ * Not concurrent with reads on the same snapshot: reads issued after the call returns see the new state.
+ * Inserts and deletes change leaf membership and need a re-transform of the leaf (not covered). */
+int stage_gpu_snapshot_apply_updates(stage_snapshot_t *s, const void *keys, const void *patches, uint32_t patch_off,
+                                     uint32_t patch_len, const uint32_t *commit_ids, uint64_t n, int flags,
+                                     uint64_t *applied_out);
+
 int stage_gpu_snapshot_info(const stage_snapshot_t *s, stage_snapshot_info_t *info);
 int stage_gpu_snapshot_destroy(stage_snapshot_t *s);
 

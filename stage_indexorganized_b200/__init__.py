@@ -53,6 +53,10 @@ SYMBOLS = {
     "stage_gpu_snapshot_add_leaves": (_i32, [_vp, _vp, _vp, _vp, _vp, _u64]),
     "stage_gpu_snapshot_seal": (_i32, [_vp]),
     "stage_gpu_snapshot_generate_ycsb": (_i32, [C.POINTER(Schema), _u64, _u64, _u64, _u32, C.POINTER(_vp)]),
+    "stage_gpu_snapshot_alloc_sorted": (_i32, [C.POINTER(Schema), _u64, _u32, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),
+                                               C.POINTER(_vp)]),
+    "stage_gpu_snapshot_seal_sorted": (_i32, [_vp]),
+    "stage_gpu_snapshot_apply_updates": (_i32, [_vp, _vp, _vp, _u32, _u32, _vp, _u64, _i32, C.POINTER(_u64)]),
     "stage_gpu_snapshot_info": (_i32, [_vp, C.POINTER(SnapshotInfo)]),
     "stage_gpu_snapshot_destroy": (_i32, [_vp]),
     "stage_gpu_snapshot_set_stream": (_i32, [_vp, _vp]),
@@ -178,6 +182,25 @@ class Snapshot:
         return cls(h, sc)
 
     @classmethod
+    def alloc_sorted(cls, n_rows, key_size, payload_size, rows_per_leaf=61, key_kind=KEY_AUTO, leaf_node_size=65536):
+        """Bulk load, step 1: returns (snapshot, raw_keys, payload, ts) — torch uint8/int32 views of the snapshot's own
+        device columns, to be filled with rows in reference key order; then call seal_sorted()."""
+        import torch
+        sc = Schema(key_size, payload_size, leaf_node_size, key_kind)
+        h, k, p, t = _vp(), _vp(), _vp(), _vp()
+        _check(lib().stage_gpu_snapshot_alloc_sorted(C.byref(sc), n_rows, rows_per_leaf, C.byref(h), C.byref(k), C.byref(p),
+                                                     C.byref(t)))
+        self = cls(h, sc)
+        dev = torch.device("cuda", torch.cuda.current_device())
+        keys = torch.as_tensor(_DeviceView(k.value, (n_rows, key_size), "|u1", self), device=dev)
+        pay = torch.as_tensor(_DeviceView(p.value, (n_rows, payload_size), "|u1", self), device=dev)
+        ts = torch.as_tensor(_DeviceView(t.value, (n_rows,), "<i4", self), device=dev)
+        return self, keys, pay, ts
+
+    def seal_sorted(self):
+        _check(lib().stage_gpu_snapshot_seal_sorted(self.h))
+
+    @classmethod
     def from_leaves(cls, leaf_ptrs, fences, has_fence, key_size, payload_size, leaf_node_size=65536,
                     key_kind=KEY_AUTO, versions=None, version_payloads=None, chain_heads=None, rows_hint=None):
         """Streaming construction: begin -> add_versions -> add_leaves -> seal."""
@@ -211,6 +234,21 @@ class Snapshot:
                                                    C.cast(heads_ptrs, _vp) if heads_ptrs is not None else None, n))
         _check(lib().stage_gpu_snapshot_seal(h))
         return self
+
+    def apply_updates(self, keys, patches, commit_ids, patch_off=0, device=False):
+        """Committed single-row updates, in order (stage_gpu_snapshot_apply_updates). keys (n,K) u8, patches
+        (n,patch_len) u8, commit_ids (n,) u32 — numpy arrays, or torch CUDA tensors with device=True.
+        Returns the number of updates applied (absent keys are ignored)."""
+        if not device:
+            keys = np.ascontiguousarray(keys, np.uint8)
+            patches = np.ascontiguousarray(patches, np.uint8)
+            commit_ids = np.ascontiguousarray(commit_ids, np.uint32)
+        n, patch_len = int(keys.shape[0]), int(patches.shape[1])
+        applied = _u64(0)
+        _check(lib().stage_gpu_snapshot_apply_updates(self.h, _ptr(keys), _ptr(patches), patch_off, patch_len,
+                                                      _ptr(commit_ids), n, IO_DEVICE if device else IO_HOST,
+                                                      C.byref(applied)))
+        return int(applied.value)
 
     def info(self):
         i = SnapshotInfo()

@@ -57,6 +57,42 @@ STAGE_HD uint32_t ycsb_rank_to_key(uint64_t N, uint64_t r) {
 }
 
 #if defined(__CUDACC__)
+// ---- bulk load from device-resident columns (stage_gpu_snapshot_alloc_sorted / seal_sorted) -------------------
+// raw keys (n x key_size bytes, already in reference key order) -> sortable key column; consolidated leaves of
+// rows_per_leaf records (slot = position in the leaf, no chains).
+template <int NW>
+__global__ void bulk_keys_kernel(const uint8_t *raw, uint64_t n, uint32_t key_size, uint32_t xormask, uint32_t rows_per_leaf,
+                                 uint32_t *skey, uint16_t *slot, uint32_t *chain) {
+    const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const SKey<NW> k = to_sortable<NW>(raw + i * key_size, key_size, xormask);
+#pragma unroll
+        for (int w = 0; w < NW; ++w) skey[i * NW + w] = k.w[w];
+        slot[i] = (uint16_t) (i % rows_per_leaf);
+        chain[i] = 0;
+    }
+}
+// leaf tables of a consolidated key column + the order check (keys must be strictly ascending: they are unique
+// in the reference, LeafNode::CheckUnique, src/vstore/b_tree.cpp:1395-1417); err = 3 on a violation.
+template <int NW>
+__global__ void bulk_leaves_kernel(const uint32_t *skey, uint64_t n, uint64_t n_leaves, uint32_t rows_per_leaf,
+                                   uint32_t *leaf_off, uint32_t *sep, uint8_t *cont, uint32_t *err) {
+    const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i + 1 < n; i += stride)
+        if (!skey_less<NW>(load_skey<NW>(skey, i), load_skey<NW>(skey, i + 1))) atomicExch(err, 3u);
+    for (uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; j <= n_leaves; j += stride) {
+        const uint64_t off = j * rows_per_leaf < n ? j * rows_per_leaf : n;
+        leaf_off[j] = (uint32_t) off;
+        if (j < n_leaves) {
+            const uint64_t end = (j + 1) * rows_per_leaf < n ? (j + 1) * rows_per_leaf : n;
+            const bool hop = j + 1 < n_leaves && end > off;      // separator of a consolidated leaf = its largest key
+#pragma unroll
+            for (int w = 0; w < NW; ++w) sep[j * NW + w] = hop ? skey[(end - 1) * NW + w] : 0xFFFFFFFFu;
+            cont[j] = hop ? 1 : 0;
+        }
+    }
+}
+
 __global__ void generate_ycsb_meta_kernel(GenArgs g) {
     const uint64_t stride = (uint64_t) gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < g.n_local; i += stride) {

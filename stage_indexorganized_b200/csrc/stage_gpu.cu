@@ -27,6 +27,8 @@
 #include "gather.cuh"
 #include "generate.cuh"
 #include "exchange.cuh"
+#include "refresh.cuh"
+#include <cub/device/device_radix_sort.cuh>
 
 using namespace stage;
 
@@ -51,6 +53,17 @@ static int g_device = 0;
         g_launches.fetch_add(1, std::memory_order_relaxed);                                  \
         CUDA_TRY(cudaGetLastError());                                                        \
     } while (0)
+
+static int g_sm_count = 0;
+static int sm_count() {
+    if (!g_sm_count) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+        if (g_sm_count <= 0) g_sm_count = 148;
+    }
+    return g_sm_count;
+}
 
 // ------------------------------------------------------------------------------------------------
 // snapshot
@@ -123,6 +136,11 @@ struct stage_snapshot {
     cudaEvent_t tev[3] = {nullptr, nullptr, nullptr};
     bool timing = false, timed_gather = false;
 
+    uint64_t ver_cap = 0;                       // capacity (versions) of the d_ver_* arrays
+    DevBuf rf_keys, rf_patch, rf_cid, rf_row, rf_order, rf_row_sorted, rf_order_sorted, rf_tmp, rf_applied;   // refresh scratch
+    uint8_t *d_raw_keys = nullptr;              // bulk load: caller-filled raw keys, released by seal_sorted
+    uint32_t bulk_rows_per_leaf = 0;
+
     // scratch for STAGE_IO_HOST batches
     DevBuf sc_keys, sc_found, sc_ts, sc_keyout, sc_payload, sc_sizes, sc_counts;
     DevBuf sc_srcrow;                           // source-row lists handed from the plan kernels to the gather
@@ -177,7 +195,7 @@ static void snapshot_free(stage_snapshot *s) {
     cudaSetDevice(s->device);
     void *ptrs[] = {s->d_skey, s->d_slot, s->d_ts, s->d_chain, s->d_payload, s->d_leaf_off, s->d_sep, s->d_cont,
                     s->d_has_sep, s->d_ver_begin, s->d_ver_commit, s->d_ver_next, s->d_ver_payload,
-                    s->d_err, s->d_stage[0], s->d_stage[1]};
+                    s->d_err, s->d_stage[0], s->d_stage[1], s->d_raw_keys};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     for (int i = 0; i < 2; ++i) {
@@ -186,6 +204,8 @@ static void snapshot_free(stage_snapshot *s) {
     }
     s->sc_keys.release(); s->sc_found.release(); s->sc_ts.release(); s->sc_keyout.release();
     s->sc_payload.release(); s->sc_sizes.release(); s->sc_counts.release(); s->sc_srcrow.release();
+    s->rf_keys.release(); s->rf_patch.release(); s->rf_cid.release(); s->rf_row.release(); s->rf_order.release();
+    s->rf_row_sorted.release(); s->rf_order_sorted.release(); s->rf_tmp.release(); s->rf_applied.release();
     for (int i = 0; i < 3; ++i)
         if (s->tev[i]) cudaEventDestroy(s->tev[i]);
     if (s->own_stream && s->stream) cudaStreamDestroy(s->stream);
@@ -465,6 +485,7 @@ extern "C" int stage_gpu_snapshot_seal(stage_snapshot_t *s) {
             (rc = dev_alloc(s, &s->d_ver_next, V)) ||
             (rc = dev_alloc(s, &s->d_ver_payload, V * (uint64_t) s->schema.payload_size)))
             return rc;
+        s->ver_cap = V;
         std::vector<uint32_t> b(V), c(V), nx(V);
         for (uint64_t i = 0; i < V; ++i) {
             b[i] = s->h_versions[i].begin_id; c[i] = s->h_versions[i].commit_id; nx[i] = s->h_versions[i].next;
@@ -635,6 +656,179 @@ extern "C" int stage_gpu_snapshot_generate_ycsb(const stage_schema_t *schema, ui
 }
 
 // ------------------------------------------------------------------------------------------------
+// bulk load from device-resident sorted columns
+// ------------------------------------------------------------------------------------------------
+extern "C" int stage_gpu_snapshot_alloc_sorted(const stage_schema_t *schema, uint64_t n_rows, uint32_t rows_per_leaf,
+                                               stage_snapshot_t **out, void **raw_keys_dev, void **payload_dev,
+                                               uint32_t **ts_dev) {
+    if (!out || !schema || n_rows == 0 || rows_per_leaf == 0 || rows_per_leaf > 0xFFFFu) return STAGE_ERR_ARG;
+    stage_snapshot *s = nullptr;
+    int rc = snapshot_new(schema, &s);
+    if (rc) return rc;
+    const uint64_t L = (n_rows + rows_per_leaf - 1) / rows_per_leaf;
+    if ((rc = alloc_columns(s, L, n_rows)) || (rc = dev_alloc(s, &s->d_raw_keys, n_rows * (uint64_t) schema->key_size))) {
+        snapshot_free(s);
+        return rc;
+    }
+    if (cudaMemsetAsync(s->d_ts, 0, n_rows * 4, s->stream) != cudaSuccess || cudaStreamSynchronize(s->stream) != cudaSuccess) {
+        snapshot_free(s);
+        return STAGE_ERR_CUDA;
+    }
+    s->n_rows = n_rows;
+    s->n_leaves = L;
+    s->max_leaf_rows = (uint32_t) std::min<uint64_t>(rows_per_leaf, n_rows);
+    s->bulk_rows_per_leaf = rows_per_leaf;
+    if (raw_keys_dev) *raw_keys_dev = s->d_raw_keys;
+    if (payload_dev) *payload_dev = s->d_payload;
+    if (ts_dev) *ts_dev = s->d_ts;
+    *out = s;
+    return STAGE_OK;
+}
+
+template <int NW>
+static int launch_bulk(stage_snapshot *s) {
+    const unsigned blocks = (unsigned) std::min<uint64_t>((s->n_rows + 255) / 256 + 1, 148ull * 32);
+    bulk_keys_kernel<NW><<<blocks, 256, 0, s->stream>>>(s->d_raw_keys, s->n_rows, s->schema.key_size, s->xormask,
+                                                        s->bulk_rows_per_leaf, s->d_skey, s->d_slot, s->d_chain);
+    LAUNCH_CHECK();
+    bulk_leaves_kernel<NW><<<blocks, 256, 0, s->stream>>>(s->d_skey, s->n_rows, s->n_leaves, s->bulk_rows_per_leaf,
+                                                          s->d_leaf_off, s->d_sep, s->d_cont, s->d_err);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_seal_sorted(stage_snapshot_t *s) {
+    if (!s || s->sealed || !s->d_raw_keys) return STAGE_ERR_STATE;
+    CUDA_TRY(cudaSetDevice(s->device));
+    CUDA_TRY(cudaDeviceSynchronize());          // the caller filled the columns on its own streams
+    int rc;
+    switch (s->nw) {
+        case 1: rc = launch_bulk<1>(s); break;
+        case 2: rc = launch_bulk<2>(s); break;
+        case 4: rc = launch_bulk<4>(s); break;
+        default: rc = launch_bulk<8>(s); break;
+    }
+    if (rc) return rc;
+    uint32_t err = 0;
+    CUDA_TRY(cudaMemcpyAsync(&err, s->d_err, 4, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    if (err == 3) {
+        g_last_error = "bulk load: keys are not strictly ascending in reference key order";
+        return STAGE_ERR_ARG;
+    }
+    const size_t raw_bytes = ((s->n_rows * (uint64_t) s->schema.key_size + 255) & ~size_t(255)) + 256;
+    cudaFree(s->d_raw_keys);
+    s->d_raw_keys = nullptr;
+    s->device_bytes -= std::min(s->device_bytes, raw_bytes);
+    return finish_seal(s);
+}
+
+// ------------------------------------------------------------------------------------------------
+// incremental refresh: committed updates (refresh.cuh)
+// ------------------------------------------------------------------------------------------------
+static int grow_versions(stage_snapshot *s, uint64_t need) {
+    if (need <= s->ver_cap) return STAGE_OK;
+    const uint64_t cap = std::max<uint64_t>(need, s->ver_cap * 2);
+    const uint64_t V = s->n_versions, P = s->schema.payload_size;
+    uint32_t *nb = nullptr, *nc = nullptr, *nn = nullptr;
+    uint8_t *np_ = nullptr;
+    int rc;
+    if ((rc = dev_alloc(s, &nb, cap)) || (rc = dev_alloc(s, &nc, cap)) || (rc = dev_alloc(s, &nn, cap)) ||
+        (rc = dev_alloc(s, &np_, cap * P)))
+        return rc;
+    if (V) {
+        CUDA_TRY(cudaMemcpyAsync(nb, s->d_ver_begin, V * 4, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_TRY(cudaMemcpyAsync(nc, s->d_ver_commit, V * 4, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_TRY(cudaMemcpyAsync(nn, s->d_ver_next, V * 4, cudaMemcpyDeviceToDevice, s->stream));
+        CUDA_TRY(cudaMemcpyAsync(np_, s->d_ver_payload, V * P, cudaMemcpyDeviceToDevice, s->stream));
+    }
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    void *old[] = {s->d_ver_begin, s->d_ver_commit, s->d_ver_next, s->d_ver_payload};
+    for (void *p : old)
+        if (p) cudaFree(p);
+    s->d_ver_begin = nb; s->d_ver_commit = nc; s->d_ver_next = nn; s->d_ver_payload = np_;
+    s->ver_cap = cap;
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_apply_updates(stage_snapshot_t *s, const void *keys, const void *patches,
+                                                uint32_t patch_off, uint32_t patch_len, const uint32_t *commit_ids,
+                                                uint64_t n, int flags, uint64_t *applied_out) {
+    if (!s || (n && (!keys || !patches || !commit_ids))) return STAGE_ERR_ARG;
+    if (!s->sealed) return STAGE_ERR_STATE;
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    if (patch_len == 0 || (uint64_t) patch_off + patch_len > P || n > 0x7FFFFFFFull ||
+        s->n_versions + n >= (uint64_t) kVersionRowFlag)
+        return STAGE_ERR_ARG;
+    if (applied_out) *applied_out = 0;
+    if (n == 0) return STAGE_OK;
+    std::lock_guard<std::mutex> lock(s->mu);
+    CUDA_TRY(cudaSetDevice(s->device));
+    int rc;
+    if ((rc = grow_versions(s, s->n_versions + n))) return rc;
+    RefreshArgs a{};
+    if (flags & STAGE_IO_DEVICE) {
+        a.keys = static_cast<const uint8_t *>(keys);
+        a.patches = static_cast<const uint8_t *>(patches);
+        a.commit_ids = commit_ids;
+    } else {
+        if ((rc = s->rf_keys.ensure(n * K)) || (rc = s->rf_patch.ensure(n * (uint64_t) patch_len)) || (rc = s->rf_cid.ensure(n * 4)))
+            return rc;
+        CUDA_TRY(cudaMemcpyAsync(s->rf_keys.p, keys, n * K, cudaMemcpyHostToDevice, s->stream));
+        CUDA_TRY(cudaMemcpyAsync(s->rf_patch.p, patches, n * (uint64_t) patch_len, cudaMemcpyHostToDevice, s->stream));
+        CUDA_TRY(cudaMemcpyAsync(s->rf_cid.p, commit_ids, n * 4, cudaMemcpyHostToDevice, s->stream));
+        a.keys = static_cast<const uint8_t *>(s->rf_keys.p);
+        a.patches = static_cast<const uint8_t *>(s->rf_patch.p);
+        a.commit_ids = static_cast<const uint32_t *>(s->rf_cid.p);
+    }
+    if ((rc = s->rf_row.ensure(n * 4)) || (rc = s->rf_order.ensure(n * 4)) || (rc = s->rf_row_sorted.ensure(n * 4)) ||
+        (rc = s->rf_order_sorted.ensure(n * 4)) || (rc = s->rf_applied.ensure(4)))
+        return rc;
+    a.n = n;
+    a.patch_off = patch_off;
+    a.patch_len = patch_len;
+    a.v0 = (uint32_t) s->n_versions;
+    a.ts = s->d_ts; a.chain = s->d_chain; a.payload = s->d_payload;
+    a.ver_begin = s->d_ver_begin; a.ver_commit = s->d_ver_commit; a.ver_next = s->d_ver_next; a.ver_payload = s->d_ver_payload;
+    a.payload_size = P;
+    a.row = static_cast<uint32_t *>(s->rf_row.p);
+    a.order = static_cast<uint32_t *>(s->rf_order.p);
+    a.applied = static_cast<uint32_t *>(s->rf_applied.p);
+    CUDA_TRY(cudaMemsetAsync(a.applied, 0, 4, s->stream));
+    {
+        const size_t smem = (size_t) std::max<uint32_t>(s->view.smem_words, 4) * 4;
+        const unsigned blocks = (unsigned) std::min<uint64_t>((n + kProbeThreads - 1) / kProbeThreads, (uint64_t) sm_count() * 8);
+        switch (s->nw) {
+            case 1: refresh_locate_kernel<1><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a); break;
+            case 2: refresh_locate_kernel<2><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a); break;
+            case 4: refresh_locate_kernel<4><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a); break;
+            default: refresh_locate_kernel<8><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a); break;
+        }
+        LAUNCH_CHECK();
+    }
+    // stable sort of (row, update index) by row: runs of equal rows keep the batch order
+    size_t tmp_bytes = 0;
+    uint32_t *row_sorted = static_cast<uint32_t *>(s->rf_row_sorted.p), *order_sorted = static_cast<uint32_t *>(s->rf_order_sorted.p);
+    CUDA_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, a.row, row_sorted, a.order, order_sorted, (int) n, 0, 32, s->stream));
+    if ((rc = s->rf_tmp.ensure(tmp_bytes))) return rc;
+    CUDA_TRY(cub::DeviceRadixSort::SortPairs(s->rf_tmp.p, tmp_bytes, a.row, row_sorted, a.order, order_sorted, (int) n, 0, 32, s->stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    a.row_sorted = row_sorted;
+    a.order = order_sorted;
+    refresh_apply_kernel<<<(unsigned) ((n * 32 + 255) / 256), 256, 0, s->stream>>>(a);
+    LAUNCH_CHECK();
+    refresh_clear_unused_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s->stream>>>(a);
+    LAUNCH_CHECK();
+    uint32_t applied = 0;
+    CUDA_TRY(cudaMemcpyAsync(&applied, a.applied, 4, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    s->n_versions += n;
+    fill_view(s);
+    if (applied_out) *applied_out = applied;
+    return STAGE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // info / lifecycle
 // ------------------------------------------------------------------------------------------------
 extern "C" int stage_gpu_init(int device) {
@@ -700,16 +894,6 @@ extern "C" void *stage_gpu_snapshot_get_stream(const stage_snapshot_t *s) { retu
 // ------------------------------------------------------------------------------------------------
 // reads
 // ------------------------------------------------------------------------------------------------
-static int g_sm_count = 0;
-static int sm_count() {
-    if (!g_sm_count) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
-        if (g_sm_count <= 0) g_sm_count = 148;
-    }
-    return g_sm_count;
-}
 
 template <typename V>
 static int launch_gather_v(stage_snapshot *s, const GatherArgs &g) {

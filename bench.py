@@ -4,13 +4,22 @@
 Workload (BASELINE.json configs[1]): YCSB int table (4-byte keys, 1000-byte payload), 10 M tuples per
 GPU, 10 % of rows overwritten by committed updates (version chains), scan_mode range scans of 1000
 rows with the MVCC visibility filter (IndexScanExecutor range semantics) at a read timestamp in the
-middle of the update commit ids. A "step" = one batch of `--scans` scans through the scan kernel.
+middle of the update commit ids. A "step" = one batch of `--scans` scans through the scan kernels.
 Secondary leg in the same JSON line ("probe"): batches of 2^20 uniform point probes on the same table.
+
+The GPU legs use product code only: the table is generated on the device with the reference's row
+function in the reference's key order (stage_gpu_snapshot_generate_ycsb) and the committed updates are
+installed by the refresh kernels (stage_gpu_snapshot_apply_updates); key streams come from the package's
+restatement of the drivers' generators. oracle/ is touched only by the cpu_baseline leg (and by
+--impl reference), which builds the same table with the reference's own loader, times the reference's
+CPU scan path on it, and — having a reference-format tree at hand — also times the record-layout
+transform on that tree ("transform") and cross-checks a sample of scans and probes ("parity_check").
+`--table host` runs the GPU legs on the flattened host tree instead.
 
   value     rows/s, whole job (all ranks), inputs and outputs resident in HBM, CUDA-event timed
   e2e       the same metric through the host-buffer C ABI call (pinned host start keys in, pinned host
             rows out; the H2D/D2H copies are inside the timed region)
-  roofline  algorithmic bytes of the scan kernel / its CUDA-event duration vs the measured HBM copy peak
+  roofline  algorithmic bytes of the dominant kernel / its CUDA-event duration vs the measured HBM copy peak
   cpu_baseline  the reference's own CPU path (oracle/_ref when its prebuilt library is present, else
             the C port) on this box's host cores over a bounded sample of the same scans
 
@@ -18,9 +27,9 @@ Secondary leg in the same JSON line ("probe"): batches of 2^20 uniform point pro
 
 N > 1 (torchrun, one rank per GPU): the table is range-partitioned in reference key order; every rank
 holds --rows-multi tuples (default 125 M = BASELINE configs[4], 1 B tuples over 8 GPUs; weak scaling: the
-per-GPU step is the same 4096 x 1000-row scans) built on the device by stage_gpu_snapshot_generate_ycsb
-plus a halo of the next shard's first rows; scans run shard-local (no data-path collective); probes are
-routed to their owning shard by kernels that store keys / result rows straight into the peers' memory over
+per-GPU step is the same 4096 x 1000-row scans) built on the device plus a halo of the next shard's first
+rows, with 10 % of its rows updated; scans run shard-local (no data-path collective); probes are routed
+to their owning shard by kernels that store keys / result rows straight into the peers' memory over
 NVLink (csrc/exchange.cuh), with the NCCL all-to-all form timed beside it.
 """
 import argparse
@@ -60,7 +69,9 @@ def parse_args():
     ap.add_argument("--e2e-scans", type=int, default=1024)
     ap.add_argument("--cpu-scans", type=int, default=0, help="scans in the CPU-baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--generated", action="store_true", help="force the on-device table generator at N=1")
+    ap.add_argument("--table", default="device", choices=["device", "host"],
+                    help="N = 1: 'device' builds the table with the on-device generator + refresh kernels (no oracle in "
+                         "the GPU leg); 'host' flattens a tree built by the reference loader (transform kernel)")
     return ap.parse_args()
 
 
@@ -137,9 +148,8 @@ def build_host_table(rows, updates):
         t, kind = pyoracle.OracleTable(P_BYTES), "port"
     assert t.load_ycsb_int(0, rows) == rows
     if updates:
-        uk = pyoracle.uniform_keys(rows, updates, seed=2) - 1         # existing keys 0..rows-1
-        uk = uk.astype(np.uint32).view(np.uint8).reshape(-1, 4)
-        assert t.commit_update_batch(uk, 10) == updates
+        uk = update_keys(rows, updates).view(np.uint8).reshape(-1, 4)
+        assert t.commit_update_batch(uk, FIRST_CID) == updates
     return t, kind
 
 
@@ -157,8 +167,29 @@ def calibrated_scan_count(table, rows, scan_size, read_ts, threads, target_s):
 
 
 def scan_start_keys(rows, n, seed):
-    from oracle import pyoracle
-    return (pyoracle.uniform_keys(rows, n, seed=seed) - 1).astype(np.uint32)
+    from stage_indexorganized_b200 import ycsb
+    return (ycsb.uniform_keys(rows, n, seed=seed) - 1).astype(np.uint32)
+
+
+FIRST_CID = 10
+
+
+def update_keys(rows, updates):
+    """Keys of the committed updates: uniform over the existing keys 0..rows-1 (FastRandom seed 2); update i commits
+    with id FIRST_CID + i and rewrites one 100-byte column with (uint8) commit id."""
+    from stage_indexorganized_b200 import ycsb
+    return (ycsb.uniform_keys(rows, updates, seed=2) - 1).astype(np.uint32)
+
+
+def apply_updates_on_device(snap, keys_u32, torch, dev):
+    """The same committed updates, installed on the GPU snapshot (stage_gpu_snapshot_apply_updates)."""
+    n = len(keys_u32)
+    if n == 0:
+        return 0
+    d_keys = torch.from_numpy(np.ascontiguousarray(keys_u32, np.uint32).view(np.uint8).reshape(-1, 4)).to(dev)
+    cids = torch.arange(FIRST_CID, FIRST_CID + n, dtype=torch.int32, device=dev)
+    patches = (cids & 0xFF).to(torch.uint8)[:, None].expand(n, 100).contiguous()
+    return snap.apply_updates(d_keys, patches, cids, patch_off=100, device=True)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -232,21 +263,30 @@ def main():
         args.rows = args.rows_multi
     rows, S, n_scans, n_probes = args.rows, args.scan_size, args.scans, args.probes
     updates = rows // 10
-    use_generated = world > 1 or args.generated
+    use_host_tree = world == 1 and args.table == "host"
     host_table, table_kind = None, None
     t_build0 = time.time()
-    if use_generated:
+    read_ts = FIRST_CID + updates // 2
+    if not use_host_tree:
+        # product-only construction: the table is generated on the device in the reference's row function and key
+        # order, then the committed updates are installed by the refresh kernels (version chains on 10 % of rows)
+        from stage_indexorganized_b200.ycsb import rank_to_key
         halo = 2 * S + 128
         total = rows * world
         first = rank * rows
         n_local = min(rows + (halo if rank + 1 < world else 0), total - first)
         snap = sg.Snapshot.generate_ycsb(total, P_BYTES, rows_per_leaf=61, first_rank=first, n_local=n_local)
-        read_ts = 1
-        table_desc = "generated on device (consolidated leaves, 61 rows/leaf, no version chains)"
+        if world == 1:
+            uk = update_keys(rows, updates)
+        else:       # updates of keys this shard owns
+            uk = rank_to_key(total, first + np.random.default_rng(77 + rank).integers(0, rows, updates))
+        applied = apply_updates_on_device(snap, uk, torch, dev)
+        assert applied == updates, (applied, updates)
+        table_desc = ("generated on device in reference key order (consolidated leaves, 61 rows/leaf), "
+                      f"{updates} committed updates installed by stage_gpu_snapshot_apply_updates")
     else:
         host_table, table_kind = build_host_table(rows, updates)
         snap = sg.Snapshot.from_tree(host_table.root, K_BYTES, P_BYTES)
-        read_ts = 10 + updates // 2
         table_desc = f"host tree built by the reference loader ({table_kind}), flattened by the transform kernel"
     t_build = time.time() - t_build0
     info = snap.info()
@@ -255,15 +295,14 @@ def main():
 
     # ---- device-resident inputs / outputs -------------------------------------------------------
     n_batches = args.warmup + args.steps
-    if use_generated:
-        from stage_indexorganized_b200.ycsb import rank_to_key
+    if world > 1:
         rng = np.random.default_rng(1000 + rank)
         sk_all = rank_to_key(rows * world, rank * rows + rng.integers(0, rows, size=(n_batches, n_scans)))
         pk_all = rng.integers(0, rows * world + 1, size=(n_batches, n_probes)).astype(np.uint32)
     else:
-        from oracle import pyoracle  # input key streams come from the reference's generators (FastRandom)
+        from stage_indexorganized_b200 import ycsb      # the drivers' generators (FastRandom), restated in the package
         sk_all = np.stack([scan_start_keys(rows, n_scans, seed=100 + b) for b in range(n_batches)])
-        pk_all = np.stack([pyoracle.uniform_keys(rows, n_probes, seed=200 + b) for b in range(n_batches)])
+        pk_all = np.stack([ycsb.uniform_keys(rows, n_probes, seed=200 + b) for b in range(n_batches)])
     d_sk = torch.from_numpy(sk_all.astype(np.uint32).view(np.int32)).to(dev)
     d_sizes = torch.full((n_scans,), S, dtype=torch.int32, device=dev)
     d_counts = torch.zeros((n_batches, n_scans), dtype=torch.int32, device=dev)
@@ -469,20 +508,37 @@ def main():
            "d2h_bytes_per_step": ne * 4 + ne * S * (K_BYTES + 4 + P_BYTES),
            "scans_per_step": ne}
 
-    # ---- CPU baseline (rank 0, N = 1) -----------------------------------------------------------
-    cpu = None
+    # ---- CPU baseline (rank 0, N = 1): the only part of the run that touches oracle/ ---------------------------
+    cpu, transform, parity = None, None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         if host_table is None:
-            host_table, table_kind = build_host_table(rows, updates)
-            cpu_ts = 10 + updates // 2
-        else:
-            cpu_ts = read_ts
+            host_table, table_kind = build_host_table(rows, updates)     # reference loader + the same updates
         threads = os.cpu_count() or 1
-        n_cpu = args.cpu_scans or calibrated_scan_count(host_table, rows, S, cpu_ts, threads, 15.0)
+        n_cpu = args.cpu_scans or calibrated_scan_count(host_table, rows, S, read_ts, threads, 15.0)
         sk = scan_start_keys(rows, n_cpu, seed=100 + args.warmup).view(np.uint8).reshape(-1, 4)
-        rps, r, sec = cpu_scan_sample(host_table, sk, S, cpu_ts, threads)
+        rps, r, sec = cpu_scan_sample(host_table, sk, S, read_ts, threads)
         cpu = {"value": rps, "unit": "rows/s", "cores": threads, "kind": table_kind,
-               "sample": f"{n_cpu} scans x {S} rows ({r} rows, {sec:.1f} s), {threads} pinned threads, same table"}
+               "sample": f"{n_cpu} scans x {S} rows ({r} rows, {sec:.1f} s), {threads} pinned threads, "
+                         "table built by the reference loader with the same rows and the same committed updates"}
+        # with the reference-format tree at hand: time the record-layout transform on it and cross-check a sample
+        t0 = time.time()
+        hsnap = snap if use_host_tree else sg.Snapshot.from_tree(host_table.root, K_BYTES, P_BYTES)
+        t_tr = time.time() - t0
+        hi = hsnap.info()
+        if not use_host_tree:
+            transform = {"leaves": int(hi.n_leaves), "rows": int(hi.n_rows), "seconds": t_tr,
+                         "leaf_image_GB_per_s": hi.n_leaves * 65536 / t_tr / 1e9,
+                         "note": "stage_gpu_snapshot_from_tree: host walk + pinned staging + H2D + leaf_transform_kernel"}
+        ns = 256
+        got = hsnap.scan(sk[:ns], S, read_ts, 1)
+        want = host_table.scan(sk[:ns], S, read_ts, 1)
+        pk = pk_all[0][:65536].astype(np.uint32).view(np.uint8).reshape(-1, 4)
+        gp, wp = snap.probe(pk, read_ts), host_table.probe(pk, read_ts)
+        ok = all(np.array_equal(g, w) for g, w in zip(got, want)) and all(np.array_equal(g, w) for g, w in zip(gp, wp))
+        parity = {"ok": bool(ok), "checked": f"{ns} scans x {S} rows (flattened host tree vs CPU {table_kind}) and "
+                                             f"{len(pk)} probes (bench table vs CPU {table_kind}), bit-exact"}
+        if hsnap is not snap:
+            hsnap.close()
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -506,6 +562,8 @@ def main():
                          "step_algorithmic_bytes": algo_bytes / args.steps,
                          "step_achieved": step_achieved, "step_frac": step_achieved / peak},
             "cpu_baseline": cpu,
+            "parity_check": parity,
+            "transform": transform,
             "e2e": e2e,
             "gpu_launches": int(launches),
             "clocks": clk.summary(),

@@ -7,6 +7,81 @@ inside a given range shard.
 """
 import numpy as np
 
+# ---- the drivers' generators (benchmark/benchmark_common.h:12-105), vectorised ------------------------------
+_LCG_A, _LCG_C, _LCG_M = 0x5DEECE66D, 0xB, (1 << 48) - 1
+
+
+def lcg_states(seed, count):
+    """States s_1..s_count of FastRandom(seed): s_0 = (seed ^ A) & M, s_{k+1} = (A s_k + C) & M
+    (benchmark_common.h:52-60). Vectorised by composing the affine step maps (A, C)^(2^j)."""
+    count = int(count)
+    idx = np.arange(1, count + 1, dtype=np.uint64)
+    mul = np.ones(count, np.uint64)
+    add = np.zeros(count, np.uint64)
+    a, c = np.uint64(_LCG_A), np.uint64(_LCG_C)
+    m = np.uint64(_LCG_M)
+    with np.errstate(over="ignore"):
+        j = 0
+        while (1 << j) <= count:
+            bit = ((idx >> np.uint64(j)) & np.uint64(1)).astype(bool)
+            # apply map (a, c) after the maps collected so far:  x -> a (mul x + add) + c
+            mul = np.where(bit, (a * mul) & m, mul)
+            add = np.where(bit, (a * add + c) & m, add)
+            a, c = (a * a) & m, (a * c + c) & m
+            j += 1
+        s0 = np.uint64((int(seed) ^ _LCG_A) & _LCG_M)
+        return (mul * s0 + add) & m
+
+
+def fastrandom_next64(seed, count):
+    """FastRandom(seed).next() called `count` times: (next(32) << 32) + next(32)."""
+    st = lcg_states(seed, 2 * count)
+    return ((st[0::2] >> np.uint64(16)) << np.uint64(32)) + (st[1::2] >> np.uint64(16))
+
+
+def uniform_keys(n_rows, count, seed=1):
+    """1 + next_u32() % N: a uniform key stream over keys 1..N, the range the YCSB driver draws from
+    (ycsb.cpp:99-103; key N is never loaded, so it misses)."""
+    x = lcg_states(seed, count) >> np.uint64(16)
+    return (np.uint64(1) + x % np.uint64(n_rows)).astype(np.uint32)
+
+
+def random_strings(seed, count, length=16):
+    """FastRandom(seed).next_string(length) called `count` times (next_char = next(8) % 256)."""
+    return (lcg_states(seed, count * length) >> np.uint64(40)).astype(np.uint8).reshape(count, length)
+
+
+class Zipf:
+    """ZipfDistribution (benchmark_common.h:67-105) with a fixed FastRandom seed."""
+
+    def __init__(self, n, theta, seed=1):
+        self.n, self.theta, self.seed = n, theta, seed
+        i = np.arange(1, n + 1, dtype=np.float64)
+        self.zetan = float(np.sum(np.power(1.0 / i, theta)))
+        self.zeta2 = float(1.0 + np.power(0.5, theta))
+
+    def draw(self, count):
+        st = lcg_states(self.seed, 2 * count)        # NextUniform = ((next(26) << 27) + next(27)) / 2^53
+        h = st[0::2] >> np.uint64(22)
+        l = st[1::2] >> np.uint64(21)
+        u = ((h << np.uint64(27)) + l).astype(np.float64) / float(1 << 53)
+        alpha = 1.0 / (1.0 - self.theta)
+        eta = (1 - (2.0 / self.n) ** (1 - self.theta)) / (1 - self.zeta2 / self.zetan)
+        uz = u * self.zetan
+        out = 1 + (self.n * np.power(eta * u - eta + 1, alpha)).astype(np.uint64)
+        out[uz < 1 + 0.5 ** self.theta] = 2
+        out[uz < 1] = 1
+        return out
+
+
+def ycsb_update_patch(payload_size, commit_ids):
+    """The committed YCSB update used by the benchmark and the tests: payload bytes [lo, hi) <- (uint8) commit id
+    (one 100-byte column of the 10 x 100-byte tuple, ycsb_mixed.cpp:38-80). Returns (patch_off, patches)."""
+    lo, hi = (100 if payload_size > 100 else 0), (200 if payload_size > 200 else payload_size)
+    cids = np.asarray(commit_ids, np.uint32)
+    return lo, np.repeat((cids & 0xFF).astype(np.uint8)[:, None], hi - lo, axis=1)
+
+
 
 def _le_count(t, al):
     t = t.astype(np.int64)

@@ -119,3 +119,74 @@ def sort_keys(keys):
     """uint32 keys sorted in reference order."""
     k = np.asarray(keys, np.uint32)
     return k[np.argsort(k.byteswap() ^ np.uint32(0x80808080), kind="stable")]
+
+
+# ---- YCSB string-key table (-m), built on the device (BASELINE configs[2]: 100 M tuples do not fit a host tree) ----
+def _lcg_jump_torch(start_idx, seed, torch):
+    """State s_k of FastRandom(seed) for every k in start_idx (int64 CUDA tensor), by composing the step maps
+    (A, C)^(2^j) over the bits of k. int64 products wrap mod 2^64, which keeps the low 48 bits exact."""
+    a, c, m = _LCG_A, _LCG_C, _LCG_M
+    mul = torch.ones_like(start_idx)
+    add = torch.zeros_like(start_idx)
+    j = 0
+    top = int(start_idx.max().item()) if start_idx.numel() else 0
+    while (1 << j) <= top:
+        bit = ((start_idx >> j) & 1).bool()
+        sa = a - (1 << 64) if a >= (1 << 63) else a
+        mul = torch.where(bit, (mul * sa) & m, mul)
+        add = torch.where(bit, (add * sa + c) & m, add)
+        a, c = (a * a) & m, (a * c + c) & m
+        j += 1
+    s0 = (int(seed) ^ _LCG_A) & m
+    return (mul * s0 + add) & m
+
+
+def string_keys_torch(seed, first_row, n_rows, device, length=16):
+    """Keys of rows [first_row, first_row + n_rows) of the YCSB string table: FastRandom(seed).next_string(16) per
+    row in rowid order (ycsb_loader.cpp:107-117; next_char = next(8) % 256). uint8 [n_rows, length] CUDA tensor."""
+    import torch
+    rows = torch.arange(first_row, first_row + n_rows, dtype=torch.int64, device=device)
+    s = _lcg_jump_torch(rows * length, seed, torch)
+    out = torch.empty((n_rows, length), dtype=torch.uint8, device=device)
+    for ch in range(length):
+        s = (s * _LCG_A + _LCG_C) & _LCG_M
+        out[:, ch] = (s >> 40).to(torch.uint8)
+    return out
+
+
+def _key16_words(keys, torch):
+    """Two int64 per 16-byte key whose SIGNED order is the memcmp order of the key bytes."""
+    b = keys.to(torch.int64)
+    hi = torch.zeros(keys.shape[0], dtype=torch.int64, device=keys.device)
+    lo = torch.zeros_like(hi)
+    for i in range(8):
+        hi = (hi << 8) | b[:, i]
+        lo = (lo << 8) | b[:, 8 + i]
+    sign = -(1 << 63)
+    return hi ^ sign, lo ^ sign
+
+
+def build_string_table_device(n_rows, payload_size=1000, seed=1804289383, rows_per_leaf=61, chunk=8_000_000):
+    """The YCSB string table in flattened form, built on the current CUDA device: 16 random key bytes per row
+    (seeded like the reference's first un-seeded rand(), 1804289383), payload payload_size x 'a', commit id 0; rows
+    sorted in reference key order (memcmp for 16-byte keys) and bulk-loaded with alloc_sorted / seal_sorted.
+    Returns (snapshot, keys_by_rowid uint8 [n,16] CUDA, order int64 [n] CUDA: order[r] = rowid of the r-th smallest key)."""
+    import torch
+    from . import Snapshot
+    dev = torch.device("cuda", torch.cuda.current_device())
+    keys = torch.empty((n_rows, 16), dtype=torch.uint8, device=dev)
+    for lo in range(0, n_rows, chunk):
+        m = min(chunk, n_rows - lo)
+        keys[lo:lo + m] = string_keys_torch(seed, lo, m, dev)
+    hi_w, lo_w = _key16_words(keys, torch)
+    p1 = torch.sort(lo_w, stable=True).indices
+    p2 = torch.sort(hi_w[p1], stable=True).indices
+    order = p1[p2]
+    del hi_w, lo_w, p1, p2
+    snap, raw, pay, _ = Snapshot.alloc_sorted(n_rows, 16, payload_size, rows_per_leaf)
+    for lo in range(0, n_rows, chunk):
+        m = min(chunk, n_rows - lo)
+        raw[lo:lo + m] = keys[order[lo:lo + m]]
+    pay.fill_(ord("a"))
+    snap.seal_sorted()
+    return snap, keys, order

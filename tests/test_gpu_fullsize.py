@@ -1,0 +1,197 @@
+"""GPU, BASELINE.json's full sizes: tables too large for a host tree are built on the device (product code) and the
+read path is checked through properties that do not need the CPU checker at that size:
+
+  * a closed-form MODEL of the table: row r of the YCSB int table in reference key order is rank_to_key(N, r), its
+    payload is 1000 x (uint8) key with one 100-byte column rewritten by every committed update, and the version a
+    reader at read_ts sees follows the executor rule (include/execute/executor.h:383-446, 465-534): the in-leaf
+    version if read_ts >= its commit id, else the newest retired version with begin <= read_ts <= commit, where
+    a retired version with begin 0 (the loader's) ends the walk — so a row is invisible before its first update;
+  * order / contiguity: a scan of S rows from the r-th key returns exactly rows r .. r+S-1 of the key order
+    (consolidated leaves), cut at the end of the table; idempotence: the same batch twice gives the same bytes.
+
+The model itself is pinned against the CPU checker at a size the checker handles (test_model_matches_checker)."""
+import numpy as np
+import pytest
+import torch
+
+import stage_indexorganized_b200 as sg
+from stage_indexorganized_b200 import ycsb
+from stage_indexorganized_b200.ycsb import rank_to_key
+from helpers import u32_keys
+from oracle import pyoracle
+
+pytestmark = pytest.mark.gpu
+FIRST_CID = 10
+
+
+class UpdateModel:
+    """Committed updates (key, commit id = FIRST_CID + i) -> what a reader sees."""
+
+    def __init__(self, upd_keys):
+        k = np.asarray(upd_keys, np.uint64)
+        cid = np.arange(FIRST_CID, FIRST_CID + len(k), dtype=np.uint64)
+        self.code = np.sort((k << np.uint64(32)) | cid)           # (key, cid) pairs, sorted
+        self.keys_sorted = self.code >> np.uint64(32)
+
+    def visible(self, keys, read_ts):
+        """-> (visible bool[n], stamp u32[n]) for existing keys."""
+        k = np.asarray(keys, np.uint64)
+        lo = np.searchsorted(self.keys_sorted, k, "left")
+        hi = np.searchsorted(self.keys_sorted, k, "right")
+        n_upd = hi - lo
+        # number of this key's updates with cid <= read_ts
+        le = np.searchsorted(self.code, (k << np.uint64(32)) | np.uint64(min(read_ts, 0xFFFFFFFF)), "right") - lo
+        le = np.clip(le, 0, n_upd)
+        stamp = np.where(le > 0, self.code[np.clip(lo + le - 1, 0, max(len(self.code) - 1, 0))] & np.uint64(0xFFFFFFFF), 0)
+        vis = (n_upd == 0) | (le > 0)
+        return vis, np.where(vis, stamp, 0).astype(np.uint32)
+
+
+def expected_payload_bytes(keys, stamp):
+    """(first byte, byte 150, last byte) of the row image: base = (uint8) key, column [100,200) = (uint8) stamp if updated."""
+    base = (np.asarray(keys, np.uint32) & 0xFF).astype(np.uint8)
+    col = np.where(stamp > 0, (stamp & 0xFF).astype(np.uint8), base)
+    return base, col, base
+
+
+def device_updates(snap, upd_keys):
+    d_keys = torch.from_numpy(u32_keys(upd_keys)).cuda()
+    cids = torch.arange(FIRST_CID, FIRST_CID + len(upd_keys), dtype=torch.int32, device="cuda")
+    patches = (cids & 0xFF).to(torch.uint8)[:, None].expand(len(upd_keys), 100).contiguous()
+    assert snap.apply_updates(d_keys, patches, cids, patch_off=100, device=True) == len(upd_keys)
+
+
+def check_against_model(snap, n_total, first, n_local, model, read_ts, n_scans, n_probes, seed):
+    """Scans and probes of rows [first, first+n_local) of an n_total-row table against the model."""
+    rng = np.random.default_rng(seed)
+    S = 1000
+    # ---- scans --------------------------------------------------------------------------------------------
+    pos = rng.integers(0, n_local, n_scans)
+    pos[:4] = [0, n_local - 1, n_local - S, max(n_local - S - 1, 0)]
+    sk = u32_keys(rank_to_key(n_total, first + pos))
+    counts, keys, ts, pay = snap.scan(sk, S, read_ts, 1)
+    again = snap.scan(sk, S, read_ts, 1)
+    for g, w in zip((counts, keys, ts, pay), again):
+        assert np.array_equal(g, w), "idempotence"
+    win = np.minimum(S, n_local - pos)
+    ranks = pos[:, None] + np.arange(S)[None, :]
+    inwin = np.arange(S)[None, :] < win[:, None]
+    wkeys = rank_to_key(n_total, first + np.where(inwin, ranks, 0))
+    vis, stamp = model.visible(wkeys.ravel(), read_ts)
+    vis = vis.reshape(wkeys.shape) & inwin
+    assert np.array_equal(counts, vis.sum(axis=1).astype(np.uint32)), "row counts"
+    got_k = keys.reshape(n_scans, S, 4).view(np.uint32).reshape(n_scans, S)
+    emitted = np.arange(S)[None, :] < counts[:, None]
+    assert np.array_equal(got_k[emitted], wkeys[vis]), "scan keys: order / contiguity / visibility"
+    assert np.array_equal(ts[emitted], stamp.reshape(wkeys.shape)[vis]), "scan stamps"
+    b0, b150, b999 = expected_payload_bytes(wkeys[vis], stamp.reshape(wkeys.shape)[vis])
+    rows = pay[emitted]
+    assert np.array_equal(rows[:, 0], b0) and np.array_equal(rows[:, 150], b150) and np.array_equal(rows[:, 999], b999)
+    assert (rows[:, 200:] == rows[:, 999:]).all() and (rows[:, 100:200] == rows[:, 150:151]).all(), "row images"
+    # ---- probes -------------------------------------------------------------------------------------------
+    pr = rng.integers(0, n_local + n_local // 20, n_probes)
+    exists = pr < n_local
+    pk = np.where(exists, rank_to_key(n_total, first + np.minimum(pr, n_local - 1)), np.uint32(n_total) + pr.astype(np.uint32))
+    found, pts, pkey, ppay = snap.probe(u32_keys(pk), read_ts)
+    vis, stamp = model.visible(pk, read_ts)
+    want_found = exists & vis
+    assert np.array_equal(found.astype(bool), want_found), "probe found"
+    assert np.array_equal(pts[want_found], stamp[want_found]), "probe stamps"
+    assert np.array_equal(pkey[want_found].view(np.uint32).ravel(), pk[want_found]), "probe keys"
+    b0, b150, b999 = expected_payload_bytes(pk[want_found], stamp[want_found])
+    rows = ppay[want_found]
+    assert np.array_equal(rows[:, 0], b0) and np.array_equal(rows[:, 150], b150) and np.array_equal(rows[:, 999], b999)
+
+
+def test_model_matches_checker():
+    """Pins the model: device-built table + device updates == model == CPU checker, at a size the checker handles."""
+    N = 60000
+    upd = (ycsb.uniform_keys(N, 9000, seed=2) - 1).astype(np.uint32)
+    t = pyoracle.OracleTable(1000)
+    assert t.load_ycsb_int(0, N) == N
+    assert t.commit_update_batch(u32_keys(upd), FIRST_CID) == len(upd)
+    model = UpdateModel(upd)
+    keys = np.random.default_rng(1).integers(0, N, 20000).astype(np.uint32)
+    with sg.Snapshot.generate_ycsb(N, 1000) as snap:
+        device_updates(snap, upd)
+        for read_ts in (0, 9, 10, 4000, 9009, 50000):
+            f, ts, _, pay = t.probe(u32_keys(keys), read_ts)
+            vis, stamp = model.visible(keys, read_ts)
+            assert np.array_equal(f.astype(bool), vis) and np.array_equal(ts[vis], stamp[vis])
+            b0, b150, _ = expected_payload_bytes(keys[vis], stamp[vis])
+            assert np.array_equal(pay[vis][:, 0], b0) and np.array_equal(pay[vis][:, 150], b150)
+            check_against_model(snap, N, 0, N, model, read_ts, 64, 20000, seed=read_ts)
+
+
+def test_config2_full_size_10m():
+    """BASELINE configs[1]: 10 M tuples, 1 M committed updates, 1000-row MVCC scans + 2^20 probes."""
+    N, U = 10_000_000, 1_000_000
+    upd = (ycsb.uniform_keys(N, U, seed=2) - 1).astype(np.uint32)
+    model = UpdateModel(upd)
+    with sg.Snapshot.generate_ycsb(N, 1000) as snap:
+        device_updates(snap, upd)
+        info = snap.info()
+        assert info.n_rows == N and info.n_versions == U
+        for read_ts in (0, FIRST_CID + U // 2, FIRST_CID + U):
+            check_against_model(snap, N, 0, N, model, read_ts, 512, 1 << 19, seed=read_ts)
+
+
+def test_config5_shard_125m():
+    """BASELINE configs[4]: one GPU's shard (rank 3 of 8) of the 1-billion-tuple table, 125 M rows + halo."""
+    free, _ = torch.cuda.mem_get_info()
+    if free < 150e9:
+        pytest.skip("needs ~145 GB of free HBM")
+    total, rows, rank = 1_000_000_000, 125_000_000, 3
+    first, n_local = rank * rows, rows + 2128
+    U = 2_000_000
+    upd = rank_to_key(total, first + np.random.default_rng(5).integers(0, rows, U)).astype(np.uint32)
+    model = UpdateModel(upd)
+    with sg.Snapshot.generate_ycsb(total, 1000, first_rank=first, n_local=n_local) as snap:
+        device_updates(snap, upd)
+        assert snap.info().n_rows == n_local
+        for read_ts in (FIRST_CID + U // 2, FIRST_CID + U):
+            check_against_model(snap, total, first, n_local, model, read_ts, 256, 1 << 18, seed=read_ts + 1)
+
+
+@pytest.mark.parametrize("n_rows", [2_000_000, 100_000_000])
+def test_config3_string_keys(n_rows):
+    """BASELINE configs[2]: YCSB string-key (-m) table, zipf 0.9 batched probes; 100 M tuples on one B200."""
+    free, _ = torch.cuda.mem_get_info()
+    if free < n_rows * 1100 + 8e9:
+        pytest.skip("not enough free HBM for this table size")
+    snap, keys, order = ycsb.build_string_table_device(n_rows)
+    try:
+        assert snap.info().n_rows == n_rows and snap.info().key_words == 4
+        # probes: ZipfDistribution(N-1, 0.9) indexing the key list by rowid (ycsb_mixed.cpp:289-309) + misses
+        z = ycsb.Zipf(n_rows - 1, 0.9, seed=1).draw(1 << 18).astype(np.int64)
+        z = np.clip(z, 1, n_rows)
+        hot = keys[torch.from_numpy(z - 1).cuda()].cpu().numpy()
+        miss = ycsb.random_strings(99, 4096)
+        probes = np.concatenate([hot, miss])
+        found, ts, kout, pay = snap.probe(probes, 1)
+        assert found[:len(hot)].all() and not found[len(hot):].any()
+        assert np.array_equal(kout[:len(hot)], hot) and not ts.any()
+        assert (pay[:len(hot)] == ord("a")).all()
+        # scans: S rows from the r-th key are rows r .. r+S-1 of the memcmp order
+        rng = np.random.default_rng(2)
+        S, n_scans = 1000, 128
+        pos = rng.integers(0, n_rows, n_scans)
+        pos[:3] = [0, n_rows - 1, n_rows - S]
+        start = keys[order[torch.from_numpy(pos).cuda()]].cpu().numpy()
+        counts, skeys, _, spay = snap.scan(start, S, 1, 1)
+        assert np.array_equal(counts, np.minimum(S, n_rows - pos).astype(np.uint32))
+        for i in range(n_scans):
+            want = keys[order[pos[i]:pos[i] + int(counts[i])]].cpu().numpy()
+            assert np.array_equal(skeys[i, :counts[i]], want), f"scan {i}"
+        assert (spay[np.arange(S)[None, :] < counts[:, None]] == ord("a")).all()
+        # a start key that is not in the table: the scan begins at its successor
+        nk = ycsb.random_strings(123, 16)
+        c2, k2, _, _ = snap.scan(nk, 5, 1, 0)
+        for i in range(16):
+            rows = k2[i, :c2[i]]
+            assert all(bytes(rows[j]) < bytes(rows[j + 1]) for j in range(len(rows) - 1))
+            assert c2[i] == 0 or bytes(rows[0]) >= bytes(nk[i])
+    finally:
+        snap.close()
+        del keys, order
+        torch.cuda.empty_cache()

@@ -1,0 +1,94 @@
+"""GPU: BASELINE configs[3] — TPC-C stock-level / CH-Q2* read pattern over the index-organized stock and order_line
+tables at w = 30 (STAGE_TEST_TPCC_W overrides), bit-exact against the CPU checker on the same host-built trees.
+
+Workload A (RunStockLevel, benchmark/tpcc/tpcc_stock_level.cpp:37-196): per transaction 20 MVCC scans of 10
+order_line rows from {w, d, o, 5}, then point probes of stock for the OL_I_IDs of the rows of that order.
+Workload B (CH-Q2*, benchmark/tpcc/tpcc_new_order.cpp:608-983): stock probes of one supplier's (w, i) pairs and
+MIN(S_QUANTITY) over them. Both tables use TPC-C's ParameterSet (64 KiB split threshold, tpcc.cpp:78); their keys
+are >= 16 bytes, i.e. memcmp-ordered raw little-endian integers."""
+import os
+
+import numpy as np
+import pytest
+
+import stage_indexorganized_b200 as sg
+from stage_indexorganized_b200 import tpcc
+from helpers import assert_probe_equal, assert_scan_equal
+from oracle import pyoracle
+
+pytestmark = pytest.mark.gpu
+W = int(os.environ.get("STAGE_TEST_TPCC_W", "30"))
+
+
+@pytest.fixture(scope="module")
+def tables():
+    sg.init(0)
+    sk, sp = tpcc.stock_rows(W)
+    stock = pyoracle.OracleTable(tpcc.STOCK_PAYLOAD, split_threshold=65536)
+    assert stock.insert(sk, sp, 0) == len(sk)
+    ok, op, _ = tpcc.order_line_rows(W)
+    ol = pyoracle.OracleTable(tpcc.OL_PAYLOAD, split_threshold=65536)
+    assert ol.insert(ok, op, 0) == len(ok)
+    # some committed updates of S_QUANTITY-bearing rows so that the MVCC branch is exercised too
+    rng = np.random.default_rng(4)
+    upd = sk[rng.integers(0, len(sk), 20000)]
+    assert stock.commit_update_batch(upd, 10) == 20000
+    s_snap = sg.Snapshot.from_tree(stock.root, tpcc.STOCK_KEY, tpcc.STOCK_PAYLOAD)
+    o_snap = sg.Snapshot.from_tree(ol.root, tpcc.OL_KEY, tpcc.OL_PAYLOAD)
+    yield stock, ol, s_snap, o_snap, len(sk), len(ok)
+    s_snap.close()
+    o_snap.close()
+
+
+def test_table_sizes(tables):
+    _, _, s_snap, o_snap, n_stock, n_ol = tables
+    assert s_snap.info().n_rows == n_stock == W * tpcc.ITEMS
+    assert o_snap.info().n_rows == n_ol
+    assert s_snap.info().key_words == 4 and o_snap.info().key_words == 8
+
+
+def test_stock_level_shape(tables):
+    stock, ol, s_snap, o_snap, _, _ = tables
+    start, w, d, o = tpcc.stock_level_requests(W, 2000)
+    for read_ts in (1, 5000):
+        got = o_snap.scan(start, 10, read_ts, 1)
+        want = ol.scan(start, 10, read_ts, 1)
+        assert_scan_equal(got, want, f"order_line scans ts={read_ts}")
+    counts, keys, _, pay = got
+    # the predicate of RunStockLevel keeps rows of the order asked for; their OL_I_IDs are probed in stock
+    k64 = keys.reshape(len(start), 10, 32).view(np.int64).reshape(len(start), 10, 4)
+    valid = np.arange(10)[None, :] < counts[:, None]
+    match = valid & (k64[..., 0] == w[:, None]) & (k64[..., 1] == d[:, None]) & (k64[..., 2] == o[:, None])
+    item = pay[..., 0:4].copy().view(np.int32).reshape(len(start), 10)
+    ww = np.broadcast_to(w[:, None], match.shape)[match]
+    probes = tpcc.stock_key(ww, item[match].astype(np.int64))
+    assert len(probes) > 1000
+    for read_ts in (1, 9, 10000, 30000):
+        assert_probe_equal(s_snap.probe(probes, read_ts), stock.probe(probes, read_ts), f"stock probes ts={read_ts}")
+    # the transaction's result: distinct items below the threshold — same rows, same answer
+    f, _, _, p = s_snap.probe(probes, 30000)
+    wf, _, _, wp = stock.probe(probes, 30000)
+    q, wq = p[:, 0:4].copy().view(np.int32).ravel(), wp[:, 0:4].copy().view(np.int32).ravel()
+    assert np.array_equal(np.unique(probes[(f == 1) & (q < 15)], axis=0), np.unique(probes[(wf == 1) & (wq < 15)], axis=0))
+
+
+def test_q2_shape(tables):
+    stock, _, s_snap, _, _, _ = tables
+    for supplier in (0, 77, 4242, 9999):
+        keys = tpcc.q2_supplier_keys(W, supplier)
+        assert len(keys) > 0
+        got, want = s_snap.probe(keys, 50000), stock.probe(keys, 50000)
+        assert_probe_equal(got, want, f"supplier {supplier}")
+        assert got[0].all()
+        q = got[3][:, 0:4].copy().view(np.int32).ravel()
+        wq = want[3][:, 0:4].copy().view(np.int32).ravel()
+        assert q.min() == wq.min()
+
+
+def test_stock_range_scans(tables):
+    stock, _, s_snap, _, n_stock, _ = tables
+    rng = np.random.default_rng(8)
+    start = tpcc.stock_key(rng.integers(1, W + 1, 300), rng.integers(0, tpcc.ITEMS + 2, 300))
+    for S in (10, 200):
+        for vis, ts in ((0, 0), (1, 1), (1, 15000)):
+            assert_scan_equal(s_snap.scan(start, S, ts, vis), stock.scan(start, S, ts, vis), f"S={S} vis={vis} ts={ts}")

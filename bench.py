@@ -376,10 +376,12 @@ def main():
         nprobe = args.steps * n_probes
         peak, peak_src = peaks()
         pbytes = hits * PROBE_HIT_BYTES + (nprobe - hits) * PROBE_MISS_BYTES
-        g_ach = hits * 2 * P_BYTES / (sum(pg) * 1e-3) / 1e9
+        fused = sum(pp) < 0.02 * sum(pg)          # one warp-specialised kernel does search + rows (probe_fused.cuh)
+        g_ach = (pbytes if fused else hits * 2 * P_BYTES) / (sum(pg) * 1e-3) / 1e9
         probe = {"value": nprobe / (pms * 1e-3), "unit": "probes/s", "ms_per_step": pms / args.steps,
                  "hit_rate": hits / nprobe, "plan_ms": sum(pp) / len(pp), "gather_ms": sum(pg) / len(pg),
-                 "roofline": {"bound": "hbm", "kernel": "stage::gather_rows_kernel", "achieved": g_ach, "peak": peak,
+                 "roofline": {"bound": "hbm", "kernel": "stage::probe_fused_kernel (search + MVCC + payload rows)" if fused
+                              else "stage::gather_rows_kernel", "achieved": g_ach, "peak": peak,
                               "unit": "GB/s", "frac": g_ach / peak, "traffic": None,
                               "step_achieved": pbytes / (pms * 1e-3) / 1e9,
                               "step_frac": pbytes / (pms * 1e-3) / 1e9 / peak}}

@@ -27,6 +27,7 @@
 #include "gather.cuh"
 #include "generate.cuh"
 #include "exchange.cuh"
+#include "probe_fused.cuh"
 #include "refresh.cuh"
 #include <cub/device/device_radix_sort.cuh>
 
@@ -941,10 +942,54 @@ static int launch_probe(stage_snapshot *s, const ProbeArgs &a) {
     return STAGE_OK;
 }
 
-// search + MVCC (probe_kernel) then payload gather; all pointers are device pointers
+template <int NW, typename V>
+static int launch_probe_fused_v(stage_snapshot *s, const ProbeArgs &a, uint8_t *payload_out) {
+    const size_t smem = (size_t) std::max<uint32_t>(s->view.smem_words, 4) * 4;
+    static int occ = 0;
+    if (!occ) {
+        int o = 0;
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, probe_fused_kernel<NW, V>, kFusedThreads, kProbeTopBytes));
+        occ = std::max(o, 1);
+    }
+    const uint64_t tiles = (a.n + kFusedTile - 1) / kFusedTile;
+    const unsigned blocks = (unsigned) std::min<uint64_t>(tiles, (uint64_t) sm_count() * occ);
+    probe_fused_kernel<NW, V><<<blocks, kFusedThreads, smem, s->stream>>>(s->view, a, payload_out);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+template <int NW>
+static int launch_probe_fused(stage_snapshot *s, const ProbeArgs &a, uint8_t *payload_out) {
+    const uintptr_t align = (uintptr_t) s->d_payload | (uintptr_t) s->d_ver_payload | (uintptr_t) payload_out |
+                            s->schema.payload_size;
+    if ((align & 15) == 0) return launch_probe_fused_v<NW, uint4>(s, a, payload_out);
+    if ((align & 7) == 0) return launch_probe_fused_v<NW, uint2>(s, a, payload_out);
+    if ((align & 3) == 0) return launch_probe_fused_v<NW, uint32_t>(s, a, payload_out);
+    return launch_probe_fused_v<NW, uint8_t>(s, a, payload_out);
+}
+
+// search + MVCC + payload rows. Default: probe_kernel then gather_rows_kernel (0.398 ms per 2^20 YCSB probes);
+// STAGE_PROBE_FUSED=1 selects the warp-specialised single kernel of probe_fused.cuh (measured 0.437 ms: under a
+// saturated memory system the producers' dependent loads are too slow to keep the consumers fed — profiles/README.md).
+// All pointers are device pointers.
 static int probe_device(stage_snapshot *s, ProbeArgs a, uint8_t *payload_out) {
     if (a.n == 0) return STAGE_OK;
     int rc;
+    static const bool fused = getenv("STAGE_PROBE_FUSED") && atoi(getenv("STAGE_PROBE_FUSED")) != 0;
+    if (fused && payload_out) {
+        if (s->timing) {
+            CUDA_TRY(cudaEventRecord(s->tev[0], s->stream));
+            CUDA_TRY(cudaEventRecord(s->tev[1], s->stream));
+        }
+        switch (s->nw) {
+            case 1: rc = launch_probe_fused<1>(s, a, payload_out); break;
+            case 2: rc = launch_probe_fused<2>(s, a, payload_out); break;
+            case 4: rc = launch_probe_fused<4>(s, a, payload_out); break;
+            default: rc = launch_probe_fused<8>(s, a, payload_out); break;
+        }
+        if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[2], s->stream));
+        s->timed_gather = true;
+        return rc;
+    }
     if (payload_out) {
         if ((rc = s->sc_srcrow.ensure(a.n * 4))) return rc;
         a.src_row = static_cast<uint32_t *>(s->sc_srcrow.p);

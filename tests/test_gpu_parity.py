@@ -141,3 +141,17 @@ def test_generated_ycsb_matches_row_function():
             assert np.array_equal(key_out[i, :counts[i]].view(np.uint32).ravel(), want)
             assert np.array_equal(pay[i, :counts[i], 0], (want & 0xFF).astype(np.uint8))
             assert np.array_equal(pay[i, :counts[i], 999], (want & 0xFF).astype(np.uint8))
+
+
+def test_fused_probe_kernel_variant():
+    """The opt-in warp-specialised probe kernel (csrc/probe_fused.cuh, STAGE_PROBE_FUSED=1) must be bit-identical to
+    the default two-kernel path: the probe tests of this file are re-run in a child process with the variant on."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("STAGE_PROBE_FUSED") == "1":
+        pytest.skip("already inside the variant run")
+    env = dict(os.environ, STAGE_PROBE_FUSED="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-m", "gpu", "-k",
+                        "probe or mvcc or other_key or generated"], env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]

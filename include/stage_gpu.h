@@ -178,6 +178,17 @@ int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys, const uint
                          uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts,
                          void *key_out, uint32_t *ts_out, void *payload_out, int flags);
 
+/* Operator push-down: the same probe / scan, but only payload bytes [col_off, col_off + col_len)
+ * of every row are returned — what the TPC-C callers of the path consume (S_QUANTITY against a threshold,
+ * benchmark/tpcc/tpcc_stock_level.cpp:167-176; MIN(S_QUANTITY), benchmark/tpcc/tpcc_new_order.cpp:808-866).
+ * col_out: n x col_len (probe) or n x out_stride x col_len (scan); entries without a row are zero.
+ * Row selection, order, found / ts / row_counts / key_out are exactly those of the full-row calls. */
+int stage_gpu_probe_project(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
+                            uint32_t *ts, uint32_t col_off, uint32_t col_len, void *col_out, int flags);
+int stage_gpu_scan_project(stage_snapshot_t *s, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
+                           uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts,
+                           void *key_out, uint32_t col_off, uint32_t col_len, void *col_out, int flags);
+
 /* Range partitioning across GPUs (one process per GPU): splitters = the largest key of every shard
  * but the last, in reference key order. owner[i] = shard that owns keys[i]. Host pointers. */
 int stage_gpu_route(const stage_schema_t *schema, const void *splitters, uint32_t n_shards, const void *keys,

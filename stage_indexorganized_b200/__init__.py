@@ -65,6 +65,8 @@ SYMBOLS = {
     "stage_gpu_snapshot_last_timing": (_i32, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "stage_gpu_probe_batch": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp, _vp, _vp, _i32]),
     "stage_gpu_scan_batch": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _vp, _vp, _i32]),
+    "stage_gpu_probe_project": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp, _u32, _u32, _vp, _i32]),
+    "stage_gpu_scan_project": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _u32, _u32, _vp, _i32]),
     "stage_gpu_route": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp]),
     "stage_gpu_route_device": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp, _vp]),
     "stage_gpu_exchange_create": (_i32, [_u32, _u32, _u64, C.POINTER(Schema), C.POINTER(_vp)]),
@@ -313,6 +315,35 @@ class Snapshot:
                                           int(apply_visibility), _ptr(counts), _ptr(key_out), _ptr(ts), _ptr(pay),
                                           IO_HOST))
         return counts, key_out, ts, pay
+
+    # -- reads with column push-down: only payload bytes [col_off, col_off + col_len) come back ----
+    def probe_column(self, keys, read_ts, col_off, col_len):
+        """-> (found u8[n], ts u32[n], col u8[n, col_len]); host arrays."""
+        keys = np.ascontiguousarray(keys, np.uint8)
+        n = keys.shape[0]
+        found, ts = np.zeros(n, np.uint8), np.zeros(n, np.uint32)
+        col = np.zeros((n, col_len), np.uint8)
+        _check(lib().stage_gpu_probe_project(self.h, _ptr(keys), n, read_ts, _ptr(found), _ptr(ts), col_off, col_len,
+                                             _ptr(col), IO_HOST))
+        return found, ts, col
+
+    def scan_column(self, start_keys, scan_sizes, read_ts, apply_visibility, col_off, col_len):
+        """-> (row_counts u32[n], key_out u8[n,S,K], col u8[n,S,col_len]); host arrays."""
+        start_keys = np.ascontiguousarray(start_keys, np.uint8)
+        n = start_keys.shape[0]
+        scan_sizes = np.ascontiguousarray(np.broadcast_to(np.asarray(scan_sizes, np.uint32), (n,)))
+        stride = int(scan_sizes.max()) if n else 0
+        counts = np.zeros(n, np.uint32)
+        key_out = np.zeros((n, stride, self.schema.key_size), np.uint8)
+        col = np.zeros((n, stride, col_len), np.uint8)
+        _check(lib().stage_gpu_scan_project(self.h, _ptr(start_keys), _ptr(scan_sizes), n, stride, read_ts,
+                                            int(apply_visibility), _ptr(counts), _ptr(key_out), col_off, col_len,
+                                            _ptr(col), IO_HOST))
+        return counts, key_out, col
+
+    def probe_column_device(self, keys, n, read_ts, col_off, col_len, col_out, found=None, ts=None):
+        _check(lib().stage_gpu_probe_project(self.h, _ptr(keys), n, read_ts, _ptr(found), _ptr(ts), col_off, col_len,
+                                             _ptr(col_out), IO_DEVICE))
 
     # -- reads: device buffers (torch tensors or raw device pointers) ---------------------------
     def probe_device(self, keys, n, read_ts, found=None, ts=None, key_out=None, payload_out=None):

@@ -74,3 +74,40 @@ __global__ void __launch_bounds__(kGatherThreads) gather_rows_kernel(GatherArgs 
 }
 
 }  // namespace stage
+
+// ---- column projection (operator push-down) -------------------------------------------------
+// The TPC-C callers of the path consume one small field of each row they read: RunStockLevel tests S_QUANTITY
+// against a threshold (benchmark/tpcc/tpcc_stock_level.cpp:167-176), CH-Q2* takes MIN(S_QUANTITY)
+// (benchmark/tpcc/tpcc_new_order.cpp:808-866). gather_cols_kernel moves only payload bytes
+// [col_off, col_off + col_len) of every source row: one 32-byte sector per row instead of the whole row, and
+// col_len instead of P bytes back to the caller — which lifts the PCIe / NVLink bound of the full-row form.
+// Rows without a source (kNoRow) get zero bytes. One thread per output slot.
+namespace stage {
+
+struct GatherColsArgs {
+    const uint32_t *src_row;
+    uint64_t n_slots;
+    const uint8_t *payload, *ver_payload;
+    uint8_t *dst;                // [n_slots][col_len]
+    uint32_t payload_size, col_off, col_len;
+};
+
+__global__ void __launch_bounds__(256) gather_cols_kernel(GatherColsArgs a) {
+    const uint64_t o = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (o >= a.n_slots) return;
+    const uint32_t row = __ldg(a.src_row + o);
+    uint8_t *d = a.dst + o * a.col_len;
+    if (row == kNoRow) {
+        for (uint32_t b = 0; b < a.col_len; ++b) d[b] = 0;
+        return;
+    }
+    const uint8_t *base = (row & kVersionRowFlag) ? a.ver_payload : a.payload;
+    const uint8_t *s = base + (uint64_t) (row & ~kVersionRowFlag) * a.payload_size + a.col_off;
+    if ((((uintptr_t) s | (uintptr_t) d | a.col_len) & 3u) == 0) {
+        for (uint32_t b = 0; b < a.col_len; b += 4) *reinterpret_cast<uint32_t *>(d + b) = __ldg(reinterpret_cast<const uint32_t *>(s + b));
+    } else {
+        for (uint32_t b = 0; b < a.col_len; ++b) d[b] = __ldg(s + b);
+    }
+}
+
+}  // namespace stage

@@ -1154,6 +1154,144 @@ extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys,
 }
 
 // ------------------------------------------------------------------------------------------------
+// column projection (push-down): plan kernels + gather_cols_kernel
+// ------------------------------------------------------------------------------------------------
+static int launch_gather_cols(stage_snapshot *s, const uint32_t *src_row, uint64_t n_slots, uint32_t col_off,
+                              uint32_t col_len, uint8_t *dst) {
+    if (n_slots == 0 || !dst) return STAGE_OK;
+    GatherColsArgs g{};
+    g.src_row = src_row; g.n_slots = n_slots; g.payload = s->d_payload; g.ver_payload = s->d_ver_payload; g.dst = dst;
+    g.payload_size = s->schema.payload_size; g.col_off = col_off; g.col_len = col_len;
+    gather_cols_kernel<<<(unsigned) ((n_slots + 255) / 256), 256, 0, s->stream>>>(g);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_probe_project(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
+                                       uint32_t *ts, uint32_t col_off, uint32_t col_len, void *col_out, int flags) {
+    if (!s || (n && (!keys || !col_out))) return STAGE_ERR_ARG;
+    if (!s->sealed) return STAGE_ERR_STATE;
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    if (col_len == 0 || (uint64_t) col_off + col_len > P) return STAGE_ERR_ARG;
+    if (n == 0) return STAGE_OK;
+    std::lock_guard<std::mutex> lock(s->mu);
+    CUDA_TRY(cudaSetDevice(s->device));
+    int rc;
+    const bool dev = flags & STAGE_IO_DEVICE;
+    const uint64_t chunk = dev ? n : std::min<uint64_t>(n, 1ull << 22);
+    if ((rc = s->sc_srcrow.ensure(chunk * 4))) return rc;
+    if (!dev) {
+        if ((rc = s->sc_keys.ensure(chunk * K)) || (rc = s->sc_payload.ensure(chunk * (uint64_t) col_len))) return rc;
+        if (found && (rc = s->sc_found.ensure(chunk))) return rc;
+        if (ts && (rc = s->sc_ts.ensure(chunk * 4))) return rc;
+    }
+    for (uint64_t b = 0; b < n; b += chunk) {
+        const uint64_t m = std::min(chunk, n - b);
+        ProbeArgs a{};
+        a.n = m;
+        a.read_ts = read_ts;
+        a.src_row = static_cast<uint32_t *>(s->sc_srcrow.p);
+        uint8_t *cdst;
+        if (dev) {
+            a.keys = static_cast<const uint8_t *>(keys);
+            a.found = found; a.ts_out = ts;
+            cdst = static_cast<uint8_t *>(col_out);
+        } else {
+            CUDA_TRY(cudaMemcpyAsync(s->sc_keys.p, static_cast<const uint8_t *>(keys) + b * K, m * K, cudaMemcpyHostToDevice, s->stream));
+            a.keys = static_cast<const uint8_t *>(s->sc_keys.p);
+            a.found = found ? static_cast<uint8_t *>(s->sc_found.p) : nullptr;
+            a.ts_out = ts ? static_cast<uint32_t *>(s->sc_ts.p) : nullptr;
+            cdst = static_cast<uint8_t *>(s->sc_payload.p);
+        }
+        switch (s->nw) {
+            case 1: rc = launch_probe<1>(s, a); break;
+            case 2: rc = launch_probe<2>(s, a); break;
+            case 4: rc = launch_probe<4>(s, a); break;
+            default: rc = launch_probe<8>(s, a); break;
+        }
+        if (rc) return rc;
+        if ((rc = launch_gather_cols(s, a.src_row, m, col_off, col_len, cdst))) return rc;
+        if (!dev) {
+            if (found) CUDA_TRY(cudaMemcpyAsync(found + b, s->sc_found.p, m, cudaMemcpyDeviceToHost, s->stream));
+            if (ts) CUDA_TRY(cudaMemcpyAsync(ts + b, s->sc_ts.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(col_out) + b * col_len, s->sc_payload.p, m * (uint64_t) col_len,
+                                     cudaMemcpyDeviceToHost, s->stream));
+            CUDA_TRY(cudaStreamSynchronize(s->stream));
+        }
+    }
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_scan_project(stage_snapshot_t *s, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
+                                      uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts,
+                                      void *key_out, uint32_t col_off, uint32_t col_len, void *col_out, int flags) {
+    if (!s || (n && (!start_keys || !scan_sizes || !row_counts || !col_out))) return STAGE_ERR_ARG;
+    if (!s->sealed) return STAGE_ERR_STATE;
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    if (col_len == 0 || (uint64_t) col_off + col_len > P) return STAGE_ERR_ARG;
+    if (n == 0) return STAGE_OK;
+    std::lock_guard<std::mutex> lock(s->mu);
+    CUDA_TRY(cudaSetDevice(s->device));
+    const bool dev = flags & STAGE_IO_DEVICE;
+    if (!dev)
+        for (uint64_t i = 0; i < n; ++i)
+            if (scan_sizes[i] > out_stride) return STAGE_ERR_ARG;
+    int rc;
+    const uint64_t chunk = dev ? n : std::min<uint64_t>(n, std::max<uint64_t>(1, (1ull << 26) / std::max<uint32_t>(out_stride, 1)));
+    if ((rc = s->sc_srcrow.ensure(chunk * out_stride * 4))) return rc;
+    if (!dev) {
+        if ((rc = s->sc_keys.ensure(chunk * K)) || (rc = s->sc_sizes.ensure(chunk * 4)) || (rc = s->sc_counts.ensure(chunk * 4)) ||
+            (rc = s->sc_payload.ensure(chunk * out_stride * (uint64_t) col_len)))
+            return rc;
+        if (key_out && (rc = s->sc_keyout.ensure(chunk * out_stride * K))) return rc;
+    }
+    for (uint64_t b = 0; b < n; b += chunk) {
+        const uint64_t m = std::min(chunk, n - b), rows = m * out_stride;
+        ScanArgs a{};
+        a.n = m;
+        a.out_stride = out_stride;
+        a.read_ts = read_ts;
+        a.apply_visibility = apply_visibility;
+        a.src_row = static_cast<uint32_t *>(s->sc_srcrow.p);
+        uint8_t *cdst;
+        if (dev) {
+            a.start_keys = static_cast<const uint8_t *>(start_keys);
+            a.scan_sizes = scan_sizes;
+            a.row_counts = row_counts;
+            a.key_out = static_cast<uint8_t *>(key_out);
+            cdst = static_cast<uint8_t *>(col_out);
+        } else {
+            CUDA_TRY(cudaMemcpyAsync(s->sc_keys.p, static_cast<const uint8_t *>(start_keys) + b * K, m * K, cudaMemcpyHostToDevice, s->stream));
+            CUDA_TRY(cudaMemcpyAsync(s->sc_sizes.p, scan_sizes + b, m * 4, cudaMemcpyHostToDevice, s->stream));
+            if (key_out) CUDA_TRY(cudaMemsetAsync(s->sc_keyout.p, 0, rows * K, s->stream));
+            a.start_keys = static_cast<const uint8_t *>(s->sc_keys.p);
+            a.scan_sizes = static_cast<const uint32_t *>(s->sc_sizes.p);
+            a.row_counts = static_cast<uint32_t *>(s->sc_counts.p);
+            a.key_out = key_out ? static_cast<uint8_t *>(s->sc_keyout.p) : nullptr;
+            cdst = static_cast<uint8_t *>(s->sc_payload.p);
+        }
+        switch (s->nw) {
+            case 1: rc = launch_scan<1>(s, a); break;
+            case 2: rc = launch_scan<2>(s, a); break;
+            case 4: rc = launch_scan<4>(s, a); break;
+            default: rc = launch_scan<8>(s, a); break;
+        }
+        if (rc) return rc;
+        if ((rc = launch_gather_cols(s, a.src_row, rows, col_off, col_len, cdst))) return rc;
+        if (!dev) {
+            CUDA_TRY(cudaMemcpyAsync(row_counts + b, s->sc_counts.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
+            if (key_out)
+                CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(key_out) + b * out_stride * K, s->sc_keyout.p, rows * K,
+                                         cudaMemcpyDeviceToHost, s->stream));
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(col_out) + b * out_stride * col_len, s->sc_payload.p,
+                                     rows * (uint64_t) col_len, cudaMemcpyDeviceToHost, s->stream));
+            CUDA_TRY(cudaStreamSynchronize(s->stream));
+        }
+    }
+    return STAGE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // routing (host): owner = number of splitters < key, in reference key order
 // ------------------------------------------------------------------------------------------------
 extern "C" int stage_gpu_route(const stage_schema_t *schema, const void *splitters, uint32_t n_shards, const void *keys,

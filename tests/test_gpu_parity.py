@@ -155,3 +155,20 @@ def test_fused_probe_kernel_variant():
     r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-m", "gpu", "-k",
                         "probe or mvcc or other_key or generated"], env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
+
+
+def test_column_pushdown_unaligned(ycsb10k):
+    """Projection of an unaligned byte range, including versions served from the staged chains."""
+    t, snap = ycsb10k
+    keys = u32_keys(pyoracle.uniform_keys(10000, 5000, seed=4))
+    f, ts, col = snap.probe_column(keys, 1, 3, 7)
+    wf, wts, _, wp = t.probe(keys, 1)
+    assert np.array_equal(f, wf) and np.array_equal(ts, wts)
+    assert np.array_equal(col[wf == 1], wp[wf == 1][:, 3:10]) and not col[wf == 0].any()
+    counts, kout, scol = snap.scan_column(keys[:40], 100, 1, 0, 996, 4)
+    wc, wk, _, wpay = t.scan(keys[:40], 100, 1, 0)
+    assert np.array_equal(counts, wc) and np.array_equal(kout, wk)
+    valid = np.arange(100)[None, :] < wc[:, None]
+    assert np.array_equal(scol[valid], wpay[valid][:, 996:1000])
+    with pytest.raises(sg.StageError):
+        snap.probe_column(keys, 1, 998, 4)

@@ -92,3 +92,23 @@ def test_stock_range_scans(tables):
     for S in (10, 200):
         for vis, ts in ((0, 0), (1, 1), (1, 15000)):
             assert_scan_equal(s_snap.scan(start, S, ts, vis), stock.scan(start, S, ts, vis), f"S={S} vis={vis} ts={ts}")
+
+
+def test_quantity_pushdown(tables):
+    """Column push-down (stage_gpu_probe_project / scan_project): S_QUANTITY only — same rows, same bytes."""
+    stock, ol, s_snap, o_snap, _, _ = tables
+    keys = np.concatenate([tpcc.q2_supplier_keys(W, 1234), tpcc.stock_key([W + 5, 0], [1, 1])])     # + two misses
+    for read_ts in (1, 50000):
+        f, ts, col = s_snap.probe_column(keys, read_ts, 0, 4)
+        wf, wts, _, wp = stock.probe(keys, read_ts)
+        assert np.array_equal(f, wf) and np.array_equal(ts, wts)
+        assert np.array_equal(col[wf == 1], wp[wf == 1][:, 0:4]) and not col[wf == 0].any()
+        q = col[f == 1].copy().view(np.int32).ravel()
+        assert q.min() == wp[wf == 1][:, 0:4].copy().view(np.int32).min()           # CH-Q2*: MIN(S_QUANTITY)
+    # stock-level: OL_I_ID (payload bytes 0..3) of the 10 order_line rows per scan
+    start, _, _, _ = tpcc.stock_level_requests(W, 500, seed=11)
+    counts, kout, col = o_snap.scan_column(start, 10, 1, 1, 0, 4)
+    wc, wk, _, wp = ol.scan(start, 10, 1, 1)
+    assert np.array_equal(counts, wc) and np.array_equal(kout, wk)
+    valid = np.arange(10)[None, :] < wc[:, None]
+    assert np.array_equal(col[valid], wp[valid][:, 0:4]) and not col[~valid].any()

@@ -142,7 +142,15 @@ int stage_gpu_snapshot_apply_updates(stage_snapshot_t *s, const void *keys, cons
                                      uint32_t patch_len, const uint32_t *commit_ids, uint64_t n, int flags,
                                      uint64_t *applied_out);
 
+/* Snapshot serialisation: dump / restore the flattened arrays (keys, slots, commit ids, chain
+ * heads, payload rows, leaf tables, version table) so that a table need not be re-flattened after a restart (the
+ * reference itself has no checkpointing, README.md:144-146). The search levels are rebuilt at load. The file is
+ * tied to this library's layout ("STGSNAP1"), little-endian. */
+int stage_gpu_snapshot_save(stage_snapshot_t *s, const char *path);
+int stage_gpu_snapshot_load(const char *path, stage_snapshot_t **out);
+
 int stage_gpu_snapshot_info(const stage_snapshot_t *s, stage_snapshot_info_t *info);
+int stage_gpu_snapshot_schema(const stage_snapshot_t *s, stage_schema_t *schema);
 int stage_gpu_snapshot_destroy(stage_snapshot_t *s);
 
 /* The CUDA stream (cudaStream_t) the snapshot launches on; set it to share a caller's stream. */

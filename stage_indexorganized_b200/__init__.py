@@ -57,7 +57,10 @@ SYMBOLS = {
                                                C.POINTER(_vp)]),
     "stage_gpu_snapshot_seal_sorted": (_i32, [_vp]),
     "stage_gpu_snapshot_apply_updates": (_i32, [_vp, _vp, _vp, _u32, _u32, _vp, _u64, _i32, C.POINTER(_u64)]),
+    "stage_gpu_snapshot_save": (_i32, [_vp, C.c_char_p]),
+    "stage_gpu_snapshot_load": (_i32, [C.c_char_p, C.POINTER(_vp)]),
     "stage_gpu_snapshot_info": (_i32, [_vp, C.POINTER(SnapshotInfo)]),
+    "stage_gpu_snapshot_schema": (_i32, [_vp, C.POINTER(Schema)]),
     "stage_gpu_snapshot_destroy": (_i32, [_vp]),
     "stage_gpu_snapshot_set_stream": (_i32, [_vp, _vp]),
     "stage_gpu_snapshot_get_stream": (_vp, [_vp]),
@@ -251,6 +254,17 @@ class Snapshot:
                                                       _ptr(commit_ids), n, IO_DEVICE if device else IO_HOST,
                                                       C.byref(applied)))
         return int(applied.value)
+
+    def save(self, path):
+        _check(lib().stage_gpu_snapshot_save(self.h, os.fsencode(path)))
+
+    @classmethod
+    def load(cls, path):
+        h = _vp()
+        _check(lib().stage_gpu_snapshot_load(os.fsencode(path), C.byref(h)))
+        sc = Schema(0, 0, 0, 0)
+        _check(lib().stage_gpu_snapshot_schema(h, C.byref(sc)))
+        return cls(h, sc)
 
     def info(self):
         i = SnapshotInfo()

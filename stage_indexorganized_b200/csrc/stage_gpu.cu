@@ -830,6 +830,98 @@ extern "C" int stage_gpu_snapshot_apply_updates(stage_snapshot_t *s, const void 
 }
 
 // ------------------------------------------------------------------------------------------------
+// snapshot serialisation: the flattened arrays, streamed through a pinned buffer
+// ------------------------------------------------------------------------------------------------
+struct SnapFileHeader {
+    char magic[8];                  // "STGSNAP1"
+    stage_schema_t schema;
+    uint32_t nw, xormask, max_leaf_rows, reserved;
+    uint64_t n_rows, n_leaves, n_versions;
+};
+
+static int stream_io(stage_snapshot *s, FILE *f, void *dev, size_t bytes, bool save, uint8_t *pinned, size_t chunk) {
+    uint8_t *d = static_cast<uint8_t *>(dev);
+    for (size_t off = 0; off < bytes; off += chunk) {
+        const size_t m = std::min(chunk, bytes - off);
+        if (save) {
+            CUDA_TRY(cudaMemcpyAsync(pinned, d + off, m, cudaMemcpyDeviceToHost, s->stream));
+            CUDA_TRY(cudaStreamSynchronize(s->stream));
+            if (fwrite(pinned, 1, m, f) != m) return STAGE_ERR_ARG;
+        } else {
+            if (fread(pinned, 1, m, f) != m) return STAGE_ERR_LAYOUT;
+            CUDA_TRY(cudaMemcpyAsync(d + off, pinned, m, cudaMemcpyHostToDevice, s->stream));
+            CUDA_TRY(cudaStreamSynchronize(s->stream));
+        }
+    }
+    return STAGE_OK;
+}
+
+static int snapshot_arrays_io(stage_snapshot *s, FILE *f, bool save) {
+    const size_t chunk = 64u << 20;
+    uint8_t *pinned = nullptr;
+    CUDA_TRY(cudaHostAlloc((void **) &pinned, chunk, cudaHostAllocDefault));
+    const uint64_t R = s->n_rows, L = s->n_leaves, V = s->n_versions, P = s->schema.payload_size, NW = s->nw;
+    struct { void *p; size_t bytes; } arr[] = {
+        {s->d_skey, R * NW * 4}, {s->d_slot, R * 2}, {s->d_ts, R * 4}, {s->d_chain, R * 4}, {s->d_payload, R * P},
+        {s->d_leaf_off, (L + 1) * 4}, {s->d_sep, L * NW * 4}, {s->d_cont, L},
+        {s->d_ver_begin, V * 4}, {s->d_ver_commit, V * 4}, {s->d_ver_next, V * 4}, {s->d_ver_payload, V * P}};
+    int rc = STAGE_OK;
+    for (auto &a : arr)
+        if (a.bytes && (rc = stream_io(s, f, a.p, a.bytes, save, pinned, chunk))) break;
+    cudaFreeHost(pinned);
+    return rc;
+}
+
+extern "C" int stage_gpu_snapshot_save(stage_snapshot_t *s, const char *path) {
+    if (!s || !path) return STAGE_ERR_ARG;
+    if (!s->sealed) return STAGE_ERR_STATE;
+    std::lock_guard<std::mutex> lock(s->mu);
+    CUDA_TRY(cudaSetDevice(s->device));
+    FILE *f = fopen(path, "wb");
+    if (!f) { g_last_error = std::string("cannot open ") + path; return STAGE_ERR_ARG; }
+    SnapFileHeader h{};
+    memcpy(h.magic, "STGSNAP1", 8);
+    h.schema = s->schema; h.nw = (uint32_t) s->nw; h.xormask = s->xormask; h.max_leaf_rows = s->max_leaf_rows;
+    h.n_rows = s->n_rows; h.n_leaves = s->n_leaves; h.n_versions = s->n_versions;
+    int rc = fwrite(&h, sizeof(h), 1, f) == 1 ? STAGE_OK : STAGE_ERR_ARG;
+    if (!rc) rc = snapshot_arrays_io(s, f, true);
+    if (fclose(f) != 0 && !rc) rc = STAGE_ERR_ARG;
+    return rc;
+}
+
+extern "C" int stage_gpu_snapshot_load(const char *path, stage_snapshot_t **out) {
+    if (!path || !out) return STAGE_ERR_ARG;
+    FILE *f = fopen(path, "rb");
+    if (!f) { g_last_error = std::string("cannot open ") + path; return STAGE_ERR_ARG; }
+    SnapFileHeader h{};
+    int nw;
+    uint32_t xm;
+    if (fread(&h, sizeof(h), 1, f) != 1 || memcmp(h.magic, "STGSNAP1", 8) != 0 || schema_check(&h.schema, &nw, &xm) ||
+        (uint32_t) nw != h.nw || xm != h.xormask || h.n_leaves == 0) {
+        fclose(f);
+        return STAGE_ERR_LAYOUT;
+    }
+    stage_snapshot *s = nullptr;
+    int rc = snapshot_new(&h.schema, &s);
+    if (rc) { fclose(f); return rc; }
+    auto fail = [&](int code) { fclose(f); snapshot_free(s); return code; };
+    if ((rc = alloc_columns(s, h.n_leaves, h.n_rows))) return fail(rc);
+    s->n_rows = h.n_rows; s->n_leaves = h.n_leaves; s->n_versions = h.n_versions; s->max_leaf_rows = h.max_leaf_rows;
+    if (h.n_versions) {
+        const uint64_t V = h.n_versions;
+        if ((rc = dev_alloc(s, &s->d_ver_begin, V)) || (rc = dev_alloc(s, &s->d_ver_commit, V)) ||
+            (rc = dev_alloc(s, &s->d_ver_next, V)) || (rc = dev_alloc(s, &s->d_ver_payload, V * (uint64_t) h.schema.payload_size)))
+            return fail(rc);
+        s->ver_cap = V;
+    }
+    if ((rc = snapshot_arrays_io(s, f, false))) return fail(rc);
+    if ((rc = finish_seal(s))) return fail(rc);
+    fclose(f);
+    *out = s;
+    return STAGE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // info / lifecycle
 // ------------------------------------------------------------------------------------------------
 extern "C" int stage_gpu_init(int device) {
@@ -851,6 +943,12 @@ extern "C" int stage_gpu_snapshot_info(const stage_snapshot_t *s, stage_snapshot
     info->n_levels = (uint32_t) s->view.n_levels;
     info->max_leaf_rows = s->max_leaf_rows;
     info->device = (uint32_t) s->device;
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_schema(const stage_snapshot_t *s, stage_schema_t *schema) {
+    if (!s || !schema) return STAGE_ERR_ARG;
+    *schema = s->schema;
     return STAGE_OK;
 }
 

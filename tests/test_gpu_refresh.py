@@ -106,3 +106,38 @@ def test_apply_updates_argument_errors():
         with pytest.raises(sg.StageError):
             snap.apply_updates(k, np.zeros((4, 8), np.uint8), np.arange(4, dtype=np.uint32), 60)    # runs past the row
         assert snap.apply_updates(k[:0], np.zeros((0, 8), np.uint8), np.zeros(0, np.uint32)) == 0
+
+
+def test_snapshot_save_load_roundtrip(tmp_path):
+    """stage_gpu_snapshot_save / load: a restored snapshot answers every read bit-identically (version chains,
+    string keys, a refreshed table), and can keep taking updates."""
+    N, P = 5000, 200
+    t = ycsb_int_table(pyoracle.OracleTable, N, P)
+    rng = np.random.default_rng(13)
+    assert t.commit_update_batch(u32_keys(rng.integers(0, N, 800)), 10) == 800
+    for k in rng.choice(N, 100, replace=False):
+        t.delete(u32_keys([k])[0])
+    path = str(tmp_path / "snap.bin")
+    probes = u32_keys(rng.integers(0, N + 10, 4000))
+    with sg.Snapshot.from_tree(t.root, 4, P) as snap:
+        snap.save(path)
+        want_info = snap.info()
+    with sg.Snapshot.load(path) as back:
+        i = back.info()
+        assert (i.n_rows, i.n_leaves, i.n_versions, i.max_leaf_rows) == (want_info.n_rows, want_info.n_leaves,
+                                                                        want_info.n_versions, want_info.max_leaf_rows)
+        assert back.schema.key_size == 4 and back.schema.payload_size == P
+        for read_ts in (0, 10, 400, 809, 5000):
+            assert_probe_equal(back.probe(probes, read_ts), t.probe(probes, read_ts), f"ts={read_ts}")
+            for vis in (0, 1):
+                assert_scan_equal(back.scan(probes[:64], 120, read_ts, vis), t.scan(probes[:64], 120, read_ts, vis), "scan")
+        k = rng.integers(0, N, 300).astype(np.uint32)
+        cids = np.arange(3000, 3300, dtype=np.uint32)
+        off, patches = ycsb_patch(P, cids)
+        present = t.commit_update_batch(u32_keys(k), 3000)
+        assert back.apply_updates(u32_keys(k), patches, cids, off) == present
+        assert_probe_equal(back.probe(probes, 3100), t.probe(probes, 3100), "after refresh of a loaded snapshot")
+    with open(path, "r+b") as f:
+        f.write(b"XXXXXXXX")
+    with pytest.raises(sg.StageError):
+        sg.Snapshot.load(path)

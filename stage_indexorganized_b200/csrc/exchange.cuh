@@ -160,6 +160,7 @@ struct ServeArgs {
     int device_sync;
     uint32_t *src_row;      // [world*cap] local scratch: row to gather per inbox entry (compact over sources)
     uint32_t *dst_slot;     // [world*cap] (requester << 28) | request index
+    int tile_order;         // 0: permuted (t * mul mod tiles); 1: all-to-all shift schedule (TilePlan)
 };
 
 // prefix offsets of the per-source inbox counts, into shared memory (ends with a barrier)
@@ -240,6 +241,61 @@ __device__ __forceinline__ uint32_t tile_multiplier(uint32_t tiles) {
     return 1u;
 }
 
+// Order 1 (all-to-all shift schedule): tiles never straddle two requesters; owner r walks the REMOTE requesters in
+// the rotated order r+1, r+2, ... (mod world), each requester's tiles in inbox order, with the tiles of its local
+// segment spread evenly in between. At any moment every requester's slab is then written by (about) one owner —
+// no incast on a single GPU's NVLink ingress — and the CTAs running together write a narrow window of that slab.
+struct TilePlan {
+    uint32_t tiles, mul, nloc, nrem_segs;
+    uint32_t rstart[kMaxExchangeRanks + 1];   // prefix of tile counts over the rotated remote segments
+    uint32_t rseg[kMaxExchangeRanks];
+};
+__device__ __forceinline__ void make_tile_plan(TilePlan *p, const uint32_t *off, uint32_t world, uint32_t rank, int order) {
+    if (threadIdx.x == 0) {
+        const uint32_t total = off[kMaxExchangeRanks];
+        if (order == 0) {
+            p->tiles = (total + kGatherRows - 1) / kGatherRows;
+            p->mul = tile_multiplier(p->tiles);
+        } else {
+            p->nloc = (off[rank + 1] - off[rank] + kGatherRows - 1) / kGatherRows;
+            uint32_t acc = 0, k = 0;
+            for (uint32_t d = 1; d < world; ++d) {
+                const uint32_t sgm = (rank + d) % world;
+                p->rseg[k] = sgm;
+                p->rstart[k] = acc;
+                acc += (off[sgm + 1] - off[sgm] + kGatherRows - 1) / kGatherRows;
+                ++k;
+            }
+            p->rstart[k] = acc;
+            p->nrem_segs = k;
+            p->tiles = p->nloc + acc;
+        }
+    }
+    __syncthreads();
+}
+// entries [*g0, *gend) of visit number t (at most kGatherRows of them are taken)
+__device__ __forceinline__ void tile_span(const TilePlan *p, const uint32_t *off, uint32_t rank, int order, uint32_t t,
+                                          uint32_t *g0, uint32_t *gend) {
+    if (order == 0) {
+        *g0 = (uint32_t) (((uint64_t) t * p->mul) % p->tiles) * kGatherRows;
+        *gend = off[kMaxExchangeRanks];
+        return;
+    }
+    const uint32_t L = p->nloc, T = p->tiles;
+    const uint32_t before = (uint32_t) (((uint64_t) t * L) / T), after = (uint32_t) (((uint64_t) (t + 1) * L) / T);
+    if (after > before) {
+        *g0 = off[rank] + before * kGatherRows;
+        *gend = off[rank + 1];
+        return;
+    }
+    const uint32_t r = t - before;
+    uint32_t k = 0;
+    while (k + 1 < p->nrem_segs && r >= p->rstart[k + 1]) ++k;
+    const uint32_t sgm = p->rseg[k];
+    *g0 = off[sgm] + (r - p->rstart[k]) * kGatherRows;
+    *gend = off[sgm + 1];
+}
+
 // Payload rows: local HBM -> the requesters' result slabs (peer stores over NVLink for remote requesters).
 // Persistent CTAs over tiles of kGatherRows inbox entries; same in-flight structure as gather_rows_kernel.
 template <typename V, int U>
@@ -252,15 +308,17 @@ __global__ void __launch_bounds__(kGatherThreads) exchange_gather_kernel(Exchang
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = kGatherThreads / 32;
     const uint32_t nvec = P / (uint32_t) sizeof(V);
-    const uint32_t tiles = (total + kGatherRows - 1) / kGatherRows;
-    const uint32_t mul = tile_multiplier(tiles);
+    __shared__ TilePlan plan;
+    make_tile_plan(&plan, off, x.world, x.rank, a.tile_order);
+    const uint32_t tiles = plan.tiles;
     for (uint32_t t = blockIdx.x; t < tiles; t += gridDim.x) {
-        const uint32_t g0 = (uint32_t) (((uint64_t) t * mul) % tiles) * kGatherRows;
+        uint32_t g0, gend;
+        tile_span(&plan, off, x.rank, a.tile_order, t, &g0, &gend);
         __syncthreads();
         if (tid < kGatherRows) {
             const uint32_t g = g0 + tid;
-            s_row[tid] = g < total ? a.src_row[g] : kNoRow;
-            s_dst[tid] = g < total ? a.dst_slot[g] : 0u;
+            s_row[tid] = g < gend ? a.src_row[g] : kNoRow;
+            s_dst[tid] = g < gend ? a.dst_slot[g] : 0u;
         }
         __syncthreads();
         for (int r0 = warp * U; r0 < kGatherRows; r0 += kWarps * U) {
@@ -305,15 +363,17 @@ __global__ void __launch_bounds__(kGatherThreads) exchange_gather16_kernel(Excha
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = kGatherThreads / 32;
     const uint32_t nfull = P / 16, tail8 = (P & 15u) >> 3;       // 16-byte chunks, then one optional 8-byte chunk
-    const uint32_t tiles = (total + kGatherRows - 1) / kGatherRows;
-    const uint32_t mul = tile_multiplier(tiles);
+    __shared__ TilePlan plan;
+    make_tile_plan(&plan, off, x.world, x.rank, a.tile_order);
+    const uint32_t tiles = plan.tiles;
     for (uint32_t t = blockIdx.x; t < tiles; t += gridDim.x) {
-        const uint32_t g0 = (uint32_t) (((uint64_t) t * mul) % tiles) * kGatherRows;
+        uint32_t g0, gend;
+        tile_span(&plan, off, x.rank, a.tile_order, t, &g0, &gend);
         __syncthreads();
         if (tid < kGatherRows) {
             const uint32_t g = g0 + tid;
-            s_row[tid] = g < total ? a.src_row[g] : kNoRow;
-            s_dst[tid] = g < total ? a.dst_slot[g] : 0u;
+            s_row[tid] = g < gend ? a.src_row[g] : kNoRow;
+            s_dst[tid] = g < gend ? a.dst_slot[g] : 0u;
         }
         __syncthreads();
         for (int r0 = warp * U; r0 < kGatherRows; r0 += kWarps * U) {

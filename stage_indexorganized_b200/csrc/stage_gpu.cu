@@ -1594,7 +1594,11 @@ extern "C" int stage_gpu_exchange_post(stage_exchange_t *x, const void *splitter
         host_sortable_nw(x->nw, static_cast<const uint8_t *>(splitters) + (size_t) i * x->schema.key_size,
                          x->schema.key_size, x->xormask, sp.w + (size_t) i * x->nw);
     if (n) {
-        const unsigned blocks = (unsigned) std::min<uint64_t>((n + 255) / 256, (uint64_t) sm_count() * 8);
+        // few CTAs on purpose: inbox slots are claimed tile by tile, so the fewer tiles are in flight at once, the
+        // closer the inbox order follows the request order (and the narrower the window of the requester's slab
+        // that the owner's concurrent CTAs write to)
+        static const int post_ctas = getenv("STAGE_XCHG_POST_CTAS") ? atoi(getenv("STAGE_XCHG_POST_CTAS")) : sm_count();
+        const unsigned blocks = (unsigned) std::min<uint64_t>((n + 255) / 256, post_ctas > 0 ? (uint64_t) post_ctas : (uint64_t) sm_count() * 8);
         const uint8_t *k = static_cast<const uint8_t *>(keys_dev);
         switch (x->nw) {
             case 1: exchange_post_kernel<1><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask); break;
@@ -1655,6 +1659,8 @@ extern "C" int stage_gpu_exchange_serve(stage_exchange_t *x, stage_snapshot_t *s
     a.device_sync = flags & STAGE_XCHG_DEVICE_SYNC ? 1 : 0;
     a.src_row = x->d_src_row;
     a.dst_slot = x->d_dst_slot;
+    static const int order = getenv("STAGE_XCHG_ORDER") ? atoi(getenv("STAGE_XCHG_ORDER")) : 1;   // shift schedule (exchange.cuh)
+    a.tile_order = order;
     int rc;
     switch (x->nw) {
         case 1: rc = launch_serve<1>(x, s, a, st); break;

@@ -13,7 +13,9 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <mutex>
+#include <thread>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -123,6 +125,7 @@ struct stage_snapshot {
     std::vector<uint8_t> h_has_sep;
     std::vector<stage_version_t> h_versions;
     std::vector<uint8_t> h_ver_payload;
+    uint8_t *ext_ver_payload = nullptr;         // malloc'd version rows handed over by from_tree (instead of h_ver_payload)
     uint8_t *h_stage[2] = {nullptr, nullptr};   // pinned
     uint8_t *d_stage[2] = {nullptr, nullptr};
     cudaEvent_t stage_ev[2] = {nullptr, nullptr};
@@ -199,6 +202,7 @@ static void snapshot_free(stage_snapshot *s) {
                     s->d_err, s->d_stage[0], s->d_stage[1], s->d_raw_keys};
     for (void *p : ptrs)
         if (p) cudaFree(p);
+    free(s->ext_ver_payload);
     for (int i = 0; i < 2; ++i) {
         if (s->h_stage[i]) cudaFreeHost(s->h_stage[i]);
         if (s->stage_ev[i]) cudaEventDestroy(s->stage_ev[i]);
@@ -358,18 +362,17 @@ static int flush_chunk(stage_snapshot *s) {
     return STAGE_OK;
 }
 
-// stage one leaf image: copy to pinned memory, count visible records, patch chain heads
-static int stage_one_leaf(stage_snapshot *s, const uint8_t *leaf, const uint8_t *fence, bool has_fence,
-                          const uint32_t *chain_heads) {
+// Copy one leaf image into its pinned staging slot, count its visible records and replace the host TupleHeader
+// pointers in RecordMetadata.next_ptr by version indices. Thread-safe: touches only `dst`.
+static int stage_copy_leaf(const stage_snapshot *s, uint8_t *dst, const uint8_t *leaf, const uint32_t *chain_heads,
+                           uint32_t *vis_out, uint32_t *count_out) {
     const uint32_t ls = s->schema.leaf_node_size;
-    if (s->n_leaves >= s->cap_leaves) return STAGE_ERR_ARG;
     if (!leaf[kOffIsLeaf]) return STAGE_ERR_LAYOUT;
     uint64_t status;
     memcpy(&status, leaf + kOffStatus, 8);
     if (status & kStatusFrozen) return STAGE_ERR_NOT_QUIESCED;
     const uint32_t count = status_record_count(status);
     if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize > ls) return STAGE_ERR_LAYOUT;
-    uint8_t *dst = s->h_stage[s->stage_cur] + (size_t) s->stage_fill * ls;
     memcpy(dst, leaf, ls);
     uint32_t vis = 0;
     for (uint32_t i = 0; i < count; ++i) {
@@ -385,17 +388,71 @@ static int stage_one_leaf(stage_snapshot *s, const uint8_t *leaf, const uint8_t 
         }
         memcpy(mp + kMetaNextPtr, &head, 8);   // pointer translation: host TupleHeader* -> version index
     }
-    if (s->rows_staged + vis > s->cap_rows) return STAGE_ERR_ARG;
-    s->rows_staged += vis;
-    s->h_leaf_off.push_back((uint32_t) s->rows_staged);
-    s->h_sep.resize((s->n_leaves + 1) * s->nw, 0xFFFFFFFFu);
-    if (has_fence) host_sortable_nw(s->nw, fence, s->schema.key_size, s->xormask, s->h_sep.data() + s->n_leaves * s->nw);
-    s->h_has_sep.push_back(has_fence ? 1 : 0);
-    s->n_leaves++;
-    s->stage_fill++;
-    s->stage_maxcount = std::max(s->stage_maxcount, count);
-    s->max_leaf_rows = std::max(s->max_leaf_rows, vis);
-    if (s->stage_fill == s->chunk_leaves) return flush_chunk(s);
+    *vis_out = vis;
+    *count_out = count;
+    return STAGE_OK;
+}
+
+static unsigned staging_threads() {
+    static const unsigned n = [] {
+        if (const char *e = getenv("STAGE_STAGING_THREADS")) return (unsigned) std::max(1, atoi(e));
+        return std::min(8u, std::max(1u, std::thread::hardware_concurrency()));
+    }();
+    return n;
+}
+
+// Stage n leaves (tree order). The 64 KiB image copies — the bulk of the host work — run on a few threads, one
+// staging chunk at a time; bookkeeping (row offsets, fences) and the chunk flush stay on the calling thread.
+// get(i, &leaf, &fence, &heads) supplies leaf i.
+template <class Get>
+static int stage_leaves(stage_snapshot *s, uint64_t n, Get get) {
+    const uint32_t ls = s->schema.leaf_node_size;
+    std::vector<uint32_t> vis, cnt;
+    std::vector<int> rcs;
+    for (uint64_t base = 0; base < n;) {
+        const uint32_t room = s->chunk_leaves - s->stage_fill;
+        const uint32_t m = (uint32_t) std::min<uint64_t>(room, n - base);
+        if (s->n_leaves + m > s->cap_leaves) return STAGE_ERR_ARG;
+        vis.assign(m, 0); cnt.assign(m, 0); rcs.assign(m, 0);
+        uint8_t *slot0 = s->h_stage[s->stage_cur] + (size_t) s->stage_fill * ls;
+        auto work = [&](uint32_t lo, uint32_t hi) {
+            for (uint32_t j = lo; j < hi; ++j) {
+                const uint8_t *leaf, *fence;
+                const uint32_t *heads;
+                get(base + j, &leaf, &fence, &heads);
+                rcs[j] = stage_copy_leaf(s, slot0 + (size_t) j * ls, leaf, heads, &vis[j], &cnt[j]);
+            }
+        };
+        const unsigned T = std::min<unsigned>(staging_threads(), std::max(1u, m / 16));
+        if (T <= 1) work(0, m);
+        else {
+            std::vector<std::thread> th;
+            for (unsigned t = 1; t < T; ++t) th.emplace_back(work, (uint32_t) ((uint64_t) m * t / T), (uint32_t) ((uint64_t) m * (t + 1) / T));
+            work(0, (uint32_t) ((uint64_t) m / T));
+            for (auto &x : th) x.join();
+        }
+        for (uint32_t j = 0; j < m; ++j) {
+            if (rcs[j]) return rcs[j];
+            const uint8_t *leaf, *fence;
+            const uint32_t *heads;
+            get(base + j, &leaf, &fence, &heads);
+            if (s->rows_staged + vis[j] > s->cap_rows) return STAGE_ERR_ARG;
+            s->rows_staged += vis[j];
+            s->h_leaf_off.push_back((uint32_t) s->rows_staged);
+            s->h_sep.resize((s->n_leaves + 1) * s->nw, 0xFFFFFFFFu);
+            if (fence) host_sortable_nw(s->nw, fence, s->schema.key_size, s->xormask, s->h_sep.data() + s->n_leaves * s->nw);
+            s->h_has_sep.push_back(fence ? 1 : 0);
+            s->n_leaves++;
+            s->stage_fill++;
+            s->stage_maxcount = std::max(s->stage_maxcount, cnt[j]);
+            s->max_leaf_rows = std::max(s->max_leaf_rows, vis[j]);
+        }
+        base += m;
+        if (s->stage_fill == s->chunk_leaves) {
+            int rc = flush_chunk(s);
+            if (rc) return rc;
+        }
+    }
     return STAGE_OK;
 }
 
@@ -405,13 +462,13 @@ extern "C" int stage_gpu_snapshot_add_leaves(stage_snapshot_t *s, const void *co
     if (!s || s->sealed || (n && !leaf_images)) return STAGE_ERR_ARG;
     CUDA_TRY(cudaSetDevice(s->device));
     const uint8_t *f = static_cast<const uint8_t *>(upper_fences);
-    for (uint64_t i = 0; i < n; ++i) {
-        bool hf = f && (!has_upper_fence || has_upper_fence[i]);
-        int rc = stage_one_leaf(s, static_cast<const uint8_t *>(leaf_images[i]),
-                                hf ? f + i * s->schema.key_size : nullptr, hf, chain_heads ? chain_heads[i] : nullptr);
-        if (rc) return rc;
-    }
-    return STAGE_OK;
+    const uint32_t K = s->schema.key_size;
+    return stage_leaves(s, n, [&](uint64_t i, const uint8_t **leaf, const uint8_t **fence, const uint32_t **heads) {
+        *leaf = static_cast<const uint8_t *>(leaf_images[i]);
+        const bool hf = f && (!has_upper_fence || has_upper_fence[i]);
+        *fence = hf ? f + i * K : nullptr;
+        *heads = chain_heads ? chain_heads[i] : nullptr;
+    });
 }
 
 template <int NW>
@@ -495,8 +552,8 @@ extern "C" int stage_gpu_snapshot_seal(stage_snapshot_t *s) {
         CUDA_TRY(cudaMemcpyAsync(s->d_ver_begin, b.data(), V * 4, cudaMemcpyHostToDevice, s->stream));
         CUDA_TRY(cudaMemcpyAsync(s->d_ver_commit, c.data(), V * 4, cudaMemcpyHostToDevice, s->stream));
         CUDA_TRY(cudaMemcpyAsync(s->d_ver_next, nx.data(), V * 4, cudaMemcpyHostToDevice, s->stream));
-        CUDA_TRY(cudaMemcpyAsync(s->d_ver_payload, s->h_ver_payload.data(), s->h_ver_payload.size(),
-                                 cudaMemcpyHostToDevice, s->stream));
+        CUDA_TRY(cudaMemcpyAsync(s->d_ver_payload, s->ext_ver_payload ? s->ext_ver_payload : s->h_ver_payload.data(),
+                                 V * (uint64_t) s->schema.payload_size, cudaMemcpyHostToDevice, s->stream));
         CUDA_TRY(cudaStreamSynchronize(s->stream));
     }
     rc = finish_seal(s);
@@ -507,6 +564,8 @@ extern "C" int stage_gpu_snapshot_seal(stage_snapshot_t *s) {
     }
     std::vector<uint8_t>().swap(s->h_ver_payload);
     std::vector<stage_version_t>().swap(s->h_versions);
+    free(s->ext_ver_payload);
+    s->ext_ver_payload = nullptr;
     return rc;
 }
 
@@ -548,8 +607,15 @@ static int walk(const uint8_t *node, uint32_t key_size, WalkOut &w, int depth) {
     return STAGE_OK;
 }
 
+static double now_s() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema_t *schema, stage_snapshot_t **out) {
     if (!root || !out) return STAGE_ERR_ARG;
+    static const bool dbg = getenv("STAGE_DEBUG_TIMING") != nullptr;
+    double t0 = now_s(), t1;
+#define PHASE(name) do { if (dbg) { t1 = now_s(); fprintf(stderr, "[from_tree] %-22s %.3f s\n", name, t1 - t0); t0 = t1; } } while (0)
     WalkOut w;
     int nw;
     uint32_t xm;
@@ -557,15 +623,17 @@ extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema
     if (rc) return rc;
     if ((rc = walk(static_cast<const uint8_t *>(root), schema->key_size, w, 0))) return rc;
 
+    PHASE("walk");
     stage_snapshot *s = nullptr;
     if ((rc = stage_gpu_snapshot_begin(schema, w.leaves.size(), w.rows_upper, &s))) return rc;
+    PHASE("alloc");
 
     // version chains: RecordMetadata.next_ptr -> TupleHeader (version_store.h:28-46), slot = [key][payload]
     const uint32_t K = schema->key_size, P = schema->payload_size;
     std::unordered_map<uint64_t, uint32_t> seen;   // TupleHeader* -> 1-based version index
     std::vector<uint32_t> heads;
     std::vector<stage_version_t> vers;
-    std::vector<uint8_t> vpay;
+    std::vector<uint64_t> vslot;                       // TupleHeader.tuple_slot_ of every staged version
     std::vector<uint64_t> path;
     auto add_chain = [&](uint64_t head) -> uint32_t {
         path.clear();
@@ -587,17 +655,19 @@ extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema
             memcpy(&slot, hd + kThSlot, 8);
             ver.next = k + 1 < path.size() ? first + (uint32_t) k + 1 : tail;
             vers.push_back(ver);
-            const size_t at = vpay.size();
-            vpay.resize(at + P, 0);
-            if (slot != 0 && slot != UINT64_MAX) memcpy(vpay.data() + at, reinterpret_cast<const uint8_t *>(slot) + K, P);
+            vslot.push_back(slot);
         }
         return path.empty() ? tail : first;
     };
-    for (size_t li = 0; li < w.leaves.size() && !rc; ++li) {
+    // pass 1 (serial, metadata only): version indices in leaf / slot order
+    std::vector<uint32_t> heads_flat;                 // chain heads of the leaves that have any
+    std::vector<int64_t> heads_at(w.leaves.size(), -1);
+    for (size_t li = 0; li < w.leaves.size(); ++li) {
         const uint8_t *leaf = w.leaves[li];
         uint64_t status;
         memcpy(&status, leaf + kOffStatus, 8);
         const uint32_t count = status_record_count(status);
+        if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize > schema->leaf_node_size) { rc = STAGE_ERR_LAYOUT; break; }
         heads.assign(count, 0);
         bool any = false;
         for (uint32_t i = 0; i < count; ++i) {
@@ -608,10 +678,45 @@ extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema
             heads[i] = add_chain(nx);
             any = true;
         }
-        rc = stage_one_leaf(s, leaf, w.fences[li], w.fences[li] != nullptr, any ? heads.data() : nullptr);
+        if (any) {
+            heads_at[li] = (int64_t) heads_flat.size();
+            heads_flat.insert(heads_flat.end(), heads.begin(), heads.end());
+        }
     }
-    if (!rc && !vers.empty()) rc = stage_gpu_snapshot_add_versions(s, vers.data(), vpay.data(), vers.size());
+    PHASE("chain discovery");
+    // pass 2: leaf images, copied by the staging threads
+    if (!rc)
+        rc = stage_leaves(s, w.leaves.size(), [&](uint64_t li, const uint8_t **leaf, const uint8_t **fence, const uint32_t **hd) {
+            *leaf = w.leaves[li];
+            *fence = w.fences[li];
+            *hd = heads_at[li] >= 0 ? heads_flat.data() + heads_at[li] : nullptr;
+        });
+    PHASE("stage + transform");
+    if (!rc && !vers.empty()) {
+        // retired rows [key][payload] -> dense version rows, copied by the staging threads
+        const size_t V = vers.size();
+        uint8_t *vbuf = static_cast<uint8_t *>(malloc(V * (size_t) P));
+        if (!vbuf) rc = STAGE_ERR_NOMEM;
+        else {
+            auto work = [&](size_t lo, size_t hi) {
+                for (size_t i = lo; i < hi; ++i) {
+                    if (vslot[i] != 0 && vslot[i] != UINT64_MAX) memcpy(vbuf + i * P, reinterpret_cast<const uint8_t *>(vslot[i]) + K, P);
+                    else memset(vbuf + i * P, 0, P);
+                }
+            };
+            const unsigned T = V > 4096 ? staging_threads() : 1;
+            std::vector<std::thread> th;
+            for (unsigned t = 1; t < T; ++t) th.emplace_back(work, V * t / T, V * (t + 1) / T);
+            work(0, V / T);
+            for (auto &x : th) x.join();
+            s->h_versions = std::move(vers);
+            s->ext_ver_payload = vbuf;
+        }
+    }
+    PHASE("version rows");
     if (!rc) rc = stage_gpu_snapshot_seal(s);
+    PHASE("seal");
+#undef PHASE
     if (rc) {
         snapshot_free(s);
         return rc;

@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
     __shared__ __align__(16) uint32_t s_chain[kScanTile + 8];
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ uint32_t s_warp[kScanThreads / 32];
-    __shared__ uint32_t s_leaf, s_min;
+    __shared__ uint32_t s_min;
     extern __shared__ __align__(16) uint16_t s_slots[];          // [max_leaf_rows] for the slot-rank rule
 
     const int tid = threadIdx.x;
@@ -129,17 +129,20 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
 
         if (S > 0 && L > 0) {
             // ---- start leaf: number of upper fences < begin (fences of leaves 0..L-2) ------------------
-            if (tid == 0) {
-                uint32_t lo = 0, hi = L - 1;
-                while (lo < hi) {
-                    const uint32_t mid = (lo + hi) >> 1;
-                    if (skey_less<NW>(load_skey<NW>(v.sep, mid), begin)) lo = mid + 1; else hi = mid;
-                }
-                s_leaf = lo;
-                s_min = 0xFFFFFFFFu;
+            // CTA-wide k-ary search: every round the 256 threads test 256 evenly spaced fences of the remaining
+            // range at once (3 dependent loads for 16 M leaves instead of 24 for a binary search by one thread).
+            uint32_t j0 = 0;
+            for (uint32_t n = L - 1; n > 0;) {
+                const uint32_t step = (n + kScanThreads - 1) / kScanThreads;
+                const uint64_t idx = (uint64_t) j0 + (uint64_t) (tid + 1) * step - 1;
+                const bool lt = idx < (uint64_t) j0 + n && skey_less<NW>(load_skey<NW>(v.sep, idx), begin);
+                const uint32_t cnt = __syncthreads_count(lt);
+                const uint32_t adv = cnt * step;                 // fences j0 .. j0+adv-1 are all < begin
+                n = min(step - 1, n - min(n, adv));
+                j0 += adv;
             }
+            if (tid == 0) s_min = 0xFFFFFFFFu;
             __syncthreads();
-            const uint32_t j0 = s_leaf;
             const uint32_t lo0 = v.leaf_off[j0], hi0 = v.leaf_off[j0 + 1];
             uint32_t below = 0;                                   // rows of the start leaf with key < begin
             for (uint32_t base = 0; base < hi0 - lo0; base += kScanThreads) {

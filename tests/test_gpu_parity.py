@@ -172,3 +172,74 @@ def test_column_pushdown_unaligned(ycsb10k):
     assert np.array_equal(scol[valid], wpay[valid][:, 996:1000])
     with pytest.raises(sg.StageError):
         snap.probe_column(keys, 1, 998, 4)
+
+
+@pytest.mark.parametrize("cls", checker_classes(), ids=lambda c: c.__name__)
+def test_empty_and_tiny_tables(cls):
+    """A tree with no rows (the root is an empty leaf), one row, and a tree emptied again by deletes."""
+    P = 64
+    probes = u32_keys(np.array([0, 1, 2, 77, 0xFFFFFFFF], np.uint32))
+    t = cls(P)
+    with sg.Snapshot.from_tree(t.root, 4, P) as snap:
+        assert snap.info().n_rows == 0
+        assert_probe_equal(snap.probe(probes, 5), t.probe(probes, 5), "empty probe")
+        assert_scan_equal(snap.scan(probes, 10, 5, 1), t.scan(probes, 10, 5, 1), "empty scan")
+    assert t.insert(u32_keys([77]), np.full((1, P), 9, np.uint8), 0) == 1
+    with sg.Snapshot.from_tree(t.root, 4, P) as snap:
+        assert snap.info().n_rows == 1
+        assert_probe_equal(snap.probe(probes, 5), t.probe(probes, 5), "one-row probe")
+        for vis in (0, 1):
+            assert_scan_equal(snap.scan(probes, 3, 5, vis), t.scan(probes, 3, 5, vis), "one-row scan")
+    t.delete(u32_keys([77])[0])
+    with sg.Snapshot.from_tree(t.root, 4, P) as snap:
+        assert snap.info().n_rows == 0
+        assert_probe_equal(snap.probe(probes, 5), t.probe(probes, 5), "deleted probe")
+        assert_scan_equal(snap.scan(probes, 3, 5, 0), t.scan(probes, 3, 5, 0), "deleted scan")
+
+
+@pytest.mark.parametrize("key_size,payload,leaf", [(32, 3000, 65536), (4, 8, 4096), (16, 1, 65536), (12, 20, 8192)])
+def test_extreme_shapes(key_size, payload, leaf):
+    """Large rows (few per leaf), tiny rows (hundreds per leaf: the slot-order truncation rule bites), small leaves,
+    a 12-byte key (signed-byte order, three key words)."""
+    cls = pyoracle.OracleTable
+    rng = np.random.default_rng(key_size * 7 + payload)
+    keys = np.unique(rng.integers(0, 256, size=(4000, key_size), dtype=np.uint8), axis=0)
+    rng.shuffle(keys)
+    pay = rng.integers(0, 256, size=(len(keys), payload), dtype=np.uint8)
+    t = cls(payload, split_threshold=min(16384, leaf // 2), leaf_node_size=leaf)
+    assert t.insert(keys, pay, 0) == len(keys)
+    for k in keys[rng.choice(len(keys), 200, replace=False)]:
+        t.delete(k)
+    with sg.Snapshot.from_tree(t.root, key_size, payload, leaf) as snap:
+        probe = np.concatenate([keys[:1500], rng.integers(0, 256, size=(200, key_size), dtype=np.uint8)])
+        assert_probe_equal(snap.probe(probe, 1), t.probe(probe, 1), "probe")
+        for S in (1, 7, 64, 500):
+            for vis in (0, 1):
+                assert_scan_equal(snap.scan(probe[:150], S, 1, vis), t.scan(probe[:150], S, 1, vis), f"S={S} vis={vis}")
+
+
+def test_concurrent_callers(ycsb10k):
+    """SURVEY §8b threading: several worker threads (the drivers pin N of them, ycsb_workload.cpp:522-529) call the
+    batch entry points on ONE snapshot at the same time; every caller must get exactly its own results."""
+    import threading
+    t, snap = ycsb10k
+    n_threads, rounds = 8, 6
+    keys = [u32_keys(pyoracle.uniform_keys(10000, 3000 + 37 * i, seed=50 + i)) for i in range(n_threads)]
+    want_p = [t.probe(k, 1) for k in keys]
+    want_s = [t.scan(k[:24], 50, 1, 1) for k in keys]
+    errors = []
+
+    def worker(i):
+        try:
+            for _ in range(rounds):
+                assert_probe_equal(snap.probe(keys[i], 1), want_p[i], f"thread {i} probe")
+                assert_scan_equal(snap.scan(keys[i][:24], 50, 1, 1), want_s[i], f"thread {i} scan")
+        except Exception as e:          # noqa: BLE001 - reported to the main thread
+            errors.append(repr(e))
+
+    th = [threading.Thread(target=worker, args=(i,)) for i in range(n_threads)]
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    assert not errors, errors[:3]

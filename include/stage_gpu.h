@@ -197,6 +197,14 @@ int stage_gpu_scan_project(stage_snapshot_t *s, const void *start_keys, const ui
                            uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts,
                            void *key_out, uint32_t col_off, uint32_t col_len, void *col_out, int flags);
 
+/* TableScanExecutor with scan_sz == -1 (include/execute/executor.h:581-619): the PHYSICAL whole-tree walk — leaves in
+ * tree order, record slots in slot (insertion) order, no visibility test. Returns rows [first_row, first_row + n) of
+ * that order (n_rows of stage_gpu_snapshot_info in total): latest in-leaf versions, keys, commit ids, payload rows.
+ * Slots that are invisible / deleted in the tree (the reference copies their stale bytes too) are not part of a
+ * snapshot and are skipped. Any output pointer may be NULL. */
+int stage_gpu_scan_physical(stage_snapshot_t *s, uint64_t first_row, uint64_t n, void *key_out, uint32_t *ts_out,
+                            void *payload_out, int flags);
+
 /* Range partitioning across GPUs (one process per GPU): splitters = the largest key of every shard
  * but the last, in reference key order. owner[i] = shard that owns keys[i]. Host pointers. */
 int stage_gpu_route(const stage_schema_t *schema, const void *splitters, uint32_t n_shards, const void *keys,

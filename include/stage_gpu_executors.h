@@ -216,9 +216,25 @@ public:
         : table_(data_table), start_key_(start_key), key_sz_(key_size), scan_sz_(scan_size), txn_(txn) {}
 
     bool Execute() {
-        if (scan_sz_ == (uint32_t) -1)
-            throw std::runtime_error("physical whole-tree scan (scan_sz == -1) is not on this path (SURVEY §8f f3)");
         const uint32_t K = table_->schema().key_size, P = table_->schema().payload_size, pad = Record::padded(K);
+        if (scan_sz_ == (uint32_t) -1) {          // physical whole-tree walk (executor.h:581-619)
+            stage_snapshot_info_t info{};
+            check(stage_gpu_snapshot_info(table_->handle(), &info), "stage_gpu_snapshot_info");
+            const uint64_t n = info.n_rows;
+            std::vector<char> keys((size_t) n * K), pays((size_t) n * P);
+            check(stage_gpu_scan_physical(table_->handle(), 0, n, keys.data(), nullptr, pays.data(), STAGE_IO_HOST),
+                  "stage_gpu_scan_physical");
+            results_.resize(n);
+            std::vector<char> img(pad + P);
+            for (uint64_t i = 0; i < n; ++i) {
+                std::fill(img.begin(), img.end(), 0);
+                std::memcpy(img.data(), keys.data() + (size_t) i * K, K);
+                std::memcpy(img.data() + pad, pays.data() + (size_t) i * P, P);
+                std::memset(&results_[i], 0, sizeof(T));
+                std::memcpy(&results_[i], img.data(), sizeof(T) < img.size() ? sizeof(T) : img.size());
+            }
+            return true;
+        }
         std::vector<char> keys((size_t) scan_sz_ * K), pays((size_t) scan_sz_ * P);
         std::vector<uint32_t> ts(scan_sz_);
         uint32_t count = 0, sz = scan_sz_;

@@ -70,6 +70,7 @@ SYMBOLS = {
     "stage_gpu_scan_batch": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _vp, _vp, _i32]),
     "stage_gpu_probe_project": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp, _u32, _u32, _vp, _i32]),
     "stage_gpu_scan_project": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _u32, _u32, _vp, _i32]),
+    "stage_gpu_scan_physical": (_i32, [_vp, _u64, _u64, _vp, _vp, _vp, _i32]),
     "stage_gpu_route": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp]),
     "stage_gpu_route_device": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp, _vp]),
     "stage_gpu_exchange_create": (_i32, [_u32, _u32, _u64, C.POINTER(Schema), C.POINTER(_vp)]),
@@ -329,6 +330,17 @@ class Snapshot:
                                           int(apply_visibility), _ptr(counts), _ptr(key_out), _ptr(ts), _ptr(pay),
                                           IO_HOST))
         return counts, key_out, ts, pay
+
+    def scan_physical(self, first_row=0, n=None, want_payload=True):
+        """TableScanExecutor(scan_sz = -1): rows [first_row, first_row+n) of the physical (leaf, slot) order.
+        -> (keys u8[n,K], ts u32[n], payload u8[n,P])."""
+        if n is None:
+            n = int(self.info().n_rows) - first_row
+        K, P = self.schema.key_size, self.schema.payload_size
+        keys, ts = np.zeros((n, K), np.uint8), np.zeros(n, np.uint32)
+        pay = np.zeros((n, P), np.uint8) if want_payload else None
+        _check(lib().stage_gpu_scan_physical(self.h, first_row, n, _ptr(keys), _ptr(ts), _ptr(pay), IO_HOST))
+        return keys, ts, pay
 
     # -- reads with column push-down: only payload bytes [col_off, col_off + col_len) come back ----
     def probe_column(self, keys, read_ts, col_off, col_len):

@@ -247,3 +247,39 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
 }
 
 }  // namespace stage
+
+// ---- physical whole-tree scan (TableScanExecutor with scan_sz == -1, include/execute/executor.h:581-619) --------
+// The reference walks the tree physically: leaves in tree order, record slots in SLOT order (insertion order), and
+// copies every slot. In the flattened table the rows of a leaf are in key order with their slot index kept, so the
+// physical order is a per-leaf permutation: phys[leaf_off[j] + rank] = row, rank = number of rows of the leaf with a
+// smaller slot. (Invisible / deleted slots, whose bytes the reference copies too — zeroed metadata, i.e. host
+// garbage — are not part of a snapshot and are skipped.)
+namespace stage {
+
+__global__ void __launch_bounds__(128) physical_order_kernel(SnapshotView v, uint32_t *phys) {
+    extern __shared__ uint16_t s_sl[];
+    const uint32_t j = blockIdx.x;
+    if (j >= v.n_leaves) return;
+    const uint32_t lo = v.leaf_off[j], n = v.leaf_off[j + 1] - lo;
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) s_sl[i] = v.slot[lo + i];
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+        const uint16_t me = s_sl[i];
+        uint32_t rank = 0;
+        for (uint32_t x = 0; x < n; ++x) rank += s_sl[x] < me;
+        phys[lo + rank] = lo + i;
+    }
+}
+
+// keys and commit ids of physical rows [first, first + n)
+template <int NW>
+__global__ void physical_emit_kernel(SnapshotView v, const uint32_t *phys, uint64_t first, uint64_t n, uint8_t *key_out,
+                                     uint32_t *ts_out) {
+    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t row = phys[first + i];
+    if (ts_out) ts_out[i] = __ldg(v.ts + row);
+    if (key_out) from_sortable<NW>(load_skey<NW>(v.level[0], row), key_out + i * v.key_size, v.key_size, v.xormask);
+}
+
+}  // namespace stage

@@ -125,6 +125,7 @@ struct stage_snapshot {
     std::vector<uint8_t> h_has_sep;
     std::vector<stage_version_t> h_versions;
     std::vector<uint8_t> h_ver_payload;
+    uint32_t *d_phys = nullptr;                 // physical (leaf, slot) order -> row, built on first use
     uint8_t *ext_ver_payload = nullptr;         // malloc'd version rows handed over by from_tree (instead of h_ver_payload)
     uint8_t *h_stage[2] = {nullptr, nullptr};   // pinned
     uint8_t *d_stage[2] = {nullptr, nullptr};
@@ -199,7 +200,7 @@ static void snapshot_free(stage_snapshot *s) {
     cudaSetDevice(s->device);
     void *ptrs[] = {s->d_skey, s->d_slot, s->d_ts, s->d_chain, s->d_payload, s->d_leaf_off, s->d_sep, s->d_cont,
                     s->d_has_sep, s->d_ver_begin, s->d_ver_commit, s->d_ver_next, s->d_ver_payload,
-                    s->d_err, s->d_stage[0], s->d_stage[1], s->d_raw_keys};
+                    s->d_err, s->d_stage[0], s->d_stage[1], s->d_raw_keys, s->d_phys};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     free(s->ext_ver_payload);
@@ -1490,6 +1491,60 @@ extern "C" int stage_gpu_scan_project(stage_snapshot_t *s, const void *start_key
                                      rows * (uint64_t) col_len, cudaMemcpyDeviceToHost, s->stream));
             CUDA_TRY(cudaStreamSynchronize(s->stream));
         }
+    }
+    return STAGE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// physical whole-tree scan (TableScanExecutor, scan_sz == -1)
+// ------------------------------------------------------------------------------------------------
+extern "C" int stage_gpu_scan_physical(stage_snapshot_t *s, uint64_t first_row, uint64_t n, void *key_out, uint32_t *ts_out,
+                                       void *payload_out, int flags) {
+    if (!s) return STAGE_ERR_ARG;
+    if (!s->sealed) return STAGE_ERR_STATE;
+    if (first_row > s->n_rows || n > s->n_rows - first_row) return STAGE_ERR_ARG;
+    if (n == 0) return STAGE_OK;
+    std::lock_guard<std::mutex> lock(s->mu);
+    CUDA_TRY(cudaSetDevice(s->device));
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    int rc;
+    if (!s->d_phys) {
+        if ((rc = dev_alloc(s, &s->d_phys, s->n_rows))) return rc;
+        physical_order_kernel<<<(unsigned) s->n_leaves, 128, (size_t) std::max<uint32_t>(s->max_leaf_rows, 8) * 2, s->stream>>>(s->view, s->d_phys);
+        LAUNCH_CHECK();
+    }
+    auto emit = [&](uint64_t first, uint64_t m, uint8_t *k, uint32_t *t) -> int {
+        if (!k && !t) return STAGE_OK;
+        const unsigned blocks = (unsigned) ((m + 255) / 256);
+        switch (s->nw) {
+            case 1: physical_emit_kernel<1><<<blocks, 256, 0, s->stream>>>(s->view, s->d_phys, first, m, k, t); break;
+            case 2: physical_emit_kernel<2><<<blocks, 256, 0, s->stream>>>(s->view, s->d_phys, first, m, k, t); break;
+            case 4: physical_emit_kernel<4><<<blocks, 256, 0, s->stream>>>(s->view, s->d_phys, first, m, k, t); break;
+            default: physical_emit_kernel<8><<<blocks, 256, 0, s->stream>>>(s->view, s->d_phys, first, m, k, t); break;
+        }
+        LAUNCH_CHECK();
+        return STAGE_OK;
+    };
+    if (flags & STAGE_IO_DEVICE) {
+        if ((rc = emit(first_row, n, static_cast<uint8_t *>(key_out), ts_out))) return rc;
+        return launch_gather(s, s->d_phys + first_row, n, static_cast<uint8_t *>(payload_out));
+    }
+    const uint64_t chunk = std::max<uint64_t>(1, std::min<uint64_t>(n, (512ull << 20) / (P + K + 4)));
+    if (key_out && (rc = s->sc_keyout.ensure(chunk * K))) return rc;
+    if (ts_out && (rc = s->sc_ts.ensure(chunk * 4))) return rc;
+    if (payload_out && (rc = s->sc_payload.ensure(chunk * (uint64_t) P))) return rc;
+    for (uint64_t b = 0; b < n; b += chunk) {
+        const uint64_t m = std::min(chunk, n - b);
+        if ((rc = emit(first_row + b, m, key_out ? static_cast<uint8_t *>(s->sc_keyout.p) : nullptr,
+                       ts_out ? static_cast<uint32_t *>(s->sc_ts.p) : nullptr)))
+            return rc;
+        if (payload_out && (rc = launch_gather(s, s->d_phys + first_row + b, m, static_cast<uint8_t *>(s->sc_payload.p)))) return rc;
+        if (key_out) CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(key_out) + b * K, s->sc_keyout.p, m * K, cudaMemcpyDeviceToHost, s->stream));
+        if (ts_out) CUDA_TRY(cudaMemcpyAsync(ts_out + b, s->sc_ts.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
+        if (payload_out)
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(payload_out) + b * (uint64_t) P, s->sc_payload.p, m * (uint64_t) P,
+                                     cudaMemcpyDeviceToHost, s->stream));
+        CUDA_TRY(cudaStreamSynchronize(s->stream));
     }
     return STAGE_OK;
 }

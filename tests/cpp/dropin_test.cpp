@@ -166,6 +166,26 @@ static int run_checks(Table &t, const std::vector<std::string> &probe_keys, cons
         }
         mgr->CommitTransaction(txn);
     }
+    // --- physical whole-tree scan: TableScanExecutor with scan_sz == -1 (executor.h:581-619) ------------------------
+    if (!scan_keys.empty()) {
+        TransactionContext *txn = mgr->BeginTransaction(0, IsolationLevelType::SERIALIZABLE);
+        txn->SetReadOnly();
+        const std::string &k = scan_keys[0];
+        TableScanExecutor<const char *, T> ref(t.tree, k.data(), t.K, (uint32_t) -1, txn, nullptr);
+        EXPECT(ref.Execute(), "reference physical scan");
+        rows += ref.GetResults().size();
+        if (!ref_only) {
+            stage_gpu::GpuTableScanExecutor<const char *, T, TransactionContext> gpu(view.get(), k.data(), t.K, (uint32_t) -1, txn,
+                                                                                    nullptr);
+            EXPECT(gpu.Execute(), "gpu physical scan");
+            EXPECT(gpu.GetResults().size() == ref.GetResults().size(), "%s physical: %zu rows, reference %zu", what,
+                   gpu.GetResults().size(), ref.GetResults().size());
+            if (gpu.GetResults().size() == ref.GetResults().size())
+                for (size_t i = 0; i < gpu.GetResults().size(); ++i)
+                    EXPECT(memcmp(&gpu.GetResults()[i], &ref.GetResults()[i], sizeof(T)) == 0, "%s physical: row %zu differs", what, i);
+        }
+        mgr->CommitTransaction(txn);
+    }
     printf("%-12s probes %zu (hits %lu) scans %zu x %u (rows %lu) crc %016lx : %s\n", what, probe_keys.size(), hits,
            scan_keys.size(), scan_size, rows, crc, g_fail == fail0 ? "OK" : "FAILED");
     return g_fail - fail0;

@@ -243,3 +243,28 @@ def test_concurrent_callers(ycsb10k):
     for x in th:
         x.join()
     assert not errors, errors[:3]
+
+
+@pytest.mark.parametrize("key_size,payload", [(4, 1000), (16, 400)])
+def test_physical_scan(key_size, payload):
+    """TableScanExecutor(scan_sz = -1): leaves in tree order, slots in slot order (executor.h:581-619). Expected order
+    is read off the checker's leaf images: slot i of leaf j, visible slots only."""
+    from stage_indexorganized_b200.csrc_layout import parse_leaf
+    if key_size == 4:
+        t = ycsb_int_table(pyoracle.OracleTable, 8000, payload)
+    else:
+        t, _, _ = random_table(pyoracle.OracleTable, 3000, key_size, payload, seed=3)
+    leaves, _, _ = pyoracle.walk_tree(t.root)
+    want_k, want_p = [], []
+    for lp in leaves:
+        k, p = parse_leaf(pyoracle.read_mem(lp, 65536), key_size, payload)
+        want_k.append(k)
+        want_p.append(p)
+    want_k, want_p = np.concatenate(want_k), np.concatenate(want_p)
+    with sg.Snapshot.from_tree(t.root, key_size, payload) as snap:
+        keys, ts, pay = snap.scan_physical()
+        assert np.array_equal(keys, want_k) and np.array_equal(pay, want_p) and not ts.any()
+        k2, _, p2 = snap.scan_physical(1234, 777)
+        assert np.array_equal(k2, want_k[1234:2011]) and np.array_equal(p2, want_p[1234:2011])
+        with pytest.raises(sg.StageError):
+            snap.scan_physical(len(want_k) - 5, 6)

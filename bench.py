@@ -69,6 +69,10 @@ def parse_args():
     ap.add_argument("--e2e-scans", type=int, default=1024)
     ap.add_argument("--cpu-scans", type=int, default=0, help="scans in the CPU-baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="scan", choices=["scan", "string", "tpcc"],
+                    help="'scan' = BASELINE configs[1] (the headline, default); 'string' = configs[2] (100 M string keys, zipf "
+                         "0.9 probes); 'tpcc' = configs[3] (w=30 stock-level / Q2 read pattern). The extra workloads are "
+                         "single-GPU legs for profiles/README.md, not the driver's metric.")
     ap.add_argument("--table", default="device", choices=["device", "host"],
                     help="N = 1: 'device' builds the table with the on-device generator + refresh kernels (no oracle in "
                          "the GPU leg); 'host' flattens a tree built by the reference loader (transform kernel)")
@@ -236,6 +240,104 @@ def workload_config(args, world, table):
             "l2": "inputs larger than L2 (table >= 10 GB, 4 GB of rows written per step); no explicit flush"}
 
 
+def _time_steps(torch, fn, warmup, steps):
+    for i in range(warmup):
+        fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        fn(warmup + i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def run_extra_workload(args):
+    """Single-GPU legs for the other BASELINE configs (device-resident inputs and outputs, CUDA-event timed)."""
+    import torch
+    import stage_indexorganized_b200 as sg
+    from stage_indexorganized_b200 import tpcc, ycsb
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    sg.init(0)
+    peak, peak_src = peaks()
+    nb = args.warmup + args.steps
+    if args.workload == "string":
+        n_rows, n = 100_000_000, args.probes
+        snap, keys, _ = ycsb.build_string_table_device(n_rows)
+        snap.set_stream(torch.cuda.current_stream().cuda_stream)
+        z = np.clip(ycsb.Zipf(n_rows - 1, 0.9, seed=1).draw(n * nb).astype(np.int64), 1, n_rows) - 1
+        d_keys = keys[torch.from_numpy(z).to(dev)].reshape(nb, n, 16).contiguous()
+        found = torch.zeros((n,), dtype=torch.uint8, device=dev)
+        ts = torch.zeros((n,), dtype=torch.int32, device=dev)
+        kout = torch.empty((n, 16), dtype=torch.uint8, device=dev)
+        pay = torch.empty((n, P_BYTES), dtype=torch.uint8, device=dev)
+        ms = _time_steps(torch, lambda b: snap.probe_device(d_keys[b], n, 1, found, ts, kout, pay), args.warmup, args.steps)
+        hits = int(found.sum().item())
+        algo = hits * (16 + 2 * (16 + P_BYTES + 4)) + (n - hits) * 17
+        line = {"metric": "YCSB string-key zipf-0.9 probes/s (100M-tuple table)", "value": n / (ms * 1e-3), "unit": "probes/s",
+                "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": "BASELINE configs[2]: YCSB string-key (-m) zipf 0.9 batched probes, 100000000 tuples, "
+                                       "built on device (FastRandom(1804289383) keys, bulk load)", "probes_per_step": n,
+                           "distinct_keys_per_step": int(np.unique(z[:n]).size), "hit_rate": hits / n},
+                "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                             "frac": algo / (ms * 1e-3) / 1e9 / peak, "peak_source": peak_src,
+                             "note": "whole step (search + rows); zipf 0.9 repeats hot rows, so part of the row traffic is L2 hits"}}
+        print(json.dumps(line), flush=True)
+        snap.close()
+        return
+    # ---- tpcc: stock-level order_line scans + stock probes, Q2-shaped probe batches with S_QUANTITY push-down ------
+    W = 30
+    sk, sp = tpcc.stock_rows(W)
+    ok_, op, _ = tpcc.order_line_rows(W)
+
+    def bulk(keys, pays, K, P):
+        order = np.lexsort(keys.T[::-1])                      # memcmp order of the raw key bytes (keys >= 16 B)
+        snap, raw, pay, _ = sg.Snapshot.alloc_sorted(len(keys), K, P, rows_per_leaf=max(8, min(500, 60000 // (K + P + 24))))
+        raw.copy_(torch.from_numpy(keys[order]))
+        pay.copy_(torch.from_numpy(pays[order]))
+        snap.seal_sorted()
+        snap.set_stream(torch.cuda.current_stream().cuda_stream)
+        return snap
+    stock, ol = bulk(sk, sp, tpcc.STOCK_KEY, tpcc.STOCK_PAYLOAD), bulk(ok_, op, tpcc.OL_KEY, tpcc.OL_PAYLOAD)
+    txns = 50_000                                             # 1 M order_line scans of 10 rows per step
+    starts = [torch.from_numpy(tpcc.stock_level_requests(W, txns, seed=10 + b)[0]).to(dev) for b in range(nb)]
+    ns = txns * 20
+    sizes = torch.full((ns,), 10, dtype=torch.int32, device=dev)
+    counts = torch.zeros((ns,), dtype=torch.int32, device=dev)
+    kout = torch.empty((ns * 10, tpcc.OL_KEY), dtype=torch.uint8, device=dev)
+    tso = torch.empty((ns * 10,), dtype=torch.int32, device=dev)
+    pout = torch.empty((ns * 10, tpcc.OL_PAYLOAD), dtype=torch.uint8, device=dev)
+    ms_scan = _time_steps(torch, lambda b: ol.scan_device(starts[b], sizes, ns, 10, 1, 1, counts, kout, tso, pout),
+                          args.warmup, args.steps)
+    rows = int(counts.sum().item())
+    rng = np.random.default_rng(3)
+    n = args.probes
+    pk = [torch.from_numpy(tpcc.stock_key(rng.integers(1, W + 1, n), rng.integers(1, tpcc.ITEMS + 1, n))).to(dev) for _ in range(nb)]
+    found = torch.zeros((n,), dtype=torch.uint8, device=dev)
+    spay = torch.empty((n, tpcc.STOCK_PAYLOAD), dtype=torch.uint8, device=dev)
+    qty = torch.empty((n, 4), dtype=torch.uint8, device=dev)
+    ms_full = _time_steps(torch, lambda b: stock.probe_device(pk[b], n, 1, found, None, None, spay), args.warmup, args.steps)
+    ms_col = _time_steps(torch, lambda b: stock.probe_column_device(pk[b], n, 1, 0, 4, qty, found), args.warmup, args.steps)
+    ol_row, st_row = 2 * (tpcc.OL_KEY + tpcc.OL_PAYLOAD + 4), tpcc.STOCK_KEY + 2 * (tpcc.STOCK_KEY + tpcc.STOCK_PAYLOAD + 4)
+    line = {"metric": "TPC-C w=30 stock-level / Q2 read pattern", "value": rows / (ms_scan * 1e-3), "unit": "order_line rows/s",
+            "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_scan, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "BASELINE configs[3]: TPC-C w=30, stock 3 M rows (16/400), order_line "
+                                   f"{len(ok_)} rows (32/60), seeded row functions, bulk-loaded on device",
+                       "order_line_scans_per_step": ns, "scan_size": 10, "stock_probes_per_step": n},
+            "order_line_scan": {"rows_per_s": rows / (ms_scan * 1e-3), "scans_per_s": ns / (ms_scan * 1e-3), "ms_per_step": ms_scan,
+                                "achieved_GBps": rows * ol_row / (ms_scan * 1e-3) / 1e9, "frac_of_peak": rows * ol_row / (ms_scan * 1e-3) / 1e9 / peak},
+            "stock_probe_full_row": {"probes_per_s": n / (ms_full * 1e-3), "ms_per_step": ms_full,
+                                     "achieved_GBps": n * st_row / (ms_full * 1e-3) / 1e9, "frac_of_peak": n * st_row / (ms_full * 1e-3) / 1e9 / peak},
+            "stock_probe_quantity_pushdown": {"probes_per_s": n / (ms_col * 1e-3), "ms_per_step": ms_col,
+                                              "bytes_returned_per_probe": 5},
+            "roofline": {"bound": "hbm", "peak": peak, "unit": "GB/s", "peak_source": peak_src}}
+    print(json.dumps(line), flush=True)
+    stock.close()
+    ol.close()
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -243,6 +345,9 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.workload != "scan":
+        run_extra_workload(args)
         return
 
     import torch

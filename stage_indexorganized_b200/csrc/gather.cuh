@@ -111,3 +111,22 @@ __global__ void __launch_bounds__(256) gather_cols_kernel(GatherColsArgs a) {
 }
 
 }  // namespace stage
+
+// ---- short rows (TPC-C order_line: 60 B) ------------------------------------------------------------------------
+// A warp per row would use 15 of 32 lanes on a 60-byte row. Here every thread moves one 32-bit word of the output:
+// consecutive threads write consecutive words (fully coalesced stores) and read consecutive words of a source row.
+namespace stage {
+
+__global__ void __launch_bounds__(256) gather_rows_small_kernel(GatherArgs a, uint32_t words_per_row) {
+    const uint64_t w = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t slot = w / words_per_row;
+    if (slot >= a.n_slots) return;
+    const uint32_t row = __ldg(a.src_row + slot);
+    if (row == kNoRow) return;
+    const uint32_t k = (uint32_t) (w - slot * words_per_row);
+    const uint8_t *base = (row & kVersionRowFlag) ? a.ver_payload : a.payload;
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(base + (uint64_t) (row & ~kVersionRowFlag) * a.payload_size);
+    reinterpret_cast<uint32_t *>(a.dst)[w] = __ldg(src + k);
+}
+
+}  // namespace stage

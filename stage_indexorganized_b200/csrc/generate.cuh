@@ -88,7 +88,7 @@ __global__ void bulk_leaves_kernel(const uint32_t *skey, uint64_t n, uint64_t n_
             const bool hop = j + 1 < n_leaves && end > off;      // separator of a consolidated leaf = its largest key
 #pragma unroll
             for (int w = 0; w < NW; ++w) sep[j * NW + w] = hop ? skey[(end - 1) * NW + w] : 0xFFFFFFFFu;
-            cont[j] = hop ? 1 : 0;
+            cont[j] = (hop ? kLeafHop : 0) | kLeafSlotOrdered;          // bulk-loaded leaves: slot order == key order
         }
     }
 }
@@ -112,7 +112,7 @@ __global__ void generate_ycsb_meta_kernel(GenArgs g) {
             uint32_t s = 0xFFFFFFFFu;
             if (!last && end > off) s = bswap32(ycsb_rank_to_key(g.n_total, g.first_rank + end - 1)) ^ 0x80808080u;
             g.sep[j] = s;
-            g.cont[j] = (!last && end > off) ? 1 : 0;
+            g.cont[j] = ((!last && end > off) ? kLeafHop : 0) | kLeafSlotOrdered;
         }
     }
 }

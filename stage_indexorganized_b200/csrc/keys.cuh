@@ -13,6 +13,10 @@
 
 namespace stage {
 
+// per-leaf flags kept in the `cont` column
+constexpr uint8_t kLeafHop = 1;          // the leaf's largest visible key equals its upper fence: the iterator hops on (Q6)
+constexpr uint8_t kLeafSlotOrdered = 2;  // slot order == key order inside the leaf: the slot-order truncation (Q5) is a no-op
+
 template <int NW>
 struct SKey {
     uint32_t w[NW];

@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
                 const uint64_t need_end = (uint64_t) q0 + S;
                 for (uint32_t base = j0;; base += kScanThreads) {
                     const uint32_t j = base + tid;
-                    if (j < L && (!v.cont[j] || (uint64_t) v.leaf_off[j + 1] >= need_end || j == L - 1)) atomicMin(&s_min, j);
+                    if (j < L && (!(v.cont[j] & kLeafHop) || (uint64_t) v.leaf_off[j + 1] >= need_end || j == L - 1)) atomicMin(&s_min, j);
                     __syncthreads();
                     const uint32_t m = s_min;
                     __syncthreads();
@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
                 const uint32_t start_l = max(q0, v.leaf_off[jl]);
                 const uint32_t T = S - (start_l - q0);            // budget left when the iterator reaches leaf jl
                 const uint32_t nql = row_end - start_l;           // qualifying rows of leaf jl
-                const bool quirk = nql > T + 1;                   // slot-order early break bites (Q5)
+                const bool quirk = nql > T + 1 && !(v.cont[jl] & kLeafSlotOrdered);   // slot-order early break bites (Q5)
                 const uint32_t main_n = quirk ? start_l - q0 : total;
 
                 // ---- rows [q0, q0 + main_n): straight window, TMA-staged commit ids / chain heads -------
@@ -280,6 +280,132 @@ __global__ void physical_emit_kernel(SnapshotView v, const uint32_t *phys, uint6
     const uint32_t row = phys[first + i];
     if (ts_out) ts_out[i] = __ldg(v.ts + row);
     if (key_out) from_sortable<NW>(load_skey<NW>(v.level[0], row), key_out + i * v.key_size, v.key_size, v.xormask);
+}
+
+}  // namespace stage
+
+// ---- short scans: one WARP per scan ---------------------------------------------------------------------------
+// RunStockLevel issues scans of 10 rows (benchmark/tpcc/tpcc_stock_level.cpp:114); a 256-thread CTA per such scan
+// idles 96 % of its lanes and pays a dozen CTA barriers. scan_plan_warp_kernel runs the SAME algorithm as
+// scan_plan_kernel — start leaf, rows below the bound, last leaf touched, straight window with the MVCC predicate,
+// slot-order selection in the leaf where the budget runs out — with warp ballots in place of CTA barriers and
+// direct loads in place of the TMA-staged tile. Chosen by the host when out_stride is small.
+namespace stage {
+
+constexpr int kScanWarpThreads = 256;          // 8 scans in flight per CTA
+
+template <int NW>
+__global__ void __launch_bounds__(kScanWarpThreads) scan_plan_warp_kernel(SnapshotView v, ScanArgs a) {
+    extern __shared__ __align__(16) uint16_t s_slots_all[];      // [warps per CTA][max_leaf_rows]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr uint32_t FULL = 0xFFFFFFFFu;
+    uint16_t *s_slots = s_slots_all + (size_t) warp * ((v.max_leaf_rows + 7u) & ~7u);
+    const uint32_t K = v.key_size;
+    const uint32_t L = (uint32_t) v.n_leaves;
+    const uint64_t n_warps = (uint64_t) gridDim.x * (kScanWarpThreads / 32);
+    const uint32_t lt_mask = (1u << lane) - 1u;
+
+    for (uint64_t sid = (uint64_t) blockIdx.x * (kScanWarpThreads / 32) + warp; sid < a.n; sid += n_warps) {
+        const uint32_t S = a.scan_sizes[sid];
+        const SKey<NW> begin = to_sortable<NW>(a.start_keys + sid * K, K, v.xormask);
+        const uint64_t out_base = sid * (uint64_t) a.out_stride;
+        uint32_t cnt = 0;
+        auto emit = [&](uint32_t row, uint32_t src, uint32_t stamp, uint32_t pos) {
+            const uint64_t o = out_base + pos;
+            a.src_row[o] = src;
+            if (a.ts_out) a.ts_out[o] = stamp;
+            if (a.key_out) from_sortable<NW>(load_skey<NW>(v.level[0], row), a.key_out + o * K, K, v.xormask);
+        };
+        if (S > 0 && L > 0) {
+            // start leaf: number of upper fences < begin, 32-ary search
+            uint32_t j0 = 0;
+            for (uint32_t n = L - 1; n > 0;) {
+                const uint32_t step = (n + 31) / 32;
+                const uint64_t idx = (uint64_t) j0 + (uint64_t) (lane + 1) * step - 1;
+                const bool lt = idx < (uint64_t) j0 + n && skey_less<NW>(load_skey<NW>(v.sep, idx), begin);
+                const uint32_t adv = __popc(__ballot_sync(FULL, lt)) * step;
+                n = min(step - 1, n - min(n, adv));
+                j0 += adv;
+            }
+            const uint32_t lo0 = v.leaf_off[j0], hi0 = v.leaf_off[j0 + 1];
+            uint32_t below = 0;                                   // rows of the start leaf with key < begin (sorted: 32-ary search)
+            for (uint32_t n = hi0 - lo0; n > 0;) {
+                const uint32_t step = (n + 31) / 32;
+                const uint64_t idx = (uint64_t) below + (uint64_t) (lane + 1) * step - 1;
+                const bool lt = idx < (uint64_t) below + n && skey_less<NW>(load_skey<NW>(v.level[0], (uint64_t) lo0 + idx), begin);
+                const uint32_t adv = __popc(__ballot_sync(FULL, lt)) * step;
+                n = min(step - 1, n - min(n, adv));
+                below += adv;
+            }
+            const uint32_t q0 = lo0 + below;
+            if (hi0 > q0) {
+                const uint64_t need_end = (uint64_t) q0 + S;
+                uint32_t jl = L - 1;
+                for (uint32_t base = j0;; base += 32) {
+                    const uint32_t j = base + lane;
+                    const bool stop = j < L && (!(v.cont[j] & kLeafHop) || (uint64_t) v.leaf_off[j + 1] >= need_end || j == L - 1);
+                    const uint32_t m = __ballot_sync(FULL, stop);
+                    if (m) { jl = base + (uint32_t) __ffs(m) - 1; break; }
+                }
+                const uint32_t row_end = v.leaf_off[jl + 1];
+                const uint32_t total = (uint64_t) row_end >= need_end ? S : row_end - q0;
+                const uint32_t start_l = max(q0, v.leaf_off[jl]);
+                const uint32_t T = S - (start_l - q0);
+                const uint32_t nql = row_end - start_l;
+                const bool quirk = nql > T + 1 && !(v.cont[jl] & kLeafSlotOrdered);
+                const uint32_t main_n = quirk ? start_l - q0 : total;
+                for (uint32_t off = 0; off < main_n; off += 32) {
+                    const uint32_t i = off + lane;
+                    uint32_t src = kNoRow, stamp = 0;
+                    const uint32_t row = q0 + i;
+                    if (i < main_n) {
+                        const uint32_t t = __ldg(v.ts + row);
+                        if (!a.apply_visibility || a.read_ts >= t) { src = row; stamp = t; }
+                        else src = visible_version(v, row, t, a.read_ts, &stamp);
+                    }
+                    const uint32_t m = __ballot_sync(FULL, src != kNoRow);
+                    if (src != kNoRow) emit(row, src, stamp, cnt + __popc(m & lt_mask));
+                    cnt += __popc(m);
+                }
+                if (quirk) {
+                    for (uint32_t i = lane; i < nql; i += 32) s_slots[i] = v.slot[start_l + i];
+                    __syncwarp();
+                    // slot value of the (T+1)-th lowest slot (slots are unique): bisection on the 16-bit value, a warp
+                    // count per step — O(16 n / 32) instead of ranking every row against every other
+                    uint32_t vlo = 0, vhi = 0xFFFFu;
+                    while (vlo < vhi) {
+                        const uint32_t mid = (vlo + vhi) >> 1;
+                        uint32_t c = 0;
+                        for (uint32_t i = lane; i < nql; i += 32) c += s_slots[i] <= mid;
+                        c = __reduce_add_sync(FULL, c);
+                        if (c >= T + 1) vhi = mid; else vlo = mid + 1;
+                    }
+                    uint32_t sel_before = 0;
+                    for (uint32_t base = 0; base < nql; base += 32) {
+                        const uint32_t i = base + lane;
+                        const bool in_first = i < nql && s_slots[i] <= vlo;      // among the T+1 lowest-slot qualifying rows
+                        bool sel = in_first;
+                        const uint32_t ms = __ballot_sync(FULL, sel);
+                        sel = sel && sel_before + __popc(ms & lt_mask) < T;
+                        sel_before += __popc(ms);
+                        uint32_t src = kNoRow, stamp = 0;
+                        const uint32_t row = start_l + i;
+                        if (sel) {
+                            const uint32_t t = __ldg(v.ts + row);
+                            if (a.apply_visibility) src = visible_version(v, row, t, a.read_ts, &stamp);
+                            else { src = row; stamp = t; }
+                        }
+                        const uint32_t m2 = __ballot_sync(FULL, src != kNoRow);
+                        if (src != kNoRow) emit(row, src, stamp, cnt + __popc(m2 & lt_mask));
+                        cnt += __popc(m2);
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+        for (uint32_t i = cnt + lane; i < a.out_stride; i += 32) a.src_row[out_base + i] = kNoRow;
+        if (lane == 0) a.row_counts[sid] = cnt;
+    }
 }
 
 }  // namespace stage

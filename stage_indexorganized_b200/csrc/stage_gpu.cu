@@ -1120,6 +1120,14 @@ static int launch_gather(stage_snapshot *s, const uint32_t *src_row, uint64_t n_
     g.dst = dst;
     g.payload_size = s->schema.payload_size;
     const uintptr_t align = (uintptr_t) g.payload | (uintptr_t) g.ver_payload | (uintptr_t) dst | g.payload_size;
+    if (g.payload_size <= 256 && (align & 3) == 0) {          // short rows: one thread per 32-bit word
+        const uint32_t wpr = g.payload_size / 4;
+        const uint64_t words = n_slots * wpr;
+        if ((words + 255) / 256 > 0x7FFFFFFFull) return STAGE_ERR_ARG;
+        gather_rows_small_kernel<<<(unsigned) ((words + 255) / 256), 256, 0, s->stream>>>(g, wpr);
+        LAUNCH_CHECK();
+        return STAGE_OK;
+    }
     if ((align & 15) == 0) return launch_gather_v<uint4>(s, g);
     if ((align & 7) == 0) return launch_gather_v<uint2>(s, g);
     if ((align & 3) == 0) return launch_gather_v<uint32_t>(s, g);
@@ -1265,6 +1273,18 @@ extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint
 
 template <int NW>
 static int launch_scan(stage_snapshot *s, const ScanArgs &a) {
+    // short scans (stock-level: 10 rows): one warp per scan instead of one CTA per scan
+    static const uint32_t warp_max = getenv("STAGE_SCAN_WARP_MAX") ? (uint32_t) atoi(getenv("STAGE_SCAN_WARP_MAX")) : 128;
+    if (a.out_stride <= warp_max) {
+        constexpr int wpc = kScanWarpThreads / 32;
+        const size_t wsmem = (size_t) wpc * ((s->view.max_leaf_rows + 7u) & ~7u) * 2 + 16;
+        if (wsmem > 48 * 1024)
+            CUDA_TRY(cudaFuncSetAttribute(scan_plan_warp_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) wsmem));
+        const unsigned wblocks = (unsigned) std::min<uint64_t>((a.n + wpc - 1) / wpc, (uint64_t) sm_count() * 16);
+        scan_plan_warp_kernel<NW><<<wblocks, kScanWarpThreads, wsmem, s->stream>>>(s->view, a);
+        LAUNCH_CHECK();
+        return STAGE_OK;
+    }
     const size_t smem = (size_t) std::max<uint32_t>(s->view.max_leaf_rows, 8) * 2;
     const unsigned blocks = (unsigned) std::min<uint64_t>(a.n, (uint64_t) sm_count() * 64);
     scan_plan_kernel<NW><<<blocks, kScanThreads, smem, s->stream>>>(s->view, a);

@@ -138,7 +138,9 @@ __global__ void __launch_bounds__(128) leaf_transform_kernel(TransformArgs a) {
             for (int w = 0; w < NW; ++w) eq = eq && (s_key[(size_t) (n - 1) * NW + w] == a.sep[gj * NW + w]);
             c = eq ? 1 : 0;
         }
-        a.cont[gj] = c;
+        bool ordered = true;                                     // slots ascending in key order?
+        for (uint32_t i = 1; i < n; ++i) ordered = ordered && s_slot[i - 1] < s_slot[i];
+        a.cont[gj] = c | (ordered ? kLeafSlotOrdered : 0);
     }
 
     // 4. payload gather: sorted row i <- record at slot s_slot[i]; one warp per row

@@ -69,7 +69,7 @@ def parse_args():
     ap.add_argument("--e2e-scans", type=int, default=1024)
     ap.add_argument("--cpu-scans", type=int, default=0, help="scans in the CPU-baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="scan", choices=["scan", "string", "tpcc"],
+    ap.add_argument("--workload", default="scan", choices=["scan", "config1", "string", "tpcc"],
                     help="'scan' = BASELINE configs[1] (the headline, default); 'string' = configs[2] (100 M string keys, zipf "
                          "0.9 probes); 'tpcc' = configs[3] (w=30 stock-level / Q2 read pattern). The extra workloads are "
                          "single-GPU legs for profiles/README.md, not the driver's metric.")
@@ -263,6 +263,45 @@ def run_extra_workload(args):
     sg.init(0)
     peak, peak_src = peaks()
     nb = args.warmup + args.steps
+    if args.workload == "config1":
+        # BASELINE configs[0]: ./ycsb -k 10000 -b 4 -o 10 -u 0 -z 0.2 — read-only point probes, int keys, 10 000 rows.
+        # (The reference's own CLI aborts at HEAD with an out-of-range key pick, SURVEY.md §3.5, so the CPU side is the
+        # reference's BTree::Read driven by the harness over the same key stream, at 4 threads like -b 4 and at all.)
+        n_rows, n = 10_000, args.probes
+        snap = sg.Snapshot.generate_ycsb(n_rows, P_BYTES)
+        snap.set_stream(torch.cuda.current_stream().cuda_stream)
+        z = ycsb.Zipf(n_rows - 1, 0.2, seed=1).draw(n * nb).astype(np.uint32).reshape(nb, n)
+        d_keys = torch.from_numpy(z.view(np.int32)).to(dev)
+        found = torch.zeros((n,), dtype=torch.uint8, device=dev)
+        ts = torch.zeros((n,), dtype=torch.int32, device=dev)
+        kout = torch.empty((n,), dtype=torch.int32, device=dev)
+        pay = torch.empty((n, P_BYTES), dtype=torch.uint8, device=dev)
+        ms = _time_steps(torch, lambda b: snap.probe_device(d_keys[b], n, 1, found, ts, kout, pay), args.warmup, args.steps)
+        hits = int(found.sum().item())
+        algo = hits * PROBE_HIT_BYTES + (n - hits) * PROBE_MISS_BYTES
+        cpu = None
+        if not args.no_cpu_baseline:
+            from oracle import pyoracle
+            pyoracle.build_oracle()
+            t = pyoracle.RefTable(P_BYTES) if pyoracle.have_ref() else pyoracle.OracleTable(P_BYTES)
+            assert t.load_ycsb_int(0, n_rows) == n_rows
+            keys = np.ascontiguousarray(z.reshape(-1)[: 1 << 22]).view(np.uint8).reshape(-1, 4)
+            ok = all(np.array_equal(g, w) for g, w in zip(snap.probe(keys[:65536], 1), t.probe(keys[:65536], 1)))
+            cpu = {"kind": "reference" if pyoracle.have_ref() else "port", "unit": "probes/s", "parity_sample_ok": bool(ok)}
+            for th in (4, os.cpu_count() or 1):
+                sec, h = t.time_probe(keys, 1, th, pin=True)
+                cpu[f"threads_{th}"] = len(keys) / sec
+        line = {"metric": "YCSB read-only point probes/s (10k-tuple int table, zipf 0.2)", "value": n / (ms * 1e-3),
+                "unit": "probes/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "dtype": "u8",
+                "data": "synthetic", "config": {"workload": "BASELINE configs[0]: ./ycsb -k 10000 -b 4 -o 10 -u 0 -z 0.2",
+                                                "probes_per_step": n, "hit_rate": hits / n,
+                                                "note": "the 10 MB table lives in L2: the bound here is L2/SM throughput, not HBM"},
+                "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                             "frac": algo / (ms * 1e-3) / 1e9 / peak, "peak_source": peak_src},
+                "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+        snap.close()
+        return
     if args.workload == "string":
         n_rows, n = 100_000_000, args.probes
         snap, keys, _ = ycsb.build_string_table_device(n_rows)

@@ -249,6 +249,28 @@ int stage_gpu_exchange_wait(stage_exchange_t *x, void *cuda_stream);
  * payload rows of payload_size bytes every *payload_stride bytes (payload_size rounded up to 128, so that the
  * owners' peer stores are line-aligned). Rows of missed probes keep their previous content. */
 int stage_gpu_exchange_results(stage_exchange_t *x, void **found, void **ts, void **payload, uint32_t *payload_stride);
+
+/* Routed range scans over the same arenas ("scans run shard-local followed by a gather"). The scan
+ * (start key, size) is posted to the owner of its START key; the owner plans it on its shard with the ordinary scan
+ * plan kernels (same iterator quirks and MVCC filter as stage_gpu_scan_batch) and writes the row count, keys, commit
+ * ids and payload rows straight into the requester's slab, request q at rows [q*rows_per_scan, +count). A scan does
+ * not continue on the next shard: shards are expected to overlap their right neighbour by a halo of rows (the
+ * caller's sharding decides how many: enough for the longest scan including the rows the filter drops).
+ * Replaces: the per-thread loop over BTree::RangeScanBySize / Iterator::GetNext (include/vstore/b_tree.h:867-950,
+ * src/execute/index_scan_executor.cpp:64-116) on a range-partitioned table. key_size must be a multiple of 4.
+ * Call order per batch as for probes: post_scans, serve_scans, wait (device sync) on one stream. */
+int stage_gpu_exchange_create_scan(uint32_t world, uint32_t rank, uint64_t max_scans, uint32_t max_scan_size,
+                                   const stage_schema_t *schema, stage_exchange_t **out);
+/* start_keys_dev: n x key_size, scan_sizes_dev: u32[n] (clamped to max_scan_size), device memory. */
+int stage_gpu_exchange_post_scans(stage_exchange_t *x, const void *splitters, const void *start_keys_dev,
+                                  const uint32_t *scan_sizes_dev, uint64_t n, int flags, void *cuda_stream);
+int stage_gpu_exchange_serve_scans(stage_exchange_t *x, stage_snapshot_t *shard, uint32_t read_ts, int apply_visibility,
+                                   int flags, void *cuda_stream);
+/* Device pointers (local) of this rank's scan result slab: row_counts u32[max_scans]; per scan *rows_per_scan rows
+ * of keys (every *key_stride bytes), commit ids (u32) and payload rows (every *payload_stride bytes). Rows beyond
+ * row_counts[q] keep their previous content. */
+int stage_gpu_exchange_scan_results(stage_exchange_t *x, void **row_counts, void **key_out, void **ts, void **payload,
+                                    uint32_t *rows_per_scan, uint32_t *key_stride, uint32_t *payload_stride);
 /* Sticky device-side error of the exchange: 0 ok, 1 inbox overflow, 2 device-sync timeout. Synchronises the stream. */
 int stage_gpu_exchange_error(stage_exchange_t *x, void *cuda_stream, uint32_t *err_out);
 /* Per-phase timing of the last post/serve/wait sequence (STAGE_XCHG_DEVICE_SYNC), CUDA events on the caller's stream:

@@ -82,6 +82,11 @@ SYMBOLS = {
     "stage_gpu_exchange_serve": (_i32, [_vp, _vp, _u32, _i32, _vp]),
     "stage_gpu_exchange_wait": (_i32, [_vp, _vp]),
     "stage_gpu_exchange_results": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_u32)]),
+    "stage_gpu_exchange_create_scan": (_i32, [_u32, _u32, _u64, _u32, C.POINTER(Schema), C.POINTER(_vp)]),
+    "stage_gpu_exchange_post_scans": (_i32, [_vp, _vp, _vp, _vp, _u64, _i32, _vp]),
+    "stage_gpu_exchange_serve_scans": (_i32, [_vp, _vp, _u32, _i32, _i32, _vp]),
+    "stage_gpu_exchange_scan_results": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),
+                                               C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u32)]),
     "stage_gpu_exchange_error": (_i32, [_vp, _vp, C.POINTER(_u32)]),
     "stage_gpu_exchange_enable_timing": (_i32, [_vp, _i32]),
     "stage_gpu_exchange_last_timing": (_i32, [_vp, C.POINTER(C.c_float)]),
@@ -415,11 +420,17 @@ class ProbeExchange:
     """Routed point probes over peer memory (include/stage_gpu.h, "routed probes over peer memory"): this rank's
     arena (inboxes + result slab) and the mappings of every peer's arena. One instance per rank."""
 
-    def __init__(self, world, rank, capacity, key_size, payload_size, key_kind=KEY_AUTO):
+    def __init__(self, world, rank, capacity, key_size, payload_size, key_kind=KEY_AUTO, max_scan_size=0):
+        """max_scan_size > 0 makes this a scan exchange (post_scans / serve_scans / scan_results_torch) for up to
+        `capacity` scans of up to max_scan_size rows per batch."""
         self.world, self.rank, self.capacity = world, rank, capacity
         self.schema = Schema(key_size, payload_size, 65536, key_kind)
         self.h = _vp()
-        _check(lib().stage_gpu_exchange_create(world, rank, capacity, C.byref(self.schema), C.byref(self.h)))
+        if max_scan_size:
+            _check(lib().stage_gpu_exchange_create_scan(world, rank, capacity, max_scan_size, C.byref(self.schema),
+                                                        C.byref(self.h)))
+        else:
+            _check(lib().stage_gpu_exchange_create(world, rank, capacity, C.byref(self.schema), C.byref(self.h)))
 
     def ipc_handle(self):
         buf = (C.c_uint8 * IPC_HANDLE_BYTES)()
@@ -447,6 +458,17 @@ class ProbeExchange:
 
     def serve(self, shard, read_ts, flags=0, cuda_stream=0):
         _check(lib().stage_gpu_exchange_serve(self.h, shard.h, read_ts, flags, _vp(int(cuda_stream))))
+
+    def post_scans(self, splitters, start_keys_dev, scan_sizes_dev, n, flags=0, cuda_stream=0):
+        sp = None
+        if self.world > 1:
+            sp = np.ascontiguousarray(splitters, np.uint8).reshape(self.world - 1, self.schema.key_size)
+        _check(lib().stage_gpu_exchange_post_scans(self.h, _ptr(sp), _ptr(start_keys_dev), _ptr(scan_sizes_dev), n, flags,
+                                                   _vp(int(cuda_stream))))
+
+    def serve_scans(self, shard, read_ts, apply_visibility=True, flags=0, cuda_stream=0):
+        _check(lib().stage_gpu_exchange_serve_scans(self.h, shard.h, read_ts, int(apply_visibility), flags,
+                                                    _vp(int(cuda_stream))))
 
     def wait(self, cuda_stream=0):
         _check(lib().stage_gpu_exchange_wait(self.h, _vp(int(cuda_stream))))
@@ -482,6 +504,24 @@ class ProbeExchange:
         ts = torch.as_tensor(_DeviceView(t, (n,), "<i4", self), device=dev)
         pay = torch.as_tensor(_DeviceView(p, (n, stride), "|u1", self), device=dev)[:, :P]
         return found, ts, pay
+
+    def scan_results_torch(self, n=None):
+        """(row_counts i32[n], keys u8[n,R,K], ts i32[n,R], payload u8[n,R,P]) torch views of the scan result slab
+        (no copy; R = rows per scan of this exchange; rows beyond row_counts[q] are stale)."""
+        import torch
+        n = self.capacity if n is None else n
+        c, k, t, p = _vp(), _vp(), _vp(), _vp()
+        R, ks, ps = _u32(0), _u32(0), _u32(0)
+        _check(lib().stage_gpu_exchange_scan_results(self.h, C.byref(c), C.byref(k), C.byref(t), C.byref(p), C.byref(R),
+                                                     C.byref(ks), C.byref(ps)))
+        R, ks, ps = int(R.value), int(ks.value), int(ps.value)
+        K, P = self.schema.key_size, self.schema.payload_size
+        dev = torch.device("cuda", torch.cuda.current_device())
+        counts = torch.as_tensor(_DeviceView(int(c.value), (n,), "<i4", self), device=dev)
+        keys = torch.as_tensor(_DeviceView(int(k.value), (n, R, ks), "|u1", self), device=dev)[:, :, :K]
+        ts = torch.as_tensor(_DeviceView(int(t.value), (n, R), "<i4", self), device=dev)
+        pay = torch.as_tensor(_DeviceView(int(p.value), (n, R, ps), "|u1", self), device=dev)[:, :, :P]
+        return counts, keys, ts, pay
 
     def close(self):
         if self.h:

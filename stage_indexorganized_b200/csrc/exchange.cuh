@@ -37,9 +37,13 @@ struct ExchangeLayout {
     uint64_t off_req;       // u32 [world][cap]       inbox: request index at the source
     uint64_t off_found;     // u8  [cap]              result slab of THIS rank's requests
     uint64_t off_ts;        // u32 [cap]
-    uint64_t off_payload;   // u8  [cap][pstride]     rows padded to 128 B so that peer stores are line-aligned
+    uint64_t off_payload;   // u8  [cap*rows][pstride] rows padded to 128 B so that peer stores are line-aligned
+    uint64_t off_sizes;     // u32 [world][cap]       inbox: scan sizes (scan exchange only)
+    uint64_t off_counts;    // u32 [cap]              result: rows returned per scan (scan exchange only)
+    uint64_t off_keyout;    // u8  [cap*rows][kpad]   result: keys of the scanned rows (scan exchange only)
     uint64_t bytes;
     uint32_t cap, kpad, pstride;
+    uint32_t rows;          // result rows per request: 1 for probes, the scan stride for scans
 };
 
 struct ExchangeView {
@@ -90,7 +94,7 @@ __device__ __forceinline__ void cta_wait_flags(const uint32_t *flags, uint32_t w
 // atomic per owner per tile on the local running counters), peer store of key + request index.
 template <int NW>
 __global__ void __launch_bounds__(256) exchange_post_kernel(ExchangeView x, ExchangeSplit sp, const uint8_t *keys, uint64_t n,
-                                                            uint32_t key_size, uint32_t xormask) {
+                                                            uint32_t key_size, uint32_t xormask, const uint32_t *sizes) {
     __shared__ uint32_t s_cnt[kMaxExchangeRanks], s_base[kMaxExchangeRanks];
     const int tid = threadIdx.x;
     const uint64_t tiles = (n + 255) / 256;
@@ -129,6 +133,7 @@ __global__ void __launch_bounds__(256) exchange_post_kernel(ExchangeView x, Exch
                     for (uint32_t b = 0; b < key_size; ++b) kd[b] = ks[b];
                 }
                 reinterpret_cast<uint32_t *>(inbox + x.lay.off_req)[slot] = (uint32_t) i;
+                if (sizes) reinterpret_cast<uint32_t *>(inbox + x.lay.off_sizes)[slot] = min(sizes[i], x.lay.rows);
             } else {
                 atomicExch(x.err, 1u);
             }
@@ -161,16 +166,17 @@ struct ServeArgs {
     uint32_t *src_row;      // [world*cap] local scratch: row to gather per inbox entry (compact over sources)
     uint32_t *dst_slot;     // [world*cap] (requester << 28) | request index
     int tile_order;         // 0: permuted (t * mul mod tiles); 1: all-to-all shift schedule (TilePlan)
+    uint32_t seg_mul;       // result rows per inbox entry (1: probes; scan stride: scans)
 };
 
 // prefix offsets of the per-source inbox counts, into shared memory (ends with a barrier)
-__device__ __forceinline__ void load_segments(const ExchangeView &x, uint32_t *s_off) {
+__device__ __forceinline__ void load_segments(const ExchangeView &x, uint32_t *s_off, uint32_t seg_mul = 1) {
     if (threadIdx.x == 0) {
         const uint32_t *cnt = reinterpret_cast<const uint32_t *>(x.arena[x.rank] + x.lay.off_count);
         uint32_t acc = 0;
         for (int s = 0; s < kMaxExchangeRanks; ++s) {
             s_off[s] = acc;
-            if (s < (int) x.world) acc += min(__ldcg(cnt + s), x.lay.cap);
+            if (s < (int) x.world) acc += min(__ldcg(cnt + s), x.lay.cap) * seg_mul;
         }
         s_off[kMaxExchangeRanks] = acc;
     }
@@ -303,7 +309,7 @@ __global__ void __launch_bounds__(kGatherThreads) exchange_gather_kernel(Exchang
                                                                         const uint8_t *ver_payload, uint32_t P) {
     __shared__ uint32_t s_row[kGatherRows], s_dst[kGatherRows];
     __shared__ uint32_t off[kMaxExchangeRanks + 1];
-    load_segments(x, off);
+    load_segments(x, off, a.seg_mul);
     const uint32_t total = off[kMaxExchangeRanks];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = kGatherThreads / 32;
@@ -358,7 +364,7 @@ __global__ void __launch_bounds__(kGatherThreads) exchange_gather16_kernel(Excha
                                                                           const uint8_t *ver_payload, uint32_t P) {
     __shared__ uint32_t s_row[kGatherRows], s_dst[kGatherRows];
     __shared__ uint32_t off[kMaxExchangeRanks + 1];
-    load_segments(x, off);
+    load_segments(x, off, a.seg_mul);
     const uint32_t total = off[kMaxExchangeRanks];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = kGatherThreads / 32;
@@ -423,6 +429,55 @@ __global__ void exchange_serve_finish_kernel(ExchangeView x, uint32_t epoch) {
 // Device sync, requester side: every owner has served this batch -> the result slab is complete.
 __global__ void exchange_wait_served_kernel(ExchangeView x, uint32_t epoch) {
     cta_wait_flags(reinterpret_cast<const uint32_t *>(x.arena[x.rank] + x.lay.off_served), x.world, epoch, x.err);
+}
+
+// ---- scans over the exchange ------------------------------------------------------------------------------
+// Scan requests (start key, size) are posted like probe keys. The owner plans them with the ordinary scan plan
+// kernels, one launch per source rank over that rank's inbox (the number of requests is read on the device), into
+// local scratch in inbox order; exchange_scan_deliver_kernel then hands every scan to its requester: row count,
+// keys and commit ids are stored into the requester's slab at the request's index, and the compact
+// (source row, destination row) lists for the payload mover — the same exchange_gather kernels as for probes — are
+// written. Result rows of request q live at rows [q*rows, q*rows + count) of the requester's slab.
+__global__ void exchange_wait_posted_kernel(ExchangeView x, uint32_t epoch) {
+    cta_wait_flags(reinterpret_cast<const uint32_t *>(x.arena[x.rank] + x.lay.off_posted), x.world, epoch, x.err);
+}
+
+struct ScanDeliverArgs {
+    const uint32_t *row_counts;   // [world*cap]           plan outputs, inbox order
+    const uint8_t *keys;          // [world*cap*rows][K]
+    const uint32_t *ts;           // [world*cap*rows]
+    const uint32_t *src_row;      // [world*cap*rows]
+    uint32_t *src_row_c;          // compact over (source, entry, pos): input of the payload mover
+    uint32_t *dst_slot_c;
+    uint32_t key_size;
+};
+
+__global__ void __launch_bounds__(256) exchange_scan_deliver_kernel(ExchangeView x, ScanDeliverArgs d) {
+    __shared__ uint32_t off[kMaxExchangeRanks + 1];
+    load_segments(x, off, 1);                                  // entries, not rows
+    const uint32_t total = off[kMaxExchangeRanks], R = x.lay.rows, K = d.key_size;
+    const uint8_t *inbox = x.arena[x.rank];
+    const uint32_t *req = reinterpret_cast<const uint32_t *>(inbox + x.lay.off_req);
+    for (uint32_t e = blockIdx.x; e < total; e += gridDim.x) {
+        uint32_t sgm = 0;
+        for (uint32_t q = 1; q < x.world; ++q) sgm += e >= off[q] ? 1u : 0u;
+        const uint64_t slot = (uint64_t) sgm * x.lay.cap + (e - off[sgm]);
+        const uint32_t q = req[slot], cnt = d.row_counts[slot];
+        uint8_t *peer = x.arena[sgm];
+        if (threadIdx.x == 0) reinterpret_cast<uint32_t *>(peer + x.lay.off_counts)[q] = cnt;
+        for (uint32_t pos = threadIdx.x; pos < R; pos += blockDim.x) {
+            const uint64_t in = slot * R + pos, g = (uint64_t) e * R + pos, out = (uint64_t) q * R + pos;
+            const uint32_t src = pos < cnt ? d.src_row[in] : kNoRow;
+            d.src_row_c[g] = src;
+            d.dst_slot_c[g] = (sgm << kDstRankShift) | (uint32_t) out;
+            if (pos < cnt) {
+                reinterpret_cast<uint32_t *>(peer + x.lay.off_ts)[out] = d.ts[in];
+                for (uint32_t b = 0; b < K; b += 4)
+                    *reinterpret_cast<uint32_t *>(peer + x.lay.off_keyout + out * x.lay.kpad + b) =
+                        *reinterpret_cast<const uint32_t *>(d.keys + in * K + b);
+            }
+        }
+    }
 }
 
 }  // namespace stage

@@ -40,6 +40,7 @@ struct ScanArgs {
     uint8_t *key_out;
     uint32_t *ts_out;
     uint32_t *src_row;          // [n][out_stride] rows to gather, kNoRow beyond row_counts[i]
+    const uint32_t *n_dev;      // optional: the number of scans lives on the device (min(*n_dev, n) are run)
 };
 
 constexpr int kScanThreads = 256;
@@ -113,7 +114,8 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
     if (tid == 0) mbar_init(&s_bar, 1);
     __syncthreads();
 
-    for (uint64_t sid = blockIdx.x; sid < a.n; sid += gridDim.x) {
+    const uint64_t n_scans = a.n_dev ? min((uint64_t) __ldcg(a.n_dev), a.n) : a.n;
+    for (uint64_t sid = blockIdx.x; sid < n_scans; sid += gridDim.x) {
         const uint32_t S = a.scan_sizes[sid];
         const SKey<NW> begin = to_sortable<NW>(a.start_keys + sid * K, K, v.xormask);
         const uint64_t out_base = sid * (uint64_t) a.out_stride;
@@ -305,7 +307,8 @@ __global__ void __launch_bounds__(kScanWarpThreads) scan_plan_warp_kernel(Snapsh
     const uint64_t n_warps = (uint64_t) gridDim.x * (kScanWarpThreads / 32);
     const uint32_t lt_mask = (1u << lane) - 1u;
 
-    for (uint64_t sid = (uint64_t) blockIdx.x * (kScanWarpThreads / 32) + warp; sid < a.n; sid += n_warps) {
+    const uint64_t n_scans = a.n_dev ? min((uint64_t) __ldcg(a.n_dev), a.n) : a.n;
+    for (uint64_t sid = (uint64_t) blockIdx.x * (kScanWarpThreads / 32) + warp; sid < n_scans; sid += n_warps) {
         const uint32_t S = a.scan_sizes[sid];
         const SKey<NW> begin = to_sortable<NW>(a.start_keys + sid * K, K, v.xormask);
         const uint64_t out_base = sid * (uint64_t) a.out_stride;

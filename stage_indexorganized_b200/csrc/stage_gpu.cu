@@ -1272,7 +1272,7 @@ extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint
 }
 
 template <int NW>
-static int launch_scan(stage_snapshot *s, const ScanArgs &a) {
+static int launch_scan(stage_snapshot *s, const ScanArgs &a, cudaStream_t st) {
     // short scans (stock-level: 10 rows): one warp per scan instead of one CTA per scan
     static const uint32_t warp_max = getenv("STAGE_SCAN_WARP_MAX") ? (uint32_t) atoi(getenv("STAGE_SCAN_WARP_MAX")) : 128;
     if (a.out_stride <= warp_max) {
@@ -1281,13 +1281,13 @@ static int launch_scan(stage_snapshot *s, const ScanArgs &a) {
         if (wsmem > 48 * 1024)
             CUDA_TRY(cudaFuncSetAttribute(scan_plan_warp_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) wsmem));
         const unsigned wblocks = (unsigned) std::min<uint64_t>((a.n + wpc - 1) / wpc, (uint64_t) sm_count() * 16);
-        scan_plan_warp_kernel<NW><<<wblocks, kScanWarpThreads, wsmem, s->stream>>>(s->view, a);
+        scan_plan_warp_kernel<NW><<<wblocks, kScanWarpThreads, wsmem, st>>>(s->view, a);
         LAUNCH_CHECK();
         return STAGE_OK;
     }
     const size_t smem = (size_t) std::max<uint32_t>(s->view.max_leaf_rows, 8) * 2;
     const unsigned blocks = (unsigned) std::min<uint64_t>(a.n, (uint64_t) sm_count() * 64);
-    scan_plan_kernel<NW><<<blocks, kScanThreads, smem, s->stream>>>(s->view, a);
+    scan_plan_kernel<NW><<<blocks, kScanThreads, smem, st>>>(s->view, a);
     LAUNCH_CHECK();
     return STAGE_OK;
 }
@@ -1301,10 +1301,10 @@ static int scan_device(stage_snapshot *s, ScanArgs a, uint8_t *payload_out) {
     a.src_row = static_cast<uint32_t *>(s->sc_srcrow.p);
     if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[0], s->stream));
     switch (s->nw) {
-        case 1: rc = launch_scan<1>(s, a); break;
-        case 2: rc = launch_scan<2>(s, a); break;
-        case 4: rc = launch_scan<4>(s, a); break;
-        default: rc = launch_scan<8>(s, a); break;
+        case 1: rc = launch_scan<1>(s, a, s->stream); break;
+        case 2: rc = launch_scan<2>(s, a, s->stream); break;
+        case 4: rc = launch_scan<4>(s, a, s->stream); break;
+        default: rc = launch_scan<8>(s, a, s->stream); break;
     }
     if (rc) return rc;
     if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[1], s->stream));
@@ -1495,10 +1495,10 @@ extern "C" int stage_gpu_scan_project(stage_snapshot_t *s, const void *start_key
             cdst = static_cast<uint8_t *>(s->sc_payload.p);
         }
         switch (s->nw) {
-            case 1: rc = launch_scan<1>(s, a); break;
-            case 2: rc = launch_scan<2>(s, a); break;
-            case 4: rc = launch_scan<4>(s, a); break;
-            default: rc = launch_scan<8>(s, a); break;
+            case 1: rc = launch_scan<1>(s, a, s->stream); break;
+            case 2: rc = launch_scan<2>(s, a, s->stream); break;
+            case 4: rc = launch_scan<4>(s, a, s->stream); break;
+            default: rc = launch_scan<8>(s, a, s->stream); break;
         }
         if (rc) return rc;
         if ((rc = launch_gather_cols(s, a.src_row, rows, col_off, col_len, cdst))) return rc;
@@ -1662,6 +1662,9 @@ struct stage_exchange {
     bool opened[kMaxExchangeRanks] = {false};
     uint32_t *d_local_cnt = nullptr, *d_err = nullptr;
     uint32_t *d_src_row = nullptr, *d_dst_slot = nullptr;
+    // scan exchange: plan outputs in inbox order (row counts, keys, commit ids, source rows)
+    uint32_t *d_sc_counts = nullptr, *d_sc_ts = nullptr, *d_sc_src = nullptr;
+    uint8_t *d_sc_keys = nullptr;
     uint32_t epoch_post = 0, epoch_serve = 0, epoch_wait = 0;
     bool attached = false;
     // per-phase CUDA events: [0] before post, [1] after post, [2] after the serve search, [3] after the row gather,
@@ -1673,15 +1676,16 @@ struct stage_exchange {
 
 static uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 
-extern "C" int stage_gpu_exchange_create(uint32_t world, uint32_t rank, uint64_t capacity, const stage_schema_t *schema,
-                                         stage_exchange_t **out) {
-    if (!out || world == 0 || world > (uint32_t) kMaxExchangeRanks || rank >= world || capacity == 0 ||
-        capacity > kDstIndexMask)
+static int exchange_create(uint32_t world, uint32_t rank, uint64_t capacity, uint32_t rows, const stage_schema_t *schema,
+                           stage_exchange_t **out) {
+    if (!out || world == 0 || world > (uint32_t) kMaxExchangeRanks || rank >= world || capacity == 0 || rows == 0 ||
+        capacity * rows > kDstIndexMask)
         return STAGE_ERR_ARG;
     int nw;
     uint32_t xm;
     int rc = schema_check(schema, &nw, &xm);
     if (rc) return rc;
+    if (rows > 1 && (schema->key_size & 3u)) return STAGE_ERR_ARG;   // scan inboxes feed the plan kernels directly
     CUDA_TRY(cudaSetDevice(g_device));
     auto *x = new stage_exchange();
     x->schema = *schema;
@@ -1698,9 +1702,14 @@ extern "C" int stage_gpu_exchange_create(uint32_t world, uint32_t rank, uint64_t
     l.off_keys = off;    off = align_up(off + (uint64_t) world * capacity * l.kpad, 256);
     l.off_req = off;     off = align_up(off + (uint64_t) world * capacity * 4, 256);
     l.off_found = off;   off = align_up(off + capacity, 256);
-    l.off_ts = off;      off = align_up(off + capacity * 4, 256);
+    l.rows = rows;
+    const bool scans = rows > 1;
+    l.off_ts = off;      off = align_up(off + capacity * rows * 4, 256);
     l.pstride = (uint32_t) align_up(schema->payload_size, 128);
-    l.off_payload = off; off = align_up(off + capacity * (uint64_t) l.pstride + 256, 256);
+    l.off_payload = off; off = align_up(off + capacity * rows * (uint64_t) l.pstride + 256, 256);
+    l.off_sizes = off;   off = align_up(off + (scans ? (uint64_t) world * capacity * 4 : 0), 256);
+    l.off_counts = off;  off = align_up(off + (scans ? capacity * 4 : 0), 256);
+    l.off_keyout = off;  off = align_up(off + (scans ? capacity * rows * (uint64_t) l.kpad : 0), 256);
     l.bytes = off;
     x->view.world = world;
     x->view.rank = rank;
@@ -1709,8 +1718,12 @@ extern "C" int stage_gpu_exchange_create(uint32_t world, uint32_t rank, uint64_t
         cudaMalloc((void **) &x->d_local_cnt, 4 * kMaxExchangeRanks) != cudaSuccess ||
         cudaMemset(x->d_local_cnt, 0, 4 * kMaxExchangeRanks) != cudaSuccess ||
         cudaMalloc((void **) &x->d_err, 4) != cudaSuccess || cudaMemset(x->d_err, 0, 4) != cudaSuccess ||
-        cudaMalloc((void **) &x->d_src_row, (uint64_t) world * capacity * 4) != cudaSuccess ||
-        cudaMalloc((void **) &x->d_dst_slot, (uint64_t) world * capacity * 4) != cudaSuccess) {
+        cudaMalloc((void **) &x->d_src_row, (uint64_t) world * capacity * rows * 4) != cudaSuccess ||
+        cudaMalloc((void **) &x->d_dst_slot, (uint64_t) world * capacity * rows * 4) != cudaSuccess ||
+        (scans && (cudaMalloc((void **) &x->d_sc_counts, (uint64_t) world * capacity * 4) != cudaSuccess ||
+                   cudaMalloc((void **) &x->d_sc_ts, (uint64_t) world * capacity * rows * 4) != cudaSuccess ||
+                   cudaMalloc((void **) &x->d_sc_src, (uint64_t) world * capacity * rows * 4) != cudaSuccess ||
+                   cudaMalloc((void **) &x->d_sc_keys, (uint64_t) world * capacity * rows * l.kpad) != cudaSuccess))) {
         g_last_error = std::string("exchange allocation: ") + cudaGetErrorString(cudaGetLastError());
         return fail(STAGE_ERR_NOMEM);
     }
@@ -1721,6 +1734,16 @@ extern "C" int stage_gpu_exchange_create(uint32_t world, uint32_t rank, uint64_t
     x->attached = world == 1;
     *out = x;
     return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_create(uint32_t world, uint32_t rank, uint64_t capacity, const stage_schema_t *schema,
+                                         stage_exchange_t **out) {
+    return exchange_create(world, rank, capacity, 1, schema, out);
+}
+extern "C" int stage_gpu_exchange_create_scan(uint32_t world, uint32_t rank, uint64_t max_scans, uint32_t max_scan_size,
+                                              const stage_schema_t *schema, stage_exchange_t **out) {
+    if (max_scan_size < 2) max_scan_size = 2;                    // rows == 1 denotes the probe exchange
+    return exchange_create(world, rank, max_scans, max_scan_size, schema, out);
 }
 
 extern "C" int stage_gpu_exchange_ipc_handle(stage_exchange_t *x, void *handle_out) {
@@ -1762,8 +1785,8 @@ extern "C" int stage_gpu_exchange_attach_ptrs(stage_exchange_t *x, void *const *
 
 extern "C" void *stage_gpu_exchange_arena(stage_exchange_t *x) { return x ? x->arena : nullptr; }
 
-extern "C" int stage_gpu_exchange_post(stage_exchange_t *x, const void *splitters, const void *keys_dev, uint64_t n,
-                                       int flags, void *cuda_stream) {
+static int exchange_post(stage_exchange_t *x, const void *splitters, const void *keys_dev, const uint32_t *sizes_dev,
+                         uint64_t n, int flags, void *cuda_stream) {
     if (!x || (n && !keys_dev) || (x->view.world > 1 && !splitters) || n > x->view.lay.cap) return STAGE_ERR_ARG;
     if (!x->attached) return STAGE_ERR_STATE;
     CUDA_TRY(cudaSetDevice(x->device));
@@ -1781,10 +1804,10 @@ extern "C" int stage_gpu_exchange_post(stage_exchange_t *x, const void *splitter
         const unsigned blocks = (unsigned) std::min<uint64_t>((n + 255) / 256, post_ctas > 0 ? (uint64_t) post_ctas : (uint64_t) sm_count() * 8);
         const uint8_t *k = static_cast<const uint8_t *>(keys_dev);
         switch (x->nw) {
-            case 1: exchange_post_kernel<1><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask); break;
-            case 2: exchange_post_kernel<2><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask); break;
-            case 4: exchange_post_kernel<4><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask); break;
-            default: exchange_post_kernel<8><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask); break;
+            case 1: exchange_post_kernel<1><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask, sizes_dev); break;
+            case 2: exchange_post_kernel<2><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask, sizes_dev); break;
+            case 4: exchange_post_kernel<4><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask, sizes_dev); break;
+            default: exchange_post_kernel<8><<<blocks, 256, 0, st>>>(x->view, sp, k, n, x->schema.key_size, x->xormask, sizes_dev); break;
         }
         LAUNCH_CHECK();
     }
@@ -1793,6 +1816,18 @@ extern "C" int stage_gpu_exchange_post(stage_exchange_t *x, const void *splitter
     LAUNCH_CHECK();
     XCHG_MARK(x, 1, st);
     return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_post(stage_exchange_t *x, const void *splitters, const void *keys_dev, uint64_t n,
+                                       int flags, void *cuda_stream) {
+    if (x && x->view.lay.rows != 1) return STAGE_ERR_STATE;
+    return exchange_post(x, splitters, keys_dev, nullptr, n, flags, cuda_stream);
+}
+extern "C" int stage_gpu_exchange_post_scans(stage_exchange_t *x, const void *splitters, const void *start_keys_dev,
+                                             const uint32_t *scan_sizes_dev, uint64_t n, int flags, void *cuda_stream) {
+    if (x && x->view.lay.rows == 1) return STAGE_ERR_STATE;
+    if (n && !scan_sizes_dev) return STAGE_ERR_ARG;
+    return exchange_post(x, splitters, start_keys_dev, scan_sizes_dev, n, flags, cuda_stream);
 }
 
 template <int NW>
@@ -1824,32 +1859,9 @@ static int launch_exchange_gather(stage_exchange *x, stage_snapshot *s, const Se
     return STAGE_OK;
 }
 
-extern "C" int stage_gpu_exchange_serve(stage_exchange_t *x, stage_snapshot_t *s, uint32_t read_ts, int flags,
-                                        void *cuda_stream) {
-    if (!x || !s) return STAGE_ERR_ARG;
-    if (!x->attached || !s->sealed) return STAGE_ERR_STATE;
-    if (s->schema.key_size != x->schema.key_size || s->schema.payload_size != x->schema.payload_size || s->nw != x->nw ||
-        s->device != x->device)
-        return STAGE_ERR_ARG;
-    CUDA_TRY(cudaSetDevice(x->device));
-    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
-    ServeArgs a{};
-    a.read_ts = read_ts;
-    a.epoch = ++x->epoch_serve;
-    a.device_sync = flags & STAGE_XCHG_DEVICE_SYNC ? 1 : 0;
-    a.src_row = x->d_src_row;
-    a.dst_slot = x->d_dst_slot;
-    static const int order = getenv("STAGE_XCHG_ORDER") ? atoi(getenv("STAGE_XCHG_ORDER")) : 1;   // shift schedule (exchange.cuh)
-    a.tile_order = order;
-    int rc;
-    switch (x->nw) {
-        case 1: rc = launch_serve<1>(x, s, a, st); break;
-        case 2: rc = launch_serve<2>(x, s, a, st); break;
-        case 4: rc = launch_serve<4>(x, s, a, st); break;
-        default: rc = launch_serve<8>(x, s, a, st); break;
-    }
-    if (rc) return rc;
-    XCHG_MARK(x, 2, st);
+// payload rows of the planned (source row, destination slot) lists -> the requesters' slabs
+static int exchange_move_rows(stage_exchange *x, stage_snapshot *s, const ServeArgs &a, cudaStream_t st) {
+    int rc = STAGE_OK;
     // vector width: every arena and the payload offset are 256-byte aligned, so the row stride decides
     const uintptr_t align = (uintptr_t) s->d_payload | (uintptr_t) s->d_ver_payload | s->schema.payload_size;
     static const bool no16 = getenv("STAGE_XCHG_NO16") != nullptr;
@@ -1868,12 +1880,126 @@ extern "C" int stage_gpu_exchange_serve(stage_exchange_t *x, stage_snapshot_t *s
     else if ((align & 7) == 0) rc = launch_exchange_gather<uint2>(x, s, a, st);
     else if ((align & 3) == 0) rc = launch_exchange_gather<uint32_t>(x, s, a, st);
     else rc = launch_exchange_gather<uint8_t>(x, s, a, st);
+    return rc;
+}
+
+extern "C" int stage_gpu_exchange_serve(stage_exchange_t *x, stage_snapshot_t *s, uint32_t read_ts, int flags,
+                                        void *cuda_stream) {
+    if (!x || !s) return STAGE_ERR_ARG;
+    if (!x->attached || !s->sealed) return STAGE_ERR_STATE;
+    if (s->schema.key_size != x->schema.key_size || s->schema.payload_size != x->schema.payload_size || s->nw != x->nw ||
+        s->device != x->device)
+        return STAGE_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(x->device));
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    ServeArgs a{};
+    a.read_ts = read_ts;
+    a.epoch = ++x->epoch_serve;
+    a.device_sync = flags & STAGE_XCHG_DEVICE_SYNC ? 1 : 0;
+    a.src_row = x->d_src_row;
+    a.dst_slot = x->d_dst_slot;
+    a.seg_mul = 1;
+    if (x->view.lay.rows != 1) return STAGE_ERR_STATE;
+    static const int order = getenv("STAGE_XCHG_ORDER") ? atoi(getenv("STAGE_XCHG_ORDER")) : 1;   // shift schedule (exchange.cuh)
+    a.tile_order = order;
+    int rc;
+    switch (x->nw) {
+        case 1: rc = launch_serve<1>(x, s, a, st); break;
+        case 2: rc = launch_serve<2>(x, s, a, st); break;
+        case 4: rc = launch_serve<4>(x, s, a, st); break;
+        default: rc = launch_serve<8>(x, s, a, st); break;
+    }
+    if (rc) return rc;
+    XCHG_MARK(x, 2, st);
+    rc = exchange_move_rows(x, s, a, st);
     if (rc) return rc;
     if (a.device_sync) {
         exchange_serve_finish_kernel<<<1, 32, 0, st>>>(x->view, a.epoch);
         LAUNCH_CHECK();
     }
     XCHG_MARK(x, 3, st);
+    return STAGE_OK;
+}
+
+// Scans posted with stage_gpu_exchange_post_scans: plan every source rank's inbox with the ordinary scan plan
+// kernels, deliver counts / keys / commit ids, then move the payload rows with the same kernels as the probes.
+extern "C" int stage_gpu_exchange_serve_scans(stage_exchange_t *x, stage_snapshot_t *s, uint32_t read_ts,
+                                              int apply_visibility, int flags, void *cuda_stream) {
+    if (!x || !s) return STAGE_ERR_ARG;
+    if (!x->attached || !s->sealed || x->view.lay.rows == 1) return STAGE_ERR_STATE;
+    if (s->schema.key_size != x->schema.key_size || s->schema.payload_size != x->schema.payload_size || s->nw != x->nw ||
+        s->device != x->device)
+        return STAGE_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(x->device));
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    const ExchangeLayout &l = x->view.lay;
+    ServeArgs a{};
+    a.read_ts = read_ts;
+    a.epoch = ++x->epoch_serve;
+    a.device_sync = flags & STAGE_XCHG_DEVICE_SYNC ? 1 : 0;
+    a.src_row = x->d_src_row;
+    a.dst_slot = x->d_dst_slot;
+    a.seg_mul = l.rows;
+    a.tile_order = 1;
+    if (a.device_sync) {
+        exchange_wait_posted_kernel<<<1, 32, 0, st>>>(x->view, a.epoch);
+        LAUNCH_CHECK();
+    }
+    int rc = STAGE_OK;
+    for (uint32_t src = 0; src < x->view.world && !rc; ++src) {
+        const uint64_t slot0 = (uint64_t) src * l.cap;
+        ScanArgs sa{};
+        sa.start_keys = x->arena + l.off_keys + slot0 * l.kpad;
+        sa.scan_sizes = reinterpret_cast<const uint32_t *>(x->arena + l.off_sizes) + slot0;
+        sa.n = l.cap;
+        sa.n_dev = reinterpret_cast<const uint32_t *>(x->arena + l.off_count) + src;
+        sa.out_stride = l.rows;
+        sa.read_ts = read_ts;
+        sa.apply_visibility = apply_visibility;
+        sa.row_counts = x->d_sc_counts + slot0;
+        sa.key_out = x->d_sc_keys + slot0 * l.rows * l.kpad;
+        sa.ts_out = x->d_sc_ts + slot0 * l.rows;
+        sa.src_row = x->d_sc_src + slot0 * l.rows;
+        switch (x->nw) {
+            case 1: rc = launch_scan<1>(s, sa, st); break;
+            case 2: rc = launch_scan<2>(s, sa, st); break;
+            case 4: rc = launch_scan<4>(s, sa, st); break;
+            default: rc = launch_scan<8>(s, sa, st); break;
+        }
+    }
+    if (rc) return rc;
+    ScanDeliverArgs d{};
+    d.row_counts = x->d_sc_counts;
+    d.keys = x->d_sc_keys;
+    d.ts = x->d_sc_ts;
+    d.src_row = x->d_sc_src;
+    d.src_row_c = x->d_src_row;
+    d.dst_slot_c = x->d_dst_slot;
+    d.key_size = x->schema.key_size;
+    exchange_scan_deliver_kernel<<<sm_count() * 8, 256, 0, st>>>(x->view, d);
+    LAUNCH_CHECK();
+    XCHG_MARK(x, 2, st);
+    if ((rc = exchange_move_rows(x, s, a, st))) return rc;
+    if (a.device_sync) {
+        exchange_serve_finish_kernel<<<1, 32, 0, st>>>(x->view, a.epoch);
+        LAUNCH_CHECK();
+    }
+    XCHG_MARK(x, 3, st);
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_scan_results(stage_exchange_t *x, void **row_counts, void **key_out, void **ts,
+                                               void **payload, uint32_t *rows_per_scan, uint32_t *key_stride,
+                                               uint32_t *payload_stride) {
+    if (!x) return STAGE_ERR_ARG;
+    if (x->view.lay.rows == 1) return STAGE_ERR_STATE;
+    if (rows_per_scan) *rows_per_scan = x->view.lay.rows;
+    if (key_stride) *key_stride = x->view.lay.kpad;
+    if (payload_stride) *payload_stride = x->view.lay.pstride;
+    if (row_counts) *row_counts = x->arena + x->view.lay.off_counts;
+    if (key_out) *key_out = x->arena + x->view.lay.off_keyout;
+    if (ts) *ts = x->arena + x->view.lay.off_ts;
+    if (payload) *payload = x->arena + x->view.lay.off_payload;
     return STAGE_OK;
 }
 
@@ -1929,7 +2055,8 @@ extern "C" int stage_gpu_exchange_destroy(stage_exchange_t *x) {
         if (x->tev[i]) cudaEventDestroy(x->tev[i]);
     for (uint32_t r = 0; r < x->view.world; ++r)
         if (x->opened[r] && x->view.arena[r]) cudaIpcCloseMemHandle(x->view.arena[r]);
-    void *ptrs[] = {x->arena, x->d_local_cnt, x->d_err, x->d_src_row, x->d_dst_slot};
+    void *ptrs[] = {x->arena, x->d_local_cnt, x->d_err, x->d_src_row, x->d_dst_slot,
+                    x->d_sc_counts, x->d_sc_ts, x->d_sc_src, x->d_sc_keys};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     delete x;

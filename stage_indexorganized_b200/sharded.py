@@ -106,13 +106,14 @@ class PeerProbe:
     arrive in request order. torch.distributed only carries the control plane (the one-time all-gather of the CUDA
     IPC handles, and — without device_sync — two stream-ordered barriers per batch)."""
 
-    def __init__(self, shard, splitters, capacity, device_sync=True, group=None):
+    def __init__(self, shard, splitters, capacity, device_sync=True, group=None, max_scan_size=0):
         import stage_indexorganized_b200 as sg
         self.sg, self.shard, self.group = sg, shard, group
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.splitters = splitters
         self.flags = sg.XCHG_DEVICE_SYNC if device_sync else 0
-        self.x = sg.ProbeExchange(self.world, self.rank, capacity, shard.schema.key_size, shard.schema.payload_size)
+        self.x = sg.ProbeExchange(self.world, self.rank, capacity, shard.schema.key_size, shard.schema.payload_size,
+                                  max_scan_size=max_scan_size)
         handles = [None] * self.world
         dist.all_gather_object(handles, self.x.ipc_handle(), group=group)
         if self.world > 1:
@@ -140,3 +141,24 @@ class PeerProbe:
         torch.cuda.synchronize()
         dist.barrier(self.group)     # nobody unmaps an arena a peer may still be writing
         self.x.close()
+
+
+class PeerScan(PeerProbe):
+    """Routed range scans over the same arenas: each scan runs on the owner of its start key (whose shard carries a
+    halo of its right neighbour's first rows) and its rows are written into this rank's slab in request order."""
+
+    def __init__(self, shard, splitters, max_scans, max_scan_size, device_sync=True, group=None):
+        super().__init__(shard, splitters, max_scans, device_sync, group, max_scan_size=max(2, max_scan_size))
+
+    def scan(self, start_keys_dev, scan_sizes_dev, n, read_ts, apply_visibility=True):
+        """Returns (row_counts[n], keys[n,R,K], ts[n,R], payload[n,R,P]) views of this rank's result slab."""
+        st = torch.cuda.current_stream().cuda_stream
+        self.x.post_scans(self.splitters, start_keys_dev, scan_sizes_dev, n, self.flags, st)
+        if not self.flags:
+            self._barrier()
+        self.x.serve_scans(self.shard, read_ts, apply_visibility, self.flags, st)
+        if self.flags:
+            self.x.wait(st)
+        else:
+            self._barrier()
+        return self.x.scan_results_torch(n)

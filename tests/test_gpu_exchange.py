@@ -120,3 +120,102 @@ def test_exchange_overflow_is_reported():
                 x.post(None, keys, 200)          # n > capacity is refused on the host
         finally:
             x.close()
+
+
+# ---- routed scans ------------------------------------------------------------------------------------------
+def _scan_full(full, keys, sizes, S, read_ts, vis, K, P):
+    n = len(keys)
+    dk = torch.from_numpy(np.ascontiguousarray(keys)).cuda()
+    ds = torch.from_numpy(np.ascontiguousarray(sizes, np.uint32).view(np.int32)).cuda()
+    cnt = torch.zeros(n, dtype=torch.int32, device="cuda")
+    ko = torch.zeros((n, S, K), dtype=torch.uint8, device="cuda")
+    to = torch.zeros((n, S), dtype=torch.int32, device="cuda")
+    po = torch.zeros((n, S, P), dtype=torch.uint8, device="cuda")
+    full.scan_device(dk, ds, n, S, read_ts, vis, cnt, ko, to, po)
+    torch.cuda.synchronize()
+    return cnt.cpu().numpy(), ko.cpu().numpy(), to.cpu().numpy(), po.cpu().numpy()
+
+
+@pytest.mark.parametrize("world,S", [(1, 100), (2, 100), (3, 100), (8, 100), (2, 1000), (8, 10)])
+@pytest.mark.parametrize("flags", [0, sg.XCHG_DEVICE_SYNC])
+def test_routed_scans_match_unsharded_table(world, S, flags):
+    """Scans posted to the owner of their start key, planned there (shard + halo of its right neighbour) and written
+    into the requester's slab == the same scans on the unsharded table (same leaf boundaries: the shard starts are
+    multiples of the leaf fill), with version chains on both sides."""
+    RPL, P, K = 61, 200, 4
+    N = RPL * 720
+    halo = 2 * S + 128
+    sg.init(0)
+    bounds = sharded.shard_bounds(N, world)
+    assert all(lo % RPL == 0 for lo, _ in bounds)
+    split = sharded.ycsb_splitters(N, world) if world > 1 else None
+    full = sg.Snapshot.generate_ycsb(N, P, rows_per_leaf=RPL)
+    shards = [sg.Snapshot.generate_ycsb(N, P, rows_per_leaf=RPL, first_rank=lo, n_local=min(hi + halo, N) - lo)
+              for lo, hi in bounds]
+    xs = []
+    try:
+        rng = np.random.default_rng(100 * world + S)
+        nu = 6000
+        ukeys = rank_to_key(N, rng.integers(0, N, nu)).astype(np.uint32).view(np.uint8).reshape(-1, 4)
+        patches = rng.integers(0, 256, (nu, 16), dtype=np.uint8)
+        cids = np.arange(10, 10 + nu, dtype=np.uint32)
+        assert full.apply_updates(ukeys, patches, cids, patch_off=8) == nu
+        for s in shards:
+            s.apply_updates(ukeys, patches, cids, patch_off=8)
+        read_ts = 10 + nu // 2
+        nscan = [300 + 7 * r for r in range(world)]
+        batches = [u32_keys(rng.integers(0, N + 40, m)) for m in nscan]
+        sizes = [rng.integers(0, S + 1, m).astype(np.uint32) for m in nscan]
+        for sz in sizes:
+            sz[:3] = (S, 1, 0)
+        cap = max(nscan)
+        xs = [sg.ProbeExchange(world, r, cap, K, P, max_scan_size=S) for r in range(world)]
+        arenas = [x.arena() for x in xs]
+        for x in xs:
+            x.attach_ptrs(arenas)
+        dk = [torch.from_numpy(np.ascontiguousarray(b)).cuda() for b in batches]
+        dsz = [torch.from_numpy(z.view(np.int32)).cuda() for z in sizes]
+        for vis in (True, False):
+            for r in range(world):
+                xs[r].post_scans(split, dk[r], dsz[r], nscan[r], flags)
+            for r in range(world):
+                xs[r].serve_scans(shards[r], read_ts, vis, flags)
+            for r in range(world):
+                if flags:
+                    xs[r].wait()
+            torch.cuda.synchronize()
+            for r in range(world):
+                assert xs[r].error() == 0
+                cnt, ko, to, po = (t.cpu().numpy() for t in xs[r].scan_results_torch(nscan[r]))
+                wc, wk, wt, wp = _scan_full(full, batches[r], sizes[r], S, read_ts, vis, K, P)
+                assert np.array_equal(cnt, wc), f"rank {r} counts (vis={vis})"
+                if vis:
+                    assert (cnt < sizes[r]).any()          # the filter drops rows somewhere
+                m = np.arange(S)[None, :] < wc[:, None]
+                assert np.array_equal(ko[m], wk[m]), f"rank {r} keys"
+                assert np.array_equal(to[m], wt[m]), f"rank {r} ts"
+                assert np.array_equal(po[m], wp[m]), f"rank {r} payload"
+    finally:
+        for x in xs:
+            x.close()
+        for s in shards:
+            s.close()
+        full.close()
+
+
+def test_scan_exchange_argument_errors():
+    sg.init(0)
+    with pytest.raises(sg.StageError):
+        sg.ProbeExchange(1, 0, 16, 6, 64, max_scan_size=10)      # key size not a multiple of 4
+    x = sg.ProbeExchange(1, 0, 16, 4, 64)
+    s = sg.Snapshot.generate_ycsb(1000, 64)
+    try:
+        k = torch.zeros((4, 4), dtype=torch.uint8, device="cuda")
+        z = torch.ones(4, dtype=torch.int32, device="cuda")
+        with pytest.raises(sg.StageError):
+            x.post_scans(None, k, z, 4)                          # probe exchange does not take scans
+        with pytest.raises(sg.StageError):
+            x.serve_scans(s, 1)
+    finally:
+        x.close()
+        s.close()

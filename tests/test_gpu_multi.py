@@ -76,3 +76,60 @@ def test_peer_probe_multi_process():
     ret = mgr.dict()
     mp.spawn(_worker, args=(world, port, ret), nprocs=world, join=True)
     assert all(ret.get(r, False) for r in range(world)), dict(ret)
+
+
+def _scan_worker(rank, world, port, ret):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    import stage_indexorganized_b200 as sg
+    from stage_indexorganized_b200 import sharded
+    sg.init(rank)
+    RPL, S, n = 61, 200, 3000 + 10 * rank
+    N = RPL * 8 * 800                                   # shard starts fall on leaf boundaries for world <= 8
+    lo, hi = sharded.shard_bounds(N, world)[rank]
+    split = sharded.ycsb_splitters(N, world)
+    shard = sg.Snapshot.generate_ycsb(N, P, rows_per_leaf=RPL, first_rank=lo, n_local=min(hi + 2 * S + 128, N) - lo)
+    full = sg.Snapshot.generate_ycsb(N, P, rows_per_leaf=RPL)   # the unsharded table, as the expected answer
+    st = torch.cuda.current_stream().cuda_stream
+    shard.set_stream(st)
+    full.set_stream(st)
+    ok = lo % RPL == 0
+    rng = np.random.default_rng(90 + rank)
+    for device_sync in (False, True):
+        ps = sharded.PeerScan(shard, split, 4000, S, device_sync=device_sync)
+        for rep in range(2):
+            keys = torch.from_numpy(rng.integers(0, N + 100, n).astype(np.uint32).view(np.uint8).reshape(-1, 4).copy()).cuda()
+            sizes = torch.from_numpy(rng.integers(0, S + 1, n).astype(np.int32)).cuda()
+            cnt, ko, to, po = ps.scan(keys, sizes, n, 1)
+            torch.cuda.synchronize()
+            ok = ok and ps.x.error() == 0
+            wc = torch.zeros(n, dtype=torch.int32, device="cuda")
+            wk = torch.zeros((n, S, 4), dtype=torch.uint8, device="cuda")
+            wt = torch.zeros((n, S), dtype=torch.int32, device="cuda")
+            wp = torch.zeros((n, S, P), dtype=torch.uint8, device="cuda")
+            full.scan_device(keys, sizes, n, S, 1, True, wc, wk, wt, wp)
+            torch.cuda.synchronize()
+            m = torch.arange(S, device="cuda")[None, :] < wc[:, None]
+            ok = ok and bool(torch.equal(cnt, wc)) and bool(torch.equal(ko[m], wk[m]))
+            ok = ok and bool(torch.equal(to[m], wt[m])) and bool(torch.equal(po[m], wp[m]))
+        ps.close()
+    shard.close()
+    full.close()
+    ret[rank] = bool(ok)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_peer_scan_multi_process():
+    import torch.multiprocessing as mp
+    world = min(torch.cuda.device_count(), 8)
+    port = 31700 + (os.getpid() % 2000)
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_scan_worker, args=(world, port, ret), nprocs=world, join=True)
+    assert all(ret.get(r, False) for r in range(world)), dict(ret)

@@ -62,6 +62,8 @@ def parse_args():
     ap.add_argument("--rows", type=int, default=10_000_000, help="tuples per GPU at N = 1 (BASELINE configs[1])")
     ap.add_argument("--rows-multi", type=int, default=125_000_000,
                     help="tuples per GPU at N > 1 (BASELINE configs[4]: 1 B tuples over 8 GPUs)")
+    ap.add_argument("--routed-scans", type=int, default=1024,
+                    help="N > 1: scans per GPU per step of the routed-scan leg (start keys over the global table); 0 = skip")
     ap.add_argument("--a2a-steps", type=int, default=2, help="steps of the NCCL all-to-all comparison leg (N > 1)")
     ap.add_argument("--scans", type=int, default=4096, help="scans per step per GPU")
     ap.add_argument("--scan-size", type=int, default=1000)
@@ -609,6 +611,40 @@ def main():
             probe["nccl_all_to_all"] = {"value": args.a2a_steps * n_probes * world / (ams * 1e-3), "unit": "probes/s",
                                         "ms_per_step": ams / args.a2a_steps}
         pp.close()
+
+        # ---- routed scans: start keys anywhere in the global table, each scan planned on the owner of its start key
+        # (shard + halo), rows stored into the requester's slab over NVLink peer memory -------------------------
+        n_rs = args.routed_scans
+        if n_rs > 0:
+            rng2 = np.random.default_rng(3000 + rank)
+            rk_all = rank_to_key(rows * world, rng2.integers(0, rows * world, size=(n_batches, n_rs)))
+            d_rk = torch.from_numpy(rk_all.astype(np.uint32).view(np.uint8).reshape(n_batches, n_rs, K_BYTES)).to(dev)
+            d_rsz = torch.full((n_rs,), S, dtype=torch.int32, device=dev)
+            ps = sharded.PeerScan(snap, split, n_rs, S, device_sync=True)
+
+            def rscan(b):
+                c = ps.scan(d_rk[b], d_rsz, n_rs, read_ts)[0]
+                return (c,)
+
+            rms, rrows = timed(rscan, args.steps)
+            if ps.x.error() != 0:
+                raise SystemExit(f"scan exchange error {ps.x.error()} on rank {rank}")
+            ps.x.enable_timing(True)
+            phases = []
+            for i in range(args.steps):
+                ps.scan(d_rk[args.warmup + i], d_rsz, n_rs, read_ts)
+                phases.append(ps.x.last_timing())
+            ps.x.enable_timing(False)
+            rstep = rms * 1e-3 / args.steps
+            rows_step_gpu = rrows / args.steps / world
+            routed_scans = {"value": rrows / (rms * 1e-3), "unit": "rows/s", "ms_per_step": rms / args.steps,
+                            "scans_per_gpu_per_step": n_rs, "scan_size": S,
+                            "nvlink_achieved": rows_step_gpu * remote * (P_BYTES + K_BYTES + 4) / rstep / 1e9,
+                            "nvlink_peak": nvl_peak, "hbm_achieved": rows_step_gpu * ROW_ALGO_BYTES / rstep / 1e9,
+                            "phase_ms_rank0": dict(zip(("post", "plan_incl_wait_for_posts", "rows", "wait_for_owners"),
+                                                       [float(np.mean(c)) for c in zip(*phases)]))}
+            probe["routed_scans"] = routed_scans
+            ps.close()
 
     # ---- max over ranks, whole-job aggregate ----------------------------------------------------
     t_ms = torch.tensor([total_ms], dtype=torch.float64, device=dev)

@@ -95,6 +95,24 @@ int stage_gpu_init(int device);
  * chasing of BTree::TraverseToLeaf (src/vstore/b_tree.cpp:1804-1846) for all later reads. */
 int stage_gpu_snapshot_from_tree(const void *root, const stage_schema_t *schema, stage_snapshot_t **out);
 
+/* Structural refresh: a NEW snapshot of the same host tree after committed inserts, updates and
+ * deletes — including the leaf splits / consolidations they caused (src/vstore/b_tree.cpp:1558-1690) — at the cost
+ * of the leaves that changed. `old` must come from stage_gpu_snapshot_from_tree or a previous refresh of this tree
+ * (it carries every leaf's host address and a fingerprint of its header, record metadata and upper fence). Leaves
+ * found unchanged are carried over device-to-device; changed and new leaves are staged and run through the
+ * record-layout transform again; the previous version table is kept as a prefix and the chains of the changed
+ * leaves are appended. The host tree is the truth: device-only changes made to `old` with
+ * stage_gpu_snapshot_apply_updates survive only in leaves the host tree did not touch. `old` stays valid and
+ * unchanged (readers keep using it until the caller swaps and destroys it); both tables are resident meanwhile.
+ * The tree must be quiesced during the call, as for stage_gpu_snapshot_from_tree. */
+typedef struct {
+    uint64_t leaves_total, leaves_carried, leaves_transformed;
+    uint64_t rows, versions_added;
+    uint64_t host_bytes_staged;     /* leaf images + version rows that crossed PCIe */
+} stage_refresh_stats_t;
+int stage_gpu_snapshot_refresh_from_tree(stage_snapshot_t *old, const void *root, stage_snapshot_t **out,
+                                         stage_refresh_stats_t *stats /* may be NULL */);
+
 /* Streaming construction for callers that own the walk (same result as from_tree):
  *   begin -> add_versions* -> add_leaves* -> seal.
  * leaf_images[i] points at leaf_node_size bytes of an unmodified LeafNode, leaves in tree order.

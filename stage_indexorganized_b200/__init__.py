@@ -44,10 +44,16 @@ class SnapshotInfo(C.Structure):
                 ("key_words", _u32), ("n_levels", _u32), ("max_leaf_rows", _u32), ("device", _u32)]
 
 
+class RefreshStats(C.Structure):
+    _fields_ = [("leaves_total", _u64), ("leaves_carried", _u64), ("leaves_transformed", _u64), ("rows", _u64),
+                ("versions_added", _u64), ("host_bytes_staged", _u64)]
+
+
 # every symbol include/stage_gpu.h declares: (restype, argtypes)
 SYMBOLS = {
     "stage_gpu_init": (_i32, [_i32]),
     "stage_gpu_snapshot_from_tree": (_i32, [_vp, C.POINTER(Schema), C.POINTER(_vp)]),
+    "stage_gpu_snapshot_refresh_from_tree": (_i32, [_vp, _vp, C.POINTER(_vp), C.POINTER(RefreshStats)]),
     "stage_gpu_snapshot_begin": (_i32, [C.POINTER(Schema), _u64, _u64, C.POINTER(_vp)]),
     "stage_gpu_snapshot_add_versions": (_i32, [_vp, _vp, _vp, _u64]),
     "stage_gpu_snapshot_add_leaves": (_i32, [_vp, _vp, _vp, _vp, _vp, _u64]),
@@ -180,6 +186,13 @@ class Snapshot:
         h = _vp()
         _check(lib().stage_gpu_snapshot_from_tree(_vp(int(root)), C.byref(sc), C.byref(h)))
         return cls(h, sc)
+
+    def refresh_from_tree(self, root):
+        """New snapshot of the same host tree after committed inserts / updates / deletes (and the splits they
+        caused); unchanged leaves are carried over on the device. Returns (snapshot, RefreshStats); self stays valid."""
+        h, st = _vp(), RefreshStats()
+        _check(lib().stage_gpu_snapshot_refresh_from_tree(self.h, _vp(int(root)), C.byref(h), C.byref(st)))
+        return type(self)(h, self.schema), st
 
     @classmethod
     def generate_ycsb(cls, n_rows_total, payload_size=1000, rows_per_leaf=61, first_rank=0, n_local=None,

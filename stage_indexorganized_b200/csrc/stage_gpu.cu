@@ -123,6 +123,7 @@ struct stage_snapshot {
     std::vector<uint32_t> h_leaf_off;           // [n_leaves+1]
     std::vector<uint32_t> h_sep;                // sortable, n_leaves * nw
     std::vector<uint8_t> h_has_sep;
+    std::vector<uint64_t> h_leaf_addr, h_leaf_fp;   // from_tree / refresh_from_tree: host address and fingerprint per leaf
     std::vector<stage_version_t> h_versions;
     std::vector<uint8_t> h_ver_payload;
     uint32_t *d_phys = nullptr;                 // physical (leaf, slot) order -> row, built on first use
@@ -306,8 +307,10 @@ extern "C" int stage_gpu_snapshot_add_versions(stage_snapshot_t *s, const stage_
 }
 
 template <int NW>
-static int launch_transform(stage_snapshot *s, int buf, uint32_t n_chunk, uint64_t base_leaf, uint32_t maxcount) {
+static int launch_transform(stage_snapshot *s, int buf, uint32_t n_chunk, uint64_t base_leaf, uint32_t maxcount,
+                            const uint32_t *leaf_index = nullptr) {
     TransformArgs a{};
+    a.leaf_index = leaf_index;
     a.leaves = s->d_stage[buf];
     a.n_chunk_leaves = n_chunk;
     a.leaf_size = s->schema.leaf_node_size;
@@ -608,6 +611,88 @@ static int walk(const uint8_t *node, uint32_t key_size, WalkOut &w, int depth) {
     return STAGE_OK;
 }
 
+// Version chains of a host tree: RecordMetadata.next_ptr -> TupleHeader (version_store.h:28-46), slot = [key][payload].
+// Stages every header reachable from the chain heads once; indices are 1-based and start after `base` versions that
+// already exist on the device (structural refresh keeps the previous version table as a prefix).
+struct ChainStager {
+    std::unordered_map<uint64_t, uint32_t> seen;   // TupleHeader* -> 1-based version index
+    std::vector<stage_version_t> vers;
+    std::vector<uint64_t> vslot;                   // TupleHeader.tuple_slot_ of every staged version
+    std::vector<uint64_t> path;
+    uint32_t base = 0;
+    uint32_t add_chain(uint64_t head) {
+        path.clear();
+        uint32_t tail = 0;
+        const uint32_t first = base + (uint32_t) vers.size() + 1;
+        for (uint64_t cur = head; cur != 0 && cur != UINT64_MAX;) {
+            auto it = seen.find(cur);
+            if (it != seen.end()) { tail = it->second; break; }      // joins a chain already staged (or a cycle)
+            seen.emplace(cur, first + (uint32_t) path.size());
+            path.push_back(cur);
+            memcpy(&cur, reinterpret_cast<const uint8_t *>(cur) + kThNext, 8);
+        }
+        for (size_t k = 0; k < path.size(); ++k) {
+            const uint8_t *hd = reinterpret_cast<const uint8_t *>(path[k]);
+            stage_version_t ver{};
+            uint64_t slot;
+            memcpy(&ver.begin_id, hd + kThBegin, 4);
+            memcpy(&ver.commit_id, hd + kThCommit, 4);
+            memcpy(&slot, hd + kThSlot, 8);
+            ver.next = k + 1 < path.size() ? first + (uint32_t) k + 1 : tail;
+            vers.push_back(ver);
+            vslot.push_back(slot);
+        }
+        return path.empty() ? tail : first;
+    }
+    // dense version rows of everything staged (malloc'd; nullptr when out of memory)
+    uint8_t *payload_rows(uint32_t K, uint32_t P) const {
+        const size_t V = vers.size();
+        uint8_t *vbuf = static_cast<uint8_t *>(malloc(std::max<size_t>(V, 1) * (size_t) P));
+        if (!vbuf) return nullptr;
+        auto work = [&](size_t lo, size_t hi) {
+            for (size_t i = lo; i < hi; ++i) {
+                if (vslot[i] != 0 && vslot[i] != UINT64_MAX) memcpy(vbuf + i * P, reinterpret_cast<const uint8_t *>(vslot[i]) + K, P);
+                else memset(vbuf + i * P, 0, P);
+            }
+        };
+        const unsigned T = V > 4096 ? staging_threads() : 1;
+        std::vector<std::thread> th;
+        for (unsigned t = 1; t < T; ++t) th.emplace_back(work, V * t / T, V * (t + 1) / T);
+        work(0, V / T);
+        for (auto &x : th) x.join();
+        return vbuf;
+    }
+};
+
+// Change detector of the structural refresh: a leaf whose header (sizes, sorted count, status word), record
+// metadata array (visibility, offsets, commit ids, chain heads) and upper fence hash to the same value at the same
+// address holds the same rows as in the previous snapshot (every committed insert, update and delete rewrites a
+// metadata word: b_tree.cpp:863-898 insert, transaction_manager.cpp:600-766 commit install).
+static uint64_t mix64(uint64_t h, uint64_t v) {
+    h ^= v + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2);
+    h *= 0xFF51AFD7ED558CCDull;
+    return h ^ (h >> 32);
+}
+static uint64_t leaf_fingerprint(const uint8_t *leaf, const uint8_t *fence, uint32_t K, uint32_t leaf_size) {
+    uint64_t status;
+    memcpy(&status, leaf + kOffStatus, 8);
+    const uint32_t count = status_record_count(status);
+    uint64_t h = 0x5354414745ull;
+    size_t end = (size_t) kOffMeta + (size_t) count * kMetaSize;
+    if (end > leaf_size) end = leaf_size;
+    for (size_t o = kOffIsLeaf; o + 8 <= end; o += 8) {
+        uint64_t v;
+        memcpy(&v, leaf + o, 8);
+        h = mix64(h, v);
+    }
+    if (fence) {
+        for (uint32_t b = 0; b < K; ++b) h = mix64(h, fence[b] + 256ull * b);
+    } else {
+        h = mix64(h, 0xFEull << 32);
+    }
+    return h;
+}
+
 static double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -629,37 +714,11 @@ extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema
     if ((rc = stage_gpu_snapshot_begin(schema, w.leaves.size(), w.rows_upper, &s))) return rc;
     PHASE("alloc");
 
-    // version chains: RecordMetadata.next_ptr -> TupleHeader (version_store.h:28-46), slot = [key][payload]
     const uint32_t K = schema->key_size, P = schema->payload_size;
-    std::unordered_map<uint64_t, uint32_t> seen;   // TupleHeader* -> 1-based version index
+    ChainStager cs;
     std::vector<uint32_t> heads;
-    std::vector<stage_version_t> vers;
-    std::vector<uint64_t> vslot;                       // TupleHeader.tuple_slot_ of every staged version
-    std::vector<uint64_t> path;
-    auto add_chain = [&](uint64_t head) -> uint32_t {
-        path.clear();
-        uint32_t tail = 0;
-        const uint32_t first = (uint32_t) vers.size() + 1;
-        for (uint64_t cur = head; cur != 0 && cur != UINT64_MAX;) {
-            auto it = seen.find(cur);
-            if (it != seen.end()) { tail = it->second; break; }      // joins a chain already staged (or a cycle)
-            seen.emplace(cur, first + (uint32_t) path.size());
-            path.push_back(cur);
-            memcpy(&cur, reinterpret_cast<const uint8_t *>(cur) + kThNext, 8);
-        }
-        for (size_t k = 0; k < path.size(); ++k) {
-            const uint8_t *hd = reinterpret_cast<const uint8_t *>(path[k]);
-            stage_version_t ver{};
-            uint64_t slot;
-            memcpy(&ver.begin_id, hd + kThBegin, 4);
-            memcpy(&ver.commit_id, hd + kThCommit, 4);
-            memcpy(&slot, hd + kThSlot, 8);
-            ver.next = k + 1 < path.size() ? first + (uint32_t) k + 1 : tail;
-            vers.push_back(ver);
-            vslot.push_back(slot);
-        }
-        return path.empty() ? tail : first;
-    };
+    std::vector<stage_version_t> &vers = cs.vers;
+    std::vector<uint64_t> &vslot = cs.vslot;
     // pass 1 (serial, metadata only): version indices in leaf / slot order
     std::vector<uint32_t> heads_flat;                 // chain heads of the leaves that have any
     std::vector<int64_t> heads_at(w.leaves.size(), -1);
@@ -676,7 +735,7 @@ extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema
             memcpy(&m, leaf + kOffMeta + (size_t) i * kMetaSize, 8);
             memcpy(&nx, leaf + kOffMeta + (size_t) i * kMetaSize + kMetaNextPtr, 8);
             if (!meta_visible(m) || nx == 0 || nx == UINT64_MAX) continue;
-            heads[i] = add_chain(nx);
+            heads[i] = cs.add_chain(nx);
             any = true;
         }
         if (any) {
@@ -695,23 +754,19 @@ extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema
     PHASE("stage + transform");
     if (!rc && !vers.empty()) {
         // retired rows [key][payload] -> dense version rows, copied by the staging threads
-        const size_t V = vers.size();
-        uint8_t *vbuf = static_cast<uint8_t *>(malloc(V * (size_t) P));
+        uint8_t *vbuf = cs.payload_rows(K, P);
         if (!vbuf) rc = STAGE_ERR_NOMEM;
         else {
-            auto work = [&](size_t lo, size_t hi) {
-                for (size_t i = lo; i < hi; ++i) {
-                    if (vslot[i] != 0 && vslot[i] != UINT64_MAX) memcpy(vbuf + i * P, reinterpret_cast<const uint8_t *>(vslot[i]) + K, P);
-                    else memset(vbuf + i * P, 0, P);
-                }
-            };
-            const unsigned T = V > 4096 ? staging_threads() : 1;
-            std::vector<std::thread> th;
-            for (unsigned t = 1; t < T; ++t) th.emplace_back(work, V * t / T, V * (t + 1) / T);
-            work(0, V / T);
-            for (auto &x : th) x.join();
             s->h_versions = std::move(vers);
             s->ext_ver_payload = vbuf;
+        }
+    }
+    if (!rc) {       // fingerprints for a later stage_gpu_snapshot_refresh_from_tree
+        s->h_leaf_addr.resize(w.leaves.size());
+        s->h_leaf_fp.resize(w.leaves.size());
+        for (size_t li = 0; li < w.leaves.size(); ++li) {
+            s->h_leaf_addr[li] = (uint64_t) (uintptr_t) w.leaves[li];
+            s->h_leaf_fp[li] = leaf_fingerprint(w.leaves[li], w.fences[li], K, schema->leaf_node_size);
         }
     }
     PHASE("version rows");
@@ -721,6 +776,242 @@ extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema
     if (rc) {
         snapshot_free(s);
         return rc;
+    }
+    *out = s;
+    return STAGE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// structural refresh: a new snapshot of the same host tree after committed inserts, updates,
+// deletes and the leaf splits they caused. Unchanged leaves (same address, same fingerprint) are carried over on
+// the device; only changed and new leaves cross PCIe and go through the transform kernel again.
+// ------------------------------------------------------------------------------------------------
+extern "C" int stage_gpu_snapshot_refresh_from_tree(stage_snapshot_t *old, const void *root, stage_snapshot_t **out,
+                                                    stage_refresh_stats_t *stats) {
+    if (!old || !root || !out) return STAGE_ERR_ARG;
+    if (!old->sealed || old->h_leaf_addr.size() != old->n_leaves || old->h_leaf_off.size() != old->n_leaves + 1)
+        return STAGE_ERR_STATE;                       // only snapshots that came from a host tree carry fingerprints
+    std::lock_guard<std::mutex> lock(old->mu);
+    const stage_schema_t *schema = &old->schema;
+    const uint32_t K = schema->key_size, P = schema->payload_size, ls = schema->leaf_node_size;
+    WalkOut w;
+    int rc;
+    if ((rc = walk(static_cast<const uint8_t *>(root), K, w, 0))) return rc;
+    const size_t L = w.leaves.size();
+    if (L >= kNoLeaf) return STAGE_ERR_ARG;
+
+    // 1. classify: carried over or re-transformed; row offsets of the new snapshot
+    std::unordered_map<uint64_t, uint32_t> old_at;
+    old_at.reserve(old->n_leaves * 2);
+    for (uint64_t i = 0; i < old->n_leaves; ++i) old_at.emplace(old->h_leaf_addr[i], (uint32_t) i);
+    std::vector<uint32_t> src_leaf(L, kNoLeaf), vis(L, 0), changed;
+    std::vector<uint64_t> fp(L);
+    {
+        auto work = [&](size_t lo, size_t hi) {
+            for (size_t j = lo; j < hi; ++j) {
+                const uint8_t *leaf = w.leaves[j];
+                fp[j] = leaf_fingerprint(leaf, w.fences[j], K, ls);
+                auto it = old_at.find((uint64_t) (uintptr_t) leaf);
+                if (it != old_at.end() && old->h_leaf_fp[it->second] == fp[j]) {
+                    src_leaf[j] = it->second;
+                    vis[j] = old->h_leaf_off[it->second + 1] - old->h_leaf_off[it->second];
+                    continue;
+                }
+                uint64_t status;
+                memcpy(&status, leaf + kOffStatus, 8);
+                const uint32_t count = status_record_count(status);
+                uint32_t v = 0;
+                if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize <= ls)
+                    for (uint32_t i = 0; i < count; ++i) {
+                        uint64_t m;
+                        memcpy(&m, leaf + kOffMeta + (size_t) i * kMetaSize, 8);
+                        v += meta_visible(m) ? 1u : 0u;
+                    }
+                vis[j] = v;
+            }
+        };
+        const unsigned T = L > 1024 ? staging_threads() : 1;
+        std::vector<std::thread> th;
+        for (unsigned t = 1; t < T; ++t) th.emplace_back(work, L * t / T, L * (t + 1) / T);
+        work(0, L / T);
+        for (auto &x : th) x.join();
+    }
+    uint64_t n_rows = 0;
+    for (size_t j = 0; j < L; ++j) {
+        n_rows += vis[j];
+        if (src_leaf[j] == kNoLeaf) changed.push_back((uint32_t) j);
+    }
+
+    stage_snapshot *s = nullptr;
+    if ((rc = stage_gpu_snapshot_begin(schema, L, n_rows, &s))) return rc;
+    auto fail = [&](int code) { snapshot_free(s); return code; };
+    s->h_leaf_off.resize(L + 1);
+    s->h_sep.assign(L * s->nw, 0xFFFFFFFFu);
+    s->h_has_sep.resize(L);
+    s->h_leaf_addr.resize(L);
+    s->h_leaf_fp = fp;
+    for (size_t j = 0; j < L; ++j) {
+        s->h_leaf_off[j + 1] = s->h_leaf_off[j] + vis[j];
+        if (w.fences[j]) host_sortable_nw(s->nw, w.fences[j], K, s->xormask, s->h_sep.data() + j * s->nw);
+        s->h_has_sep[j] = w.fences[j] ? 1 : 0;
+        s->h_leaf_addr[j] = (uint64_t) (uintptr_t) w.leaves[j];
+        s->max_leaf_rows = std::max(s->max_leaf_rows, vis[j]);
+    }
+    s->n_leaves = L;
+    s->rows_staged = n_rows;
+    cudaStream_t st = s->stream;
+#define RF_TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { g_last_error = cudaGetErrorString(e_); return fail(STAGE_ERR_CUDA); } } while (0)
+    RF_TRY(cudaMemcpyAsync(s->d_leaf_off, s->h_leaf_off.data(), (L + 1) * 4, cudaMemcpyHostToDevice, st));
+    RF_TRY(cudaMemcpyAsync(s->d_sep, s->h_sep.data(), L * s->nw * 4, cudaMemcpyHostToDevice, st));
+    RF_TRY(cudaMemcpyAsync(s->d_has_sep, s->h_has_sep.data(), L, cudaMemcpyHostToDevice, st));
+
+    // 2. carried-over leaves: old columns -> new columns, on the device
+    uint32_t *d_src_leaf = nullptr, *d_changed = nullptr;
+    RF_TRY(cudaMalloc((void **) &d_src_leaf, std::max<size_t>(L, 1) * 4));
+    RF_TRY(cudaMemcpyAsync(d_src_leaf, src_leaf.data(), L * 4, cudaMemcpyHostToDevice, st));
+    RF_TRY(cudaStreamSynchronize(old->stream));      // the previous snapshot's columns are final (refresh kernels done)
+    if (L > changed.size()) {
+        LeafCarryArgs c{};
+        c.src_leaf = d_src_leaf; c.n_leaves = (uint32_t) L;
+        c.old_off = old->d_leaf_off; c.new_off = s->d_leaf_off;
+        c.old_skey = old->d_skey; c.new_skey = s->d_skey;
+        c.old_slot = old->d_slot; c.new_slot = s->d_slot;
+        c.old_ts = old->d_ts; c.new_ts = s->d_ts;
+        c.old_chain = old->d_chain; c.new_chain = s->d_chain;
+        c.old_payload = old->d_payload; c.new_payload = s->d_payload;
+        c.old_cont = old->d_cont; c.new_cont = s->d_cont;
+        c.nw = (uint32_t) s->nw; c.payload_size = P;
+        leaf_carry_kernel<<<(unsigned) std::min<uint64_t>(L, (uint64_t) sm_count() * 8), 256, 0, st>>>(c);
+        if (cudaGetLastError() != cudaSuccess) { cudaFree(d_src_leaf); return fail(STAGE_ERR_CUDA); }
+        g_launches.fetch_add(1);
+    }
+
+    // 3. changed leaves: chains (new version indices follow the previous table), images, transform
+    ChainStager cs;
+    cs.base = (uint32_t) old->n_versions;
+    std::vector<uint32_t> heads_flat;
+    std::vector<int64_t> heads_at(changed.size(), -1);
+    std::vector<uint32_t> heads;
+    for (size_t c = 0; c < changed.size() && !rc; ++c) {
+        const uint8_t *leaf = w.leaves[changed[c]];
+        uint64_t status;
+        memcpy(&status, leaf + kOffStatus, 8);
+        const uint32_t count = status_record_count(status);
+        if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize > ls) { rc = STAGE_ERR_LAYOUT; break; }
+        heads.assign(count, 0);
+        bool any = false;
+        for (uint32_t i = 0; i < count; ++i) {
+            uint64_t m, nx;
+            memcpy(&m, leaf + kOffMeta + (size_t) i * kMetaSize, 8);
+            memcpy(&nx, leaf + kOffMeta + (size_t) i * kMetaSize + kMetaNextPtr, 8);
+            if (!meta_visible(m) || nx == 0 || nx == UINT64_MAX) continue;
+            heads[i] = cs.add_chain(nx);
+            any = true;
+        }
+        if (any) {
+            heads_at[c] = (int64_t) heads_flat.size();
+            heads_flat.insert(heads_flat.end(), heads.begin(), heads.end());
+        }
+    }
+    if (!rc && !changed.empty()) {
+        if (cudaMalloc((void **) &d_changed, changed.size() * 4) != cudaSuccess) rc = STAGE_ERR_NOMEM;
+        else if (cudaMemcpyAsync(d_changed, changed.data(), changed.size() * 4, cudaMemcpyHostToDevice, st) != cudaSuccess)
+            rc = STAGE_ERR_CUDA;
+    }
+    std::vector<uint32_t> cvis, ccnt;
+    std::vector<int> rcs;
+    bool used[2] = {false, false};
+    for (size_t c0 = 0; c0 < changed.size() && !rc; c0 += s->chunk_leaves) {
+        const uint32_t m = (uint32_t) std::min<size_t>(s->chunk_leaves, changed.size() - c0);
+        const int buf = s->stage_cur;
+        if (used[buf] && cudaEventSynchronize(s->stage_ev[buf]) != cudaSuccess) { rc = STAGE_ERR_CUDA; break; }
+        cvis.assign(m, 0); ccnt.assign(m, 0); rcs.assign(m, 0);
+        auto work = [&](uint32_t lo, uint32_t hi) {
+            for (uint32_t j = lo; j < hi; ++j) {
+                const size_t c = c0 + j;
+                rcs[j] = stage_copy_leaf(s, s->h_stage[buf] + (size_t) j * ls, w.leaves[changed[c]],
+                                         heads_at[c] >= 0 ? heads_flat.data() + heads_at[c] : nullptr, &cvis[j], &ccnt[j]);
+            }
+        };
+        const unsigned T = std::min<unsigned>(staging_threads(), std::max(1u, m / 16));
+        std::vector<std::thread> th;
+        for (unsigned t = 1; t < T; ++t) th.emplace_back(work, (uint32_t) ((uint64_t) m * t / T), (uint32_t) ((uint64_t) m * (t + 1) / T));
+        work(0, (uint32_t) ((uint64_t) m / T));
+        for (auto &x : th) x.join();
+        uint32_t maxcount = 0;
+        for (uint32_t j = 0; j < m && !rc; ++j) {
+            if (rcs[j]) rc = rcs[j];
+            else if (cvis[j] != vis[changed[c0 + j]]) rc = STAGE_ERR_NOT_QUIESCED;      // the tree moved under the walk
+            maxcount = std::max(maxcount, ccnt[j]);
+        }
+        if (rc) break;
+        if (cudaMemcpyAsync(s->d_stage[buf], s->h_stage[buf], (size_t) m * ls, cudaMemcpyHostToDevice, st) != cudaSuccess) { rc = STAGE_ERR_CUDA; break; }
+        switch (s->nw) {
+            case 1: rc = launch_transform<1>(s, buf, m, 0, maxcount, d_changed + c0); break;
+            case 2: rc = launch_transform<2>(s, buf, m, 0, maxcount, d_changed + c0); break;
+            case 4: rc = launch_transform<4>(s, buf, m, 0, maxcount, d_changed + c0); break;
+            default: rc = launch_transform<8>(s, buf, m, 0, maxcount, d_changed + c0); break;
+        }
+        if (rc) break;
+        if (cudaEventRecord(s->stage_ev[buf], st) != cudaSuccess) { rc = STAGE_ERR_CUDA; break; }
+        used[buf] = true;
+        s->stage_cur ^= 1;
+    }
+
+    // 4. version table: the previous one (device copy) followed by the chains of the changed leaves
+    const uint64_t V0 = old->n_versions, V1 = cs.vers.size(), V = V0 + V1;
+    uint8_t *vbuf = nullptr;
+    if (!rc && V) {
+        if ((rc = dev_alloc(s, &s->d_ver_begin, V)) || (rc = dev_alloc(s, &s->d_ver_commit, V)) ||
+            (rc = dev_alloc(s, &s->d_ver_next, V)) || (rc = dev_alloc(s, &s->d_ver_payload, V * (uint64_t) P))) {
+        } else {
+            s->ver_cap = V;
+            s->n_versions = V;
+            cudaError_t e = cudaSuccess;
+            if (V0) {
+                e = cudaMemcpyAsync(s->d_ver_begin, old->d_ver_begin, V0 * 4, cudaMemcpyDeviceToDevice, st);
+                if (e == cudaSuccess) e = cudaMemcpyAsync(s->d_ver_commit, old->d_ver_commit, V0 * 4, cudaMemcpyDeviceToDevice, st);
+                if (e == cudaSuccess) e = cudaMemcpyAsync(s->d_ver_next, old->d_ver_next, V0 * 4, cudaMemcpyDeviceToDevice, st);
+                if (e == cudaSuccess) e = cudaMemcpyAsync(s->d_ver_payload, old->d_ver_payload, V0 * (uint64_t) P, cudaMemcpyDeviceToDevice, st);
+            }
+            if (e == cudaSuccess && V1) {
+                std::vector<uint32_t> b(V1), c(V1), nx(V1);
+                for (uint64_t i = 0; i < V1; ++i) { b[i] = cs.vers[i].begin_id; c[i] = cs.vers[i].commit_id; nx[i] = cs.vers[i].next; }
+                vbuf = cs.payload_rows(K, P);
+                if (!vbuf) rc = STAGE_ERR_NOMEM;
+                else {
+                    e = cudaMemcpyAsync(s->d_ver_begin + V0, b.data(), V1 * 4, cudaMemcpyHostToDevice, st);
+                    if (e == cudaSuccess) e = cudaMemcpyAsync(s->d_ver_commit + V0, c.data(), V1 * 4, cudaMemcpyHostToDevice, st);
+                    if (e == cudaSuccess) e = cudaMemcpyAsync(s->d_ver_next + V0, nx.data(), V1 * 4, cudaMemcpyHostToDevice, st);
+                    if (e == cudaSuccess) e = cudaMemcpyAsync(s->d_ver_payload + V0 * (uint64_t) P, vbuf, V1 * (uint64_t) P, cudaMemcpyHostToDevice, st);
+                    if (e == cudaSuccess) e = cudaStreamSynchronize(st);     // b / c / nx / vbuf are pageable locals
+                }
+            }
+            if (e != cudaSuccess) { g_last_error = cudaGetErrorString(e); rc = STAGE_ERR_CUDA; }
+        }
+    }
+    free(vbuf);
+    if (!rc) {
+        s->n_rows = n_rows;
+        rc = finish_seal(s);
+    } else {
+        cudaStreamSynchronize(st);
+    }
+    cudaFree(d_src_leaf);
+    if (d_changed) cudaFree(d_changed);
+    for (int i = 0; i < 2; ++i) {
+        if (s->h_stage[i]) { cudaFreeHost(s->h_stage[i]); s->h_stage[i] = nullptr; }
+        if (s->d_stage[i]) { cudaFree(s->d_stage[i]); s->d_stage[i] = nullptr; }
+    }
+#undef RF_TRY
+    if (rc) return fail(rc);
+    if (stats) {
+        stats->leaves_total = L;
+        stats->leaves_carried = L - changed.size();
+        stats->leaves_transformed = changed.size();
+        stats->rows = n_rows;
+        stats->versions_added = V1;
+        stats->host_bytes_staged = (uint64_t) changed.size() * ls + V1 * (uint64_t) P;
     }
     *out = s;
     return STAGE_OK;

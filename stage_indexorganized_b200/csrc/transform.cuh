@@ -22,6 +22,8 @@ struct TransformArgs {
     uint32_t n_chunk_leaves;
     uint32_t leaf_size;
     uint64_t base_leaf;         // index of the chunk's first leaf in the snapshot
+    const uint32_t *leaf_index; // optional [n_chunk_leaves]: snapshot index of every staged leaf (scattered leaves:
+                                // structural refresh); base_leaf + j when null
     const uint32_t *leaf_off;   // [n_leaves+1] row offset of every leaf (device)
     const uint32_t *sep;        // [n_leaves] sortable upper fence of every leaf
     const uint8_t *has_sep;     // [n_leaves]
@@ -63,7 +65,7 @@ __global__ void __launch_bounds__(128) leaf_transform_kernel(TransformArgs a) {
 
     const uint32_t j = blockIdx.x;
     if (j >= a.n_chunk_leaves) return;
-    const uint64_t gj = a.base_leaf + j;
+    const uint64_t gj = a.leaf_index ? (uint64_t) a.leaf_index[j] : a.base_leaf + j;
     const uint8_t *leaf = a.leaves + (size_t) j * a.leaf_size;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
 
@@ -151,6 +153,52 @@ __global__ void __launch_bounds__(128) leaf_transform_kernel(TransformArgs a) {
         const uint8_t *src = leaf + meta_offset(m) + pad_key_len(meta_key_len(m));
         uint8_t *dst = a.payload + ((uint64_t) row0 + i) * P;
         warp_copy_bytes(src, dst, P, lane);
+    }
+}
+
+// Structural refresh: rows of the leaves that did not change since the previous snapshot are carried over on the
+// device (old columns -> new columns at the leaf's new row offset); only changed leaves are re-staged from the host.
+struct LeafCarryArgs {
+    const uint32_t *src_leaf;     // [n_leaves] leaf index in the previous snapshot, kNoLeaf = re-transformed
+    uint32_t n_leaves;
+    const uint32_t *old_off, *new_off;
+    const uint32_t *old_skey; uint32_t *new_skey;
+    const uint16_t *old_slot; uint16_t *new_slot;
+    const uint32_t *old_ts; uint32_t *new_ts;
+    const uint32_t *old_chain; uint32_t *new_chain;
+    const uint8_t *old_payload; uint8_t *new_payload;
+    const uint8_t *old_cont; uint8_t *new_cont;
+    uint32_t nw, payload_size;
+};
+constexpr uint32_t kNoLeaf = 0xFFFFFFFFu;
+
+template <typename V>
+__device__ __forceinline__ void cta_copy_vec(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, uint64_t nbytes) {
+    const V *s = reinterpret_cast<const V *>(src);
+    V *d = reinterpret_cast<V *>(dst);
+    const uint64_t n = nbytes / sizeof(V);
+    for (uint64_t i = threadIdx.x; i < n; i += blockDim.x) d[i] = s[i];
+}
+__device__ __forceinline__ void cta_copy_bytes(const uint8_t *src, uint8_t *dst, uint64_t nbytes) {
+    const uintptr_t a = (uintptr_t) src | (uintptr_t) dst | (uintptr_t) nbytes;
+    if ((a & 15) == 0) cta_copy_vec<uint4>(src, dst, nbytes);
+    else if ((a & 7) == 0) cta_copy_vec<uint2>(src, dst, nbytes);
+    else if ((a & 3) == 0) cta_copy_vec<uint32_t>(src, dst, nbytes);
+    else if ((a & 1) == 0) cta_copy_vec<uint16_t>(src, dst, nbytes);
+    else cta_copy_vec<uint8_t>(src, dst, nbytes);
+}
+
+__global__ void __launch_bounds__(256) leaf_carry_kernel(LeafCarryArgs a) {
+    for (uint32_t j = blockIdx.x; j < a.n_leaves; j += gridDim.x) {
+        const uint32_t o = a.src_leaf[j];
+        if (o == kNoLeaf) continue;
+        const uint64_t r0 = a.old_off[o], n = a.old_off[o + 1] - r0, d0 = a.new_off[j];
+        cta_copy_bytes(reinterpret_cast<const uint8_t *>(a.old_skey + r0 * a.nw), reinterpret_cast<uint8_t *>(a.new_skey + d0 * a.nw), n * a.nw * 4);
+        cta_copy_bytes(reinterpret_cast<const uint8_t *>(a.old_slot + r0), reinterpret_cast<uint8_t *>(a.new_slot + d0), n * 2);
+        cta_copy_bytes(reinterpret_cast<const uint8_t *>(a.old_ts + r0), reinterpret_cast<uint8_t *>(a.new_ts + d0), n * 4);
+        cta_copy_bytes(reinterpret_cast<const uint8_t *>(a.old_chain + r0), reinterpret_cast<uint8_t *>(a.new_chain + d0), n * 4);
+        cta_copy_bytes(a.old_payload + r0 * a.payload_size, a.new_payload + d0 * a.payload_size, n * a.payload_size);
+        if (threadIdx.x == 0) a.new_cont[j] = a.old_cont[o];
     }
 }
 

@@ -1,0 +1,119 @@
+"""GPU: structural refresh (stage_gpu_snapshot_refresh_from_tree) — after committed inserts (with leaf splits), updates
+and deletes on the host tree, the refreshed snapshot must answer exactly like the tree (and like a snapshot flattened
+from scratch), while only the leaves that changed are staged again (the rest is carried over on the device)."""
+import numpy as np
+import pytest
+
+import stage_indexorganized_b200 as sg
+from helpers import assert_probe_equal, assert_scan_equal, u32_keys, ycsb_int_table, random_table
+from oracle import pyoracle
+
+pytestmark = pytest.mark.gpu
+
+
+def checker_classes():
+    return [pyoracle.OracleTable] + ([pyoracle.RefTable] if pyoracle.have_ref() else [])
+
+
+def _check(snap, t, probes, starts, S, stamps, what):
+    for read_ts in stamps:
+        assert_probe_equal(snap.probe(probes, read_ts), t.probe(probes, read_ts), f"{what} probe ts={read_ts}")
+        for vis in (0, 1):
+            assert_scan_equal(snap.scan(starts, S, read_ts, vis), t.scan(starts, S, read_ts, vis),
+                              f"{what} scan ts={read_ts} vis={vis}")
+
+
+@pytest.mark.parametrize("cls", checker_classes(), ids=lambda c: c.__name__)
+def test_refresh_after_updates_inserts_deletes(cls):
+    N, P = 40000, 200
+    t = ycsb_int_table(cls, N, P)
+    rng = np.random.default_rng(31)
+    assert t.commit_update_batch(u32_keys(rng.integers(0, N, 3000)), 10) == 3000      # chains before the first snapshot
+    snap = sg.Snapshot.from_tree(t.root, 4, P)
+    probes = u32_keys(np.concatenate([rng.integers(0, N + 50, 6000), 0x10000007 + 256 * rng.integers(0, 2600, 3000)]))
+    starts = np.concatenate([u32_keys(rng.integers(0, N, 96)), u32_keys(0x10000007 + 256 * rng.integers(0, 2500, 32))])
+    stamps = (0, 10, 1500, 3009, 5000, 5010, 5020, 6000, 6500, 9000)
+    try:
+        _check(snap, t, probes, starts, 150, (0, 1500, 9000), "initial")
+        L0 = snap.info().n_leaves
+
+        # round 1: a few committed updates -> only their leaves are re-transformed
+        k = rng.integers(0, N, 12).astype(np.uint32)
+        assert t.commit_update_batch(u32_keys(k), 5000) == 12
+        s1, st = snap.refresh_from_tree(t.root)
+        assert st.leaves_total == L0 and 1 <= st.leaves_transformed <= 12
+        assert st.leaves_carried == L0 - st.leaves_transformed and st.versions_added >= 12
+        assert st.host_bytes_staged < 0.25 * L0 * 65536
+        _check(s1, t, probes, starts, 150, stamps, "after updates")
+        _check(snap, t, probes[:0], starts[:0], 1, (), "")
+        snap.close()
+        snap = s1
+
+        # round 2: 2500 inserts into one region of the key order (same low byte) -> leaf splits there
+        ik = (0x10000007 + 256 * np.arange(2500)).astype(np.uint32)
+        rng.shuffle(ik)
+        ipay = np.repeat((ik >> 8).astype(np.uint8)[:, None], P, axis=1)
+        assert t.insert(u32_keys(ik), ipay, 5010) == 2500
+        s2, st = snap.refresh_from_tree(t.root)
+        assert st.leaves_total > L0, "the inserts split leaves"
+        assert st.rows == N + 2500
+        assert st.leaves_carried >= L0 - 8 and st.leaves_transformed <= 8 + 2 * (st.leaves_total - L0)
+        _check(s2, t, probes, starts, 150, stamps, "after inserts")
+        snap.close()
+        snap = s2
+
+        # round 3: deletes (old and freshly inserted rows) + updates of inserted rows
+        dk = np.concatenate([rng.choice(N, 40, replace=False).astype(np.uint32), ik[:200]])
+        for key in u32_keys(dk):
+            t.delete(key)
+        assert t.commit_update_batch(u32_keys(ik[300:400]), 6000) == 100
+        s3, st = snap.refresh_from_tree(t.root)
+        assert st.rows == N + 2500 - 240
+        assert 0 < st.leaves_transformed < st.leaves_total // 2
+        _check(s3, t, probes, starts, 150, stamps, "after deletes")
+        snap.close()
+        snap = s3
+
+        # the refreshed snapshot equals one flattened from scratch (same rows, leaves and answers) ...
+        with sg.Snapshot.from_tree(t.root, 4, P) as fresh:
+            a, b = snap.info(), fresh.info()
+            assert (a.n_rows, a.n_leaves, a.max_leaf_rows) == (b.n_rows, b.n_leaves, b.max_leaf_rows)
+            for read_ts in (0, 5005, 9000):
+                assert_probe_equal(snap.probe(probes, read_ts), fresh.probe(probes, read_ts), "vs fresh")
+        # ... and a refresh with nothing changed carries every leaf over
+        s4, st = snap.refresh_from_tree(t.root)
+        assert st.leaves_transformed == 0 and st.host_bytes_staged == 0 and st.versions_added == 0
+        _check(s4, t, probes, starts, 150, (0, 5015, 9000), "no-op refresh")
+        s4.close()
+    finally:
+        snap.close()
+
+
+def test_refresh_string_keys_random_order_inserts():
+    """16-byte keys (memcmp order, 4 key words), inserts in random order everywhere: most leaves change and the
+    refresh degenerates to a rebuild — still exact."""
+    t, keys, pay = random_table(pyoracle.OracleTable, 6000, 16, 120, seed=8)
+    rng = np.random.default_rng(2)
+    with sg.Snapshot.from_tree(t.root, 16, 120) as snap:
+        more = rng.integers(0, 256, size=(3000, 16), dtype=np.uint8)
+        mpay = np.repeat(more[:, :1], 120, axis=1)
+        n_new = t.insert(more, mpay, 7)
+        assert n_new >= 2990
+        for k in keys[:150]:
+            t.delete(k)
+        s2, st = snap.refresh_from_tree(t.root)
+        try:
+            assert st.rows == keys.shape[0] + n_new - 150
+            probes = np.concatenate([keys[:2000], more[:1000], rng.integers(0, 256, size=(500, 16), dtype=np.uint8)])
+            for read_ts in (0, 6, 7, 100):
+                assert_probe_equal(s2.probe(probes, read_ts), t.probe(probes, read_ts), f"ts={read_ts}")
+                assert_scan_equal(s2.scan(probes[:80], 90, read_ts, 1), t.scan(probes[:80], 90, read_ts, 1), "scan")
+        finally:
+            s2.close()
+
+
+def test_refresh_needs_a_tree_snapshot():
+    with sg.Snapshot.generate_ycsb(1000, 64) as snap:
+        t = ycsb_int_table(pyoracle.OracleTable, 1000, 64)
+        with pytest.raises(sg.StageError):
+            snap.refresh_from_tree(t.root)              # generated snapshots carry no host fingerprints

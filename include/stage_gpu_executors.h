@@ -99,6 +99,17 @@ public:
                                    row_counts, key_out, ts_out, payload_out, STAGE_IO_HOST), "stage_gpu_scan_batch");
     }
 
+    // After the host tree took committed inserts / updates / deletes (quiesced again): swap in the next snapshot.
+    // Only the leaves that changed are staged again (stage_gpu_snapshot_refresh_from_tree).
+    stage_refresh_stats_t Refresh(const void *root) {
+        stage_snapshot_t *next = nullptr;
+        stage_refresh_stats_t st{};
+        check(stage_gpu_snapshot_refresh_from_tree(snap_, root, &next, &st), "stage_gpu_snapshot_refresh_from_tree");
+        stage_gpu_snapshot_destroy(snap_);
+        snap_ = next;
+        return st;
+    }
+
     const stage_schema_t &schema() const { return schema_; }
     stage_snapshot_t *handle() { return snap_; }
 

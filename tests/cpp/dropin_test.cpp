@@ -86,10 +86,15 @@ static void insert_row(Table &t, const char *key, const char *payload) {
 
 template <class T>
 static int run_checks(Table &t, const std::vector<std::string> &probe_keys, const std::vector<std::string> &scan_keys,
-                      uint32_t scan_size, bool ref_only, const char *what) {
+                      uint32_t scan_size, bool ref_only, const char *what, stage_gpu::GpuTreeView *reuse = nullptr) {
     auto *mgr = SSNTransactionManager::GetInstance();
-    std::unique_ptr<stage_gpu::GpuTreeView> view;
-    if (!ref_only) view.reset(new stage_gpu::GpuTreeView(t.tree->GetRootNodeSafe(), t.K, t.P));
+    std::unique_ptr<stage_gpu::GpuTreeView> owned;
+    if (!ref_only && !reuse) owned.reset(new stage_gpu::GpuTreeView(t.tree->GetRootNodeSafe(), t.K, t.P));
+    struct ViewRef {                       // the checks below use view-> / view.get() for either kind of view
+        stage_gpu::GpuTreeView *p;
+        stage_gpu::GpuTreeView *operator->() const { return p; }
+        stage_gpu::GpuTreeView *get() const { return p; }
+    } view{reuse ? reuse : owned.get()};
     uint64_t hits = 0, rows = 0, crc = 0;
     const int fail0 = g_fail;
 
@@ -224,6 +229,28 @@ int main(int argc, char **argv) {
         }
         run_checks<TupleInt>(t, probes, scans, 1000, ref_only, "ycsb-int");
         run_checks<TupleInt>(t, {}, scans, 10, ref_only, "ycsb-int/10");
+        // structural refresh through the adapter: rows inserted after the first snapshot (leaf splits), then
+        // GpuTreeView::Refresh stages only the changed leaves; all read shapes again on the refreshed view
+        std::unique_ptr<stage_gpu::GpuTreeView> live;
+        if (!ref_only) live.reset(new stage_gpu::GpuTreeView(t.tree->GetRootNodeSafe(), t.K, t.P));
+        const uint32_t n_more = n_rows / 10;
+        for (uint32_t i = 0; i < n_more; ++i) {
+            const uint32_t rowid = 0x20000005u + 256u * i;           // one region of the reference key order
+            memset(payload.data(), (int) i, payload.size());
+            insert_row(t, reinterpret_cast<const char *>(&rowid), payload.data());
+            if (i % 16 == 0) {
+                probes.emplace_back(reinterpret_cast<const char *>(&rowid), 4);
+                scans.emplace_back(reinterpret_cast<const char *>(&rowid), 4);
+            }
+        }
+        if (!ref_only) {
+            const stage_refresh_stats_t st = live->Refresh(t.tree->GetRootNodeSafe());
+            printf("refresh: %lu leaves, %lu carried over, %lu re-transformed, %lu rows\n", (unsigned long) st.leaves_total,
+                   (unsigned long) st.leaves_carried, (unsigned long) st.leaves_transformed, (unsigned long) st.rows);
+            EXPECT(st.rows == (uint64_t) n_rows + n_more, "refresh: row count");
+            EXPECT(st.leaves_carried > st.leaves_total / 2, "refresh: most leaves must be carried over");
+        }
+        run_checks<TupleInt>(t, probes, scans, 100, ref_only, "int/refresh", live.get());
     }
     // ---- YCSB string table (ycsb_loader.cpp:107-143): 16 random bytes per key, payload 1000 x 'a' ---------------
     {

@@ -95,6 +95,22 @@ int stage_gpu_init(int device);
  * chasing of BTree::TraverseToLeaf (src/vstore/b_tree.cpp:1804-1846) for all later reads. */
 int stage_gpu_snapshot_from_tree(const void *root, const stage_schema_t *schema, stage_snapshot_t **out);
 
+/* Snapshot of a tree with writers in flight. A record whose update has not committed carries the
+ * control bit and next_ptr = the location of its undo copy in the EphemeralPool (LeafNode::Update,
+ * src/vstore/b_tree.cpp:1122-1159). BTree::Read (b_tree.cpp:2087-2113) hands readers that copy — old payload, the
+ * unchanged commit id, and the version chain saved in the copy's header — and the snapshot stages exactly that, so
+ * probes answer as the reference answers them while the writer is in flight (the uncommitted bytes never reach the
+ * device). `resolve` is called on the calling thread for every in-flight record with RecordMetadata.next_ptr and
+ * returns 1 after filling *next_tuple_header (EphemeralPool::GetNext) and *old_record (the copy: [key_len bytes of
+ * key][payload]), or 0 when there is no copy (in-flight insert; copy already released): BTree::Read misses then and
+ * the row is left out. Range scans return the same committed rows; the reference's iterator reads the uncommitted
+ * in-place bytes there (LeafNode::RangeScanBySize takes no such care, b_tree.cpp:1276-1302), which is not reproduced.
+ * Node structure must still be stable during the call (no split in progress: frozen nodes are refused). */
+typedef int (*stage_undo_resolver_t)(void *ctx, uint64_t copy_location, uint64_t *next_tuple_header,
+                                     const void **old_record);
+int stage_gpu_snapshot_from_tree_live(const void *root, const stage_schema_t *schema, stage_undo_resolver_t resolve,
+                                      void *resolve_ctx, stage_snapshot_t **out);
+
 /* Structural refresh: a NEW snapshot of the same host tree after committed inserts, updates and
  * deletes — including the leaf splits / consolidations they caused (src/vstore/b_tree.cpp:1558-1690) — at the cost
  * of the leaves that changed. `old` must come from stage_gpu_snapshot_from_tree or a previous refresh of this tree

@@ -65,6 +65,14 @@ public:
         schema_ = stage_schema_t{key_size, payload_size, leaf_node_size, key_kind};
         check(stage_gpu_snapshot_from_tree(root, &schema_, &snap_), "stage_gpu_snapshot_from_tree");
     }
+    // Tree with writers in flight: `resolve` looks an undo copy up in the tree's EphemeralPool (stage_undo_resolver_t,
+    // include/stage_gpu.h), as BTree::Read does for a record whose update has not committed (b_tree.cpp:2087-2103).
+    GpuTreeView(const void *root, uint32_t key_size, uint32_t payload_size, stage_undo_resolver_t resolve, void *resolve_ctx,
+                uint32_t leaf_node_size = 65536, uint32_t key_kind = STAGE_KEY_AUTO) {
+        schema_ = stage_schema_t{key_size, payload_size, leaf_node_size, key_kind};
+        check(stage_gpu_snapshot_from_tree_live(root, &schema_, resolve, resolve_ctx, &snap_),
+              "stage_gpu_snapshot_from_tree_live");
+    }
     ~GpuTreeView() { if (snap_) stage_gpu_snapshot_destroy(snap_); }
     GpuTreeView(const GpuTreeView &) = delete;
     GpuTreeView &operator=(const GpuTreeView &) = delete;

@@ -182,6 +182,20 @@ class RefTable(_Table):
     def close(self):
         self.h = None  # the reference has no working table destructor path; pools are leaked
 
+    # -- in-flight updates (live reference only) ------------------------------------
+    def begin_update(self, key, new_payload, txn_id):
+        """LeafNode::Update without the finalize: control bit set, undo copy in the EphemeralPool, payload
+        overwritten in place. Returns 0 on success (the reference's ReturnCode byte otherwise)."""
+        key = np.ascontiguousarray(key, np.uint8)
+        new_payload = np.ascontiguousarray(new_payload, np.uint8)
+        assert new_payload.size == self.payload_size
+        f = self._fn("begin_update", _i32, [_vp, _vp, _u32, _vp, _u32])
+        return f(self.h, _ptr(key), key.size, _ptr(new_payload), txn_id)
+
+    def undo_resolver(self):
+        """(function address, context) of the stage_undo_resolver_t over this table's EphemeralPool."""
+        return C.cast(getattr(self._lib, "ref_resolve_undo"), _vp).value, int(self.h)
+
 
 def walk_tree(root):
     """(leaf_ptrs[L] u64, sep_ptrs[L-1] u64, sep_lens[L-1] u32) of a tree in the reference node layout."""

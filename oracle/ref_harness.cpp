@@ -7,10 +7,16 @@
 //                            (/root/reference/benchmark/ycsb/ycsb_loader.cpp:93-173)
 //   * point probe          : BTree::Read (src/vstore/b_tree.cpp:2066-2129) + the visibility rule of
 //                            IndexScanExecutor (include/execute/executor.h:383-446)
-//   * range scan           : BTree::RangeScanBySize -> Iterator::GetNext (include/vstore/b_tree.h:830-941)
-//                            + executor loop (executor.h:459-535 MVCC, :626-638 table scan)
-// The two executor chain-walk branches are undefined behaviour at HEAD, so the
-// harness applies the same visibility rule itself: "emit the matching version once, then stop".
+//   * range scan, MVCC     : the reference's own IndexScanExecutor range branch (executor.h:455-535) run
+//                            with a read-only TransactionContext of the requested read id; rows are captured
+//                            in its predicate callback (its result vector holds pointers into freed Records)
+//   * range scan, no filter: BTree::RangeScanBySize -> Iterator::GetNext (include/vstore/b_tree.h:830-941)
+//                            + the TableScanExecutor loop (executor.h:626-638), restated here because that
+//                            executor copies a compile-time struct; tests/cpp/dropin_test.cpp pins the
+//                            restatement against the real TableScanExecutor
+// The point executor's chain-hit branch is undefined behaviour at HEAD (it copies into a null tuple,
+// SURVEY.md §3.4 Q10), so for probes the harness applies the visibility rule itself on the Record that
+// BTree::Read returns: "emit the matching version once, then stop".
 //
 // Used by tests/ (as the checker) and by bench.py's cpu_baseline / --impl reference legs only.
 
@@ -22,6 +28,8 @@
 #include <atomic>
 #include <limits>
 
+#include <cstddef>
+#include "execute/executor.h"
 #include "vstore/b_tree.h"
 #include "vstore/valen_buffer.h"
 #include "vstore/version_store.h"
@@ -67,6 +75,7 @@ ref_table *ref_table_create(uint32_t catalog_key_len, uint32_t payload_size, uin
     UndoBuffer *undo = new UndoBuffer(p2);
     t->undo_pool = new EphemeralPool(undo);
     t->tree = new BTree(param, *t->catalog, t->leaf_pool, t->inner_pool, t->undo_pool);
+    SSNTransactionManager::GetInstance()->Init(t->undo_pool);        // the executors ask the singleton (PerformRead)
     return t;
 }
 
@@ -197,6 +206,26 @@ int64_t ref_commit_update_batch(ref_table *t, const void *keys, uint32_t key_siz
     return ok;
 }
 
+// An update left IN FLIGHT: LeafNode::Update (b_tree.cpp:1061-1163) sets the control bit, parks the
+// old record in the EphemeralPool, points next_ptr at that copy and overwrites the payload in place — and nothing
+// finalizes it. new_payload replaces column 1. Returns the ReturnCode byte (0 = ok).
+int ref_begin_update(ref_table *t, const void *key, uint32_t key_size, const void *new_payload, uint32_t txn_id) {
+    std::vector<oid_t> columns{1};
+    RecordMeta meta;
+    ReturnCode rc = t->tree->Update(static_cast<const char *>(key), (uint16_t) key_size,
+                                    static_cast<const char *>(new_payload), columns, &meta, false, txn_id);
+    return rc.IsOk() ? 0 : (int) rc.rc;
+}
+// stage_undo_resolver_t over the table's EphemeralPool (what BTree::Read does, b_tree.cpp:2087-2103); ctx = ref_table*
+int ref_resolve_undo(void *ctx, uint64_t copy_location, uint64_t *next_tuple_header, const void **old_record) {
+    ref_table *t = static_cast<ref_table *>(ctx);
+    auto hd = t->undo_pool->GetOversionHeader(copy_location);
+    if (hd == nullptr) return 0;
+    *next_tuple_header = t->undo_pool->GetNext(copy_location);
+    *old_record = reinterpret_cast<const void *>(copy_location);
+    return 1;
+}
+
 const void *ref_root(ref_table *t) { return t->tree->GetRootNodeSafe(); }
 uint64_t ref_tuple_count(ref_table *t) { return t->tree->GetTupleCount(); }
 
@@ -213,7 +242,10 @@ static inline int visible_version(Record *rec, uint32_t key_size, uint32_t paylo
         if (payload_out) memcpy(payload_out, rec->GetPayload(), payload_size);
         return 1;
     }
-    uint64_t next = rec->meta.meta_data.GetNextPointer();   // == RecordMeta.next_tuple_ptr (b_tree.cpp:2116)
+    // The executors follow RecordMeta::next_tuple_ptr (executor.h:407 point, :489 range). BTree::Read fills it
+    // (b_tree.cpp:2099/2116); the records Iterator::GetNext hands out leave it 0 (record_meta.h:240), so a range
+    // scan never walks a chain: a row whose in-leaf version is newer than the reader is dropped.
+    uint64_t next = rec->meta.next_tuple_ptr;
     while (next != 0 && next != std::numeric_limits<uint64_t>::max()) {
         TupleHeader *hd = reinterpret_cast<TupleHeader *>(next);
         cid_t begn = hd->GetBeginId(), comm = hd->GetEndCommitId();
@@ -256,6 +288,31 @@ int ref_probe(ref_table *t, const void *keys, uint32_t key_size, uint64_t n, uin
 }
 
 // One scan: executor loop over Iterator::GetNext. Rows go to out row index base .. base+count.
+// MVCC scan through the UNMODIFIED IndexScanExecutor (range branch). The predicate sees every row the executor
+// returns, while the Record behind it is still alive.
+static inline uint32_t scan_one_executor(ref_table *t, const char *start_key, uint32_t key_size, uint32_t scan_size,
+                                         uint32_t read_ts, uint32_t *ts_out, char *key_out, char *payload_out) {
+    const uint32_t P = t->payload_size;
+    TransactionContext txn(0, IsolationLevelType::SERIALIZABLE, read_ts, read_ts);
+    txn.SetReadOnly();                                       // PerformRead returns at once (transaction_manager.cpp:364)
+    uint32_t cnt = 0;
+    const char *k = start_key;
+    IndexScanExecutor<const char *, char> ex(
+        t->tree, (uint16_t) key_size, k, scan_size, false,
+        [&](const char *data, bool &) {
+            // data == Record::GetData() == tuple_data_ + sizeof(cid_t) (b_tree.h:496-498)
+            const Record *r = reinterpret_cast<const Record *>(data - sizeof(cid_t) - offsetof(Record, tuple_data_));
+            if (ts_out) ts_out[cnt] = r->meta.meta_data.GetTxnCommitId();
+            if (key_out) memcpy(key_out + (uint64_t) cnt * key_size, data, key_size);
+            if (payload_out) memcpy(payload_out + (uint64_t) cnt * P, data + r->meta.meta_data.GetPaddedKeyLength(), P);
+            ++cnt;
+            return true;
+        },
+        false, &txn, nullptr);
+    ex.Execute();
+    return cnt;
+}
+
 static inline uint32_t scan_one(ref_table *t, const char *start_key, uint32_t key_size, uint32_t scan_size,
                                 uint32_t read_ts, int apply_visibility, uint32_t *ts_out, char *key_out,
                                 char *payload_out) {
@@ -289,10 +346,12 @@ int ref_scan(ref_table *t, const void *start_keys, uint32_t key_size, const uint
     const uint32_t P = t->payload_size;
     for (uint64_t i = 0; i < n; ++i) {
         uint64_t base = i * (uint64_t) out_stride;
-        row_counts[i] = scan_one(t, k + i * key_size, key_size, scan_sizes[i], read_ts, apply_visibility,
-                                 ts_out ? ts_out + base : nullptr,
-                                 key_out ? static_cast<char *>(key_out) + base * key_size : nullptr,
-                                 payload_out ? static_cast<char *>(payload_out) + base * P : nullptr);
+        uint32_t *to = ts_out ? ts_out + base : nullptr;
+        char *ko = key_out ? static_cast<char *>(key_out) + base * key_size : nullptr;
+        char *po = payload_out ? static_cast<char *>(payload_out) + base * P : nullptr;
+        row_counts[i] = apply_visibility && scan_sizes[i]
+                            ? scan_one_executor(t, k + i * key_size, key_size, scan_sizes[i], read_ts, to, ko, po)
+                            : scan_one(t, k + i * key_size, key_size, scan_sizes[i], read_ts, apply_visibility, to, ko, po);
     }
     return 0;
 }

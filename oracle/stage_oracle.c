@@ -635,11 +635,14 @@ static uint32_t scan_one(so_tree *t, scan_buf *buf, const u8 *start, uint32_t ks
                     buf->n = buf->head = 0;                  /* "hit the same record": scan ends */
             }
         }
+        /* IndexScanExecutor range branch, executor.h:465-534: the row is returned iff read_id >= the commit id of
+         * its in-leaf version. The else-branch reads RecordMeta::next_tuple_ptr, which is 0 for every record the
+         * iterator hands out (RecordMeta ctor record_meta.h:240; LeafNode::RangeScanBySize b_tree.cpp:1290-1297
+         * never sets it; only BTree::Read does, b_tree.cpp:2099/2116): no chain walk ever happens in a range scan,
+         * a too-new row is dropped. Verified on the unmodified executor (tests/cpp/dropin_test.cpp). */
         int f = 1;
-        if (apply_visibility) {
-            f = visible_version(cur.leaf, cur.mp, ks, P, read_ts, ts_out ? ts_out + cnt : NULL,
-                                key_out ? key_out + (uint64_t) cnt * ks : NULL,
-                                payload_out ? payload_out + (uint64_t) cnt * P : NULL);
+        if (apply_visibility && read_ts < m_cid(cur.mp[0])) {
+            f = 0;
         } else {
             uint64_t m = cur.mp[0];
             if (ts_out) ts_out[cnt] = m_cid(m);

@@ -53,6 +53,7 @@ class RefreshStats(C.Structure):
 SYMBOLS = {
     "stage_gpu_init": (_i32, [_i32]),
     "stage_gpu_snapshot_from_tree": (_i32, [_vp, C.POINTER(Schema), C.POINTER(_vp)]),
+    "stage_gpu_snapshot_from_tree_live": (_i32, [_vp, C.POINTER(Schema), _vp, _vp, C.POINTER(_vp)]),
     "stage_gpu_snapshot_refresh_from_tree": (_i32, [_vp, _vp, C.POINTER(_vp), C.POINTER(RefreshStats)]),
     "stage_gpu_snapshot_begin": (_i32, [C.POINTER(Schema), _u64, _u64, C.POINTER(_vp)]),
     "stage_gpu_snapshot_add_versions": (_i32, [_vp, _vp, _vp, _u64]),
@@ -185,6 +186,17 @@ class Snapshot:
         sc = Schema(key_size, payload_size, leaf_node_size, key_kind)
         h = _vp()
         _check(lib().stage_gpu_snapshot_from_tree(_vp(int(root)), C.byref(sc), C.byref(h)))
+        return cls(h, sc)
+
+    @classmethod
+    def from_tree_live(cls, root, key_size, payload_size, resolve_fn, resolve_ctx, leaf_node_size=65536, key_kind=KEY_AUTO):
+        """Snapshot of a tree with updates in flight. resolve_fn: address of a C function
+        int(void *ctx, uint64_t copy_location, uint64_t *next_tuple_header, const void **old_record) that looks the undo
+        copy up in the caller's EphemeralPool (include/stage_gpu.h, stage_undo_resolver_t); resolve_ctx: its context."""
+        sc = Schema(key_size, payload_size, leaf_node_size, key_kind)
+        h = _vp()
+        _check(lib().stage_gpu_snapshot_from_tree_live(_vp(int(root)), C.byref(sc), _vp(int(resolve_fn)),
+                                                       _vp(int(resolve_ctx)), C.byref(h)))
         return cls(h, sc)
 
     def refresh_from_tree(self, root):

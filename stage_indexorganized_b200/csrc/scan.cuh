@@ -43,6 +43,18 @@ struct ScanArgs {
     const uint32_t *n_dev;      // optional: the number of scans lives on the device (min(*n_dev, n) are run)
 };
 
+// MVCC filter of a scanned row, exactly as the reference's executors apply it. TableScanExecutor: none
+// (executor.h:620-638). IndexScanExecutor range branch (executor.h:455-535): a row is returned iff
+// read_id >= the commit id of its in-leaf version. The branch that would walk the version chain of a too-new row
+// reads RecordMeta::next_tuple_ptr, which is 0 for every record the iterator produces (RecordMeta's constructor
+// zeroes it, record_meta.h:240; LeafNode::RangeScanBySize never sets it, b_tree.cpp:1290-1297; only BTree::Read
+// does, b_tree.cpp:2099/2116) — so in a range scan a row whose latest version is newer than the reader is
+// DROPPED, never replaced by an older version. Checked against the unmodified executor in
+// tests/cpp/dropin_test.cpp ("range over chains"). Point probes do walk the chain (probe.cuh).
+__device__ __forceinline__ bool scan_row_visible(const ScanArgs &a, uint32_t t) {
+    return !a.apply_visibility || a.read_ts >= t;
+}
+
 constexpr int kScanThreads = 256;
 constexpr int kScanRowsPerThread = 4;
 constexpr int kScanTile = kScanThreads * kScanRowsPerThread;     // rows staged per TMA tile
@@ -101,7 +113,6 @@ __device__ __forceinline__ uint32_t block_exclusive_sum(uint32_t x, uint32_t *s_
 template <int NW>
 __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v, ScanArgs a) {
     __shared__ __align__(16) uint32_t s_ts[kScanTile + 8];
-    __shared__ __align__(16) uint32_t s_chain[kScanTile + 8];
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ uint32_t s_warp[kScanThreads / 32];
     __shared__ uint32_t s_min;
@@ -180,9 +191,8 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
                     const uint32_t a0 = r0 & ~3u;                 // 16-byte aligned start of the staged window
                     const uint32_t bytes = ((r0 + n - a0) * 4u + 15u) & ~15u;
                     if (tid == 0) {
-                        mbar_expect_tx(&s_bar, a.apply_visibility ? 2 * bytes : bytes);
+                        mbar_expect_tx(&s_bar, bytes);
                         tma_load_1d(s_ts, v.ts + a0, bytes, &s_bar);
-                        if (a.apply_visibility) tma_load_1d(s_chain, v.chain + a0, bytes, &s_bar);
                     }
                     mbar_wait(&s_bar, parity);
                     parity ^= 1;
@@ -194,9 +204,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
                         stamp[k] = 0;
                         if (i < n) {
                             const uint32_t row = r0 + i, t = s_ts[row - a0];
-                            if (!a.apply_visibility) { src[k] = row; stamp[k] = t; }
-                            else if (a.read_ts >= t) { src[k] = row; stamp[k] = t; }
-                            else if (s_chain[row - a0] != 0) src[k] = visible_version(v, row, t, a.read_ts, &stamp[k]);
+                            if (scan_row_visible(a, t)) { src[k] = row; stamp[k] = t; }
                             mine += src[k] != kNoRow;
                         }
                     }
@@ -231,8 +239,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
                         const uint32_t row = start_l + i;
                         if (sel) {
                             const uint32_t t = __ldg(v.ts + row);
-                            if (a.apply_visibility) src = visible_version(v, row, t, a.read_ts, &stamp);
-                            else { src = row; stamp = t; }
+                            if (scan_row_visible(a, t)) { src = row; stamp = t; }
                         }
                         const uint32_t p2 = block_exclusive_sum(src != kNoRow ? 1u : 0u, s_warp, &tot);
                         if (src != kNoRow) emit(row, src, stamp, cnt + p2);
@@ -363,8 +370,7 @@ __global__ void __launch_bounds__(kScanWarpThreads) scan_plan_warp_kernel(Snapsh
                     const uint32_t row = q0 + i;
                     if (i < main_n) {
                         const uint32_t t = __ldg(v.ts + row);
-                        if (!a.apply_visibility || a.read_ts >= t) { src = row; stamp = t; }
-                        else src = visible_version(v, row, t, a.read_ts, &stamp);
+                        if (scan_row_visible(a, t)) { src = row; stamp = t; }
                     }
                     const uint32_t m = __ballot_sync(FULL, src != kNoRow);
                     if (src != kNoRow) emit(row, src, stamp, cnt + __popc(m & lt_mask));
@@ -395,8 +401,7 @@ __global__ void __launch_bounds__(kScanWarpThreads) scan_plan_warp_kernel(Snapsh
                         const uint32_t row = start_l + i;
                         if (sel) {
                             const uint32_t t = __ldg(v.ts + row);
-                            if (a.apply_visibility) src = visible_version(v, row, t, a.read_ts, &stamp);
-                            else { src = row; stamp = t; }
+                            if (scan_row_visible(a, t)) { src = row; stamp = t; }
                         }
                         const uint32_t m2 = __ballot_sync(FULL, src != kNoRow);
                         if (src != kNoRow) emit(row, src, stamp, cnt + __popc(m2 & lt_mask));

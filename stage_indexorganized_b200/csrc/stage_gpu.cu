@@ -366,9 +366,24 @@ static int flush_chunk(stage_snapshot *s) {
     return STAGE_OK;
 }
 
+// In-flight (overwritten) versions, SURVEY 8f f2: a record whose update has not committed (control bit set,
+// next_ptr = location of its undo copy in the EphemeralPool, b_tree.cpp:1122-1159) is staged as a reader sees it
+// (BTree::Read, b_tree.cpp:2087-2113): the payload of the undo copy, the unchanged commit id, and the chain the
+// undo header saved. Without an undo copy (an in-flight insert, or the copy is gone) the read misses: the row is
+// dropped from the snapshot.
+struct InflightPatch {
+    uint32_t slot;
+    const uint8_t *old_payload;      // nullptr = drop the row
+};
+struct LeafExtras {
+    const uint32_t *heads = nullptr;           // [record_count] 1-based version index per slot (0 = none)
+    const InflightPatch *patches = nullptr;    // in-flight records of this leaf, resolved by the caller
+    uint32_t n_patches = 0;
+};
+
 // Copy one leaf image into its pinned staging slot, count its visible records and replace the host TupleHeader
 // pointers in RecordMetadata.next_ptr by version indices. Thread-safe: touches only `dst`.
-static int stage_copy_leaf(const stage_snapshot *s, uint8_t *dst, const uint8_t *leaf, const uint32_t *chain_heads,
+static int stage_copy_leaf(const stage_snapshot *s, uint8_t *dst, const uint8_t *leaf, const LeafExtras &ex,
                            uint32_t *vis_out, uint32_t *count_out) {
     const uint32_t ls = s->schema.leaf_node_size;
     if (!leaf[kOffIsLeaf]) return STAGE_ERR_LAYOUT;
@@ -378,6 +393,20 @@ static int stage_copy_leaf(const stage_snapshot *s, uint8_t *dst, const uint8_t 
     const uint32_t count = status_record_count(status);
     if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize > ls) return STAGE_ERR_LAYOUT;
     memcpy(dst, leaf, ls);
+    for (uint32_t p = 0; p < ex.n_patches; ++p) {
+        const InflightPatch &ip = ex.patches[p];
+        if (ip.slot >= count) return STAGE_ERR_LAYOUT;
+        uint8_t *mp = dst + kOffMeta + (size_t) ip.slot * kMetaSize;
+        uint64_t m;
+        memcpy(&m, mp, 8);
+        m &= ~kMetaControl;
+        if (!ip.old_payload) m &= ~kMetaVisible;
+        else {
+            if (meta_offset(m) + pad_key_len(meta_key_len(m)) + s->schema.payload_size > ls) return STAGE_ERR_LAYOUT;
+            memcpy(dst + meta_offset(m) + pad_key_len(meta_key_len(m)), ip.old_payload, s->schema.payload_size);
+        }
+        memcpy(mp, &m, 8);
+    }
     uint32_t vis = 0;
     for (uint32_t i = 0; i < count; ++i) {
         uint8_t *mp = dst + kOffMeta + (size_t) i * kMetaSize;
@@ -388,7 +417,7 @@ static int stage_copy_leaf(const stage_snapshot *s, uint8_t *dst, const uint8_t 
             if (m & kMetaControl) return STAGE_ERR_NOT_QUIESCED;
             if (meta_offset(m) + pad_key_len(meta_key_len(m)) + s->schema.payload_size > ls) return STAGE_ERR_LAYOUT;
             ++vis;
-            if (chain_heads) head = chain_heads[i];
+            if (ex.heads) head = ex.heads[i];
         }
         memcpy(mp + kMetaNextPtr, &head, 8);   // pointer translation: host TupleHeader* -> version index
     }
@@ -407,7 +436,7 @@ static unsigned staging_threads() {
 
 // Stage n leaves (tree order). The 64 KiB image copies — the bulk of the host work — run on a few threads, one
 // staging chunk at a time; bookkeeping (row offsets, fences) and the chunk flush stay on the calling thread.
-// get(i, &leaf, &fence, &heads) supplies leaf i.
+// get(i, &leaf, &fence, &extras) supplies leaf i.
 template <class Get>
 static int stage_leaves(stage_snapshot *s, uint64_t n, Get get) {
     const uint32_t ls = s->schema.leaf_node_size;
@@ -422,9 +451,9 @@ static int stage_leaves(stage_snapshot *s, uint64_t n, Get get) {
         auto work = [&](uint32_t lo, uint32_t hi) {
             for (uint32_t j = lo; j < hi; ++j) {
                 const uint8_t *leaf, *fence;
-                const uint32_t *heads;
-                get(base + j, &leaf, &fence, &heads);
-                rcs[j] = stage_copy_leaf(s, slot0 + (size_t) j * ls, leaf, heads, &vis[j], &cnt[j]);
+                LeafExtras ex;
+                get(base + j, &leaf, &fence, &ex);
+                rcs[j] = stage_copy_leaf(s, slot0 + (size_t) j * ls, leaf, ex, &vis[j], &cnt[j]);
             }
         };
         const unsigned T = std::min<unsigned>(staging_threads(), std::max(1u, m / 16));
@@ -438,8 +467,8 @@ static int stage_leaves(stage_snapshot *s, uint64_t n, Get get) {
         for (uint32_t j = 0; j < m; ++j) {
             if (rcs[j]) return rcs[j];
             const uint8_t *leaf, *fence;
-            const uint32_t *heads;
-            get(base + j, &leaf, &fence, &heads);
+            LeafExtras ex;
+            get(base + j, &leaf, &fence, &ex);
             if (s->rows_staged + vis[j] > s->cap_rows) return STAGE_ERR_ARG;
             s->rows_staged += vis[j];
             s->h_leaf_off.push_back((uint32_t) s->rows_staged);
@@ -467,11 +496,11 @@ extern "C" int stage_gpu_snapshot_add_leaves(stage_snapshot_t *s, const void *co
     CUDA_TRY(cudaSetDevice(s->device));
     const uint8_t *f = static_cast<const uint8_t *>(upper_fences);
     const uint32_t K = s->schema.key_size;
-    return stage_leaves(s, n, [&](uint64_t i, const uint8_t **leaf, const uint8_t **fence, const uint32_t **heads) {
+    return stage_leaves(s, n, [&](uint64_t i, const uint8_t **leaf, const uint8_t **fence, LeafExtras *ex) {
         *leaf = static_cast<const uint8_t *>(leaf_images[i]);
         const bool hf = f && (!has_upper_fence || has_upper_fence[i]);
         *fence = hf ? f + i * K : nullptr;
-        *heads = chain_heads ? chain_heads[i] : nullptr;
+        ex->heads = chain_heads ? chain_heads[i] : nullptr;
     });
 }
 
@@ -697,7 +726,8 @@ static double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
-extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema_t *schema, stage_snapshot_t **out) {
+static int from_tree_impl(const void *root, const stage_schema_t *schema, stage_undo_resolver_t resolve, void *resolve_ctx,
+                          stage_snapshot_t **out) {
     if (!root || !out) return STAGE_ERR_ARG;
     static const bool dbg = getenv("STAGE_DEBUG_TIMING") != nullptr;
     double t0 = now_s(), t1;
@@ -722,7 +752,9 @@ extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema
     // pass 1 (serial, metadata only): version indices in leaf / slot order
     std::vector<uint32_t> heads_flat;                 // chain heads of the leaves that have any
     std::vector<int64_t> heads_at(w.leaves.size(), -1);
-    for (size_t li = 0; li < w.leaves.size(); ++li) {
+    std::vector<InflightPatch> patches;               // in-flight records, in leaf / slot order
+    std::vector<std::pair<size_t, uint32_t>> patch_at(resolve ? w.leaves.size() : 0, {0, 0});
+    for (size_t li = 0; li < w.leaves.size() && !rc; ++li) {
         const uint8_t *leaf = w.leaves[li];
         uint64_t status;
         memcpy(&status, leaf + kOffStatus, 8);
@@ -734,7 +766,19 @@ extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema
             uint64_t m, nx;
             memcpy(&m, leaf + kOffMeta + (size_t) i * kMetaSize, 8);
             memcpy(&nx, leaf + kOffMeta + (size_t) i * kMetaSize + kMetaNextPtr, 8);
-            if (!meta_visible(m) || nx == 0 || nx == UINT64_MAX) continue;
+            if (!meta_visible(m)) continue;
+            if ((m & kMetaControl) && !resolve) { rc = STAGE_ERR_NOT_QUIESCED; break; }   // next_ptr is an undo copy, not a chain
+            if (m & kMetaControl) {
+                // in flight: the reader's version is the undo copy [key][payload]; its header saved the chain
+                uint64_t saved_next = 0;
+                const void *old_rec = nullptr;
+                const bool have = nx != 0 && nx != UINT64_MAX && resolve(resolve_ctx, nx, &saved_next, &old_rec) == 1 && old_rec;
+                if (patch_at[li].second == 0) patch_at[li].first = patches.size();
+                patch_at[li].second++;
+                patches.push_back({i, have ? static_cast<const uint8_t *>(old_rec) + meta_key_len(m) : nullptr});
+                nx = have ? saved_next : 0;
+            }
+            if (nx == 0 || nx == UINT64_MAX) continue;
             heads[i] = cs.add_chain(nx);
             any = true;
         }
@@ -746,10 +790,14 @@ extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema
     PHASE("chain discovery");
     // pass 2: leaf images, copied by the staging threads
     if (!rc)
-        rc = stage_leaves(s, w.leaves.size(), [&](uint64_t li, const uint8_t **leaf, const uint8_t **fence, const uint32_t **hd) {
+        rc = stage_leaves(s, w.leaves.size(), [&](uint64_t li, const uint8_t **leaf, const uint8_t **fence, LeafExtras *ex) {
             *leaf = w.leaves[li];
             *fence = w.fences[li];
-            *hd = heads_at[li] >= 0 ? heads_flat.data() + heads_at[li] : nullptr;
+            ex->heads = heads_at[li] >= 0 ? heads_flat.data() + heads_at[li] : nullptr;
+            if (resolve && patch_at[li].second) {
+                ex->patches = patches.data() + patch_at[li].first;
+                ex->n_patches = patch_at[li].second;
+            }
         });
     PHASE("stage + transform");
     if (!rc && !vers.empty()) {
@@ -779,6 +827,15 @@ extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema
     }
     *out = s;
     return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_from_tree(const void *root, const stage_schema_t *schema, stage_snapshot_t **out) {
+    return from_tree_impl(root, schema, nullptr, nullptr, out);
+}
+extern "C" int stage_gpu_snapshot_from_tree_live(const void *root, const stage_schema_t *schema,
+                                                 stage_undo_resolver_t resolve, void *resolve_ctx, stage_snapshot_t **out) {
+    if (!resolve) return STAGE_ERR_ARG;
+    return from_tree_impl(root, schema, resolve, resolve_ctx, out);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -904,7 +961,9 @@ extern "C" int stage_gpu_snapshot_refresh_from_tree(stage_snapshot_t *old, const
             uint64_t m, nx;
             memcpy(&m, leaf + kOffMeta + (size_t) i * kMetaSize, 8);
             memcpy(&nx, leaf + kOffMeta + (size_t) i * kMetaSize + kMetaNextPtr, 8);
-            if (!meta_visible(m) || nx == 0 || nx == UINT64_MAX) continue;
+            if (!meta_visible(m)) continue;
+            if (m & kMetaControl) { rc = STAGE_ERR_NOT_QUIESCED; break; }     // next_ptr is an undo copy, not a chain
+            if (nx == 0 || nx == UINT64_MAX) continue;
             heads[i] = cs.add_chain(nx);
             any = true;
         }
@@ -929,8 +988,9 @@ extern "C" int stage_gpu_snapshot_refresh_from_tree(stage_snapshot_t *old, const
         auto work = [&](uint32_t lo, uint32_t hi) {
             for (uint32_t j = lo; j < hi; ++j) {
                 const size_t c = c0 + j;
-                rcs[j] = stage_copy_leaf(s, s->h_stage[buf] + (size_t) j * ls, w.leaves[changed[c]],
-                                         heads_at[c] >= 0 ? heads_flat.data() + heads_at[c] : nullptr, &cvis[j], &ccnt[j]);
+                LeafExtras ex;
+                ex.heads = heads_at[c] >= 0 ? heads_flat.data() + heads_at[c] : nullptr;
+                rcs[j] = stage_copy_leaf(s, s->h_stage[buf] + (size_t) j * ls, w.leaves[changed[c]], ex, &cvis[j], &ccnt[j]);
             }
         };
         const unsigned T = std::min<unsigned>(staging_threads(), std::max(1u, m / 16));

@@ -43,6 +43,7 @@ struct TupleStock {
 };
 
 static int g_fail = 0;
+static EphemeralPool *g_undo = nullptr;      // pool of the table made last (make_table)
 #define EXPECT(cond, ...)                                   \
     do {                                                    \
         if (!(cond)) {                                      \
@@ -70,6 +71,7 @@ static Table make_table(uint32_t K, uint32_t P, uint32_t split, uint64_t blocks)
     auto *leaf_pool = new DramBlockPool(blocks, blocks);
     auto *inner = new InnerNodeBuffer(new RecordBufferPool(5000000, 5000000));
     auto *undo = new EphemeralPool(new UndoBuffer(new RecordBufferPool(5000000, 5000000)));
+    g_undo = undo;
     SSNTransactionManager::GetInstance()->Init(undo);
     t.tree = new BTree(param, *t.catalog, leaf_pool, inner, undo);
     return t;
@@ -196,7 +198,130 @@ static int run_checks(Table &t, const std::vector<std::string> &probe_keys, cons
     return g_fail - fail0;
 }
 
+
+// ---- MVCC: committed version chains and in-flight updates -------------------------------------------------------
+// A committed update as SSNTransactionManager::CommitTransaction leaves it (transaction_manager.cpp:610-676): the
+// old version retired into a TupleHeader chain, the record overwritten in place, meta = new commit id.
+static void commit_update(Table &t, uint32_t key, int fill, uint32_t cid, std::vector<char *> &allocs) {
+    LeafNode *leaf = t.tree->TraverseToLeaf(nullptr, reinterpret_cast<const char *>(&key), (uint16_t) t.K);
+    RecordMetadata *mp = nullptr;
+    if (!leaf || !leaf->Read(reinterpret_cast<const char *>(&key), (uint16_t) t.K, t.P, &mp, false).IsOk()) return;
+    char *rk = nullptr, *rp = nullptr;
+    leaf->GetRawRecord(*mp, &rk, &rp);
+    char *mem = new char[sizeof(TupleHeader) + t.K + t.P];
+    allocs.push_back(mem);
+    TupleHeader *hd = new (mem) TupleHeader();
+    char *slot = mem + sizeof(TupleHeader);
+    hd->init(hd, reinterpret_cast<uint64_t>(slot), (oid_t) allocs.size());
+    memcpy(slot, rk, t.K);
+    memcpy(slot + t.K, rp, t.P);
+    hd->SetBeginId(mp->GetTxnCommitId());
+    hd->SetCommitId(cid);
+    hd->SetNextHeaderPointer(mp->GetNextPointer());
+    memset(rp + 100, fill, 100);
+    mp->FinalizeForUpdate(cid);
+    mp->SetNextPointer(reinterpret_cast<uint64_t>(hd));
+}
+
+static int resolve_undo(void *ctx, uint64_t copy_location, uint64_t *next_tuple_header, const void **old_record) {
+    EphemeralPool *pool = static_cast<EphemeralPool *>(ctx);
+    if (pool->GetOversionHeader(copy_location) == nullptr) return 0;
+    *next_tuple_header = pool->GetNext(copy_location);
+    *old_record = reinterpret_cast<const void *>(copy_location);
+    return 1;
+}
+
+static void run_mvcc_checks(bool ref_only, uint32_t n_rows) {
+    const int fail0 = g_fail;
+    Table t = make_table(4, 1000, 16 * 1024, n_rows / 16 + 4096);
+    std::vector<char> payload(1000);
+    for (uint32_t rowid = 0; rowid < n_rows; ++rowid) {
+        memset(payload.data(), (int) rowid, payload.size());
+        insert_row(t, reinterpret_cast<const char *>(&rowid), payload.data());
+    }
+    benchmark::FastRandom rng(11);
+    std::vector<char *> allocs;
+    uint32_t cid = 10;
+    for (uint32_t i = 0; i < n_rows / 4; ++i) commit_update(t, (uint32_t) (rng.next() % n_rows), (int) cid, cid, allocs), ++cid;   // many rows twice or more
+    const uint32_t last_cid = cid - 1;
+    std::unique_ptr<stage_gpu::GpuTreeView> view;
+    if (!ref_only) view.reset(new stage_gpu::GpuTreeView(t.tree->GetRootNodeSafe(), t.K, t.P));
+
+    // (1) IndexScanExecutor RANGE branch over version chains, at read ids straddling the commit ids. The rows are
+    // captured in the predicate (the reference's result vector points into freed Records). This pins the rule that a
+    // range scan never walks a chain: a row whose in-leaf version is newer than the reader is dropped.
+    uint64_t rows = 0, dropped = 0;
+    for (uint32_t read_id : {0u, 9u, 10u, 10u + n_rows / 16, 10u + n_rows / 8, last_cid - 1, last_cid, 0x7FFFFFFFu}) {
+        for (uint32_t s = 0; s < 24; ++s) {
+            const uint32_t start = (uint32_t) (rng.next() % n_rows), scan_size = s % 3 ? 100 : 400;
+            TransactionContext txn(0, IsolationLevelType::SERIALIZABLE, read_id, read_id);
+            txn.SetReadOnly();
+            std::vector<TupleInt> want, got;
+            IndexScanExecutor<const char *, TupleInt> ref(
+                t.tree, (uint16_t) t.K, reinterpret_cast<const char *>(&start), scan_size, false,
+                [&](const TupleInt *r, bool &) { want.push_back(*r); return true; }, false, &txn, nullptr);
+            EXPECT(ref.Execute(), "reference range Execute");
+            rows += want.size();
+            dropped += scan_size - want.size();
+            if (ref_only) continue;
+            stage_gpu::GpuIndexScanExecutor<const char *, TupleInt, TransactionContext> gpu(
+                view.get(), (uint16_t) t.K, reinterpret_cast<const char *>(&start), scan_size, false,
+                [&](const TupleInt *r, bool &) { got.push_back(*r); return true; }, false, &txn, nullptr);
+            EXPECT(gpu.Execute(), "gpu range Execute");
+            EXPECT(got.size() == want.size(), "range over chains (read id %u): %zu rows, reference %zu", read_id, got.size(), want.size());
+            if (got.size() == want.size())
+                for (size_t i = 0; i < got.size(); ++i)
+                    EXPECT(memcmp(&got[i], &want[i], sizeof(TupleInt)) == 0, "range over chains (read id %u): row %zu differs", read_id, i);
+        }
+    }
+    printf("%-12s range scans over version chains: %lu rows returned, %lu dropped as too new : %s\n", "mvcc", rows, dropped,
+           g_fail == fail0 ? "OK" : "FAILED");
+
+    // (2) updates IN FLIGHT (LeafNode::Update without the finalize, b_tree.cpp:1061-1163): BTree::Read serves the undo
+    // copy; GpuTreeView built with the undo resolver must return the same Record bytes, commit id and cstamp.
+    std::vector<uint32_t> flying;
+    std::vector<oid_t> columns{1};
+    std::vector<char> delta(1000, (char) 0x5A);
+    for (uint32_t i = 0; i < 200; ++i) {
+        const uint32_t k = (uint32_t) (rng.next() % n_rows);
+        if ((k & 0xFF) == 0x5A) continue;                      // the row's committed bytes must differ from the delta
+        RecordMeta meta;
+        if (t.tree->Update(reinterpret_cast<const char *>(&k), (uint16_t) t.K, delta.data(), columns, &meta, false, 0x70000000u + i).IsOk())
+            flying.push_back(k);
+    }
+    EXPECT(flying.size() > 100, "in-flight updates were not accepted");
+    std::unique_ptr<stage_gpu::GpuTreeView> live;
+    if (!ref_only) {
+        stage_snapshot_t *refused = nullptr;
+        stage_schema_t sc{t.K, t.P, 65536, STAGE_KEY_AUTO};
+        EXPECT(stage_gpu_snapshot_from_tree(t.tree->GetRootNodeSafe(), &sc, &refused) == STAGE_ERR_NOT_QUIESCED,
+               "plain from_tree must refuse a tree with writers in flight");
+        live.reset(new stage_gpu::GpuTreeView(t.tree->GetRootNodeSafe(), t.K, t.P, resolve_undo, g_undo));
+    }
+    uint32_t checked = 0;
+    for (uint32_t i = 0; i < flying.size() + 300; ++i) {
+        const uint32_t k = i < flying.size() ? flying[i] : (uint32_t) (rng.next() % (n_rows + 10));
+        const cid_t reader = 0x7FFFFFFFu;
+        std::unique_ptr<Record> r = t.tree->Read(reinterpret_cast<const char *>(&k), (uint16_t) t.K, reader, false);
+        if (i < flying.size()) EXPECT(r != nullptr && (unsigned char) r->GetPayload()[500] != 0x5A, "reference serves uncommitted bytes for key %u", k);
+        if (live) {
+            std::unique_ptr<stage_gpu::Record> g = live->Read(reinterpret_cast<const char *>(&k), (uint16_t) t.K, reader, false);
+            EXPECT((r == nullptr) == (g == nullptr), "in-flight Read: found mismatch for key %u", k);
+            if (r && g) {
+                // Record::Neww (b_tree.h:430-448) leaves the key's padding bytes uninitialised: compare key and payload
+                EXPECT(memcmp(r->GetKey(), g->GetData(), t.K) == 0, "in-flight Read: key %u key bytes differ", k);
+                EXPECT(memcmp(r->GetPayload(), g->GetPayload(), t.P) == 0, "in-flight Read: key %u payload differs", k);
+                EXPECT(r->meta.meta_data.GetTxnCommitId() == g->commit_id, "in-flight Read: key %u commit id", k);
+                ++checked;
+            }
+        }
+        if (r) delete[] reinterpret_cast<char *>(r.release());
+    }
+    printf("%-12s %zu updates in flight, %u reads compared : %s\n", "mvcc", flying.size(), checked, g_fail == fail0 ? "OK" : "FAILED");
+}
+
 int main(int argc, char **argv) {
+    setvbuf(stdout, nullptr, _IOLBF, 0);      // a crash must not swallow the lines before it
     bool ref_only = false;
     uint32_t n_rows = 20000, n_probe = 2000, n_scan = 60;
     for (int i = 1; i < argc; ++i) {
@@ -292,6 +417,7 @@ int main(int argc, char **argv) {
         for (uint32_t i = 0; i < n_scan; ++i) scans.push_back(keys[rng.next() % n]);
         run_checks<TupleStock>(t, probes, scans, 10, ref_only, "stock");       // stock-level scans 10 rows
     }
+    run_mvcc_checks(ref_only, n_rows);
     printf("%s: %d failure(s)\n", ref_only ? "reference half only" : "drop-in parity", g_fail);
     return g_fail ? 1 : 0;
 }

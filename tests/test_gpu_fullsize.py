@@ -3,9 +3,11 @@ read path is checked through properties that do not need the CPU checker at that
 
   * a closed-form MODEL of the table: row r of the YCSB int table in reference key order is rank_to_key(N, r), its
     payload is 1000 x (uint8) key with one 100-byte column rewritten by every committed update, and the version a
-    reader at read_ts sees follows the executor rule (include/execute/executor.h:383-446, 465-534): the in-leaf
-    version if read_ts >= its commit id, else the newest retired version with begin <= read_ts <= commit, where
-    a retired version with begin 0 (the loader's) ends the walk — so a row is invisible before its first update;
+    reader at read_ts sees follows the executor rules. Point probe (include/execute/executor.h:383-446): the
+    in-leaf version if read_ts >= its commit id, else the newest retired version with begin <= read_ts <= commit,
+    where a retired version with begin 0 (the loader's) ends the walk — so a row is invisible before its first
+    update. Range scan (executor.h:465-534): the in-leaf version if read_ts >= its commit id, else the row is
+    dropped (the iterator's records carry no chain pointer);
   * order / contiguity: a scan of S rows from the r-th key returns exactly rows r .. r+S-1 of the key order
     (consolidated leaves), cut at the end of the table; idempotence: the same batch twice gives the same bytes.
 
@@ -17,7 +19,7 @@ import torch
 import stage_indexorganized_b200 as sg
 from stage_indexorganized_b200 import ycsb
 from stage_indexorganized_b200.ycsb import rank_to_key
-from helpers import u32_keys
+from helpers import assert_scan_equal, u32_keys
 from oracle import pyoracle
 
 pytestmark = pytest.mark.gpu
@@ -33,8 +35,10 @@ class UpdateModel:
         self.code = np.sort((k << np.uint64(32)) | cid)           # (key, cid) pairs, sorted
         self.keys_sorted = self.code >> np.uint64(32)
 
-    def visible(self, keys, read_ts):
-        """-> (visible bool[n], stamp u32[n]) for existing keys."""
+    def visible(self, keys, read_ts, scan=False):
+        """-> (visible bool[n], stamp u32[n]) for existing keys. Point probes walk the version chain (an older
+        version with begin != 0 can answer); a range scan only ever returns the in-leaf version, i.e. the row is
+        visible iff ALL its updates committed at or before read_ts (executor.h:465-534 with next_tuple_ptr == 0)."""
         k = np.asarray(keys, np.uint64)
         lo = np.searchsorted(self.keys_sorted, k, "left")
         hi = np.searchsorted(self.keys_sorted, k, "right")
@@ -43,7 +47,7 @@ class UpdateModel:
         le = np.searchsorted(self.code, (k << np.uint64(32)) | np.uint64(min(read_ts, 0xFFFFFFFF)), "right") - lo
         le = np.clip(le, 0, n_upd)
         stamp = np.where(le > 0, self.code[np.clip(lo + le - 1, 0, max(len(self.code) - 1, 0))] & np.uint64(0xFFFFFFFF), 0)
-        vis = (n_upd == 0) | (le > 0)
+        vis = (n_upd == 0) | ((le == n_upd) if scan else (le > 0))
         return vis, np.where(vis, stamp, 0).astype(np.uint32)
 
 
@@ -77,7 +81,7 @@ def check_against_model(snap, n_total, first, n_local, model, read_ts, n_scans, 
     ranks = pos[:, None] + np.arange(S)[None, :]
     inwin = np.arange(S)[None, :] < win[:, None]
     wkeys = rank_to_key(n_total, first + np.where(inwin, ranks, 0))
-    vis, stamp = model.visible(wkeys.ravel(), read_ts)
+    vis, stamp = model.visible(wkeys.ravel(), read_ts, scan=True)
     vis = vis.reshape(wkeys.shape) & inwin
     assert np.array_equal(counts, vis.sum(axis=1).astype(np.uint32)), "row counts"
     got_k = keys.reshape(n_scans, S, 4).view(np.uint32).reshape(n_scans, S)
@@ -121,6 +125,8 @@ def test_model_matches_checker():
             b0, b150, _ = expected_payload_bytes(keys[vis], stamp[vis])
             assert np.array_equal(pay[vis][:, 0], b0) and np.array_equal(pay[vis][:, 150], b150)
             check_against_model(snap, N, 0, N, model, read_ts, 64, 20000, seed=read_ts)
+            sk = u32_keys(rank_to_key(N, np.random.default_rng(read_ts).integers(0, N, 24)))
+            assert_scan_equal(snap.scan(sk, 1000, read_ts, 1), t.scan(sk, 1000, read_ts, 1), f"scan vs checker ts={read_ts}")
 
 
 def test_config2_full_size_10m():

@@ -117,3 +117,38 @@ def test_refresh_needs_a_tree_snapshot():
         t = ycsb_int_table(pyoracle.OracleTable, 1000, 64)
         with pytest.raises(sg.StageError):
             snap.refresh_from_tree(t.root)              # generated snapshots carry no host fingerprints
+
+
+# ---- snapshots with writers in flight --------------------------------------------------------
+@pytest.mark.skipif(not pyoracle.have_ref(), reason="needs the live reference (EphemeralPool undo copies)")
+def test_snapshot_with_updates_in_flight_reads_the_undo_copies():
+    """Updates begun through the reference's LeafNode::Update and NOT finalized: BTree::Read serves the undo copy
+    (old payload, old commit id, saved chain). stage_gpu_snapshot_from_tree_live stages exactly that; the plain
+    from_tree refuses such a tree."""
+    N, P = 8000, 200
+    t = ycsb_int_table(pyoracle.RefTable, N, P)
+    rng = np.random.default_rng(44)
+    assert t.commit_update_batch(u32_keys(rng.integers(0, N, 1500)), 10) == 1500        # committed history first
+    assert t.commit_update_batch(u32_keys(rng.integers(0, N, 1500)), 2000) == 1500
+    probes = u32_keys(rng.integers(0, N + 20, 8000))
+    stamps = (0, 10, 800, 1509, 2000, 2900, 3499, 5000, 9000)
+    before = {ts: t.probe(probes, ts) for ts in stamps}
+    sk = u32_keys(rng.integers(0, N, 48))
+    scans_before = {ts: t.scan(sk, 120, ts, 1) for ts in stamps}
+    # 300 updates in flight, half of them on rows that already have a committed chain
+    flying = rng.choice(N, 300, replace=False).astype(np.uint32)
+    flying_before = t.probe(u32_keys(flying), 9000)
+    for i, k in enumerate(flying):                         # new bytes differ from every committed byte of the row
+        assert t.begin_update(u32_keys([k])[0], np.full(P, (int(k) & 0xFF) ^ 0x5A, np.uint8), 7000 + i) == 0
+    with pytest.raises(sg.StageError):
+        sg.Snapshot.from_tree(t.root, 4, P)                                            # not quiesced
+    fn, ctx = t.undo_resolver()
+    with sg.Snapshot.from_tree_live(t.root, 4, P, fn, ctx) as snap:
+        assert snap.info().n_rows == N
+        for ts in stamps:
+            now = t.probe(probes, ts)                      # the reference, writers still in flight
+            assert_probe_equal(snap.probe(probes, ts), now, f"in-flight probe ts={ts}")
+            assert_probe_equal(now, before[ts], f"reference serves the committed state ts={ts}")
+            # scans: the snapshot holds the committed rows (the reference's iterator would read dirty bytes)
+            assert_scan_equal(snap.scan(sk, 120, ts, 1), scans_before[ts], f"in-flight scan ts={ts}")
+        assert_probe_equal(snap.probe(u32_keys(flying), 9000), flying_before, "no uncommitted bytes on the device")

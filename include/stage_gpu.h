@@ -215,7 +215,10 @@ int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint64_t n, uin
  * for scan_sizes[i] rows; its rows are written, in the reference's order, to row slots
  * [i*out_stride, i*out_stride + row_counts[i]) of key_out / ts_out / payload_out
  * (out_stride >= max scan size). Reproduces the iterator's slot-order truncation and
- * leaf-hop termination rules exactly. */
+ * leaf-hop termination rules exactly. apply_visibility = 1 is the executor's
+ * range rule: a row is returned iff read_ts >= the commit id of its in-leaf version; a newer row is
+ * dropped — the range branch never reaches a version chain, because the iterator's records carry no
+ * chain pointer (record_meta.h:240; only BTree::Read fills RecordMeta::next_tuple_ptr). */
 int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
                          uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts,
                          void *key_out, uint32_t *ts_out, void *payload_out, int flags);

@@ -732,7 +732,8 @@ def main():
         line = {
             "metric": "YCSB scan rows/s (1000-row MVCC range scans, 10M-tuple int table)",
             "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": total_ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+            "ms_per_step": total_ms_max / args.steps, "step_ms_median": float(np.median(step_ms)),
+            "step_ms_best": float(min(step_ms)), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": workload_config(args, world, table_desc),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

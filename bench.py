@@ -397,6 +397,10 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
     torch.cuda.set_device(local_rank)
+    numa = None
+    if world > 1 and not os.environ.get("STAGE_NO_NUMA_BIND"):
+        from stage_indexorganized_b200.numa import bind_to_gpu_node
+        numa = bind_to_gpu_node(local_rank)      # pinned e2e buffers local to this GPU's PCIe root
     dev = torch.device("cuda", local_rank)
     sg.init(local_rank)
     dist = None
@@ -688,7 +692,7 @@ def main():
     e2e = {"value": float(e_r.item()) / float(e_t.item()), "unit": "rows/s",
            "h2d_bytes_per_step": ne * (K_BYTES + 4),
            "d2h_bytes_per_step": ne * 4 + ne * S * (K_BYTES + 4 + P_BYTES),
-           "scans_per_step": ne}
+           "scans_per_step": ne, "rank0_seconds": e_sec, "numa_bind_rank0": numa}
 
     # ---- CPU baseline (rank 0, N = 1): the only part of the run that touches oracle/ ---------------------------
     cpu, transform, parity = None, None, None
@@ -719,6 +723,21 @@ def main():
         ok = all(np.array_equal(g, w) for g, w in zip(got, want)) and all(np.array_equal(g, w) for g, w in zip(gp, wp))
         parity = {"ok": bool(ok), "checked": f"{ns} scans x {S} rows (flattened host tree vs CPU {table_kind}) and "
                                              f"{len(pk)} probes (bench table vs CPU {table_kind}), bit-exact"}
+        if not use_host_tree:
+            # structural refresh: 10 k more committed updates on the host tree, then only the changed leaves are staged
+            uk2 = np.random.default_rng(99).integers(0, rows, 10_000).astype(np.uint32).view(np.uint8).reshape(-1, 4)
+            host_table.commit_update_batch(uk2, FIRST_CID + updates + 1000)
+            t0 = time.time()
+            nsnap, st = hsnap.refresh_from_tree(host_table.root)
+            t_rf = time.time() - t0
+            ts2 = FIRST_CID + updates + 6000
+            ok2 = all(np.array_equal(g, w) for g, w in zip(nsnap.scan(sk[:64], S, ts2, 1), host_table.scan(sk[:64], S, ts2, 1)))
+            transform["refresh_after_10k_updates"] = {
+                "seconds": t_rf, "leaves_transformed": int(st.leaves_transformed), "leaves_carried": int(st.leaves_carried),
+                "host_MB_staged": st.host_bytes_staged / 1e6, "parity_ok": bool(ok2),
+                "note": "stage_gpu_snapshot_refresh_from_tree: unchanged leaves carried over on the device"}
+            parity["ok"] = bool(parity["ok"] and ok2)
+            nsnap.close()
         if hsnap is not snap:
             hsnap.close()
 

@@ -50,7 +50,7 @@ PROBE_HIT_BYTES = K_BYTES + 2 * (K_BYTES + P_BYTES + 4)
 PROBE_MISS_BYTES = K_BYTES + 1
 # dram__bytes_read.sum + dram__bytes_write.sum of one gather_rows_kernel launch of the default workload, from the
 # committed `ncu --set full` capture (profiles/); None until a capture of the current kernel exists.
-NCU_TRAFFIC_PER_LAUNCH = 7.769e9   # profiles/r1_v2_ncu_summary_scan.txt: 3.939 GB read + 3.851 GB written
+NCU_TRAFFIC_PER_LAUNCH = 7.769e9   # profiles/r1_v10_ncu_summary.txt: 3.925 GB read + 3.844 GB written
 
 
 def parse_args():

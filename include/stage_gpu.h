@@ -128,6 +128,12 @@ typedef struct {
 } stage_refresh_stats_t;
 int stage_gpu_snapshot_refresh_from_tree(stage_snapshot_t *old, const void *root, stage_snapshot_t **out,
                                          stage_refresh_stats_t *stats /* may be NULL */);
+/* Same, with writers in flight: in-flight records of the changed leaves are staged from their undo copies
+ * (stage_gpu_snapshot_from_tree_live above). Together: a snapshot kept current without ever stopping the update
+ * transactions — only structural changes (splits) must not be running during the call. */
+int stage_gpu_snapshot_refresh_from_tree_live(stage_snapshot_t *old, const void *root, stage_undo_resolver_t resolve,
+                                              void *resolve_ctx, stage_snapshot_t **out,
+                                              stage_refresh_stats_t *stats /* may be NULL */);
 
 /* Streaming construction for callers that own the walk (same result as from_tree):
  *   begin -> add_versions* -> add_leaves* -> seal.

@@ -109,10 +109,15 @@ public:
 
     // After the host tree took committed inserts / updates / deletes (quiesced again): swap in the next snapshot.
     // Only the leaves that changed are staged again (stage_gpu_snapshot_refresh_from_tree).
-    stage_refresh_stats_t Refresh(const void *root) {
+    // With `resolve` (see the second constructor) update transactions may stay in flight during the call.
+    stage_refresh_stats_t Refresh(const void *root, stage_undo_resolver_t resolve = nullptr, void *resolve_ctx = nullptr) {
         stage_snapshot_t *next = nullptr;
         stage_refresh_stats_t st{};
-        check(stage_gpu_snapshot_refresh_from_tree(snap_, root, &next, &st), "stage_gpu_snapshot_refresh_from_tree");
+        if (resolve)
+            check(stage_gpu_snapshot_refresh_from_tree_live(snap_, root, resolve, resolve_ctx, &next, &st),
+                  "stage_gpu_snapshot_refresh_from_tree_live");
+        else
+            check(stage_gpu_snapshot_refresh_from_tree(snap_, root, &next, &st), "stage_gpu_snapshot_refresh_from_tree");
         stage_gpu_snapshot_destroy(snap_);
         snap_ = next;
         return st;

@@ -55,6 +55,7 @@ SYMBOLS = {
     "stage_gpu_snapshot_from_tree": (_i32, [_vp, C.POINTER(Schema), C.POINTER(_vp)]),
     "stage_gpu_snapshot_from_tree_live": (_i32, [_vp, C.POINTER(Schema), _vp, _vp, C.POINTER(_vp)]),
     "stage_gpu_snapshot_refresh_from_tree": (_i32, [_vp, _vp, C.POINTER(_vp), C.POINTER(RefreshStats)]),
+    "stage_gpu_snapshot_refresh_from_tree_live": (_i32, [_vp, _vp, _vp, _vp, C.POINTER(_vp), C.POINTER(RefreshStats)]),
     "stage_gpu_snapshot_begin": (_i32, [C.POINTER(Schema), _u64, _u64, C.POINTER(_vp)]),
     "stage_gpu_snapshot_add_versions": (_i32, [_vp, _vp, _vp, _u64]),
     "stage_gpu_snapshot_add_leaves": (_i32, [_vp, _vp, _vp, _vp, _vp, _u64]),
@@ -199,11 +200,16 @@ class Snapshot:
                                                        _vp(int(resolve_ctx)), C.byref(h)))
         return cls(h, sc)
 
-    def refresh_from_tree(self, root):
+    def refresh_from_tree(self, root, resolve_fn=None, resolve_ctx=0):
         """New snapshot of the same host tree after committed inserts / updates / deletes (and the splits they
-        caused); unchanged leaves are carried over on the device. Returns (snapshot, RefreshStats); self stays valid."""
+        caused); unchanged leaves are carried over on the device. Returns (snapshot, RefreshStats); self stays valid.
+        With resolve_fn (see from_tree_live) update transactions may be in flight during the call."""
         h, st = _vp(), RefreshStats()
-        _check(lib().stage_gpu_snapshot_refresh_from_tree(self.h, _vp(int(root)), C.byref(h), C.byref(st)))
+        if resolve_fn:
+            _check(lib().stage_gpu_snapshot_refresh_from_tree_live(self.h, _vp(int(root)), _vp(int(resolve_fn)),
+                                                                   _vp(int(resolve_ctx)), C.byref(h), C.byref(st)))
+        else:
+            _check(lib().stage_gpu_snapshot_refresh_from_tree(self.h, _vp(int(root)), C.byref(h), C.byref(st)))
         return type(self)(h, self.schema), st
 
     @classmethod

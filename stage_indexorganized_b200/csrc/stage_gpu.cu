@@ -843,8 +843,8 @@ extern "C" int stage_gpu_snapshot_from_tree_live(const void *root, const stage_s
 // deletes and the leaf splits they caused. Unchanged leaves (same address, same fingerprint) are carried over on
 // the device; only changed and new leaves cross PCIe and go through the transform kernel again.
 // ------------------------------------------------------------------------------------------------
-extern "C" int stage_gpu_snapshot_refresh_from_tree(stage_snapshot_t *old, const void *root, stage_snapshot_t **out,
-                                                    stage_refresh_stats_t *stats) {
+static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_resolver_t resolve, void *resolve_ctx,
+                        stage_snapshot_t **out, stage_refresh_stats_t *stats) {
     if (!old || !root || !out) return STAGE_ERR_ARG;
     if (!old->sealed || old->h_leaf_addr.size() != old->n_leaves || old->h_leaf_off.size() != old->n_leaves + 1)
         return STAGE_ERR_STATE;                       // only snapshots that came from a host tree carry fingerprints
@@ -893,11 +893,55 @@ extern "C" int stage_gpu_snapshot_refresh_from_tree(stage_snapshot_t *old, const
         work(0, L / T);
         for (auto &x : th) x.join();
     }
-    uint64_t n_rows = 0;
-    for (size_t j = 0; j < L; ++j) {
-        n_rows += vis[j];
+    for (size_t j = 0; j < L; ++j)
         if (src_leaf[j] == kNoLeaf) changed.push_back((uint32_t) j);
+    rc = STAGE_OK;
+    // 1b. changed leaves: version chains (new indices follow the previous table) and in-flight records
+    ChainStager cs;
+    cs.base = (uint32_t) old->n_versions;
+    std::vector<uint32_t> heads_flat;
+    std::vector<int64_t> heads_at(changed.size(), -1);
+    std::vector<uint32_t> heads;
+    std::vector<InflightPatch> patches;
+    std::vector<std::pair<size_t, uint32_t>> patch_at(changed.size(), {0, 0});
+    std::vector<uint32_t> dropped(changed.size(), 0);            // in-flight rows without an undo copy
+    for (size_t c = 0; c < changed.size() && !rc; ++c) {
+        const uint8_t *leaf = w.leaves[changed[c]];
+        uint64_t status;
+        memcpy(&status, leaf + kOffStatus, 8);
+        const uint32_t count = status_record_count(status);
+        if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize > ls) { rc = STAGE_ERR_LAYOUT; break; }
+        heads.assign(count, 0);
+        bool any = false;
+        for (uint32_t i = 0; i < count; ++i) {
+            uint64_t m, nx;
+            memcpy(&m, leaf + kOffMeta + (size_t) i * kMetaSize, 8);
+            memcpy(&nx, leaf + kOffMeta + (size_t) i * kMetaSize + kMetaNextPtr, 8);
+            if (!meta_visible(m)) continue;
+            if ((m & kMetaControl) && !resolve) { rc = STAGE_ERR_NOT_QUIESCED; break; }   // next_ptr is an undo copy
+            if (m & kMetaControl) {                               // in flight: stage what BTree::Read serves (f2)
+                uint64_t saved_next = 0;
+                const void *old_rec = nullptr;
+                const bool have = nx != 0 && nx != UINT64_MAX && resolve(resolve_ctx, nx, &saved_next, &old_rec) == 1 && old_rec;
+                if (patch_at[c].second == 0) patch_at[c].first = patches.size();
+                patch_at[c].second++;
+                patches.push_back({i, have ? static_cast<const uint8_t *>(old_rec) + meta_key_len(m) : nullptr});
+                if (!have) dropped[c]++;
+                nx = have ? saved_next : 0;
+            }
+            if (nx == 0 || nx == UINT64_MAX) continue;
+            heads[i] = cs.add_chain(nx);
+            any = true;
+        }
+        if (any) {
+            heads_at[c] = (int64_t) heads_flat.size();
+            heads_flat.insert(heads_flat.end(), heads.begin(), heads.end());
+        }
     }
+    if (rc) return rc;
+    uint64_t n_rows = 0;
+    for (size_t c = 0; c < changed.size(); ++c) vis[changed[c]] -= dropped[c];
+    for (size_t j = 0; j < L; ++j) n_rows += vis[j];
 
     stage_snapshot *s = nullptr;
     if ((rc = stage_gpu_snapshot_begin(schema, L, n_rows, &s))) return rc;
@@ -943,35 +987,7 @@ extern "C" int stage_gpu_snapshot_refresh_from_tree(stage_snapshot_t *old, const
         g_launches.fetch_add(1);
     }
 
-    // 3. changed leaves: chains (new version indices follow the previous table), images, transform
-    ChainStager cs;
-    cs.base = (uint32_t) old->n_versions;
-    std::vector<uint32_t> heads_flat;
-    std::vector<int64_t> heads_at(changed.size(), -1);
-    std::vector<uint32_t> heads;
-    for (size_t c = 0; c < changed.size() && !rc; ++c) {
-        const uint8_t *leaf = w.leaves[changed[c]];
-        uint64_t status;
-        memcpy(&status, leaf + kOffStatus, 8);
-        const uint32_t count = status_record_count(status);
-        if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize > ls) { rc = STAGE_ERR_LAYOUT; break; }
-        heads.assign(count, 0);
-        bool any = false;
-        for (uint32_t i = 0; i < count; ++i) {
-            uint64_t m, nx;
-            memcpy(&m, leaf + kOffMeta + (size_t) i * kMetaSize, 8);
-            memcpy(&nx, leaf + kOffMeta + (size_t) i * kMetaSize + kMetaNextPtr, 8);
-            if (!meta_visible(m)) continue;
-            if (m & kMetaControl) { rc = STAGE_ERR_NOT_QUIESCED; break; }     // next_ptr is an undo copy, not a chain
-            if (nx == 0 || nx == UINT64_MAX) continue;
-            heads[i] = cs.add_chain(nx);
-            any = true;
-        }
-        if (any) {
-            heads_at[c] = (int64_t) heads_flat.size();
-            heads_flat.insert(heads_flat.end(), heads.begin(), heads.end());
-        }
-    }
+    // 3. changed leaves: images, transform
     if (!rc && !changed.empty()) {
         if (cudaMalloc((void **) &d_changed, changed.size() * 4) != cudaSuccess) rc = STAGE_ERR_NOMEM;
         else if (cudaMemcpyAsync(d_changed, changed.data(), changed.size() * 4, cudaMemcpyHostToDevice, st) != cudaSuccess)
@@ -990,6 +1006,10 @@ extern "C" int stage_gpu_snapshot_refresh_from_tree(stage_snapshot_t *old, const
                 const size_t c = c0 + j;
                 LeafExtras ex;
                 ex.heads = heads_at[c] >= 0 ? heads_flat.data() + heads_at[c] : nullptr;
+                if (patch_at[c].second) {
+                    ex.patches = patches.data() + patch_at[c].first;
+                    ex.n_patches = patch_at[c].second;
+                }
                 rcs[j] = stage_copy_leaf(s, s->h_stage[buf] + (size_t) j * ls, w.leaves[changed[c]], ex, &cvis[j], &ccnt[j]);
             }
         };
@@ -1075,6 +1095,17 @@ extern "C" int stage_gpu_snapshot_refresh_from_tree(stage_snapshot_t *old, const
     }
     *out = s;
     return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_refresh_from_tree(stage_snapshot_t *old, const void *root, stage_snapshot_t **out,
+                                                    stage_refresh_stats_t *stats) {
+    return refresh_impl(old, root, nullptr, nullptr, out, stats);
+}
+extern "C" int stage_gpu_snapshot_refresh_from_tree_live(stage_snapshot_t *old, const void *root,
+                                                         stage_undo_resolver_t resolve, void *resolve_ctx,
+                                                         stage_snapshot_t **out, stage_refresh_stats_t *stats) {
+    if (!resolve) return STAGE_ERR_ARG;
+    return refresh_impl(old, root, resolve, resolve_ctx, out, stats);
 }
 
 // ------------------------------------------------------------------------------------------------

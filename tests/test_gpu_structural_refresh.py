@@ -138,6 +138,7 @@ def test_snapshot_with_updates_in_flight_reads_the_undo_copies():
     # 300 updates in flight, half of them on rows that already have a committed chain
     flying = rng.choice(N, 300, replace=False).astype(np.uint32)
     flying_before = t.probe(u32_keys(flying), 9000)
+    quiesced = sg.Snapshot.from_tree(t.root, 4, P)         # taken before the writers start
     for i, k in enumerate(flying):                         # new bytes differ from every committed byte of the row
         assert t.begin_update(u32_keys([k])[0], np.full(P, (int(k) & 0xFF) ^ 0x5A, np.uint8), 7000 + i) == 0
     with pytest.raises(sg.StageError):
@@ -152,3 +153,14 @@ def test_snapshot_with_updates_in_flight_reads_the_undo_copies():
             # scans: the snapshot holds the committed rows (the reference's iterator would read dirty bytes)
             assert_scan_equal(snap.scan(sk, 120, ts, 1), scans_before[ts], f"in-flight scan ts={ts}")
         assert_probe_equal(snap.probe(u32_keys(flying), 9000), flying_before, "no uncommitted bytes on the device")
+    # refreshing the earlier, quiesced snapshot while the writers are in flight: the leaves they touched are staged
+    # again (their metadata changed) from the undo copies, everything else is carried over; same answers
+    with quiesced:
+        with pytest.raises(sg.StageError):
+            quiesced.refresh_from_tree(t.root)
+        nxt, st = quiesced.refresh_from_tree(t.root, fn, ctx)
+        with nxt:
+            assert st.rows == N and 0 < st.leaves_transformed <= st.leaves_total
+            for ts in stamps:
+                assert_probe_equal(nxt.probe(probes, ts), before[ts], f"live refresh probe ts={ts}")
+                assert_scan_equal(nxt.scan(sk, 120, ts, 1), scans_before[ts], f"live refresh scan ts={ts}")

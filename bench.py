@@ -62,6 +62,10 @@ def parse_args():
     ap.add_argument("--rows", type=int, default=10_000_000, help="tuples per GPU at N = 1 (BASELINE configs[1])")
     ap.add_argument("--rows-multi", type=int, default=125_000_000,
                     help="tuples per GPU at N > 1 (BASELINE configs[4]: 1 B tuples over 8 GPUs)")
+    ap.add_argument("--read-ts", choices=["first", "mid", "latest"], default="mid",
+                    help="read id of the timed scans / probes relative to the update commit ids (SURVEY 8d config 2)")
+    ap.add_argument("--table-scan", action="store_true",
+                    help="scans without the visibility filter (TableScanExecutor semantics) instead of IndexScanExecutor's")
     ap.add_argument("--routed-scans", type=int, default=1024,
                     help="N > 1: scans per GPU per step of the routed-scan leg (start keys over the global table); 0 = skip")
     ap.add_argument("--a2a-steps", type=int, default=2, help="steps of the NCCL all-to-all comparison leg (N > 1)")
@@ -159,8 +163,8 @@ def build_host_table(rows, updates):
     return t, kind
 
 
-def cpu_scan_sample(table, start_keys, scan_size, read_ts, threads):
-    sec, rows = table.time_scan(start_keys, scan_size, read_ts, 1, threads, pin=True)
+def cpu_scan_sample(table, start_keys, scan_size, read_ts, threads, vis=1):
+    sec, rows = table.time_scan(start_keys, scan_size, read_ts, vis, threads, pin=True)
     return rows / sec, rows, sec
 
 
@@ -206,14 +210,15 @@ def run_reference(args, rank, world):
     threads = os.cpu_count() or 1
     rows = args.rows
     updates = rows // 10
-    read_ts = 10 + updates // 2
+    read_ts = {"first": FIRST_CID, "mid": FIRST_CID + updates // 2, "latest": FIRST_CID + updates}[args.read_ts]
+    vis = 0 if args.table_scan else 1
     table, kind = build_host_table(rows, updates)
     # each step is a bounded sample: ~4 s of work on all host threads
     n = args.cpu_scans or calibrated_scan_count(table, rows, args.scan_size, read_ts, threads, 4.0)
     times, total_rows = [], 0
     for step in range(args.warmup + args.steps):
         sk = scan_start_keys(rows, n, seed=100 + step).view(np.uint8).reshape(-1, 4)
-        rps, r, sec = cpu_scan_sample(table, sk, args.scan_size, read_ts, threads)
+        rps, r, sec = cpu_scan_sample(table, sk, args.scan_size, read_ts, threads, vis)
         if step >= args.warmup:
             times.append(sec)
             total_rows += r
@@ -237,7 +242,9 @@ def workload_config(args, world, table):
             "rows_per_gpu": args.rows, "payload_bytes": P_BYTES, "key_bytes": K_BYTES,
             "scans_per_step_per_gpu": args.scans, "scan_size": args.scan_size,
             "probes_per_step_per_gpu": args.probes, "updates_per_gpu": args.rows // 10,
-            "read_ts": "middle of the update commit ids", "table": table,
+            "read_ts": {"first": "first update commit id", "mid": "middle of the update commit ids",
+                        "latest": "last update commit id"}[args.read_ts],
+            "visibility": "none (TableScanExecutor)" if args.table_scan else "IndexScanExecutor range rule", "table": table,
             "partitioning": f"range x{world}" if world > 1 else "single shard",
             "l2": "inputs larger than L2 (table >= 10 GB, 4 GB of rows written per step); no explicit flush"}
 
@@ -416,7 +423,8 @@ def main():
     use_host_tree = world == 1 and args.table == "host"
     host_table, table_kind = None, None
     t_build0 = time.time()
-    read_ts = FIRST_CID + updates // 2
+    read_ts = {"first": FIRST_CID, "mid": FIRST_CID + updates // 2, "latest": FIRST_CID + updates}[args.read_ts]
+    vis = 0 if args.table_scan else 1
     if not use_host_tree:
         # product-only construction: the table is generated on the device in the reference's row function and key
         # order, then the committed updates are installed by the refresh kernels (version chains on 10 % of rows)
@@ -461,7 +469,7 @@ def main():
     d_payout = torch.empty((n_scans * S * P_BYTES,), dtype=torch.uint8, device=dev)
 
     def scan_step(b):
-        snap.scan_device(d_sk[b], d_sizes, n_scans, S, read_ts, 1, d_counts[b], d_keyout, d_tsout, d_payout)
+        snap.scan_device(d_sk[b], d_sizes, n_scans, S, read_ts, vis, d_counts[b], d_keyout, d_tsout, d_payout)
 
     def barrier():
         if dist is not None:
@@ -672,7 +680,7 @@ def main():
 
     def e2e_step(b):
         sg._check(sg.lib().stage_gpu_scan_batch(snap.h, h_sk.array[b].ctypes.data, h_sizes.ctypes.data, ne, S, read_ts,
-                                                1, h_counts.ptr, h_key.ptr, h_ts.ptr, h_pay.ptr, sg.IO_HOST))
+                                                vis, h_counts.ptr, h_key.ptr, h_ts.ptr, h_pay.ptr, sg.IO_HOST))
         return int(h_counts.array.sum())
 
     for b in range(min(args.warmup, 2)):
@@ -702,7 +710,7 @@ def main():
         threads = os.cpu_count() or 1
         n_cpu = args.cpu_scans or calibrated_scan_count(host_table, rows, S, read_ts, threads, 15.0)
         sk = scan_start_keys(rows, n_cpu, seed=100 + args.warmup).view(np.uint8).reshape(-1, 4)
-        rps, r, sec = cpu_scan_sample(host_table, sk, S, read_ts, threads)
+        rps, r, sec = cpu_scan_sample(host_table, sk, S, read_ts, threads, vis)
         cpu = {"value": rps, "unit": "rows/s", "cores": threads, "kind": table_kind,
                "sample": f"{n_cpu} scans x {S} rows ({r} rows, {sec:.1f} s), {threads} pinned threads, "
                          "table built by the reference loader with the same rows and the same committed updates"}
@@ -716,8 +724,8 @@ def main():
                          "leaf_image_GB_per_s": hi.n_leaves * 65536 / t_tr / 1e9,
                          "note": "stage_gpu_snapshot_from_tree: host walk + pinned staging + H2D + leaf_transform_kernel"}
         ns = 256
-        got = hsnap.scan(sk[:ns], S, read_ts, 1)
-        want = host_table.scan(sk[:ns], S, read_ts, 1)
+        got = hsnap.scan(sk[:ns], S, read_ts, vis)
+        want = host_table.scan(sk[:ns], S, read_ts, vis)
         pk = pk_all[0][:65536].astype(np.uint32).view(np.uint8).reshape(-1, 4)
         gp, wp = snap.probe(pk, read_ts), host_table.probe(pk, read_ts)
         ok = all(np.array_equal(g, w) for g, w in zip(got, want)) and all(np.array_equal(g, w) for g, w in zip(gp, wp))

@@ -56,7 +56,7 @@ NCU_TRAFFIC_PER_LAUNCH = 7.769e9   # profiles/r1_v10_ncu_summary.txt: 3.925 GB r
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rows", type=int, default=10_000_000, help="tuples per GPU at N = 1 (BASELINE configs[1])")

@@ -185,10 +185,10 @@ __device__ __forceinline__ void load_segments(const ExchangeView &x, uint32_t *s
 
 // Search + MVCC over everything posted to this rank. found / commit id go straight to the requester's slab;
 // the payload row to move and its destination are handed to exchange_gather_kernel.
-template <int NW, int kProbePerLane>
+template <int NW, int kProbePerLane, bool kDir = false>
 __global__ void __launch_bounds__(kProbeThreads) exchange_serve_kernel(SnapshotView v, ExchangeView x, ServeArgs a) {
     extern __shared__ __align__(16) uint32_t s_top[];
-    load_top_level(v, s_top, NW);
+    if constexpr (!kDir) load_top_level(v, s_top, NW);
     if (a.device_sync)
         cta_wait_flags(reinterpret_cast<const uint32_t *>(x.arena[x.rank] + x.lay.off_posted), x.world, a.epoch, x.err);
     __shared__ uint32_t off[kMaxExchangeRanks + 1];
@@ -215,7 +215,13 @@ __global__ void __launch_bounds__(kProbeThreads) exchange_serve_kernel(SnapshotV
                 dst[p] = (s << kDstRankShift) | (req[slot] & kDstIndexMask);
             }
         }
-        fence_search<NW, kProbePerLane>(v, s_top, k, c, hit);
+        if constexpr (kDir) {
+            dir_lookup<NW, kProbePerLane>(v, k, c, hit);
+#pragma unroll
+            for (int p = 0; p < kProbePerLane; ++p) hit[p] = hit[p] && g0 + p * stride < total;
+        } else {
+            fence_search<NW, kProbePerLane>(v, s_top, k, c, hit);
+        }
         uint32_t t[kProbePerLane];
 #pragma unroll
         for (int p = 0; p < kProbePerLane; ++p) t[p] = hit[p] ? __ldg(v.ts + c[p]) : 0u;

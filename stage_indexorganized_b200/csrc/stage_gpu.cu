@@ -118,6 +118,8 @@ struct stage_snapshot {
     uint32_t *d_ver_begin = nullptr, *d_ver_commit = nullptr, *d_ver_next = nullptr;
     uint8_t *d_ver_payload = nullptr;
     uint32_t *d_err = nullptr;
+    uint2 *d_dir = nullptr;                     // point-probe directory (probe.cuh), built at seal time
+    uint32_t dir_cap = 0;
 
     // streaming build state
     std::vector<uint32_t> h_leaf_off;           // [n_leaves+1]
@@ -201,7 +203,7 @@ static void snapshot_free(stage_snapshot *s) {
     cudaSetDevice(s->device);
     void *ptrs[] = {s->d_skey, s->d_slot, s->d_ts, s->d_chain, s->d_payload, s->d_leaf_off, s->d_sep, s->d_cont,
                     s->d_has_sep, s->d_ver_begin, s->d_ver_commit, s->d_ver_next, s->d_ver_payload,
-                    s->d_err, s->d_stage[0], s->d_stage[1], s->d_raw_keys, s->d_phys};
+                    s->d_err, s->d_stage[0], s->d_stage[1], s->d_raw_keys, s->d_phys, s->d_dir};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     free(s->ext_ver_payload);
@@ -541,6 +543,32 @@ static void fill_view(stage_snapshot *s) {
     v.n_rows = s->n_rows; v.n_leaves = s->n_leaves;
     v.key_size = s->schema.key_size; v.payload_size = s->schema.payload_size; v.xormask = s->xormask;
     v.max_leaf_rows = s->max_leaf_rows;
+    v.dir = s->d_dir; v.dir_cap = s->dir_cap;
+}
+
+// point-probe directory over the sealed key column (probe.cuh); STAGE_PROBE_DIR=0 keeps the fence search
+static int build_directory(stage_snapshot *s) {
+    static const bool off = getenv("STAGE_PROBE_DIR") && atoi(getenv("STAGE_PROBE_DIR")) == 0;
+    if (off || s->n_rows == 0 || s->n_rows > 0x7FFFFFF0ull) return STAGE_OK;
+    if (s->d_dir) { cudaFree(s->d_dir); s->d_dir = nullptr; }
+    const uint32_t cap = (uint32_t) (2 * s->n_rows + 64);
+    if (dev_alloc(s, &s->d_dir, cap) != STAGE_OK) {          // optional structure: fall back to the fences
+        cudaGetLastError();
+        s->d_dir = nullptr;
+        return STAGE_OK;
+    }
+    s->dir_cap = cap;
+    CUDA_TRY(cudaMemsetAsync(s->d_dir, 0xFF, (size_t) cap * 8, s->stream));
+    const unsigned blocks = (unsigned) ((s->n_rows + 255) / 256);
+    unsigned long long *d = reinterpret_cast<unsigned long long *>(s->d_dir);
+    switch (s->nw) {
+        case 1: dir_build_kernel<1><<<blocks, 256, 0, s->stream>>>(s->d_skey, s->n_rows, d, cap); break;
+        case 2: dir_build_kernel<2><<<blocks, 256, 0, s->stream>>>(s->d_skey, s->n_rows, d, cap); break;
+        case 4: dir_build_kernel<4><<<blocks, 256, 0, s->stream>>>(s->d_skey, s->n_rows, d, cap); break;
+        default: dir_build_kernel<8><<<blocks, 256, 0, s->stream>>>(s->d_skey, s->n_rows, d, cap); break;
+    }
+    LAUNCH_CHECK();
+    return STAGE_OK;
 }
 
 static int finish_seal(stage_snapshot *s) {
@@ -552,6 +580,7 @@ static int finish_seal(stage_snapshot *s) {
         default: rc = build_levels<8>(s); break;
     }
     if (rc) return rc;
+    if ((rc = build_directory(s))) return rc;
     fill_view(s);
     uint32_t err = 0;
     CUDA_TRY(cudaMemcpyAsync(&err, s->d_err, 4, cudaMemcpyDeviceToHost, s->stream));
@@ -1518,6 +1547,23 @@ static int launch_gather(stage_snapshot *s, const uint32_t *src_row, uint64_t n_
 
 template <int NW>
 static int launch_probe(stage_snapshot *s, const ProbeArgs &a) {
+    static const int ppl = getenv("STAGE_PROBE_PPL") ? atoi(getenv("STAGE_PROBE_PPL")) : 4;
+    const uint64_t want_blocks = (a.n + kProbeThreads * ppl - 1) / (kProbeThreads * ppl);
+    if (s->view.dir) {
+        // directory lookup: no shared-memory top level
+        static int occd[9] = {0};
+        if (!occd[NW]) {
+            int o = 0;
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, probe_kernel<NW, 4, true>, kProbeThreads, 0));
+            occd[NW] = std::max(o, 1);
+        }
+        const unsigned blocks = (unsigned) std::min<uint64_t>(want_blocks, (uint64_t) sm_count() * occd[NW]);
+        if (ppl == 8) probe_kernel<NW, 8, true><<<blocks, kProbeThreads, 0, s->stream>>>(s->view, a);
+        else if (ppl == 4) probe_kernel<NW, 4, true><<<blocks, kProbeThreads, 0, s->stream>>>(s->view, a);
+        else probe_kernel<NW, 2, true><<<blocks, kProbeThreads, 0, s->stream>>>(s->view, a);
+        LAUNCH_CHECK();
+        return STAGE_OK;
+    }
     const size_t smem = (size_t) std::max<uint32_t>(s->view.smem_words, 4) * 4;
     // persistent grid: the CTAs that are resident at once; threads stride over the probes
     static int occ[9] = {0};
@@ -1526,8 +1572,6 @@ static int launch_probe(stage_snapshot *s, const ProbeArgs &a) {
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, probe_kernel<NW, 4>, kProbeThreads, kProbeTopBytes));
         occ[NW] = std::max(o, 1);
     }
-    static const int ppl = getenv("STAGE_PROBE_PPL") ? atoi(getenv("STAGE_PROBE_PPL")) : 4;
-    const uint64_t want_blocks = (a.n + kProbeThreads * ppl - 1) / (kProbeThreads * ppl);
     const unsigned blocks = (unsigned) std::min<uint64_t>(want_blocks, (uint64_t) sm_count() * occ[NW]);
     if (ppl == 8) probe_kernel<NW, 8><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a);
     else if (ppl == 4) probe_kernel<NW, 4><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a);
@@ -2214,6 +2258,18 @@ extern "C" int stage_gpu_exchange_post_scans(stage_exchange_t *x, const void *sp
 
 template <int NW>
 static int launch_serve(stage_exchange *x, stage_snapshot *s, const ServeArgs &a, cudaStream_t st) {
+    // persistent grid: the inbox sizes are only known on the device
+    if (s->view.dir) {
+        static int occd[9] = {0};
+        if (!occd[NW]) {
+            int o = 0;
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, exchange_serve_kernel<NW, 4, true>, kProbeThreads, 0));
+            occd[NW] = std::max(o, 1);
+        }
+        exchange_serve_kernel<NW, 4, true><<<sm_count() * occd[NW], kProbeThreads, 0, st>>>(s->view, x->view, a);
+        LAUNCH_CHECK();
+        return STAGE_OK;
+    }
     const size_t smem = (size_t) std::max<uint32_t>(s->view.smem_words, 4) * 4;
     static int occ[9] = {0};
     if (!occ[NW]) {
@@ -2221,7 +2277,6 @@ static int launch_serve(stage_exchange *x, stage_snapshot *s, const ServeArgs &a
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, exchange_serve_kernel<NW, 4>, kProbeThreads, kProbeTopBytes));
         occ[NW] = std::max(o, 1);
     }
-    // persistent grid: the inbox sizes are only known on the device
     exchange_serve_kernel<NW, 4><<<sm_count() * occ[NW], kProbeThreads, smem, st>>>(s->view, x->view, a);
     LAUNCH_CHECK();
     return STAGE_OK;

@@ -149,11 +149,29 @@ def test_fused_probe_kernel_variant():
     import os
     import subprocess
     import sys
-    if os.environ.get("STAGE_PROBE_FUSED") == "1":
-        pytest.skip("already inside the variant run")
-    env = dict(os.environ, STAGE_PROBE_FUSED="1")
+    if os.environ.get("STAGE_VARIANT_RUN"):
+        pytest.skip("already inside a variant run")
+    env = dict(os.environ, STAGE_PROBE_FUSED="1", STAGE_VARIANT_RUN="1")
     r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-m", "gpu", "-k",
                         "probe or mvcc or other_key or generated"], env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
+
+
+def test_fence_search_probe_variant():
+    """Point probes normally locate rows through the seal-time directory (csrc/probe.cuh, dir_lookup); with
+    STAGE_PROBE_DIR=0 they descend the ordered fence levels like the scans do. Both must give the same bytes: the
+    probe tests of this file, the goldens and the routed probes are re-run in a child process with the directory off."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("STAGE_VARIANT_RUN"):
+        pytest.skip("already inside a variant run")
+    env = dict(os.environ, STAGE_PROBE_DIR="0", STAGE_VARIANT_RUN="1")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), os.path.join(here, "test_gpu_golden.py"),
+                        os.path.join(here, "test_gpu_exchange.py"), "-x", "-q", "-m", "gpu", "-k",
+                        "probe or mvcc or other_key or generated or golden"], env=env, capture_output=True, text=True,
+                       timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
 
 

@@ -32,7 +32,7 @@ __global__ void __launch_bounds__(kFusedThreads) probe_fused_kernel(SnapshotView
     extern __shared__ __align__(16) uint32_t s_top[];                 // top fence level (dynamic)
     __shared__ uint32_t s_row[kFusedStages][kFusedTile];
     __shared__ __align__(8) uint64_t s_full[kFusedStages], s_empty[kFusedStages];
-    load_top_level(v, s_top, NW);
+    if (!v.dir) load_top_level(v, s_top, NW);
     if (threadIdx.x == 0) {
         for (int i = 0; i < kFusedStages; ++i) {
             mbar_init(&s_full[i], kFusedProducerWarps);
@@ -61,7 +61,13 @@ __global__ void __launch_bounds__(kFusedThreads) probe_fused_kernel(SnapshotView
                 const uint64_t gi = g0 + 32 * p;
                 k[p] = gi < a.n ? to_sortable<NW>(a.keys + gi * K, K, v.xormask) : skey_inf<NW>();
             }
-            fence_search<NW, kFusedPPL>(v, s_top, k, c, hit);
+            if (v.dir) {
+                dir_lookup<NW, kFusedPPL>(v, k, c, hit);
+#pragma unroll
+                for (int p = 0; p < kFusedPPL; ++p) hit[p] = hit[p] && g0 + 32 * p < a.n;
+            } else {
+                fence_search<NW, kFusedPPL>(v, s_top, k, c, hit);
+            }
             uint32_t t[kFusedPPL];
 #pragma unroll
             for (int p = 0; p < kFusedPPL; ++p) t[p] = hit[p] ? __ldg(v.ts + c[p]) : 0u;

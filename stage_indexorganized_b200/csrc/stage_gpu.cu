@@ -549,7 +549,7 @@ static void fill_view(stage_snapshot *s) {
 // point-probe directory over the sealed key column (probe.cuh); STAGE_PROBE_DIR=0 keeps the fence search
 static int build_directory(stage_snapshot *s) {
     static const bool off = getenv("STAGE_PROBE_DIR") && atoi(getenv("STAGE_PROBE_DIR")) == 0;
-    if (off || s->n_rows == 0 || s->n_rows > 0x7FFFFFF0ull) return STAGE_OK;
+    if (off || s->n_rows == 0 || s->n_rows > 0x7FFFFF00ull) return STAGE_OK;      // 2n + 64 must fit 32 bits
     if (s->d_dir) { cudaFree(s->d_dir); s->d_dir = nullptr; }
     const uint32_t cap = (uint32_t) (2 * s->n_rows + 64);
     if (dev_alloc(s, &s->d_dir, cap) != STAGE_OK) {          // optional structure: fall back to the fences

@@ -360,6 +360,10 @@ def run_extra_workload(args):
     ms_scan = _time_steps(torch, lambda b: ol.scan_device(starts[b], sizes, ns, 10, 1, 1, counts, kout, tso, pout),
                           args.warmup, args.steps)
     rows = int(counts.sum().item())
+    ol.enable_timing(True)
+    ol.scan_device(starts[0], sizes, ns, 10, 1, 1, counts, kout, tso, pout)
+    ol_plan_ms, ol_gather_ms = ol.last_timing()
+    ol.enable_timing(False)
     rng = np.random.default_rng(3)
     n = args.probes
     pk = [torch.from_numpy(tpcc.stock_key(rng.integers(1, W + 1, n), rng.integers(1, tpcc.ITEMS + 1, n))).to(dev) for _ in range(nb)]
@@ -375,6 +379,7 @@ def run_extra_workload(args):
                                    f"{len(ok_)} rows (32/60), seeded row functions, bulk-loaded on device",
                        "order_line_scans_per_step": ns, "scan_size": 10, "stock_probes_per_step": n},
             "order_line_scan": {"rows_per_s": rows / (ms_scan * 1e-3), "scans_per_s": ns / (ms_scan * 1e-3), "ms_per_step": ms_scan,
+                                "plan_ms": ol_plan_ms, "gather_ms": ol_gather_ms,
                                 "achieved_GBps": rows * ol_row / (ms_scan * 1e-3) / 1e9, "frac_of_peak": rows * ol_row / (ms_scan * 1e-3) / 1e9 / peak},
             "stock_probe_full_row": {"probes_per_s": n / (ms_full * 1e-3), "ms_per_step": ms_full,
                                      "achieved_GBps": n * st_row / (ms_full * 1e-3) / 1e9, "frac_of_peak": n * st_row / (ms_full * 1e-3) / 1e9 / peak},

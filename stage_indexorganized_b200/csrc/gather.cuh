@@ -117,16 +117,30 @@ __global__ void __launch_bounds__(256) gather_cols_kernel(GatherColsArgs a) {
 // consecutive threads write consecutive words (fully coalesced stores) and read consecutive words of a source row.
 namespace stage {
 
-__global__ void __launch_bounds__(256) gather_rows_small_kernel(GatherArgs a, uint32_t words_per_row) {
-    const uint64_t w = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    const uint64_t slot = w / words_per_row;
-    if (slot >= a.n_slots) return;
-    const uint32_t row = __ldg(a.src_row + slot);
-    if (row == kNoRow) return;
-    const uint32_t k = (uint32_t) (w - slot * words_per_row);
-    const uint8_t *base = (row & kVersionRowFlag) ? a.ver_payload : a.payload;
-    const uint32_t *src = reinterpret_cast<const uint32_t *>(base + (uint64_t) (row & ~kVersionRowFlag) * a.payload_size);
-    reinterpret_cast<uint32_t *>(a.dst)[w] = __ldg(src + k);
+constexpr int kSmallWordsPerThread = 4;      // independent loads per thread, each warp access still fully coalesced
+
+// I = uint32_t when the batch has fewer than 2^32 words (32-bit index arithmetic: the divide is the hot instruction)
+template <typename I>
+__global__ void __launch_bounds__(256) gather_rows_small_kernel(GatherArgs a, uint32_t words_per_row, uint64_t n_words) {
+    const I base_w = (I) blockIdx.x * (I) (256 * kSmallWordsPerThread) + (I) threadIdx.x;
+    uint32_t val[kSmallWordsPerThread];
+    bool ok[kSmallWordsPerThread];
+#pragma unroll
+    for (int j = 0; j < kSmallWordsPerThread; ++j) {
+        const I w = base_w + (I) (j * 256);
+        ok[j] = false;
+        if ((uint64_t) w >= n_words) continue;
+        const I slot = w / (I) words_per_row;
+        const uint32_t row = __ldg(a.src_row + slot);
+        if (row == kNoRow) continue;
+        const uint32_t k = (uint32_t) (w - slot * (I) words_per_row);
+        const uint8_t *base = (row & kVersionRowFlag) ? a.ver_payload : a.payload;
+        val[j] = __ldg(reinterpret_cast<const uint32_t *>(base + (uint64_t) (row & ~kVersionRowFlag) * a.payload_size) + k);
+        ok[j] = true;
+    }
+#pragma unroll
+    for (int j = 0; j < kSmallWordsPerThread; ++j)
+        if (ok[j]) reinterpret_cast<uint32_t *>(a.dst)[(uint64_t) base_w + (uint64_t) (j * 256)] = val[j];
 }
 
 }  // namespace stage

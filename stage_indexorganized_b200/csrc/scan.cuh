@@ -327,25 +327,55 @@ __global__ void __launch_bounds__(kScanWarpThreads) scan_plan_warp_kernel(Snapsh
             if (a.key_out) from_sortable<NW>(load_skey<NW>(v.level[0], row), a.key_out + o * K, K, v.xormask);
         };
         if (S > 0 && L > 0) {
-            // start leaf: number of upper fences < begin, 32-ary search
-            uint32_t j0 = 0;
-            for (uint32_t n = L - 1; n > 0;) {
-                const uint32_t step = (n + 31) / 32;
-                const uint64_t idx = (uint64_t) j0 + (uint64_t) (lane + 1) * step - 1;
-                const bool lt = idx < (uint64_t) j0 + n && skey_less<NW>(load_skey<NW>(v.sep, idx), begin);
-                const uint32_t adv = __popc(__ballot_sync(FULL, lt)) * step;
-                n = min(step - 1, n - min(n, adv));
-                j0 += adv;
+            // A start key that IS a row (the usual case: the callers scan from keys they know) is found through the
+            // point-probe directory: its row is the scan's first row and its leaf is the one the fences would select
+            // (a leaf's keys lie in (sep[j-1], sep[j]]; an equal separator routes left). All lanes look the same slot up
+            // (broadcast loads). Then only a 32-ary search over the u32 leaf offsets is left, instead of ~5 KB of keys.
+            bool have_row = false;
+            uint32_t row0 = 0;
+            if (v.dir) {
+                const SKey<NW> kk[1] = {begin};
+                uint32_t cc[1];
+                bool hh[1];
+                dir_lookup<NW, 1>(v, kk, cc, hh);
+                have_row = hh[0];
+                row0 = cc[0];
             }
-            const uint32_t lo0 = v.leaf_off[j0], hi0 = v.leaf_off[j0 + 1];
-            uint32_t below = 0;                                   // rows of the start leaf with key < begin (sorted: 32-ary search)
-            for (uint32_t n = hi0 - lo0; n > 0;) {
-                const uint32_t step = (n + 31) / 32;
-                const uint64_t idx = (uint64_t) below + (uint64_t) (lane + 1) * step - 1;
-                const bool lt = idx < (uint64_t) below + n && skey_less<NW>(load_skey<NW>(v.level[0], (uint64_t) lo0 + idx), begin);
-                const uint32_t adv = __popc(__ballot_sync(FULL, lt)) * step;
-                n = min(step - 1, n - min(n, adv));
-                below += adv;
+            uint32_t j0 = 0, lo0, hi0, below = 0;
+            if (have_row) {
+                // start leaf: number of leaves that end at or before row0
+                for (uint32_t n = L; n > 0;) {
+                    const uint32_t step = (n + 31) / 32;
+                    const uint64_t idx = (uint64_t) j0 + (uint64_t) (lane + 1) * step - 1;
+                    const bool lt = idx < (uint64_t) j0 + n && __ldg(v.leaf_off + idx + 1) <= row0;
+                    const uint32_t adv = __popc(__ballot_sync(FULL, lt)) * step;
+                    n = min(step - 1, n - min(n, adv));
+                    j0 += adv;
+                }
+                lo0 = v.leaf_off[j0];
+                hi0 = v.leaf_off[j0 + 1];
+                below = row0 - lo0;
+            } else {
+                // start leaf: number of upper fences < begin, 32-ary search
+                for (uint32_t n = L - 1; n > 0;) {
+                    const uint32_t step = (n + 31) / 32;
+                    const uint64_t idx = (uint64_t) j0 + (uint64_t) (lane + 1) * step - 1;
+                    const bool lt = idx < (uint64_t) j0 + n && skey_less<NW>(load_skey<NW>(v.sep, idx), begin);
+                    const uint32_t adv = __popc(__ballot_sync(FULL, lt)) * step;
+                    n = min(step - 1, n - min(n, adv));
+                    j0 += adv;
+                }
+                lo0 = v.leaf_off[j0];
+                hi0 = v.leaf_off[j0 + 1];
+                // rows of the start leaf with key < begin (sorted: 32-ary search)
+                for (uint32_t n = hi0 - lo0; n > 0;) {
+                    const uint32_t step = (n + 31) / 32;
+                    const uint64_t idx = (uint64_t) below + (uint64_t) (lane + 1) * step - 1;
+                    const bool lt = idx < (uint64_t) below + n && skey_less<NW>(load_skey<NW>(v.level[0], (uint64_t) lo0 + idx), begin);
+                    const uint32_t adv = __popc(__ballot_sync(FULL, lt)) * step;
+                    n = min(step - 1, n - min(n, adv));
+                    below += adv;
+                }
             }
             const uint32_t q0 = lo0 + below;
             if (hi0 > q0) {

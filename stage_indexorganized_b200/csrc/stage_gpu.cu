@@ -1534,8 +1534,11 @@ static int launch_gather(stage_snapshot *s, const uint32_t *src_row, uint64_t n_
     if (g.payload_size <= 256 && (align & 3) == 0) {          // short rows: one thread per 32-bit word
         const uint32_t wpr = g.payload_size / 4;
         const uint64_t words = n_slots * wpr;
-        if ((words + 255) / 256 > 0x7FFFFFFFull) return STAGE_ERR_ARG;
-        gather_rows_small_kernel<<<(unsigned) ((words + 255) / 256), 256, 0, s->stream>>>(g, wpr);
+        const uint64_t per_cta = 256 * kSmallWordsPerThread;
+        const uint64_t ctas = (words + per_cta - 1) / per_cta;
+        if (ctas > 0x7FFFFFFFull) return STAGE_ERR_ARG;
+        if (words + per_cta < 0xFFFFFFFFull) gather_rows_small_kernel<uint32_t><<<(unsigned) ctas, 256, 0, s->stream>>>(g, wpr, words);
+        else gather_rows_small_kernel<uint64_t><<<(unsigned) ctas, 256, 0, s->stream>>>(g, wpr, words);
         LAUNCH_CHECK();
         return STAGE_OK;
     }

@@ -775,7 +775,9 @@ def main():
                          "launch_ms": sum(gather_ms) / args.steps,
                          "plan_kernel_ms": sum(plan_ms) / args.steps,
                          "step_algorithmic_bytes": algo_bytes / args.steps,
-                         "step_achieved": step_achieved, "step_frac": step_achieved / peak},
+                         "step_achieved": step_achieved, "step_frac": step_achieved / peak,
+                         "nominal_peak": 8000.0, "frac_of_nominal": achieved / 8000.0,
+                         "step_frac_of_nominal": step_achieved / 8000.0},
             "cpu_baseline": cpu,
             "parity_check": parity,
             "transform": transform,

@@ -316,7 +316,6 @@ __global__ void __launch_bounds__(kGatherThreads) exchange_gather_kernel(Exchang
     __shared__ uint32_t s_row[kGatherRows], s_dst[kGatherRows];
     __shared__ uint32_t off[kMaxExchangeRanks + 1];
     load_segments(x, off, a.seg_mul);
-    const uint32_t total = off[kMaxExchangeRanks];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = kGatherThreads / 32;
     const uint32_t nvec = P / (uint32_t) sizeof(V);
@@ -371,7 +370,6 @@ __global__ void __launch_bounds__(kGatherThreads) exchange_gather16_kernel(Excha
     __shared__ uint32_t s_row[kGatherRows], s_dst[kGatherRows];
     __shared__ uint32_t off[kMaxExchangeRanks + 1];
     load_segments(x, off, a.seg_mul);
-    const uint32_t total = off[kMaxExchangeRanks];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = kGatherThreads / 32;
     const uint32_t nfull = P / 16, tail8 = (P & 15u) >> 3;       // 16-byte chunks, then one optional 8-byte chunk

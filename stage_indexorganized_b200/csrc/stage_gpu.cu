@@ -777,7 +777,6 @@ static int from_tree_impl(const void *root, const stage_schema_t *schema, stage_
     ChainStager cs;
     std::vector<uint32_t> heads;
     std::vector<stage_version_t> &vers = cs.vers;
-    std::vector<uint64_t> &vslot = cs.vslot;
     // pass 1 (serial, metadata only): version indices in leaf / slot order
     std::vector<uint32_t> heads_flat;                 // chain heads of the leaves that have any
     std::vector<int64_t> heads_at(w.leaves.size(), -1);

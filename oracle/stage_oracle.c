@@ -6,6 +6,11 @@
  * inner-node growth/split) so that byte-identical trees can be built where /root/reference is absent.
  * All citations are relative to /root/reference.
  *
+ * PARITY PINNED (tests/test_oracle_golden.py): against golden vectors produced by the live, unmodified reference
+ * (tests/golden/make_golden.py; MVCC range scans there run the reference's own IndexScanExecutor), against the
+ * reference's known-answer tests for this path (test/testing_btree.cpp), and against the live reference library
+ * where it is present (leaf images byte for byte, probes, scans, read ids straddling the commit ids, deletes).
+ *
  * Node byte layout restated from include/vstore/b_tree.h:109-113, version_store.h:158-231,
  * record_meta.h:30-70 (sizes verified by compiling the reference):
  *   node+8  bool is_leaf        node+16 u32 size        node+20 u32 sorted_count

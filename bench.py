@@ -372,6 +372,11 @@ def run_extra_workload(args):
     qty = torch.empty((n, 4), dtype=torch.uint8, device=dev)
     ms_full = _time_steps(torch, lambda b: stock.probe_device(pk[b], n, 1, found, None, None, spay), args.warmup, args.steps)
     ms_col = _time_steps(torch, lambda b: stock.probe_column_device(pk[b], n, 1, 0, 4, qty, found), args.warmup, args.steps)
+    agg = [None]
+
+    def agg_step(b):
+        agg[0] = stock.probe_aggregate_i32(pk[b], 1, 0, 15, n=n)
+    ms_agg = _time_steps(torch, agg_step, args.warmup, args.steps)
     ol_row, st_row = 2 * (tpcc.OL_KEY + tpcc.OL_PAYLOAD + 4), tpcc.STOCK_KEY + 2 * (tpcc.STOCK_KEY + tpcc.STOCK_PAYLOAD + 4)
     line = {"metric": "TPC-C w=30 stock-level / Q2 read pattern", "value": rows / (ms_scan * 1e-3), "unit": "order_line rows/s",
             "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_scan, "dtype": "u8", "data": "synthetic",
@@ -385,6 +390,11 @@ def run_extra_workload(args):
                                      "achieved_GBps": n * st_row / (ms_full * 1e-3) / 1e9, "frac_of_peak": n * st_row / (ms_full * 1e-3) / 1e9 / peak},
             "stock_probe_quantity_pushdown": {"probes_per_s": n / (ms_col * 1e-3), "ms_per_step": ms_col,
                                               "bytes_returned_per_probe": 5},
+            "stock_probe_quantity_aggregate": {"probes_per_s": n / (ms_agg * 1e-3), "ms_per_step": ms_agg,
+                                               "bytes_returned_per_batch": 24, "found": int(agg[0].found),
+                                               "below_threshold_15": int(agg[0].below), "min_quantity": int(agg[0].min_value),
+                                               "note": "count(S_QUANTITY < 15) and MIN(S_QUANTITY) reduced on the device; "
+                                                       "includes the 24-byte D2H read and its synchronisation per batch"},
             "roofline": {"bound": "hbm", "peak": peak, "unit": "GB/s", "peak_source": peak_src}}
     print(json.dumps(line), flush=True)
     stock.close()

@@ -240,6 +240,18 @@ int stage_gpu_scan_project(stage_snapshot_t *s, const void *start_keys, const ui
                            uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts,
                            void *key_out, uint32_t col_off, uint32_t col_len, void *col_out, int flags);
 
+/* Predicate / aggregate push-down: probe the batch and reduce one little-endian int32 payload column (at byte col_off,
+ * any alignment) of the visible rows on the device. found = probes that hit a visible version, below = those whose
+ * column is < threshold (RunStockLevel's S_QUANTITY test, benchmark/tpcc/tpcc_stock_level.cpp:167-176), min / max over
+ * the found rows (CH-Q2*'s MIN(S_QUANTITY), benchmark/tpcc/tpcc_new_order.cpp:808-866; INT32_MAX / INT32_MIN when
+ * nothing was found). 24 bytes come back for the whole batch. `out` is a host pointer; keys follow `flags`. */
+typedef struct {
+    uint64_t found, below;
+    int32_t min_value, max_value;
+} stage_agg_i32_t;
+int stage_gpu_probe_aggregate_i32(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint32_t col_off,
+                                  int32_t threshold, stage_agg_i32_t *out, int flags);
+
 /* TableScanExecutor with scan_sz == -1 (include/execute/executor.h:581-619): the PHYSICAL whole-tree walk — leaves in
  * tree order, record slots in slot (insertion) order, no visibility test. Returns rows [first_row, first_row + n) of
  * that order (n_rows of stage_gpu_snapshot_info in total): latest in-leaf versions, keys, commit ids, payload rows.

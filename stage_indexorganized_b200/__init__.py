@@ -44,6 +44,10 @@ class SnapshotInfo(C.Structure):
                 ("key_words", _u32), ("n_levels", _u32), ("max_leaf_rows", _u32), ("device", _u32)]
 
 
+class AggI32(C.Structure):
+    _fields_ = [("found", _u64), ("below", _u64), ("min_value", C.c_int32), ("max_value", C.c_int32)]
+
+
 class RefreshStats(C.Structure):
     _fields_ = [("leaves_total", _u64), ("leaves_carried", _u64), ("leaves_transformed", _u64), ("rows", _u64),
                 ("versions_added", _u64), ("host_bytes_staged", _u64)]
@@ -77,6 +81,7 @@ SYMBOLS = {
     "stage_gpu_probe_batch": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp, _vp, _vp, _i32]),
     "stage_gpu_scan_batch": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _vp, _vp, _i32]),
     "stage_gpu_probe_project": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp, _u32, _u32, _vp, _i32]),
+    "stage_gpu_probe_aggregate_i32": (_i32, [_vp, _vp, _u64, _u32, _u32, C.c_int32, C.POINTER(AggI32), _i32]),
     "stage_gpu_scan_project": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _u32, _u32, _vp, _i32]),
     "stage_gpu_scan_physical": (_i32, [_vp, _u64, _u64, _vp, _vp, _vp, _i32]),
     "stage_gpu_route": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp]),
@@ -388,6 +393,18 @@ class Snapshot:
         _check(lib().stage_gpu_probe_project(self.h, _ptr(keys), n, read_ts, _ptr(found), _ptr(ts), col_off, col_len,
                                              _ptr(col), IO_HOST))
         return found, ts, col
+
+    def probe_aggregate_i32(self, keys, read_ts, col_off, threshold, n=None):
+        """Probe + reduce an int32 payload column on the device -> AggI32(found, below, min_value, max_value).
+        keys: host uint8 array (n, K), or a CUDA tensor / device pointer with n given."""
+        out = AggI32()
+        if n is None:
+            keys = np.ascontiguousarray(keys, np.uint8)
+            n, flags = keys.shape[0], IO_HOST
+        else:
+            flags = IO_DEVICE
+        _check(lib().stage_gpu_probe_aggregate_i32(self.h, _ptr(keys), n, read_ts, col_off, threshold, C.byref(out), flags))
+        return out
 
     def scan_column(self, start_keys, scan_sizes, read_ts, apply_visibility, col_off, col_len):
         """-> (row_counts u32[n], key_out u8[n,S,K], col u8[n,S,col_len]); host arrays."""

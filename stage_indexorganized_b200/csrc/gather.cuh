@@ -112,6 +112,49 @@ __global__ void __launch_bounds__(256) gather_cols_kernel(GatherColsArgs a) {
 
 }  // namespace stage
 
+// ---- predicate / aggregate push-down ---------------------------------------------------------
+// What the TPC-C callers finally compute from the rows they probe: RunStockLevel counts the items whose S_QUANTITY is
+// below a threshold (benchmark/tpcc/tpcc_stock_level.cpp:167-176), CH-Q2* takes MIN(S_QUANTITY)
+// (benchmark/tpcc/tpcc_new_order.cpp:808-866). The whole batch answers with one 24-byte record: nothing per probe
+// crosses PCIe. Column = little-endian int32 at payload byte col_off (any alignment).
+namespace stage {
+
+struct AggI32 {
+    unsigned long long found, below;
+    int min_value, max_value;
+};
+
+__global__ void __launch_bounds__(256) aggregate_i32_kernel(const uint32_t *__restrict__ src_row, uint64_t n_slots,
+                                                            const uint8_t *payload, const uint8_t *ver_payload,
+                                                            uint32_t payload_size, uint32_t col_off, int threshold, AggI32 *out) {
+    unsigned found = 0, below = 0;
+    int mn = 0x7FFFFFFF, mx = (int) 0x80000000;
+    for (uint64_t o = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; o < n_slots; o += (uint64_t) gridDim.x * blockDim.x) {
+        const uint32_t row = __ldg(src_row + o);
+        if (row == kNoRow) continue;
+        const uint8_t *base = (row & kVersionRowFlag) ? ver_payload : payload;
+        const uint8_t *p = base + (uint64_t) (row & ~kVersionRowFlag) * payload_size + col_off;
+        const int v = (int) ((uint32_t) __ldg(p) | ((uint32_t) __ldg(p + 1) << 8) | ((uint32_t) __ldg(p + 2) << 16) |
+                             ((uint32_t) __ldg(p + 3) << 24));
+        ++found;
+        below += v < threshold ? 1u : 0u;
+        mn = min(mn, v);
+        mx = max(mx, v);
+    }
+    found = __reduce_add_sync(0xFFFFFFFFu, found);
+    below = __reduce_add_sync(0xFFFFFFFFu, below);
+    mn = __reduce_min_sync(0xFFFFFFFFu, mn);
+    mx = __reduce_max_sync(0xFFFFFFFFu, mx);
+    if ((threadIdx.x & 31) == 0 && found) {
+        atomicAdd(&out->found, (unsigned long long) found);
+        atomicAdd(&out->below, (unsigned long long) below);
+        atomicMin(&out->min_value, mn);
+        atomicMax(&out->max_value, mx);
+    }
+}
+
+}  // namespace stage
+
 // ---- short rows (TPC-C order_line: 60 B) ------------------------------------------------------------------------
 // A warp per row would use 15 of 32 lanes on a 60-byte row. Here every thread moves one 32-bit word of the output:
 // consecutive threads write consecutive words (fully coalesced stores) and read consecutive words of a source row.

@@ -1874,6 +1874,55 @@ extern "C" int stage_gpu_probe_project(stage_snapshot_t *s, const void *keys, ui
     return STAGE_OK;
 }
 
+extern "C" int stage_gpu_probe_aggregate_i32(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts,
+                                             uint32_t col_off, int32_t threshold, stage_agg_i32_t *out, int flags) {
+    if (!s || !out || (n && !keys)) return STAGE_ERR_ARG;
+    if (!s->sealed) return STAGE_ERR_STATE;
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    if ((uint64_t) col_off + 4 > P) return STAGE_ERR_ARG;
+    static_assert(sizeof(AggI32) == sizeof(stage_agg_i32_t), "aggregate record layout");
+    AggI32 init{0, 0, 0x7FFFFFFF, (int) 0x80000000};
+    if (n == 0) {
+        memcpy(out, &init, sizeof(init));
+        return STAGE_OK;
+    }
+    std::lock_guard<std::mutex> lock(s->mu);
+    CUDA_TRY(cudaSetDevice(s->device));
+    int rc;
+    const bool dev = flags & STAGE_IO_DEVICE;
+    const uint64_t chunk = dev ? n : std::min<uint64_t>(n, 1ull << 22);
+    if ((rc = s->sc_srcrow.ensure(chunk * 4)) || (rc = s->sc_counts.ensure(sizeof(AggI32)))) return rc;
+    if (!dev && (rc = s->sc_keys.ensure(chunk * K))) return rc;
+    AggI32 *d_out = static_cast<AggI32 *>(s->sc_counts.p);
+    CUDA_TRY(cudaMemcpyAsync(d_out, &init, sizeof(init), cudaMemcpyHostToDevice, s->stream));
+    for (uint64_t b = 0; b < n; b += chunk) {
+        const uint64_t m = std::min(chunk, n - b);
+        ProbeArgs a{};
+        a.n = m;
+        a.read_ts = read_ts;
+        a.src_row = static_cast<uint32_t *>(s->sc_srcrow.p);
+        if (dev) a.keys = static_cast<const uint8_t *>(keys);
+        else {
+            CUDA_TRY(cudaMemcpyAsync(s->sc_keys.p, static_cast<const uint8_t *>(keys) + b * K, m * K, cudaMemcpyHostToDevice, s->stream));
+            a.keys = static_cast<const uint8_t *>(s->sc_keys.p);
+        }
+        switch (s->nw) {
+            case 1: rc = launch_probe<1>(s, a); break;
+            case 2: rc = launch_probe<2>(s, a); break;
+            case 4: rc = launch_probe<4>(s, a); break;
+            default: rc = launch_probe<8>(s, a); break;
+        }
+        if (rc) return rc;
+        const unsigned blocks = (unsigned) std::min<uint64_t>((m + 255) / 256, (uint64_t) sm_count() * 8);
+        aggregate_i32_kernel<<<blocks, 256, 0, s->stream>>>(a.src_row, m, s->d_payload, s->d_ver_payload, P, col_off, threshold, d_out);
+        LAUNCH_CHECK();
+        if (!dev) CUDA_TRY(cudaStreamSynchronize(s->stream));    // sc_keys is reused by the next chunk
+    }
+    CUDA_TRY(cudaMemcpyAsync(out, d_out, sizeof(AggI32), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return STAGE_OK;
+}
+
 extern "C" int stage_gpu_scan_project(stage_snapshot_t *s, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
                                       uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts,
                                       void *key_out, uint32_t col_off, uint32_t col_len, void *col_out, int flags) {

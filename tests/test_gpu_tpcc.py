@@ -112,3 +112,33 @@ def test_quantity_pushdown(tables):
     assert np.array_equal(counts, wc) and np.array_equal(kout, wk)
     valid = np.arange(10)[None, :] < wc[:, None]
     assert np.array_equal(col[valid], wp[valid][:, 0:4]) and not col[~valid].any()
+
+
+def test_quantity_aggregate_pushdown(tables):
+    """Predicate / aggregate push-down (stage_gpu_probe_aggregate_i32): the stock-level count of S_QUANTITY < threshold
+    and CH-Q2*'s MIN(S_QUANTITY), reduced on the device, against the checker's rows; host and device key buffers,
+    an unaligned column and an empty batch."""
+    import torch
+    stock, _, s_snap, _, _, _ = tables
+    rng = np.random.default_rng(21)
+    keys = np.concatenate([tpcc.q2_supplier_keys(W, 77), tpcc.stock_key(rng.integers(1, W + 1, 5000), rng.integers(1, tpcc.ITEMS + 1, 5000)),
+                           tpcc.stock_key([W + 3, 0, W + 9], [5, 1, 2])])                     # + three misses
+    for read_ts in (1, 50000):
+        wf, _, _, wp = stock.probe(keys, read_ts)
+        wq = wp[wf == 1][:, 0:4].copy().view(np.int32).ravel()
+        for thr in (15, 50, -1):
+            a = s_snap.probe_aggregate_i32(keys, read_ts, 0, thr)
+            assert (a.found, a.below, a.min_value, a.max_value) == (int(wf.sum()), int((wq < thr).sum()), int(wq.min()), int(wq.max()))
+        dk = torch.from_numpy(keys).cuda()
+        a = s_snap.probe_aggregate_i32(dk, read_ts, 0, 15, n=len(keys))
+        assert (a.found, a.below, a.min_value) == (int(wf.sum()), int((wq < 15).sum()), int(wq.min()))
+        # a column at an odd offset: bytes 3..6 read as a little-endian int32
+        wo = np.ascontiguousarray(wp[wf == 1][:, 3:7]).view("<i4").ravel()
+        a = s_snap.probe_aggregate_i32(keys, read_ts, 3, 0)
+        assert (a.below, a.min_value, a.max_value) == (int((wo < 0).sum()), int(wo.min()), int(wo.max()))
+    a = s_snap.probe_aggregate_i32(keys[:0], 1, 0, 15)
+    assert (a.found, a.below, a.min_value, a.max_value) == (0, 0, 2**31 - 1, -2**31)
+    a = s_snap.probe_aggregate_i32(tpcc.stock_key([W + 3], [5]), 1, 0, 15)                    # only a miss
+    assert (a.found, a.min_value) == (0, 2**31 - 1)
+    with pytest.raises(sg.StageError):
+        s_snap.probe_aggregate_i32(keys, 1, tpcc.STOCK_PAYLOAD - 3, 15)                         # column runs past the row

@@ -16,8 +16,15 @@
  * adapters in include/stage_gpu_executors.h put the reference's own class shapes back on top.
  *
  * All functions return 0 on success or a negative stage_status code; stage_gpu_strerror() names it.
- * A snapshot is immutable once sealed; *_batch calls on one snapshot are serialised on the
- * snapshot's CUDA stream.
+ * A snapshot is immutable once sealed. Threading (the reference's callers are N pinned worker threads sharing one
+ * BTree, benchmark/ycsb/ycsb_workload.cpp:522-529): any number of threads may call the *_batch reads on one snapshot
+ * at once. STAGE_IO_HOST calls each run on a context of their own (streams + scratch, up to 16 in flight, then
+ * callers queue); STAGE_IO_DEVICE calls are enqueued one after the other on the snapshot's stream and return
+ * without waiting for the GPU.
+ *
+ * Limits: keys are fixed-length per table, 1..32 bytes; a snapshot (one range shard) holds fewer than 2^31 rows and
+ * fewer than 2^31 staged versions (source rows travel as 32-bit indices whose top bit selects the version table);
+ * leaf_node_size <= 65536; the routed-scan exchange additionally needs key_size % 4 == 0.
  */
 #ifndef STAGE_GPU_H_
 #define STAGE_GPU_H_
@@ -52,7 +59,7 @@ enum stage_key_kind {
  * (include/common/catalog.h:69) the read path depends on. Keys are fixed-length per table, as in
  * every driver table (YCSB int 4 B, YCSB string 16 B, TPC-C 8/16/32 B). */
 typedef struct stage_schema {
-    uint32_t key_size;       /* bytes of key actually passed to Read/Insert (YCSB int: 4) */
+    uint32_t key_size;       /* bytes of key actually passed to Read/Insert (YCSB int: 4); 1..32 */
     uint32_t payload_size;   /* ParameterSet.payload_size */
     uint32_t leaf_node_size; /* ParameterSet.leaf_node_size (64 KiB in both drivers) */
     uint32_t key_kind;       /* enum stage_key_kind */
@@ -82,6 +89,10 @@ enum {
     STAGE_IO_HOST = 0,   /* all in/out pointers are host memory (pinned or pageable) */
     STAGE_IO_DEVICE = 1  /* all in/out pointers are device memory on the snapshot's GPU */
 };
+/* STAGE_IO_HOST results cross PCIe in one of two ways. When every output buffer is pinned (stage_gpu_host_alloc or
+ * stage_gpu_host_register) the kernels store keys, commit ids and payload rows straight into it: one pass, only the
+ * rows that exist, no result slab in HBM. Otherwise results are staged in double-buffered HBM scratch and copied
+ * out by the DMA engine while the next chunk is planned and gathered. STAGE_HOST_PATH=staged|zerocopy forces one. */
 
 /* ---- lifecycle --------------------------------------------------------------------------- */
 
@@ -210,7 +221,9 @@ int stage_gpu_snapshot_last_timing(stage_snapshot_t *s, float *plan_ms, float *g
  *   found[i]   1 if a version visible at read_ts exists (latest in-leaf version if
  *              read_ts >= its commit id, else the first chain version with begin <= read_ts <= commit)
  *   ts[i]      commit id of the version returned (in-leaf: meta & 0xFFFFFFFF; chain: begin_id_)
- *   key_out    n x key_size, payload_out n x payload_size: written only where found[i] == 1
+ *   key_out    n x key_size, payload_out n x payload_size: the key / payload of the version returned where
+ *              found[i] == 1; rows of missed probes are either left untouched (device buffers, pinned host
+ *              buffers) or zero-filled (pageable host buffers) — pre-fill if the difference matters
  * Any output pointer may be NULL. */
 int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
                           uint32_t *ts, void *key_out, void *payload_out, int flags);
@@ -220,7 +233,9 @@ int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint64_t n, uin
  * executor.h:620-638 with apply_visibility = 0). Scan i starts at start_keys[i] (inclusive) and asks
  * for scan_sizes[i] rows; its rows are written, in the reference's order, to row slots
  * [i*out_stride, i*out_stride + row_counts[i]) of key_out / ts_out / payload_out
- * (out_stride >= max scan size). Reproduces the iterator's slot-order truncation and
+ * (out_stride >= max scan size: STAGE_ERR_ARG otherwise with host buffers; with device buffers, where the sizes are
+ * not visible to the host, a larger size is clamped to out_stride). Row slots beyond row_counts[i] are either left
+ * untouched or zero-filled. Reproduces the iterator's slot-order truncation and
  * leaf-hop termination rules exactly. apply_visibility = 1 is the executor's
  * range rule: a row is returned iff read_ts >= the commit id of its in-leaf version; a newer row is
  * dropped — the range branch never reaches a version chain, because the iterator's records carry no
@@ -311,8 +326,9 @@ int stage_gpu_exchange_results(stage_exchange_t *x, void **found, void **ts, voi
  * ids and payload rows straight into the requester's slab, request q at rows [q*rows_per_scan, +count). A scan does
  * not continue on the next shard: shards are expected to overlap their right neighbour by a halo of rows (the
  * caller's sharding decides how many: enough for the longest scan including the rows the filter drops).
- * Replaces: the per-thread loop over BTree::RangeScanBySize / Iterator::GetNext (include/vstore/b_tree.h:867-950,
- * src/execute/index_scan_executor.cpp:64-116) on a range-partitioned table. key_size must be a multiple of 4.
+ * Replaces: the per-thread loop over BTree::RangeScanBySize / Iterator::GetNext (include/vstore/b_tree.h:830-835,
+ * 883-941) inside IndexScanExecutor / TableScanExecutor::Execute (include/execute/executor.h:455-535, 620-638) on a
+ * range-partitioned table. key_size must be a multiple of 4.
  * Call order per batch as for probes: post_scans, serve_scans, wait (device sync) on one stream. */
 int stage_gpu_exchange_create_scan(uint32_t world, uint32_t rank, uint64_t max_scans, uint32_t max_scan_size,
                                    const stage_schema_t *schema, stage_exchange_t **out);
@@ -338,6 +354,18 @@ int stage_gpu_exchange_destroy(stage_exchange_t *x);
 /* ---- utilities ---------------------------------------------------------------------------- */
 void *stage_gpu_host_alloc(size_t bytes); /* pinned host memory for STAGE_IO_HOST batches */
 void stage_gpu_host_free(void *p);
+/* Pin memory the caller already owns (e.g. the std::vector<T> storage a TableScanExecutor-style caller returns rows
+ * in, include/execute/executor.h:644-649) so that results can be stored into it directly. */
+int stage_gpu_host_register(void *p, size_t bytes);
+int stage_gpu_host_unregister(void *p);
+/* Counters kept on the device since the snapshot was sealed (or last reset). slot_order_scans: range scans in which
+ * the reference's slot-order early break (LeafNode::RangeScanBySize, src/vstore/b_tree.cpp:1276-1309; SURVEY.md §3.4
+ * Q5) decided which rows of the last leaf were returned — 0 on consolidated tables. Synchronises the device. */
+typedef struct {
+    uint64_t slot_order_scans;
+    uint64_t reserved[7];
+} stage_counters_t;
+int stage_gpu_snapshot_counters(stage_snapshot_t *s, stage_counters_t *out, int reset);
 /* Kernels launched by this library since process start (for bench.py's gpu_launches). */
 uint64_t stage_gpu_launch_count(void);
 const char *stage_gpu_strerror(int status);

@@ -20,6 +20,7 @@
 #include <cstring>
 #include <functional>
 #include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -63,17 +64,20 @@ public:
     GpuTreeView(const void *root, uint32_t key_size, uint32_t payload_size, uint32_t leaf_node_size = 65536,
                 uint32_t key_kind = STAGE_KEY_AUTO) {
         schema_ = stage_schema_t{key_size, payload_size, leaf_node_size, key_kind};
-        check(stage_gpu_snapshot_from_tree(root, &schema_, &snap_), "stage_gpu_snapshot_from_tree");
+        stage_snapshot_t *h = nullptr;
+        check(stage_gpu_snapshot_from_tree(root, &schema_, &h), "stage_gpu_snapshot_from_tree");
+        snap_ = wrap(h);
     }
     // Tree with writers in flight: `resolve` looks an undo copy up in the tree's EphemeralPool (stage_undo_resolver_t,
     // include/stage_gpu.h), as BTree::Read does for a record whose update has not committed (b_tree.cpp:2087-2103).
     GpuTreeView(const void *root, uint32_t key_size, uint32_t payload_size, stage_undo_resolver_t resolve, void *resolve_ctx,
                 uint32_t leaf_node_size = 65536, uint32_t key_kind = STAGE_KEY_AUTO) {
         schema_ = stage_schema_t{key_size, payload_size, leaf_node_size, key_kind};
-        check(stage_gpu_snapshot_from_tree_live(root, &schema_, resolve, resolve_ctx, &snap_),
-              "stage_gpu_snapshot_from_tree_live");
+        stage_snapshot_t *h = nullptr;
+        check(stage_gpu_snapshot_from_tree_live(root, &schema_, resolve, resolve_ctx, &h), "stage_gpu_snapshot_from_tree_live");
+        snap_ = wrap(h);
     }
-    ~GpuTreeView() { if (snap_) stage_gpu_snapshot_destroy(snap_); }
+    ~GpuTreeView() = default;          // the snapshot goes when its last user (this view or a reader in flight) lets go
     GpuTreeView(const GpuTreeView &) = delete;
     GpuTreeView &operator=(const GpuTreeView &) = delete;
 
@@ -85,7 +89,7 @@ public:
         uint8_t found = 0;
         uint32_t ts = 0;
         // read_ts = MAX_CID: the in-leaf version is always "visible" here
-        check(stage_gpu_probe_batch(snap_, key, 1, 0xFFFFFFFFu, &found, &ts, rec->GetData(), rec->GetPayload(),
+        check(stage_gpu_probe_batch(pin().get(), key, 1, 0xFFFFFFFFu, &found, &ts, rec->GetData(), rec->GetPayload(),
                                     STAGE_IO_HOST), "stage_gpu_probe_batch");
         if (!found) return nullptr;
         rec->commit_id = ts;
@@ -98,37 +102,55 @@ public:
     // Batched forms: the ones that reach HBM speed. Outputs are caller-allocated host buffers.
     void ReadBatch(const void *keys, uint64_t n, cid_t read_ts, uint8_t *found, uint32_t *ts, void *key_out,
                    void *payload_out) {
-        check(stage_gpu_probe_batch(snap_, keys, n, read_ts, found, ts, key_out, payload_out, STAGE_IO_HOST),
+        check(stage_gpu_probe_batch(pin().get(), keys, n, read_ts, found, ts, key_out, payload_out, STAGE_IO_HOST),
               "stage_gpu_probe_batch");
     }
     void ScanBatch(const void *start_keys, const uint32_t *scan_sizes, uint64_t n, uint32_t out_stride, cid_t read_ts,
                    bool apply_visibility, uint32_t *row_counts, void *key_out, uint32_t *ts_out, void *payload_out) {
-        check(stage_gpu_scan_batch(snap_, start_keys, scan_sizes, n, out_stride, read_ts, apply_visibility ? 1 : 0,
+        check(stage_gpu_scan_batch(pin().get(), start_keys, scan_sizes, n, out_stride, read_ts, apply_visibility ? 1 : 0,
                                    row_counts, key_out, ts_out, payload_out, STAGE_IO_HOST), "stage_gpu_scan_batch");
     }
 
     // After the host tree took committed inserts / updates / deletes (quiesced again): swap in the next snapshot.
     // Only the leaves that changed are staged again (stage_gpu_snapshot_refresh_from_tree).
     // With `resolve` (see the second constructor) update transactions may stay in flight during the call.
+    // Readers are never blocked: calls already running finish on the snapshot they pinned (it is destroyed when the
+    // last of them returns), calls that start after the swap see the new one. One Refresh at a time.
     stage_refresh_stats_t Refresh(const void *root, stage_undo_resolver_t resolve = nullptr, void *resolve_ctx = nullptr) {
+        std::lock_guard<std::mutex> one(refresh_mu_);
+        std::shared_ptr<stage_snapshot_t> cur = pin();
         stage_snapshot_t *next = nullptr;
         stage_refresh_stats_t st{};
         if (resolve)
-            check(stage_gpu_snapshot_refresh_from_tree_live(snap_, root, resolve, resolve_ctx, &next, &st),
+            check(stage_gpu_snapshot_refresh_from_tree_live(cur.get(), root, resolve, resolve_ctx, &next, &st),
                   "stage_gpu_snapshot_refresh_from_tree_live");
         else
-            check(stage_gpu_snapshot_refresh_from_tree(snap_, root, &next, &st), "stage_gpu_snapshot_refresh_from_tree");
-        stage_gpu_snapshot_destroy(snap_);
-        snap_ = next;
+            check(stage_gpu_snapshot_refresh_from_tree(cur.get(), root, &next, &st), "stage_gpu_snapshot_refresh_from_tree");
+        std::shared_ptr<stage_snapshot_t> fresh = wrap(next);
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            snap_.swap(fresh);
+        }
         return st;
     }
 
     const stage_schema_t &schema() const { return schema_; }
-    stage_snapshot_t *handle() { return snap_; }
+    // The current snapshot, kept alive for as long as the returned pointer lives.
+    std::shared_ptr<stage_snapshot_t> pin() const {
+        std::lock_guard<std::mutex> g(mu_);
+        return snap_;
+    }
+    // Raw handle of the current snapshot; only valid until the next Refresh (use pin() from concurrent readers).
+    stage_snapshot_t *handle() { return pin().get(); }
 
 private:
+    static std::shared_ptr<stage_snapshot_t> wrap(stage_snapshot_t *h) {
+        return std::shared_ptr<stage_snapshot_t>(h, [](stage_snapshot_t *p) { if (p) stage_gpu_snapshot_destroy(p); });
+    }
     stage_schema_t schema_{};
-    stage_snapshot_t *snap_ = nullptr;
+    mutable std::mutex mu_;
+    std::mutex refresh_mu_;
+    std::shared_ptr<stage_snapshot_t> snap_;
 };
 
 // Iterator::GetNext shape over one scan's result slab (the scan runs when the iterator is created).

@@ -48,6 +48,10 @@ class AggI32(C.Structure):
     _fields_ = [("found", _u64), ("below", _u64), ("min_value", C.c_int32), ("max_value", C.c_int32)]
 
 
+class Counters(C.Structure):
+    _fields_ = [("slot_order_scans", _u64), ("reserved", _u64 * 7)]
+
+
 class RefreshStats(C.Structure):
     _fields_ = [("leaves_total", _u64), ("leaves_carried", _u64), ("leaves_transformed", _u64), ("rows", _u64),
                 ("versions_added", _u64), ("host_bytes_staged", _u64)]
@@ -104,6 +108,9 @@ SYMBOLS = {
     "stage_gpu_exchange_enable_timing": (_i32, [_vp, _i32]),
     "stage_gpu_exchange_last_timing": (_i32, [_vp, C.POINTER(C.c_float)]),
     "stage_gpu_exchange_destroy": (_i32, [_vp]),
+    "stage_gpu_snapshot_counters": (_i32, [_vp, C.POINTER(Counters), _i32]),
+    "stage_gpu_host_register": (_i32, [_vp, C.c_size_t]),
+    "stage_gpu_host_unregister": (_i32, [_vp]),
     "stage_gpu_host_alloc": (_vp, [C.c_size_t]),
     "stage_gpu_host_free": (None, [_vp]),
     "stage_gpu_launch_count": (_u64, []),
@@ -312,6 +319,11 @@ class Snapshot:
         i = SnapshotInfo()
         _check(lib().stage_gpu_snapshot_info(self.h, C.byref(i)))
         return i
+
+    def counters(self, reset=False):
+        c = Counters()
+        _check(lib().stage_gpu_snapshot_counters(self.h, C.byref(c), int(reset)))
+        return c
 
     def set_stream(self, cuda_stream):
         _check(lib().stage_gpu_snapshot_set_stream(self.h, _vp(int(cuda_stream))))

@@ -155,6 +155,52 @@ __global__ void __launch_bounds__(256) aggregate_i32_kernel(const uint32_t *__re
 
 }  // namespace stage
 
+// ---- mid-size rows (TPC-C stock: 400 B) ---------------------------------------------------------------------------
+// gather_rows_kernel is shaped for ~1 KB rows: a warp covers a row with 4 unrolled accesses per lane, so a 400-byte row
+// (25 x 16 B) leaves 7 lanes idle and issues ONE of the four loads — 1.6 KB in flight per warp instead of 4 KB
+// (0.47 of the HBM peak on `stock` probes). Here the output is a flat stream of 16-byte vectors:
+// thread t moves vectors t, t+256, t+512, ... of its CTA's span (kMidVecs independent loads before the first store),
+// consecutive threads write consecutive vectors (fully coalesced stores) and read consecutive vectors of a source row.
+namespace stage {
+
+constexpr uint32_t kMidRowMax = 512;         // rows of 272..512 bytes, 16-byte aligned
+
+template <int kMidVecs>
+__global__ void __launch_bounds__(kGatherThreads) gather_rows_mid_kernel(GatherArgs a) {
+    __shared__ uint32_t s_row[kGatherRows];
+    const uint64_t slot0 = (uint64_t) blockIdx.x * kGatherRows;
+    const int tid = threadIdx.x;
+    if (tid < kGatherRows) {
+        const uint64_t o = slot0 + tid;
+        s_row[tid] = o < a.n_slots ? __ldg(a.src_row + o) : kNoRow;
+    }
+    __syncthreads();
+    const uint32_t P = a.payload_size, vpr = P / 16;          // vectors per row
+    const uint32_t total = kGatherRows * vpr;                 // vectors of this CTA's 64 output rows
+    uint4 *dst = reinterpret_cast<uint4 *>(a.dst + slot0 * P);
+    for (uint32_t v0 = tid; v0 < total; v0 += kGatherThreads * kMidVecs) {
+        uint4 val[kMidVecs];
+        bool ok[kMidVecs];
+#pragma unroll
+        for (int j = 0; j < kMidVecs; ++j) {
+            const uint32_t v = v0 + j * kGatherThreads;
+            ok[j] = false;
+            if (v >= total) continue;
+            const uint32_t r = v / vpr, k = v - r * vpr;
+            const uint32_t row = s_row[r];
+            if (row == kNoRow) continue;
+            const uint8_t *base = (row & kVersionRowFlag) ? a.ver_payload : a.payload;
+            val[j] = __ldcs(reinterpret_cast<const uint4 *>(base + (uint64_t) (row & ~kVersionRowFlag) * P) + k);
+            ok[j] = true;
+        }
+#pragma unroll
+        for (int j = 0; j < kMidVecs; ++j)
+            if (ok[j]) __stcs(dst + v0 + j * kGatherThreads, val[j]);
+    }
+}
+
+}  // namespace stage
+
 // ---- short rows (TPC-C order_line: 60 B) ------------------------------------------------------------------------
 // A warp per row would use 15 of 32 lanes on a 60-byte row. Here every thread moves one 32-bit word of the output:
 // consecutive threads write consecutive words (fully coalesced stores) and read consecutive words of a source row.

@@ -41,6 +41,7 @@ struct ScanArgs {
     uint32_t *ts_out;
     uint32_t *src_row;          // [n][out_stride] rows to gather, kNoRow beyond row_counts[i]
     const uint32_t *n_dev;      // optional: the number of scans lives on the device (min(*n_dev, n) are run)
+    unsigned long long *stats;  // optional: [0] += scans whose rows were selected by the slot-order rule (Q5)
 };
 
 // MVCC filter of a scanned row, exactly as the reference's executors apply it. TableScanExecutor: none
@@ -127,7 +128,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
 
     const uint64_t n_scans = a.n_dev ? min((uint64_t) __ldcg(a.n_dev), a.n) : a.n;
     for (uint64_t sid = blockIdx.x; sid < n_scans; sid += gridDim.x) {
-        const uint32_t S = a.scan_sizes[sid];
+        const uint32_t S = min(a.scan_sizes[sid], a.out_stride);   // a scan never writes past its slab
         const SKey<NW> begin = to_sortable<NW>(a.start_keys + sid * K, K, v.xormask);
         const uint64_t out_base = sid * (uint64_t) a.out_stride;
         uint32_t cnt = 0;
@@ -219,6 +220,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
 
                 // ---- the leaf where the budget runs out, when the slot-order rule changes the result -----
                 if (quirk) {
+                    if (tid == 0 && a.stats) atomicAdd(a.stats, 1ull);
                     for (uint32_t i = tid; i < nql; i += kScanThreads) s_slots[i] = v.slot[start_l + i];
                     __syncthreads();
                     uint32_t sel_before = 0;
@@ -316,7 +318,7 @@ __global__ void __launch_bounds__(kScanWarpThreads) scan_plan_warp_kernel(Snapsh
 
     const uint64_t n_scans = a.n_dev ? min((uint64_t) __ldcg(a.n_dev), a.n) : a.n;
     for (uint64_t sid = (uint64_t) blockIdx.x * (kScanWarpThreads / 32) + warp; sid < n_scans; sid += n_warps) {
-        const uint32_t S = a.scan_sizes[sid];
+        const uint32_t S = min(a.scan_sizes[sid], a.out_stride);   // a scan never writes past its slab
         const SKey<NW> begin = to_sortable<NW>(a.start_keys + sid * K, K, v.xormask);
         const uint64_t out_base = sid * (uint64_t) a.out_stride;
         uint32_t cnt = 0;
@@ -407,6 +409,7 @@ __global__ void __launch_bounds__(kScanWarpThreads) scan_plan_warp_kernel(Snapsh
                     cnt += __popc(m);
                 }
                 if (quirk) {
+                    if (lane == 0 && a.stats) atomicAdd(a.stats, 1ull);
                     for (uint32_t i = lane; i < nql; i += 32) s_slots[i] = v.slot[start_l + i];
                     __syncwarp();
                     // slot value of the (T+1)-th lowest slot (slots are unique): bisection on the 16-bit value, a warp

@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <mutex>
 #include <thread>
 #include <string>
@@ -91,6 +92,37 @@ struct DevBuf {
     }
 };
 
+// Where a read call runs: the stream it launches on and the scratch its plan kernel hands to its gather kernel.
+struct Lane {
+    cudaStream_t st = nullptr;
+    DevBuf *srcrow = nullptr;
+    bool timing = false;            // record the snapshot's timing events around the launches (device-I/O calls only)
+};
+
+// One in-flight STAGE_IO_HOST call: its own streams and scratch, so that concurrent callers (the reference's N pinned
+// worker threads, ycsb_workload.cpp:522-529) overlap instead of queueing behind one snapshot-wide lock.
+struct HostCtx {
+    cudaStream_t st = nullptr, cp = nullptr;        // kernels + H2D; D2H copies of the staged mode
+    cudaEvent_t done[2] = {nullptr, nullptr};       // chunk planned + gathered (on st)
+    cudaEvent_t drained[2] = {nullptr, nullptr};    // chunk copied out (on cp)
+    DevBuf keys, sizes, srcrow;
+    DevBuf counts[2], found[2], ts[2], keyout[2], payload[2];
+    uint32_t *h_counts = nullptr;                   // pinned: row counts of the chunk in flight (per-scan copies)
+    size_t h_counts_cap = 0;
+    bool busy = false;
+    void release_all() {
+        keys.release(); sizes.release(); srcrow.release();
+        for (int i = 0; i < 2; ++i) {
+            counts[i].release(); found[i].release(); ts[i].release(); keyout[i].release(); payload[i].release();
+            if (done[i]) cudaEventDestroy(done[i]);
+            if (drained[i]) cudaEventDestroy(drained[i]);
+        }
+        if (h_counts) cudaFreeHost(h_counts);
+        if (st) cudaStreamDestroy(st);
+        if (cp) cudaStreamDestroy(cp);
+    }
+};
+
 struct stage_snapshot {
     stage_schema_t schema{};
     int nw = 1;
@@ -149,9 +181,14 @@ struct stage_snapshot {
     uint8_t *d_raw_keys = nullptr;              // bulk load: caller-filled raw keys, released by seal_sorted
     uint32_t bulk_rows_per_leaf = 0;
 
-    // scratch for STAGE_IO_HOST batches
+    // scratch for STAGE_IO_HOST batches of the push-down calls (serialised on `mu`)
     DevBuf sc_keys, sc_found, sc_ts, sc_keyout, sc_payload, sc_sizes, sc_counts;
     DevBuf sc_srcrow;                           // source-row lists handed from the plan kernels to the gather
+    // contexts of the host-buffer probe / scan calls (one per concurrent caller, created on demand)
+    std::mutex ctx_mu;
+    std::condition_variable ctx_cv;
+    std::vector<HostCtx *> ctx_pool;
+    unsigned long long *d_stats = nullptr;      // [0] scans in which the slot-order truncation (Q5) selected the rows
 };
 
 template <typename T>
@@ -203,7 +240,7 @@ static void snapshot_free(stage_snapshot *s) {
     cudaSetDevice(s->device);
     void *ptrs[] = {s->d_skey, s->d_slot, s->d_ts, s->d_chain, s->d_payload, s->d_leaf_off, s->d_sep, s->d_cont,
                     s->d_has_sep, s->d_ver_begin, s->d_ver_commit, s->d_ver_next, s->d_ver_payload,
-                    s->d_err, s->d_stage[0], s->d_stage[1], s->d_raw_keys, s->d_phys, s->d_dir};
+                    s->d_err, s->d_stage[0], s->d_stage[1], s->d_raw_keys, s->d_phys, s->d_dir, s->d_stats};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     free(s->ext_ver_payload);
@@ -211,6 +248,11 @@ static void snapshot_free(stage_snapshot *s) {
         if (s->h_stage[i]) cudaFreeHost(s->h_stage[i]);
         if (s->stage_ev[i]) cudaEventDestroy(s->stage_ev[i]);
     }
+    for (HostCtx *c : s->ctx_pool) {
+        c->release_all();
+        delete c;
+    }
+    s->ctx_pool.clear();
     s->sc_keys.release(); s->sc_found.release(); s->sc_ts.release(); s->sc_keyout.release();
     s->sc_payload.release(); s->sc_sizes.release(); s->sc_counts.release(); s->sc_srcrow.release();
     s->rf_keys.release(); s->rf_patch.release(); s->rf_cid.release(); s->rf_row.release(); s->rf_order.release();
@@ -247,7 +289,9 @@ static int snapshot_new(const stage_schema_t *schema, stage_snapshot **out) {
 }
 
 static int alloc_columns(stage_snapshot *s, uint64_t cap_leaves, uint64_t cap_rows) {
-    if (cap_rows >= 0xFFFFFFF0ull) return STAGE_ERR_ARG;
+    // source rows travel as u32 with bit 31 = "row of the version table" (gather.cuh kVersionRowFlag): a shard holds
+    // fewer than 2^31 rows (include/stage_gpu.h, stage_schema_t)
+    if (cap_rows >= (uint64_t) kVersionRowFlag) return STAGE_ERR_ARG;
     s->cap_leaves = cap_leaves;
     s->cap_rows = cap_rows;
     int rc;
@@ -270,6 +314,8 @@ static int alloc_columns(stage_snapshot *s, uint64_t cap_leaves, uint64_t cap_ro
     if ((rc = dev_alloc(s, &s->d_has_sep, cap_leaves + 1))) return rc;
     if ((rc = dev_alloc(s, &s->d_err, 1))) return rc;
     CUDA_TRY(cudaMemsetAsync(s->d_err, 0, 4, s->stream));
+    if ((rc = dev_alloc(s, &s->d_stats, 8))) return rc;
+    CUDA_TRY(cudaMemsetAsync(s->d_stats, 0, 64, s->stream));
     return STAGE_OK;
 }
 
@@ -973,7 +1019,14 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
 
     stage_snapshot *s = nullptr;
     if ((rc = stage_gpu_snapshot_begin(schema, L, n_rows, &s))) return rc;
-    auto fail = [&](int code) { snapshot_free(s); return code; };
+    uint32_t *d_src_leaf = nullptr, *d_changed = nullptr;
+    auto fail = [&](int code) {
+        cudaStreamSynchronize(s->stream);
+        if (d_src_leaf) cudaFree(d_src_leaf);
+        if (d_changed) cudaFree(d_changed);
+        snapshot_free(s);
+        return code;
+    };
     s->h_leaf_off.resize(L + 1);
     s->h_sep.assign(L * s->nw, 0xFFFFFFFFu);
     s->h_has_sep.resize(L);
@@ -995,7 +1048,6 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
     RF_TRY(cudaMemcpyAsync(s->d_has_sep, s->h_has_sep.data(), L, cudaMemcpyHostToDevice, st));
 
     // 2. carried-over leaves: old columns -> new columns, on the device
-    uint32_t *d_src_leaf = nullptr, *d_changed = nullptr;
     RF_TRY(cudaMalloc((void **) &d_src_leaf, std::max<size_t>(L, 1) * 4));
     RF_TRY(cudaMemcpyAsync(d_src_leaf, src_leaf.data(), L * 4, cudaMemcpyHostToDevice, st));
     RF_TRY(cudaStreamSynchronize(old->stream));      // the previous snapshot's columns are final (refresh kernels done)
@@ -1011,7 +1063,7 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
         c.old_cont = old->d_cont; c.new_cont = s->d_cont;
         c.nw = (uint32_t) s->nw; c.payload_size = P;
         leaf_carry_kernel<<<(unsigned) std::min<uint64_t>(L, (uint64_t) sm_count() * 8), 256, 0, st>>>(c);
-        if (cudaGetLastError() != cudaSuccess) { cudaFree(d_src_leaf); return fail(STAGE_ERR_CUDA); }
+        if (cudaGetLastError() != cudaSuccess) return fail(STAGE_ERR_CUDA);
         g_launches.fetch_add(1);
     }
 
@@ -1105,14 +1157,14 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
     } else {
         cudaStreamSynchronize(st);
     }
-    cudaFree(d_src_leaf);
-    if (d_changed) cudaFree(d_changed);
     for (int i = 0; i < 2; ++i) {
         if (s->h_stage[i]) { cudaFreeHost(s->h_stage[i]); s->h_stage[i] = nullptr; }
         if (s->d_stage[i]) { cudaFree(s->d_stage[i]); s->d_stage[i] = nullptr; }
     }
 #undef RF_TRY
     if (rc) return fail(rc);
+    cudaFree(d_src_leaf);
+    if (d_changed) cudaFree(d_changed);
     if (stats) {
         stats->leaves_total = L;
         stats->leaves_carried = L - changed.size();
@@ -1142,7 +1194,7 @@ extern "C" int stage_gpu_snapshot_refresh_from_tree_live(stage_snapshot_t *old, 
 extern "C" int stage_gpu_snapshot_generate_ycsb(const stage_schema_t *schema, uint64_t n_rows_total, uint64_t first_rank,
                                                 uint64_t n_local, uint32_t rows_per_leaf, stage_snapshot_t **out) {
     if (!out || !schema || schema->key_size != 4 || rows_per_leaf == 0 || first_rank + n_local > n_rows_total ||
-        n_rows_total > 0xFFFFFFFFull)
+        n_rows_total > 0xFFFFFFFFull || n_local >= (uint64_t) kVersionRowFlag)
         return STAGE_ERR_ARG;
     stage_snapshot *s = nullptr;
     int rc = snapshot_new(schema, &s);
@@ -1282,7 +1334,9 @@ extern "C" int stage_gpu_snapshot_apply_updates(stage_snapshot_t *s, const void 
     std::lock_guard<std::mutex> lock(s->mu);
     CUDA_TRY(cudaSetDevice(s->device));
     int rc;
-    if ((rc = grow_versions(s, s->n_versions + n))) return rc;
+    rc = grow_versions(s, s->n_versions + n);
+    fill_view(s);                 // the version arrays may have moved: never leave the kernels' view dangling
+    if (rc) return rc;
     RefreshArgs a{};
     if (flags & STAGE_IO_DEVICE) {
         a.keys = static_cast<const uint8_t *>(keys);
@@ -1511,15 +1565,16 @@ extern "C" void *stage_gpu_snapshot_get_stream(const stage_snapshot_t *s) { retu
 // ------------------------------------------------------------------------------------------------
 
 template <typename V>
-static int launch_gather_v(stage_snapshot *s, const GatherArgs &g) {
+static int launch_gather_v(cudaStream_t st, const GatherArgs &g) {
     const unsigned blocks = (unsigned) ((g.n_slots + kGatherRows - 1) / kGatherRows);
-    gather_rows_kernel<V, 4><<<blocks, kGatherThreads, 0, s->stream>>>(g);
+    gather_rows_kernel<V, 4><<<blocks, kGatherThreads, 0, st>>>(g);
     LAUNCH_CHECK();
     return STAGE_OK;
 }
 
-// payload rows named by src_row[0..n_slots) -> dst[n_slots][P]
-static int launch_gather(stage_snapshot *s, const uint32_t *src_row, uint64_t n_slots, uint8_t *dst) {
+// payload rows named by src_row[0..n_slots) -> dst[n_slots][P]. dst may be device memory or the device alias of
+// pinned host memory (the gather then streams the rows straight across PCIe).
+static int launch_gather(stage_snapshot *s, cudaStream_t st, const uint32_t *src_row, uint64_t n_slots, uint8_t *dst) {
     if (n_slots == 0 || !dst) return STAGE_OK;
     if ((n_slots + kGatherRows - 1) / kGatherRows > 0x7FFFFFFFull) return STAGE_ERR_ARG;
     GatherArgs g{};
@@ -1536,19 +1591,28 @@ static int launch_gather(stage_snapshot *s, const uint32_t *src_row, uint64_t n_
         const uint64_t per_cta = 256 * kSmallWordsPerThread;
         const uint64_t ctas = (words + per_cta - 1) / per_cta;
         if (ctas > 0x7FFFFFFFull) return STAGE_ERR_ARG;
-        if (words + per_cta < 0xFFFFFFFFull) gather_rows_small_kernel<uint32_t><<<(unsigned) ctas, 256, 0, s->stream>>>(g, wpr, words);
-        else gather_rows_small_kernel<uint64_t><<<(unsigned) ctas, 256, 0, s->stream>>>(g, wpr, words);
+        if (words + per_cta < 0xFFFFFFFFull) gather_rows_small_kernel<uint32_t><<<(unsigned) ctas, 256, 0, st>>>(g, wpr, words);
+        else gather_rows_small_kernel<uint64_t><<<(unsigned) ctas, 256, 0, st>>>(g, wpr, words);
         LAUNCH_CHECK();
         return STAGE_OK;
     }
-    if ((align & 15) == 0) return launch_gather_v<uint4>(s, g);
-    if ((align & 7) == 0) return launch_gather_v<uint2>(s, g);
-    if ((align & 3) == 0) return launch_gather_v<uint32_t>(s, g);
-    return launch_gather_v<uint8_t>(s, g);
+    if (g.payload_size <= kMidRowMax && (align & 15) == 0) {  // mid-size rows (TPC-C stock: 400 B): flat 16-byte vector stream
+        static const int vecs = getenv("STAGE_MID_VECS") ? atoi(getenv("STAGE_MID_VECS")) : 4;
+        const unsigned blocks = (unsigned) ((n_slots + kGatherRows - 1) / kGatherRows);
+        if (vecs >= 7) gather_rows_mid_kernel<7><<<blocks, kGatherThreads, 0, st>>>(g);
+        else if (vecs <= 2) gather_rows_mid_kernel<2><<<blocks, kGatherThreads, 0, st>>>(g);
+        else gather_rows_mid_kernel<4><<<blocks, kGatherThreads, 0, st>>>(g);
+        LAUNCH_CHECK();
+        return STAGE_OK;
+    }
+    if ((align & 15) == 0) return launch_gather_v<uint4>(st, g);
+    if ((align & 7) == 0) return launch_gather_v<uint2>(st, g);
+    if ((align & 3) == 0) return launch_gather_v<uint32_t>(st, g);
+    return launch_gather_v<uint8_t>(st, g);
 }
 
 template <int NW>
-static int launch_probe(stage_snapshot *s, const ProbeArgs &a) {
+static int launch_probe(stage_snapshot *s, cudaStream_t st, const ProbeArgs &a) {
     static const int ppl = getenv("STAGE_PROBE_PPL") ? atoi(getenv("STAGE_PROBE_PPL")) : 4;
     const uint64_t want_blocks = (a.n + kProbeThreads * ppl - 1) / (kProbeThreads * ppl);
     if (s->view.dir) {
@@ -1560,9 +1624,9 @@ static int launch_probe(stage_snapshot *s, const ProbeArgs &a) {
             occd[NW] = std::max(o, 1);
         }
         const unsigned blocks = (unsigned) std::min<uint64_t>(want_blocks, (uint64_t) sm_count() * occd[NW]);
-        if (ppl == 8) probe_kernel<NW, 8, true><<<blocks, kProbeThreads, 0, s->stream>>>(s->view, a);
-        else if (ppl == 4) probe_kernel<NW, 4, true><<<blocks, kProbeThreads, 0, s->stream>>>(s->view, a);
-        else probe_kernel<NW, 2, true><<<blocks, kProbeThreads, 0, s->stream>>>(s->view, a);
+        if (ppl == 8) probe_kernel<NW, 8, true><<<blocks, kProbeThreads, 0, st>>>(s->view, a);
+        else if (ppl == 4) probe_kernel<NW, 4, true><<<blocks, kProbeThreads, 0, st>>>(s->view, a);
+        else probe_kernel<NW, 2, true><<<blocks, kProbeThreads, 0, st>>>(s->view, a);
         LAUNCH_CHECK();
         return STAGE_OK;
     }
@@ -1575,15 +1639,23 @@ static int launch_probe(stage_snapshot *s, const ProbeArgs &a) {
         occ[NW] = std::max(o, 1);
     }
     const unsigned blocks = (unsigned) std::min<uint64_t>(want_blocks, (uint64_t) sm_count() * occ[NW]);
-    if (ppl == 8) probe_kernel<NW, 8><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a);
-    else if (ppl == 4) probe_kernel<NW, 4><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a);
-    else probe_kernel<NW, 2><<<blocks, kProbeThreads, smem, s->stream>>>(s->view, a);
+    if (ppl == 8) probe_kernel<NW, 8><<<blocks, kProbeThreads, smem, st>>>(s->view, a);
+    else if (ppl == 4) probe_kernel<NW, 4><<<blocks, kProbeThreads, smem, st>>>(s->view, a);
+    else probe_kernel<NW, 2><<<blocks, kProbeThreads, smem, st>>>(s->view, a);
     LAUNCH_CHECK();
     return STAGE_OK;
 }
+static int launch_probe_nw(stage_snapshot *s, cudaStream_t st, const ProbeArgs &a) {
+    switch (s->nw) {
+        case 1: return launch_probe<1>(s, st, a);
+        case 2: return launch_probe<2>(s, st, a);
+        case 4: return launch_probe<4>(s, st, a);
+        default: return launch_probe<8>(s, st, a);
+    }
+}
 
 template <int NW, typename V>
-static int launch_probe_fused_v(stage_snapshot *s, const ProbeArgs &a, uint8_t *payload_out) {
+static int launch_probe_fused_v(stage_snapshot *s, cudaStream_t st, const ProbeArgs &a, uint8_t *payload_out) {
     const size_t smem = (size_t) std::max<uint32_t>(s->view.smem_words, 4) * 4;
     static int occ = 0;
     if (!occ) {
@@ -1593,110 +1665,236 @@ static int launch_probe_fused_v(stage_snapshot *s, const ProbeArgs &a, uint8_t *
     }
     const uint64_t tiles = (a.n + kFusedTile - 1) / kFusedTile;
     const unsigned blocks = (unsigned) std::min<uint64_t>(tiles, (uint64_t) sm_count() * occ);
-    probe_fused_kernel<NW, V><<<blocks, kFusedThreads, smem, s->stream>>>(s->view, a, payload_out);
+    probe_fused_kernel<NW, V><<<blocks, kFusedThreads, smem, st>>>(s->view, a, payload_out);
     LAUNCH_CHECK();
     return STAGE_OK;
 }
 template <int NW>
-static int launch_probe_fused(stage_snapshot *s, const ProbeArgs &a, uint8_t *payload_out) {
+static int launch_probe_fused(stage_snapshot *s, cudaStream_t st, const ProbeArgs &a, uint8_t *payload_out) {
     const uintptr_t align = (uintptr_t) s->d_payload | (uintptr_t) s->d_ver_payload | (uintptr_t) payload_out |
                             s->schema.payload_size;
-    if ((align & 15) == 0) return launch_probe_fused_v<NW, uint4>(s, a, payload_out);
-    if ((align & 7) == 0) return launch_probe_fused_v<NW, uint2>(s, a, payload_out);
-    if ((align & 3) == 0) return launch_probe_fused_v<NW, uint32_t>(s, a, payload_out);
-    return launch_probe_fused_v<NW, uint8_t>(s, a, payload_out);
+    if ((align & 15) == 0) return launch_probe_fused_v<NW, uint4>(s, st, a, payload_out);
+    if ((align & 7) == 0) return launch_probe_fused_v<NW, uint2>(s, st, a, payload_out);
+    if ((align & 3) == 0) return launch_probe_fused_v<NW, uint32_t>(s, st, a, payload_out);
+    return launch_probe_fused_v<NW, uint8_t>(s, st, a, payload_out);
 }
 
 // search + MVCC + payload rows. Default: probe_kernel then gather_rows_kernel (0.398 ms per 2^20 YCSB probes);
 // STAGE_PROBE_FUSED=1 selects the warp-specialised single kernel of probe_fused.cuh (measured 0.437 ms: under a
 // saturated memory system the producers' dependent loads are too slow to keep the consumers fed — profiles/README.md).
-// All pointers are device pointers.
-static int probe_device(stage_snapshot *s, ProbeArgs a, uint8_t *payload_out) {
+// All pointers are device-visible (device memory, or device aliases of pinned host memory for the outputs).
+static int probe_device(stage_snapshot *s, const Lane &ln, ProbeArgs a, uint8_t *payload_out) {
     if (a.n == 0) return STAGE_OK;
     int rc;
     static const bool fused = getenv("STAGE_PROBE_FUSED") && atoi(getenv("STAGE_PROBE_FUSED")) != 0;
     if (fused && payload_out) {
-        if (s->timing) {
-            CUDA_TRY(cudaEventRecord(s->tev[0], s->stream));
-            CUDA_TRY(cudaEventRecord(s->tev[1], s->stream));
+        if (ln.timing) {
+            CUDA_TRY(cudaEventRecord(s->tev[0], ln.st));
+            CUDA_TRY(cudaEventRecord(s->tev[1], ln.st));
         }
         switch (s->nw) {
-            case 1: rc = launch_probe_fused<1>(s, a, payload_out); break;
-            case 2: rc = launch_probe_fused<2>(s, a, payload_out); break;
-            case 4: rc = launch_probe_fused<4>(s, a, payload_out); break;
-            default: rc = launch_probe_fused<8>(s, a, payload_out); break;
+            case 1: rc = launch_probe_fused<1>(s, ln.st, a, payload_out); break;
+            case 2: rc = launch_probe_fused<2>(s, ln.st, a, payload_out); break;
+            case 4: rc = launch_probe_fused<4>(s, ln.st, a, payload_out); break;
+            default: rc = launch_probe_fused<8>(s, ln.st, a, payload_out); break;
         }
-        if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[2], s->stream));
-        s->timed_gather = true;
+        if (ln.timing) {
+            CUDA_TRY(cudaEventRecord(s->tev[2], ln.st));
+            s->timed_gather = true;
+        }
         return rc;
     }
     if (payload_out) {
-        if ((rc = s->sc_srcrow.ensure(a.n * 4))) return rc;
-        a.src_row = static_cast<uint32_t *>(s->sc_srcrow.p);
+        if ((rc = ln.srcrow->ensure(a.n * 4))) return rc;
+        a.src_row = static_cast<uint32_t *>(ln.srcrow->p);
     }
-    if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[0], s->stream));
-    switch (s->nw) {
-        case 1: rc = launch_probe<1>(s, a); break;
-        case 2: rc = launch_probe<2>(s, a); break;
-        case 4: rc = launch_probe<4>(s, a); break;
-        default: rc = launch_probe<8>(s, a); break;
+    if (ln.timing) CUDA_TRY(cudaEventRecord(s->tev[0], ln.st));
+    if ((rc = launch_probe_nw(s, ln.st, a))) return rc;
+    if (ln.timing) CUDA_TRY(cudaEventRecord(s->tev[1], ln.st));
+    rc = launch_gather(s, ln.st, a.src_row, a.n, payload_out);
+    if (ln.timing) {
+        CUDA_TRY(cudaEventRecord(s->tev[2], ln.st));
+        s->timed_gather = payload_out != nullptr;
     }
-    if (rc) return rc;
-    if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[1], s->stream));
-    rc = launch_gather(s, a.src_row, a.n, payload_out);
-    if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[2], s->stream));
-    s->timed_gather = payload_out != nullptr;
     return rc;
+}
+
+// ---- host-buffer calls: contexts, device aliases of pinned memory ---------------------------------------------
+static HostCtx *ctx_acquire(stage_snapshot *s, int *rc_out) {
+    constexpr size_t kMaxCtx = 16;
+    std::unique_lock<std::mutex> lk(s->ctx_mu);
+    for (;;) {
+        for (HostCtx *c : s->ctx_pool)
+            if (!c->busy) {
+                c->busy = true;
+                return c;
+            }
+        if (s->ctx_pool.size() < kMaxCtx) break;
+        s->ctx_cv.wait(lk);
+    }
+    auto *c = new HostCtx();
+    cudaError_t e = cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->cp, cudaStreamNonBlocking);
+    for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+        e = cudaEventCreateWithFlags(&c->done[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->drained[i], cudaEventDisableTiming);
+    }
+    if (e != cudaSuccess) {
+        g_last_error = std::string("host-call context: ") + cudaGetErrorString(e);
+        c->release_all();
+        delete c;
+        *rc_out = STAGE_ERR_CUDA;
+        return nullptr;
+    }
+    c->busy = true;
+    s->ctx_pool.push_back(c);
+    return c;
+}
+struct CtxGuard {
+    stage_snapshot *s;
+    HostCtx *c;
+    ~CtxGuard() {
+        if (!c) return;
+        {
+            std::lock_guard<std::mutex> lk(s->ctx_mu);
+            c->busy = false;
+        }
+        s->ctx_cv.notify_one();
+    }
+};
+
+// Device alias of a host pointer the kernels may store to directly (cudaHostAlloc / cudaHostRegister memory under
+// unified addressing), or nullptr for pageable memory.
+static void *mapped_alias(const void *p) {
+    if (!p) return nullptr;
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return at.type == cudaMemoryTypeHost ? at.devicePointer : nullptr;
+}
+
+// How STAGE_IO_HOST results cross PCIe. "zerocopy": the kernels store keys, commit ids and payload rows straight into
+// the caller's pinned buffers (one pass, only the rows that exist, no result slab in HBM); needs pinned outputs
+// (stage_gpu_host_alloc / stage_gpu_host_register). "staged": results are produced into double-buffered HBM scratch
+// and copied out by the DMA engine while the next chunk is planned and gathered; works with any host memory.
+// STAGE_HOST_PATH=staged|zerocopy forces one; the default picks zero copy whenever every output is pinned
+// (profiles/r2_pcie_ceiling.txt has the measurements behind that choice).
+enum { kHostAuto = 0, kHostStaged = 1, kHostZeroCopy = 2 };
+static int host_path_mode() {
+    static const int m = [] {
+        const char *e = getenv("STAGE_HOST_PATH");
+        if (e && !strcmp(e, "staged")) return (int) kHostStaged;
+        if (e && !strcmp(e, "zerocopy")) return (int) kHostZeroCopy;
+        return (int) kHostAuto;
+    }();
+    return m;
+}
+
+static int probe_host_zerocopy(stage_snapshot *s, HostCtx *c, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *d_found,
+                               uint32_t *d_ts, uint8_t *d_key, uint8_t *d_pay) {
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    int rc;
+    if ((rc = c->keys.ensure(n * K))) return rc;
+    CUDA_TRY(cudaMemcpyAsync(c->keys.p, keys, n * K, cudaMemcpyHostToDevice, c->st));
+    const Lane ln{c->st, &c->srcrow, false};
+    const uint64_t chunk = 1ull << 22;                       // bounds the source-row scratch (16 MiB)
+    for (uint64_t b = 0; b < n; b += chunk) {
+        ProbeArgs a{};
+        a.n = std::min(chunk, n - b);
+        a.read_ts = read_ts;
+        a.keys = static_cast<const uint8_t *>(c->keys.p) + b * K;
+        a.found = d_found ? d_found + b : nullptr;
+        a.ts_out = d_ts ? d_ts + b : nullptr;
+        a.key_out = d_key ? d_key + b * K : nullptr;
+        if ((rc = probe_device(s, ln, a, d_pay ? d_pay + b * (uint64_t) P : nullptr))) return rc;
+    }
+    CUDA_TRY(cudaStreamSynchronize(c->st));
+    return STAGE_OK;
+}
+
+static int probe_host_staged(stage_snapshot *s, HostCtx *c, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
+                             uint32_t *ts, void *key_out, void *payload_out) {
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    // ~64 MiB of result rows per chunk, two chunks in flight: chunk i is copied out (copy stream) while chunk i+1 is
+    // searched and gathered (kernel stream)
+    const uint64_t chunk = std::max<uint64_t>(1024, std::min<uint64_t>(1ull << 20, (64ull << 20) / std::max<uint32_t>(P, 1)));
+    const uint64_t cm = std::min(chunk, n);
+    int rc;
+    if ((rc = c->keys.ensure(n * K))) return rc;
+    for (int i = 0; i < 2; ++i) {
+        if (found && (rc = c->found[i].ensure(cm))) return rc;
+        if (ts && (rc = c->ts[i].ensure(cm * 4))) return rc;
+        if (key_out && (rc = c->keyout[i].ensure(cm * K))) return rc;
+        if (payload_out && (rc = c->payload[i].ensure(cm * (uint64_t) P))) return rc;
+    }
+    CUDA_TRY(cudaMemcpyAsync(c->keys.p, keys, n * K, cudaMemcpyHostToDevice, c->st));
+    const Lane ln{c->st, &c->srcrow, false};
+    uint64_t i = 0;
+    for (uint64_t b = 0; b < n; b += chunk, ++i) {
+        const int buf = (int) (i & 1);
+        const uint64_t m = std::min(chunk, n - b);
+        if (i >= 2) CUDA_TRY(cudaStreamWaitEvent(c->st, c->drained[buf], 0));
+        ProbeArgs a{};
+        a.n = m;
+        a.read_ts = read_ts;
+        a.keys = static_cast<const uint8_t *>(c->keys.p) + b * K;
+        a.found = found ? static_cast<uint8_t *>(c->found[buf].p) : nullptr;
+        a.ts_out = ts ? static_cast<uint32_t *>(c->ts[buf].p) : nullptr;
+        a.key_out = key_out ? static_cast<uint8_t *>(c->keyout[buf].p) : nullptr;
+        // rows of missed probes come back zero-filled in this mode
+        if (key_out) CUDA_TRY(cudaMemsetAsync(c->keyout[buf].p, 0, m * K, c->st));
+        if (payload_out) CUDA_TRY(cudaMemsetAsync(c->payload[buf].p, 0, m * (uint64_t) P, c->st));
+        if ((rc = probe_device(s, ln, a, payload_out ? static_cast<uint8_t *>(c->payload[buf].p) : nullptr))) return rc;
+        CUDA_TRY(cudaEventRecord(c->done[buf], c->st));
+        CUDA_TRY(cudaStreamWaitEvent(c->cp, c->done[buf], 0));
+        if (found) CUDA_TRY(cudaMemcpyAsync(found + b, c->found[buf].p, m, cudaMemcpyDeviceToHost, c->cp));
+        if (ts) CUDA_TRY(cudaMemcpyAsync(ts + b, c->ts[buf].p, m * 4, cudaMemcpyDeviceToHost, c->cp));
+        if (key_out)
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(key_out) + b * K, c->keyout[buf].p, m * K, cudaMemcpyDeviceToHost, c->cp));
+        if (payload_out)
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(payload_out) + b * (uint64_t) P, c->payload[buf].p, m * (uint64_t) P,
+                                     cudaMemcpyDeviceToHost, c->cp));
+        CUDA_TRY(cudaEventRecord(c->drained[buf], c->cp));
+    }
+    CUDA_TRY(cudaStreamSynchronize(c->cp));
+    CUDA_TRY(cudaStreamSynchronize(c->st));
+    return STAGE_OK;
 }
 
 extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
                                      uint32_t *ts, void *key_out, void *payload_out, int flags) {
     if (!s || (n && !keys)) return STAGE_ERR_ARG;
     if (!s->sealed) return STAGE_ERR_STATE;
-    std::lock_guard<std::mutex> lock(s->mu);
     CUDA_TRY(cudaSetDevice(s->device));
-    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
-    ProbeArgs a{};
-    a.n = n;
-    a.read_ts = read_ts;
     if (flags & STAGE_IO_DEVICE) {
+        std::lock_guard<std::mutex> lock(s->mu);        // one enqueue at a time on the snapshot stream (shared scratch)
+        ProbeArgs a{};
+        a.n = n;
+        a.read_ts = read_ts;
         a.keys = static_cast<const uint8_t *>(keys);
         a.found = found; a.ts_out = ts;
         a.key_out = static_cast<uint8_t *>(key_out);
-        return probe_device(s, a, static_cast<uint8_t *>(payload_out));
+        return probe_device(s, Lane{s->stream, &s->sc_srcrow, s->timing}, a, static_cast<uint8_t *>(payload_out));
     }
-    // host I/O: chunked so the device scratch stays bounded (<= 256 Ki probes per chunk)
-    const uint64_t chunk = 1ull << 18;
-    int rc;
-    if ((rc = s->sc_keys.ensure(std::min(n, chunk) * K))) return rc;
-    if (found && (rc = s->sc_found.ensure(std::min(n, chunk)))) return rc;
-    if (ts && (rc = s->sc_ts.ensure(std::min(n, chunk) * 4))) return rc;
-    if (key_out && (rc = s->sc_keyout.ensure(std::min(n, chunk) * K))) return rc;
-    if (payload_out && (rc = s->sc_payload.ensure(std::min(n, chunk) * (uint64_t) P))) return rc;
-    for (uint64_t b = 0; b < n; b += chunk) {
-        const uint64_t m = std::min(chunk, n - b);
-        CUDA_TRY(cudaMemcpyAsync(s->sc_keys.p, static_cast<const uint8_t *>(keys) + b * K, m * K, cudaMemcpyHostToDevice,
-                                 s->stream));
-        // rows of missed probes are left untouched in the caller's buffer: start from its content
-        if (key_out) CUDA_TRY(cudaMemsetAsync(s->sc_keyout.p, 0, m * K, s->stream));
-        a.keys = static_cast<const uint8_t *>(s->sc_keys.p);
-        a.n = m;
-        a.found = found ? static_cast<uint8_t *>(s->sc_found.p) : nullptr;
-        a.ts_out = ts ? static_cast<uint32_t *>(s->sc_ts.p) : nullptr;
-        a.key_out = key_out ? static_cast<uint8_t *>(s->sc_keyout.p) : nullptr;
-        if (payload_out) CUDA_TRY(cudaMemsetAsync(s->sc_payload.p, 0, m * (uint64_t) P, s->stream));
-        if ((rc = probe_device(s, a, payload_out ? static_cast<uint8_t *>(s->sc_payload.p) : nullptr))) return rc;
-        if (found) CUDA_TRY(cudaMemcpyAsync(found + b, s->sc_found.p, m, cudaMemcpyDeviceToHost, s->stream));
-        if (ts) CUDA_TRY(cudaMemcpyAsync(ts + b, s->sc_ts.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
-        if (key_out)
-            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(key_out) + b * K, s->sc_keyout.p, m * K, cudaMemcpyDeviceToHost,
-                                     s->stream));
-        if (payload_out)
-            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(payload_out) + b * (uint64_t) P, s->sc_payload.p,
-                                     m * (uint64_t) P, cudaMemcpyDeviceToHost, s->stream));
-        CUDA_TRY(cudaStreamSynchronize(s->stream));
+    if (n == 0) return STAGE_OK;
+    int rc = STAGE_OK;
+    CtxGuard g{s, ctx_acquire(s, &rc)};
+    if (!g.c) return rc;
+    const int mode = host_path_mode();
+    if (mode != kHostStaged) {
+        uint8_t *df = static_cast<uint8_t *>(mapped_alias(found)), *dk = static_cast<uint8_t *>(mapped_alias(key_out)),
+                *dp = static_cast<uint8_t *>(mapped_alias(payload_out));
+        uint32_t *dt = static_cast<uint32_t *>(mapped_alias(ts));
+        if ((!found || df) && (!ts || dt) && (!key_out || dk) && (!payload_out || dp))
+            return probe_host_zerocopy(s, g.c, keys, n, read_ts, df, dt, dk, dp);
+        if (mode == kHostZeroCopy) {
+            g_last_error = "STAGE_HOST_PATH=zerocopy needs pinned output buffers (stage_gpu_host_alloc / stage_gpu_host_register)";
+            return STAGE_ERR_ARG;
+        }
     }
-    return STAGE_OK;
+    return probe_host_staged(s, g.c, keys, n, read_ts, found, ts, key_out, payload_out);
 }
 
 template <int NW>
@@ -1719,27 +1917,141 @@ static int launch_scan(stage_snapshot *s, const ScanArgs &a, cudaStream_t st) {
     LAUNCH_CHECK();
     return STAGE_OK;
 }
+static int launch_scan_nw(stage_snapshot *s, const ScanArgs &a, cudaStream_t st) {
+    switch (s->nw) {
+        case 1: return launch_scan<1>(s, a, st);
+        case 2: return launch_scan<2>(s, a, st);
+        case 4: return launch_scan<4>(s, a, st);
+        default: return launch_scan<8>(s, a, st);
+    }
+}
 
-// plan (scan_plan_kernel) then payload gather; all pointers are device pointers
-static int scan_device(stage_snapshot *s, ScanArgs a, uint8_t *payload_out) {
+// plan (scan_plan_kernel) then payload gather; all pointers are device-visible
+static int scan_device(stage_snapshot *s, const Lane &ln, ScanArgs a, uint8_t *payload_out) {
     if (a.n == 0) return STAGE_OK;
     const uint64_t slots = a.n * (uint64_t) a.out_stride;
     int rc;
-    if ((rc = s->sc_srcrow.ensure(std::max<uint64_t>(slots, 1) * 4))) return rc;
-    a.src_row = static_cast<uint32_t *>(s->sc_srcrow.p);
-    if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[0], s->stream));
-    switch (s->nw) {
-        case 1: rc = launch_scan<1>(s, a, s->stream); break;
-        case 2: rc = launch_scan<2>(s, a, s->stream); break;
-        case 4: rc = launch_scan<4>(s, a, s->stream); break;
-        default: rc = launch_scan<8>(s, a, s->stream); break;
+    if ((rc = ln.srcrow->ensure(std::max<uint64_t>(slots, 1) * 4))) return rc;
+    a.src_row = static_cast<uint32_t *>(ln.srcrow->p);
+    a.stats = s->d_stats;
+    if (ln.timing) CUDA_TRY(cudaEventRecord(s->tev[0], ln.st));
+    if ((rc = launch_scan_nw(s, a, ln.st))) return rc;
+    if (ln.timing) CUDA_TRY(cudaEventRecord(s->tev[1], ln.st));
+    rc = launch_gather(s, ln.st, a.src_row, slots, payload_out);
+    if (ln.timing) {
+        CUDA_TRY(cudaEventRecord(s->tev[2], ln.st));
+        s->timed_gather = payload_out != nullptr;
     }
-    if (rc) return rc;
-    if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[1], s->stream));
-    rc = launch_gather(s, a.src_row, slots, payload_out);
-    if (s->timing) CUDA_TRY(cudaEventRecord(s->tev[2], s->stream));
-    s->timed_gather = payload_out != nullptr;
     return rc;
+}
+
+static int scan_host_zerocopy(stage_snapshot *s, HostCtx *c, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
+                              uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *d_counts, uint8_t *d_key,
+                              uint32_t *d_ts, uint8_t *d_pay) {
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    int rc;
+    if ((rc = c->keys.ensure(n * K)) || (rc = c->sizes.ensure(n * 4))) return rc;
+    CUDA_TRY(cudaMemcpyAsync(c->keys.p, start_keys, n * K, cudaMemcpyHostToDevice, c->st));
+    CUDA_TRY(cudaMemcpyAsync(c->sizes.p, scan_sizes, n * 4, cudaMemcpyHostToDevice, c->st));
+    const Lane ln{c->st, &c->srcrow, false};
+    // bounds the source-row scratch: <= 64 Mi result slots per launch pair
+    const uint64_t chunk = std::max<uint64_t>(1, (1ull << 26) / std::max<uint32_t>(out_stride, 1));
+    for (uint64_t b = 0; b < n; b += chunk) {
+        const uint64_t rb = b * out_stride;
+        ScanArgs a{};
+        a.out_stride = out_stride;
+        a.read_ts = read_ts;
+        a.apply_visibility = apply_visibility;
+        a.n = std::min(chunk, n - b);
+        a.start_keys = static_cast<const uint8_t *>(c->keys.p) + b * K;
+        a.scan_sizes = static_cast<const uint32_t *>(c->sizes.p) + b;
+        a.row_counts = d_counts + b;
+        a.key_out = d_key ? d_key + rb * K : nullptr;
+        a.ts_out = d_ts ? d_ts + rb : nullptr;
+        if ((rc = scan_device(s, ln, a, d_pay ? d_pay + rb * (uint64_t) P : nullptr))) return rc;
+    }
+    CUDA_TRY(cudaStreamSynchronize(c->st));
+    return STAGE_OK;
+}
+
+static int scan_host_staged(stage_snapshot *s, HostCtx *c, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
+                            uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts, void *key_out,
+                            uint32_t *ts_out, void *payload_out) {
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    const uint64_t slot_bytes = (uint64_t) P + K + 4;
+    // ~128 MiB of result slots per chunk, two chunks in flight (kernel stream / copy stream)
+    const uint64_t chunk = std::min<uint64_t>(n, std::max<uint64_t>(1, (128ull << 20) / std::max<uint64_t>(1, slot_bytes * out_stride)));
+    // long scans: only the rows a scan returned cross PCIe (one copy per run of scans); short scans: the whole chunk
+    const bool per_scan = payload_out && (uint64_t) out_stride * P >= (64u << 10);
+    int rc;
+    if ((rc = c->keys.ensure(n * K)) || (rc = c->sizes.ensure(n * 4))) return rc;
+    for (int i = 0; i < 2; ++i) {
+        if ((rc = c->counts[i].ensure(chunk * 4))) return rc;
+        if (key_out && (rc = c->keyout[i].ensure(chunk * out_stride * K))) return rc;
+        if (ts_out && (rc = c->ts[i].ensure(chunk * out_stride * 4))) return rc;
+        if (payload_out && (rc = c->payload[i].ensure(chunk * out_stride * (uint64_t) P))) return rc;
+    }
+    if (c->h_counts_cap < 2 * chunk) {
+        if (c->h_counts) cudaFreeHost(c->h_counts);
+        c->h_counts = nullptr;
+        c->h_counts_cap = 0;
+        CUDA_TRY(cudaHostAlloc((void **) &c->h_counts, 2 * chunk * 4, cudaHostAllocDefault));
+        c->h_counts_cap = 2 * chunk;
+    }
+    CUDA_TRY(cudaMemcpyAsync(c->keys.p, start_keys, n * K, cudaMemcpyHostToDevice, c->st));
+    CUDA_TRY(cudaMemcpyAsync(c->sizes.p, scan_sizes, n * 4, cudaMemcpyHostToDevice, c->st));
+    const Lane ln{c->st, &c->srcrow, false};
+    uint64_t i = 0;
+    for (uint64_t b = 0; b < n; b += chunk, ++i) {
+        const int buf = (int) (i & 1);
+        const uint64_t m = std::min(chunk, n - b), rows = m * out_stride, rb = b * out_stride;
+        if (i >= 2) CUDA_TRY(cudaStreamWaitEvent(c->st, c->drained[buf], 0));
+        // slots beyond a scan's row count come back zero-filled (keys / commit ids always; payload in whole-chunk mode)
+        if (key_out) CUDA_TRY(cudaMemsetAsync(c->keyout[buf].p, 0, rows * K, c->st));
+        if (ts_out) CUDA_TRY(cudaMemsetAsync(c->ts[buf].p, 0, rows * 4, c->st));
+        if (payload_out && !per_scan) CUDA_TRY(cudaMemsetAsync(c->payload[buf].p, 0, rows * (uint64_t) P, c->st));
+        ScanArgs a{};
+        a.out_stride = out_stride;
+        a.read_ts = read_ts;
+        a.apply_visibility = apply_visibility;
+        a.n = m;
+        a.start_keys = static_cast<const uint8_t *>(c->keys.p) + b * K;
+        a.scan_sizes = static_cast<const uint32_t *>(c->sizes.p) + b;
+        a.row_counts = static_cast<uint32_t *>(c->counts[buf].p);
+        a.key_out = key_out ? static_cast<uint8_t *>(c->keyout[buf].p) : nullptr;
+        a.ts_out = ts_out ? static_cast<uint32_t *>(c->ts[buf].p) : nullptr;
+        uint8_t *d_pay = payload_out ? static_cast<uint8_t *>(c->payload[buf].p) : nullptr;
+        if ((rc = scan_device(s, ln, a, d_pay))) return rc;
+        uint32_t *hc = c->h_counts + (size_t) buf * chunk;
+        CUDA_TRY(cudaMemcpyAsync(hc, c->counts[buf].p, m * 4, cudaMemcpyDeviceToHost, c->st));
+        CUDA_TRY(cudaEventRecord(c->done[buf], c->st));
+        // the row counts are needed on the host to size the copies; the copy stream is still busy with chunk i-1
+        CUDA_TRY(cudaEventSynchronize(c->done[buf]));
+        memcpy(row_counts + b, hc, m * 4);
+        CUDA_TRY(cudaStreamWaitEvent(c->cp, c->done[buf], 0));
+        if (key_out)
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(key_out) + rb * K, c->keyout[buf].p, rows * K, cudaMemcpyDeviceToHost, c->cp));
+        if (ts_out) CUDA_TRY(cudaMemcpyAsync(ts_out + rb, c->ts[buf].p, rows * 4, cudaMemcpyDeviceToHost, c->cp));
+        if (payload_out && !per_scan)
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(payload_out) + rb * (uint64_t) P, d_pay, rows * (uint64_t) P,
+                                     cudaMemcpyDeviceToHost, c->cp));
+        if (per_scan) {
+            uint8_t *hp = static_cast<uint8_t *>(payload_out) + rb * (uint64_t) P;
+            for (uint64_t j = 0; j < m;) {
+                // a run of full scans and the scan that ends it are contiguous in both buffers: one copy
+                uint64_t e = j;
+                while (e + 1 < m && hc[e] == out_stride) ++e;
+                const uint64_t bytes = ((e - j) * (uint64_t) out_stride + hc[e]) * P;
+                if (bytes)
+                    CUDA_TRY(cudaMemcpyAsync(hp + j * (uint64_t) out_stride * P, d_pay + j * (uint64_t) out_stride * P, bytes,
+                                             cudaMemcpyDeviceToHost, c->cp));
+                j = e + 1;
+            }
+        }
+        CUDA_TRY(cudaEventRecord(c->drained[buf], c->cp));
+    }
+    CUDA_TRY(cudaStreamSynchronize(c->cp));
+    return STAGE_OK;
 }
 
 extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
@@ -1747,62 +2059,40 @@ extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys,
                                     void *key_out, uint32_t *ts_out, void *payload_out, int flags) {
     if (!s || (n && (!start_keys || !scan_sizes || !row_counts))) return STAGE_ERR_ARG;
     if (!s->sealed) return STAGE_ERR_STATE;
-    std::lock_guard<std::mutex> lock(s->mu);
     CUDA_TRY(cudaSetDevice(s->device));
-    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
-    ScanArgs a{};
-    a.out_stride = out_stride;
-    a.read_ts = read_ts;
-    a.apply_visibility = apply_visibility;
     if (flags & STAGE_IO_DEVICE) {
+        std::lock_guard<std::mutex> lock(s->mu);        // one enqueue at a time on the snapshot stream (shared scratch)
+        ScanArgs a{};
+        a.out_stride = out_stride;
+        a.read_ts = read_ts;
+        a.apply_visibility = apply_visibility;
         a.start_keys = static_cast<const uint8_t *>(start_keys);
-        a.scan_sizes = scan_sizes;
+        a.scan_sizes = scan_sizes;                      // sizes above out_stride are clamped by the plan kernels
         a.n = n;
         a.row_counts = row_counts;
         a.key_out = static_cast<uint8_t *>(key_out);
         a.ts_out = ts_out;
-        return scan_device(s, a, static_cast<uint8_t *>(payload_out));
+        return scan_device(s, Lane{s->stream, &s->sc_srcrow, s->timing}, a, static_cast<uint8_t *>(payload_out));
     }
     for (uint64_t i = 0; i < n; ++i)
         if (scan_sizes[i] > out_stride) return STAGE_ERR_ARG;
-    // host I/O: chunks of scans so that the result scratch stays <= ~1 GiB
-    const uint64_t row_bytes = (uint64_t) P + K + 4;
-    uint64_t chunk = std::max<uint64_t>(1, (1ull << 30) / std::max<uint64_t>(1, row_bytes * out_stride));
-    chunk = std::min<uint64_t>(chunk, std::max<uint64_t>(n, 1));
-    int rc;
-    if ((rc = s->sc_keys.ensure(chunk * K)) || (rc = s->sc_sizes.ensure(chunk * 4)) || (rc = s->sc_counts.ensure(chunk * 4)))
-        return rc;
-    if (key_out && (rc = s->sc_keyout.ensure(chunk * out_stride * K))) return rc;
-    if (ts_out && (rc = s->sc_ts.ensure(chunk * out_stride * 4))) return rc;
-    if (payload_out && (rc = s->sc_payload.ensure(chunk * out_stride * (uint64_t) P))) return rc;
-    for (uint64_t b = 0; b < n; b += chunk) {
-        const uint64_t m = std::min(chunk, n - b);
-        const uint64_t rows = m * out_stride;
-        CUDA_TRY(cudaMemcpyAsync(s->sc_keys.p, static_cast<const uint8_t *>(start_keys) + b * K, m * K,
-                                 cudaMemcpyHostToDevice, s->stream));
-        CUDA_TRY(cudaMemcpyAsync(s->sc_sizes.p, scan_sizes + b, m * 4, cudaMemcpyHostToDevice, s->stream));
-        if (key_out) CUDA_TRY(cudaMemsetAsync(s->sc_keyout.p, 0, rows * K, s->stream));
-        if (ts_out) CUDA_TRY(cudaMemsetAsync(s->sc_ts.p, 0, rows * 4, s->stream));
-        if (payload_out) CUDA_TRY(cudaMemsetAsync(s->sc_payload.p, 0, rows * (uint64_t) P, s->stream));
-        a.start_keys = static_cast<const uint8_t *>(s->sc_keys.p);
-        a.scan_sizes = static_cast<const uint32_t *>(s->sc_sizes.p);
-        a.n = m;
-        a.row_counts = static_cast<uint32_t *>(s->sc_counts.p);
-        a.key_out = key_out ? static_cast<uint8_t *>(s->sc_keyout.p) : nullptr;
-        a.ts_out = ts_out ? static_cast<uint32_t *>(s->sc_ts.p) : nullptr;
-        if ((rc = scan_device(s, a, payload_out ? static_cast<uint8_t *>(s->sc_payload.p) : nullptr))) return rc;
-        CUDA_TRY(cudaMemcpyAsync(row_counts + b, s->sc_counts.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
-        const uint64_t rb = b * out_stride;
-        if (key_out)
-            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(key_out) + rb * K, s->sc_keyout.p, rows * K,
-                                     cudaMemcpyDeviceToHost, s->stream));
-        if (ts_out) CUDA_TRY(cudaMemcpyAsync(ts_out + rb, s->sc_ts.p, rows * 4, cudaMemcpyDeviceToHost, s->stream));
-        if (payload_out)
-            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(payload_out) + rb * (uint64_t) P, s->sc_payload.p,
-                                     rows * (uint64_t) P, cudaMemcpyDeviceToHost, s->stream));
-        CUDA_TRY(cudaStreamSynchronize(s->stream));
+    if (n == 0) return STAGE_OK;
+    int rc = STAGE_OK;
+    CtxGuard g{s, ctx_acquire(s, &rc)};
+    if (!g.c) return rc;
+    const int mode = host_path_mode();
+    if (mode != kHostStaged) {
+        uint32_t *dc = static_cast<uint32_t *>(mapped_alias(row_counts)), *dt = static_cast<uint32_t *>(mapped_alias(ts_out));
+        uint8_t *dk = static_cast<uint8_t *>(mapped_alias(key_out)), *dp = static_cast<uint8_t *>(mapped_alias(payload_out));
+        if (dc && (!ts_out || dt) && (!key_out || dk) && (!payload_out || dp))
+            return scan_host_zerocopy(s, g.c, start_keys, scan_sizes, n, out_stride, read_ts, apply_visibility, dc, dk, dt, dp);
+        if (mode == kHostZeroCopy) {
+            g_last_error = "STAGE_HOST_PATH=zerocopy needs pinned output buffers (stage_gpu_host_alloc / stage_gpu_host_register)";
+            return STAGE_ERR_ARG;
+        }
     }
-    return STAGE_OK;
+    return scan_host_staged(s, g.c, start_keys, scan_sizes, n, out_stride, read_ts, apply_visibility, row_counts, key_out, ts_out,
+                            payload_out);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1855,13 +2145,7 @@ extern "C" int stage_gpu_probe_project(stage_snapshot_t *s, const void *keys, ui
             a.ts_out = ts ? static_cast<uint32_t *>(s->sc_ts.p) : nullptr;
             cdst = static_cast<uint8_t *>(s->sc_payload.p);
         }
-        switch (s->nw) {
-            case 1: rc = launch_probe<1>(s, a); break;
-            case 2: rc = launch_probe<2>(s, a); break;
-            case 4: rc = launch_probe<4>(s, a); break;
-            default: rc = launch_probe<8>(s, a); break;
-        }
-        if (rc) return rc;
+        if ((rc = launch_probe_nw(s, s->stream, a))) return rc;
         if ((rc = launch_gather_cols(s, a.src_row, m, col_off, col_len, cdst))) return rc;
         if (!dev) {
             if (found) CUDA_TRY(cudaMemcpyAsync(found + b, s->sc_found.p, m, cudaMemcpyDeviceToHost, s->stream));
@@ -1906,13 +2190,7 @@ extern "C" int stage_gpu_probe_aggregate_i32(stage_snapshot_t *s, const void *ke
             CUDA_TRY(cudaMemcpyAsync(s->sc_keys.p, static_cast<const uint8_t *>(keys) + b * K, m * K, cudaMemcpyHostToDevice, s->stream));
             a.keys = static_cast<const uint8_t *>(s->sc_keys.p);
         }
-        switch (s->nw) {
-            case 1: rc = launch_probe<1>(s, a); break;
-            case 2: rc = launch_probe<2>(s, a); break;
-            case 4: rc = launch_probe<4>(s, a); break;
-            default: rc = launch_probe<8>(s, a); break;
-        }
-        if (rc) return rc;
+        if ((rc = launch_probe_nw(s, s->stream, a))) return rc;
         const unsigned blocks = (unsigned) std::min<uint64_t>((m + 255) / 256, (uint64_t) sm_count() * 8);
         aggregate_i32_kernel<<<blocks, 256, 0, s->stream>>>(a.src_row, m, s->d_payload, s->d_ver_payload, P, col_off, threshold, d_out);
         LAUNCH_CHECK();
@@ -1971,13 +2249,8 @@ extern "C" int stage_gpu_scan_project(stage_snapshot_t *s, const void *start_key
             a.key_out = key_out ? static_cast<uint8_t *>(s->sc_keyout.p) : nullptr;
             cdst = static_cast<uint8_t *>(s->sc_payload.p);
         }
-        switch (s->nw) {
-            case 1: rc = launch_scan<1>(s, a, s->stream); break;
-            case 2: rc = launch_scan<2>(s, a, s->stream); break;
-            case 4: rc = launch_scan<4>(s, a, s->stream); break;
-            default: rc = launch_scan<8>(s, a, s->stream); break;
-        }
-        if (rc) return rc;
+        a.stats = s->d_stats;
+        if ((rc = launch_scan_nw(s, a, s->stream))) return rc;
         if ((rc = launch_gather_cols(s, a.src_row, rows, col_off, col_len, cdst))) return rc;
         if (!dev) {
             CUDA_TRY(cudaMemcpyAsync(row_counts + b, s->sc_counts.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
@@ -2024,7 +2297,7 @@ extern "C" int stage_gpu_scan_physical(stage_snapshot_t *s, uint64_t first_row, 
     };
     if (flags & STAGE_IO_DEVICE) {
         if ((rc = emit(first_row, n, static_cast<uint8_t *>(key_out), ts_out))) return rc;
-        return launch_gather(s, s->d_phys + first_row, n, static_cast<uint8_t *>(payload_out));
+        return launch_gather(s, s->stream, s->d_phys + first_row, n, static_cast<uint8_t *>(payload_out));
     }
     const uint64_t chunk = std::max<uint64_t>(1, std::min<uint64_t>(n, (512ull << 20) / (P + K + 4)));
     if (key_out && (rc = s->sc_keyout.ensure(chunk * K))) return rc;
@@ -2035,7 +2308,7 @@ extern "C" int stage_gpu_scan_physical(stage_snapshot_t *s, uint64_t first_row, 
         if ((rc = emit(first_row + b, m, key_out ? static_cast<uint8_t *>(s->sc_keyout.p) : nullptr,
                        ts_out ? static_cast<uint32_t *>(s->sc_ts.p) : nullptr)))
             return rc;
-        if (payload_out && (rc = launch_gather(s, s->d_phys + first_row + b, m, static_cast<uint8_t *>(s->sc_payload.p)))) return rc;
+        if (payload_out && (rc = launch_gather(s, s->stream, s->d_phys + first_row + b, m, static_cast<uint8_t *>(s->sc_payload.p)))) return rc;
         if (key_out) CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(key_out) + b * K, s->sc_keyout.p, m * K, cudaMemcpyDeviceToHost, s->stream));
         if (ts_out) CUDA_TRY(cudaMemcpyAsync(ts_out + b, s->sc_ts.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
         if (payload_out)
@@ -2448,12 +2721,8 @@ extern "C" int stage_gpu_exchange_serve_scans(stage_exchange_t *x, stage_snapsho
         sa.key_out = x->d_sc_keys + slot0 * l.rows * l.kpad;
         sa.ts_out = x->d_sc_ts + slot0 * l.rows;
         sa.src_row = x->d_sc_src + slot0 * l.rows;
-        switch (x->nw) {
-            case 1: rc = launch_scan<1>(s, sa, st); break;
-            case 2: rc = launch_scan<2>(s, sa, st); break;
-            case 4: rc = launch_scan<4>(s, sa, st); break;
-            default: rc = launch_scan<8>(s, sa, st); break;
-        }
+        sa.stats = s->d_stats;
+        rc = launch_scan_nw(s, sa, st);
     }
     if (rc) return rc;
     ScanDeliverArgs d{};
@@ -2554,6 +2823,28 @@ extern "C" int stage_gpu_exchange_destroy(stage_exchange_t *x) {
 // ------------------------------------------------------------------------------------------------
 // utilities
 // ------------------------------------------------------------------------------------------------
+extern "C" int stage_gpu_snapshot_counters(stage_snapshot_t *s, stage_counters_t *out, int reset) {
+    if (!s || !out) return STAGE_ERR_ARG;
+    if (!s->d_stats) return STAGE_ERR_STATE;
+    CUDA_TRY(cudaSetDevice(s->device));
+    CUDA_TRY(cudaDeviceSynchronize());
+    unsigned long long h[8] = {0};
+    CUDA_TRY(cudaMemcpy(h, s->d_stats, sizeof(h), cudaMemcpyDeviceToHost));
+    out->slot_order_scans = h[0];
+    if (reset) CUDA_TRY(cudaMemset(s->d_stats, 0, sizeof(h)));
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_host_register(void *p, size_t bytes) {
+    if (!p || !bytes) return STAGE_ERR_ARG;
+    CUDA_TRY(cudaHostRegister(p, bytes, cudaHostRegisterDefault));
+    return STAGE_OK;
+}
+extern "C" int stage_gpu_host_unregister(void *p) {
+    if (!p) return STAGE_ERR_ARG;
+    CUDA_TRY(cudaHostUnregister(p));
+    return STAGE_OK;
+}
 extern "C" void *stage_gpu_host_alloc(size_t bytes) {
     void *p = nullptr;
     if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) return nullptr;

@@ -1,0 +1,183 @@
+"""Host-buffer (STAGE_IO_HOST) paths of the batch calls: pinned outputs are written by the kernels directly
+("zero copy"), pageable outputs go through double-buffered HBM scratch + DMA copies. Both must return what the CPU
+checker returns; concurrent callers share one snapshot like the reference's pinned worker threads share one BTree
+(/root/reference/benchmark/ycsb/ycsb_workload.cpp:522-529)."""
+import threading
+
+import numpy as np
+import pytest
+
+import stage_indexorganized_b200 as sg
+from helpers import assert_probe_equal, assert_scan_equal, random_table, u32_keys, ycsb_int_table
+from oracle import pyoracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _checker():
+    return pyoracle.RefTable if pyoracle.have_ref() else pyoracle.OracleTable
+
+
+@pytest.fixture(scope="module")
+def mvcc_table():
+    """20 k YCSB rows, 3 k committed updates (chains), a few deletes: leaves with unsorted suffixes from the loader."""
+    t = ycsb_int_table(_checker(), 20000)
+    uk = u32_keys(pyoracle.uniform_keys(20000, 3000, seed=2) - 1)
+    assert t.commit_update_batch(uk, 10) == 3000
+    for k in (17, 4242, 19999):
+        t.delete(u32_keys(np.array([k], np.uint32))[0])
+    snap = sg.Snapshot.from_tree(t.root, 4, 1000)
+    yield t, snap
+    snap.close()
+
+
+def _pinned_scan(snap, sk, sizes, stride, read_ts, vis, want_payload=True):
+    n, K, P = sk.shape[0], snap.schema.key_size, snap.schema.payload_size
+    hk = sg.PinnedArray((max(n, 1), K), np.uint8)
+    hk.array[:n] = sk
+    sz = np.ascontiguousarray(np.broadcast_to(np.asarray(sizes, np.uint32), (n,)))
+    counts = sg.PinnedArray((max(n, 1),), np.uint32)
+    keys = sg.PinnedArray((max(n, 1), stride, K), np.uint8)
+    ts = sg.PinnedArray((max(n, 1), stride), np.uint32)
+    pay = sg.PinnedArray((max(n, 1), stride, P), np.uint8) if want_payload else None
+    for a in (counts, keys, ts, pay):
+        if a is not None:
+            a.array[...] = 0
+    sg._check(sg.lib().stage_gpu_scan_batch(snap.h, hk.ptr, sz.ctypes.data, n, stride, read_ts, vis, counts.ptr, keys.ptr,
+                                            ts.ptr, pay.ptr if pay else None, sg.IO_HOST))
+    out = (counts.array[:n].copy(), keys.array[:n].copy(), ts.array[:n].copy(), pay.array[:n].copy() if pay else None)
+    for a in (hk, counts, keys, ts, pay):
+        if a is not None:
+            a.free()
+    return out
+
+
+def _pinned_probe(snap, keys, read_ts):
+    n, K, P = keys.shape[0], snap.schema.key_size, snap.schema.payload_size
+    hk = sg.PinnedArray((max(n, 1), K), np.uint8)
+    hk.array[:n] = keys
+    found = sg.PinnedArray((max(n, 1),), np.uint8)
+    ts = sg.PinnedArray((max(n, 1),), np.uint32)
+    ko = sg.PinnedArray((max(n, 1), K), np.uint8)
+    pay = sg.PinnedArray((max(n, 1), P), np.uint8)
+    for a in (found, ts, ko, pay):
+        a.array[...] = 0
+    sg._check(sg.lib().stage_gpu_probe_batch(snap.h, hk.ptr, n, read_ts, found.ptr, ts.ptr, ko.ptr, pay.ptr, sg.IO_HOST))
+    out = (found.array[:n].copy(), ts.array[:n].copy(), ko.array[:n].copy(), pay.array[:n].copy())
+    for a in (hk, found, ts, ko, pay):
+        a.free()
+    return out
+
+
+@pytest.mark.parametrize("vis", [0, 1])
+@pytest.mark.parametrize("scan_size", [10, 100, 1000])
+def test_scan_pinned_outputs_match_checker(mvcc_table, scan_size, vis):
+    t, snap = mvcc_table
+    sk = u32_keys(pyoracle.uniform_keys(20000, 96, seed=5) - 1)
+    for read_ts in (0, 1500, 5000):
+        want = t.scan(sk, scan_size, read_ts, vis)
+        assert_scan_equal(_pinned_scan(snap, sk, scan_size, scan_size, read_ts, vis), want, f"pinned S={scan_size} ts={read_ts}")
+        assert_scan_equal(snap.scan(sk, scan_size, read_ts, vis), want, f"pageable S={scan_size} ts={read_ts}")
+
+
+def test_scan_staged_chunking_many_scans(mvcc_table):
+    """More result bytes than one staging chunk (128 MiB): several chunks, both buffers reused, per-scan copies."""
+    t, snap = mvcc_table
+    sk = u32_keys(pyoracle.uniform_keys(20000, 400, seed=9) - 1)
+    sizes = np.where(np.arange(400) % 7 == 0, 3, 1000).astype(np.uint32)          # ragged: short scans between long ones
+    want = t.scan(sk, sizes, 2000, 1)
+    assert_scan_equal(snap.scan(sk, sizes, 2000, 1), want, "pageable, 400 scans")
+    assert_scan_equal(_pinned_scan(snap, sk, sizes, 1000, 2000, 1), want, "pinned, 400 scans")
+
+
+def test_probe_pinned_and_pageable_match_checker(mvcc_table):
+    t, snap = mvcc_table
+    keys = u32_keys(np.concatenate([pyoracle.uniform_keys(20000, 150000, seed=4), np.array([17, 4242, 70000], np.uint32)]))
+    for read_ts in (0, 9, 1500, 0xFFFFFFFF):
+        want = t.probe(keys, read_ts)
+        assert_probe_equal(_pinned_probe(snap, keys, read_ts), want, f"pinned ts={read_ts}")
+        assert_probe_equal(snap.probe(keys, read_ts), want, f"pageable ts={read_ts}")     # > 1 staging chunk (64 Ki probes)
+
+
+def test_registered_caller_memory_is_written_in_place(mvcc_table):
+    """stage_gpu_host_register: a caller-owned array becomes a zero-copy target."""
+    t, snap = mvcc_table
+    sk = u32_keys(np.array([5, 9000, 15000], np.uint32))
+    n, S = 3, 50
+    arena = np.zeros(1 << 20, np.uint8)          # one caller-owned allocation, registered once, carved into the outputs
+    counts = arena[0:4 * n].view(np.uint32)
+    ts = arena[4096:4096 + 4 * n * S].view(np.uint32).reshape(n, S)
+    keys = arena[8192:8192 + 4 * n * S].reshape(n, S, 4)
+    pay = arena[16384:16384 + n * S * 1000].reshape(n, S, 1000)
+    sizes = np.full(n, S, np.uint32)
+    sg._check(sg.lib().stage_gpu_host_register(arena.ctypes.data, arena.nbytes))
+    try:
+        sg._check(sg.lib().stage_gpu_scan_batch(snap.h, sk.ctypes.data, sizes.ctypes.data, n, S, 3000, 1, counts.ctypes.data,
+                                                keys.ctypes.data, ts.ctypes.data, pay.ctypes.data, sg.IO_HOST))
+    finally:
+        sg._check(sg.lib().stage_gpu_host_unregister(arena.ctypes.data))
+    assert_scan_equal((counts, keys, ts, pay), t.scan(sk, S, 3000, 1), "registered")
+
+
+def test_concurrent_callers_share_one_snapshot(mvcc_table):
+    """8 threads, each its own batches of probes and scans on the same handle (contexts instead of a global lock)."""
+    t, snap = mvcc_table
+    errors = []
+
+    def worker(w):
+        try:
+            rng = np.random.default_rng(100 + w)
+            for it in range(4):
+                keys = u32_keys(rng.integers(0, 20100, 5000).astype(np.uint32))
+                assert_probe_equal(snap.probe(keys, 2000 + w), t.probe(keys, 2000 + w), f"thread {w} probe {it}")
+                sk = u32_keys(rng.integers(0, 20000, 24).astype(np.uint32))
+                S = int(rng.choice([7, 200, 1000]))
+                assert_scan_equal(_pinned_scan(snap, sk, S, S, 1000 * w, 1), t.scan(sk, S, 1000 * w, 1), f"thread {w} scan {it}")
+        except Exception as e:      # noqa: BLE001
+            errors.append(repr(e))
+
+    th = [threading.Thread(target=worker, args=(w,)) for w in range(8)]
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    assert not errors, errors[:3]
+
+
+def test_slot_order_counter_counts_quirk_scans():
+    """The counter sees the scans whose last leaf is truncated in slot order; a consolidated table has none."""
+    cls = _checker()
+    t, keys, _ = random_table(cls, 3000, 8, 96, seed=3)
+    snap = sg.Snapshot.from_tree(t.root, 8, 96)
+    snap.counters(reset=True)
+    rng = np.random.default_rng(1)
+    sk = keys[rng.integers(0, keys.shape[0], 512)]
+    assert_scan_equal(snap.scan(sk, 10, 0, 0), t.scan(sk, 10, 0, 0), "tiny rows")
+    q = snap.counters().slot_order_scans
+    assert q > 0                                   # random insertion order: most leaves are not slot-ordered
+    snap.close()
+    g = sg.Snapshot.generate_ycsb(5000, 1000)
+    g.scan(u32_keys(np.arange(100, dtype=np.uint32)), 10, 0, 0)
+    assert g.counters().slot_order_scans == 0
+    g.close()
+
+
+def test_scan_size_above_stride_is_clamped_on_device_and_rejected_on_host(mvcc_table):
+    import torch
+    t, snap = mvcc_table
+    sk = u32_keys(np.array([100, 200], np.uint32))
+    with pytest.raises(sg.StageError):
+        snap.scan(sk, np.array([30, 10], np.uint32), 0, 0, out_stride=20)
+    dev = torch.device("cuda", 0)
+    d_sk = torch.from_numpy(sk).to(dev)
+    d_sz = torch.tensor([30, 10], dtype=torch.int32, device=dev)
+    counts = torch.zeros(2, dtype=torch.int32, device=dev)
+    kout = torch.full((3, 20, 4), 0xEE, dtype=torch.uint8, device=dev)       # one guard scan behind the two real ones
+    tso = torch.zeros((3, 20), dtype=torch.int32, device=dev)
+    pay = torch.full((3, 20, 1000), 0xEE, dtype=torch.uint8, device=dev)
+    snap.scan_device(d_sk, d_sz, 2, 20, 0, 0, counts, kout, tso, pay)
+    torch.cuda.synchronize()
+    assert counts.tolist() == [20, 10]
+    want = t.scan(sk, np.array([20, 10], np.uint32), 0, 0)
+    assert np.array_equal(pay[:2].cpu().numpy()[0], want[3][0])
+    assert int((pay[2] != 0xEE).sum()) == 0 and int((kout[1, 10:] != 0xEE).sum()) == 0    # nothing written past a slab

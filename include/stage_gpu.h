@@ -87,12 +87,13 @@ typedef struct stage_snapshot_info {
 /* flags for *_batch */
 enum {
     STAGE_IO_HOST = 0,   /* all in/out pointers are host memory (pinned or pageable) */
-    STAGE_IO_DEVICE = 1  /* all in/out pointers are device memory on the snapshot's GPU */
+    STAGE_IO_DEVICE = 1, /* all in/out pointers are device memory on the snapshot's GPU */
+    STAGE_IO_COMPACT = 2 /* stage_gpu_scan_batch with host buffers: pack the result rows (see there) */
 };
-/* STAGE_IO_HOST results cross PCIe in one of two ways. When every output buffer is pinned (stage_gpu_host_alloc or
- * stage_gpu_host_register) the kernels store keys, commit ids and payload rows straight into it: one pass, only the
- * rows that exist, no result slab in HBM. Otherwise results are staged in double-buffered HBM scratch and copied
- * out by the DMA engine while the next chunk is planned and gathered. STAGE_HOST_PATH=staged|zerocopy forces one. */
+/* STAGE_IO_HOST results are produced into double-buffered HBM scratch and copied out by the DMA engine (one large
+ * copy per output array and chunk) while the next chunk is planned and gathered; pinned buffers (stage_gpu_host_alloc,
+ * stage_gpu_host_register) make those copies run at link speed. STAGE_HOST_PATH=zerocopy lets the kernels store into
+ * pinned outputs directly instead (lower latency for small batches, lower bandwidth for large ones). */
 
 /* ---- lifecycle --------------------------------------------------------------------------- */
 
@@ -235,7 +236,9 @@ int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint64_t n, uin
  * [i*out_stride, i*out_stride + row_counts[i]) of key_out / ts_out / payload_out
  * (out_stride >= max scan size: STAGE_ERR_ARG otherwise with host buffers; with device buffers, where the sizes are
  * not visible to the host, a larger size is clamped to out_stride). Row slots beyond row_counts[i] are either left
- * untouched or zero-filled. Reproduces the iterator's slot-order truncation and
+ * untouched or zero-filled. With STAGE_IO_COMPACT (host buffers only) the rows of all scans are packed back to back
+ * instead: scan i occupies row slots [sum of row_counts[0..i), + row_counts[i]) — exactly the rows that exist cross
+ * PCIe; the buffers must still hold n * out_stride rows in the worst case. Reproduces the iterator's slot-order truncation and
  * leaf-hop termination rules exactly. apply_visibility = 1 is the executor's
  * range rule: a row is returned iff read_ts >= the commit id of its in-leaf version; a newer row is
  * dropped — the range branch never reaches a version chain, because the iterator's records carry no

@@ -19,7 +19,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libstage_gpu.so")
 
-IO_HOST, IO_DEVICE = 0, 1
+IO_HOST, IO_DEVICE, IO_COMPACT = 0, 1, 2
 XCHG_DEVICE_SYNC = 1
 IPC_HANDLE_BYTES = 64
 KEY_AUTO, KEY_SIGNED_BYTES, KEY_MEMCMP = 0, 1, 2
@@ -366,6 +366,25 @@ class Snapshot:
         _check(lib().stage_gpu_probe_batch(self.h, _ptr(keys), n, read_ts, _ptr(found), _ptr(ts), _ptr(key_out),
                                            _ptr(pay), IO_HOST))
         return found, ts, key_out, pay
+
+    def scan_compact(self, start_keys, scan_sizes, read_ts, apply_visibility, want_payload=True):
+        """The same scans with STAGE_IO_COMPACT: rows of all scans packed back to back. Returns (row_counts u32[n],
+        keys u8[R,K], ts u32[R], payload u8[R,P]) with R = row_counts.sum(); scan i owns rows
+        [row_counts[:i].sum(), +row_counts[i])."""
+        start_keys = np.ascontiguousarray(start_keys, np.uint8)
+        n = start_keys.shape[0]
+        K, P = self.schema.key_size, self.schema.payload_size
+        scan_sizes = np.ascontiguousarray(np.broadcast_to(np.asarray(scan_sizes, np.uint32), (n,)))
+        stride = int(scan_sizes.max()) if n else 0
+        counts = np.zeros(n, np.uint32)
+        key_out = np.zeros((n * stride, K), np.uint8)
+        ts = np.zeros(n * stride, np.uint32)
+        pay = np.zeros((n * stride, P), np.uint8) if want_payload else None
+        _check(lib().stage_gpu_scan_batch(self.h, _ptr(start_keys), _ptr(scan_sizes), n, stride, read_ts,
+                                          int(apply_visibility), _ptr(counts), _ptr(key_out), _ptr(ts), _ptr(pay),
+                                          IO_HOST | IO_COMPACT))
+        r = int(counts.sum())
+        return counts, key_out[:r], ts[:r], (pay[:r] if pay is not None else None)
 
     def scan(self, start_keys, scan_sizes, read_ts, apply_visibility, want_payload=True, out_stride=None):
         """Batched RangeScanBySize + executor loop. Returns (row_counts u32[n], key_out u8[n,S,K],

@@ -28,17 +28,30 @@ struct GatherArgs {
     const uint8_t *ver_payload;  // staged version rows
     uint8_t *dst;                // [n_slots][P]
     uint32_t payload_size;
+    // compact destination (STAGE_IO_COMPACT): slot o = scan o / out_stride, position o % out_stride goes to row
+    // dst_base[scan] + position instead of row o; nullptr = dense slab
+    const uint32_t *dst_base;
+    uint32_t out_stride;
 };
+
+__device__ __forceinline__ uint64_t gather_dst_row(const GatherArgs &a, uint64_t slot) {
+    if (!a.dst_base) return slot;
+    const uint64_t scan = slot / a.out_stride;
+    return (uint64_t) __ldg(a.dst_base + scan) + (slot - scan * a.out_stride);
+}
 
 template <typename V, int U>
 __global__ void __launch_bounds__(kGatherThreads) gather_rows_kernel(GatherArgs a) {
     __shared__ uint32_t s_row[kGatherRows];
+    __shared__ uint64_t s_dst[kGatherRows];
     const uint64_t slot0 = (uint64_t) blockIdx.x * kGatherRows;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = kGatherThreads / 32;
     if (tid < kGatherRows) {
         const uint64_t o = slot0 + tid;
-        s_row[tid] = o < a.n_slots ? __ldg(a.src_row + o) : kNoRow;
+        const uint32_t r = o < a.n_slots ? __ldg(a.src_row + o) : kNoRow;
+        s_row[tid] = r;
+        s_dst[tid] = r == kNoRow ? 0 : gather_dst_row(a, o);
     }
     __syncthreads();
     const uint32_t P = a.payload_size;
@@ -53,7 +66,7 @@ __global__ void __launch_bounds__(kGatherThreads) gather_rows_kernel(GatherArgs 
             const uint8_t *base = (row & kVersionRowFlag) ? a.ver_payload : a.payload;
             src[u] = row == kNoRow ? nullptr
                                    : reinterpret_cast<const V *>(base + (uint64_t) (row & ~kVersionRowFlag) * P);
-            dst[u] = reinterpret_cast<V *>(a.dst + (slot0 + r0 + u) * P);
+            dst[u] = reinterpret_cast<V *>(a.dst + s_dst[r0 + u] * P);
         }
         // 4 x U loads per lane are issued before the first store (K = 4 covers a 1000-byte row at 8 B/lane)
         constexpr int K = 4;
@@ -168,34 +181,63 @@ constexpr uint32_t kMidRowMax = 512;         // rows of 272..512 bytes, 16-byte 
 template <int kMidVecs>
 __global__ void __launch_bounds__(kGatherThreads) gather_rows_mid_kernel(GatherArgs a) {
     __shared__ uint32_t s_row[kGatherRows];
+    __shared__ uint64_t s_dst[kGatherRows];
     const uint64_t slot0 = (uint64_t) blockIdx.x * kGatherRows;
     const int tid = threadIdx.x;
     if (tid < kGatherRows) {
         const uint64_t o = slot0 + tid;
-        s_row[tid] = o < a.n_slots ? __ldg(a.src_row + o) : kNoRow;
+        const uint32_t r = o < a.n_slots ? __ldg(a.src_row + o) : kNoRow;
+        s_row[tid] = r;
+        s_dst[tid] = r == kNoRow ? 0 : gather_dst_row(a, o);
     }
     __syncthreads();
     const uint32_t P = a.payload_size, vpr = P / 16;          // vectors per row
     const uint32_t total = kGatherRows * vpr;                 // vectors of this CTA's 64 output rows
-    uint4 *dst = reinterpret_cast<uint4 *>(a.dst + slot0 * P);
     for (uint32_t v0 = tid; v0 < total; v0 += kGatherThreads * kMidVecs) {
         uint4 val[kMidVecs];
-        bool ok[kMidVecs];
+        uint4 *dst[kMidVecs];
 #pragma unroll
         for (int j = 0; j < kMidVecs; ++j) {
             const uint32_t v = v0 + j * kGatherThreads;
-            ok[j] = false;
+            dst[j] = nullptr;
             if (v >= total) continue;
             const uint32_t r = v / vpr, k = v - r * vpr;
             const uint32_t row = s_row[r];
             if (row == kNoRow) continue;
             const uint8_t *base = (row & kVersionRowFlag) ? a.ver_payload : a.payload;
             val[j] = __ldcs(reinterpret_cast<const uint4 *>(base + (uint64_t) (row & ~kVersionRowFlag) * P) + k);
-            ok[j] = true;
+            dst[j] = reinterpret_cast<uint4 *>(a.dst + s_dst[r] * P) + k;
         }
 #pragma unroll
         for (int j = 0; j < kMidVecs; ++j)
-            if (ok[j]) __stcs(dst + v0 + j * kGatherThreads, val[j]);
+            if (dst[j]) __stcs(dst[j], val[j]);
+    }
+}
+
+}  // namespace stage
+
+// ---- compact layout of keys / commit ids (STAGE_IO_COMPACT) -------------------------------------------------------
+// The plan kernels write a scan's keys and commit ids at [scan * out_stride + position]; this moves them to
+// [dst_base[scan] + position], next to each other, so that one DMA copy per array returns exactly the rows that exist.
+namespace stage {
+
+__global__ void __launch_bounds__(256) compact_keys_ts_kernel(const uint32_t *__restrict__ row_counts, const uint32_t *__restrict__ dst_base,
+                                                              uint64_t n_slots, uint32_t out_stride, uint32_t key_size,
+                                                              const uint8_t *key_in, uint8_t *key_out, const uint32_t *ts_in,
+                                                              uint32_t *ts_out) {
+    const uint64_t o = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (o >= n_slots) return;
+    const uint64_t scan = o / out_stride;
+    const uint32_t pos = (uint32_t) (o - scan * out_stride);
+    if (pos >= __ldg(row_counts + scan)) return;
+    const uint64_t d = (uint64_t) __ldg(dst_base + scan) + pos;
+    if (ts_out) ts_out[d] = ts_in[o];
+    if (key_out) {
+        if ((key_size & 3u) == 0)
+            for (uint32_t b = 0; b < key_size; b += 4)
+                *reinterpret_cast<uint32_t *>(key_out + d * key_size + b) = *reinterpret_cast<const uint32_t *>(key_in + o * key_size + b);
+        else
+            for (uint32_t b = 0; b < key_size; ++b) key_out[d * key_size + b] = key_in[o * key_size + b];
     }
 }
 
@@ -213,11 +255,11 @@ template <typename I>
 __global__ void __launch_bounds__(256) gather_rows_small_kernel(GatherArgs a, uint32_t words_per_row, uint64_t n_words) {
     const I base_w = (I) blockIdx.x * (I) (256 * kSmallWordsPerThread) + (I) threadIdx.x;
     uint32_t val[kSmallWordsPerThread];
-    bool ok[kSmallWordsPerThread];
+    uint32_t *dst[kSmallWordsPerThread];
 #pragma unroll
     for (int j = 0; j < kSmallWordsPerThread; ++j) {
         const I w = base_w + (I) (j * 256);
-        ok[j] = false;
+        dst[j] = nullptr;
         if ((uint64_t) w >= n_words) continue;
         const I slot = w / (I) words_per_row;
         const uint32_t row = __ldg(a.src_row + slot);
@@ -225,11 +267,11 @@ __global__ void __launch_bounds__(256) gather_rows_small_kernel(GatherArgs a, ui
         const uint32_t k = (uint32_t) (w - slot * (I) words_per_row);
         const uint8_t *base = (row & kVersionRowFlag) ? a.ver_payload : a.payload;
         val[j] = __ldg(reinterpret_cast<const uint32_t *>(base + (uint64_t) (row & ~kVersionRowFlag) * a.payload_size) + k);
-        ok[j] = true;
+        dst[j] = reinterpret_cast<uint32_t *>(a.dst) + (a.dst_base ? gather_dst_row(a, (uint64_t) slot) * words_per_row + k : (uint64_t) w);
     }
 #pragma unroll
     for (int j = 0; j < kSmallWordsPerThread; ++j)
-        if (ok[j]) reinterpret_cast<uint32_t *>(a.dst)[(uint64_t) base_w + (uint64_t) (j * 256)] = val[j];
+        if (dst[j]) *dst[j] = val[j];
 }
 
 }  // namespace stage

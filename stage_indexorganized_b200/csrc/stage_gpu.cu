@@ -33,6 +33,7 @@
 #include "probe_fused.cuh"
 #include "refresh.cuh"
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 using namespace stage;
 
@@ -107,11 +108,13 @@ struct HostCtx {
     cudaEvent_t drained[2] = {nullptr, nullptr};    // chunk copied out (on cp)
     DevBuf keys, sizes, srcrow;
     DevBuf counts[2], found[2], ts[2], keyout[2], payload[2];
+    DevBuf kstr, tstr, off, cubtmp;                 // compact mode: strided keys / commit ids of the plan, row offsets, scan temp
     uint32_t *h_counts = nullptr;                   // pinned: row counts of the chunk in flight (per-scan copies)
     size_t h_counts_cap = 0;
     bool busy = false;
     void release_all() {
         keys.release(); sizes.release(); srcrow.release();
+        kstr.release(); tstr.release(); off.release(); cubtmp.release();
         for (int i = 0; i < 2; ++i) {
             counts[i].release(); found[i].release(); ts[i].release(); keyout[i].release(); payload[i].release();
             if (done[i]) cudaEventDestroy(done[i]);
@@ -1574,7 +1577,8 @@ static int launch_gather_v(cudaStream_t st, const GatherArgs &g) {
 
 // payload rows named by src_row[0..n_slots) -> dst[n_slots][P]. dst may be device memory or the device alias of
 // pinned host memory (the gather then streams the rows straight across PCIe).
-static int launch_gather(stage_snapshot *s, cudaStream_t st, const uint32_t *src_row, uint64_t n_slots, uint8_t *dst) {
+static int launch_gather(stage_snapshot *s, cudaStream_t st, const uint32_t *src_row, uint64_t n_slots, uint8_t *dst,
+                         const uint32_t *dst_base = nullptr, uint32_t out_stride = 1) {
     if (n_slots == 0 || !dst) return STAGE_OK;
     if ((n_slots + kGatherRows - 1) / kGatherRows > 0x7FFFFFFFull) return STAGE_ERR_ARG;
     GatherArgs g{};
@@ -1584,6 +1588,8 @@ static int launch_gather(stage_snapshot *s, cudaStream_t st, const uint32_t *src
     g.ver_payload = s->d_ver_payload;
     g.dst = dst;
     g.payload_size = s->schema.payload_size;
+    g.dst_base = dst_base;
+    g.out_stride = std::max<uint32_t>(out_stride, 1);
     const uintptr_t align = (uintptr_t) g.payload | (uintptr_t) g.ver_payload | (uintptr_t) dst | g.payload_size;
     if (g.payload_size <= 256 && (align & 3) == 0) {          // short rows: one thread per 32-bit word
         const uint32_t wpr = g.payload_size / 4;
@@ -1775,12 +1781,12 @@ static void *mapped_alias(const void *p) {
     return at.type == cudaMemoryTypeHost ? at.devicePointer : nullptr;
 }
 
-// How STAGE_IO_HOST results cross PCIe. "zerocopy": the kernels store keys, commit ids and payload rows straight into
-// the caller's pinned buffers (one pass, only the rows that exist, no result slab in HBM); needs pinned outputs
-// (stage_gpu_host_alloc / stage_gpu_host_register). "staged": results are produced into double-buffered HBM scratch
-// and copied out by the DMA engine while the next chunk is planned and gathered; works with any host memory.
-// STAGE_HOST_PATH=staged|zerocopy forces one; the default picks zero copy whenever every output is pinned
-// (profiles/r2_pcie_ceiling.txt has the measurements behind that choice).
+// How STAGE_IO_HOST results cross PCIe. Default ("staged"): results are produced into double-buffered HBM scratch and
+// leave through the DMA engine as one large copy per output array and chunk, while the next chunk is planned and
+// gathered; works with any host memory, fastest with pinned memory. STAGE_HOST_PATH=zerocopy: the kernels store keys,
+// commit ids and payload rows straight into pinned caller buffers (one pass, no slab) — lowest latency for small batches,
+// but on this pool SM stores into mapped host memory reach 44-53 GB/s against 57.3 GB/s for the DMA engine
+// (profiles/r2_pcie_ceiling.txt), so it is opt-in.
 enum { kHostAuto = 0, kHostStaged = 1, kHostZeroCopy = 2 };
 static int host_path_mode() {
     static const int m = [] {
@@ -1882,17 +1888,14 @@ extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint
     int rc = STAGE_OK;
     CtxGuard g{s, ctx_acquire(s, &rc)};
     if (!g.c) return rc;
-    const int mode = host_path_mode();
-    if (mode != kHostStaged) {
+    if (host_path_mode() == kHostZeroCopy) {
         uint8_t *df = static_cast<uint8_t *>(mapped_alias(found)), *dk = static_cast<uint8_t *>(mapped_alias(key_out)),
                 *dp = static_cast<uint8_t *>(mapped_alias(payload_out));
         uint32_t *dt = static_cast<uint32_t *>(mapped_alias(ts));
         if ((!found || df) && (!ts || dt) && (!key_out || dk) && (!payload_out || dp))
             return probe_host_zerocopy(s, g.c, keys, n, read_ts, df, dt, dk, dp);
-        if (mode == kHostZeroCopy) {
-            g_last_error = "STAGE_HOST_PATH=zerocopy needs pinned output buffers (stage_gpu_host_alloc / stage_gpu_host_register)";
-            return STAGE_ERR_ARG;
-        }
+        g_last_error = "STAGE_HOST_PATH=zerocopy needs pinned output buffers (stage_gpu_host_alloc / stage_gpu_host_register)";
+        return STAGE_ERR_ARG;
     }
     return probe_host_staged(s, g.c, keys, n, read_ts, found, ts, key_out, payload_out);
 }
@@ -1926,9 +1929,9 @@ static int launch_scan_nw(stage_snapshot *s, const ScanArgs &a, cudaStream_t st)
     }
 }
 
-// plan (scan_plan_kernel) then payload gather; all pointers are device-visible
-static int scan_device(stage_snapshot *s, const Lane &ln, ScanArgs a, uint8_t *payload_out) {
-    if (a.n == 0) return STAGE_OK;
+// plan (scan_plan_kernel) then payload gather; all pointers are device-visible. dst_base (compact layout): row offset of
+// every scan in payload_out, computed by the caller between the two launches (scan_plan_launch / scan_gather_launch).
+static int scan_plan_launch(stage_snapshot *s, const Lane &ln, ScanArgs &a) {
     const uint64_t slots = a.n * (uint64_t) a.out_stride;
     int rc;
     if ((rc = ln.srcrow->ensure(std::max<uint64_t>(slots, 1) * 4))) return rc;
@@ -1937,12 +1940,22 @@ static int scan_device(stage_snapshot *s, const Lane &ln, ScanArgs a, uint8_t *p
     if (ln.timing) CUDA_TRY(cudaEventRecord(s->tev[0], ln.st));
     if ((rc = launch_scan_nw(s, a, ln.st))) return rc;
     if (ln.timing) CUDA_TRY(cudaEventRecord(s->tev[1], ln.st));
-    rc = launch_gather(s, ln.st, a.src_row, slots, payload_out);
+    return STAGE_OK;
+}
+static int scan_gather_launch(stage_snapshot *s, const Lane &ln, const ScanArgs &a, uint8_t *payload_out,
+                              const uint32_t *dst_base = nullptr) {
+    const int rc = launch_gather(s, ln.st, a.src_row, a.n * (uint64_t) a.out_stride, payload_out, dst_base, a.out_stride);
     if (ln.timing) {
         CUDA_TRY(cudaEventRecord(s->tev[2], ln.st));
         s->timed_gather = payload_out != nullptr;
     }
     return rc;
+}
+static int scan_device(stage_snapshot *s, const Lane &ln, ScanArgs a, uint8_t *payload_out) {
+    if (a.n == 0) return STAGE_OK;
+    int rc;
+    if ((rc = scan_plan_launch(s, ln, a))) return rc;
+    return scan_gather_launch(s, ln, a, payload_out);
 }
 
 static int scan_host_zerocopy(stage_snapshot *s, HostCtx *c, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
@@ -1974,15 +1987,21 @@ static int scan_host_zerocopy(stage_snapshot *s, HostCtx *c, const void *start_k
     return STAGE_OK;
 }
 
+// Results through HBM scratch and the DMA engine, two chunks in flight: chunk i is copied out on the copy stream while
+// chunk i+1 is planned and gathered on the kernel stream. Measured on this pool (profiles/r2_pcie_ceiling.txt): one
+// large cudaMemcpyAsync reaches 57.3 GB/s of the Gen5 x16 link, one copy per scan 46 GB/s, kernel stores into mapped
+// pinned memory 44-53 GB/s — so every chunk leaves as ONE copy per output array. compact = STAGE_IO_COMPACT: the rows
+// of all scans are packed back to back on the device first, so the copies carry exactly the rows that exist.
 static int scan_host_staged(stage_snapshot *s, HostCtx *c, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
                             uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts, void *key_out,
-                            uint32_t *ts_out, void *payload_out) {
+                            uint32_t *ts_out, void *payload_out, bool compact) {
     const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
     const uint64_t slot_bytes = (uint64_t) P + K + 4;
-    // ~128 MiB of result slots per chunk, two chunks in flight (kernel stream / copy stream)
-    const uint64_t chunk = std::min<uint64_t>(n, std::max<uint64_t>(1, (128ull << 20) / std::max<uint64_t>(1, slot_bytes * out_stride)));
-    // long scans: only the rows a scan returned cross PCIe (one copy per run of scans); short scans: the whole chunk
-    const bool per_scan = payload_out && (uint64_t) out_stride * P >= (64u << 10);
+    // ~128 MiB of result slots per chunk; fewer for small batches so that the first copy starts early
+    uint64_t chunk = std::max<uint64_t>(1, (128ull << 20) / std::max<uint64_t>(1, slot_bytes * out_stride));
+    if (n < 4 * chunk) chunk = std::max<uint64_t>(1, (n + 3) / 4);
+    chunk = std::min<uint64_t>(chunk, n);
+    if (chunk * out_stride >= 0xFFFFFFFFull) return STAGE_ERR_ARG;
     int rc;
     if ((rc = c->keys.ensure(n * K)) || (rc = c->sizes.ensure(n * 4))) return rc;
     for (int i = 0; i < 2; ++i) {
@@ -1990,6 +2009,14 @@ static int scan_host_staged(stage_snapshot *s, HostCtx *c, const void *start_key
         if (key_out && (rc = c->keyout[i].ensure(chunk * out_stride * K))) return rc;
         if (ts_out && (rc = c->ts[i].ensure(chunk * out_stride * 4))) return rc;
         if (payload_out && (rc = c->payload[i].ensure(chunk * out_stride * (uint64_t) P))) return rc;
+    }
+    size_t cub_bytes = 0;
+    if (compact) {
+        if (key_out && (rc = c->kstr.ensure(chunk * out_stride * K))) return rc;
+        if (ts_out && (rc = c->tstr.ensure(chunk * out_stride * 4))) return rc;
+        if ((rc = c->off.ensure(chunk * 4))) return rc;
+        CUDA_TRY(cub::DeviceScan::ExclusiveSum(nullptr, cub_bytes, (const uint32_t *) nullptr, (uint32_t *) nullptr, (int) chunk, c->st));
+        if ((rc = c->cubtmp.ensure(cub_bytes))) return rc;
     }
     if (c->h_counts_cap < 2 * chunk) {
         if (c->h_counts) cudaFreeHost(c->h_counts);
@@ -2001,15 +2028,19 @@ static int scan_host_staged(stage_snapshot *s, HostCtx *c, const void *start_key
     CUDA_TRY(cudaMemcpyAsync(c->keys.p, start_keys, n * K, cudaMemcpyHostToDevice, c->st));
     CUDA_TRY(cudaMemcpyAsync(c->sizes.p, scan_sizes, n * 4, cudaMemcpyHostToDevice, c->st));
     const Lane ln{c->st, &c->srcrow, false};
-    uint64_t i = 0;
+    uint64_t i = 0, row_base = 0;                 // row_base: rows already returned (compact layout)
     for (uint64_t b = 0; b < n; b += chunk, ++i) {
         const int buf = (int) (i & 1);
-        const uint64_t m = std::min(chunk, n - b), rows = m * out_stride, rb = b * out_stride;
+        const uint64_t m = std::min(chunk, n - b), slots = m * out_stride;
         if (i >= 2) CUDA_TRY(cudaStreamWaitEvent(c->st, c->drained[buf], 0));
-        // slots beyond a scan's row count come back zero-filled (keys / commit ids always; payload in whole-chunk mode)
-        if (key_out) CUDA_TRY(cudaMemsetAsync(c->keyout[buf].p, 0, rows * K, c->st));
-        if (ts_out) CUDA_TRY(cudaMemsetAsync(c->ts[buf].p, 0, rows * 4, c->st));
-        if (payload_out && !per_scan) CUDA_TRY(cudaMemsetAsync(c->payload[buf].p, 0, rows * (uint64_t) P, c->st));
+        uint8_t *d_key = key_out ? static_cast<uint8_t *>(c->keyout[buf].p) : nullptr;
+        uint32_t *d_ts = ts_out ? static_cast<uint32_t *>(c->ts[buf].p) : nullptr;
+        uint8_t *d_pay = payload_out ? static_cast<uint8_t *>(c->payload[buf].p) : nullptr;
+        if (!compact) {        // slots beyond a scan's row count come back zero-filled
+            if (d_key) CUDA_TRY(cudaMemsetAsync(d_key, 0, slots * K, c->st));
+            if (d_ts) CUDA_TRY(cudaMemsetAsync(d_ts, 0, slots * 4, c->st));
+            if (d_pay) CUDA_TRY(cudaMemsetAsync(d_pay, 0, slots * (uint64_t) P, c->st));
+        }
         ScanArgs a{};
         a.out_stride = out_stride;
         a.read_ts = read_ts;
@@ -2018,35 +2049,44 @@ static int scan_host_staged(stage_snapshot *s, HostCtx *c, const void *start_key
         a.start_keys = static_cast<const uint8_t *>(c->keys.p) + b * K;
         a.scan_sizes = static_cast<const uint32_t *>(c->sizes.p) + b;
         a.row_counts = static_cast<uint32_t *>(c->counts[buf].p);
-        a.key_out = key_out ? static_cast<uint8_t *>(c->keyout[buf].p) : nullptr;
-        a.ts_out = ts_out ? static_cast<uint32_t *>(c->ts[buf].p) : nullptr;
-        uint8_t *d_pay = payload_out ? static_cast<uint8_t *>(c->payload[buf].p) : nullptr;
-        if ((rc = scan_device(s, ln, a, d_pay))) return rc;
+        a.key_out = compact ? (key_out ? static_cast<uint8_t *>(c->kstr.p) : nullptr) : d_key;
+        a.ts_out = compact ? (ts_out ? static_cast<uint32_t *>(c->tstr.p) : nullptr) : d_ts;
+        if ((rc = scan_plan_launch(s, ln, a))) return rc;
         uint32_t *hc = c->h_counts + (size_t) buf * chunk;
-        CUDA_TRY(cudaMemcpyAsync(hc, c->counts[buf].p, m * 4, cudaMemcpyDeviceToHost, c->st));
+        CUDA_TRY(cudaMemcpyAsync(hc, a.row_counts, m * 4, cudaMemcpyDeviceToHost, c->st));
+        if (compact) {
+            uint32_t *d_off = static_cast<uint32_t *>(c->off.p);
+            size_t tb = c->cubtmp.cap;
+            CUDA_TRY(cub::DeviceScan::ExclusiveSum(c->cubtmp.p, tb, a.row_counts, d_off, (int) m, c->st));
+            g_launches.fetch_add(1, std::memory_order_relaxed);
+            if ((rc = scan_gather_launch(s, ln, a, d_pay, d_off))) return rc;
+            if (d_key || d_ts) {
+                compact_keys_ts_kernel<<<(unsigned) ((slots + 255) / 256), 256, 0, c->st>>>(a.row_counts, d_off, slots, out_stride, K,
+                                                                                           a.key_out, d_key, a.ts_out, d_ts);
+                LAUNCH_CHECK();
+            }
+        } else if ((rc = scan_gather_launch(s, ln, a, d_pay))) {
+            return rc;
+        }
         CUDA_TRY(cudaEventRecord(c->done[buf], c->st));
-        // the row counts are needed on the host to size the copies; the copy stream is still busy with chunk i-1
+        // the row counts size the copies of the compact layout; the copy stream is still busy with chunk i-1 meanwhile
         CUDA_TRY(cudaEventSynchronize(c->done[buf]));
         memcpy(row_counts + b, hc, m * 4);
+        uint64_t rows = slots, dst_row = b * out_stride;
+        if (compact) {
+            rows = 0;
+            for (uint64_t j = 0; j < m; ++j) rows += hc[j];
+            dst_row = row_base;
+            row_base += rows;
+        }
         CUDA_TRY(cudaStreamWaitEvent(c->cp, c->done[buf], 0));
-        if (key_out)
-            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(key_out) + rb * K, c->keyout[buf].p, rows * K, cudaMemcpyDeviceToHost, c->cp));
-        if (ts_out) CUDA_TRY(cudaMemcpyAsync(ts_out + rb, c->ts[buf].p, rows * 4, cudaMemcpyDeviceToHost, c->cp));
-        if (payload_out && !per_scan)
-            CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(payload_out) + rb * (uint64_t) P, d_pay, rows * (uint64_t) P,
-                                     cudaMemcpyDeviceToHost, c->cp));
-        if (per_scan) {
-            uint8_t *hp = static_cast<uint8_t *>(payload_out) + rb * (uint64_t) P;
-            for (uint64_t j = 0; j < m;) {
-                // a run of full scans and the scan that ends it are contiguous in both buffers: one copy
-                uint64_t e = j;
-                while (e + 1 < m && hc[e] == out_stride) ++e;
-                const uint64_t bytes = ((e - j) * (uint64_t) out_stride + hc[e]) * P;
-                if (bytes)
-                    CUDA_TRY(cudaMemcpyAsync(hp + j * (uint64_t) out_stride * P, d_pay + j * (uint64_t) out_stride * P, bytes,
-                                             cudaMemcpyDeviceToHost, c->cp));
-                j = e + 1;
-            }
+        if (rows) {
+            if (key_out)
+                CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(key_out) + dst_row * K, d_key, rows * K, cudaMemcpyDeviceToHost, c->cp));
+            if (ts_out) CUDA_TRY(cudaMemcpyAsync(ts_out + dst_row, d_ts, rows * 4, cudaMemcpyDeviceToHost, c->cp));
+            if (payload_out)
+                CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(payload_out) + dst_row * (uint64_t) P, d_pay, rows * (uint64_t) P,
+                                         cudaMemcpyDeviceToHost, c->cp));
         }
         CUDA_TRY(cudaEventRecord(c->drained[buf], c->cp));
     }
@@ -2061,6 +2101,7 @@ extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys,
     if (!s->sealed) return STAGE_ERR_STATE;
     CUDA_TRY(cudaSetDevice(s->device));
     if (flags & STAGE_IO_DEVICE) {
+        if (flags & STAGE_IO_COMPACT) return STAGE_ERR_ARG;      // the compact layout is a host-buffer (PCIe) feature
         std::lock_guard<std::mutex> lock(s->mu);        // one enqueue at a time on the snapshot stream (shared scratch)
         ScanArgs a{};
         a.out_stride = out_stride;
@@ -2080,19 +2121,17 @@ extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys,
     int rc = STAGE_OK;
     CtxGuard g{s, ctx_acquire(s, &rc)};
     if (!g.c) return rc;
-    const int mode = host_path_mode();
-    if (mode != kHostStaged) {
+    const bool compact = (flags & STAGE_IO_COMPACT) != 0;
+    if (host_path_mode() == kHostZeroCopy && !compact) {
         uint32_t *dc = static_cast<uint32_t *>(mapped_alias(row_counts)), *dt = static_cast<uint32_t *>(mapped_alias(ts_out));
         uint8_t *dk = static_cast<uint8_t *>(mapped_alias(key_out)), *dp = static_cast<uint8_t *>(mapped_alias(payload_out));
         if (dc && (!ts_out || dt) && (!key_out || dk) && (!payload_out || dp))
             return scan_host_zerocopy(s, g.c, start_keys, scan_sizes, n, out_stride, read_ts, apply_visibility, dc, dk, dt, dp);
-        if (mode == kHostZeroCopy) {
-            g_last_error = "STAGE_HOST_PATH=zerocopy needs pinned output buffers (stage_gpu_host_alloc / stage_gpu_host_register)";
-            return STAGE_ERR_ARG;
-        }
+        g_last_error = "STAGE_HOST_PATH=zerocopy needs pinned output buffers (stage_gpu_host_alloc / stage_gpu_host_register)";
+        return STAGE_ERR_ARG;
     }
     return scan_host_staged(s, g.c, start_keys, scan_sizes, n, out_stride, read_ts, apply_visibility, row_counts, key_out, ts_out,
-                            payload_out);
+                            payload_out, compact);
 }
 
 // ------------------------------------------------------------------------------------------------

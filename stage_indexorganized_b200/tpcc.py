@@ -6,7 +6,10 @@ Key and tuple shapes follow the reference's benchmark/tpcc/tpcc_record.h:
   OrderLine  key {int64 OL_W_ID, OL_D_ID, OL_O_ID, OL_NUMBER} (32 B, :694-714), payload 60 B
              [OL_I_ID i32][OL_SUPPLY_W_ID i32][OL_DELIVERY_D i64][OL_QUANTITY i32][OL_AMOUNT 8 B][OL_DIST_INFO 32 B]
 Field values follow BuildStockTuple / BuildOrderLineTuple (benchmark/tpcc/tpcc_loader.cpp:1281-1374) with a
-seeded numpy generator in place of the loader's un-seeded rand() (SURVEY.md §8d, config 4 input).
+seeded numpy generator in place of the loader's un-seeded rand() (SURVEY.md §8d, config 4 input): the loader's
+"random strings" are ONE random alphanumeric character repeated (GetRandomAlphaNumericString, tpcc_loader.cpp:849-860),
+S_DIST_xx = 31 of them + NUL (name_length = 31, strncpy into char[32]), S_DATA = 64, OL_DIST_INFO = 32.
+tests/test_tpcc_rows.py holds these rows to the bytes the reference's own builders produce (oracle/_ref).
 Both keys are >= 16 bytes, so the reference orders them with memcmp over the raw little-endian bytes
 (include/vstore/b_tree.h:116-134) — NOT numerically; the table order is whatever that gives.
 """
@@ -15,7 +18,9 @@ import numpy as np
 STOCK_KEY, STOCK_PAYLOAD = 16, 400
 OL_KEY, OL_PAYLOAD = 32, 60
 ITEMS, DISTRICTS, ORDERS = 100_000, 10, 3000
-_ALNUM = np.frombuffer(b"0123456789ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz", np.uint8)
+# GetRandomAlphaNumericString draws an index in [0, sizeof(alphanumeric) - 1], i.e. the terminating NUL included
+# (tpcc_loader.cpp:850-857): 1 string in 63 is all zero bytes
+_ALNUM = np.frombuffer(b"0123456789ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz\x00", np.uint8)
 
 
 def stock_key(w, i):
@@ -38,11 +43,11 @@ def stock_rows(warehouses, items=ITEMS, seed=1):
     n = len(w)
     pay = np.zeros((n, STOCK_PAYLOAD), np.uint8)
     pay[:, 0:4] = rng.integers(10, 101, n).astype(np.int32).view(np.uint8).reshape(n, 4)      # S_QUANTITY 10..100
-    dist = _ALNUM[rng.integers(0, len(_ALNUM), size=(n, 32))]
+    dist = np.repeat(_ALNUM[rng.integers(0, len(_ALNUM), size=n)][:, None], 32, axis=1)         # one character, 31 times
     dist[:, 31] = 0
     for c in range(10):                                                                        # the same string ten times
         pay[:, 16 + 32 * c: 48 + 32 * c] = dist
-    pay[:, 336:400] = _ALNUM[rng.integers(0, len(_ALNUM), size=(n, 64))]
+    pay[:, 336:400] = _ALNUM[rng.integers(0, len(_ALNUM), size=n)][:, None]                     # S_DATA: one character x 64
     return stock_key(w, i), pay
 
 
@@ -65,7 +70,7 @@ def order_line_rows(warehouses, districts=DISTRICTS, orders=ORDERS, seed=2):
     pay[:, 8:16] = (1_600_000_000 + oid).view(np.uint8).reshape(total, 8)
     pay[:, 16:20] = np.full(total, 5, np.int32).view(np.uint8).reshape(total, 4)
     pay[:, 20:28] = np.frombuffer(b"0.000000", np.uint8)
-    pay[:, 28:60] = _ALNUM[rng.integers(0, len(_ALNUM), size=(total, 32))]
+    pay[:, 28:60] = _ALNUM[rng.integers(0, len(_ALNUM), size=total)][:, None]                   # OL_DIST_INFO: one character x 32
     return order_line_key(w, d, o, number), pay, item
 
 

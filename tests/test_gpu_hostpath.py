@@ -1,7 +1,11 @@
-"""Host-buffer (STAGE_IO_HOST) paths of the batch calls: pinned outputs are written by the kernels directly
-("zero copy"), pageable outputs go through double-buffered HBM scratch + DMA copies. Both must return what the CPU
-checker returns; concurrent callers share one snapshot like the reference's pinned worker threads share one BTree
+"""Host-buffer (STAGE_IO_HOST) paths of the batch calls: results go through double-buffered HBM scratch + DMA copies
+(default; strided or STAGE_IO_COMPACT layout) or — STAGE_HOST_PATH=zerocopy, re-run in a child process — are stored by
+the kernels straight into pinned outputs. All must return what the CPU checker returns; concurrent callers share one
+snapshot like the reference's pinned worker threads share one BTree
 (/root/reference/benchmark/ycsb/ycsb_workload.cpp:522-529)."""
+import os
+import subprocess
+import sys
 import threading
 
 import numpy as np
@@ -12,6 +16,7 @@ from helpers import assert_probe_equal, assert_scan_equal, random_table, u32_key
 from oracle import pyoracle
 
 pytestmark = pytest.mark.gpu
+ZEROCOPY = os.environ.get("STAGE_HOST_PATH") == "zerocopy"      # forced zero copy refuses pageable outputs
 
 
 def _checker():
@@ -77,17 +82,67 @@ def test_scan_pinned_outputs_match_checker(mvcc_table, scan_size, vis):
     for read_ts in (0, 1500, 5000):
         want = t.scan(sk, scan_size, read_ts, vis)
         assert_scan_equal(_pinned_scan(snap, sk, scan_size, scan_size, read_ts, vis), want, f"pinned S={scan_size} ts={read_ts}")
-        assert_scan_equal(snap.scan(sk, scan_size, read_ts, vis), want, f"pageable S={scan_size} ts={read_ts}")
+        if not ZEROCOPY:
+            assert_scan_equal(snap.scan(sk, scan_size, read_ts, vis), want, f"pageable S={scan_size} ts={read_ts}")
+
+
+def _expand_compact(got, stride):
+    """compact result -> the strided arrays the checker returns"""
+    counts, keys, ts, pay = got
+    n = counts.shape[0]
+    K, P = keys.shape[1], pay.shape[1]
+    ko, to, po = np.zeros((n, stride, K), np.uint8), np.zeros((n, stride), np.uint32), np.zeros((n, stride, P), np.uint8)
+    off = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    for i in range(n):
+        c = int(counts[i])
+        ko[i, :c], to[i, :c], po[i, :c] = keys[off[i]:off[i] + c], ts[off[i]:off[i] + c], pay[off[i]:off[i] + c]
+    return counts, ko, to, po
+
+
+@pytest.mark.parametrize("scan_size", [10, 1000])
+def test_scan_compact_layout_matches_checker(mvcc_table, scan_size):
+    """STAGE_IO_COMPACT: rows packed back to back (exactly the rows that exist cross PCIe), several chunks."""
+    t, snap = mvcc_table
+    n = 300 if scan_size == 1000 else 5000
+    sk = u32_keys(pyoracle.uniform_keys(20000, n, seed=11) - 1)
+    sizes = np.where(np.arange(n) % 5 == 0, max(scan_size // 3, 1), scan_size).astype(np.uint32)
+    for read_ts, vis in ((0, 1), (1500, 1), (0, 0)):
+        want = t.scan(sk, sizes, read_ts, vis)
+        got = snap.scan_compact(sk, sizes, read_ts, vis)
+        assert got[1].shape[0] == int(want[0].sum())
+        assert_scan_equal(_expand_compact(got, scan_size), want, f"compact S={scan_size} ts={read_ts} vis={vis}")
+
+
+def test_compact_with_empty_scans_and_table_end():
+    g = sg.Snapshot.generate_ycsb(3000, 1000)
+    from stage_indexorganized_b200.ycsb import rank_to_key
+    sk = u32_keys(np.concatenate([rank_to_key(3000, np.array([2990, 2999, 0, 1500])), np.array([0x7F7F7F7F], np.uint32)]))
+    counts, keys, ts, pay = g.scan_compact(sk, np.array([50, 50, 0, 7, 9], np.uint32), 0, 0)
+    assert counts.tolist() == [10, 1, 0, 7, 0] and pay.shape == (18, 1000)
+    c2, k2, _, p2 = g.scan(sk, np.array([50, 50, 0, 7, 9], np.uint32), 0, 0)
+    assert np.array_equal(c2, counts) and np.array_equal(pay[:10], p2[0, :10]) and np.array_equal(pay[11:18], p2[3, :7])
+    assert np.array_equal(keys[10], k2[1, 0])
+    g.close()
+
+
+def test_zero_copy_variant_in_child_process():
+    """The same file with STAGE_HOST_PATH=zerocopy: kernels store into the pinned outputs directly."""
+    if os.environ.get("STAGE_VARIANT_RUN"):
+        pytest.skip("already inside a variant run")
+    env = dict(os.environ, STAGE_HOST_PATH="zerocopy", STAGE_VARIANT_RUN="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-m", "gpu", "-k", "pinned or registered"],
+                       env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
 
 
 def test_scan_staged_chunking_many_scans(mvcc_table):
-    """More result bytes than one staging chunk (128 MiB): several chunks, both buffers reused, per-scan copies."""
+    """More result bytes than one staging chunk (128 MiB): several chunks, both buffers reused."""
     t, snap = mvcc_table
     sk = u32_keys(pyoracle.uniform_keys(20000, 400, seed=9) - 1)
     sizes = np.where(np.arange(400) % 7 == 0, 3, 1000).astype(np.uint32)          # ragged: short scans between long ones
     want = t.scan(sk, sizes, 2000, 1)
     assert_scan_equal(snap.scan(sk, sizes, 2000, 1), want, "pageable, 400 scans")
-    assert_scan_equal(_pinned_scan(snap, sk, sizes, 1000, 2000, 1), want, "pinned, 400 scans")
+    assert_scan_equal(_pinned_scan(snap, sk, sizes, 1000, 2000, 1), want, "pinned outputs, 400 scans")
 
 
 def test_probe_pinned_and_pageable_match_checker(mvcc_table):
@@ -96,7 +151,8 @@ def test_probe_pinned_and_pageable_match_checker(mvcc_table):
     for read_ts in (0, 9, 1500, 0xFFFFFFFF):
         want = t.probe(keys, read_ts)
         assert_probe_equal(_pinned_probe(snap, keys, read_ts), want, f"pinned ts={read_ts}")
-        assert_probe_equal(snap.probe(keys, read_ts), want, f"pageable ts={read_ts}")     # > 1 staging chunk (64 Ki probes)
+        if not ZEROCOPY:
+            assert_probe_equal(snap.probe(keys, read_ts), want, f"pageable ts={read_ts}")     # > 1 staging chunk (64 Ki probes)
 
 
 def test_registered_caller_memory_is_written_in_place(mvcc_table):

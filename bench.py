@@ -75,6 +75,8 @@ def parse_args():
     ap.add_argument("--e2e-scans", type=int, default=1024)
     ap.add_argument("--cpu-scans", type=int, default=0, help="scans in the CPU-baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-workloads", action="store_true",
+                    help="N = 1: skip the compact entries for BASELINE configs[0], [2], [3] (\"workloads\" in the line)")
     ap.add_argument("--workload", default="scan", choices=["scan", "config1", "string", "tpcc"],
                     help="'scan' = BASELINE configs[1] (the headline, default); 'string' = configs[2] (100 M string keys, zipf "
                          "0.9 probes); 'tpcc' = configs[3] (w=30 stock-level / Q2 read pattern). The extra workloads are "
@@ -182,6 +184,10 @@ def scan_start_keys(rows, n, seed):
 
 
 FIRST_CID = 10
+# what the CPU arm runs (oracle/ref_harness.cpp ref_time_scan): stated in every cpu_baseline.sample
+CPU_ARM_NOTE = ("MVCC scans through the reference's unmodified IndexScanExecutor (range branch, rows copied out in its "
+                "predicate), unfiltered scans through BTree::RangeScanBySize/GetNext; built -O2 -DNDEBUG with glibc "
+                "malloc (the reference links tcmalloc, which is not in this image)")
 
 
 def update_keys(rows, updates):
@@ -230,7 +236,8 @@ def run_reference(args, rank, world):
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": workload_config(args, world=1, table="reference loader (host tree)"),
         "cpu_baseline": {"value": value, "unit": "rows/s", "cores": threads, "kind": kind,
-                         "sample": f"{n} scans x {args.scan_size} rows per step, {args.steps} steps, {threads} pinned threads"},
+                         "sample": f"{n} scans x {args.scan_size} rows per step, {args.steps} steps, {threads} pinned threads; "
+                                   + CPU_ARM_NOTE},
         "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -263,142 +270,264 @@ def _time_steps(torch, fn, warmup, steps):
 
 
 def run_extra_workload(args):
-    """Single-GPU legs for the other BASELINE configs (device-resident inputs and outputs, CUDA-event timed)."""
+    """`--workload config1|string|tpcc`: one of the other BASELINE configs alone (the default run carries all three as
+    compact entries under "workloads")."""
     import torch
     import stage_indexorganized_b200 as sg
-    from stage_indexorganized_b200 import tpcc, ycsb
+    import bench_workloads as bw
     torch.cuda.set_device(0)
     dev = torch.device("cuda", 0)
     sg.init(0)
     peak, peak_src = peaks()
-    nb = args.warmup + args.steps
-    if args.workload == "config1":
-        # BASELINE configs[0]: ./ycsb -k 10000 -b 4 -o 10 -u 0 -z 0.2 — read-only point probes, int keys, 10 000 rows.
-        # (The reference's own CLI aborts at HEAD with an out-of-range key pick, SURVEY.md §3.5, so the CPU side is the
-        # reference's BTree::Read driven by the harness over the same key stream, at 4 threads like -b 4 and at all.)
-        n_rows, n = 10_000, args.probes
-        snap = sg.Snapshot.generate_ycsb(n_rows, P_BYTES)
-        snap.set_stream(torch.cuda.current_stream().cuda_stream)
-        z = ycsb.Zipf(n_rows - 1, 0.2, seed=1).draw(n * nb).astype(np.uint32).reshape(nb, n)
-        d_keys = torch.from_numpy(z.view(np.int32)).to(dev)
-        found = torch.zeros((n,), dtype=torch.uint8, device=dev)
-        ts = torch.zeros((n,), dtype=torch.int32, device=dev)
-        kout = torch.empty((n,), dtype=torch.int32, device=dev)
-        pay = torch.empty((n, P_BYTES), dtype=torch.uint8, device=dev)
-        ms = _time_steps(torch, lambda b: snap.probe_device(d_keys[b], n, 1, found, ts, kout, pay), args.warmup, args.steps)
-        hits = int(found.sum().item())
-        algo = hits * PROBE_HIT_BYTES + (n - hits) * PROBE_MISS_BYTES
-        cpu = None
-        if not args.no_cpu_baseline:
-            from oracle import pyoracle
-            pyoracle.build_oracle()
-            t = pyoracle.RefTable(P_BYTES) if pyoracle.have_ref() else pyoracle.OracleTable(P_BYTES)
-            assert t.load_ycsb_int(0, n_rows) == n_rows
-            keys = np.ascontiguousarray(z.reshape(-1)[: 1 << 22]).view(np.uint8).reshape(-1, 4)
-            ok = all(np.array_equal(g, w) for g, w in zip(snap.probe(keys[:65536], 1), t.probe(keys[:65536], 1)))
-            cpu = {"kind": "reference" if pyoracle.have_ref() else "port", "unit": "probes/s", "parity_sample_ok": bool(ok)}
-            for th in (4, os.cpu_count() or 1):
-                sec, h = t.time_probe(keys, 1, th, pin=True)
-                cpu[f"threads_{th}"] = len(keys) / sec
-        line = {"metric": "YCSB read-only point probes/s (10k-tuple int table, zipf 0.2)", "value": n / (ms * 1e-3),
-                "unit": "probes/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "dtype": "u8",
-                "data": "synthetic", "config": {"workload": "BASELINE configs[0]: ./ycsb -k 10000 -b 4 -o 10 -u 0 -z 0.2",
-                                                "probes_per_step": n, "hit_rate": hits / n,
-                                                "note": "the 10 MB table lives in L2: the bound here is L2/SM throughput, not HBM"},
-                "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                             "frac": algo / (ms * 1e-3) / 1e9 / peak, "peak_source": peak_src},
-                "cpu_baseline": cpu}
-        print(json.dumps(line), flush=True)
-        snap.close()
-        return
-    if args.workload == "string":
-        n_rows, n = 100_000_000, args.probes
-        snap, keys, _ = ycsb.build_string_table_device(n_rows)
-        snap.set_stream(torch.cuda.current_stream().cuda_stream)
-        z = np.clip(ycsb.Zipf(n_rows - 1, 0.9, seed=1).draw(n * nb).astype(np.int64), 1, n_rows) - 1
-        d_keys = keys[torch.from_numpy(z).to(dev)].reshape(nb, n, 16).contiguous()
-        found = torch.zeros((n,), dtype=torch.uint8, device=dev)
-        ts = torch.zeros((n,), dtype=torch.int32, device=dev)
-        kout = torch.empty((n, 16), dtype=torch.uint8, device=dev)
-        pay = torch.empty((n, P_BYTES), dtype=torch.uint8, device=dev)
-        ms = _time_steps(torch, lambda b: snap.probe_device(d_keys[b], n, 1, found, ts, kout, pay), args.warmup, args.steps)
-        hits = int(found.sum().item())
-        algo = hits * (16 + 2 * (16 + P_BYTES + 4)) + (n - hits) * 17
-        line = {"metric": "YCSB string-key zipf-0.9 probes/s (100M-tuple table)", "value": n / (ms * 1e-3), "unit": "probes/s",
-                "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "dtype": "u8", "data": "synthetic",
-                "config": {"workload": "BASELINE configs[2]: YCSB string-key (-m) zipf 0.9 batched probes, 100000000 tuples, "
-                                       "built on device (FastRandom(1804289383) keys, bulk load)", "probes_per_step": n,
-                           "distinct_keys_per_step": int(np.unique(z[:n]).size), "hit_rate": hits / n},
-                "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                             "frac": algo / (ms * 1e-3) / 1e9 / peak, "peak_source": peak_src,
-                             "note": "whole step (search + rows); zipf 0.9 repeats hot rows, so part of the row traffic is L2 hits"}}
-        print(json.dumps(line), flush=True)
-        snap.close()
-        return
-    # ---- tpcc: stock-level order_line scans + stock probes, Q2-shaped probe batches with S_QUANTITY push-down ------
-    W = 30
-    sk, sp = tpcc.stock_rows(W)
-    ok_, op, _ = tpcc.order_line_rows(W)
-
-    def bulk(keys, pays, K, P):
-        order = np.lexsort(keys.T[::-1])                      # memcmp order of the raw key bytes (keys >= 16 B)
-        snap, raw, pay, _ = sg.Snapshot.alloc_sorted(len(keys), K, P, rows_per_leaf=max(8, min(500, 60000 // (K + P + 24))))
-        raw.copy_(torch.from_numpy(keys[order]))
-        pay.copy_(torch.from_numpy(pays[order]))
-        snap.seal_sorted()
-        snap.set_stream(torch.cuda.current_stream().cuda_stream)
-        return snap
-    stock, ol = bulk(sk, sp, tpcc.STOCK_KEY, tpcc.STOCK_PAYLOAD), bulk(ok_, op, tpcc.OL_KEY, tpcc.OL_PAYLOAD)
-    txns = 50_000                                             # 1 M order_line scans of 10 rows per step
-    starts = [torch.from_numpy(tpcc.stock_level_requests(W, txns, seed=10 + b)[0]).to(dev) for b in range(nb)]
-    ns = txns * 20
-    sizes = torch.full((ns,), 10, dtype=torch.int32, device=dev)
-    counts = torch.zeros((ns,), dtype=torch.int32, device=dev)
-    kout = torch.empty((ns * 10, tpcc.OL_KEY), dtype=torch.uint8, device=dev)
-    tso = torch.empty((ns * 10,), dtype=torch.int32, device=dev)
-    pout = torch.empty((ns * 10, tpcc.OL_PAYLOAD), dtype=torch.uint8, device=dev)
-    ms_scan = _time_steps(torch, lambda b: ol.scan_device(starts[b], sizes, ns, 10, 1, 1, counts, kout, tso, pout),
-                          args.warmup, args.steps)
-    rows = int(counts.sum().item())
-    ol.enable_timing(True)
-    ol.scan_device(starts[0], sizes, ns, 10, 1, 1, counts, kout, tso, pout)
-    ol_plan_ms, ol_gather_ms = ol.last_timing()
-    ol.enable_timing(False)
-    rng = np.random.default_rng(3)
-    n = args.probes
-    pk = [torch.from_numpy(tpcc.stock_key(rng.integers(1, W + 1, n), rng.integers(1, tpcc.ITEMS + 1, n))).to(dev) for _ in range(nb)]
-    found = torch.zeros((n,), dtype=torch.uint8, device=dev)
-    spay = torch.empty((n, tpcc.STOCK_PAYLOAD), dtype=torch.uint8, device=dev)
-    qty = torch.empty((n, 4), dtype=torch.uint8, device=dev)
-    ms_full = _time_steps(torch, lambda b: stock.probe_device(pk[b], n, 1, found, None, None, spay), args.warmup, args.steps)
-    ms_col = _time_steps(torch, lambda b: stock.probe_column_device(pk[b], n, 1, 0, 4, qty, found), args.warmup, args.steps)
-    agg = [None]
-
-    def agg_step(b):
-        agg[0] = stock.probe_aggregate_i32(pk[b], 1, 0, 15, n=n)
-    ms_agg = _time_steps(torch, agg_step, args.warmup, args.steps)
-    ol_row, st_row = 2 * (tpcc.OL_KEY + tpcc.OL_PAYLOAD + 4), tpcc.STOCK_KEY + 2 * (tpcc.STOCK_KEY + tpcc.STOCK_PAYLOAD + 4)
-    line = {"metric": "TPC-C w=30 stock-level / Q2 read pattern", "value": rows / (ms_scan * 1e-3), "unit": "order_line rows/s",
-            "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_scan, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "BASELINE configs[3]: TPC-C w=30, stock 3 M rows (16/400), order_line "
-                                   f"{len(ok_)} rows (32/60), seeded row functions, bulk-loaded on device",
-                       "order_line_scans_per_step": ns, "scan_size": 10, "stock_probes_per_step": n},
-            "order_line_scan": {"rows_per_s": rows / (ms_scan * 1e-3), "scans_per_s": ns / (ms_scan * 1e-3), "ms_per_step": ms_scan,
-                                "plan_ms": ol_plan_ms, "gather_ms": ol_gather_ms,
-                                "achieved_GBps": rows * ol_row / (ms_scan * 1e-3) / 1e9, "frac_of_peak": rows * ol_row / (ms_scan * 1e-3) / 1e9 / peak},
-            "stock_probe_full_row": {"probes_per_s": n / (ms_full * 1e-3), "ms_per_step": ms_full,
-                                     "achieved_GBps": n * st_row / (ms_full * 1e-3) / 1e9, "frac_of_peak": n * st_row / (ms_full * 1e-3) / 1e9 / peak},
-            "stock_probe_quantity_pushdown": {"probes_per_s": n / (ms_col * 1e-3), "ms_per_step": ms_col,
-                                              "bytes_returned_per_probe": 5},
-            "stock_probe_quantity_aggregate": {"probes_per_s": n / (ms_agg * 1e-3), "ms_per_step": ms_agg,
-                                               "bytes_returned_per_batch": 24, "found": int(agg[0].found),
-                                               "below_threshold_15": int(agg[0].below), "min_quantity": int(agg[0].min_value),
-                                               "note": "count(S_QUANTITY < 15) and MIN(S_QUANTITY) reduced on the device; "
-                                                       "includes the 24-byte D2H read and its synchronisation per batch"},
-            "roofline": {"bound": "hbm", "peak": peak, "unit": "GB/s", "peak_source": peak_src}}
+    fn = {"config1": bw.config0, "string": bw.config2, "tpcc": bw.config3}[args.workload]
+    line = fn(args, sg, torch, dev, peak, cpu=not args.no_cpu_baseline)
+    line.update({"n_gpus": 1, "steps": min(args.steps, 10), "warmup": 3, "dtype": "u8", "data": "synthetic",
+                 "peak_source": peak_src})
     print(json.dumps(line), flush=True)
-    stock.close()
-    ol.close()
+
+
+def measure_pcie_d2h(torch, dev, mb=1024, reps=3):
+    """The link ceiling the e2e legs are held against, measured in this run the plain way: ONE cudaMemcpyAsync of
+    `mb` MiB from HBM into pinned host memory (torch copy_ non_blocking = one cudaMemcpyAsync), best of `reps`."""
+    d = torch.empty(mb << 20, dtype=torch.uint8, device=dev)
+    h = torch.empty(mb << 20, dtype=torch.uint8, pin_memory=True)
+    best = None
+    for _ in range(reps + 1):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        h.copy_(d, non_blocking=True)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        best = ms if best is None else min(best, ms)
+    del d, h
+    return (mb << 20) / (best * 1e-3) / 1e9
+
+
+def e2e_legs(args, sg, torch, dist, dev, snap, sk_all, pk_all, read_ts, vis, barrier, numa, world):
+    """The same scans / probes through the host-buffer C ABI calls a caller of the reference's interface would make:
+    pinned host keys in, pinned host rows out, every H2D / D2H copy inside the timed region (wall clock around the
+    calls, which return when the results are in host memory). Headline = scans with STAGE_IO_COMPACT (exactly the rows
+    that exist cross PCIe); the strided layout and the probe call are reported beside it."""
+    S = args.scan_size
+    n_batches = args.warmup + args.steps
+    ne = min(args.e2e_scans, args.scans)
+    h_sk = sg.PinnedArray((n_batches, ne, K_BYTES), np.uint8)
+    h_sk.array[:] = sk_all[:, :ne].astype(np.uint32).view(np.uint8).reshape(n_batches, ne, K_BYTES)
+    h_sizes = np.full(ne, S, np.uint32)
+    h_counts = sg.PinnedArray((ne,), np.uint32)
+    h_key = sg.PinnedArray((ne * S, K_BYTES), np.uint8)
+    h_ts = sg.PinnedArray((ne * S,), np.uint32)
+    h_pay = sg.PinnedArray((ne * S, P_BYTES), np.uint8)
+    pcie = measure_pcie_d2h(torch, dev)
+
+    def timed(step_fn):
+        for b in range(min(args.warmup, 2)):
+            step_fn(b)
+        barrier()
+        t0 = time.perf_counter()
+        units = 0
+        for i in range(args.steps):
+            units += step_fn(args.warmup + i)
+        torch.cuda.synchronize()
+        sec = time.perf_counter() - t0
+        t = torch.tensor([sec], dtype=torch.float64, device=dev)
+        u = torch.tensor([units], dtype=torch.float64, device=dev)
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(u, op=dist.ReduceOp.SUM)
+        return float(u.item()), float(t.item()), units, sec
+
+    def scan_step(flags):
+        def f(b):
+            sg._check(sg.lib().stage_gpu_scan_batch(snap.h, h_sk.array[b].ctypes.data, h_sizes.ctypes.data, ne, S, read_ts, vis,
+                                                    h_counts.ptr, h_key.ptr, h_ts.ptr, h_pay.ptr, flags))
+            return int(h_counts.array.sum())
+        return f
+
+    row_bytes = K_BYTES + 4 + P_BYTES
+    rows_c, sec_c, my_rows, my_sec = timed(scan_step(sg.IO_HOST | sg.IO_COMPACT))
+    rows_s, sec_s, _, my_sec_s = timed(scan_step(sg.IO_HOST))
+    d2h_compact = ne * 4 + my_rows / args.steps * row_bytes
+    e2e = {"value": rows_c / sec_c, "unit": "rows/s", "h2d_bytes_per_step": ne * (K_BYTES + 4),
+           "d2h_bytes_per_step": int(d2h_compact), "scans_per_step": ne, "rank0_seconds": my_sec,
+           "call": "stage_gpu_scan_batch(STAGE_IO_HOST | STAGE_IO_COMPACT), pinned buffers",
+           "numa_bind_rank0": numa,
+           "roofline": {"bound": "pcie", "peak": pcie, "unit": "GB/s",
+                        "peak_source": "measured in this run: one cudaMemcpyAsync D2H of 1 GiB into pinned memory, this rank alone",
+                        "achieved": d2h_compact * args.steps / my_sec / 1e9,
+                        "frac": d2h_compact * args.steps / my_sec / 1e9 / pcie},
+           "strided_layout": {"value": rows_s / sec_s, "unit": "rows/s",
+                              "d2h_bytes_per_step": ne * 4 + ne * S * row_bytes,
+                              "achieved_GBps_rank0": (ne * 4 + ne * S * row_bytes) * args.steps / my_sec_s / 1e9,
+                              "note": "rows of scan i at [i*out_stride, ...): the unused tail of every slab crosses PCIe too"}}
+    for a in (h_counts, h_key, h_ts, h_pay, h_sk):
+        a.free()
+    # probes: 2^18 keys per call (pinned), full rows back
+    npb = min(args.probes, 1 << 18)
+    h_pk = sg.PinnedArray((n_batches, npb, K_BYTES), np.uint8)
+    h_pk.array[:] = pk_all[:, :npb].astype(np.uint32).view(np.uint8).reshape(n_batches, npb, K_BYTES)
+    h_found = sg.PinnedArray((npb,), np.uint8)
+    h_pts = sg.PinnedArray((npb,), np.uint32)
+    h_pkey = sg.PinnedArray((npb, K_BYTES), np.uint8)
+    h_ppay = sg.PinnedArray((npb, P_BYTES), np.uint8)
+    p_ts = read_ts
+
+    def probe_step(b):
+        sg._check(sg.lib().stage_gpu_probe_batch(snap.h, h_pk.array[b].ctypes.data, npb, p_ts, h_found.ptr, h_pts.ptr,
+                                                 h_pkey.ptr, h_ppay.ptr, sg.IO_HOST))
+        return npb
+
+    pr, psec, _, my_psec = timed(probe_step)
+    pb = npb * (1 + 4 + K_BYTES + P_BYTES)
+    e2e["probe"] = {"value": pr / psec, "unit": "probes/s", "probes_per_step": npb, "h2d_bytes_per_step": npb * K_BYTES,
+                    "d2h_bytes_per_step": pb, "achieved_GBps_rank0": pb * args.steps / my_psec / 1e9,
+                    "frac_of_pcie": pb * args.steps / my_psec / 1e9 / pcie,
+                    "call": "stage_gpu_probe_batch(STAGE_IO_HOST), pinned buffers; at N > 1 keys of this rank's own shard range"}
+    for a in (h_pk, h_found, h_pts, h_pkey, h_ppay):
+        a.free()
+    return e2e
+
+
+def time_host_tree(args, torch, hsnap, stream, d_sk, d_sizes, d_counts, d_keyout, d_tsout, d_payout, d_pk, d_found, d_pts,
+                   d_pkey, d_ppay, read_ts, vis, peak):
+    """The timed scan and probe steps of the headline, run on the snapshot flattened from the tree the reference's own
+    loader built (same keys, same updates, same key streams, same device buffers)."""
+    n_scans, S, n_probes = args.scans, args.scan_size, args.probes
+    hsnap.set_stream(stream.cuda_stream)
+    hsnap.counters(reset=True)
+
+    def run(fn):
+        for b in range(args.warmup):
+            fn(b)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(args.steps):
+            fn(args.warmup + i)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1)
+
+    d_counts.zero_()
+    ms = run(lambda b: hsnap.scan_device(d_sk[b], d_sizes, n_scans, S, read_ts, vis, d_counts[b], d_keyout, d_tsout, d_payout))
+    quirk = int(hsnap.counters(reset=True).slot_order_scans)
+    rows = int(d_counts[args.warmup:].sum().item())
+    algo = rows * ROW_ALGO_BYTES + args.steps * n_scans * (K_BYTES + 8)
+    d_found.zero_()
+    pms = run(lambda b: hsnap.probe_device(d_pk[b], n_probes, read_ts, d_found[b], d_pts, d_pkey, d_ppay))
+    hits = int(d_found[args.warmup:].sum().item())
+    nprobe = args.steps * n_probes
+    pbytes = hits * PROBE_HIT_BYTES + (nprobe - hits) * PROBE_MISS_BYTES
+    info = hsnap.info()
+    return {"table": "tree built by the reference's loader (LoadYCSBRows order, single loader thread) + the same committed "
+                     "updates, flattened by stage_gpu_snapshot_from_tree", "leaves": int(info.n_leaves),
+            "value": rows / (ms * 1e-3), "unit": "rows/s", "ms_per_step": ms / args.steps,
+            "roofline": {"bound": "hbm", "step_achieved": algo / (ms * 1e-3) / 1e9, "peak": peak,
+                         "frac": algo / (ms * 1e-3) / 1e9 / peak, "unit": "GB/s"},
+            "quirk_scans": quirk, "scans_timed": (args.warmup + args.steps) * n_scans,
+            "quirk_note": "scans (warm-up included) whose last leaf was cut by the reference's slot-order early break "
+                          "(b_tree.cpp:1276-1309), counted on the device",
+            "probe": {"value": nprobe / (pms * 1e-3), "unit": "probes/s", "ms_per_step": pms / args.steps,
+                      "hit_rate": hits / nprobe, "step_frac": pbytes / (pms * 1e-3) / 1e9 / peak}}
+
+
+def scan_digest(torch, counts, keys, ts, pay):
+    """Order-sensitive 64-bit digest of every scan's emitted rows (keys, commit ids, payload bytes; int64 arithmetic
+    wraps): equal digests on two ranks <=> the same rows in the same order, up to a 2^-64 collision."""
+    n, R, P = pay.shape
+    K = keys.shape[2]
+    dev = pay.device
+    g = torch.Generator(device="cpu")
+    g.manual_seed(20261105)
+    wp = torch.randint(1, 1 << 31, (P,), generator=g, dtype=torch.int64).to(dev)
+    wk = torch.randint(1, 1 << 31, (K,), generator=g, dtype=torch.int64).to(dev)
+    wr = (torch.arange(R, dtype=torch.int64, device=dev) * 2654435761 + 1)
+    valid = torch.arange(R, device=dev)[None, :] < counts.to(torch.int64)[:, None]
+    out = torch.zeros(n, dtype=torch.int64, device=dev)
+    for c0 in range(0, n, 16):
+        sl = slice(c0, min(c0 + 16, n))
+        h = (pay[sl].to(torch.int64) * wp).sum(-1) + (keys[sl].to(torch.int64) * wk).sum(-1) + ts[sl].to(torch.int64) * 1000003
+        out[sl] = torch.where(valid[sl], h * wr[None, :], torch.zeros_like(h)).sum(-1)
+    return torch.stack([counts.to(torch.int64), out], 1)
+
+
+def multi_gpu_parity(args, sg, torch, dist, dev, snap, rank, world, rows, split, uk, pp, d_pk, ps, d_rk, d_rsz, read_ts):
+    """parity_check at N > 1 (evidence gap 1). Routed probes: >= 65 536 per rank, every result (found,
+    commit id, row image) against the closed-form row function + update model evaluated by the OWNER of the key (the only
+    rank that knows that shard's updates), exchanged with one all-reduce. Routed scans: 256 per rank, digest of the rows
+    delivered over NVLink against the digest of the same scan run shard-locally by the owner of its start key."""
+    from stage_indexorganized_b200.model import UpdateModel, expected_payload_bytes
+    total = rows * world
+    n_probes, S = args.probes, args.scan_size
+    NS = min(65536, n_probes)
+    found, ts, pay = pp.probe(d_pk[0], n_probes, read_ts)
+    torch.cuda.synchronize()
+    dist.barrier()
+    r = pay[:NS]
+    image_ok = ((r[:, 200:] == r[:, 999:1000]).all(1) & (r[:, 100:200] == r[:, 150:151]).all(1) & (r[:, :100] == r[:, 0:1]).all(1))
+    got = torch.stack([found[:NS].to(torch.int64), ts[:NS].to(torch.int64) & 0xFFFFFFFF, r[:, 0].to(torch.int64),
+                       r[:, 150].to(torch.int64), r[:, 999].to(torch.int64)], 1).cpu().numpy()
+    image_ok = image_ok.cpu().numpy()
+    my_keys = d_pk[0][:NS].contiguous().view(torch.int32).reshape(NS)
+    all_keys = [torch.empty_like(my_keys) for _ in range(world)]
+    dist.all_gather(all_keys, my_keys)
+    allk = torch.cat(all_keys).cpu().numpy().view(np.uint32)
+    owner = sg.route(np.ascontiguousarray(allk).view(np.uint8).reshape(-1, 4), split, K_BYTES)
+    mine = owner == rank
+    model = UpdateModel(uk)
+    km = allk[mine]
+    vis, stamp = model.visible(km, read_ts)
+    fnd = vis & (km < total)
+    b0, b150, b999 = expected_payload_bytes(km, stamp)
+    exp = np.zeros((world * NS, 5), np.int64)
+    exp[mine, 0] = fnd
+    exp[mine, 1] = np.where(fnd, stamp, 0)
+    exp[mine, 2], exp[mine, 3], exp[mine, 4] = np.where(fnd, b0, 0), np.where(fnd, b150, 0), np.where(fnd, b999, 0)
+    exp_t = torch.from_numpy(exp).to(dev)
+    dist.all_reduce(exp_t, op=dist.ReduceOp.SUM)              # exactly one owner contributes to every row
+    want = exp_t[rank * NS:(rank + 1) * NS].cpu().numpy()
+    hit = want[:, 0] == 1
+    probes_ok = bool(np.array_equal(got[:, 0], want[:, 0]) and np.array_equal(got[hit, 1:], want[hit, 1:]) and image_ok[hit].all())
+    # ---- routed scans vs the owner's shard-local scans ----------------------------------------------------
+    scans_ok, n_sc = True, 0
+    if ps is not None:
+        n_rs = d_rk.shape[1]
+        n_sc = min(256, n_rs)
+        counts, keys, tss, pays = ps.scan(d_rk[0], d_rsz, n_rs, read_ts)
+        torch.cuda.synchronize()
+        dist.barrier()
+        mine_d = scan_digest(torch, counts[:n_sc], keys[:n_sc], tss[:n_sc], pays[:n_sc])
+        my_sk = d_rk[0][:n_sc].contiguous().view(torch.int32).reshape(n_sc)
+        all_sk = [torch.empty_like(my_sk) for _ in range(world)]
+        dist.all_gather(all_sk, my_sk)
+        allsk = torch.cat(all_sk)
+        own = sg.route(np.ascontiguousarray(allsk.cpu().numpy().view(np.uint32)).view(np.uint8).reshape(-1, 4), split, K_BYTES) == rank
+        idx = torch.from_numpy(np.nonzero(own)[0]).to(dev)
+        exp_d = torch.zeros((world * n_sc, 2), dtype=torch.int64, device=dev)
+        for c0 in range(0, len(idx), 256):
+            ii = idx[c0:c0 + 256]
+            m = len(ii)
+            lk = allsk[ii].contiguous()
+            lsz = torch.full((m,), S, dtype=torch.int32, device=dev)
+            lc = torch.zeros((m,), dtype=torch.int32, device=dev)
+            lkeys = torch.zeros((m, S, K_BYTES), dtype=torch.uint8, device=dev)
+            lts = torch.zeros((m, S), dtype=torch.int32, device=dev)
+            lpay = torch.zeros((m, S, P_BYTES), dtype=torch.uint8, device=dev)
+            snap.scan_device(lk, lsz, m, S, read_ts, 1, lc, lkeys, lts, lpay)
+            torch.cuda.synchronize()
+            exp_d[ii] = scan_digest(torch, lc, lkeys, lts, lpay)
+            del lkeys, lts, lpay
+        dist.all_reduce(exp_d, op=dist.ReduceOp.SUM)
+        scans_ok = bool(torch.equal(exp_d[rank * n_sc:(rank + 1) * n_sc], mine_d))
+    verdict = torch.tensor([int(probes_ok), int(scans_ok)], dtype=torch.int32, device=dev)
+    dist.all_reduce(verdict, op=dist.ReduceOp.MIN)
+    ok_p, ok_s = bool(verdict[0].item()), bool(verdict[1].item())
+    return {"ok": ok_p and ok_s, "routed_probes_ok": ok_p, "routed_scans_ok": ok_s,
+            "checked": f"per rank: {NS} routed probes (found flag, commit id, row image) against the closed-form row function + "
+                       f"update model evaluated by the owning rank; {n_sc} routed {S}-row MVCC scans (digest of keys, commit ids, "
+                       "payload rows, order-sensitive) against the same scans run shard-locally by the owner of the start key; "
+                       "verdicts all-reduced (MIN) over the ranks"}
 
 
 def main():
@@ -637,11 +766,11 @@ def main():
             ams, _ = timed(a2a_step, args.a2a_steps)
             probe["nccl_all_to_all"] = {"value": args.a2a_steps * n_probes * world / (ams * 1e-3), "unit": "probes/s",
                                         "ms_per_step": ams / args.a2a_steps}
-        pp.close()
 
         # ---- routed scans: start keys anywhere in the global table, each scan planned on the owner of its start key
         # (shard + halo), rows stored into the requester's slab over NVLink peer memory -------------------------
         n_rs = args.routed_scans
+        ps, d_rk, d_rsz = None, None, None
         if n_rs > 0:
             rng2 = np.random.default_rng(3000 + rank)
             rk_all = rank_to_key(rows * world, rng2.integers(0, rows * world, size=(n_batches, n_rs)))
@@ -671,7 +800,25 @@ def main():
                             "phase_ms_rank0": dict(zip(("post", "plan_incl_wait_for_posts", "rows", "wait_for_owners"),
                                                        [float(np.mean(c)) for c in zip(*phases)]))}
             probe["routed_scans"] = routed_scans
+        # ---- the same number of probes with keys of the own shard (no exchange): the denominator of the routed leg ----
+        lk = rank_to_key(rows * world, rank * rows + np.random.default_rng(7000 + rank).integers(0, rows, size=(4, n_probes)))
+        d_lk = torch.from_numpy(lk.astype(np.uint32).view(np.int32)).to(dev)
+        d_lf = torch.zeros((n_probes,), dtype=torch.uint8, device=dev)
+        d_lt = torch.empty((n_probes,), dtype=torch.int32, device=dev)
+        lms, _ = timed(lambda b: (snap.probe_device(d_lk[b % 4], n_probes, read_ts, d_lf, d_lt, None, d_payout[: n_probes * P_BYTES]), d_lf)[1:],
+                       args.steps)
+        probe["shard_local"] = {"value": args.steps * n_probes * world / (lms * 1e-3), "unit": "probes/s",
+                                "ms_per_step": lms / args.steps, "note": "keys of the rank's own shard, no exchange"}
+        probe["routed_over_local"] = probe["value"] / probe["shard_local"]["value"]
+        del d_lk
+        # ---- bit-exactness of what crossed NVLink, on every rank (all-reduced verdict) --------------------
+        multi_parity = multi_gpu_parity(args, sg, torch, dist, dev, snap, rank, world, rows, split, uk, pp, d_pk, ps, d_rk,
+                                        d_rsz, read_ts)
+        if not multi_parity["ok"]:
+            raise SystemExit(f"parity_check failed at N = {world}: {multi_parity}")
+        if ps is not None:
             ps.close()
+        pp.close()
 
     # ---- max over ranks, whole-job aggregate ----------------------------------------------------
     t_ms = torch.tensor([total_ms], dtype=torch.float64, device=dev)
@@ -684,41 +831,17 @@ def main():
     value = rows_all / (total_ms_max * 1e-3)
 
     # ---- e2e: host buffers through the C ABI ----------------------------------------------------
-    ne = min(args.e2e_scans, n_scans)
-    h_sk = sg.PinnedArray((n_batches, ne, K_BYTES), np.uint8)
-    h_sk.array[:] = sk_all[:, :ne].astype(np.uint32).view(np.uint8).reshape(n_batches, ne, K_BYTES)
-    h_sizes = np.full(ne, S, np.uint32)
-    h_counts = sg.PinnedArray((ne,), np.uint32)
-    h_key = sg.PinnedArray((ne * S, K_BYTES), np.uint8)
-    h_ts = sg.PinnedArray((ne * S,), np.uint32)
-    h_pay = sg.PinnedArray((ne * S, P_BYTES), np.uint8)
-
-    def e2e_step(b):
-        sg._check(sg.lib().stage_gpu_scan_batch(snap.h, h_sk.array[b].ctypes.data, h_sizes.ctypes.data, ne, S, read_ts,
-                                                vis, h_counts.ptr, h_key.ptr, h_ts.ptr, h_pay.ptr, sg.IO_HOST))
-        return int(h_counts.array.sum())
-
-    for b in range(min(args.warmup, 2)):
-        e2e_step(b)
-    barrier()
-    t0 = time.perf_counter()
-    e_rows = 0
-    for i in range(args.steps):
-        e_rows += e2e_step(args.warmup + i)
-    torch.cuda.synchronize()
-    e_sec = time.perf_counter() - t0
-    e_t = torch.tensor([e_sec], dtype=torch.float64, device=dev)
-    e_r = torch.tensor([e_rows], dtype=torch.float64, device=dev)
-    if dist is not None:
-        dist.all_reduce(e_t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(e_r, op=dist.ReduceOp.SUM)
-    e2e = {"value": float(e_r.item()) / float(e_t.item()), "unit": "rows/s",
-           "h2d_bytes_per_step": ne * (K_BYTES + 4),
-           "d2h_bytes_per_step": ne * 4 + ne * S * (K_BYTES + 4 + P_BYTES),
-           "scans_per_step": ne, "rank0_seconds": e_sec, "numa_bind_rank0": numa}
+    if world > 1:       # probe keys of this rank's own shard (the e2e probe call is shard-local)
+        pk_e2e = rank_to_key(rows * world, rank * rows + np.random.default_rng(5000 + rank).integers(
+            0, rows, size=(n_batches, min(n_probes, 1 << 18))))
+    else:
+        pk_e2e = pk_all
+    e2e = e2e_legs(args, sg, torch, dist, dev, snap, sk_all, pk_e2e, read_ts, vis, barrier, numa, world)
 
     # ---- CPU baseline (rank 0, N = 1): the only part of the run that touches oracle/ ---------------------------
-    cpu, transform, parity = None, None, None
+    cpu, transform, parity, host_tree = None, None, None, None
+    if world > 1:
+        parity = multi_parity
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         if host_table is None:
             host_table, table_kind = build_host_table(rows, updates)     # reference loader + the same updates
@@ -728,7 +851,8 @@ def main():
         rps, r, sec = cpu_scan_sample(host_table, sk, S, read_ts, threads, vis)
         cpu = {"value": rps, "unit": "rows/s", "cores": threads, "kind": table_kind,
                "sample": f"{n_cpu} scans x {S} rows ({r} rows, {sec:.1f} s), {threads} pinned threads, "
-                         "table built by the reference loader with the same rows and the same committed updates"}
+                         "table built by the reference loader with the same rows and the same committed updates; "
+                         + CPU_ARM_NOTE}
         # with the reference-format tree at hand: time the record-layout transform on it and cross-check a sample
         t0 = time.time()
         hsnap = snap if use_host_tree else sg.Snapshot.from_tree(host_table.root, K_BYTES, P_BYTES)
@@ -738,6 +862,11 @@ def main():
             transform = {"leaves": int(hi.n_leaves), "rows": int(hi.n_rows), "seconds": t_tr,
                          "leaf_image_GB_per_s": hi.n_leaves * 65536 / t_tr / 1e9,
                          "note": "stage_gpu_snapshot_from_tree: host walk + pinned staging + H2D + leaf_transform_kernel"}
+        # the same timed steps on the flattened reference-built tree (leaves with unsorted suffixes: the iterator's
+        # slot-order rule is live there) — VERDICT r1 NS-1
+        if not use_host_tree:
+            host_tree = time_host_tree(args, torch, hsnap, stream, d_sk, d_sizes, d_counts, d_keyout, d_tsout, d_payout,
+                                       d_pk, d_found, d_pts, d_pkey, d_ppay, read_ts, vis, peaks()[0])
         ns = 256
         got = hsnap.scan(sk[:ns], S, read_ts, vis)
         want = host_table.scan(sk[:ns], S, read_ts, vis)
@@ -763,6 +892,16 @@ def main():
             nsnap.close()
         if hsnap is not snap:
             hsnap.close()
+
+    # ---- the other BASELINE configs, compact (N = 1): the 10 M-row table is released first (config 2 needs 105 GB) ----
+    workloads = None
+    if world == 1 and not args.no_workloads:
+        import bench_workloads as bw
+        snap.close()
+        snap = None
+        del d_payout, d_keyout, d_tsout, d_sk, d_ppay, d_pk
+        torch.cuda.empty_cache()
+        workloads = bw.run_all(args, sg, torch, dev, peaks()[0], cpu=not args.no_cpu_baseline)
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -791,15 +930,18 @@ def main():
             "cpu_baseline": cpu,
             "parity_check": parity,
             "transform": transform,
+            "host_tree": host_tree,
             "e2e": e2e,
             "gpu_launches": int(launches),
             "clocks": clk.summary(),
             "probe": probe,
+            "workloads": workloads,
             "snapshot": {"rows": int(info.n_rows), "leaves": int(info.n_leaves), "versions": int(info.n_versions),
                          "hbm_bytes": int(info.device_bytes), "build_s": t_build},
         }
         print(json.dumps(line), flush=True)
-    snap.close()
+    if snap is not None:
+        snap.close()
     if dist is not None:
         dist.destroy_process_group()
 

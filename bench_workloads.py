@@ -1,0 +1,273 @@
+"""bench_workloads.py — the other BASELINE.json configs as compact entries of bench.py's JSON line (N = 1).
+
+  config0  configs[0]  ./ycsb -k 10000 -b 4 -o 10 -u 0 -z 0.2: read-only point probes, 10 k-row int table (lives in L2)
+  config2  configs[2]  YCSB string keys (-m), zipf 0.9 batched probes, 100 M tuples (built on the device)
+  config3  configs[3]  TPC-C w = 30: stock-level order_line scans (10 rows) + stock probes, CH-Q2* MIN(S_QUANTITY)
+
+Every entry carries value / unit, a roofline fraction against its declared bound, a cpu_baseline (the reference's own
+BTree::Read / scan path from oracle/_ref on all host cores, over a bounded sample) and an in-run bit-exact sample
+against that CPU path. The GPU legs use product code only; oracle/ is imported by the cpu_baseline parts alone.
+Sizes are chosen so that the three entries together add about a minute to the N = 1 run.
+"""
+import os
+import time
+
+import numpy as np
+
+K_BYTES, P_BYTES = 4, 1000
+
+
+def _time_steps(torch, fn, warmup, steps):
+    for i in range(warmup):
+        fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        fn(warmup + i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def _cpu_table(payload, **kw):
+    from oracle import pyoracle
+    pyoracle.build_oracle()
+    if pyoracle.have_ref():
+        return pyoracle.RefTable(payload, **kw), "reference"
+    kw.pop("catalog_key_len", None)
+    kw.pop("leaf_pool_blocks", None)
+    return pyoracle.OracleTable(payload, **kw), "port"
+
+
+def _eq(a, b):
+    return all(np.array_equal(x, y) for x, y in zip(a, b))
+
+
+MALLOC_NOTE = "reference built -O2 -DNDEBUG with glibc malloc (no tcmalloc in this image)"
+
+
+def config0(args, sg, torch, dev, peak, cpu=True):
+    """BASELINE configs[0]. The reference's own CLI aborts at HEAD with an out-of-range key pick, so the
+    CPU side is the reference's BTree::Read driven over the same key stream at 4 threads (-b 4) and at all cores."""
+    from stage_indexorganized_b200 import ycsb
+    n_rows, n = 10_000, args.probes
+    steps, warm = min(args.steps, 10), 3
+    nb = steps + warm
+    snap = sg.Snapshot.generate_ycsb(n_rows, P_BYTES)
+    snap.set_stream(torch.cuda.current_stream().cuda_stream)
+    z = ycsb.Zipf(n_rows - 1, 0.2, seed=1).draw(n * nb).astype(np.uint32).reshape(nb, n)
+    d_keys = torch.from_numpy(z.view(np.int32)).to(dev)
+    found = torch.zeros((n,), dtype=torch.uint8, device=dev)
+    ts = torch.zeros((n,), dtype=torch.int32, device=dev)
+    kout = torch.empty((n,), dtype=torch.int32, device=dev)
+    pay = torch.empty((n, P_BYTES), dtype=torch.uint8, device=dev)
+    ms = _time_steps(torch, lambda b: snap.probe_device(d_keys[b], n, 1, found, ts, kout, pay), warm, steps)
+    hits = int(found.sum().item())
+    algo = hits * (K_BYTES + 2 * (K_BYTES + P_BYTES + 4)) + (n - hits) * (K_BYTES + 1)
+    ach = algo / (ms * 1e-3) / 1e9
+    out = {"workload": "BASELINE configs[0]: ./ycsb -k 10000 -b 4 -o 10 -u 0 -z 0.2 (read-only point probes, 10 k-row int table)",
+           "value": n / (ms * 1e-3), "unit": "probes/s", "ms_per_step": ms, "probes_per_step": n, "hit_rate": hits / n,
+           "roofline": {"bound": "l2", "achieved": ach, "unit": "GB/s", "peak": None, "frac": None,
+                        "hbm_write_frac": hits * (K_BYTES + P_BYTES + 4) / (ms * 1e-3) / 1e9 / peak,
+                        "note": "the 10 MB table is L2-resident: reads never reach HBM, only the result rows are written "
+                                "there (hbm_write_frac = result bytes / time / measured HBM copy peak); no measured L2 peak "
+                                "exists for this pool, so no fraction is claimed against the read side"}}
+    if cpu:
+        t, kind = _cpu_table(P_BYTES)
+        assert t.load_ycsb_int(0, n_rows) == n_rows
+        keys = np.ascontiguousarray(z.reshape(-1)[: 1 << 21]).view(np.uint8).reshape(-1, 4)
+        ok = _eq(snap.probe(keys[:65536], 1), t.probe(keys[:65536], 1))
+        cores = os.cpu_count() or 1
+        s4, _ = t.time_probe(keys, 1, 4, pin=True)
+        sa, _ = t.time_probe(keys, 1, cores, pin=True)
+        out["cpu_baseline"] = {"value": len(keys) / sa, "unit": "probes/s", "cores": cores, "kind": kind,
+                               "threads_4": len(keys) / s4, "sample": f"{len(keys)} probes of the same stream; " + MALLOC_NOTE}
+        out["parity_sample"] = {"ok": bool(ok), "checked": "65536 probes bit-exact vs CPU " + kind}
+    snap.close()
+    return out
+
+
+def config2(args, sg, torch, dev, peak, cpu=True, n_rows=100_000_000, cpu_rows=2_000_000):
+    """BASELINE configs[2]. The 100 M-row table (102 GB) only exists on the device; the CPU side (and the reference-
+    pinned bit-exact sample) uses the first cpu_rows keys of the same key function in a tree built by the reference."""
+    from stage_indexorganized_b200 import ycsb
+    n = args.probes
+    steps, warm = min(args.steps, 10), 3
+    nb = steps + warm
+    t0 = time.time()
+    snap, keys, _ = ycsb.build_string_table_device(n_rows)
+    build_s = time.time() - t0
+    snap.set_stream(torch.cuda.current_stream().cuda_stream)
+    z = np.clip(ycsb.Zipf(n_rows - 1, 0.9, seed=1).draw(n * nb).astype(np.int64), 1, n_rows) - 1
+    d_keys = keys[torch.from_numpy(z).to(dev)].reshape(nb, n, 16).contiguous()
+    found = torch.zeros((n,), dtype=torch.uint8, device=dev)
+    ts = torch.zeros((n,), dtype=torch.int32, device=dev)
+    kout = torch.empty((n, 16), dtype=torch.uint8, device=dev)
+    pay = torch.empty((n, P_BYTES), dtype=torch.uint8, device=dev)
+    ms = _time_steps(torch, lambda b: snap.probe_device(d_keys[b], n, 1, found, ts, kout, pay), warm, steps)
+    hits = int(found.sum().item())
+    algo = hits * (16 + 2 * (16 + P_BYTES + 4)) + (n - hits) * 17
+    ach = algo / (ms * 1e-3) / 1e9
+    out = {"workload": f"BASELINE configs[2]: YCSB string-key (-m) zipf 0.9 batched probes, {n_rows} tuples "
+                       "(FastRandom(1804289383) keys, built and bulk-loaded on the device)",
+           "value": n / (ms * 1e-3), "unit": "probes/s", "ms_per_step": ms, "probes_per_step": n, "hit_rate": hits / n,
+           "distinct_keys_per_step": int(np.unique(z[:n]).size), "build_s": build_s,
+           "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                        "note": "whole step (directory lookup + MVCC + rows); zipf 0.9 repeats hot rows, so part of the row "
+                                "reads are L2 hits"}}
+    del d_keys, pay
+    snap.close()
+    del keys
+    torch.cuda.empty_cache()
+    if cpu:
+        skeys = ycsb.random_strings(1804289383, cpu_rows, 16)
+        t, kind = _cpu_table(P_BYTES, catalog_key_len=16, leaf_pool_blocks=max(cpu_rows // 16, 4096))
+        row = np.full((1, P_BYTES), ord("a"), np.uint8)
+        for lo in range(0, cpu_rows, 250_000):
+            m = min(250_000, cpu_rows - lo)
+            assert t.insert(skeys[lo:lo + m], np.broadcast_to(row, (m, P_BYTES)), 0) == m
+        zc = np.clip(ycsb.Zipf(cpu_rows - 1, 0.9, seed=1).draw(1 << 21).astype(np.int64), 1, cpu_rows) - 1
+        pk = skeys[zc]
+        cores = os.cpu_count() or 1
+        sec, _ = t.time_probe(pk, 1, cores, pin=True)
+        hs = sg.Snapshot.from_tree(t.root, 16, P_BYTES)
+        miss = ycsb.random_strings(99, 1024, 16)
+        probe_keys = np.concatenate([pk[:64512], miss])
+        ok = _eq(hs.probe(probe_keys, 1), t.probe(probe_keys, 1))
+        ok = ok and _eq(hs.scan(pk[:256], 100, 1, 1), t.scan(pk[:256], 100, 1, 1))
+        ok = ok and _eq(hs.scan(pk[256:2304], 10, 1, 0), t.scan(pk[256:2304], 10, 1, 0))
+        quirk = int(hs.counters().slot_order_scans)
+        hs.close()
+        out["cpu_baseline"] = {"value": len(pk) / sec, "unit": "probes/s", "cores": cores, "kind": kind,
+                               "sample": f"{len(pk)} zipf-0.9 probes on a {cpu_rows}-row tree built by the reference from the "
+                                         "first keys of the same key function (a 100 M-row host tree needs 110 GB); " + MALLOC_NOTE}
+        out["parity_sample"] = {"ok": bool(ok), "slot_order_scans": quirk,
+                                "checked": f"the {cpu_rows}-row reference-built string tree flattened by from_tree: 65536 probes "
+                                           f"(1024 misses), 256 x 100-row MVCC scans and 2048 x 10-row scans bit-exact vs CPU {kind}"}
+        t.close()
+    return out
+
+
+def _bulk(sg, torch, keys, pays, K, P):
+    order = np.lexsort(keys.T[::-1])                      # memcmp order of the raw key bytes (keys >= 16 B)
+    snap, raw, pay, _ = sg.Snapshot.alloc_sorted(len(keys), K, P, rows_per_leaf=max(8, min(500, 60000 // (K + P + 24))))
+    raw.copy_(torch.from_numpy(keys[order]))
+    pay.copy_(torch.from_numpy(pays[order]))
+    snap.seal_sorted()
+    snap.set_stream(torch.cuda.current_stream().cuda_stream)
+    return snap
+
+
+def config3(args, sg, torch, dev, peak, cpu=True, W=30, cpu_w=4):
+    """BASELINE configs[3]: RunStockLevel's reads (benchmark/tpcc/tpcc_stock_level.cpp:37-196: 20 order_line scans of 10
+    rows + the stock probes of their items) and CH-Q2*'s stock probes with MIN(S_QUANTITY)
+    (benchmark/tpcc/tpcc_new_order.cpp:808-866) on the w = 30 tables. CPU side: trees of the first cpu_w warehouses built
+    by the reference from the same row functions."""
+    from stage_indexorganized_b200 import tpcc
+    steps, warm = min(args.steps, 10), 3
+    nb = steps + warm
+    sk, sp = tpcc.stock_rows(W)
+    ok_, op, _ = tpcc.order_line_rows(W)
+    stock = _bulk(sg, torch, sk, sp, tpcc.STOCK_KEY, tpcc.STOCK_PAYLOAD)
+    ol = _bulk(sg, torch, ok_, op, tpcc.OL_KEY, tpcc.OL_PAYLOAD)
+    txns = 50_000                                         # 1 M order_line scans of 10 rows per step
+    starts = [torch.from_numpy(tpcc.stock_level_requests(W, txns, seed=10 + b)[0]).to(dev) for b in range(nb)]
+    ns = txns * 20
+    sizes = torch.full((ns,), 10, dtype=torch.int32, device=dev)
+    counts = torch.zeros((ns,), dtype=torch.int32, device=dev)
+    kout = torch.empty((ns * 10, tpcc.OL_KEY), dtype=torch.uint8, device=dev)
+    tso = torch.empty((ns * 10,), dtype=torch.int32, device=dev)
+    pout = torch.empty((ns * 10, tpcc.OL_PAYLOAD), dtype=torch.uint8, device=dev)
+    ms_scan = _time_steps(torch, lambda b: ol.scan_device(starts[b], sizes, ns, 10, 1, 1, counts, kout, tso, pout), warm, steps)
+    rows = int(counts.sum().item())
+    ol.enable_timing(True)
+    ol.scan_device(starts[0], sizes, ns, 10, 1, 1, counts, kout, tso, pout)
+    ol_plan_ms, ol_gather_ms = ol.last_timing()
+    ol.enable_timing(False)
+    rng = np.random.default_rng(3)
+    n = args.probes
+    pk = [torch.from_numpy(tpcc.stock_key(rng.integers(1, W + 1, n), rng.integers(1, tpcc.ITEMS + 1, n))).to(dev) for _ in range(nb)]
+    found = torch.zeros((n,), dtype=torch.uint8, device=dev)
+    spay = torch.empty((n, tpcc.STOCK_PAYLOAD), dtype=torch.uint8, device=dev)
+    qty = torch.empty((n, 4), dtype=torch.uint8, device=dev)
+    ms_full = _time_steps(torch, lambda b: stock.probe_device(pk[b], n, 1, found, None, None, spay), warm, steps)
+    stock.enable_timing(True)
+    stock.probe_device(pk[0], n, 1, found, None, None, spay)
+    st_plan_ms, st_gather_ms = stock.last_timing()
+    stock.enable_timing(False)
+    ms_col = _time_steps(torch, lambda b: stock.probe_column_device(pk[b], n, 1, 0, 4, qty, found), warm, steps)
+    agg = [None]
+
+    def agg_step(b):
+        agg[0] = stock.probe_aggregate_i32(pk[b], 1, 0, 15, n=n)
+    ms_agg = _time_steps(torch, agg_step, warm, steps)
+    ol_row = 2 * (tpcc.OL_KEY + tpcc.OL_PAYLOAD + 4)
+    st_row = tpcc.STOCK_KEY + 2 * (tpcc.STOCK_KEY + tpcc.STOCK_PAYLOAD + 4)
+    ol_ach = (rows * ol_row + ns * (tpcc.OL_KEY + 8)) / (ms_scan * 1e-3) / 1e9
+    st_ach = n * st_row / (ms_full * 1e-3) / 1e9
+    out = {"workload": f"BASELINE configs[3]: TPC-C w={W} stock-level / CH-Q2* read pattern, stock {len(sk)} rows (16/400), "
+                       f"order_line {len(ok_)} rows (32/60), seeded row functions pinned to the reference's builders, bulk-loaded",
+           "value": rows / (ms_scan * 1e-3), "unit": "order_line rows/s", "ms_per_step": ms_scan,
+           "order_line_scan": {"scans_per_s": ns / (ms_scan * 1e-3), "scans_per_step": ns, "scan_size": 10,
+                               "plan_ms": ol_plan_ms, "gather_ms": ol_gather_ms},
+           "roofline": {"bound": "hbm", "achieved": ol_ach, "peak": peak, "unit": "GB/s", "frac": ol_ach / peak,
+                        "note": "order_line 10-row MVCC scans: 192 B per row + 40 B per scan (SURVEY 8d), whole step"},
+           "stock_probe_full_row": {"value": n / (ms_full * 1e-3), "unit": "probes/s", "ms_per_step": ms_full,
+                                    "plan_ms": st_plan_ms, "gather_ms": st_gather_ms,
+                                    "roofline": {"bound": "hbm", "achieved": st_ach, "peak": peak, "frac": st_ach / peak}},
+           "stock_probe_quantity_pushdown": {"value": n / (ms_col * 1e-3), "unit": "probes/s", "bytes_returned_per_probe": 5},
+           "stock_probe_quantity_aggregate": {"value": n / (ms_agg * 1e-3), "unit": "probes/s", "bytes_returned_per_batch": 24,
+                                              "below_threshold_15": int(agg[0].below), "min_quantity": int(agg[0].min_value)}}
+    extra = getattr(config3, "fused_stock_level", None)
+    if extra is not None:
+        out["stock_level_fused"] = extra(args, sg, torch, dev, stock, ol, W, warm, steps)
+    stock.close()
+    ol.close()
+    del kout, tso, pout, spay, starts, pk
+    torch.cuda.empty_cache()
+    if cpu:
+        w64 = sk.view(np.int64).reshape(-1, 2)[:, 0]
+        ow64 = ok_.view(np.int64).reshape(-1, 4)[:, 0]
+        csk, csp = sk[w64 <= cpu_w], sp[w64 <= cpu_w]
+        cok, cop = ok_[ow64 <= cpu_w], op[ow64 <= cpu_w]
+        ts_, kind = _cpu_table(tpcc.STOCK_PAYLOAD, split_threshold=65536, catalog_key_len=16, leaf_pool_blocks=max(len(csk) // 40, 4096))
+        assert ts_.insert(csk, csp, 0) == len(csk)
+        to_, _ = _cpu_table(tpcc.OL_PAYLOAD, split_threshold=65536, catalog_key_len=32, leaf_pool_blocks=max(len(cok) // 100, 4096))
+        assert to_.insert(cok, cop, 0) == len(cok)
+        cores = os.cpu_count() or 1
+        cstart = tpcc.stock_level_requests(cpu_w, 20_000, seed=77)[0]
+        sec_s, crow = to_.time_scan(cstart, 10, 1, 1, cores, pin=True)
+        cpk = tpcc.stock_key(rng.integers(1, cpu_w + 1, 1 << 21), rng.integers(1, tpcc.ITEMS + 1, 1 << 21))
+        sec_p, _ = ts_.time_probe(cpk, 1, cores, pin=True)
+        hs = sg.Snapshot.from_tree(ts_.root, tpcc.STOCK_KEY, tpcc.STOCK_PAYLOAD)
+        ho = sg.Snapshot.from_tree(to_.root, tpcc.OL_KEY, tpcc.OL_PAYLOAD)
+        ok = _eq(ho.scan(cstart[:20000], 10, 1, 1), to_.scan(cstart[:20000], 10, 1, 1))
+        ok = ok and _eq(hs.probe(cpk[:65536], 1), ts_.probe(cpk[:65536], 1))
+        quirk = int(ho.counters().slot_order_scans)
+        hs.close()
+        ho.close()
+        out["cpu_baseline"] = {"value": crow / sec_s, "unit": "order_line rows/s", "cores": cores, "kind": kind,
+                               "stock_probes_per_s": len(cpk) / sec_p,
+                               "sample": f"trees of warehouses 1..{cpu_w} built by the reference from the same row functions: "
+                                         f"{len(cstart)} stock-level scans of 10 rows through the unmodified IndexScanExecutor, "
+                                         f"{len(cpk)} BTree::Read stock probes; " + MALLOC_NOTE}
+        out["parity_sample"] = {"ok": bool(ok), "slot_order_scans": quirk,
+                                "checked": f"those trees flattened by from_tree: 20000 stock-level scans and 65536 stock probes "
+                                           f"bit-exact vs CPU {kind}"}
+        ts_.close()
+        to_.close()
+    return out
+
+
+def run_all(args, sg, torch, dev, peak, cpu=True):
+    out = {}
+    for name, fn in (("config0", config0), ("config2", config2), ("config3", config3)):
+        t0 = time.time()
+        try:
+            out[name] = fn(args, sg, torch, dev, peak, cpu)
+        except Exception as e:      # noqa: BLE001 — a failed side leg must not take the headline line down with it
+            out[name] = {"error": repr(e)[:300]}
+        out[name]["leg_seconds"] = time.time() - t0
+        torch.cuda.empty_cache()
+    return out

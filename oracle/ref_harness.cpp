@@ -419,9 +419,14 @@ double ref_time_scan(ref_table *t, const void *start_keys, uint32_t key_size, ui
             uint64_t b = n * w / threads, e = n * (w + 1) / threads, r = 0;
             ready++;
             while (!go.load()) {}
+            // MVCC scans run the reference's own IndexScanExecutor (range branch), rows copied out in its predicate
+            // callback — the same code the parity tests compare against; unfiltered scans run the restated
+            // TableScanExecutor loop over the unmodified BTree::RangeScanBySize / Iterator::GetNext.
             for (uint64_t i = b; i < e; ++i)
-                r += scan_one(t, k + i * key_size, key_size, scan_size, read_ts, apply_visibility, ts.data(),
-                              key.data(), pay.data());
+                r += apply_visibility && scan_size
+                         ? scan_one_executor(t, k + i * key_size, key_size, scan_size, read_ts, ts.data(), key.data(), pay.data())
+                         : scan_one(t, k + i * key_size, key_size, scan_size, read_ts, apply_visibility, ts.data(), key.data(),
+                                    pay.data());
             rows[w] = r;
         });
     }

@@ -11,26 +11,42 @@ import numpy as np
 _LCG_A, _LCG_C, _LCG_M = 0x5DEECE66D, 0xB, (1 << 48) - 1
 
 
+_JUMP_BLOCK = 1 << 16
+_jump_tab = None
+
+
+def _jump_table():
+    """(A_k, C_k), k = 1.._JUMP_BLOCK, with s_{i+k} = A_k s_i + C_k (mod 2^48): the k-fold composition of the LCG step."""
+    global _jump_tab
+    if _jump_tab is None:
+        A = np.empty(_JUMP_BLOCK, np.uint64)
+        Cc = np.empty(_JUMP_BLOCK, np.uint64)
+        aa, cc = 1, 0
+        for i in range(_JUMP_BLOCK):
+            aa, cc = (aa * _LCG_A) & _LCG_M, (cc * _LCG_A + _LCG_C) & _LCG_M
+            A[i], Cc[i] = aa, cc
+        _jump_tab = (A, Cc)
+    return _jump_tab
+
+
 def lcg_states(seed, count):
     """States s_1..s_count of FastRandom(seed): s_0 = (seed ^ A) & M, s_{k+1} = (A s_k + C) & M
-    (benchmark_common.h:52-60). Vectorised by composing the affine step maps (A, C)^(2^j)."""
+    (benchmark_common.h:52-60). Vectorised block by block with the jump table (uint64 products wrap mod 2^64, which
+    keeps the low 48 bits exact)."""
     count = int(count)
-    idx = np.arange(1, count + 1, dtype=np.uint64)
-    mul = np.ones(count, np.uint64)
-    add = np.zeros(count, np.uint64)
-    a, c = np.uint64(_LCG_A), np.uint64(_LCG_C)
+    A, Cc = _jump_table()
     m = np.uint64(_LCG_M)
+    s = np.uint64((int(seed) ^ _LCG_A) & _LCG_M)
+    out = np.empty(count, np.uint64)
+    done = 0
     with np.errstate(over="ignore"):
-        j = 0
-        while (1 << j) <= count:
-            bit = ((idx >> np.uint64(j)) & np.uint64(1)).astype(bool)
-            # apply map (a, c) after the maps collected so far:  x -> a (mul x + add) + c
-            mul = np.where(bit, (a * mul) & m, mul)
-            add = np.where(bit, (a * add + c) & m, add)
-            a, c = (a * a) & m, (a * c + c) & m
-            j += 1
-        s0 = np.uint64((int(seed) ^ _LCG_A) & _LCG_M)
-        return (mul * s0 + add) & m
+        while done < count:
+            nb = min(_JUMP_BLOCK, count - done)
+            st = (A[:nb] * s + Cc[:nb]) & m
+            out[done:done + nb] = st
+            s = st[-1]
+            done += nb
+    return out
 
 
 def fastrandom_next64(seed, count):

@@ -19,43 +19,12 @@ import torch
 import stage_indexorganized_b200 as sg
 from stage_indexorganized_b200 import ycsb
 from stage_indexorganized_b200.ycsb import rank_to_key
+from stage_indexorganized_b200.model import UpdateModel, expected_payload_bytes
 from helpers import assert_scan_equal, u32_keys
 from oracle import pyoracle
 
 pytestmark = pytest.mark.gpu
 FIRST_CID = 10
-
-
-class UpdateModel:
-    """Committed updates (key, commit id = FIRST_CID + i) -> what a reader sees."""
-
-    def __init__(self, upd_keys):
-        k = np.asarray(upd_keys, np.uint64)
-        cid = np.arange(FIRST_CID, FIRST_CID + len(k), dtype=np.uint64)
-        self.code = np.sort((k << np.uint64(32)) | cid)           # (key, cid) pairs, sorted
-        self.keys_sorted = self.code >> np.uint64(32)
-
-    def visible(self, keys, read_ts, scan=False):
-        """-> (visible bool[n], stamp u32[n]) for existing keys. Point probes walk the version chain (an older
-        version with begin != 0 can answer); a range scan only ever returns the in-leaf version, i.e. the row is
-        visible iff ALL its updates committed at or before read_ts (executor.h:465-534 with next_tuple_ptr == 0)."""
-        k = np.asarray(keys, np.uint64)
-        lo = np.searchsorted(self.keys_sorted, k, "left")
-        hi = np.searchsorted(self.keys_sorted, k, "right")
-        n_upd = hi - lo
-        # number of this key's updates with cid <= read_ts
-        le = np.searchsorted(self.code, (k << np.uint64(32)) | np.uint64(min(read_ts, 0xFFFFFFFF)), "right") - lo
-        le = np.clip(le, 0, n_upd)
-        stamp = np.where(le > 0, self.code[np.clip(lo + le - 1, 0, max(len(self.code) - 1, 0))] & np.uint64(0xFFFFFFFF), 0)
-        vis = (n_upd == 0) | ((le == n_upd) if scan else (le > 0))
-        return vis, np.where(vis, stamp, 0).astype(np.uint32)
-
-
-def expected_payload_bytes(keys, stamp):
-    """(first byte, byte 150, last byte) of the row image: base = (uint8) key, column [100,200) = (uint8) stamp if updated."""
-    base = (np.asarray(keys, np.uint32) & 0xFF).astype(np.uint8)
-    col = np.where(stamp > 0, (stamp & 0xFF).astype(np.uint8), base)
-    return base, col, base
 
 
 def device_updates(snap, upd_keys):

@@ -26,6 +26,7 @@
 #include "node_layout.h"
 #include "probe.cuh"
 #include "scan.cuh"
+#include "scan_short.cuh"
 #include "transform.cuh"
 #include "gather.cuh"
 #include "generate.cuh"
@@ -191,6 +192,8 @@ struct stage_snapshot {
     std::mutex ctx_mu;
     std::condition_variable ctx_cv;
     std::vector<HostCtx *> ctx_pool;
+    uint32_t *d_row_leaf = nullptr;             // row -> leaf table of the fused short-scan kernel, built on first use
+    std::mutex aux_mu;
     unsigned long long *d_stats = nullptr;      // [0] scans in which the slot-order truncation (Q5) selected the rows
 };
 
@@ -243,7 +246,7 @@ static void snapshot_free(stage_snapshot *s) {
     cudaSetDevice(s->device);
     void *ptrs[] = {s->d_skey, s->d_slot, s->d_ts, s->d_chain, s->d_payload, s->d_leaf_off, s->d_sep, s->d_cont,
                     s->d_has_sep, s->d_ver_begin, s->d_ver_commit, s->d_ver_next, s->d_ver_payload,
-                    s->d_err, s->d_stage[0], s->d_stage[1], s->d_raw_keys, s->d_phys, s->d_dir, s->d_stats};
+                    s->d_err, s->d_stage[0], s->d_stage[1], s->d_raw_keys, s->d_phys, s->d_dir, s->d_stats, s->d_row_leaf};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     free(s->ext_ver_payload);
@@ -1929,6 +1932,51 @@ static int launch_scan_nw(stage_snapshot *s, const ScanArgs &a, cudaStream_t st)
     }
 }
 
+// ---- fused short scans (scan_short.cuh) ---------------------------------------------------------------------
+static int ensure_row_leaf(stage_snapshot *s) {
+    std::lock_guard<std::mutex> lk(s->aux_mu);
+    if (s->d_row_leaf) return STAGE_OK;
+    uint32_t *p = nullptr;
+    int rc = dev_alloc(s, &p, s->n_rows);
+    if (rc) return rc;
+    row_leaf_build_kernel<<<(unsigned) std::min<uint64_t>(std::max<uint64_t>(s->n_leaves, 1), (uint64_t) sm_count() * 16), 128, 0, s->stream>>>(
+        s->d_leaf_off, (uint32_t) s->n_leaves, p);
+    LAUNCH_CHECK();
+    CUDA_TRY(cudaStreamSynchronize(s->stream));       // other streams (host-call contexts) read it next
+    s->d_row_leaf = p;
+    return STAGE_OK;
+}
+
+static bool short_scan_eligible(const stage_snapshot *s, const ScanArgs &a, const uint8_t *payload_out) {
+    static const bool off = getenv("STAGE_SCAN_FUSED") && atoi(getenv("STAGE_SCAN_FUSED")) == 0;
+    const uint32_t P = s->schema.payload_size, K = s->schema.key_size;
+    return !off && a.out_stride >= 1 && a.out_stride <= 32 && (P & 3u) == 0 && P <= kShortMaxRow && K == (uint32_t) s->nw * 4 &&
+           (((uintptr_t) payload_out | (uintptr_t) a.key_out | (uintptr_t) s->d_payload) & 3u) == 0 && s->n_rows > 0;
+}
+
+template <int NW>
+static int launch_short_scan(stage_snapshot *s, const ScanArgs &a, uint8_t *payload_out, cudaStream_t st) {
+    ShortScanOut o{payload_out, s->d_row_leaf};
+    const size_t slots = ((s->view.max_leaf_rows + 7u) & ~7u) * 2;
+    if (a.out_stride <= 16) {
+        constexpr int tiles = kShortThreads / 16;
+        const size_t smem = slots * tiles + 16;
+        if (smem > 48 * 1024)
+            CUDA_TRY(cudaFuncSetAttribute(scan_short_fused_kernel<NW, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        const unsigned blocks = (unsigned) std::min<uint64_t>((a.n + tiles - 1) / tiles, (uint64_t) sm_count() * 16);
+        scan_short_fused_kernel<NW, 16><<<blocks, kShortThreads, smem, st>>>(s->view, a, o);
+    } else {
+        constexpr int tiles = kShortThreads / 32;
+        const size_t smem = slots * tiles + 16;
+        if (smem > 48 * 1024)
+            CUDA_TRY(cudaFuncSetAttribute(scan_short_fused_kernel<NW, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        const unsigned blocks = (unsigned) std::min<uint64_t>((a.n + tiles - 1) / tiles, (uint64_t) sm_count() * 16);
+        scan_short_fused_kernel<NW, 32><<<blocks, kShortThreads, smem, st>>>(s->view, a, o);
+    }
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
 // plan (scan_plan_kernel) then payload gather; all pointers are device-visible. dst_base (compact layout): row offset of
 // every scan in payload_out, computed by the caller between the two launches (scan_plan_launch / scan_gather_launch).
 static int scan_plan_launch(stage_snapshot *s, const Lane &ln, ScanArgs &a) {
@@ -1954,6 +2002,24 @@ static int scan_gather_launch(stage_snapshot *s, const Lane &ln, const ScanArgs 
 static int scan_device(stage_snapshot *s, const Lane &ln, ScanArgs a, uint8_t *payload_out) {
     if (a.n == 0) return STAGE_OK;
     int rc;
+    if (short_scan_eligible(s, a, payload_out)) {      // short scans of short rows: one kernel plans and emits the rows
+        if (!s->d_row_leaf && (rc = ensure_row_leaf(s))) return rc;
+        a.src_row = nullptr;
+        a.stats = s->d_stats;
+        if (ln.timing) CUDA_TRY(cudaEventRecord(s->tev[0], ln.st));
+        switch (s->nw) {
+            case 1: rc = launch_short_scan<1>(s, a, payload_out, ln.st); break;
+            case 2: rc = launch_short_scan<2>(s, a, payload_out, ln.st); break;
+            case 4: rc = launch_short_scan<4>(s, a, payload_out, ln.st); break;
+            default: rc = launch_short_scan<8>(s, a, payload_out, ln.st); break;
+        }
+        if (ln.timing) {
+            CUDA_TRY(cudaEventRecord(s->tev[1], ln.st));
+            CUDA_TRY(cudaEventRecord(s->tev[2], ln.st));
+            s->timed_gather = false;
+        }
+        return rc;
+    }
     if ((rc = scan_plan_launch(s, ln, a))) return rc;
     return scan_gather_launch(s, ln, a, payload_out);
 }

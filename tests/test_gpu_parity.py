@@ -175,6 +175,23 @@ def test_fence_search_probe_variant():
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
 
 
+def test_two_kernel_short_scan_variant():
+    """Scans of <= 32 rows over rows of <= 256 bytes normally run in one kernel that plans the scan and emits its rows
+    (csrc/scan_short.cuh); STAGE_SCAN_FUSED=0 keeps the plan kernel + gather pair. Both must give the checker's bytes:
+    the scan tests of this file, the fuzz and the TPC-C tests are re-run in a child process with the fused kernel off."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("STAGE_VARIANT_RUN"):
+        pytest.skip("already inside a variant run")
+    env = dict(os.environ, STAGE_SCAN_FUSED="0", STAGE_VARIANT_RUN="1", STAGE_TEST_TPCC_W="4")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), os.path.join(here, "test_gpu_fuzz.py"),
+                        os.path.join(here, "test_gpu_tpcc.py"), "-x", "-q", "-m", "gpu", "-k", "scan or fuzz or stock_level or other_key"],
+                       env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
+
+
 def test_column_pushdown_unaligned(ycsb10k):
     """Projection of an unaligned byte range, including versions served from the staged chains."""
     t, snap = ycsb10k

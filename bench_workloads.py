@@ -219,9 +219,25 @@ def config3(args, sg, torch, dev, peak, cpu=True, W=30, cpu_w=4):
            "stock_probe_quantity_pushdown": {"value": n / (ms_col * 1e-3), "unit": "probes/s", "bytes_returned_per_probe": 5},
            "stock_probe_quantity_aggregate": {"value": n / (ms_agg * 1e-3), "unit": "probes/s", "bytes_returned_per_batch": 24,
                                               "below_threshold_15": int(agg[0].below), "min_quantity": int(agg[0].min_value)}}
-    extra = getattr(config3, "fused_stock_level", None)
-    if extra is not None:
-        out["stock_level_fused"] = extra(args, sg, torch, dev, stock, ol, W, warm, steps)
+    # the whole read side of RunStockLevel as one device-side operator (stage_gpu_tpcc_stock_level): 20 scans + first
+    # item + stock probe + threshold + distinct count per transaction, 4 bytes per transaction returned
+    req = np.zeros((nb, txns), sg.STOCK_LEVEL_REQ)
+    rq = np.random.default_rng(17)
+    req["w_id"] = rq.integers(1, W + 1, (nb, txns))
+    req["d_id"] = rq.integers(1, tpcc.DISTRICTS + 1, (nb, txns))
+    req["next_o_id"] = tpcc.ORDERS + 1
+    req["threshold"] = rq.integers(10, 21, (nb, txns))
+    d_req = torch.from_numpy(req.view(np.uint8).reshape(nb, txns, 32)).to(dev)
+    d_cnt = torch.zeros((txns,), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    ms_sl = _time_steps(torch, lambda b: sg.tpcc_stock_level(ol, stock, d_req[b], 1, out=d_cnt, n=txns), warm, steps)
+    sl_bytes = txns * 20 * (32 + 8 + 10 * (32 + 4 + 4) + 16 + 2 * 4)       # keys + commit ids + OL_I_ID of the scanned rows, one stock probe
+    out["stock_level_fused"] = {"value": txns / (ms_sl * 1e-3), "unit": "stock-level transactions/s", "ms_per_step": ms_sl,
+                                "transactions_per_step": txns, "order_line_scans_per_s": txns * 20 / (ms_sl * 1e-3),
+                                "bytes_returned_per_transaction": 4, "mean_distinct_items": float(d_cnt.float().mean().item()),
+                                "touched_GBps": sl_bytes / (ms_sl * 1e-3) / 1e9,
+                                "note": "stage_gpu_tpcc_stock_level, device-resident requests; latency-bound (dependent loads), "
+                                        "not bandwidth-bound: only keys, commit ids and two 4-byte columns are touched"}
     stock.close()
     ol.close()
     del kout, tso, pout, spay, starts, pk

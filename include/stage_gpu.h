@@ -270,6 +270,25 @@ typedef struct {
 int stage_gpu_probe_aggregate_i32(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint32_t col_off,
                                   int32_t threshold, stage_agg_i32_t *out, int flags);
 
+/* RunStockLevel's read side as ONE device-side operator (benchmark/tpcc/tpcc_stock_level.cpp:37-196).
+ * Per request: for each of the 20 orders o in [next_o_id - 20, next_o_id) a range scan of 10 order_line rows from
+ * {w_id, d_id, o, 5} under the executor's range visibility rule (:100-150); the FIRST returned row that still belongs
+ * to (w_id, d_id, o) names an item (:152-155); stock {w_id, item} is probed under the point visibility rule (version
+ * chains walked, :156-186); items whose visible S_QUANTITY is below `threshold` are counted once (:187-190).
+ * distinct_items[i] = that count. Nothing but 4 bytes per transaction leaves the device. Table layouts are TPC-C's
+ * (benchmark/tpcc/tpcc_record.h): order_line key {int64 w, d, o, number} (32 B), payload starts with int32 OL_I_ID;
+ * stock key {int64 w, i} (16 B), payload starts with int32 S_QUANTITY. reqs / distinct_items follow `flags`
+ * (STAGE_IO_HOST: the call returns when the counts are in host memory; STAGE_IO_DEVICE: enqueued on order_line's
+ * stream). */
+typedef struct {
+    int64_t w_id, d_id;
+    int64_t next_o_id;   /* D_NEXT_O_ID of the district (the caller's first read, tpcc_stock_level.cpp:58-90) */
+    int32_t threshold;
+    int32_t reserved;
+} stage_stock_level_req_t;
+int stage_gpu_tpcc_stock_level(stage_snapshot_t *order_line, stage_snapshot_t *stock, const stage_stock_level_req_t *reqs,
+                               uint64_t n, uint32_t read_ts, uint32_t *distinct_items, int flags);
+
 /* TableScanExecutor with scan_sz == -1 (include/execute/executor.h:581-619): the PHYSICAL whole-tree walk — leaves in
  * tree order, record slots in slot (insertion) order, no visibility test. Returns rows [first_row, first_row + n) of
  * that order (n_rows of stage_gpu_snapshot_info in total): latest in-leaf versions, keys, commit ids, payload rows.

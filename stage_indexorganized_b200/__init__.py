@@ -87,6 +87,7 @@ SYMBOLS = {
     "stage_gpu_probe_project": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp, _u32, _u32, _vp, _i32]),
     "stage_gpu_probe_aggregate_i32": (_i32, [_vp, _vp, _u64, _u32, _u32, C.c_int32, C.POINTER(AggI32), _i32]),
     "stage_gpu_scan_project": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _u32, _u32, _vp, _i32]),
+    "stage_gpu_tpcc_stock_level": (_i32, [_vp, _vp, _vp, _u64, _u32, _vp, _i32]),
     "stage_gpu_scan_physical": (_i32, [_vp, _u64, _u64, _vp, _vp, _vp, _i32]),
     "stage_gpu_route": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp]),
     "stage_gpu_route_device": (_i32, [C.POINTER(Schema), _vp, _u32, _vp, _u64, _vp, _vp]),
@@ -465,6 +466,21 @@ class Snapshot:
         _check(lib().stage_gpu_scan_batch(self.h, _ptr(start_keys), _ptr(scan_sizes), n, out_stride, read_ts,
                                           int(apply_visibility), _ptr(row_counts), _ptr(key_out), _ptr(ts_out),
                                           _ptr(payload_out), IO_DEVICE))
+
+
+STOCK_LEVEL_REQ = np.dtype([("w_id", "<i8"), ("d_id", "<i8"), ("next_o_id", "<i8"), ("threshold", "<i4"), ("reserved", "<i4")])
+
+
+def tpcc_stock_level(order_line, stock, reqs, read_ts, out=None, n=None):
+    """stage_gpu_tpcc_stock_level: reqs = numpy array of STOCK_LEVEL_REQ (host) -> uint32 distinct-item counts; or, with n
+    given, reqs / out are CUDA tensors (device pointers) and the call is enqueued on order_line's stream."""
+    if n is None:
+        reqs = np.ascontiguousarray(reqs, STOCK_LEVEL_REQ)
+        out = np.zeros(len(reqs), np.uint32)
+        _check(lib().stage_gpu_tpcc_stock_level(order_line.h, stock.h, _ptr(reqs), len(reqs), read_ts, _ptr(out), IO_HOST))
+        return out
+    _check(lib().stage_gpu_tpcc_stock_level(order_line.h, stock.h, _ptr(reqs), n, read_ts, _ptr(out), IO_DEVICE))
+    return out
 
 
 def route(keys, splitters, key_size, key_kind=KEY_AUTO):

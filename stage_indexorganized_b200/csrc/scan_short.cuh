@@ -39,8 +39,8 @@ struct ShortScanOut {
     const uint32_t *row_leaf;    // [n_rows]
 };
 
-template <int NW, int TW>
-__global__ void __launch_bounds__(kShortThreads) scan_short_fused_kernel(SnapshotView v, ScanArgs a, ShortScanOut o) {
+template <int NW, int TW, int MINB>
+__global__ void __launch_bounds__(kShortThreads, MINB) scan_short_fused_kernel(SnapshotView v, ScanArgs a, ShortScanOut o) {
     constexpr int kTiles = kShortThreads / TW;                   // scans in flight per CTA
     extern __shared__ __align__(16) uint16_t s_slots_all[];      // [kTiles][max_leaf_rows] for the slot-order rule
     __shared__ uint32_t s_src[kTiles][TW], s_tsv[kTiles][TW];
@@ -65,28 +65,34 @@ __global__ void __launch_bounds__(kShortThreads) scan_short_fused_kernel(Snapsho
         uint32_t cnt = 0;
         if (S > 0 && L > 0) {
             bool have_row = false;
-            uint32_t row0 = 0;
+            uint32_t row0 = 0, j0 = 0;
+            uint32_t t_spec = 0;                  // commit id of row q0 + tl, requested as soon as the first row is known
             if (v.dir) {
-                const SKey<NW> kk[1] = {begin};
-                uint32_t cc[1];
-                bool hh[1];
-                dir_lookup<NW, 1>(v, kk, cc, hh);
-                have_row = hh[0];
-                row0 = cc[0];
-            }
-            uint32_t j0 = 0, lo0, hi0, below = 0;
-            uint32_t t_spec = 0;                  // commit id of row q0 + tl, requested early when the first row is known
-            bool spec = false;
-            if (have_row) {
-                j0 = __ldg(o.row_leaf + row0);
-                if ((uint64_t) row0 + tl < v.n_rows) {
-                    t_spec = __ldg(v.ts + row0 + tl);
-                    spec = true;
+                // directory probe (probe.cuh dir_lookup) with the follow-up loads issued together: on a tag match the key
+                // to verify, the row's leaf and the window's commit ids are requested in one round
+                uint32_t h = __umulhi(skey_hash<NW>(begin, 0x9E3779B9u), v.dir_cap);
+                const uint32_t tag = skey_tag<NW>(begin);
+                for (;;) {
+                    const uint2 e = __ldg(v.dir + h);
+                    if (e.y == kNoRow) break;
+                    if (e.x == tag) {
+                        const uint32_t jj = __ldg(o.row_leaf + e.y);
+                        const uint32_t tt = (uint64_t) e.y + tl < v.n_rows ? __ldg(v.ts + e.y + tl) : 0u;
+                        if (NW == 1 || skey_equal<NW>(load_skey<NW>(v.level[0], e.y), begin)) {
+                            have_row = true;
+                            row0 = e.y;
+                            j0 = jj;
+                            t_spec = tt;
+                            break;
+                        }
+                    }
+                    h = h + 1 == v.dir_cap ? 0 : h + 1;
                 }
-                lo0 = v.leaf_off[j0];
-                hi0 = v.leaf_off[j0 + 1];
-                below = row0 - lo0;
-            } else {
+            }
+            uint32_t q0 = row0;
+            bool nonempty = true;                 // the start leaf holds a row >= begin
+            if (!have_row) {
+                uint32_t below = 0;
                 for (uint32_t n = L - 1; n > 0;) {                  // start leaf: number of upper fences < begin
                     const uint32_t step = (n + TW - 1) / TW;
                     const uint64_t idx = (uint64_t) j0 + (uint64_t) (tl + 1) * step - 1;
@@ -95,8 +101,7 @@ __global__ void __launch_bounds__(kShortThreads) scan_short_fused_kernel(Snapsho
                     n = min(step - 1, n - min(n, adv));
                     j0 += adv;
                 }
-                lo0 = v.leaf_off[j0];
-                hi0 = v.leaf_off[j0 + 1];
+                const uint32_t lo0 = v.leaf_off[j0], hi0 = v.leaf_off[j0 + 1];
                 for (uint32_t n = hi0 - lo0; n > 0;) {              // rows of the start leaf with key < begin
                     const uint32_t step = (n + TW - 1) / TW;
                     const uint64_t idx = (uint64_t) below + (uint64_t) (tl + 1) * step - 1;
@@ -105,29 +110,41 @@ __global__ void __launch_bounds__(kShortThreads) scan_short_fused_kernel(Snapsho
                     n = min(step - 1, n - min(n, adv));
                     below += adv;
                 }
+                q0 = lo0 + below;
+                nonempty = hi0 > q0;
             }
-            const uint32_t q0 = lo0 + below;
-            if (hi0 > q0) {
+            if (nonempty) {
                 const uint64_t need_end = (uint64_t) q0 + S;
-                uint32_t jl = L - 1;
+                // leaves j0 .. j0+TW-1 in one round: offsets and flags per lane, the last leaf touched by ballot, its
+                // bounds by shuffle (a window of <= TW rows rarely spans more leaves; then the loop goes on)
+                uint32_t jl = L - 1, row_end = 0, lo_jl = 0, cont_jl = 0;
                 for (uint32_t base = j0;; base += TW) {
                     const uint32_t j = base + tl;
-                    const bool stop = j < L && (!(v.cont[j] & kLeafHop) || (uint64_t) v.leaf_off[j + 1] >= need_end || j == L - 1);
+                    const uint32_t lo_t = j < L ? __ldg(v.leaf_off + j) : 0u, hi_t = j < L ? __ldg(v.leaf_off + j + 1) : 0u;
+                    const uint32_t c_t = j < L ? (uint32_t) __ldg(v.cont + j) : 0u;
+                    const bool stop = j < L && (!(c_t & kLeafHop) || (uint64_t) hi_t >= need_end || j == L - 1);
                     const uint32_t m = tballot(stop);
-                    if (m) { jl = base + (uint32_t) __ffs(m) - 1; break; }
+                    if (m) {
+                        const int src = tbase + __ffs(m) - 1;
+                        jl = base + (uint32_t) __ffs(m) - 1;
+                        row_end = __shfl_sync(tmask, hi_t, src);
+                        lo_jl = __shfl_sync(tmask, lo_t, src);
+                        cont_jl = __shfl_sync(tmask, c_t, src);
+                        break;
+                    }
                 }
-                const uint32_t row_end = v.leaf_off[jl + 1];
+                (void) jl;
                 const uint32_t total = (uint64_t) row_end >= need_end ? S : row_end - q0;
-                const uint32_t start_l = max(q0, v.leaf_off[jl]);
+                const uint32_t start_l = max(q0, lo_jl);
                 const uint32_t T = S - (start_l - q0);
                 const uint32_t nql = row_end - start_l;
-                const bool quirk = nql > T + 1 && !(v.cont[jl] & kLeafSlotOrdered);
+                const bool quirk = nql > T + 1 && !(cont_jl & kLeafSlotOrdered);
                 const uint32_t main_n = quirk ? start_l - q0 : total;        // <= S <= TW: one pass
                 {
                     uint32_t src = kNoRow, stamp = 0;
                     const uint32_t row = q0 + tl;
                     if ((uint32_t) tl < main_n) {
-                        const uint32_t t = spec ? t_spec : __ldg(v.ts + row);
+                        const uint32_t t = have_row ? t_spec : __ldg(v.ts + row);
                         if (scan_row_visible(a, t)) { src = row; stamp = t; }
                     }
                     const uint32_t m = tballot(src != kNoRow);

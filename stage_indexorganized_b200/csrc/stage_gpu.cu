@@ -33,6 +33,7 @@
 #include "exchange.cuh"
 #include "probe_fused.cuh"
 #include "refresh.cuh"
+#include "tpcc_ops.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
@@ -188,6 +189,7 @@ struct stage_snapshot {
     // scratch for STAGE_IO_HOST batches of the push-down calls (serialised on `mu`)
     DevBuf sc_keys, sc_found, sc_ts, sc_keyout, sc_payload, sc_sizes, sc_counts;
     DevBuf sc_srcrow;                           // source-row lists handed from the plan kernels to the gather
+    DevBuf sl_req, sl_keys, sl_sizes, sl_counts, sl_src, sl_skeys, sl_psrc, sl_out;   // stage_gpu_tpcc_stock_level scratch
     // contexts of the host-buffer probe / scan calls (one per concurrent caller, created on demand)
     std::mutex ctx_mu;
     std::condition_variable ctx_cv;
@@ -261,6 +263,8 @@ static void snapshot_free(stage_snapshot *s) {
     s->ctx_pool.clear();
     s->sc_keys.release(); s->sc_found.release(); s->sc_ts.release(); s->sc_keyout.release();
     s->sc_payload.release(); s->sc_sizes.release(); s->sc_counts.release(); s->sc_srcrow.release();
+    s->sl_req.release(); s->sl_keys.release(); s->sl_sizes.release(); s->sl_counts.release(); s->sl_src.release();
+    s->sl_skeys.release(); s->sl_psrc.release(); s->sl_out.release();
     s->rf_keys.release(); s->rf_patch.release(); s->rf_cid.release(); s->rf_row.release(); s->rf_order.release();
     s->rf_row_sorted.release(); s->rf_order_sorted.release(); s->rf_tmp.release(); s->rf_applied.release();
     for (int i = 0; i < 3; ++i)
@@ -1954,27 +1958,24 @@ static bool short_scan_eligible(const stage_snapshot *s, const ScanArgs &a, cons
            (((uintptr_t) payload_out | (uintptr_t) a.key_out | (uintptr_t) s->d_payload) & 3u) == 0 && s->n_rows > 0;
 }
 
-template <int NW>
-static int launch_short_scan(stage_snapshot *s, const ScanArgs &a, uint8_t *payload_out, cudaStream_t st) {
-    ShortScanOut o{payload_out, s->d_row_leaf};
-    const size_t slots = ((s->view.max_leaf_rows + 7u) & ~7u) * 2;
-    if (a.out_stride <= 16) {
-        constexpr int tiles = kShortThreads / 16;
-        const size_t smem = slots * tiles + 16;
-        if (smem > 48 * 1024)
-            CUDA_TRY(cudaFuncSetAttribute(scan_short_fused_kernel<NW, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        const unsigned blocks = (unsigned) std::min<uint64_t>((a.n + tiles - 1) / tiles, (uint64_t) sm_count() * 16);
-        scan_short_fused_kernel<NW, 16><<<blocks, kShortThreads, smem, st>>>(s->view, a, o);
-    } else {
-        constexpr int tiles = kShortThreads / 32;
-        const size_t smem = slots * tiles + 16;
-        if (smem > 48 * 1024)
-            CUDA_TRY(cudaFuncSetAttribute(scan_short_fused_kernel<NW, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        const unsigned blocks = (unsigned) std::min<uint64_t>((a.n + tiles - 1) / tiles, (uint64_t) sm_count() * 16);
-        scan_short_fused_kernel<NW, 32><<<blocks, kShortThreads, smem, st>>>(s->view, a, o);
-    }
+template <int NW, int TW, int MINB>
+static int launch_short_scan_v(stage_snapshot *s, const ScanArgs &a, const ShortScanOut &o, cudaStream_t st) {
+    constexpr int tiles = kShortThreads / TW;
+    const size_t smem = (size_t) ((s->view.max_leaf_rows + 7u) & ~7u) * 2 * tiles + 16;
+    if (smem > 48 * 1024)
+        CUDA_TRY(cudaFuncSetAttribute(scan_short_fused_kernel<NW, TW, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    const unsigned blocks = (unsigned) std::min<uint64_t>((a.n + tiles - 1) / tiles, (uint64_t) sm_count() * 16);
+    scan_short_fused_kernel<NW, TW, MINB><<<blocks, kShortThreads, smem, st>>>(s->view, a, o);
     LAUNCH_CHECK();
     return STAGE_OK;
+}
+template <int NW>
+static int launch_short_scan(stage_snapshot *s, const ScanArgs &a, uint8_t *payload_out, cudaStream_t st) {
+    const ShortScanOut o{payload_out, s->d_row_leaf};
+    // MINB = resident CTAs per SM the register allocation is held to (8 = all 2048 threads, 32 registers each)
+    static const int minb = getenv("STAGE_SHORT_MINB") ? atoi(getenv("STAGE_SHORT_MINB")) : 5;
+    if (a.out_stride <= 16) return minb >= 8 ? launch_short_scan_v<NW, 16, 8>(s, a, o, st) : launch_short_scan_v<NW, 16, 5>(s, a, o, st);
+    return minb >= 8 ? launch_short_scan_v<NW, 32, 8>(s, a, o, st) : launch_short_scan_v<NW, 32, 5>(s, a, o, st);
 }
 
 // plan (scan_plan_kernel) then payload gather; all pointers are device-visible. dst_base (compact layout): row offset of
@@ -2365,6 +2366,80 @@ extern "C" int stage_gpu_scan_project(stage_snapshot_t *s, const void *start_key
             CUDA_TRY(cudaMemcpyAsync(static_cast<uint8_t *>(col_out) + b * out_stride * col_len, s->sc_payload.p,
                                      rows * (uint64_t) col_len, cudaMemcpyDeviceToHost, s->stream));
             CUDA_TRY(cudaStreamSynchronize(s->stream));
+        }
+    }
+    return STAGE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// RunStockLevel's read side as one operator (tpcc_ops.cuh)
+// ------------------------------------------------------------------------------------------------
+extern "C" int stage_gpu_tpcc_stock_level(stage_snapshot_t *order_line, stage_snapshot_t *stock, const stage_stock_level_req_t *reqs,
+                                          uint64_t n, uint32_t read_ts, uint32_t *distinct_items, int flags) {
+    static_assert(sizeof(StockLevelReq) == sizeof(stage_stock_level_req_t), "request layout");
+    if (!order_line || !stock || (n && (!reqs || !distinct_items))) return STAGE_ERR_ARG;
+    if (!order_line->sealed || !stock->sealed) return STAGE_ERR_STATE;
+    stage_snapshot *ol = order_line;
+    if (ol->schema.key_size != 32 || stock->schema.key_size != 16 || (ol->schema.payload_size & 3u) || ol->schema.payload_size < 4 ||
+        (stock->schema.payload_size & 3u) || stock->schema.payload_size < 4 || ol->device != stock->device || ol->xormask || stock->xormask)
+        return STAGE_ERR_ARG;
+    if (n == 0) return STAGE_OK;
+    std::lock_guard<std::mutex> lock(ol->mu);
+    CUDA_TRY(cudaSetDevice(ol->device));
+    cudaStream_t st = ol->stream;
+    const bool dev = flags & STAGE_IO_DEVICE;
+    const uint64_t chunk = std::min<uint64_t>(n, 1ull << 16);           // transactions per pass: ~130 MB of scratch
+    const uint64_t cs = chunk * kStockLevelOrders;
+    int rc;
+    if ((rc = ol->sl_keys.ensure(cs * 32)) || (rc = ol->sl_sizes.ensure(cs * 4)) || (rc = ol->sl_counts.ensure(cs * 4)) ||
+        (rc = ol->sl_src.ensure(cs * kStockLevelScan * 4)) || (rc = ol->sl_skeys.ensure(cs * 16)) || (rc = ol->sl_psrc.ensure(cs * 4)))
+        return rc;
+    if (!dev && ((rc = ol->sl_req.ensure(chunk * sizeof(StockLevelReq))) || (rc = ol->sl_out.ensure(chunk * 4)))) return rc;
+    if (!ol->d_row_leaf && (rc = ensure_row_leaf(ol))) return rc;
+    if (dev) CUDA_TRY(cudaStreamSynchronize(stock->stream));            // the stock snapshot's own pending work (updates)
+    for (uint64_t b = 0; b < n; b += chunk) {
+        const uint64_t m = std::min(chunk, n - b), ms = m * kStockLevelOrders;
+        const StockLevelReq *d_req;
+        uint32_t *d_out;
+        if (dev) {
+            d_req = reinterpret_cast<const StockLevelReq *>(reqs) + b;
+            d_out = distinct_items + b;
+        } else {
+            CUDA_TRY(cudaMemcpyAsync(ol->sl_req.p, reqs + b, m * sizeof(StockLevelReq), cudaMemcpyHostToDevice, st));
+            d_req = static_cast<const StockLevelReq *>(ol->sl_req.p);
+            d_out = static_cast<uint32_t *>(ol->sl_out.p);
+        }
+        int64_t *d_keys = static_cast<int64_t *>(ol->sl_keys.p);
+        stock_level_keys_kernel<<<(unsigned) ((ms + 255) / 256), 256, 0, st>>>(d_req, m, d_keys, static_cast<uint32_t *>(ol->sl_sizes.p));
+        LAUNCH_CHECK();
+        ScanArgs a{};
+        a.start_keys = static_cast<const uint8_t *>(ol->sl_keys.p);
+        a.scan_sizes = static_cast<const uint32_t *>(ol->sl_sizes.p);
+        a.n = ms;
+        a.out_stride = kStockLevelScan;
+        a.read_ts = read_ts;
+        a.apply_visibility = 1;
+        a.row_counts = static_cast<uint32_t *>(ol->sl_counts.p);
+        a.src_row = static_cast<uint32_t *>(ol->sl_src.p);
+        a.stats = ol->d_stats;
+        if (short_scan_eligible(ol, a, nullptr)) rc = launch_short_scan<8>(ol, a, nullptr, st);
+        else rc = launch_scan_nw(ol, a, st);
+        if (rc) return rc;
+        int64_t *d_skeys = static_cast<int64_t *>(ol->sl_skeys.p);
+        stock_level_pick_kernel<<<(unsigned) ((ms + 255) / 256), 256, 0, st>>>(ol->view, d_keys, a.row_counts, a.src_row, ms, d_skeys);
+        LAUNCH_CHECK();
+        ProbeArgs pa{};
+        pa.keys = reinterpret_cast<const uint8_t *>(d_skeys);
+        pa.n = ms;
+        pa.read_ts = read_ts;
+        pa.src_row = static_cast<uint32_t *>(ol->sl_psrc.p);
+        if ((rc = launch_probe_nw(stock, st, pa))) return rc;
+        stock_level_count_kernel<<<(unsigned) ((m + 127) / 128), 128, 0, st>>>(d_req, m, d_skeys, pa.src_row, stock->d_payload,
+                                                                              stock->d_ver_payload, stock->schema.payload_size, d_out);
+        LAUNCH_CHECK();
+        if (!dev) {
+            CUDA_TRY(cudaMemcpyAsync(distinct_items + b, d_out, m * 4, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaStreamSynchronize(st));
         }
     }
     return STAGE_OK;

@@ -142,3 +142,63 @@ def test_quantity_aggregate_pushdown(tables):
     assert (a.found, a.min_value) == (0, 2**31 - 1)
     with pytest.raises(sg.StageError):
         s_snap.probe_aggregate_i32(keys, 1, tpcc.STOCK_PAYLOAD - 3, 15)                         # column runs past the row
+
+
+def _stock_level_by_the_three_steps(ol, stock, reqs, read_ts):
+    """RunStockLevel's reads done the reference's way on the checker's tables (tpcc_stock_level.cpp:92-190): 20 scans of
+    10 rows, first returned row of the order -> one stock probe -> S_QUANTITY < threshold -> distinct items."""
+    n = len(reqs)
+    w = np.repeat(reqs["w_id"], 20)
+    d = np.repeat(reqs["d_id"], 20)
+    o = (reqs["next_o_id"][:, None] - 20 + np.arange(20)[None, :]).ravel()
+    start = tpcc.order_line_key(w, d, o, np.full(len(w), 5, np.int64))
+    counts, keys, _, pay = ol.scan(start, 10, read_ts, 1)
+    k64 = keys.reshape(len(start), 10, 32).view(np.int64).reshape(len(start), 10, 4)
+    valid = np.arange(10)[None, :] < counts[:, None]
+    match = valid & (k64[..., 0] == w[:, None]) & (k64[..., 1] == d[:, None]) & (k64[..., 2] == o[:, None])
+    has = match.any(axis=1)
+    first = match.argmax(axis=1)
+    item = pay[..., 0:4].copy().view(np.int32).reshape(len(start), 10)[np.arange(len(start)), first].astype(np.int64)
+    probes = tpcc.stock_key(w[has], item[has])
+    f, _, _, p = stock.probe(probes, read_ts)
+    qty = p[:, 0:4].copy().view(np.int32).ravel()
+    thr = np.repeat(reqs["threshold"], 20)[has]
+    below = (f == 1) & (qty < thr)
+    txn = np.repeat(np.arange(n), 20)[has]
+    out = np.zeros(n, np.uint32)
+    for t in np.unique(txn[below]):
+        out[t] = len(np.unique(item[has][below & (txn == t)]))
+    return out
+
+
+def test_stock_level_operator(tables):
+    """stage_gpu_tpcc_stock_level: the whole read side of RunStockLevel in one call, counts only coming back — against the
+    three steps run through the checker. Requests include districts' last orders, order ids below the first order
+    (scans that find nothing of the order) and thresholds from "nothing" to "everything"."""
+    import torch
+    stock, ol, s_snap, o_snap, _, _ = tables
+    rng = np.random.default_rng(31)
+    n = 3000
+    reqs = np.zeros(n, sg.STOCK_LEVEL_REQ)
+    reqs["w_id"] = rng.integers(1, W + 1, n)
+    reqs["d_id"] = rng.integers(1, tpcc.DISTRICTS + 1, n)
+    reqs["next_o_id"] = rng.integers(21, tpcc.ORDERS + 2, n)
+    reqs["threshold"] = rng.integers(10, 21, n)
+    reqs["next_o_id"][:50] = tpcc.ORDERS + 1                    # the district's newest orders (what the driver asks for)
+    reqs["next_o_id"][50:60] = 5                                # order ids -15 .. 4: nothing (or little) to find
+    reqs["threshold"][60:80] = 1000                             # every probed item counts
+    reqs["threshold"][80:100] = 0                               # none does
+    for read_ts in (1, 9000, 40000):
+        want = _stock_level_by_the_three_steps(ol, stock, reqs, read_ts)
+        got = sg.tpcc_stock_level(o_snap, s_snap, reqs, read_ts)
+        assert np.array_equal(got, want), (read_ts, np.nonzero(got != want)[0][:10], got[:10], want[:10])
+        assert want[60:80].max() > 10 and not want[80:100].any()
+    # device-resident requests / results
+    d_req = torch.from_numpy(reqs.view(np.uint8).reshape(n, 32)).cuda()
+    d_out = torch.zeros(n, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    sg.tpcc_stock_level(o_snap, s_snap, d_req, 40000, out=d_out, n=n)
+    torch.cuda.synchronize()
+    assert np.array_equal(d_out.cpu().numpy().view(np.uint32), _stock_level_by_the_three_steps(ol, stock, reqs, 40000))
+    with pytest.raises(sg.StageError):
+        sg.tpcc_stock_level(s_snap, o_snap, reqs, 1)             # tables swapped: key sizes do not fit

@@ -489,6 +489,18 @@ def multi_gpu_parity(args, sg, torch, dist, dev, snap, rank, world, rows, split,
     want = exp_t[rank * NS:(rank + 1) * NS].cpu().numpy()
     hit = want[:, 0] == 1
     probes_ok = bool(np.array_equal(got[:, 0], want[:, 0]) and np.array_equal(got[hit, 1:], want[hit, 1:]) and image_ok[hit].all())
+    # ---- routed push-down: the projected column and the aggregate record against the same model -----------------
+    n_found_full = int(found.sum().item())
+    f2, t2, c2 = pp.probe_column(d_pk[0], n_probes, read_ts, 148, 4)
+    torch.cuda.synchronize()
+    dist.barrier()
+    f2h, c2h = f2[:NS].cpu().numpy(), c2[:NS].cpu().numpy()
+    pushdown_ok = bool(np.array_equal(f2h.astype(np.int64), want[:, 0]) and (c2h[hit] == want[hit, 3][:, None].astype(np.uint8)).all()
+                       and int(f2.sum().item()) == n_found_full)
+    agg = pp.probe_aggregate_i32(d_pk[0], n_probes, read_ts, 148, 0)
+    dist.barrier()
+    pushdown_ok = pushdown_ok and agg.found == n_found_full
+    probes_ok = probes_ok and pushdown_ok
     # ---- routed scans vs the owner's shard-local scans ----------------------------------------------------
     scans_ok, n_sc = True, 0
     if ps is not None:
@@ -524,7 +536,9 @@ def multi_gpu_parity(args, sg, torch, dist, dev, snap, rank, world, rows, split,
     dist.all_reduce(verdict, op=dist.ReduceOp.MIN)
     ok_p, ok_s = bool(verdict[0].item()), bool(verdict[1].item())
     return {"ok": ok_p and ok_s, "routed_probes_ok": ok_p, "routed_scans_ok": ok_s,
-            "checked": f"per rank: {NS} routed probes (found flag, commit id, row image) against the closed-form row function + "
+            "routed_pushdown_ok": bool(pushdown_ok),
+            "checked": f"per rank: {NS} routed probes (found flag, commit id, row image; also the projected column and the "
+                       f"aggregate's found count of the push-down forms) against the closed-form row function + "
                        f"update model evaluated by the owning rank; {n_sc} routed {S}-row MVCC scans (digest of keys, commit ids, "
                        "payload rows, order-sensitive) against the same scans run shard-locally by the owner of the start key; "
                        "verdicts all-reduced (MIN) over the ranks"}
@@ -800,6 +814,23 @@ def main():
                             "phase_ms_rank0": dict(zip(("post", "plan_incl_wait_for_posts", "rows", "wait_for_owners"),
                                                        [float(np.mean(c)) for c in zip(*phases)]))}
             probe["routed_scans"] = routed_scans
+        # ---- routed push-down: 4 bytes per probe / 24 bytes per batch back instead of the row ----
+        cms, _ = timed(lambda b: pp.probe_column(d_pk[b], n_probes, read_ts, 0, 4), args.steps)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(args.steps):
+            pp.probe_aggregate_i32(d_pk[args.warmup + i], n_probes, read_ts, 0, 15)
+        e1.record(stream)
+        barrier()
+        at = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(at, op=dist.ReduceOp.MAX)
+        probe["routed_pushdown"] = {
+            "column_4B": {"value": nprobe / (cms * 1e-3), "unit": "probes/s", "ms_per_step": cms / args.steps,
+                          "nvlink_bytes_per_probe": remote * (K_BYTES + 4 + 1 + 4 + 4)},
+            "aggregate_i32": {"value": nprobe / (float(at.item()) * 1e-3), "unit": "probes/s",
+                              "ms_per_step": float(at.item()) / args.steps, "bytes_returned_per_batch": 24,
+                              "note": "includes the 24-byte D2H read and its synchronisation per batch"}}
         # ---- the same number of probes with keys of the own shard (no exchange): the denominator of the routed leg ----
         lk = rank_to_key(rows * world, rank * rows + np.random.default_rng(7000 + rank).integers(0, rows, size=(4, n_probes)))
         d_lk = torch.from_numpy(lk.astype(np.uint32).view(np.int32)).to(dev)

@@ -342,6 +342,22 @@ int stage_gpu_exchange_wait(stage_exchange_t *x, void *cuda_stream);
  * owners' peer stores are line-aligned). Rows of missed probes keep their previous content. */
 int stage_gpu_exchange_results(stage_exchange_t *x, void **found, void **ts, void **payload, uint32_t *payload_stride);
 
+/* Routed push-down: the same post / serve / wait sequence, but the owner sends back only what the
+ * caller consumes instead of the payload row — what lifts the NVLink bound of the full-row form (4-16 B instead of
+ * 416-1004 B per probe). serve_project: payload bytes [col_off, col_off + col_len) of every found row (zeros for a miss)
+ * into the requester's slab, found / ts as usual; project_results returns the device pointers (column every
+ * *col_stride bytes = col_len rounded up to 4). serve_aggregate_i32: every owner reduces the little-endian int32
+ * column at col_off over each requester's probes (found, below threshold, MIN, MAX — RunStockLevel's S_QUANTITY test,
+ * benchmark/tpcc/tpcc_stock_level.cpp:167-190; CH-Q2*'s MIN(S_QUANTITY) over a supplier's (w, i) keys that span all
+ * warehouses, i.e. all shards, benchmark/tpcc/tpcc_new_order.cpp:808-866) and ships ONE 24-byte record per requester;
+ * aggregate_result (after the wait) combines the owners' records of this rank's batch into *out (host pointer). */
+int stage_gpu_exchange_serve_project(stage_exchange_t *x, stage_snapshot_t *shard, uint32_t read_ts, uint32_t col_off,
+                                     uint32_t col_len, int flags, void *cuda_stream);
+int stage_gpu_exchange_project_results(stage_exchange_t *x, void **found, void **ts, void **col, uint32_t *col_stride);
+int stage_gpu_exchange_serve_aggregate_i32(stage_exchange_t *x, stage_snapshot_t *shard, uint32_t read_ts, uint32_t col_off,
+                                           int32_t threshold, int flags, void *cuda_stream);
+int stage_gpu_exchange_aggregate_result(stage_exchange_t *x, stage_agg_i32_t *out, void *cuda_stream);
+
 /* Routed range scans over the same arenas ("scans run shard-local followed by a gather"). The scan
  * (start key, size) is posted to the owner of its START key; the owner plans it on its shard with the ordinary scan
  * plan kernels (same iterator quirks and MVCC filter as stage_gpu_scan_batch) and writes the row count, keys, commit

@@ -98,6 +98,10 @@ SYMBOLS = {
     "stage_gpu_exchange_arena": (_vp, [_vp]),
     "stage_gpu_exchange_post": (_i32, [_vp, _vp, _vp, _u64, _i32, _vp]),
     "stage_gpu_exchange_serve": (_i32, [_vp, _vp, _u32, _i32, _vp]),
+    "stage_gpu_exchange_serve_project": (_i32, [_vp, _vp, _u32, _u32, _u32, _i32, _vp]),
+    "stage_gpu_exchange_project_results": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_u32)]),
+    "stage_gpu_exchange_serve_aggregate_i32": (_i32, [_vp, _vp, _u32, _u32, C.c_int32, _i32, _vp]),
+    "stage_gpu_exchange_aggregate_result": (_i32, [_vp, C.POINTER(AggI32), _vp]),
     "stage_gpu_exchange_wait": (_i32, [_vp, _vp]),
     "stage_gpu_exchange_results": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_u32)]),
     "stage_gpu_exchange_create_scan": (_i32, [_u32, _u32, _u64, _u32, C.POINTER(Schema), C.POINTER(_vp)]),
@@ -553,6 +557,29 @@ class ProbeExchange:
 
     def serve(self, shard, read_ts, flags=0, cuda_stream=0):
         _check(lib().stage_gpu_exchange_serve(self.h, shard.h, read_ts, flags, _vp(int(cuda_stream))))
+
+    def serve_project(self, shard, read_ts, col_off, col_len, flags=0, cuda_stream=0):
+        _check(lib().stage_gpu_exchange_serve_project(self.h, shard.h, read_ts, col_off, col_len, flags, _vp(int(cuda_stream))))
+
+    def serve_aggregate_i32(self, shard, read_ts, col_off, threshold, flags=0, cuda_stream=0):
+        _check(lib().stage_gpu_exchange_serve_aggregate_i32(self.h, shard.h, read_ts, col_off, threshold, flags,
+                                                            _vp(int(cuda_stream))))
+
+    def aggregate_result(self, cuda_stream=0):
+        out = AggI32()
+        _check(lib().stage_gpu_exchange_aggregate_result(self.h, C.byref(out), _vp(int(cuda_stream))))
+        return out
+
+    def project_results_torch(self, n, col_len):
+        """(found u8[n], ts i32[n], col u8[n, col_len]) torch views of the result slab after serve_project."""
+        import torch
+        f, t, c, st = _vp(), _vp(), _vp(), _u32(0)
+        _check(lib().stage_gpu_exchange_project_results(self.h, C.byref(f), C.byref(t), C.byref(c), C.byref(st)))
+        dev = torch.device("cuda", torch.cuda.current_device())
+        found = torch.as_tensor(_DeviceView(int(f.value), (n,), "|u1", self), device=dev)
+        ts = torch.as_tensor(_DeviceView(int(t.value), (n,), "<i4", self), device=dev)
+        col = torch.as_tensor(_DeviceView(int(c.value), (n, int(st.value)), "|u1", self), device=dev)[:, :col_len]
+        return found, ts, col
 
     def post_scans(self, splitters, start_keys_dev, scan_sizes_dev, n, flags=0, cuda_stream=0):
         sp = None

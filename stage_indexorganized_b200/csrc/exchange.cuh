@@ -41,6 +41,7 @@ struct ExchangeLayout {
     uint64_t off_sizes;     // u32 [world][cap]       inbox: scan sizes (scan exchange only)
     uint64_t off_counts;    // u32 [cap]              result: rows returned per scan (scan exchange only)
     uint64_t off_keyout;    // u8  [cap*rows][kpad]   result: keys of the scanned rows (scan exchange only)
+    uint64_t off_agg;       // AggI32 [world]         result: every owner's partial aggregate of MY requests (probe exchange)
     uint64_t bytes;
     uint32_t cap, kpad, pstride;
     uint32_t rows;          // result rows per request: 1 for probes, the scan stride for scans
@@ -419,6 +420,88 @@ __global__ void __launch_bounds__(kGatherThreads) exchange_gather16_kernel(Excha
                     }
             }
         }
+    }
+}
+
+// ---- routed push-down ("return 4-16 B per probe instead of 416-1004 B, lifts the NVLink bound") ------
+// Column projection: after exchange_serve_kernel has located and MVCC-filtered every inbox entry, only payload bytes
+// [col_off, col_off + col_len) of each found row cross NVLink, into the requester's slab at stride col_stride (rows of
+// missed probes get zeros). One thread per inbox entry.
+__global__ void __launch_bounds__(256) exchange_cols_kernel(ExchangeView x, ServeArgs a, const uint8_t *payload, const uint8_t *ver_payload,
+                                                            uint32_t P, uint32_t col_off, uint32_t col_len, uint32_t col_stride) {
+    __shared__ uint32_t off[kMaxExchangeRanks + 1];
+    load_segments(x, off, 1);
+    const uint32_t total = off[kMaxExchangeRanks];
+    for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < total; g += gridDim.x * blockDim.x) {
+        const uint32_t row = a.src_row[g], d = a.dst_slot[g];
+        uint8_t *dst = x.arena[d >> kDstRankShift] + x.lay.off_payload + (uint64_t) (d & kDstIndexMask) * col_stride;
+        if (row == kNoRow) {
+            for (uint32_t b = 0; b < col_len; ++b) dst[b] = 0;
+            continue;
+        }
+        const uint8_t *base = (row & kVersionRowFlag) ? ver_payload : payload;
+        const uint8_t *src = base + (uint64_t) (row & ~kVersionRowFlag) * P + col_off;
+        if ((((uintptr_t) src | col_len | col_stride) & 3u) == 0)
+            for (uint32_t b = 0; b < col_len; b += 4) *reinterpret_cast<uint32_t *>(dst + b) = __ldg(reinterpret_cast<const uint32_t *>(src + b));
+        else
+            for (uint32_t b = 0; b < col_len; ++b) dst[b] = __ldg(src + b);
+    }
+}
+
+// Aggregate push-down: every owner reduces an int32 column over the entries of each requester's segment (count found,
+// count below the threshold, MIN, MAX — what RunStockLevel and CH-Q2* compute from their stock probes) into local
+// partials; exchange_agg_publish_kernel then stores ONE 24-byte record per requester over NVLink. blockIdx.y = segment.
+__global__ void __launch_bounds__(256) exchange_agg_kernel(ExchangeView x, ServeArgs a, const uint8_t *payload, const uint8_t *ver_payload,
+                                                           uint32_t P, uint32_t col_off, int threshold, AggI32 *partial /* [world] */) {
+    __shared__ uint32_t off[kMaxExchangeRanks + 1];
+    load_segments(x, off, 1);
+    const uint32_t sgm = blockIdx.y;
+    if (sgm >= x.world) return;
+    unsigned found = 0, below = 0;
+    int mn = 0x7FFFFFFF, mx = (int) 0x80000000;
+    for (uint32_t g = off[sgm] + blockIdx.x * blockDim.x + threadIdx.x; g < off[sgm + 1]; g += gridDim.x * blockDim.x) {
+        const uint32_t row = a.src_row[g];
+        if (row == kNoRow) continue;
+        const uint8_t *base = (row & kVersionRowFlag) ? ver_payload : payload;
+        const uint8_t *p = base + (uint64_t) (row & ~kVersionRowFlag) * P + col_off;
+        const int v = (int) ((uint32_t) __ldg(p) | ((uint32_t) __ldg(p + 1) << 8) | ((uint32_t) __ldg(p + 2) << 16) | ((uint32_t) __ldg(p + 3) << 24));
+        ++found;
+        below += v < threshold ? 1u : 0u;
+        mn = min(mn, v);
+        mx = max(mx, v);
+    }
+    found = __reduce_add_sync(0xFFFFFFFFu, found);
+    below = __reduce_add_sync(0xFFFFFFFFu, below);
+    mn = __reduce_min_sync(0xFFFFFFFFu, mn);
+    mx = __reduce_max_sync(0xFFFFFFFFu, mx);
+    if ((threadIdx.x & 31) == 0 && found) {
+        atomicAdd(&partial[sgm].found, (unsigned long long) found);
+        atomicAdd(&partial[sgm].below, (unsigned long long) below);
+        atomicMin(&partial[sgm].min_value, mn);
+        atomicMax(&partial[sgm].max_value, mx);
+    }
+}
+// partial[t] -> requester t's arena, slot [my rank]; the local partials are reset for the next batch
+__global__ void exchange_agg_publish_kernel(ExchangeView x, AggI32 *partial) {
+    const uint32_t t = threadIdx.x;
+    if (t < x.world) {
+        AggI32 *dst = reinterpret_cast<AggI32 *>(x.arena[t] + x.lay.off_agg) + x.rank;
+        *dst = partial[t];
+        partial[t] = AggI32{0ull, 0ull, 0x7FFFFFFF, (int) 0x80000000};
+    }
+}
+// requester side, after the wait: combine the owners' partials of my batch
+__global__ void exchange_agg_combine_kernel(ExchangeView x, AggI32 *out) {
+    if (threadIdx.x == 0) {
+        const AggI32 *p = reinterpret_cast<const AggI32 *>(x.arena[x.rank] + x.lay.off_agg);
+        AggI32 r{0ull, 0ull, 0x7FFFFFFF, (int) 0x80000000};
+        for (uint32_t o = 0; o < x.world; ++o) {
+            r.found += p[o].found;
+            r.below += p[o].below;
+            r.min_value = min(r.min_value, p[o].min_value);
+            r.max_value = max(r.max_value, p[o].max_value);
+        }
+        *out = r;
     }
 }
 

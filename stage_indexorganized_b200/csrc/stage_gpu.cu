@@ -1974,8 +1974,11 @@ static int launch_short_scan(stage_snapshot *s, const ScanArgs &a, uint8_t *payl
     const ShortScanOut o{payload_out, s->d_row_leaf};
     // MINB = resident CTAs per SM the register allocation is held to (8 = all 2048 threads, 32 registers each)
     static const int minb = getenv("STAGE_SHORT_MINB") ? atoi(getenv("STAGE_SHORT_MINB")) : 5;
-    if (a.out_stride <= 16) return minb >= 8 ? launch_short_scan_v<NW, 16, 8>(s, a, o, st) : launch_short_scan_v<NW, 16, 5>(s, a, o, st);
-    return minb >= 8 ? launch_short_scan_v<NW, 32, 8>(s, a, o, st) : launch_short_scan_v<NW, 32, 5>(s, a, o, st);
+    if (a.out_stride <= 16)
+        return minb >= 8 ? launch_short_scan_v<NW, 16, 8>(s, a, o, st)
+                         : minb <= 4 ? launch_short_scan_v<NW, 16, 4>(s, a, o, st) : launch_short_scan_v<NW, 16, 5>(s, a, o, st);
+    return minb >= 8 ? launch_short_scan_v<NW, 32, 8>(s, a, o, st)
+                     : minb <= 4 ? launch_short_scan_v<NW, 32, 4>(s, a, o, st) : launch_short_scan_v<NW, 32, 5>(s, a, o, st);
 }
 
 // plan (scan_plan_kernel) then payload gather; all pointers are device-visible. dst_base (compact layout): row offset of
@@ -2597,6 +2600,8 @@ struct stage_exchange {
     uint8_t *d_sc_keys = nullptr;
     uint32_t epoch_post = 0, epoch_serve = 0, epoch_wait = 0;
     bool attached = false;
+    AggI32 *d_agg = nullptr;                     // [kMaxExchangeRanks] partials per requester + [1] combined result
+    uint32_t col_stride = 0;                     // stride of the projected column in the result slab (last serve_project)
     // per-phase CUDA events: [0] before post, [1] after post, [2] after the serve search, [3] after the row gather,
     // [4] after the wait kernel
     cudaEvent_t tev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -2640,6 +2645,7 @@ static int exchange_create(uint32_t world, uint32_t rank, uint64_t capacity, uin
     l.off_sizes = off;   off = align_up(off + (scans ? (uint64_t) world * capacity * 4 : 0), 256);
     l.off_counts = off;  off = align_up(off + (scans ? capacity * 4 : 0), 256);
     l.off_keyout = off;  off = align_up(off + (scans ? capacity * rows * (uint64_t) l.kpad : 0), 256);
+    l.off_agg = off;     off = align_up(off + sizeof(AggI32) * kMaxExchangeRanks, 256);
     l.bytes = off;
     x->view.world = world;
     x->view.rank = rank;
@@ -2648,6 +2654,7 @@ static int exchange_create(uint32_t world, uint32_t rank, uint64_t capacity, uin
         cudaMalloc((void **) &x->d_local_cnt, 4 * kMaxExchangeRanks) != cudaSuccess ||
         cudaMemset(x->d_local_cnt, 0, 4 * kMaxExchangeRanks) != cudaSuccess ||
         cudaMalloc((void **) &x->d_err, 4) != cudaSuccess || cudaMemset(x->d_err, 0, 4) != cudaSuccess ||
+        cudaMalloc((void **) &x->d_agg, sizeof(AggI32) * (kMaxExchangeRanks + 1)) != cudaSuccess ||
         cudaMalloc((void **) &x->d_src_row, (uint64_t) world * capacity * rows * 4) != cudaSuccess ||
         cudaMalloc((void **) &x->d_dst_slot, (uint64_t) world * capacity * rows * 4) != cudaSuccess ||
         (scans && (cudaMalloc((void **) &x->d_sc_counts, (uint64_t) world * capacity * 4) != cudaSuccess ||
@@ -2656,6 +2663,11 @@ static int exchange_create(uint32_t world, uint32_t rank, uint64_t capacity, uin
                    cudaMalloc((void **) &x->d_sc_keys, (uint64_t) world * capacity * rows * l.kpad) != cudaSuccess))) {
         g_last_error = std::string("exchange allocation: ") + cudaGetErrorString(cudaGetLastError());
         return fail(STAGE_ERR_NOMEM);
+    }
+    {
+        AggI32 init[kMaxExchangeRanks + 1];
+        for (auto &a : init) a = AggI32{0ull, 0ull, 0x7FFFFFFF, (int) 0x80000000};
+        CUDA_TRY(cudaMemcpy(x->d_agg, init, sizeof(init), cudaMemcpyHostToDevice));
     }
     CUDA_TRY(cudaDeviceSynchronize());
     x->view.arena[rank] = x->arena;
@@ -2824,13 +2836,18 @@ static int exchange_move_rows(stage_exchange *x, stage_snapshot *s, const ServeA
     return rc;
 }
 
-extern "C" int stage_gpu_exchange_serve(stage_exchange_t *x, stage_snapshot_t *s, uint32_t read_ts, int flags,
-                                        void *cuda_stream) {
+// what the owner sends back for every probe of its inboxes: the payload row, one column of it, or nothing per probe
+// (one aggregate record per requester)
+enum { kServeRows = 0, kServeProject = 1, kServeAggregate = 2 };
+
+static int exchange_serve_common(stage_exchange_t *x, stage_snapshot_t *s, uint32_t read_ts, int flags, void *cuda_stream, int mode,
+                                 uint32_t col_off, uint32_t col_len, int32_t threshold) {
     if (!x || !s) return STAGE_ERR_ARG;
     if (!x->attached || !s->sealed) return STAGE_ERR_STATE;
     if (s->schema.key_size != x->schema.key_size || s->schema.payload_size != x->schema.payload_size || s->nw != x->nw ||
         s->device != x->device)
         return STAGE_ERR_ARG;
+    if (mode != kServeRows && (col_len == 0 || (uint64_t) col_off + col_len > s->schema.payload_size)) return STAGE_ERR_ARG;
     CUDA_TRY(cudaSetDevice(x->device));
     cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
     ServeArgs a{};
@@ -2852,13 +2869,56 @@ extern "C" int stage_gpu_exchange_serve(stage_exchange_t *x, stage_snapshot_t *s
     }
     if (rc) return rc;
     XCHG_MARK(x, 2, st);
-    rc = exchange_move_rows(x, s, a, st);
-    if (rc) return rc;
+    if (mode == kServeRows) {
+        if ((rc = exchange_move_rows(x, s, a, st))) return rc;
+    } else if (mode == kServeProject) {
+        x->col_stride = (col_len + 3u) & ~3u;
+        exchange_cols_kernel<<<sm_count() * 8, 256, 0, st>>>(x->view, a, s->d_payload, s->d_ver_payload, s->schema.payload_size, col_off,
+                                                            col_len, x->col_stride);
+        LAUNCH_CHECK();
+    } else {
+        exchange_agg_kernel<<<dim3((unsigned) sm_count(), x->view.world), 256, 0, st>>>(x->view, a, s->d_payload, s->d_ver_payload,
+                                                                                        s->schema.payload_size, col_off, threshold, x->d_agg);
+        LAUNCH_CHECK();
+        exchange_agg_publish_kernel<<<1, 32, 0, st>>>(x->view, x->d_agg);
+        LAUNCH_CHECK();
+    }
     if (a.device_sync) {
         exchange_serve_finish_kernel<<<1, 32, 0, st>>>(x->view, a.epoch);
         LAUNCH_CHECK();
     }
     XCHG_MARK(x, 3, st);
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_exchange_serve(stage_exchange_t *x, stage_snapshot_t *s, uint32_t read_ts, int flags, void *cuda_stream) {
+    return exchange_serve_common(x, s, read_ts, flags, cuda_stream, kServeRows, 0, 0, 0);
+}
+extern "C" int stage_gpu_exchange_serve_project(stage_exchange_t *x, stage_snapshot_t *s, uint32_t read_ts, uint32_t col_off,
+                                                uint32_t col_len, int flags, void *cuda_stream) {
+    return exchange_serve_common(x, s, read_ts, flags, cuda_stream, kServeProject, col_off, col_len, 0);
+}
+extern "C" int stage_gpu_exchange_serve_aggregate_i32(stage_exchange_t *x, stage_snapshot_t *s, uint32_t read_ts, uint32_t col_off,
+                                                      int32_t threshold, int flags, void *cuda_stream) {
+    return exchange_serve_common(x, s, read_ts, flags, cuda_stream, kServeAggregate, col_off, 4, threshold);
+}
+extern "C" int stage_gpu_exchange_project_results(stage_exchange_t *x, void **found, void **ts, void **col, uint32_t *col_stride) {
+    if (!x) return STAGE_ERR_ARG;
+    if (x->view.lay.rows != 1 || !x->col_stride) return STAGE_ERR_STATE;
+    if (found) *found = x->arena + x->view.lay.off_found;
+    if (ts) *ts = x->arena + x->view.lay.off_ts;
+    if (col) *col = x->arena + x->view.lay.off_payload;
+    if (col_stride) *col_stride = x->col_stride;
+    return STAGE_OK;
+}
+extern "C" int stage_gpu_exchange_aggregate_result(stage_exchange_t *x, stage_agg_i32_t *out, void *cuda_stream) {
+    if (!x || !out) return STAGE_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(x->device));
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    exchange_agg_combine_kernel<<<1, 32, 0, st>>>(x->view, x->d_agg + kMaxExchangeRanks);
+    LAUNCH_CHECK();
+    CUDA_TRY(cudaMemcpyAsync(out, x->d_agg + kMaxExchangeRanks, sizeof(AggI32), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
     return STAGE_OK;
 }
 
@@ -2992,7 +3052,7 @@ extern "C" int stage_gpu_exchange_destroy(stage_exchange_t *x) {
         if (x->tev[i]) cudaEventDestroy(x->tev[i]);
     for (uint32_t r = 0; r < x->view.world; ++r)
         if (x->opened[r] && x->view.arena[r]) cudaIpcCloseMemHandle(x->view.arena[r]);
-    void *ptrs[] = {x->arena, x->d_local_cnt, x->d_err, x->d_src_row, x->d_dst_slot,
+    void *ptrs[] = {x->arena, x->d_local_cnt, x->d_err, x->d_src_row, x->d_dst_slot, x->d_agg,
                     x->d_sc_counts, x->d_sc_ts, x->d_sc_src, x->d_sc_keys};
     for (void *p : ptrs)
         if (p) cudaFree(p);

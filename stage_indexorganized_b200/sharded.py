@@ -137,6 +137,34 @@ class PeerProbe:
             self._barrier()
         return self.x.results_torch(n)
 
+    def probe_column(self, keys_dev, n, read_ts, col_off, col_len):
+        """Routed probes with column push-down: only payload bytes [col_off, col_off + col_len) of every found row cross
+        NVLink. Returns (found, ts, col[n, col_len]) views of this rank's result slab."""
+        st = torch.cuda.current_stream().cuda_stream
+        self.x.post(self.splitters, keys_dev, n, self.flags, st)
+        if not self.flags:
+            self._barrier()
+        self.x.serve_project(self.shard, read_ts, col_off, col_len, self.flags, st)
+        if self.flags:
+            self.x.wait(st)
+        else:
+            self._barrier()
+        return self.x.project_results_torch(n, col_len)
+
+    def probe_aggregate_i32(self, keys_dev, n, read_ts, col_off, threshold):
+        """Routed probes reduced on the owners: AggI32(found, below, min_value, max_value) over this rank's batch; one
+        24-byte record per (owner, requester) pair crosses NVLink."""
+        st = torch.cuda.current_stream().cuda_stream
+        self.x.post(self.splitters, keys_dev, n, self.flags, st)
+        if not self.flags:
+            self._barrier()
+        self.x.serve_aggregate_i32(self.shard, read_ts, col_off, threshold, self.flags, st)
+        if self.flags:
+            self.x.wait(st)
+        else:
+            self._barrier()
+        return self.x.aggregate_result(st)
+
     def close(self):
         torch.cuda.synchronize()
         dist.barrier(self.group)     # nobody unmaps an arena a peer may still be writing

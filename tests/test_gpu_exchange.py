@@ -219,3 +219,92 @@ def test_scan_exchange_argument_errors():
     finally:
         x.close()
         s.close()
+
+
+def _run_world_pushdown(world, shards, split, key_batches, read_ts, K, P, flags, col_off, col_len, threshold):
+    """post / serve_project / wait and post / serve_aggregate_i32 / wait for every rank of a one-device world.
+    -> per rank: (found, ts, col[n, col_len]) and AggI32."""
+    cap = max(len(k) for k in key_batches)
+    xs = [sg.ProbeExchange(world, r, cap, K, P) for r in range(world)]
+    try:
+        arenas = [x.arena() for x in xs]
+        for x in xs:
+            x.attach_ptrs(arenas)
+        dkeys = [torch.from_numpy(np.ascontiguousarray(k)).cuda() for k in key_batches]
+        cols, aggs = [], []
+        for rep in range(2):
+            for r in range(world):
+                xs[r].post(split, dkeys[r], len(key_batches[r]), flags)
+            for r in range(world):
+                xs[r].serve_project(shards[r], read_ts, col_off, col_len, flags)
+            for r in range(world):
+                if flags:
+                    xs[r].wait()
+            torch.cuda.synchronize()
+            cols = []
+            for r in range(world):
+                assert xs[r].error() == 0
+                f, t, c = xs[r].project_results_torch(len(key_batches[r]), col_len)
+                cols.append((f.cpu().numpy().copy(), t.cpu().numpy().view(np.uint32).copy(), c.cpu().numpy().copy()))
+            for r in range(world):
+                xs[r].post(split, dkeys[r], len(key_batches[r]), flags)
+            for r in range(world):
+                xs[r].serve_aggregate_i32(shards[r], read_ts, col_off, threshold, flags)
+            for r in range(world):
+                if flags:
+                    xs[r].wait()
+            torch.cuda.synchronize()
+            aggs = [xs[r].aggregate_result() for r in range(world)]
+        return cols, aggs
+    finally:
+        for x in xs:
+            x.close()
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+@pytest.mark.parametrize("flags", [0, sg.XCHG_DEVICE_SYNC])
+def test_routed_pushdown_matches_unsharded_table(world, flags):
+    """Routed column projection and routed aggregate (SURVEY 8f f3 over the exchange): the column bytes and the
+    (found, below, min, max) record every requester gets equal what the unsharded table gives for its batch — version
+    rows served from the owners' chains included."""
+    N, P = 9000, 64
+    sg.init(0)
+    full = pyoracle.OracleTable(P)
+    full.load_ycsb_int(0, N)
+    rng = np.random.default_rng(30 + world)
+    upd = u32_keys(rng.integers(0, N, 2000))
+    assert full.commit_update_batch(upd, 10) == 2000
+    bounds = sharded.shard_bounds(N, world)
+    split = sharded.ycsb_splitters(N, world) if world > 1 else None
+    order = rank_to_key(N, np.arange(N)).astype(np.uint32)
+    rank_of = np.empty(N, np.int64)
+    rank_of[order.astype(np.int64)] = np.arange(N)
+    tables = []
+    for lo, hi in bounds:
+        t = pyoracle.OracleTable(P)
+        mine = order[lo:hi]
+        pay = np.empty((len(mine), P), np.uint8)
+        pay[:] = (mine & 0xFF).astype(np.uint8)[:, None]
+        t.insert(u32_keys(mine), pay, 0)
+        tables.append(t)
+    ends = np.array([hi for _, hi in bounds])
+    for i, k in enumerate(upd.view(np.uint32).ravel()):
+        own = int(np.searchsorted(ends, rank_of[int(k)], "right"))
+        assert tables[own].commit_update_batch(upd[i:i + 1], 10 + i) == 1
+    shards = [sg.Snapshot.from_tree(t.root, 4, P) for t in tables]
+    try:
+        batches = [u32_keys(rng.integers(0, N + 30, 2500 + 11 * r)) for r in range(world)]
+        for read_ts, col_off, col_len, thr in ((0, 0, 4, 0x30303030), (900, 3, 7, 0), (5000, 60, 4, 0x7F000000)):
+            cols, aggs = _run_world_pushdown(world, shards, split, batches, read_ts, 4, P, flags, col_off, col_len, thr)
+            for r in range(world):
+                wf, wt, _, wp = full.probe(batches[r], read_ts)
+                f, t, c = cols[r]
+                assert np.array_equal(f, wf) and np.array_equal(t[wf == 1], wt[wf == 1]), f"rank {r} found / stamps"
+                assert np.array_equal(c[wf == 1], wp[wf == 1][:, col_off:col_off + col_len]) and not c[wf == 0].any(), f"rank {r} column"
+                v = np.ascontiguousarray(wp[wf == 1][:, col_off:col_off + 4]).view("<i4").ravel()
+                a = aggs[r]
+                assert (a.found, a.below) == (int(wf.sum()), int((v < thr).sum())), f"rank {r} aggregate counts"
+                assert (a.min_value, a.max_value) == (int(v.min()), int(v.max())), f"rank {r} min / max"
+    finally:
+        for s in shards:
+            s.close()

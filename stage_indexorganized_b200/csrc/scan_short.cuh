@@ -197,42 +197,28 @@ __global__ void __launch_bounds__(kShortThreads, MINB) scan_short_fused_kernel(S
         if (tl == 0) a.row_counts[sid] = cnt;
         if (a.ts_out && (uint32_t) tl < cnt) a.ts_out[out_base + tl] = my_ts[tl];
         if (a.src_row && (uint32_t) tl < a.out_stride) a.src_row[out_base + tl] = (uint32_t) tl < cnt ? my_src[tl] : kNoRow;
-        // all loads of a phase are issued before its first store: a scan's keys (<= NW words per lane) and the payload
-        // words of up to 8 rows per lane are in flight together, so the emit costs ~2 memory latencies, not one per row
-        uint32_t kv[NW];
-        uint32_t *ko = reinterpret_cast<uint32_t *>(a.key_out) + out_base * NW;
+        // (holding a whole scan's key and payload words in registers before the first store was measured and is slower:
+        //  0.55 -> 0.62 ms per 10^6 scans at 48 registers, 0.53 -> 0.83 ms at 32 — profiles/README.md; the SM overlaps the
+        //  tiles' emit phases by itself)
         if (a.key_out) {
-#pragma unroll
-            for (int i = 0; i < NW; ++i) {
-                const uint32_t it = (uint32_t) tl + (uint32_t) i * TW;
-                if (it < cnt * NW) kv[i] = __ldg(v.level[0] + (uint64_t) my_src[it / NW] * NW + (it % NW));
+            uint32_t *ko = reinterpret_cast<uint32_t *>(a.key_out) + out_base * NW;
+            for (uint32_t it = tl; it < cnt * NW; it += TW) {
+                const uint32_t r = it / NW, w = it % NW;
+                ko[it] = bswap32(__ldg(v.level[0] + (uint64_t) my_src[r] * NW + w) ^ v.xormask);
             }
         }
-        constexpr int kRowsPerPhase = 8;
-        uint32_t *po = reinterpret_cast<uint32_t *>(o.payload_out) + out_base * wpr;
-        for (uint32_t r0 = 0; r0 < (o.payload_out ? cnt : 0u); r0 += kRowsPerPhase) {
-            for (uint32_t w0 = tl; w0 < wpr; w0 += TW) {
-                uint32_t val[kRowsPerPhase];
+        if (o.payload_out) {
+            uint32_t *po = reinterpret_cast<uint32_t *>(o.payload_out) + out_base * wpr;
+            for (uint32_t r0 = 0; r0 < cnt; r0 += 4) {
+                for (uint32_t w0 = tl; w0 < wpr; w0 += TW) {
+                    uint32_t val[4];
 #pragma unroll
-                for (int u = 0; u < kRowsPerPhase; ++u)
-                    if (r0 + u < cnt) val[u] = __ldg(pay32 + (uint64_t) my_src[r0 + u] * wpr + w0);
-                if (a.key_out && r0 == 0 && w0 == (uint32_t) tl) {
+                    for (int u = 0; u < 4; ++u)
+                        if (r0 + u < cnt) val[u] = __ldg(pay32 + (uint64_t) my_src[r0 + u] * wpr + w0);
 #pragma unroll
-                    for (int i = 0; i < NW; ++i) {
-                        const uint32_t it = (uint32_t) tl + (uint32_t) i * TW;
-                        if (it < cnt * NW) ko[it] = bswap32(kv[i] ^ v.xormask);
-                    }
+                    for (int u = 0; u < 4; ++u)
+                        if (r0 + u < cnt) po[(uint64_t) (r0 + u) * wpr + w0] = val[u];
                 }
-#pragma unroll
-                for (int u = 0; u < kRowsPerPhase; ++u)
-                    if (r0 + u < cnt) po[(uint64_t) (r0 + u) * wpr + w0] = val[u];
-            }
-        }
-        if (a.key_out && (!o.payload_out || cnt == 0 || (uint32_t) tl >= wpr)) {      // lanes the payload loop never entered
-#pragma unroll
-            for (int i = 0; i < NW; ++i) {
-                const uint32_t it = (uint32_t) tl + (uint32_t) i * TW;
-                if (it < cnt * NW) ko[it] = bswap32(kv[i] ^ v.xormask);
             }
         }
         __syncwarp(tmask);                                        // my_src / my_ts are reused by the next scan

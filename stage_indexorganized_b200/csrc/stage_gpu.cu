@@ -1973,7 +1973,7 @@ template <int NW>
 static int launch_short_scan(stage_snapshot *s, const ScanArgs &a, uint8_t *payload_out, cudaStream_t st) {
     const ShortScanOut o{payload_out, s->d_row_leaf};
     // MINB = resident CTAs per SM the register allocation is held to (8 = all 2048 threads, 32 registers each)
-    static const int minb = getenv("STAGE_SHORT_MINB") ? atoi(getenv("STAGE_SHORT_MINB")) : 5;
+    static const int minb = getenv("STAGE_SHORT_MINB") ? atoi(getenv("STAGE_SHORT_MINB")) : 8;
     if (a.out_stride <= 16)
         return minb >= 8 ? launch_short_scan_v<NW, 16, 8>(s, a, o, st)
                          : minb <= 4 ? launch_short_scan_v<NW, 16, 4>(s, a, o, st) : launch_short_scan_v<NW, 16, 5>(s, a, o, st);

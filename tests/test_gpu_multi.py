@@ -45,16 +45,6 @@ def _worker(rank, world, port, ret):
             ok = ok and np.array_equal(p[hit, 0], (keys_np[hit] & 0xFF).astype(np.uint8))
             ok = ok and np.array_equal(p[hit, P - 1], (keys_np[hit] & 0xFF).astype(np.uint8))
             ok = ok and bool((p[hit] == p[hit, :1]).all())
-            # routed push-down over real NVLink: 4 bytes per probe back, then one 24-byte record per (owner, requester)
-            f3, _, c3 = pp.probe_column(keys, n, 1, P - 4, 4)
-            torch.cuda.synchronize()
-            c3 = c3.cpu().numpy()
-            ok = ok and np.array_equal(f3.cpu().numpy(), want_f) and bool((c3[hit] == (keys_np[hit] & 0xFF).astype(np.uint8)[:, None]).all())
-            ok = ok and not c3[~hit].any()
-            agg = pp.probe_aggregate_i32(keys, n, 1, 0, 0x40404040)
-            v = ((keys_np[hit] & 0xFF).astype(np.int64) * 0x01010101).astype(np.uint32).view(np.int32)
-            ok = ok and (agg.found, agg.below, agg.min_value, agg.max_value) == (int(hit.sum()), int((v < 0x40404040).sum()),
-                                                                                  int(v.min()), int(v.max()))
             # against the NCCL all-to-all form of the same probe
             owner = torch.empty((n,), dtype=torch.int32, device="cuda")
             sg.route_device(keys, n, split, owner, 4, torch.cuda.current_stream().cuda_stream)
@@ -70,6 +60,16 @@ def _worker(rank, world, port, ret):
 
             f2, t2, p2 = sharded.routed_probe(keys, owner, local_probe, P)
             ok = ok and bool(torch.equal(found, f2)) and bool(torch.equal(pay[found.bool()], p2[found.bool()]))
+            # routed push-down over real NVLink (last: it reuses the result slab that `pay` is a view of): 4 bytes per probe back, then one 24-byte record per (owner, requester)
+            f3, _, c3 = pp.probe_column(keys, n, 1, P - 4, 4)
+            torch.cuda.synchronize()
+            c3 = c3.cpu().numpy()
+            ok = ok and np.array_equal(f3.cpu().numpy(), want_f) and bool((c3[hit] == (keys_np[hit] & 0xFF).astype(np.uint8)[:, None]).all())
+            ok = ok and not c3[~hit].any()
+            agg = pp.probe_aggregate_i32(keys, n, 1, 0, 0x40404040)
+            v = ((keys_np[hit] & 0xFF).astype(np.int64) * 0x01010101).astype(np.uint32).view(np.int32)
+            ok = ok and (agg.found, agg.below, agg.min_value, agg.max_value) == (int(hit.sum()), int((v < 0x40404040).sum()),
+                                                                                  int(v.min()), int(v.max()))
         pp.close()
     shard.close()
     ret[rank] = bool(ok)

@@ -197,6 +197,34 @@ class RefTable(_Table):
         return C.cast(getattr(self._lib, "ref_resolve_undo"), _vp).value, int(self.h)
 
 
+class Writer:
+    """A thread running real update transactions on a RefTable (ref_update_loop: LeafNode::Update + the commit install,
+    in the reference's order) while the caller takes snapshots. ctypes releases the GIL, so it truly runs beside the
+    caller. stop() -> (tried, committed u8[n])."""
+
+    def __init__(self, table, keys_u32, first_cid):
+        import threading
+        self.keys = np.ascontiguousarray(keys_u32, np.uint32)
+        self.first_cid = first_cid
+        self.committed = np.zeros(len(self.keys), np.uint8)
+        self._stop = C.c_int(0)
+        self.tried = 0
+        f = table._fn("update_loop", C.c_uint64, [_vp, _vp, _u32, _u64, _u32, _vp, _vp])
+
+        def run():
+            self.tried = f(table.h, _ptr(self.keys), 4, len(self.keys), first_cid, C.byref(self._stop), _ptr(self.committed))
+        self._t = threading.Thread(target=run)
+        self._t.start()
+
+    def alive(self):
+        return self._t.is_alive()
+
+    def stop(self):
+        self._stop.value = 1
+        self._t.join()
+        return int(self.tried), self.committed
+
+
 def walk_tree(root):
     """(leaf_ptrs[L] u64, sep_ptrs[L-1] u64, sep_lens[L-1] u32) of a tree in the reference node layout."""
     if OracleTable._lib is None:

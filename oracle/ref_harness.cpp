@@ -216,6 +216,61 @@ int ref_begin_update(ref_table *t, const void *key, uint32_t key_size, const voi
                                     static_cast<const char *>(new_payload), columns, &meta, false, txn_id);
     return rc.IsOk() ? 0 : (int) rc.rc;
 }
+// One whole update transaction on the record of `key`, with the reference's own steps and their order: LeafNode::Update
+// (control bit set by compare-and-swap, old record parked in the EphemeralPool, next_ptr -> that copy, payload overwritten
+// in place, b_tree.cpp:1061-1163), then the commit install of SSNTransactionManager::CommitTransaction
+// (transaction_manager.cpp:610-676): the parked copy becomes a TupleHeader slot (begin = old commit stamp, commit =
+// committer stamp, next = the chain the copy saved), the record's meta word is finalized by compare-and-swap and THEN
+// next_ptr is swung to the new header by a second compare-and-swap. Used by the tests that snapshot a tree while
+// writers are really running. Returns 0, or the ReturnCode byte of a refused update.
+int ref_update_txn(ref_table *t, const void *key, uint32_t key_size, const void *new_payload, uint32_t commit_id) {
+    std::vector<oid_t> columns{1};
+    RecordMeta rm;
+    ReturnCode rc = t->tree->Update(static_cast<const char *>(key), (uint16_t) key_size, static_cast<const char *>(new_payload),
+                                    columns, &rm, false, commit_id);
+    if (!rc.IsOk()) return (int) rc.rc ? (int) rc.rc : -1;
+    RecordMetadata *meta_ptr = reinterpret_cast<RecordMetadata *>(rm.GetMetaData().GetLocationPtr()->record_meta_ptr);
+    const uint64_t copy_location = meta_ptr->GetNextPointer();
+    const uint32_t klen = meta_ptr->GetKeyLength();
+    char *mem = new char[sizeof(TupleHeader) + klen + t->payload_size];
+    t->chain_allocs.push_back(mem);
+    TupleHeader *hd = new (mem) TupleHeader();
+    char *slot = mem + sizeof(TupleHeader);
+    hd->init(hd, reinterpret_cast<uint64_t>(slot), (oid_t) t->chain_allocs.size());
+    memcpy(slot, reinterpret_cast<const char *>(copy_location), klen + t->payload_size);
+    hd->SetBeginId(meta_ptr->GetTxnCommitId());
+    hd->SetCommitId(commit_id);
+    hd->SetNextHeaderPointer(t->undo_pool->GetNext(copy_location));
+    RecordMetadata finl = *meta_ptr, fresh = finl;
+    fresh.FinalizeForUpdate(commit_id);
+    fresh.SetNextPointer(reinterpret_cast<uint64_t>(hd));
+    if (!__atomic_compare_exchange_n(&meta_ptr->meta, &finl.meta, fresh.meta, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) return -2;
+    if (!__atomic_compare_exchange_n(&meta_ptr->next_ptr, &finl.next_ptr, fresh.next_ptr, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) return -3;
+    return 0;
+}
+
+// A writer: update transactions over keys[0..n) (YCSB rows: payload = (uint8) rowid, column [100,200) <- (uint8) commit id,
+// commit ids first_cid + i) until *stop becomes non-zero. committed[i] = 1 for the transactions that went through (an
+// update whose new column equals the old one is refused as "not needed", b_tree.cpp:1087-1089). Returns how many were tried.
+uint64_t ref_update_loop(ref_table *t, const void *keys, uint32_t key_size, uint64_t n, uint32_t first_cid, volatile int *stop,
+                         uint8_t *committed) {
+    const char *k = static_cast<const char *>(keys);
+    const uint32_t P = t->payload_size;
+    std::vector<char> pay(P);
+    uint64_t i = 0;
+    for (; i < n && !*stop; ++i) {
+        uint32_t rowid;
+        memcpy(&rowid, k + i * key_size, 4);
+        memset(pay.data(), (int) (rowid & 0xFF), P);
+        uint32_t lo = P > 100 ? 100 : 0, hi = P > 200 ? 200 : P;
+        memset(pay.data() + lo, (int) ((first_cid + i) & 0xFF), hi - lo);
+        const int rc = ref_update_txn(t, k + i * key_size, key_size, pay.data(), first_cid + (uint32_t) i);
+        if (committed) committed[i] = rc == 0;
+        if (rc != 0 && rc != (int) ReturnCode::RetNotNeededUpdate) break;
+    }
+    return i;
+}
+
 // stage_undo_resolver_t over the table's EphemeralPool (what BTree::Read does, b_tree.cpp:2087-2103); ctx = ref_table*
 int ref_resolve_undo(void *ctx, uint64_t copy_location, uint64_t *next_tuple_header, const void **old_record) {
     ref_table *t = static_cast<ref_table *>(ctx);

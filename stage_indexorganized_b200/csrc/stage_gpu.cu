@@ -15,6 +15,7 @@
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
+#include <deque>
 #include <mutex>
 #include <thread>
 #include <string>
@@ -437,7 +438,10 @@ struct LeafExtras {
     const uint32_t *heads = nullptr;           // [record_count] 1-based version index per slot (0 = none)
     const InflightPatch *patches = nullptr;    // in-flight records of this leaf, resolved by the caller
     uint32_t n_patches = 0;
+    const uint64_t *expect_fp = nullptr;       // live trees: fingerprint of header + record metadata seen by the discovery pass
 };
+static uint64_t leaf_fingerprint(const uint8_t *leaf, const uint8_t *fence, uint32_t K, uint32_t leaf_size);
+constexpr int kStageRetry = -100;              // internal: the leaf moved between the discovery pass and its copy
 
 // Copy one leaf image into its pinned staging slot, count its visible records and replace the host TupleHeader
 // pointers in RecordMetadata.next_ptr by version indices. Thread-safe: touches only `dst`.
@@ -451,6 +455,13 @@ static int stage_copy_leaf(const stage_snapshot *s, uint8_t *dst, const uint8_t 
     const uint32_t count = status_record_count(status);
     if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize > ls) return STAGE_ERR_LAYOUT;
     memcpy(dst, leaf, ls);
+    if (ex.expect_fp) {
+        // writers are running: what was copied (and what the leaf holds right after the copy) must still be what the
+        // discovery pass saw — every begin / commit / abort of an update rewrites a metadata word or the chain pointer
+        // (b_tree.cpp:1122-1159, transaction_manager.cpp:640-664). Otherwise the caller re-discovers and re-copies.
+        if (leaf_fingerprint(dst, nullptr, 0, ls) != *ex.expect_fp || leaf_fingerprint(leaf, nullptr, 0, ls) != *ex.expect_fp)
+            return kStageRetry;
+    }
     for (uint32_t p = 0; p < ex.n_patches; ++p) {
         const InflightPatch &ip = ex.patches[p];
         if (ip.slot >= count) return STAGE_ERR_LAYOUT;
@@ -495,8 +506,12 @@ static unsigned staging_threads() {
 // Stage n leaves (tree order). The 64 KiB image copies — the bulk of the host work — run on a few threads, one
 // staging chunk at a time; bookkeeping (row offsets, fences) and the chunk flush stay on the calling thread.
 // get(i, &leaf, &fence, &extras) supplies leaf i.
-template <class Get>
-static int stage_leaves(stage_snapshot *s, uint64_t n, Get get) {
+struct NoRedo {
+    int operator()(uint64_t) const { return STAGE_ERR_NOT_QUIESCED; }
+};
+// redo(i): re-run the discovery pass for leaf i (serial, on the calling thread) after its copy found the leaf changed.
+template <class Get, class Redo = NoRedo>
+static int stage_leaves(stage_snapshot *s, uint64_t n, Get get, Redo redo = Redo()) {
     const uint32_t ls = s->schema.leaf_node_size;
     std::vector<uint32_t> vis, cnt;
     std::vector<int> rcs;
@@ -523,6 +538,15 @@ static int stage_leaves(stage_snapshot *s, uint64_t n, Get get) {
             for (auto &x : th) x.join();
         }
         for (uint32_t j = 0; j < m; ++j) {
+            for (int attempt = 0; rcs[j] == kStageRetry; ++attempt) {      // a writer touched the leaf under the copy
+                if (attempt >= 64) return STAGE_ERR_NOT_QUIESCED;
+                int rr = redo(base + j);
+                if (rr) return rr;
+                const uint8_t *leaf2, *fence2;
+                LeafExtras ex2;
+                get(base + j, &leaf2, &fence2, &ex2);
+                rcs[j] = stage_copy_leaf(s, slot0 + (size_t) j * ls, leaf2, ex2, &vis[j], &cnt[j]);
+            }
             if (rcs[j]) return rcs[j];
             const uint8_t *leaf, *fence;
             LeafExtras ex;
@@ -807,6 +831,111 @@ static uint64_t leaf_fingerprint(const uint8_t *leaf, const uint8_t *fence, uint
     return h;
 }
 
+// Discovery pass over the leaves that will be staged (serial, metadata only): the version chains hanging off the records,
+// the in-flight records resolved through the caller's undo pool — their old payload is COPIED here, the pool slot may be
+// recycled before the copy pass runs — and, for live trees, the fingerprint of header + record metadata that the copy
+// pass validates against (stage_copy_leaf). discover() can be repeated for one leaf: its blocks are appended again and
+// the previous ones are simply no longer referenced.
+struct LeafDiscovery {
+    const stage_schema_t *schema = nullptr;
+    stage_undo_resolver_t resolve = nullptr;
+    void *ctx = nullptr;
+    ChainStager cs;
+    std::vector<uint32_t> heads_flat;
+    std::vector<int64_t> heads_at;                            // per leaf: offset into heads_flat, -1 = no chain
+    std::vector<InflightPatch> patches;                       // blocks per leaf, slot order
+    std::vector<std::pair<size_t, uint32_t>> patch_at;
+    std::vector<uint32_t> dropped;                            // in-flight rows without an undo copy
+    std::vector<uint64_t> fp;
+    std::deque<std::vector<uint8_t>> undo_copies;             // stable addresses
+    std::vector<uint32_t> heads;                              // scratch
+    std::vector<InflightPatch> tmp;
+
+    void init(size_t n) {
+        heads_at.assign(n, -1);
+        patch_at.assign(n, {0, 0});
+        dropped.assign(n, 0);
+        fp.assign(resolve ? n : 0, 0);
+    }
+    int discover(size_t idx, const uint8_t *leaf) {
+        const uint32_t ls = schema->leaf_node_size, P = schema->payload_size;
+        for (int spin = 0;; ++spin) {
+            if (spin > 100000) return STAGE_ERR_NOT_QUIESCED;
+            const uint64_t f = resolve ? leaf_fingerprint(leaf, nullptr, 0, ls) : 0;
+            uint64_t status;
+            memcpy(&status, leaf + kOffStatus, 8);
+            const uint32_t count = status_record_count(status);
+            if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize > ls) return STAGE_ERR_LAYOUT;
+            heads.assign(count, 0);
+            tmp.clear();
+            bool any = false, moving = false;
+            uint32_t drop = 0;
+            for (uint32_t i = 0; i < count && !moving; ++i) {
+                uint64_t m, nx;
+                memcpy(&m, leaf + kOffMeta + (size_t) i * kMetaSize, 8);
+                memcpy(&nx, leaf + kOffMeta + (size_t) i * kMetaSize + kMetaNextPtr, 8);
+                if (!meta_visible(m)) continue;
+                if ((m & kMetaControl) && !resolve) return STAGE_ERR_NOT_QUIESCED;   // next_ptr is an undo copy, not a chain
+                const bool has_next = nx != 0 && nx != UINT64_MAX;
+                if (m & kMetaControl) {
+                    // in flight: the reader's version is the undo copy [key][payload]; its header saved the chain
+                    uint64_t saved_next = 0;
+                    const void *old_rec = nullptr;
+                    const bool have = has_next && resolve(ctx, nx, &saved_next, &old_rec) == 1 && old_rec;
+                    const uint8_t *pay = nullptr;
+                    if (!have && spin < 2000) {
+                        // control bit set but no undo copy behind next_ptr: either an insert in flight (stays like this
+                        // until its transaction ends) or an update caught between its two compare-and-swaps
+                        // (LeafNode::Update, b_tree.cpp:1122-1148: the copy is published a moment later). Look again.
+                        moving = true;
+                        continue;
+                    }
+                    if (have) {
+                        undo_copies.emplace_back(static_cast<const uint8_t *>(old_rec) + meta_key_len(m),
+                                                 static_cast<const uint8_t *>(old_rec) + meta_key_len(m) + P);
+                        pay = undo_copies.back().data();
+                    } else {
+                        ++drop;
+                    }
+                    tmp.push_back({i, pay});
+                    nx = have ? saved_next : 0;
+                } else if (resolve && has_next) {
+                    // committed record of a live tree: between the two compare-and-swaps of CommitTransaction
+                    // (transaction_manager.cpp:651-664) next_ptr still names the undo copy, not a TupleHeader
+                    uint64_t sn = 0;
+                    const void *rec = nullptr;
+                    if (resolve(ctx, nx, &sn, &rec) == 1) moving = true;
+                }
+                if (moving || nx == 0 || nx == UINT64_MAX) continue;
+                heads[i] = cs.add_chain(nx);
+                any = true;
+            }
+            if (moving || (resolve && leaf_fingerprint(leaf, nullptr, 0, ls) != f)) {            // re-read the leaf
+                if (spin > 16) std::this_thread::yield();
+                continue;
+            }
+            if (resolve) fp[idx] = f;
+            heads_at[idx] = -1;
+            if (any) {
+                heads_at[idx] = (int64_t) heads_flat.size();
+                heads_flat.insert(heads_flat.end(), heads.begin(), heads.end());
+            }
+            patch_at[idx] = {patches.size(), (uint32_t) tmp.size()};
+            patches.insert(patches.end(), tmp.begin(), tmp.end());
+            dropped[idx] = drop;
+            return STAGE_OK;
+        }
+    }
+    void fill(size_t idx, LeafExtras *ex) const {
+        ex->heads = heads_at[idx] >= 0 ? heads_flat.data() + heads_at[idx] : nullptr;
+        if (patch_at[idx].second) {
+            ex->patches = patches.data() + patch_at[idx].first;
+            ex->n_patches = patch_at[idx].second;
+        }
+        ex->expect_fp = resolve ? &fp[idx] : nullptr;
+    }
+};
+
 static double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -830,59 +959,25 @@ static int from_tree_impl(const void *root, const stage_schema_t *schema, stage_
     PHASE("alloc");
 
     const uint32_t K = schema->key_size, P = schema->payload_size;
-    ChainStager cs;
-    std::vector<uint32_t> heads;
+    LeafDiscovery d;
+    d.schema = schema;
+    d.resolve = resolve;
+    d.ctx = resolve_ctx;
+    d.init(w.leaves.size());
+    ChainStager &cs = d.cs;
     std::vector<stage_version_t> &vers = cs.vers;
-    // pass 1 (serial, metadata only): version indices in leaf / slot order
-    std::vector<uint32_t> heads_flat;                 // chain heads of the leaves that have any
-    std::vector<int64_t> heads_at(w.leaves.size(), -1);
-    std::vector<InflightPatch> patches;               // in-flight records, in leaf / slot order
-    std::vector<std::pair<size_t, uint32_t>> patch_at(resolve ? w.leaves.size() : 0, {0, 0});
-    for (size_t li = 0; li < w.leaves.size() && !rc; ++li) {
-        const uint8_t *leaf = w.leaves[li];
-        uint64_t status;
-        memcpy(&status, leaf + kOffStatus, 8);
-        const uint32_t count = status_record_count(status);
-        if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize > schema->leaf_node_size) { rc = STAGE_ERR_LAYOUT; break; }
-        heads.assign(count, 0);
-        bool any = false;
-        for (uint32_t i = 0; i < count; ++i) {
-            uint64_t m, nx;
-            memcpy(&m, leaf + kOffMeta + (size_t) i * kMetaSize, 8);
-            memcpy(&nx, leaf + kOffMeta + (size_t) i * kMetaSize + kMetaNextPtr, 8);
-            if (!meta_visible(m)) continue;
-            if ((m & kMetaControl) && !resolve) { rc = STAGE_ERR_NOT_QUIESCED; break; }   // next_ptr is an undo copy, not a chain
-            if (m & kMetaControl) {
-                // in flight: the reader's version is the undo copy [key][payload]; its header saved the chain
-                uint64_t saved_next = 0;
-                const void *old_rec = nullptr;
-                const bool have = nx != 0 && nx != UINT64_MAX && resolve(resolve_ctx, nx, &saved_next, &old_rec) == 1 && old_rec;
-                if (patch_at[li].second == 0) patch_at[li].first = patches.size();
-                patch_at[li].second++;
-                patches.push_back({i, have ? static_cast<const uint8_t *>(old_rec) + meta_key_len(m) : nullptr});
-                nx = have ? saved_next : 0;
-            }
-            if (nx == 0 || nx == UINT64_MAX) continue;
-            heads[i] = cs.add_chain(nx);
-            any = true;
-        }
-        if (any) {
-            heads_at[li] = (int64_t) heads_flat.size();
-            heads_flat.insert(heads_flat.end(), heads.begin(), heads.end());
-        }
-    }
+    // pass 1 (serial, metadata only): version indices in leaf / slot order, in-flight records
+    for (size_t li = 0; li < w.leaves.size() && !rc; ++li) rc = d.discover(li, w.leaves[li]);
     PHASE("chain discovery");
-    // pass 2: leaf images, copied by the staging threads
+    // pass 2: leaf images, copied by the staging threads (live trees: validated against pass 1, re-discovered on a miss)
     if (!rc)
-        rc = stage_leaves(s, w.leaves.size(), [&](uint64_t li, const uint8_t **leaf, const uint8_t **fence, LeafExtras *ex) {
-            *leaf = w.leaves[li];
-            *fence = w.fences[li];
-            ex->heads = heads_at[li] >= 0 ? heads_flat.data() + heads_at[li] : nullptr;
-            if (resolve && patch_at[li].second) {
-                ex->patches = patches.data() + patch_at[li].first;
-                ex->n_patches = patch_at[li].second;
-            }
-        });
+        rc = stage_leaves(s, w.leaves.size(),
+                          [&](uint64_t li, const uint8_t **leaf, const uint8_t **fence, LeafExtras *ex) {
+                              *leaf = w.leaves[li];
+                              *fence = w.fences[li];
+                              d.fill(li, ex);
+                          },
+                          [&](uint64_t li) { return d.discover(li, w.leaves[li]); });
     PHASE("stage + transform");
     if (!rc && !vers.empty()) {
         // retired rows [key][payload] -> dense version rows, copied by the staging threads
@@ -981,47 +1076,15 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
         if (src_leaf[j] == kNoLeaf) changed.push_back((uint32_t) j);
     rc = STAGE_OK;
     // 1b. changed leaves: version chains (new indices follow the previous table) and in-flight records
-    ChainStager cs;
+    LeafDiscovery d;
+    d.schema = schema;
+    d.resolve = resolve;
+    d.ctx = resolve_ctx;
+    d.init(changed.size());
+    ChainStager &cs = d.cs;
     cs.base = (uint32_t) old->n_versions;
-    std::vector<uint32_t> heads_flat;
-    std::vector<int64_t> heads_at(changed.size(), -1);
-    std::vector<uint32_t> heads;
-    std::vector<InflightPatch> patches;
-    std::vector<std::pair<size_t, uint32_t>> patch_at(changed.size(), {0, 0});
-    std::vector<uint32_t> dropped(changed.size(), 0);            // in-flight rows without an undo copy
-    for (size_t c = 0; c < changed.size() && !rc; ++c) {
-        const uint8_t *leaf = w.leaves[changed[c]];
-        uint64_t status;
-        memcpy(&status, leaf + kOffStatus, 8);
-        const uint32_t count = status_record_count(status);
-        if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize > ls) { rc = STAGE_ERR_LAYOUT; break; }
-        heads.assign(count, 0);
-        bool any = false;
-        for (uint32_t i = 0; i < count; ++i) {
-            uint64_t m, nx;
-            memcpy(&m, leaf + kOffMeta + (size_t) i * kMetaSize, 8);
-            memcpy(&nx, leaf + kOffMeta + (size_t) i * kMetaSize + kMetaNextPtr, 8);
-            if (!meta_visible(m)) continue;
-            if ((m & kMetaControl) && !resolve) { rc = STAGE_ERR_NOT_QUIESCED; break; }   // next_ptr is an undo copy
-            if (m & kMetaControl) {                               // in flight: stage what BTree::Read serves (f2)
-                uint64_t saved_next = 0;
-                const void *old_rec = nullptr;
-                const bool have = nx != 0 && nx != UINT64_MAX && resolve(resolve_ctx, nx, &saved_next, &old_rec) == 1 && old_rec;
-                if (patch_at[c].second == 0) patch_at[c].first = patches.size();
-                patch_at[c].second++;
-                patches.push_back({i, have ? static_cast<const uint8_t *>(old_rec) + meta_key_len(m) : nullptr});
-                if (!have) dropped[c]++;
-                nx = have ? saved_next : 0;
-            }
-            if (nx == 0 || nx == UINT64_MAX) continue;
-            heads[i] = cs.add_chain(nx);
-            any = true;
-        }
-        if (any) {
-            heads_at[c] = (int64_t) heads_flat.size();
-            heads_flat.insert(heads_flat.end(), heads.begin(), heads.end());
-        }
-    }
+    std::vector<uint32_t> &dropped = d.dropped;
+    for (size_t c = 0; c < changed.size() && !rc; ++c) rc = d.discover(c, w.leaves[changed[c]]);
     if (rc) return rc;
     uint64_t n_rows = 0;
     for (size_t c = 0; c < changed.size(); ++c) vis[changed[c]] -= dropped[c];
@@ -1095,11 +1158,7 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
             for (uint32_t j = lo; j < hi; ++j) {
                 const size_t c = c0 + j;
                 LeafExtras ex;
-                ex.heads = heads_at[c] >= 0 ? heads_flat.data() + heads_at[c] : nullptr;
-                if (patch_at[c].second) {
-                    ex.patches = patches.data() + patch_at[c].first;
-                    ex.n_patches = patch_at[c].second;
-                }
+                d.fill(c, &ex);
                 rcs[j] = stage_copy_leaf(s, s->h_stage[buf] + (size_t) j * ls, w.leaves[changed[c]], ex, &cvis[j], &ccnt[j]);
             }
         };
@@ -1110,6 +1169,17 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
         for (auto &x : th) x.join();
         uint32_t maxcount = 0;
         for (uint32_t j = 0; j < m && !rc; ++j) {
+            for (int attempt = 0; rcs[j] == kStageRetry && !rc; ++attempt) {    // a writer touched the leaf under the copy
+                const size_t c = c0 + j;
+                if (attempt >= 64 || (rc = d.discover(c, w.leaves[changed[c]]))) {
+                    if (!rc) rc = STAGE_ERR_NOT_QUIESCED;
+                    break;
+                }
+                LeafExtras ex;
+                d.fill(c, &ex);
+                rcs[j] = stage_copy_leaf(s, s->h_stage[buf] + (size_t) j * ls, w.leaves[changed[c]], ex, &cvis[j], &ccnt[j]);
+            }
+            if (rc) break;
             if (rcs[j]) rc = rcs[j];
             else if (cvis[j] != vis[changed[c0 + j]]) rc = STAGE_ERR_NOT_QUIESCED;      // the tree moved under the walk
             maxcount = std::max(maxcount, ccnt[j]);

@@ -164,3 +164,78 @@ def test_snapshot_with_updates_in_flight_reads_the_undo_copies():
             for ts in stamps:
                 assert_probe_equal(nxt.probe(probes, ts), before[ts], f"live refresh probe ts={ts}")
                 assert_scan_equal(nxt.scan(sk, 120, ts, 1), scans_before[ts], f"live refresh scan ts={ts}")
+
+
+def _snapshot_is_consistent(snap, N, P, keys, first_cid, committed):
+    """What a snapshot taken while the writer ran must satisfy, whatever instant it caught (the writer's transactions are
+    known: update i rewrites column [100,200) of keys[i] with (uint8)(first_cid + i) and commits with id first_cid + i):
+      * every row is there; its in-leaf commit id is 0 or the id of one of ITS OWN committed updates;
+      * the row image belongs to that version: column = (uint8) commit id (or the loader's byte), the rest untouched —
+        never a new payload under an old commit id, never a torn row;
+      * the version chain is intact: a reader just older than the in-leaf version gets the PREVIOUS update of that key
+        (or, before the second update, nothing: the loader's version ends the walk, executor.h:418)."""
+    allk = np.arange(N, dtype=np.uint32)
+    f, ts, _, pay = snap.probe(u32_keys(allk), 0xFFFFFFFF)
+    assert f.all(), "rows missing"
+    base = (allk & 0xFF).astype(np.uint8)
+    col = np.where(ts > 0, (ts & 0xFF).astype(np.uint8), base)
+    assert (pay[:, :100] == base[:, None]).all() and (pay[:, 200:] == base[:, None]).all(), "bytes outside the column changed"
+    assert (pay[:, 100:200] == col[:, None]).all(), "column does not belong to the commit id of the row"
+    cids = first_cid + np.nonzero(committed)[0]
+    ck = keys[np.nonzero(committed)[0]]
+    order = np.lexsort((cids, ck))
+    ck, cids = ck[order], cids[order]
+    upd = ts > 0
+    # the in-leaf commit id is one of the key's own updates
+    pos = np.searchsorted(ck.astype(np.uint64) << np.uint64(32) | cids.astype(np.uint64),
+                          allk[upd].astype(np.uint64) << np.uint64(32) | ts[upd].astype(np.uint64))
+    assert (pos < len(ck)).all() and (ck[pos] == allk[upd]).all() and (cids[pos] == ts[upd]).all(), "foreign commit id"
+    # previous version through the chain
+    has_prev = (pos > 0) & (ck[np.maximum(pos - 1, 0)] == allk[upd])
+    prev_cid = np.where(has_prev, cids[np.maximum(pos - 1, 0)], 0)
+    uk, uts = allk[upd], ts[upd]
+    for lo in range(0, len(uk), 4096):                       # one read id per probe: small batches per distinct stamp
+        sl = slice(lo, lo + 4096)
+        for k_, t_, p_, h_ in zip(uk[sl][:64], uts[sl][:64], prev_cid[sl][:64], has_prev[sl][:64]):
+            f1, s1, _, p1 = snap.probe(u32_keys(np.array([k_], np.uint32)), int(t_) - 1)
+            if h_:
+                assert f1[0] == 1 and s1[0] == p_ and p1[0, 150] == (p_ & 0xFF), "version chain lost a version"
+            else:
+                assert f1[0] == 0, "a version older than the first update must not be visible"
+
+
+@pytest.mark.skipif(not pyoracle.have_ref(), reason="needs the unmodified reference (oracle/_ref)")
+def test_snapshots_while_update_transactions_are_running():
+    """from_tree_live / refresh_from_tree_live with a writer thread that is actually running update
+    transactions (LeafNode::Update + commit install, the reference's own steps and order). Every leaf copy is validated
+    against the discovery pass and re-done when a writer got in between; the snapshots must be consistent."""
+    N, P = 30000, 1000
+    t = ycsb_int_table(pyoracle.RefTable, N, P)
+    rng = np.random.default_rng(5)
+    keys = rng.integers(0, N, 3_000_000).astype(np.uint32)
+    fn, ctx = t.undo_resolver()
+    w = pyoracle.Writer(t, keys, 100)
+    snaps = []
+    try:
+        first = None
+        for it in range(4):
+            assert w.alive(), "the writer finished before the snapshots were taken: enlarge the key stream"
+            if first is None:
+                first = sg.Snapshot.from_tree_live(t.root, 4, P, fn, ctx)
+                snaps.append(first)
+            else:
+                nxt, st = snaps[-1].refresh_from_tree(t.root, fn, ctx)
+                assert st.leaves_transformed > 0
+                snaps.append(nxt)
+            snaps.append(sg.Snapshot.from_tree_live(t.root, 4, P, fn, ctx))
+    finally:
+        tried, committed = w.stop()
+    assert tried > 10000 and committed[:tried].sum() > 0.9 * tried
+    for s in snaps:
+        _snapshot_is_consistent(s, N, P, keys[:tried], 100, committed[:tried])
+        s.close()
+    # quiesced again: the plain path agrees with the tree
+    with sg.Snapshot.from_tree(t.root, 4, P) as q:
+        pk = u32_keys(rng.integers(0, N, 20000))
+        for read_ts in (0, 50000, 0xFFFFFFFF):
+            assert_probe_equal(q.probe(pk, read_ts), t.probe(pk, read_ts), f"quiesced ts={read_ts}")

@@ -60,7 +60,12 @@ __global__ void __launch_bounds__(kShortThreads, MINB) scan_short_fused_kernel(S
     const uint64_t n_scans = a.n_dev ? min((uint64_t) __ldcg(a.n_dev), a.n) : a.n;
     for (uint64_t sid = (uint64_t) blockIdx.x * kTiles + tile; sid < n_scans; sid += n_tiles) {
         const uint32_t S = min(a.scan_sizes[sid], a.out_stride);
-        const SKey<NW> begin = to_sortable<NW>(a.start_keys + sid * K, K, v.xormask);
+        SKey<NW> begin;                            // K == 4 NW and 4-byte aligned keys (checked by the host): word path only
+        {
+            const uint32_t *k32 = reinterpret_cast<const uint32_t *>(a.start_keys + sid * K);
+#pragma unroll
+            for (int i = 0; i < NW; ++i) begin.w[i] = bswap32(__ldg(k32 + i)) ^ v.xormask;
+        }
         const uint64_t out_base = sid * (uint64_t) a.out_stride;
         uint32_t cnt = 0;
         if (S > 0 && L > 0) {
@@ -197,27 +202,54 @@ __global__ void __launch_bounds__(kShortThreads, MINB) scan_short_fused_kernel(S
         if (tl == 0) a.row_counts[sid] = cnt;
         if (a.ts_out && (uint32_t) tl < cnt) a.ts_out[out_base + tl] = my_ts[tl];
         if (a.src_row && (uint32_t) tl < a.out_stride) a.src_row[out_base + tl] = (uint32_t) tl < cnt ? my_src[tl] : kNoRow;
-        // (holding a whole scan's key and payload words in registers before the first store was measured and is slower:
-        //  0.55 -> 0.62 ms per 10^6 scans at 48 registers, 0.53 -> 0.83 ms at 32 — profiles/README.md; the SM overlaps the
-        //  tiles' emit phases by itself)
+        // The kernel is ISSUE-bound, not memory-bound (ncu r2: 76 % issue-slot utilisation, DRAM at 22 %; the newest orders of
+        // a district are L2-resident), so the emit is written for few instructions: when no row was dropped the selected
+        // rows are consecutive in the table, and keys / payload are flat runs copied with one index (no per-row address
+        // arithmetic). (Holding a whole scan's words in registers before the first store was measured and is slower.)
+        const bool contig = cnt > 0 && my_src[cnt - 1] - my_src[0] == cnt - 1;        // rows ascend: consecutive iff so
         if (a.key_out) {
-            uint32_t *ko = reinterpret_cast<uint32_t *>(a.key_out) + out_base * NW;
-            for (uint32_t it = tl; it < cnt * NW; it += TW) {
-                const uint32_t r = it / NW, w = it % NW;
-                ko[it] = bswap32(__ldg(v.level[0] + (uint64_t) my_src[r] * NW + w) ^ v.xormask);
+            if (contig && NW % 4 == 0) {
+                const uint4 *kin = reinterpret_cast<const uint4 *>(v.level[0] + (uint64_t) my_src[0] * NW);
+                uint4 *ko4 = reinterpret_cast<uint4 *>(reinterpret_cast<uint32_t *>(a.key_out) + out_base * NW);
+                for (uint32_t it = tl; it < cnt * (NW / 4); it += TW) {
+                    uint4 q = __ldg(kin + it);
+                    q.x = bswap32(q.x ^ v.xormask); q.y = bswap32(q.y ^ v.xormask);
+                    q.z = bswap32(q.z ^ v.xormask); q.w = bswap32(q.w ^ v.xormask);
+                    ko4[it] = q;
+                }
+            } else {
+                uint32_t *ko = reinterpret_cast<uint32_t *>(a.key_out) + out_base * NW;
+                for (uint32_t it = tl; it < cnt * NW; it += TW) {
+                    const uint32_t r = it / NW, w = it % NW;
+                    ko[it] = bswap32(__ldg(v.level[0] + (uint64_t) my_src[r] * NW + w) ^ v.xormask);
+                }
             }
         }
         if (o.payload_out) {
             uint32_t *po = reinterpret_cast<uint32_t *>(o.payload_out) + out_base * wpr;
-            for (uint32_t r0 = 0; r0 < cnt; r0 += 4) {
-                for (uint32_t w0 = tl; w0 < wpr; w0 += TW) {
+            if (contig) {
+                const uint32_t *pin = pay32 + (uint64_t) my_src[0] * wpr;
+                const uint32_t n_words = cnt * wpr;
+                for (uint32_t it = tl; it < n_words; it += 4 * TW) {
                     uint32_t val[4];
 #pragma unroll
                     for (int u = 0; u < 4; ++u)
-                        if (r0 + u < cnt) val[u] = __ldg(pay32 + (uint64_t) my_src[r0 + u] * wpr + w0);
+                        if (it + u * TW < n_words) val[u] = __ldg(pin + it + u * TW);
 #pragma unroll
                     for (int u = 0; u < 4; ++u)
-                        if (r0 + u < cnt) po[(uint64_t) (r0 + u) * wpr + w0] = val[u];
+                        if (it + u * TW < n_words) po[it + u * TW] = val[u];
+                }
+            } else {
+                for (uint32_t r0 = 0; r0 < cnt; r0 += 4) {
+                    for (uint32_t w0 = tl; w0 < wpr; w0 += TW) {
+                        uint32_t val[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            if (r0 + u < cnt) val[u] = __ldg(pay32 + (uint64_t) my_src[r0 + u] * wpr + w0);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            if (r0 + u < cnt) po[(uint64_t) (r0 + u) * wpr + w0] = val[u];
+                    }
                 }
             }
         }

@@ -2025,7 +2025,8 @@ static bool short_scan_eligible(const stage_snapshot *s, const ScanArgs &a, cons
     static const bool off = getenv("STAGE_SCAN_FUSED") && atoi(getenv("STAGE_SCAN_FUSED")) == 0;
     const uint32_t P = s->schema.payload_size, K = s->schema.key_size;
     return !off && a.out_stride >= 1 && a.out_stride <= 32 && (P & 3u) == 0 && P <= kShortMaxRow && K == (uint32_t) s->nw * 4 &&
-           (((uintptr_t) payload_out | (uintptr_t) a.key_out | (uintptr_t) s->d_payload) & 3u) == 0 && s->n_rows > 0;
+           (((uintptr_t) payload_out | (uintptr_t) s->d_payload | (uintptr_t) a.start_keys) & 3u) == 0 &&
+           ((uintptr_t) a.key_out & 15u) == 0 && s->n_rows > 0;
 }
 
 template <int NW, int TW, int MINB>

@@ -16,6 +16,7 @@
 #include <chrono>
 #include <condition_variable>
 #include <deque>
+#include <functional>
 #include <mutex>
 #include <thread>
 #include <string>
@@ -167,7 +168,8 @@ struct stage_snapshot {
     std::vector<stage_version_t> h_versions;
     std::vector<uint8_t> h_ver_payload;
     uint32_t *d_phys = nullptr;                 // physical (leaf, slot) order -> row, built on first use
-    uint8_t *ext_ver_payload = nullptr;         // malloc'd version rows handed over by from_tree (instead of h_ver_payload)
+    uint8_t *ext_ver_payload = nullptr;         // malloc'd version rows handed over by a caller (instead of h_ver_payload)
+    bool versions_on_device = false;            // the version table was uploaded before the seal (from_tree)
     uint8_t *h_stage[2] = {nullptr, nullptr};   // pinned
     uint8_t *d_stage[2] = {nullptr, nullptr};
     cudaEvent_t stage_ev[2] = {nullptr, nullptr};
@@ -498,10 +500,85 @@ static int stage_copy_leaf(const stage_snapshot *s, uint8_t *dst, const uint8_t 
 static unsigned staging_threads() {
     static const unsigned n = [] {
         if (const char *e = getenv("STAGE_STAGING_THREADS")) return (unsigned) std::max(1, atoi(e));
-        return std::min(8u, std::max(1u, std::thread::hardware_concurrency()));
+        return std::min(32u, std::max(1u, std::thread::hardware_concurrency()));
     }();
     return n;
 }
+
+// Host threads that copy leaf images / version rows into the pinned staging buffers. They live for the process (a
+// flattening call used to spawn and join its threads once per 32 MiB chunk: ~4000 thread creations for the 10 M-row
+// table); work is handed out in grains through one atomic counter, the calling thread takes part.
+class WorkPool {
+public:
+    static WorkPool &get() {
+        static WorkPool pool(staging_threads() > 1 ? staging_threads() - 1 : 0);
+        return pool;
+    }
+    void run(uint64_t n, uint64_t grain, const std::function<void(uint64_t, uint64_t)> &f) {
+        if (n == 0) return;
+        grain = std::max<uint64_t>(grain, 1);
+        if (th_.empty() || n <= grain) {
+            f(0, n);
+            return;
+        }
+        std::lock_guard<std::mutex> one(run_mu_);          // one parallel region at a time
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            job_ = &f;
+            n_ = n;
+            grain_ = grain;
+            next_.store(0);
+            active_ = (unsigned) th_.size();
+            ++gen_;
+        }
+        cv_start_.notify_all();
+        drain();
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_done_.wait(lk, [&] { return active_ == 0; });
+        job_ = nullptr;
+    }
+    ~WorkPool() {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            quit_ = true;
+        }
+        cv_start_.notify_all();
+        for (auto &t : th_) t.join();
+    }
+
+private:
+    explicit WorkPool(unsigned workers) {
+        for (unsigned i = 0; i < workers; ++i) th_.emplace_back([this] { loop(); });
+    }
+    void drain() {
+        for (;;) {
+            const uint64_t lo = next_.fetch_add(grain_);
+            if (lo >= n_) break;
+            (*job_)(lo, std::min(n_, lo + grain_));
+        }
+    }
+    void loop() {
+        uint64_t seen = 0;
+        std::unique_lock<std::mutex> lk(mu_);
+        for (;;) {
+            cv_start_.wait(lk, [&] { return quit_ || gen_ != seen; });
+            if (quit_) return;
+            seen = gen_;
+            lk.unlock();
+            drain();
+            lk.lock();
+            if (--active_ == 0) cv_done_.notify_one();
+        }
+    }
+    std::vector<std::thread> th_;
+    std::mutex mu_, run_mu_;
+    std::condition_variable cv_start_, cv_done_;
+    const std::function<void(uint64_t, uint64_t)> *job_ = nullptr;
+    uint64_t n_ = 0, grain_ = 1, gen_ = 0;
+    std::atomic<uint64_t> next_{0};
+    unsigned active_ = 0;
+    bool quit_ = false;
+};
 
 // Stage n leaves (tree order). The 64 KiB image copies — the bulk of the host work — run on a few threads, one
 // staging chunk at a time; bookkeeping (row offsets, fences) and the chunk flush stay on the calling thread.
@@ -529,14 +606,7 @@ static int stage_leaves(stage_snapshot *s, uint64_t n, Get get, Redo redo = Redo
                 rcs[j] = stage_copy_leaf(s, slot0 + (size_t) j * ls, leaf, ex, &vis[j], &cnt[j]);
             }
         };
-        const unsigned T = std::min<unsigned>(staging_threads(), std::max(1u, m / 16));
-        if (T <= 1) work(0, m);
-        else {
-            std::vector<std::thread> th;
-            for (unsigned t = 1; t < T; ++t) th.emplace_back(work, (uint32_t) ((uint64_t) m * t / T), (uint32_t) ((uint64_t) m * (t + 1) / T));
-            work(0, (uint32_t) ((uint64_t) m / T));
-            for (auto &x : th) x.join();
-        }
+        WorkPool::get().run(m, 4, [&](uint64_t lo, uint64_t hi) { work((uint32_t) lo, (uint32_t) hi); });
         for (uint32_t j = 0; j < m; ++j) {
             for (int attempt = 0; rcs[j] == kStageRetry; ++attempt) {      // a writer touched the leaf under the copy
                 if (attempt >= 64) return STAGE_ERR_NOT_QUIESCED;
@@ -677,9 +747,9 @@ extern "C" int stage_gpu_snapshot_seal(stage_snapshot_t *s) {
     int rc = flush_chunk(s);
     if (rc) return rc;
     s->n_rows = s->rows_staged;
-    // versions
-    s->n_versions = s->h_versions.size();
-    if (s->n_versions) {
+    // versions (from_tree uploads them itself through the staging buffers: versions_on_device)
+    if (!s->versions_on_device) s->n_versions = s->h_versions.size();
+    if (s->n_versions && !s->versions_on_device) {
         const uint64_t V = s->n_versions;
         if ((rc = dev_alloc(s, &s->d_ver_begin, V)) || (rc = dev_alloc(s, &s->d_ver_commit, V)) ||
             (rc = dev_alloc(s, &s->d_ver_next, V)) ||
@@ -793,11 +863,7 @@ struct ChainStager {
                 else memset(vbuf + i * P, 0, P);
             }
         };
-        const unsigned T = V > 4096 ? staging_threads() : 1;
-        std::vector<std::thread> th;
-        for (unsigned t = 1; t < T; ++t) th.emplace_back(work, V * t / T, V * (t + 1) / T);
-        work(0, V / T);
-        for (auto &x : th) x.join();
+        WorkPool::get().run(V, 1024, [&](uint64_t lo, uint64_t hi) { work((size_t) lo, (size_t) hi); });
         return vbuf;
     }
 };
@@ -940,6 +1006,49 @@ static double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
+// Version table of a freshly walked tree -> device: headers in three small copies, the retired rows [key][payload] ->
+// dense payload rows gathered by the staging threads into the pinned staging buffers and copied chunk by chunk (DMA at
+// link speed; a pageable 1 GB source used to go through the driver's bounce buffers).
+static int upload_versions_staged(stage_snapshot *s, const ChainStager &cs) {
+    const uint64_t V = cs.vers.size();
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    int rc = flush_chunk(s);                       // the last (partial) chunk of leaf images leaves the buffers first
+    if (rc) return rc;
+    if ((rc = dev_alloc(s, &s->d_ver_begin, V)) || (rc = dev_alloc(s, &s->d_ver_commit, V)) || (rc = dev_alloc(s, &s->d_ver_next, V)) ||
+        (rc = dev_alloc(s, &s->d_ver_payload, V * (uint64_t) P)))
+        return rc;
+    s->ver_cap = V;
+    std::vector<uint32_t> b(V), c(V), nx(V);
+    for (uint64_t i = 0; i < V; ++i) {
+        b[i] = cs.vers[i].begin_id; c[i] = cs.vers[i].commit_id; nx[i] = cs.vers[i].next;
+        if (nx[i] > V) return STAGE_ERR_ARG;
+    }
+    CUDA_TRY(cudaMemcpyAsync(s->d_ver_begin, b.data(), V * 4, cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(s->d_ver_commit, c.data(), V * 4, cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(s->d_ver_next, nx.data(), V * 4, cudaMemcpyHostToDevice, s->stream));
+    const uint64_t per = std::max<uint64_t>(1, (uint64_t) s->chunk_leaves * s->schema.leaf_node_size / P);
+    for (uint64_t v0 = 0; v0 < V; v0 += per) {
+        const uint64_t m = std::min(per, V - v0);
+        const int buf = s->stage_cur;
+        CUDA_TRY(cudaEventSynchronize(s->stage_ev[buf]));
+        uint8_t *dst = s->h_stage[buf];
+        WorkPool::get().run(m, 512, [&](uint64_t lo, uint64_t hi) {
+            for (uint64_t i = lo; i < hi; ++i) {
+                const uint64_t slot = cs.vslot[v0 + i];
+                if (slot != 0 && slot != UINT64_MAX) memcpy(dst + i * P, reinterpret_cast<const uint8_t *>(slot) + K, P);
+                else memset(dst + i * P, 0, P);
+            }
+        });
+        CUDA_TRY(cudaMemcpyAsync(s->d_ver_payload + v0 * P, dst, m * P, cudaMemcpyHostToDevice, s->stream));
+        CUDA_TRY(cudaEventRecord(s->stage_ev[buf], s->stream));
+        s->stage_cur ^= 1;
+    }
+    CUDA_TRY(cudaStreamSynchronize(s->stream));    // b / c / nx are pageable locals
+    s->n_versions = V;
+    s->versions_on_device = true;
+    return STAGE_OK;
+}
+
 static int from_tree_impl(const void *root, const stage_schema_t *schema, stage_undo_resolver_t resolve, void *resolve_ctx,
                           stage_snapshot_t **out) {
     if (!root || !out) return STAGE_ERR_ARG;
@@ -979,22 +1088,16 @@ static int from_tree_impl(const void *root, const stage_schema_t *schema, stage_
                           },
                           [&](uint64_t li) { return d.discover(li, w.leaves[li]); });
     PHASE("stage + transform");
-    if (!rc && !vers.empty()) {
-        // retired rows [key][payload] -> dense version rows, copied by the staging threads
-        uint8_t *vbuf = cs.payload_rows(K, P);
-        if (!vbuf) rc = STAGE_ERR_NOMEM;
-        else {
-            s->h_versions = std::move(vers);
-            s->ext_ver_payload = vbuf;
-        }
-    }
+    if (!rc && !vers.empty()) rc = upload_versions_staged(s, cs);
     if (!rc) {       // fingerprints for a later stage_gpu_snapshot_refresh_from_tree
         s->h_leaf_addr.resize(w.leaves.size());
         s->h_leaf_fp.resize(w.leaves.size());
-        for (size_t li = 0; li < w.leaves.size(); ++li) {
-            s->h_leaf_addr[li] = (uint64_t) (uintptr_t) w.leaves[li];
-            s->h_leaf_fp[li] = leaf_fingerprint(w.leaves[li], w.fences[li], K, schema->leaf_node_size);
-        }
+        WorkPool::get().run(w.leaves.size(), 512, [&](uint64_t lo, uint64_t hi) {
+            for (uint64_t li = lo; li < hi; ++li) {
+                s->h_leaf_addr[li] = (uint64_t) (uintptr_t) w.leaves[li];
+                s->h_leaf_fp[li] = leaf_fingerprint(w.leaves[li], w.fences[li], K, schema->leaf_node_size);
+            }
+        });
     }
     PHASE("version rows");
     if (!rc) rc = stage_gpu_snapshot_seal(s);
@@ -1066,11 +1169,7 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
                 vis[j] = v;
             }
         };
-        const unsigned T = L > 1024 ? staging_threads() : 1;
-        std::vector<std::thread> th;
-        for (unsigned t = 1; t < T; ++t) th.emplace_back(work, L * t / T, L * (t + 1) / T);
-        work(0, L / T);
-        for (auto &x : th) x.join();
+        WorkPool::get().run(L, 256, [&](uint64_t lo, uint64_t hi) { work((size_t) lo, (size_t) hi); });
     }
     for (size_t j = 0; j < L; ++j)
         if (src_leaf[j] == kNoLeaf) changed.push_back((uint32_t) j);
@@ -1162,11 +1261,7 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
                 rcs[j] = stage_copy_leaf(s, s->h_stage[buf] + (size_t) j * ls, w.leaves[changed[c]], ex, &cvis[j], &ccnt[j]);
             }
         };
-        const unsigned T = std::min<unsigned>(staging_threads(), std::max(1u, m / 16));
-        std::vector<std::thread> th;
-        for (unsigned t = 1; t < T; ++t) th.emplace_back(work, (uint32_t) ((uint64_t) m * t / T), (uint32_t) ((uint64_t) m * (t + 1) / T));
-        work(0, (uint32_t) ((uint64_t) m / T));
-        for (auto &x : th) x.join();
+        WorkPool::get().run(m, 4, [&](uint64_t lo, uint64_t hi) { work((uint32_t) lo, (uint32_t) hi); });
         uint32_t maxcount = 0;
         for (uint32_t j = 0; j < m && !rc; ++j) {
             for (int attempt = 0; rcs[j] == kStageRetry && !rc; ++attempt) {    // a writer touched the leaf under the copy
@@ -2043,8 +2138,9 @@ static int launch_short_scan_v(stage_snapshot *s, const ScanArgs &a, const Short
 template <int NW>
 static int launch_short_scan(stage_snapshot *s, const ScanArgs &a, uint8_t *payload_out, cudaStream_t st) {
     const ShortScanOut o{payload_out, s->d_row_leaf};
-    // MINB = resident CTAs per SM the register allocation is held to (8 = all 2048 threads, 32 registers each)
-    static const int minb = getenv("STAGE_SHORT_MINB") ? atoi(getenv("STAGE_SHORT_MINB")) : 8;
+    // MINB = resident CTAs per SM the register allocation is held to (8 = all 2048 threads at 32 registers, with spills;
+    // 5 = 48 registers, no spills: measured fastest, 0.399 vs 0.460 ms per 10^6 order_line scans)
+    static const int minb = getenv("STAGE_SHORT_MINB") ? atoi(getenv("STAGE_SHORT_MINB")) : 5;
     if (a.out_stride <= 16)
         return minb >= 8 ? launch_short_scan_v<NW, 16, 8>(s, a, o, st)
                          : minb <= 4 ? launch_short_scan_v<NW, 16, 4>(s, a, o, st) : launch_short_scan_v<NW, 16, 5>(s, a, o, st);

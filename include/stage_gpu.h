@@ -389,6 +389,25 @@ int stage_gpu_exchange_enable_timing(stage_exchange_t *x, int on);
 int stage_gpu_exchange_last_timing(stage_exchange_t *x, float *ms4);
 int stage_gpu_exchange_destroy(stage_exchange_t *x);
 
+/* ---- batching front-end for per-operation callers ------------------------------------------- */
+
+/* The reference's drivers run ONE operation per executor on N pinned threads (benchmark/ycsb/ycsb_workload.cpp:522-529,
+ * ycsb_mixed.cpp:83-93: IndexScanExecutor per key). A batcher coalesces the operations that concurrent callers have in
+ * flight into one batched launch: the first caller of a forming batch leads it, waits up to max_wait_us (or until
+ * max_batch operations joined), runs the batch with every operation's own read id, and all callers pick up their
+ * results. The calls block until the caller's operation is done and are safe from any number of threads. Results are
+ * those of stage_gpu_probe_batch / stage_gpu_scan_batch for the same (key, read id). The batcher must be destroyed
+ * before its snapshot, with no call in flight. */
+typedef struct stage_batcher stage_batcher_t;
+int stage_gpu_batcher_create(stage_snapshot_t *s, uint32_t max_batch, uint32_t max_wait_us, stage_batcher_t **out);
+int stage_gpu_batcher_probe(stage_batcher_t *b, const void *key, uint32_t read_ts, uint8_t *found, uint32_t *ts, void *key_out,
+                            void *payload_out);
+/* key_out / ts_out / payload_out hold scan_size rows; *row_count rows are written */
+int stage_gpu_batcher_scan(stage_batcher_t *b, const void *start_key, uint32_t scan_size, uint32_t read_ts, int apply_visibility,
+                           uint32_t *row_count, void *key_out, uint32_t *ts_out, void *payload_out);
+int stage_gpu_batcher_stats(stage_batcher_t *b, uint64_t *batches, uint64_t *operations);
+int stage_gpu_batcher_destroy(stage_batcher_t *b);
+
 /* ---- utilities ---------------------------------------------------------------------------- */
 void *stage_gpu_host_alloc(size_t bytes); /* pinned host memory for STAGE_IO_HOST batches */
 void stage_gpu_host_free(void *p);

@@ -66,7 +66,7 @@ public:
         schema_ = stage_schema_t{key_size, payload_size, leaf_node_size, key_kind};
         stage_snapshot_t *h = nullptr;
         check(stage_gpu_snapshot_from_tree(root, &schema_, &h), "stage_gpu_snapshot_from_tree");
-        snap_ = wrap(h);
+        snap_ = wrap(h, 0, 0);
     }
     // Tree with writers in flight: `resolve` looks an undo copy up in the tree's EphemeralPool (stage_undo_resolver_t,
     // include/stage_gpu.h), as BTree::Read does for a record whose update has not committed (b_tree.cpp:2087-2103).
@@ -75,7 +75,7 @@ public:
         schema_ = stage_schema_t{key_size, payload_size, leaf_node_size, key_kind};
         stage_snapshot_t *h = nullptr;
         check(stage_gpu_snapshot_from_tree_live(root, &schema_, resolve, resolve_ctx, &h), "stage_gpu_snapshot_from_tree_live");
-        snap_ = wrap(h);
+        snap_ = wrap(h, 0, 0);
     }
     ~GpuTreeView() = default;          // the snapshot goes when its last user (this view or a reader in flight) lets go
     GpuTreeView(const GpuTreeView &) = delete;
@@ -89,8 +89,7 @@ public:
         uint8_t found = 0;
         uint32_t ts = 0;
         // read_ts = MAX_CID: the in-leaf version is always "visible" here
-        check(stage_gpu_probe_batch(pin().get(), key, 1, 0xFFFFFFFFu, &found, &ts, rec->GetData(), rec->GetPayload(),
-                                    STAGE_IO_HOST), "stage_gpu_probe_batch");
+        ReadBatch(key, 1, 0xFFFFFFFFu, &found, &ts, rec->GetData(), rec->GetPayload());
         if (!found) return nullptr;
         rec->commit_id = ts;
         rec->SetCstamp(commit_id);
@@ -102,13 +101,22 @@ public:
     // Batched forms: the ones that reach HBM speed. Outputs are caller-allocated host buffers.
     void ReadBatch(const void *keys, uint64_t n, cid_t read_ts, uint8_t *found, uint32_t *ts, void *key_out,
                    void *payload_out) {
-        check(stage_gpu_probe_batch(pin().get(), keys, n, read_ts, found, ts, key_out, payload_out, STAGE_IO_HOST),
-              "stage_gpu_probe_batch");
+        std::shared_ptr<Handle> h = pin();
+        if (n == 1 && h->batcher)      // a single operation: coalesced with the other threads' operations in flight
+            check(stage_gpu_batcher_probe(h->batcher, keys, read_ts, found, ts, key_out, payload_out), "stage_gpu_batcher_probe");
+        else
+            check(stage_gpu_probe_batch(h->snap, keys, n, read_ts, found, ts, key_out, payload_out, STAGE_IO_HOST),
+                  "stage_gpu_probe_batch");
     }
     void ScanBatch(const void *start_keys, const uint32_t *scan_sizes, uint64_t n, uint32_t out_stride, cid_t read_ts,
                    bool apply_visibility, uint32_t *row_counts, void *key_out, uint32_t *ts_out, void *payload_out) {
-        check(stage_gpu_scan_batch(pin().get(), start_keys, scan_sizes, n, out_stride, read_ts, apply_visibility ? 1 : 0,
-                                   row_counts, key_out, ts_out, payload_out, STAGE_IO_HOST), "stage_gpu_scan_batch");
+        std::shared_ptr<Handle> h = pin();
+        if (n == 1 && h->batcher && scan_sizes[0] <= out_stride)
+            check(stage_gpu_batcher_scan(h->batcher, start_keys, scan_sizes[0], read_ts, apply_visibility ? 1 : 0, row_counts, key_out,
+                                         ts_out, payload_out), "stage_gpu_batcher_scan");
+        else
+            check(stage_gpu_scan_batch(h->snap, start_keys, scan_sizes, n, out_stride, read_ts, apply_visibility ? 1 : 0,
+                                       row_counts, key_out, ts_out, payload_out, STAGE_IO_HOST), "stage_gpu_scan_batch");
     }
 
     // After the host tree took committed inserts / updates / deletes (quiesced again): swap in the next snapshot.
@@ -118,15 +126,15 @@ public:
     // last of them returns), calls that start after the swap see the new one. One Refresh at a time.
     stage_refresh_stats_t Refresh(const void *root, stage_undo_resolver_t resolve = nullptr, void *resolve_ctx = nullptr) {
         std::lock_guard<std::mutex> one(refresh_mu_);
-        std::shared_ptr<stage_snapshot_t> cur = pin();
+        std::shared_ptr<Handle> cur = pin();
         stage_snapshot_t *next = nullptr;
         stage_refresh_stats_t st{};
         if (resolve)
-            check(stage_gpu_snapshot_refresh_from_tree_live(cur.get(), root, resolve, resolve_ctx, &next, &st),
+            check(stage_gpu_snapshot_refresh_from_tree_live(cur->snap, root, resolve, resolve_ctx, &next, &st),
                   "stage_gpu_snapshot_refresh_from_tree_live");
         else
-            check(stage_gpu_snapshot_refresh_from_tree(cur.get(), root, &next, &st), "stage_gpu_snapshot_refresh_from_tree");
-        std::shared_ptr<stage_snapshot_t> fresh = wrap(next);
+            check(stage_gpu_snapshot_refresh_from_tree(cur->snap, root, &next, &st), "stage_gpu_snapshot_refresh_from_tree");
+        std::shared_ptr<Handle> fresh = wrap(next, batch_max_, batch_wait_us_);
         {
             std::lock_guard<std::mutex> g(mu_);
             snap_.swap(fresh);
@@ -134,23 +142,52 @@ public:
         return st;
     }
 
+    // The reference's drivers run one executor per operation on N worker threads (ycsb_workload.cpp:522-529). With
+    // batching enabled, single operations (Read, ReadBatch / ScanBatch of one, i.e. what the executor adapters issue) of
+    // concurrent threads are coalesced into batched launches (stage_gpu_batcher_*). Call before the workers start.
+    void EnableBatching(uint32_t max_batch = 256, uint32_t max_wait_us = 30) {
+        std::lock_guard<std::mutex> one(refresh_mu_);
+        batch_max_ = max_batch;
+        batch_wait_us_ = max_wait_us;
+        std::shared_ptr<Handle> cur = pin();
+        if (!cur->batcher) check(stage_gpu_batcher_create(cur->snap, max_batch, max_wait_us, &cur->batcher), "stage_gpu_batcher_create");
+    }
+    void BatchingStats(uint64_t *batches, uint64_t *operations) {
+        std::shared_ptr<Handle> cur = pin();
+        *batches = *operations = 0;
+        if (cur->batcher) stage_gpu_batcher_stats(cur->batcher, batches, operations);
+    }
+
     const stage_schema_t &schema() const { return schema_; }
+    // snapshot (+ its batcher), destroyed together when the last user lets go
+    struct Handle {
+        stage_snapshot_t *snap = nullptr;
+        stage_batcher_t *batcher = nullptr;
+        ~Handle() {
+            if (batcher) stage_gpu_batcher_destroy(batcher);
+            if (snap) stage_gpu_snapshot_destroy(snap);
+        }
+    };
     // The current snapshot, kept alive for as long as the returned pointer lives.
-    std::shared_ptr<stage_snapshot_t> pin() const {
+    std::shared_ptr<Handle> pin() const {
         std::lock_guard<std::mutex> g(mu_);
         return snap_;
     }
     // Raw handle of the current snapshot; only valid until the next Refresh (use pin() from concurrent readers).
-    stage_snapshot_t *handle() { return pin().get(); }
+    stage_snapshot_t *handle() { return pin()->snap; }
 
 private:
-    static std::shared_ptr<stage_snapshot_t> wrap(stage_snapshot_t *h) {
-        return std::shared_ptr<stage_snapshot_t>(h, [](stage_snapshot_t *p) { if (p) stage_gpu_snapshot_destroy(p); });
+    static std::shared_ptr<Handle> wrap(stage_snapshot_t *h, uint32_t batch_max, uint32_t wait_us) {
+        auto p = std::make_shared<Handle>();
+        p->snap = h;
+        if (batch_max) check(stage_gpu_batcher_create(h, batch_max, wait_us, &p->batcher), "stage_gpu_batcher_create");
+        return p;
     }
     stage_schema_t schema_{};
     mutable std::mutex mu_;
     std::mutex refresh_mu_;
-    std::shared_ptr<stage_snapshot_t> snap_;
+    std::shared_ptr<Handle> snap_;
+    uint32_t batch_max_ = 0, batch_wait_us_ = 0;
 };
 
 // Iterator::GetNext shape over one scan's result slab (the scan runs when the iterator is created).

@@ -113,6 +113,11 @@ SYMBOLS = {
     "stage_gpu_exchange_enable_timing": (_i32, [_vp, _i32]),
     "stage_gpu_exchange_last_timing": (_i32, [_vp, C.POINTER(C.c_float)]),
     "stage_gpu_exchange_destroy": (_i32, [_vp]),
+    "stage_gpu_batcher_create": (_i32, [_vp, _u32, _u32, C.POINTER(_vp)]),
+    "stage_gpu_batcher_probe": (_i32, [_vp, _vp, _u32, _vp, _vp, _vp, _vp]),
+    "stage_gpu_batcher_scan": (_i32, [_vp, _vp, _u32, _u32, _i32, _vp, _vp, _vp, _vp]),
+    "stage_gpu_batcher_stats": (_i32, [_vp, C.POINTER(_u64), C.POINTER(_u64)]),
+    "stage_gpu_batcher_destroy": (_i32, [_vp]),
     "stage_gpu_snapshot_counters": (_i32, [_vp, C.POINTER(Counters), _i32]),
     "stage_gpu_host_register": (_i32, [_vp, C.c_size_t]),
     "stage_gpu_host_unregister": (_i32, [_vp]),
@@ -485,6 +490,44 @@ def tpcc_stock_level(order_line, stock, reqs, read_ts, out=None, n=None):
         return out
     _check(lib().stage_gpu_tpcc_stock_level(order_line.h, stock.h, _ptr(reqs), n, read_ts, _ptr(out), IO_DEVICE))
     return out
+
+
+class Batcher:
+    """Coalesces single operations of concurrent callers into batched launches (stage_gpu_batcher_*)."""
+
+    def __init__(self, snap, max_batch=256, max_wait_us=30):
+        self.snap = snap
+        self.h = _vp()
+        _check(lib().stage_gpu_batcher_create(snap.h, max_batch, max_wait_us, C.byref(self.h)))
+
+    def probe(self, key, read_ts):
+        """-> (found, ts, key_out u8[K], payload u8[P])"""
+        K, P = self.snap.schema.key_size, self.snap.schema.payload_size
+        key = np.ascontiguousarray(key, np.uint8)
+        f, t = C.c_uint8(0), _u32(0)
+        ko, po = np.zeros(K, np.uint8), np.zeros(P, np.uint8)
+        _check(lib().stage_gpu_batcher_probe(self.h, _ptr(key), read_ts, C.byref(f), C.byref(t), _ptr(ko), _ptr(po)))
+        return int(f.value), int(t.value), ko, po
+
+    def scan(self, start_key, scan_size, read_ts, apply_visibility):
+        """-> (count, keys u8[S,K], ts u32[S], payload u8[S,P])"""
+        K, P = self.snap.schema.key_size, self.snap.schema.payload_size
+        start_key = np.ascontiguousarray(start_key, np.uint8)
+        c = _u32(0)
+        ko, to, po = np.zeros((scan_size, K), np.uint8), np.zeros(scan_size, np.uint32), np.zeros((scan_size, P), np.uint8)
+        _check(lib().stage_gpu_batcher_scan(self.h, _ptr(start_key), scan_size, read_ts, int(apply_visibility), C.byref(c),
+                                            _ptr(ko), _ptr(to), _ptr(po)))
+        return int(c.value), ko, to, po
+
+    def stats(self):
+        b, o = _u64(0), _u64(0)
+        _check(lib().stage_gpu_batcher_stats(self.h, C.byref(b), C.byref(o)))
+        return int(b.value), int(o.value)
+
+    def close(self):
+        if self.h:
+            _check(lib().stage_gpu_batcher_destroy(self.h))
+            self.h = None
 
 
 def route(keys, splitters, key_size, key_kind=KEY_AUTO):

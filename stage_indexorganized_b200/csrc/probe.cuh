@@ -56,6 +56,8 @@ struct ProbeArgs {
     uint32_t *ts_out;
     uint8_t *key_out;
     uint32_t *src_row;   // [n] row to gather (gather.cuh encoding), kNoRow on a miss
+    const uint32_t *read_ts_each;   // optional [n]: a read id per probe (coalesced single operations of different
+                                    // transactions, csrc/stage_gpu.cu "batching front-end"); nullptr = read_ts for all
 };
 
 // MVCC visibility (executor.h:383-446): the version of `row` visible at read_ts, in gather.cuh's
@@ -270,7 +272,7 @@ __global__ void __launch_bounds__(kProbeThreads) probe_kernel(SnapshotView v, Pr
             const uint64_t gi = g0 + p * stride;
             if (gi >= a.n) continue;
             uint32_t src = kNoRow, stamp = 0;
-            if (hit[p]) src = visible_version(v, c[p], t[p], a.read_ts, &stamp);
+            if (hit[p]) src = visible_version(v, c[p], t[p], a.read_ts_each ? a.read_ts_each[gi] : a.read_ts, &stamp);
             if (a.found) a.found[gi] = src != kNoRow ? 1 : 0;
             if (a.ts_out) a.ts_out[gi] = stamp;
             if (a.key_out && src != kNoRow) from_sortable<NW>(k[p], a.key_out + gi * K, K, v.xormask);

@@ -42,6 +42,8 @@ struct ScanArgs {
     uint32_t *src_row;          // [n][out_stride] rows to gather, kNoRow beyond row_counts[i]
     const uint32_t *n_dev;      // optional: the number of scans lives on the device (min(*n_dev, n) are run)
     unsigned long long *stats;  // optional: [0] += scans whose rows were selected by the slot-order rule (Q5)
+    const uint32_t *read_ts_each;    // optional [n]: read id per scan (coalesced single operations); nullptr = read_ts
+    const uint8_t *visibility_each;  // optional [n]: apply_visibility per scan; nullptr = apply_visibility
 };
 
 // MVCC filter of a scanned row, exactly as the reference's executors apply it. TableScanExecutor: none
@@ -52,8 +54,15 @@ struct ScanArgs {
 // does, b_tree.cpp:2099/2116) — so in a range scan a row whose latest version is newer than the reader is
 // DROPPED, never replaced by an older version. Checked against the unmodified executor in
 // tests/cpp/dropin_test.cpp ("range over chains"). Point probes do walk the chain (probe.cuh).
-__device__ __forceinline__ bool scan_row_visible(const ScanArgs &a, uint32_t t) {
-    return !a.apply_visibility || a.read_ts >= t;
+__device__ __forceinline__ bool scan_row_visible(int apply_visibility, uint32_t read_ts, uint32_t t) {
+    return !apply_visibility || read_ts >= t;
+}
+// the filter of scan `sid`: (apply_visibility, read id)
+__device__ __forceinline__ int scan_vis_of(const ScanArgs &a, uint64_t sid) {
+    return a.visibility_each ? (int) a.visibility_each[sid] : a.apply_visibility;
+}
+__device__ __forceinline__ uint32_t scan_ts_of(const ScanArgs &a, uint64_t sid) {
+    return a.read_ts_each ? a.read_ts_each[sid] : a.read_ts;
 }
 
 constexpr int kScanThreads = 256;
@@ -131,6 +140,8 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
         const uint32_t S = min(a.scan_sizes[sid], a.out_stride);   // a scan never writes past its slab
         const SKey<NW> begin = to_sortable<NW>(a.start_keys + sid * K, K, v.xormask);
         const uint64_t out_base = sid * (uint64_t) a.out_stride;
+        const int vis_on = scan_vis_of(a, sid);
+        const uint32_t rts = scan_ts_of(a, sid);
         uint32_t cnt = 0;
 
         // emits one row (already selected) at output position `pos` of this scan
@@ -205,7 +216,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
                         stamp[k] = 0;
                         if (i < n) {
                             const uint32_t row = r0 + i, t = s_ts[row - a0];
-                            if (scan_row_visible(a, t)) { src[k] = row; stamp[k] = t; }
+                            if (scan_row_visible(vis_on, rts, t)) { src[k] = row; stamp[k] = t; }
                             mine += src[k] != kNoRow;
                         }
                     }
@@ -241,7 +252,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_plan_kernel(SnapshotView v,
                         const uint32_t row = start_l + i;
                         if (sel) {
                             const uint32_t t = __ldg(v.ts + row);
-                            if (scan_row_visible(a, t)) { src = row; stamp = t; }
+                            if (scan_row_visible(vis_on, rts, t)) { src = row; stamp = t; }
                         }
                         const uint32_t p2 = block_exclusive_sum(src != kNoRow ? 1u : 0u, s_warp, &tot);
                         if (src != kNoRow) emit(row, src, stamp, cnt + p2);
@@ -321,6 +332,8 @@ __global__ void __launch_bounds__(kScanWarpThreads) scan_plan_warp_kernel(Snapsh
         const uint32_t S = min(a.scan_sizes[sid], a.out_stride);   // a scan never writes past its slab
         const SKey<NW> begin = to_sortable<NW>(a.start_keys + sid * K, K, v.xormask);
         const uint64_t out_base = sid * (uint64_t) a.out_stride;
+        const int vis_on = scan_vis_of(a, sid);
+        const uint32_t rts = scan_ts_of(a, sid);
         uint32_t cnt = 0;
         auto emit = [&](uint32_t row, uint32_t src, uint32_t stamp, uint32_t pos) {
             const uint64_t o = out_base + pos;
@@ -402,7 +415,7 @@ __global__ void __launch_bounds__(kScanWarpThreads) scan_plan_warp_kernel(Snapsh
                     const uint32_t row = q0 + i;
                     if (i < main_n) {
                         const uint32_t t = __ldg(v.ts + row);
-                        if (scan_row_visible(a, t)) { src = row; stamp = t; }
+                        if (scan_row_visible(vis_on, rts, t)) { src = row; stamp = t; }
                     }
                     const uint32_t m = __ballot_sync(FULL, src != kNoRow);
                     if (src != kNoRow) emit(row, src, stamp, cnt + __popc(m & lt_mask));
@@ -434,7 +447,7 @@ __global__ void __launch_bounds__(kScanWarpThreads) scan_plan_warp_kernel(Snapsh
                         const uint32_t row = start_l + i;
                         if (sel) {
                             const uint32_t t = __ldg(v.ts + row);
-                            if (scan_row_visible(a, t)) { src = row; stamp = t; }
+                            if (scan_row_visible(vis_on, rts, t)) { src = row; stamp = t; }
                         }
                         const uint32_t m2 = __ballot_sync(FULL, src != kNoRow);
                         if (src != kNoRow) emit(row, src, stamp, cnt + __popc(m2 & lt_mask));

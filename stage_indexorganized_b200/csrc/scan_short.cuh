@@ -67,6 +67,8 @@ __global__ void __launch_bounds__(kShortThreads, MINB) scan_short_fused_kernel(S
             for (int i = 0; i < NW; ++i) begin.w[i] = bswap32(__ldg(k32 + i)) ^ v.xormask;
         }
         const uint64_t out_base = sid * (uint64_t) a.out_stride;
+        const int vis_on = scan_vis_of(a, sid);
+        const uint32_t rts = scan_ts_of(a, sid);
         uint32_t cnt = 0;
         if (S > 0 && L > 0) {
             bool have_row = false;
@@ -150,7 +152,7 @@ __global__ void __launch_bounds__(kShortThreads, MINB) scan_short_fused_kernel(S
                     const uint32_t row = q0 + tl;
                     if ((uint32_t) tl < main_n) {
                         const uint32_t t = have_row ? t_spec : __ldg(v.ts + row);
-                        if (scan_row_visible(a, t)) { src = row; stamp = t; }
+                        if (scan_row_visible(vis_on, rts, t)) { src = row; stamp = t; }
                     }
                     const uint32_t m = tballot(src != kNoRow);
                     if (src != kNoRow) {
@@ -184,7 +186,7 @@ __global__ void __launch_bounds__(kShortThreads, MINB) scan_short_fused_kernel(S
                         const uint32_t row = start_l + i;
                         if (sel) {
                             const uint32_t t = __ldg(v.ts + row);
-                            if (scan_row_visible(a, t)) { src = row; stamp = t; }
+                            if (scan_row_visible(vis_on, rts, t)) { src = row; stamp = t; }
                         }
                         const uint32_t m2 = tballot(src != kNoRow);
                         if (src != kNoRow) {

@@ -113,12 +113,13 @@ struct HostCtx {
     DevBuf keys, sizes, srcrow;
     DevBuf counts[2], found[2], ts[2], keyout[2], payload[2];
     DevBuf kstr, tstr, off, cubtmp;                 // compact mode: strided keys / commit ids of the plan, row offsets, scan temp
+    DevBuf tse, vise;                               // per-operation read ids / visibility flags (batching front-end)
     uint32_t *h_counts = nullptr;                   // pinned: row counts of the chunk in flight (per-scan copies)
     size_t h_counts_cap = 0;
     bool busy = false;
     void release_all() {
         keys.release(); sizes.release(); srcrow.release();
-        kstr.release(); tstr.release(); off.release(); cubtmp.release();
+        kstr.release(); tstr.release(); off.release(); cubtmp.release(); tse.release(); vise.release();
         for (int i = 0; i < 2; ++i) {
             counts[i].release(); found[i].release(); ts[i].release(); keyout[i].release(); payload[i].release();
             if (done[i]) cudaEventDestroy(done[i]);
@@ -1993,7 +1994,7 @@ static int probe_host_zerocopy(stage_snapshot *s, HostCtx *c, const void *keys, 
 }
 
 static int probe_host_staged(stage_snapshot *s, HostCtx *c, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
-                             uint32_t *ts, void *key_out, void *payload_out) {
+                             uint32_t *ts, void *key_out, void *payload_out, const uint32_t *read_ts_each = nullptr) {
     const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
     // ~64 MiB of result rows per chunk, two chunks in flight: chunk i is copied out (copy stream) while chunk i+1 is
     // searched and gathered (kernel stream)
@@ -2008,6 +2009,10 @@ static int probe_host_staged(stage_snapshot *s, HostCtx *c, const void *keys, ui
         if (payload_out && (rc = c->payload[i].ensure(cm * (uint64_t) P))) return rc;
     }
     CUDA_TRY(cudaMemcpyAsync(c->keys.p, keys, n * K, cudaMemcpyHostToDevice, c->st));
+    if (read_ts_each) {
+        if ((rc = c->tse.ensure(n * 4))) return rc;
+        CUDA_TRY(cudaMemcpyAsync(c->tse.p, read_ts_each, n * 4, cudaMemcpyHostToDevice, c->st));
+    }
     const Lane ln{c->st, &c->srcrow, false};
     uint64_t i = 0;
     for (uint64_t b = 0; b < n; b += chunk, ++i) {
@@ -2017,6 +2022,7 @@ static int probe_host_staged(stage_snapshot *s, HostCtx *c, const void *keys, ui
         ProbeArgs a{};
         a.n = m;
         a.read_ts = read_ts;
+        a.read_ts_each = read_ts_each ? static_cast<const uint32_t *>(c->tse.p) + b : nullptr;
         a.keys = static_cast<const uint8_t *>(c->keys.p) + b * K;
         a.found = found ? static_cast<uint8_t *>(c->found[buf].p) : nullptr;
         a.ts_out = ts ? static_cast<uint32_t *>(c->ts[buf].p) : nullptr;
@@ -2231,7 +2237,8 @@ static int scan_host_zerocopy(stage_snapshot *s, HostCtx *c, const void *start_k
 // of all scans are packed back to back on the device first, so the copies carry exactly the rows that exist.
 static int scan_host_staged(stage_snapshot *s, HostCtx *c, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
                             uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts, void *key_out,
-                            uint32_t *ts_out, void *payload_out, bool compact) {
+                            uint32_t *ts_out, void *payload_out, bool compact, const uint32_t *read_ts_each = nullptr,
+                            const uint8_t *vis_each = nullptr) {
     const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
     const uint64_t slot_bytes = (uint64_t) P + K + 4;
     // ~128 MiB of result slots per chunk; fewer for small batches so that the first copy starts early
@@ -2264,6 +2271,14 @@ static int scan_host_staged(stage_snapshot *s, HostCtx *c, const void *start_key
     }
     CUDA_TRY(cudaMemcpyAsync(c->keys.p, start_keys, n * K, cudaMemcpyHostToDevice, c->st));
     CUDA_TRY(cudaMemcpyAsync(c->sizes.p, scan_sizes, n * 4, cudaMemcpyHostToDevice, c->st));
+    if (read_ts_each) {
+        if ((rc = c->tse.ensure(n * 4))) return rc;
+        CUDA_TRY(cudaMemcpyAsync(c->tse.p, read_ts_each, n * 4, cudaMemcpyHostToDevice, c->st));
+    }
+    if (vis_each) {
+        if ((rc = c->vise.ensure(n))) return rc;
+        CUDA_TRY(cudaMemcpyAsync(c->vise.p, vis_each, n, cudaMemcpyHostToDevice, c->st));
+    }
     const Lane ln{c->st, &c->srcrow, false};
     uint64_t i = 0, row_base = 0;                 // row_base: rows already returned (compact layout)
     for (uint64_t b = 0; b < n; b += chunk, ++i) {
@@ -2286,6 +2301,8 @@ static int scan_host_staged(stage_snapshot *s, HostCtx *c, const void *start_key
         a.start_keys = static_cast<const uint8_t *>(c->keys.p) + b * K;
         a.scan_sizes = static_cast<const uint32_t *>(c->sizes.p) + b;
         a.row_counts = static_cast<uint32_t *>(c->counts[buf].p);
+        a.read_ts_each = read_ts_each ? static_cast<const uint32_t *>(c->tse.p) + b : nullptr;
+        a.visibility_each = vis_each ? static_cast<const uint8_t *>(c->vise.p) + b : nullptr;
         a.key_out = compact ? (key_out ? static_cast<uint8_t *>(c->kstr.p) : nullptr) : d_key;
         a.ts_out = compact ? (ts_out ? static_cast<uint32_t *>(c->tstr.p) : nullptr) : d_ts;
         if ((rc = scan_plan_launch(s, ln, a))) return rc;
@@ -2370,6 +2387,8 @@ extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys,
     return scan_host_staged(s, g.c, start_keys, scan_sizes, n, out_stride, read_ts, apply_visibility, row_counts, key_out, ts_out,
                             payload_out, compact);
 }
+
+#include "batcher.inc"
 
 // ------------------------------------------------------------------------------------------------
 // column projection (push-down): plan kernels + gather_cols_kernel

@@ -20,6 +20,9 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <thread>
+#include <atomic>
+#include <chrono>
 
 #include "execute/executor.h"
 #include "benchmark_common.h"
@@ -320,6 +323,70 @@ static void run_mvcc_checks(bool ref_only, uint32_t n_rows) {
     printf("%-12s %zu updates in flight, %u reads compared : %s\n", "mvcc", flying.size(), checked, g_fail == fail0 ? "OK" : "FAILED");
 }
 
+// The reference's driver loop shape (benchmark/ycsb/ycsb_mixed.cpp:18-110 RunMixed with -u 0: `ops` point reads per
+// transaction, one IndexScanExecutor per read, N worker threads as in ycsb_workload.cpp:522-529) through the GPU adapters,
+// first as literal batches of one, then with the batching front-end coalescing the threads' operations. Every tuple is
+// compared with the reference executor's; the rates are printed for profiles/README.md.
+static void run_driver_shape(Table &t, uint32_t n_rows, int threads, int ops_per_txn, int txns_per_thread) {
+    stage_gpu::GpuTreeView view(t.tree->GetRootNodeSafe(), t.K, t.P);
+    const int fail0 = g_fail;
+    for (int pass = 0; pass < 3; ++pass) {                // 0: reference executors, 1: GPU adapters, 2: GPU adapters + batching
+        if (pass == 2) view.EnableBatching(256, 50);
+        std::atomic<uint64_t> hits{0}, mism{0};
+        std::vector<std::thread> th;
+        const auto t0 = std::chrono::steady_clock::now();
+        for (int w = 0; w < threads; ++w)
+            th.emplace_back([&, w] {
+                benchmark::FastRandom rng(1000 + w);
+                uint64_t h = 0, bad = 0;
+                for (int x = 0; x < txns_per_thread; ++x) {
+                    // a read-only context built directly (the manager's transaction table is a stub container here and
+                    // not meant for concurrent BeginTransaction calls; reads only need the read id)
+                    TransactionContext txn_obj((size_t) w, IsolationLevelType::SERIALIZABLE, 100 + x, 100 + x);
+                    TransactionContext *txn = &txn_obj;
+                    txn->SetReadOnly();
+                    for (int o = 0; o < ops_per_txn; ++o) {
+                        uint32_t k = (uint32_t) (1 + rng.next() % n_rows);              // keys 1..N like the driver: key N misses
+                        const char *kp = reinterpret_cast<const char *>(&k);
+                        if (pass == 0) {
+                            IndexScanExecutor<const char *, TupleInt> ref(t.tree, (uint16_t) t.K, kp, 1, true, nullptr, false, txn, nullptr);
+                            ref.Execute();
+                            const TupleInt *r = ref.GetRecord();
+                            h += r != nullptr;
+                            delete r;
+                        } else {
+                            stage_gpu::GpuIndexScanExecutor<const char *, TupleInt, TransactionContext> gpu(&view, (uint16_t) t.K, kp, 1, true,
+                                                                                                           nullptr, false, txn, nullptr);
+                            gpu.Execute();
+                            const TupleInt *g = gpu.GetRecord();
+                            h += g != nullptr;
+                            if (x % 8 == 0) {                                                // spot-check against the reference
+                                IndexScanExecutor<const char *, TupleInt> ref(t.tree, (uint16_t) t.K, kp, 1, true, nullptr, false, txn, nullptr);
+                                ref.Execute();
+                                const TupleInt *r = ref.GetRecord();
+                                bad += (r == nullptr) != (g == nullptr) || (r && g && memcmp(r, g, sizeof(TupleInt)) != 0);
+                                delete r;
+                            }
+                        }
+                    }
+                }
+                hits += h;
+                mism += bad;
+            });
+        for (auto &x : th) x.join();
+        const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        const double ops = (double) threads * txns_per_thread * ops_per_txn;
+        uint64_t nb = 0, no = 0;
+        view.BatchingStats(&nb, &no);
+        printf("driver-shape  %-34s %2d threads x %d reads/txn: %10.0f reads/s (hits %lu%s)\n",
+               pass == 0 ? "reference IndexScanExecutor" : pass == 1 ? "GPU adapter, batches of one" : "GPU adapter + batching front-end",
+               threads, ops_per_txn, ops / sec, (unsigned long) hits.load(),
+               pass == 2 ? (", " + std::to_string(no) + " reads in " + std::to_string(nb) + " launches").c_str() : "");
+        EXPECT(mism.load() == 0, "driver shape pass %d: tuples differ from the reference", pass);
+    }
+    printf("%-12s %s\n", "driver-shape", g_fail == fail0 ? "OK" : "FAILED");
+}
+
 int main(int argc, char **argv) {
     setvbuf(stdout, nullptr, _IOLBF, 0);      // a crash must not swallow the lines before it
     bool ref_only = false;
@@ -376,6 +443,7 @@ int main(int argc, char **argv) {
             EXPECT(st.leaves_carried > st.leaves_total / 2, "refresh: most leaves must be carried over");
         }
         run_checks<TupleInt>(t, probes, scans, 100, ref_only, "int/refresh", live.get());
+        if (!ref_only) run_driver_shape(t, n_rows, 16, 10, 150);
     }
     // ---- YCSB string table (ycsb_loader.cpp:107-143): 16 random bytes per key, payload 1000 x 'a' ---------------
     {

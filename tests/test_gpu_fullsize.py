@@ -170,3 +170,56 @@ def test_config3_string_keys(n_rows):
         snap.close()
         del keys, order
         torch.cuda.empty_cache()
+
+
+# ---- reference-pinned parity at a size where the loader's leaf shapes matter ----------------------------
+# 2 M-row trees built by the unmodified reference (≈ 2.2 GB of leaf images each, ≈ 33 k leaves with unsorted suffixes and
+# leaves whose largest key is not the separator), flattened by from_tree and compared on 10^5 probes and 10^4 scans —
+# including 10-row scans, where SURVEY measured 39 % of the scans to be cut by the slot-order rule (Q5).
+@pytest.mark.skipif(not pyoracle.have_ref(), reason="needs the unmodified reference (oracle/_ref)")
+def test_reference_built_int_table_2m_with_updates_and_deletes():
+    from helpers import assert_probe_equal
+    N = 2_000_000
+    t = pyoracle.RefTable(1000, leaf_pool_blocks=N // 16)
+    assert t.load_ycsb_int(0, N) == N
+    rng = np.random.default_rng(2026)
+    upd = rng.integers(0, N, 200_000).astype(np.uint32)
+    assert t.commit_update_batch(u32_keys(upd), FIRST_CID) == len(upd)
+    dele = rng.choice(N, 20_000, replace=False).astype(np.uint32)
+    for k in dele:
+        assert t.delete(u32_keys(np.array([k], np.uint32))[0]) == 0
+    with sg.Snapshot.from_tree(t.root, 4, 1000) as snap:
+        assert snap.info().n_rows == N - len(dele)
+        pk = u32_keys(np.concatenate([rng.integers(0, N + 1000, 90_000).astype(np.uint32), dele[:5000], upd[:5000]]))
+        for read_ts in (0, FIRST_CID + 100_000, 0xFFFFFFFF):
+            assert_probe_equal(snap.probe(pk, read_ts), t.probe(pk, read_ts), f"2M int probes ts={read_ts}")
+        snap.counters(reset=True)
+        sk10 = u32_keys(rng.integers(0, N, 8000).astype(np.uint32))
+        for read_ts, vis in ((0xFFFFFFFF, 1), (FIRST_CID + 100_000, 1), (0, 0)):
+            assert_scan_equal(snap.scan(sk10, 10, read_ts, vis), t.scan(sk10, 10, read_ts, vis), f"2M int 10-row scans ts={read_ts}")
+        quirk10 = snap.counters(reset=True).slot_order_scans
+        assert quirk10 > 0.2 * 3 * len(sk10), "the slot-order rule should bite on a large share of the 10-row scans"
+        sk = u32_keys(rng.integers(0, N, 2000).astype(np.uint32))
+        assert_scan_equal(snap.scan(sk, 100, FIRST_CID + 50_000, 1), t.scan(sk, 100, FIRST_CID + 50_000, 1), "2M int 100-row scans")
+        assert_scan_equal(snap.scan(sk[:200], 1000, 0xFFFFFFFF, 1), t.scan(sk[:200], 1000, 0xFFFFFFFF, 1), "2M int 1000-row scans")
+
+
+@pytest.mark.skipif(not pyoracle.have_ref(), reason="needs the unmodified reference (oracle/_ref)")
+def test_reference_built_string_table_2m():
+    from helpers import assert_probe_equal
+    N = 2_000_000
+    keys = ycsb.random_strings(1804289383, N, 16)
+    t = pyoracle.RefTable(1000, catalog_key_len=16, leaf_pool_blocks=N // 16)
+    row = np.full((1, 1000), ord("a"), np.uint8)
+    for lo in range(0, N, 250_000):
+        assert t.insert(keys[lo:lo + 250_000], np.broadcast_to(row, (min(250_000, N - lo), 1000)), 0) == min(250_000, N - lo)
+    z = np.clip(ycsb.Zipf(N - 1, 0.9, seed=1).draw(95_000).astype(np.int64), 1, N) - 1
+    pk = np.concatenate([keys[z], ycsb.random_strings(99, 5000, 16)])
+    rng = np.random.default_rng(7)
+    with sg.Snapshot.from_tree(t.root, 16, 1000) as snap:
+        assert snap.info().n_rows == N
+        assert_probe_equal(snap.probe(pk, 1), t.probe(pk, 1), "2M string probes")
+        sk = np.concatenate([keys[rng.integers(0, N, 8000)], ycsb.random_strings(5, 1000, 16)])     # rows and absent keys
+        assert_scan_equal(snap.scan(sk, 10, 1, 1), t.scan(sk, 10, 1, 1), "2M string 10-row scans")
+        assert_scan_equal(snap.scan(sk[:1500], 100, 1, 0), t.scan(sk[:1500], 100, 1, 0), "2M string 100-row scans")
+        assert snap.counters().slot_order_scans > 0

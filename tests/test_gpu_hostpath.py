@@ -237,3 +237,46 @@ def test_scan_size_above_stride_is_clamped_on_device_and_rejected_on_host(mvcc_t
     want = t.scan(sk, np.array([20, 10], np.uint32), 0, 0)
     assert np.array_equal(pay[:2].cpu().numpy()[0], want[3][0])
     assert int((pay[2] != 0xEE).sum()) == 0 and int((kout[1, 10:] != 0xEE).sum()) == 0    # nothing written past a slab
+
+
+def test_batching_front_end_coalesces_concurrent_single_operations(mvcc_table):
+    """stage_gpu_batcher_*: 16 threads, each one operation at a time with its OWN read id (the reference's driver shape:
+    one executor per operation on N worker threads, ycsb_mixed.cpp:83-93). Every answer must be the checker's answer
+    for that (key, read id); the operations must have been coalesced (fewer batches than operations)."""
+    t, snap = mvcc_table
+    b = sg.Batcher(snap, max_batch=64, max_wait_us=200)
+    errors = []
+    n_threads, per = 16, 150
+
+    def worker(w):
+        try:
+            rng = np.random.default_rng(500 + w)
+            keys = rng.integers(0, 20050, per).astype(np.uint32)
+            stamps = rng.integers(0, 3200, per)
+            for k, ts in zip(keys, stamps):
+                kk = u32_keys(np.array([k], np.uint32))
+                if k % 5 == 0:
+                    S = int(rng.choice([5, 40, 300]))
+                    vis = int(k % 2)
+                    c, ko, to, po = b.scan(kk[0], S, int(ts), vis)
+                    wc, wk, wt, wp = t.scan(kk, S, int(ts), vis)
+                    assert c == wc[0] and np.array_equal(ko[:c], wk[0, :c]) and np.array_equal(to[:c], wt[0, :c]) \
+                        and np.array_equal(po[:c], wp[0, :c]), f"thread {w} scan key {k} ts {ts}"
+                else:
+                    f, s, ko, po = b.probe(kk[0], int(ts))
+                    wf, ws, wk, wp = t.probe(kk, int(ts))
+                    assert f == wf[0], f"thread {w} probe key {k} ts {ts}"
+                    if f:
+                        assert s == ws[0] and np.array_equal(ko, wk[0]) and np.array_equal(po, wp[0]), f"thread {w} key {k}"
+        except Exception as e:      # noqa: BLE001
+            errors.append(repr(e))
+
+    th = [threading.Thread(target=worker, args=(w,)) for w in range(n_threads)]
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    batches, ops = b.stats()
+    b.close()
+    assert not errors, errors[:3]
+    assert ops == n_threads * per and batches < ops, (batches, ops)

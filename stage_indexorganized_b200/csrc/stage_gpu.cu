@@ -1003,6 +1003,52 @@ struct LeafDiscovery {
     }
 };
 
+// Discovery over n leaves. Quiesced trees: contiguous ranges of leaves are discovered by the staging threads, each with
+// its own chain stager (version chains belong to one record each, so ranges never share a TupleHeader), then the parts are
+// concatenated and their version indices shifted. Live trees stay serial: the caller's resolver runs on the calling thread.
+template <class LeafAt>
+static int discover_all(LeafDiscovery &d, size_t n, LeafAt leaf_at) {
+    const unsigned T = (d.resolve || n < 4096) ? 1u : std::min<unsigned>(staging_threads(), 64u);
+    if (T <= 1) {
+        for (size_t i = 0; i < n; ++i) {
+            const int rc = d.discover(i, leaf_at(i));
+            if (rc) return rc;
+        }
+        return STAGE_OK;
+    }
+    std::vector<LeafDiscovery> part(T);
+    std::vector<int> rcs(T, STAGE_OK);
+    WorkPool::get().run(T, 1, [&](uint64_t tlo, uint64_t thi) {
+        for (uint64_t t = tlo; t < thi; ++t) {
+            const size_t lo = n * t / T, hi = n * (t + 1) / T;
+            LeafDiscovery &p = part[t];
+            p.schema = d.schema;
+            p.cs.base = d.cs.base;
+            p.init(hi - lo);
+            for (size_t i = lo; i < hi && !rcs[t]; ++i) rcs[t] = p.discover(i - lo, leaf_at(i));
+        }
+    });
+    for (unsigned t = 0; t < T; ++t)
+        if (rcs[t]) return rcs[t];
+    for (unsigned t = 0; t < T; ++t) {
+        const size_t lo = n * t / T, hi = n * (t + 1) / T;
+        LeafDiscovery &p = part[t];
+        const uint32_t voff = (uint32_t) d.cs.vers.size();           // versions staged by the parts before this one
+        for (stage_version_t v : p.cs.vers) {
+            if (v.next) v.next += voff;
+            d.cs.vers.push_back(v);
+        }
+        d.cs.vslot.insert(d.cs.vslot.end(), p.cs.vslot.begin(), p.cs.vslot.end());
+        const int64_t hbase = (int64_t) d.heads_flat.size();
+        for (uint32_t h : p.heads_flat) d.heads_flat.push_back(h ? h + voff : 0u);
+        for (size_t i = lo; i < hi; ++i) {
+            d.heads_at[i] = p.heads_at[i - lo] >= 0 ? p.heads_at[i - lo] + hbase : -1;
+            d.dropped[i] = p.dropped[i - lo];
+        }
+    }
+    return STAGE_OK;
+}
+
 static double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -1076,8 +1122,8 @@ static int from_tree_impl(const void *root, const stage_schema_t *schema, stage_
     d.init(w.leaves.size());
     ChainStager &cs = d.cs;
     std::vector<stage_version_t> &vers = cs.vers;
-    // pass 1 (serial, metadata only): version indices in leaf / slot order, in-flight records
-    for (size_t li = 0; li < w.leaves.size() && !rc; ++li) rc = d.discover(li, w.leaves[li]);
+    // pass 1 (metadata only): version indices in leaf / slot order, in-flight records
+    rc = discover_all(d, w.leaves.size(), [&](size_t li) { return w.leaves[li]; });
     PHASE("chain discovery");
     // pass 2: leaf images, copied by the staging threads (live trees: validated against pass 1, re-discovered on a miss)
     if (!rc)
@@ -1184,7 +1230,7 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
     ChainStager &cs = d.cs;
     cs.base = (uint32_t) old->n_versions;
     std::vector<uint32_t> &dropped = d.dropped;
-    for (size_t c = 0; c < changed.size() && !rc; ++c) rc = d.discover(c, w.leaves[changed[c]]);
+    rc = discover_all(d, changed.size(), [&](size_t c) { return w.leaves[changed[c]]; });
     if (rc) return rc;
     uint64_t n_rows = 0;
     for (size_t c = 0; c < changed.size(); ++c) vis[changed[c]] -= dropped[c];

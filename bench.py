@@ -50,7 +50,7 @@ PROBE_HIT_BYTES = K_BYTES + 2 * (K_BYTES + P_BYTES + 4)
 PROBE_MISS_BYTES = K_BYTES + 1
 # dram__bytes_read.sum + dram__bytes_write.sum of one gather_rows_kernel launch of the default workload, from the
 # committed `ncu --set full` capture (profiles/); None until a capture of the current kernel exists.
-NCU_TRAFFIC_PER_LAUNCH = 7.769e9   # profiles/r1_v10_ncu_summary.txt: 3.925 GB read + 3.844 GB written
+NCU_TRAFFIC_PER_LAUNCH = 7.767e9   # profiles/r2_ncu_summary.txt: 3.925 GB read + 3.843 GB written (7.792 GB algorithmic)
 
 
 def parse_args():
@@ -354,7 +354,8 @@ def e2e_legs(args, sg, torch, dist, dev, snap, sk_all, pk_all, read_ts, vis, bar
            "call": "stage_gpu_scan_batch(STAGE_IO_HOST | STAGE_IO_COMPACT), pinned buffers",
            "numa_bind_rank0": numa,
            "roofline": {"bound": "pcie", "peak": pcie, "unit": "GB/s",
-                        "peak_source": "measured in this run: one cudaMemcpyAsync D2H of 1 GiB into pinned memory, this rank alone",
+                        "peak_source": "measured in this run: one cudaMemcpyAsync D2H of 1 GiB into pinned memory per rank"
+                                       + (", all ranks copying at the same time (the box's shared host side included)" if world > 1 else ""),
                         "achieved": d2h_compact * args.steps / my_sec / 1e9,
                         "frac": d2h_compact * args.steps / my_sec / 1e9 / pcie},
            "strided_layout": {"value": rows_s / sec_s, "unit": "rows/s",

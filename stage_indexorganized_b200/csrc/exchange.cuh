@@ -423,6 +423,88 @@ __global__ void __launch_bounds__(kGatherThreads) exchange_gather16_kernel(Excha
     }
 }
 
+// ---- TMA row mover (opt-in, STAGE_XCHG_TMA=1) ---------------------------------------------------------------------
+// Same job as exchange_gather16_kernel, with the store side handed to the TMA unit: a warp loads kTmaRows rows from local
+// HBM into shared memory (8-byte loads: 1000-byte rows are only 8-byte aligned), then ONE lane issues one
+// cp.async.bulk shared -> global per row — a single bulk write of align16(P) bytes into the requester's slab row (slab
+// rows are padded to 128 B, so the few pad bytes land in the padding) instead of 63 lanes x 16-byte stores. Two groups of
+// kTmaRows buffers per warp: the next group is loaded while the previous group's bulk stores drain.
+constexpr int kTmaRows = 4;
+constexpr int kTmaGroups = 2;
+constexpr uint32_t kTmaRowBytes = 1024;       // shared-memory slot per row (P <= 1016)
+
+__device__ __forceinline__ void tma_store_1d(void *gmem_dst, const void *smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"((uint32_t) __cvta_generic_to_shared(smem_src)),
+                 "r"(bytes)
+                 : "memory");
+}
+
+__global__ void __launch_bounds__(kGatherThreads) exchange_gather_tma_kernel(ExchangeView x, ServeArgs a, const uint8_t *payload,
+                                                                            const uint8_t *ver_payload, uint32_t P) {
+    extern __shared__ __align__(128) uint8_t s_buf[];     // [warps][kTmaGroups][kTmaRows][kTmaRowBytes]
+    __shared__ uint32_t s_row[kGatherRows], s_dst[kGatherRows];
+    __shared__ uint32_t off[kMaxExchangeRanks + 1];
+    load_segments(x, off, a.seg_mul);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int kWarps = kGatherThreads / 32;
+    const uint32_t n8 = P / 8, bulk = (P + 15u) & ~15u;
+    uint8_t *wbuf = s_buf + (size_t) warp * kTmaGroups * kTmaRows * kTmaRowBytes;
+    __shared__ TilePlan plan;
+    make_tile_plan(&plan, off, x.world, x.rank, a.tile_order);
+    const uint32_t tiles = plan.tiles;
+    uint32_t grp = 0;
+    for (uint32_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+        uint32_t g0, gend;
+        tile_span(&plan, off, x.rank, a.tile_order, t, &g0, &gend);
+        __syncthreads();
+        if (tid < kGatherRows) {
+            const uint32_t g = g0 + tid;
+            s_row[tid] = g < gend ? a.src_row[g] : kNoRow;
+            s_dst[tid] = g < gend ? a.dst_slot[g] : 0u;
+        }
+        __syncthreads();
+        for (int r0 = warp * kTmaRows; r0 < kGatherRows; r0 += kWarps * kTmaRows) {
+            uint8_t *gbuf = wbuf + (size_t) (grp & 1) * kTmaRows * kTmaRowBytes;
+            // the bulk stores issued two groups ago have finished READING this group's buffers
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kTmaGroups - 1) : "memory");
+            __syncwarp();
+            uint2 v[kTmaRows][4];
+#pragma unroll
+            for (int u = 0; u < kTmaRows; ++u) {
+                const uint32_t row = s_row[r0 + u];
+                if (row == kNoRow) continue;
+                const uint8_t *base = (row & kVersionRowFlag) ? ver_payload : payload;
+                const uint2 *src = reinterpret_cast<const uint2 *>(base + (uint64_t) (row & ~kVersionRowFlag) * P);
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (lane + 32 * k < n8) v[u][k] = __ldcs(src + lane + 32 * k);
+            }
+#pragma unroll
+            for (int u = 0; u < kTmaRows; ++u) {
+                if (s_row[r0 + u] == kNoRow) continue;
+                uint2 *dst = reinterpret_cast<uint2 *>(gbuf + (size_t) u * kTmaRowBytes);
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (lane + 32 * k < n8) dst[lane + 32 * k] = v[u][k];
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> visible to the TMA unit
+            __syncwarp();
+            if (lane == 0) {
+#pragma unroll
+                for (int u = 0; u < kTmaRows; ++u) {
+                    if (s_row[r0 + u] == kNoRow) continue;
+                    const uint32_t d = s_dst[r0 + u];
+                    uint8_t *dst = x.arena[d >> kDstRankShift] + x.lay.off_payload + (uint64_t) (d & kDstIndexMask) * x.lay.pstride;
+                    tma_store_1d(dst, gbuf + (size_t) u * kTmaRowBytes, bulk);
+                }
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            ++grp;
+        }
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // all rows written before the kernel ends
+}
+
 // ---- routed push-down ("return 4-16 B per probe instead of 416-1004 B, lifts the NVLink bound") ------
 // Column projection: after exchange_serve_kernel has located and MVCC-filtered every inbox entry, only payload bytes
 // [col_off, col_off + col_len) of each found row cross NVLink, into the requester's slab at stride col_stride (rows of

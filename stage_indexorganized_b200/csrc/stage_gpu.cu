@@ -3050,6 +3050,24 @@ static int exchange_move_rows(stage_exchange *x, stage_snapshot *s, const ServeA
     // vector width: every arena and the payload offset are 256-byte aligned, so the row stride decides
     const uintptr_t align = (uintptr_t) s->d_payload | (uintptr_t) s->d_ver_payload | s->schema.payload_size;
     static const bool no16 = getenv("STAGE_XCHG_NO16") != nullptr;
+    const char *tma = getenv("STAGE_XCHG_TMA");                 // read per call: tools/xchg_sweep.py flips it between runs
+    const char *cps = getenv("STAGE_XCHG_CTAS_PER_SM");
+    const int ctas_per_sm = cps ? std::max(1, atoi(cps)) : 0;   // 0 = as many as fit
+    if (tma && atoi(tma) != 0 && (align & 7) == 0 && s->schema.payload_size <= 1016 && x->view.lay.pstride >= ((s->schema.payload_size + 15u) & ~15u)) {
+        const size_t smem = (size_t) (kGatherThreads / 32) * kTmaGroups * kTmaRows * kTmaRowBytes;
+        static int occt = 0;
+        if (!occt) {
+            CUDA_TRY(cudaFuncSetAttribute(exchange_gather_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+            int o = 0;
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, exchange_gather_tma_kernel, kGatherThreads, smem));
+            occt = std::max(o, 1);
+        }
+        const int per_sm = ctas_per_sm ? std::min(ctas_per_sm, occt) : occt;
+        exchange_gather_tma_kernel<<<sm_count() * per_sm, kGatherThreads, smem, st>>>(x->view, a, s->d_payload, s->d_ver_payload,
+                                                                                   s->schema.payload_size);
+        LAUNCH_CHECK();
+        return STAGE_OK;
+    }
     if ((align & 15) == 0) rc = launch_exchange_gather<uint4>(x, s, a, st);
     else if ((align & 7) == 0 && !no16) {
         static int occ16 = 0;
@@ -3058,8 +3076,8 @@ static int exchange_move_rows(stage_exchange *x, stage_snapshot *s, const ServeA
             CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, exchange_gather16_kernel<4>, kGatherThreads, 0));
             occ16 = std::max(o, 1);
         }
-        exchange_gather16_kernel<4><<<sm_count() * occ16, kGatherThreads, 0, st>>>(x->view, a, s->d_payload, s->d_ver_payload,
-                                                                                 s->schema.payload_size);
+        exchange_gather16_kernel<4><<<sm_count() * (ctas_per_sm ? std::min(ctas_per_sm, occ16) : occ16), kGatherThreads, 0, st>>>(
+            x->view, a, s->d_payload, s->d_ver_payload, s->schema.payload_size);
         LAUNCH_CHECK();
     }
     else if ((align & 7) == 0) rc = launch_exchange_gather<uint2>(x, s, a, st);
@@ -3090,8 +3108,7 @@ static int exchange_serve_common(stage_exchange_t *x, stage_snapshot_t *s, uint3
     a.dst_slot = x->d_dst_slot;
     a.seg_mul = 1;
     if (x->view.lay.rows != 1) return STAGE_ERR_STATE;
-    static const int order = getenv("STAGE_XCHG_ORDER") ? atoi(getenv("STAGE_XCHG_ORDER")) : 1;   // shift schedule (exchange.cuh)
-    a.tile_order = order;
+    a.tile_order = getenv("STAGE_XCHG_ORDER") ? atoi(getenv("STAGE_XCHG_ORDER")) : 1;             // 1 = shift schedule (exchange.cuh)
     int rc;
     switch (x->nw) {
         case 1: rc = launch_serve<1>(x, s, a, st); break;

@@ -308,3 +308,17 @@ def test_routed_pushdown_matches_unsharded_table(world, flags):
     finally:
         for s in shards:
             s.close()
+
+
+def test_tma_row_mover_variant():
+    """STAGE_XCHG_TMA=1: payload rows leave through cp.async.bulk shared -> global stores (one bulk write per row) instead
+    of per-lane 16-byte stores. Same results: the routed probe / scan tests of this file re-run in a child process."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("STAGE_VARIANT_RUN"):
+        pytest.skip("already inside a variant run")
+    env = dict(os.environ, STAGE_XCHG_TMA="1", STAGE_VARIANT_RUN="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-m", "gpu", "-k",
+                        "routed_probe or routed_scans"], env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]

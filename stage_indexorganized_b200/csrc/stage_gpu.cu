@@ -1030,22 +1030,33 @@ static int discover_all(LeafDiscovery &d, size_t n, LeafAt leaf_at) {
     });
     for (unsigned t = 0; t < T; ++t)
         if (rcs[t]) return rcs[t];
+    // concatenate the parts (offsets first, then every part copies itself into place in parallel)
+    std::vector<size_t> voff(T + 1, d.cs.vers.size()), hoff(T + 1, d.heads_flat.size());
     for (unsigned t = 0; t < T; ++t) {
-        const size_t lo = n * t / T, hi = n * (t + 1) / T;
-        LeafDiscovery &p = part[t];
-        const uint32_t voff = (uint32_t) d.cs.vers.size();           // versions staged by the parts before this one
-        for (stage_version_t v : p.cs.vers) {
-            if (v.next) v.next += voff;
-            d.cs.vers.push_back(v);
-        }
-        d.cs.vslot.insert(d.cs.vslot.end(), p.cs.vslot.begin(), p.cs.vslot.end());
-        const int64_t hbase = (int64_t) d.heads_flat.size();
-        for (uint32_t h : p.heads_flat) d.heads_flat.push_back(h ? h + voff : 0u);
-        for (size_t i = lo; i < hi; ++i) {
-            d.heads_at[i] = p.heads_at[i - lo] >= 0 ? p.heads_at[i - lo] + hbase : -1;
-            d.dropped[i] = p.dropped[i - lo];
-        }
+        voff[t + 1] = voff[t] + part[t].cs.vers.size();
+        hoff[t + 1] = hoff[t] + part[t].heads_flat.size();
     }
+    d.cs.vers.resize(voff[T]);
+    d.cs.vslot.resize(voff[T]);
+    d.heads_flat.resize(hoff[T]);
+    WorkPool::get().run(T, 1, [&](uint64_t tlo, uint64_t thi) {
+        for (uint64_t t = tlo; t < thi; ++t) {
+            const size_t lo = n * t / T, hi = n * (t + 1) / T;
+            LeafDiscovery &p = part[t];
+            const uint32_t shift = (uint32_t) (voff[t] - voff[0]);       // versions staged by the parts before this one
+            for (size_t i = 0; i < p.cs.vers.size(); ++i) {
+                stage_version_t v = p.cs.vers[i];
+                if (v.next) v.next += shift;
+                d.cs.vers[voff[t] + i] = v;
+                d.cs.vslot[voff[t] + i] = p.cs.vslot[i];
+            }
+            for (size_t i = 0; i < p.heads_flat.size(); ++i) d.heads_flat[hoff[t] + i] = p.heads_flat[i] ? p.heads_flat[i] + shift : 0u;
+            for (size_t i = lo; i < hi; ++i) {
+                d.heads_at[i] = p.heads_at[i - lo] >= 0 ? p.heads_at[i - lo] + (int64_t) hoff[t] : -1;
+                d.dropped[i] = p.dropped[i - lo];
+            }
+        }
+    });
     return STAGE_OK;
 }
 

@@ -761,6 +761,15 @@ def main():
         pp.x.enable_timing(False)
         probe["phase_ms_rank0"] = dict(zip(("post", "search_incl_wait_for_posts", "rows", "wait_for_owners"),
                                            [float(np.mean(c)) for c in zip(*phases)]))
+        # the link ceiling of THIS box for this traffic pattern: copy engines, every rank into every other rank's slab at once
+        link = pp.measure_link_ceiling()
+        rows_ms = probe["phase_ms_rank0"]["rows"]
+        row_phase_gbps = n_probes * remote * hit_rate * P_BYTES / (rows_ms * 1e-3) / 1e9
+        probe["roofline"].update({"nvlink_measured_all_to_all_copy": link, "row_phase_nvlink_achieved": row_phase_gbps,
+                                  "row_phase_frac_of_measured_copy": row_phase_gbps / link if link else None,
+                                  "row_phase_frac_of_770": row_phase_gbps / nvl_peak,
+                                  "note": "nvlink_measured_all_to_all_copy = cudaMemcpyAsync peer copies of equal slab slices, all "
+                                          "ranks sending and receiving at once (both directions busy), max over ranks"})
         # comparison: the same probes with NCCL all-to-all collectives around the local kernels
         d_owner = torch.empty((n_probes,), dtype=torch.int32, device=dev)
 

@@ -380,6 +380,10 @@ int stage_gpu_exchange_serve_scans(stage_exchange_t *x, stage_snapshot_t *shard,
  * row_counts[q] keep their previous content. */
 int stage_gpu_exchange_scan_results(stage_exchange_t *x, void **row_counts, void **key_out, void **ts, void **payload,
                                     uint32_t *rows_per_scan, uint32_t *key_stride, uint32_t *payload_stride);
+/* Measurement helper: one cudaMemcpyAsync of `bytes` from this rank's result slab into rank dst_rank's slab at byte
+ * dst_offset (copy engine over NVLink). Timed on all ranks at once it gives the box's link ceiling for the exchange's
+ * traffic pattern. The slab contents are undefined afterwards, until the next batch. */
+int stage_gpu_exchange_peer_copy(stage_exchange_t *x, uint32_t dst_rank, uint64_t dst_offset, uint64_t bytes, void *cuda_stream);
 /* Sticky device-side error of the exchange: 0 ok, 1 inbox overflow, 2 device-sync timeout. Synchronises the stream. */
 int stage_gpu_exchange_error(stage_exchange_t *x, void *cuda_stream, uint32_t *err_out);
 /* Per-phase timing of the last post/serve/wait sequence (STAGE_XCHG_DEVICE_SYNC), CUDA events on the caller's stream:

@@ -109,6 +109,7 @@ SYMBOLS = {
     "stage_gpu_exchange_serve_scans": (_i32, [_vp, _vp, _u32, _i32, _i32, _vp]),
     "stage_gpu_exchange_scan_results": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),
                                                C.POINTER(_u32), C.POINTER(_u32), C.POINTER(_u32)]),
+    "stage_gpu_exchange_peer_copy": (_i32, [_vp, _u32, _u64, _u64, _vp]),
     "stage_gpu_exchange_error": (_i32, [_vp, _vp, C.POINTER(_u32)]),
     "stage_gpu_exchange_enable_timing": (_i32, [_vp, _i32]),
     "stage_gpu_exchange_last_timing": (_i32, [_vp, C.POINTER(C.c_float)]),
@@ -637,6 +638,9 @@ class ProbeExchange:
 
     def wait(self, cuda_stream=0):
         _check(lib().stage_gpu_exchange_wait(self.h, _vp(int(cuda_stream))))
+
+    def peer_copy(self, dst_rank, dst_offset, nbytes, cuda_stream=0):
+        _check(lib().stage_gpu_exchange_peer_copy(self.h, dst_rank, dst_offset, nbytes, _vp(int(cuda_stream))))
 
     def error(self, cuda_stream=0):
         e = _u32(0)

@@ -3279,6 +3279,19 @@ extern "C" int stage_gpu_exchange_results(stage_exchange_t *x, void **found, voi
     return STAGE_OK;
 }
 
+// Measurement helper: ONE cudaMemcpyAsync of `bytes` from this rank's result slab into rank dst_rank's result slab (peer
+// memory over NVLink, copy engine). bench.py / tools/xchg_sweep.py time it on all ranks at once to get the link ceiling
+// for the exchange's traffic pattern on the box at hand; the slab contents are garbage afterwards (until the next batch).
+extern "C" int stage_gpu_exchange_peer_copy(stage_exchange_t *x, uint32_t dst_rank, uint64_t dst_offset, uint64_t bytes, void *cuda_stream) {
+    if (!x || dst_rank >= x->view.world || !x->attached) return STAGE_ERR_ARG;
+    const uint64_t cap_bytes = (uint64_t) x->view.lay.cap * x->view.lay.rows * x->view.lay.pstride;
+    if (dst_offset + bytes > cap_bytes || bytes > cap_bytes) return STAGE_ERR_ARG;
+    CUDA_TRY(cudaSetDevice(x->device));
+    CUDA_TRY(cudaMemcpyAsync(x->view.arena[dst_rank] + x->view.lay.off_payload + dst_offset, x->arena + x->view.lay.off_payload, bytes,
+                             cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(cuda_stream)));
+    return STAGE_OK;
+}
+
 extern "C" int stage_gpu_exchange_error(stage_exchange_t *x, void *cuda_stream, uint32_t *err_out) {
     if (!x || !err_out) return STAGE_ERR_ARG;
     CUDA_TRY(cudaSetDevice(x->device));

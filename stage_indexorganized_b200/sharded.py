@@ -137,6 +137,32 @@ class PeerProbe:
             self._barrier()
         return self.x.results_torch(n)
 
+    def measure_link_ceiling(self, reps=3):
+        """GB/s per direction per GPU that the copy engines reach on THIS box for the exchange's traffic pattern: every rank
+        copies an equal slice of its slab into every other rank's slab, all ranks at once (best of `reps`, max over
+        ranks). The slab contents are garbage afterwards."""
+        if self.world == 1:
+            return None
+        _, _, _, stride = self.x.result_ptrs()
+        total = self.x.capacity * stride
+        per = (total // self.world) // 4096 * 4096
+        stream = torch.cuda.current_stream()
+        best = None
+        for _ in range(reps + 1):
+            torch.cuda.synchronize()
+            dist.barrier(self.group)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for d in range(1, self.world):
+                self.x.peer_copy((self.rank + d) % self.world, self.rank * per, per, stream.cuda_stream)
+            e1.record(stream)
+            torch.cuda.synchronize()
+            ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=torch.device("cuda", torch.cuda.current_device()))
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX, group=self.group)
+            best = float(ms.item()) if best is None else min(best, float(ms.item()))
+        dist.barrier(self.group)
+        return per * (self.world - 1) / (best * 1e-3) / 1e9
+
     def probe_column(self, keys_dev, n, read_ts, col_off, col_len):
         """Routed probes with column push-down: only payload bytes [col_off, col_off + col_len) of every found row cross
         NVLink. Returns (found, ts, col[n, col_len]) views of this rank's result slab."""

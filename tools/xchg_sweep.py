@@ -47,6 +47,12 @@ def main():
     variants.append(("batch=2^22", {}, 1 << 22))
     variants.append(("tma batch=2^22", {"STAGE_XCHG_TMA": "1"}, 1 << 22))
     knobs = ("STAGE_XCHG_CTAS_PER_SM", "STAGE_XCHG_ORDER", "STAGE_XCHG_TMA")
+    pp0 = sharded.PeerProbe(snap, split, 1 << 20, device_sync=True)
+    link = pp0.measure_link_ceiling()
+    pp0.close()
+    if rank == 0:
+        print(json.dumps({"variant": "link ceiling: peer copies (copy engines), all ranks at once, GB/s per direction per GPU",
+                          "world": world, "GBps": link}), flush=True)
     for name, env, n in variants:
         for k in knobs:
             os.environ.pop(k, None)

@@ -286,13 +286,15 @@ def run_extra_workload(args):
     print(json.dumps(line), flush=True)
 
 
-def measure_pcie_d2h(torch, dev, mb=1024, reps=3):
+def measure_pcie_d2h(torch, dev, mb=1024, reps=3, barrier=None):
     """The link ceiling the e2e legs are held against, measured in this run the plain way: ONE cudaMemcpyAsync of
     `mb` MiB from HBM into pinned host memory (torch copy_ non_blocking = one cudaMemcpyAsync), best of `reps`."""
     d = torch.empty(mb << 20, dtype=torch.uint8, device=dev)
     h = torch.empty(mb << 20, dtype=torch.uint8, pin_memory=True)
     best = None
     for _ in range(reps + 1):
+        if barrier is not None:
+            barrier()               # N > 1: every rank copies at the same moment (the box's host side is shared)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         h.copy_(d, non_blocking=True)
@@ -319,7 +321,7 @@ def e2e_legs(args, sg, torch, dist, dev, snap, sk_all, pk_all, read_ts, vis, bar
     h_key = sg.PinnedArray((ne * S, K_BYTES), np.uint8)
     h_ts = sg.PinnedArray((ne * S,), np.uint32)
     h_pay = sg.PinnedArray((ne * S, P_BYTES), np.uint8)
-    pcie = measure_pcie_d2h(torch, dev)
+    pcie = measure_pcie_d2h(torch, dev, barrier=barrier if world > 1 else None)
 
     def timed(step_fn):
         for b in range(min(args.warmup, 2)):
@@ -355,7 +357,9 @@ def e2e_legs(args, sg, torch, dist, dev, snap, sk_all, pk_all, read_ts, vis, bar
            "numa_bind_rank0": numa,
            "roofline": {"bound": "pcie", "peak": pcie, "unit": "GB/s",
                         "peak_source": "measured in this run: one cudaMemcpyAsync D2H of 1 GiB into pinned memory per rank"
-                                       + (", all ranks copying at the same time (the box's shared host side included)" if world > 1 else ""),
+                                       + (", all ranks copying at the same moment (barrier before every copy): the box's shared host side included; "
+                                          "tools/pcie_ceiling on an 8-GPU box of the pool: 57 / 72 / 73 / 94 GB/s in total at 1 / 2 / 4 / 8 "
+                                          "GPUs (profiles/r2_pcie_ceiling_8gpu.txt)" if world > 1 else ""),
                         "achieved": d2h_compact * args.steps / my_sec / 1e9,
                         "frac": d2h_compact * args.steps / my_sec / 1e9 / pcie},
            "strided_layout": {"value": rows_s / sec_s, "unit": "rows/s",

@@ -3063,7 +3063,9 @@ static int exchange_move_rows(stage_exchange *x, stage_snapshot *s, const ServeA
     static const bool no16 = getenv("STAGE_XCHG_NO16") != nullptr;
     const char *tma = getenv("STAGE_XCHG_TMA");                 // read per call: tools/xchg_sweep.py flips it between runs
     const char *cps = getenv("STAGE_XCHG_CTAS_PER_SM");
-    const int ctas_per_sm = cps ? std::max(1, atoi(cps)) : 0;   // 0 = as many as fit
+    // 0 = as many as fit. From four ranks on, two CTAs per SM keep a narrower window of every requester's slab in flight
+    // and were 2-4 % faster in the row phase (profiles/r2_xchg_sweep_n8.txt); at two ranks full occupancy is (slightly) better
+    const int ctas_per_sm = cps ? std::max(1, atoi(cps)) : (x->view.world >= 4 ? 2 : 0);
     if (tma && atoi(tma) != 0 && (align & 7) == 0 && s->schema.payload_size <= 1016 && x->view.lay.pstride >= ((s->schema.payload_size + 15u) & ~15u)) {
         const size_t smem = (size_t) (kGatherThreads / 32) * kTmaGroups * kTmaRows * kTmaRowBytes;
         static int occt = 0;

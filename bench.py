@@ -50,6 +50,7 @@ PROBE_HIT_BYTES = K_BYTES + 2 * (K_BYTES + P_BYTES + 4)
 PROBE_MISS_BYTES = K_BYTES + 1
 # dram__bytes_read.sum + dram__bytes_write.sum of one gather_rows_kernel launch of the default workload, from the
 # committed `ncu --set full` capture (profiles/); None until a capture of the current kernel exists.
+NCU_PROBE_GATHER_TRAFFIC = 2.0705e9   # gather_rows_kernel, probe mode, 2^20 probes: 1.122 GB read + 0.949 GB written (same capture)
 NCU_TRAFFIC_PER_LAUNCH = 7.767e9   # profiles/r2_ncu_summary.txt: 3.925 GB read + 3.843 GB written (7.792 GB algorithmic)
 
 
@@ -703,7 +704,8 @@ def main():
                  "hit_rate": hits / nprobe, "plan_ms": sum(pp) / len(pp), "gather_ms": sum(pg) / len(pg),
                  "roofline": {"bound": "hbm", "kernel": "stage::probe_fused_kernel (search + MVCC + payload rows)" if fused
                               else "stage::gather_rows_kernel", "achieved": g_ach, "peak": peak,
-                              "unit": "GB/s", "frac": g_ach / peak, "traffic": None,
+                              "unit": "GB/s", "frac": g_ach / peak,
+                              "traffic": NCU_PROBE_GATHER_TRAFFIC if (n_probes == 1 << 20 and not fused) else None,
                               "step_achieved": pbytes / (pms * 1e-3) / 1e9,
                               "step_frac": pbytes / (pms * 1e-3) / 1e9 / peak}}
 

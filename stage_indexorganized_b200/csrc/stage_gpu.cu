@@ -34,6 +34,7 @@
 #include "generate.cuh"
 #include "exchange.cuh"
 #include "probe_fused.cuh"
+#include "probe_rows.cuh"
 #include "refresh.cuh"
 #include "tpcc_ops.cuh"
 #include <cub/device/device_radix_sort.cuh>
@@ -1915,6 +1916,35 @@ static int launch_probe_fused(stage_snapshot *s, cudaStream_t st, const ProbeArg
     return launch_probe_fused_v<NW, uint8_t>(s, st, a, payload_out);
 }
 
+constexpr bool kProbeRowsDefault = false;            // set by measurement, see profiles/README.md
+constexpr uint32_t kProbeRowsDefaultMaxRow = 512;
+// lookup + rows in one kernel, the warp that found 32 rows copies them (probe_rows.cuh). STAGE_PROBE_ROWS=1 forces it,
+// =0 forbids it; default: see probe_device.
+template <int NW, typename V, int U>
+static int launch_probe_rows_v(stage_snapshot *s, cudaStream_t st, const ProbeArgs &a, uint8_t *payload_out) {
+    static int occ = 0;
+    if (!occ) {
+        int o = 0;
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, probe_rows_kernel<NW, V, U>, kProbeRowsThreads, 0));
+        occ = std::max(o, 1);
+    }
+    const uint64_t want = (a.n + kProbeRowsThreads - 1) / kProbeRowsThreads;
+    const unsigned blocks = (unsigned) std::min<uint64_t>(want, (uint64_t) sm_count() * occ);
+    probe_rows_kernel<NW, V, U><<<blocks, kProbeRowsThreads, 0, st>>>(s->view, a, payload_out);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+template <int NW>
+static int launch_probe_rows(stage_snapshot *s, cudaStream_t st, const ProbeArgs &a, uint8_t *payload_out) {
+    const uintptr_t align = (uintptr_t) s->d_payload | (uintptr_t) s->d_ver_payload | (uintptr_t) payload_out | s->schema.payload_size;
+    if ((align & 15) == 0) return launch_probe_rows_v<NW, uint4, 5>(s, st, a, payload_out);
+    return launch_probe_rows_v<NW, uint2, 8>(s, st, a, payload_out);
+}
+static bool probe_rows_eligible(const stage_snapshot *s, const uint8_t *payload_out) {
+    const uintptr_t align = (uintptr_t) s->d_payload | (uintptr_t) s->d_ver_payload | (uintptr_t) payload_out | s->schema.payload_size;
+    return s->view.dir != nullptr && payload_out != nullptr && (align & 7) == 0 && s->schema.payload_size >= 64;
+}
+
 // search + MVCC + payload rows. Default: probe_kernel then gather_rows_kernel (0.398 ms per 2^20 YCSB probes);
 // STAGE_PROBE_FUSED=1 selects the warp-specialised single kernel of probe_fused.cuh (measured 0.437 ms: under a
 // saturated memory system the producers' dependent loads are too slow to keep the consumers fed — profiles/README.md).
@@ -1939,6 +1969,28 @@ static int probe_device(stage_snapshot *s, const Lane &ln, ProbeArgs a, uint8_t 
             s->timed_gather = true;
         }
         return rc;
+    }
+    {
+        const char *e = getenv("STAGE_PROBE_ROWS");
+        const int mode = e ? atoi(e) : -1;                                   // -1 = default rule
+        const bool use = mode == 1 || (mode == -1 && kProbeRowsDefault && s->schema.payload_size <= kProbeRowsDefaultMaxRow);
+        if (use && probe_rows_eligible(s, payload_out)) {
+            if (ln.timing) {
+                CUDA_TRY(cudaEventRecord(s->tev[0], ln.st));
+                CUDA_TRY(cudaEventRecord(s->tev[1], ln.st));
+            }
+            switch (s->nw) {
+                case 1: rc = launch_probe_rows<1>(s, ln.st, a, payload_out); break;
+                case 2: rc = launch_probe_rows<2>(s, ln.st, a, payload_out); break;
+                case 4: rc = launch_probe_rows<4>(s, ln.st, a, payload_out); break;
+                default: rc = launch_probe_rows<8>(s, ln.st, a, payload_out); break;
+            }
+            if (ln.timing) {
+                CUDA_TRY(cudaEventRecord(s->tev[2], ln.st));
+                s->timed_gather = true;
+            }
+            return rc;
+        }
     }
     if (payload_out) {
         if ((rc = ln.srcrow->ensure(a.n * 4))) return rc;

@@ -303,3 +303,21 @@ def test_physical_scan(key_size, payload):
         assert np.array_equal(k2, want_k[1234:2011]) and np.array_equal(p2, want_p[1234:2011])
         with pytest.raises(sg.StageError):
             snap.scan_physical(len(want_k) - 5, 6)
+
+
+def test_probe_rows_kernel_variant():
+    """STAGE_PROBE_ROWS=1: directory lookup, MVCC and the payload rows in ONE kernel (the warp that found 32 rows copies
+    them, csrc/probe_rows.cuh). Same bytes as the two-kernel path: the probe tests of this file, the goldens, the TPC-C and
+    host-path tests re-run in a child process with the variant forced on."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("STAGE_VARIANT_RUN"):
+        pytest.skip("already inside a variant run")
+    env = dict(os.environ, STAGE_PROBE_ROWS="1", STAGE_VARIANT_RUN="1", STAGE_TEST_TPCC_W="4")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), os.path.join(here, "test_gpu_golden.py"),
+                        os.path.join(here, "test_gpu_tpcc.py"), os.path.join(here, "test_gpu_hostpath.py"), "-x", "-q", "-m", "gpu",
+                        "-k", "probe or mvcc or other_key or golden or q2 or stock_level_shape or batching"], env=env,
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]

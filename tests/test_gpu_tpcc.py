@@ -1,5 +1,7 @@
 """GPU: BASELINE configs[3] — TPC-C stock-level / CH-Q2* read pattern over the index-organized stock and order_line
-tables at w = 30 (STAGE_TEST_TPCC_W overrides), bit-exact against the CPU checker on the same host-built trees.
+tables at w = 30 (STAGE_TEST_TPCC_W overrides), bit-exact against the CPU checker — the unmodified reference when its
+prebuilt library is there, else the C restatement — on the same host-built trees (rows from stage_indexorganized_b200/tpcc.py,
+whose shapes tests/test_tpcc_rows.py pins to the reference's own BuildStockTuple / BuildOrderLineTuple).
 
 Workload A (RunStockLevel, benchmark/tpcc/tpcc_stock_level.cpp:37-196): per transaction 20 MVCC scans of 10
 order_line rows from {w, d, o, 5}, then point probes of stock for the OL_I_IDs of the rows of that order.
@@ -24,10 +26,14 @@ W = int(os.environ.get("STAGE_TEST_TPCC_W", "30"))
 def tables():
     sg.init(0)
     sk, sp = tpcc.stock_rows(W)
-    stock = pyoracle.OracleTable(tpcc.STOCK_PAYLOAD, split_threshold=65536)
-    assert stock.insert(sk, sp, 0) == len(sk)
     ok, op, _ = tpcc.order_line_rows(W)
-    ol = pyoracle.OracleTable(tpcc.OL_PAYLOAD, split_threshold=65536)
+    if pyoracle.have_ref():        # the unmodified reference builds the trees (TPC-C's ParameterSet, tpcc.cpp:78) and checks the reads
+        stock = pyoracle.RefTable(tpcc.STOCK_PAYLOAD, split_threshold=65536, catalog_key_len=16, leaf_pool_blocks=max(len(sk) // 40, 4096))
+        ol = pyoracle.RefTable(tpcc.OL_PAYLOAD, split_threshold=65536, catalog_key_len=32, leaf_pool_blocks=max(len(ok) // 100, 4096))
+    else:
+        stock = pyoracle.OracleTable(tpcc.STOCK_PAYLOAD, split_threshold=65536)
+        ol = pyoracle.OracleTable(tpcc.OL_PAYLOAD, split_threshold=65536)
+    assert stock.insert(sk, sp, 0) == len(sk)
     assert ol.insert(ok, op, 0) == len(ok)
     # some committed updates of S_QUANTITY-bearing rows so that the MVCC branch is exercised too
     rng = np.random.default_rng(4)

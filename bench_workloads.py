@@ -203,6 +203,14 @@ def config3(args, sg, torch, dev, peak, cpu=True, W=30, cpu_w=4):
     def agg_step(b):
         agg[0] = stock.probe_aggregate_i32(pk[b], 1, 0, 15, n=n)
     ms_agg = _time_steps(torch, agg_step, warm, steps)
+    # CH-Q2*'s loop over the 10 000 suppliers as one call: every (w, i) of supp_stock_map grouped by supplier, one
+    # 24-byte record (MIN(S_QUANTITY), its row, the row the reference's loop keeps) per supplier
+    qk, qoff = tpcc.q2_all_supplier_keys(W)
+    d_qk, d_qoff = torch.from_numpy(qk).to(dev), torch.from_numpy(qoff.astype(np.int64)).to(dev)
+    d_qout = torch.zeros((len(qoff) - 1, 24), dtype=torch.uint8, device=dev)
+    ms_q2 = _time_steps(torch, lambda b: stock.probe_group_aggregate_i32(d_qk, d_qoff, 1, 0, 32767, n=len(qk), out=d_qout), warm, steps)
+    q2rec = d_qout.cpu().numpy().view(sg.GROUP_AGG_I32).ravel()
+    del d_qk
     ol_row = 2 * (tpcc.OL_KEY + tpcc.OL_PAYLOAD + 4)
     st_row = tpcc.STOCK_KEY + 2 * (tpcc.STOCK_KEY + tpcc.STOCK_PAYLOAD + 4)
     ol_ach = (rows * ol_row + ns * (tpcc.OL_KEY + 8)) / (ms_scan * 1e-3) / 1e9
@@ -223,7 +231,13 @@ def config3(args, sg, torch, dev, peak, cpu=True, W=30, cpu_w=4):
                                     "roofline": {"bound": "hbm", "achieved": st_ach, "peak": peak, "frac": st_ach / peak}},
            "stock_probe_quantity_pushdown": {"value": n / (ms_col * 1e-3), "unit": "probes/s", "bytes_returned_per_probe": 5},
            "stock_probe_quantity_aggregate": {"value": n / (ms_agg * 1e-3), "unit": "probes/s", "bytes_returned_per_batch": 24,
-                                              "below_threshold_15": int(agg[0].below), "min_quantity": int(agg[0].min_value)}}
+                                              "below_threshold_15": int(agg[0].below), "min_quantity": int(agg[0].min_value)},
+           "q2_supplier_loop": {"value": len(qk) / (ms_q2 * 1e-3), "unit": "probes/s", "ms_per_step": ms_q2,
+                                "suppliers_per_step": len(qoff) - 1, "probes_per_step": len(qk),
+                                "suppliers_per_s": (len(qoff) - 1) / (ms_q2 * 1e-3), "bytes_returned_per_supplier": 24,
+                                "found": int(q2rec["found"].sum()), "min_quantity": int(q2rec["min_value"].min()),
+                                "note": "stage_gpu_probe_group_aggregate_i32: the stock probes of all 10 000 suppliers "
+                                        "(supp_stock_map order) with one record per supplier, device-resident keys"}}
     # the whole read side of RunStockLevel as one device-side operator (stage_gpu_tpcc_stock_level): 20 scans + first
     # item + stock probe + threshold + distinct count per transaction, 4 bytes per transaction returned
     req = np.zeros((nb, txns), sg.STOCK_LEVEL_REQ)

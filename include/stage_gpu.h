@@ -93,7 +93,10 @@ enum {
 /* STAGE_IO_HOST results are produced into double-buffered HBM scratch and copied out by the DMA engine (one large
  * copy per output array and chunk) while the next chunk is planned and gathered; pinned buffers (stage_gpu_host_alloc,
  * stage_gpu_host_register) make those copies run at link speed. STAGE_HOST_PATH=zerocopy lets the kernels store into
- * pinned outputs directly instead (lower latency for small batches, lower bandwidth for large ones). */
+ * pinned outputs directly instead (lower latency for small batches, lower bandwidth for large ones). Calls whose keys
+ * and results fit 192 KiB (a handful of operations: what one executor of the reference issues) skip the staging: the
+ * kernels work on a pinned slab of the call context through its device alias — memcpy in, two launches, one stream
+ * synchronisation, memcpy out. */
 
 /* ---- lifecycle --------------------------------------------------------------------------- */
 
@@ -269,6 +272,30 @@ typedef struct {
 } stage_agg_i32_t;
 int stage_gpu_probe_aggregate_i32(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint32_t col_off,
                                   int32_t threshold, stage_agg_i32_t *out, int flags);
+
+/* The same reduction per GROUP of consecutive probes: CH-Q2* loops over the suppliers and reduces the ~300 stock rows
+ * of each (benchmark/tpcc/tpcc_new_order.cpp:803-866; the (w, i) lists come from supp_stock_map,
+ * benchmark/tpcc/tpcc_workload.cpp:581-585). Group g = probes [group_offsets[g], group_offsets[g+1]); group_offsets has
+ * n_groups + 1 ascending entries, [0] = 0 and [n_groups] = n <= 2^26. One 24-byte record per group comes back:
+ *   found, below            probes of the group that hit a visible version / whose column is < threshold
+ *   min_value, max_value    over the found rows (INT32_MAX / INT32_MIN when none)
+ *   min_index               batch index of the FIRST probe attaining min_value ("the stock tuple having min. stock
+ *                           level"), 0xFFFFFFFF when none
+ *   last_below_index        batch index of the LAST found probe whose column is < threshold, 0xFFFFFFFF when none — with
+ *                           threshold = 32767 this is the row the reference's loop literally keeps: its running minimum
+ *                           is never lowered (min_qty stays INT16_MAX, tpcc_new_order.cpp:810-860), so every row below it
+ *                           overwrites the pick
+ * keys, group_offsets and out all follow `flags` (host or device). */
+typedef struct {
+    uint32_t found, below;
+    int32_t min_value;
+    uint32_t min_index;
+    int32_t max_value;
+    uint32_t last_below_index;
+} stage_group_agg_i32_t;
+int stage_gpu_probe_group_aggregate_i32(stage_snapshot_t *s, const void *keys, uint64_t n, const uint64_t *group_offsets,
+                                        uint64_t n_groups, uint32_t read_ts, uint32_t col_off, int32_t threshold,
+                                        stage_group_agg_i32_t *out, int flags);
 
 /* RunStockLevel's read side as ONE device-side operator (benchmark/tpcc/tpcc_stock_level.cpp:37-196).
  * Per request: for each of the 20 orders o in [next_o_id - 20, next_o_id) a range scan of 10 order_line rows from

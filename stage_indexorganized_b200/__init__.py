@@ -48,6 +48,11 @@ class AggI32(C.Structure):
     _fields_ = [("found", _u64), ("below", _u64), ("min_value", C.c_int32), ("max_value", C.c_int32)]
 
 
+# stage_group_agg_i32_t: one record per group of consecutive probes
+GROUP_AGG_I32 = np.dtype([("found", "<u4"), ("below", "<u4"), ("min_value", "<i4"), ("min_index", "<u4"),
+                          ("max_value", "<i4"), ("last_below_index", "<u4")])
+
+
 class Counters(C.Structure):
     _fields_ = [("slot_order_scans", _u64), ("reserved", _u64 * 7)]
 
@@ -86,6 +91,7 @@ SYMBOLS = {
     "stage_gpu_scan_batch": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _vp, _vp, _i32]),
     "stage_gpu_probe_project": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp, _u32, _u32, _vp, _i32]),
     "stage_gpu_probe_aggregate_i32": (_i32, [_vp, _vp, _u64, _u32, _u32, C.c_int32, C.POINTER(AggI32), _i32]),
+    "stage_gpu_probe_group_aggregate_i32": (_i32, [_vp, _vp, _u64, _vp, _u64, _u32, _u32, C.c_int32, _vp, _i32]),
     "stage_gpu_scan_project": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _u32, _u32, _vp, _i32]),
     "stage_gpu_tpcc_stock_level": (_i32, [_vp, _vp, _vp, _u64, _u32, _vp, _i32]),
     "stage_gpu_scan_physical": (_i32, [_vp, _u64, _u64, _vp, _vp, _vp, _i32]),
@@ -446,6 +452,23 @@ class Snapshot:
         else:
             flags = IO_DEVICE
         _check(lib().stage_gpu_probe_aggregate_i32(self.h, _ptr(keys), n, read_ts, col_off, threshold, C.byref(out), flags))
+        return out
+
+    def probe_group_aggregate_i32(self, keys, group_offsets, read_ts, col_off, threshold, n=None, out=None):
+        """Probe + reduce an int32 payload column per GROUP of consecutive probes (CH-Q2*: one group per supplier) ->
+        numpy array of GROUP_AGG_I32, one record per group. keys (n, K) uint8 and group_offsets (n_groups + 1) uint64
+        host arrays; or, with n given, CUDA tensors (keys, offsets as int64, out as uint8 [n_groups, 24]) and the call
+        is enqueued on the snapshot's stream."""
+        if n is None:
+            keys = np.ascontiguousarray(keys, np.uint8)
+            off = np.ascontiguousarray(group_offsets, np.uint64)
+            res = np.zeros(len(off) - 1, GROUP_AGG_I32)
+            _check(lib().stage_gpu_probe_group_aggregate_i32(self.h, _ptr(keys), keys.shape[0], _ptr(off), len(off) - 1, read_ts,
+                                                             col_off, threshold, _ptr(res), IO_HOST))
+            return res
+        n_groups = int(group_offsets.numel()) - 1
+        _check(lib().stage_gpu_probe_group_aggregate_i32(self.h, _ptr(keys), n, _ptr(group_offsets), n_groups, read_ts, col_off,
+                                                         threshold, _ptr(out), IO_DEVICE))
         return out
 
     def scan_column(self, start_keys, scan_sizes, read_ts, apply_visibility, col_off, col_len):

@@ -166,6 +166,58 @@ __global__ void __launch_bounds__(256) aggregate_i32_kernel(const uint32_t *__re
     }
 }
 
+// One record per GROUP of consecutive probes (CH-Q2* loops over suppliers and reduces the ~300 stock rows of each,
+// benchmark/tpcc/tpcc_new_order.cpp:803-866). min_index = first probe of the group that attains the minimum (what
+// "the stock tuple having min. stock level" means); last_below_index = the last found probe whose value is below the
+// threshold — what the reference's loop literally keeps, because its running minimum is never lowered (min_qty stays
+// INT16_MAX, :810-860), with threshold = 32767. Indices count from the start of the batch; 0xFFFFFFFF = none.
+struct GroupAggI32 {
+    uint32_t found, below;
+    int min_value;
+    uint32_t min_index;
+    int max_value;
+    uint32_t last_below_index;
+};
+
+__global__ void __launch_bounds__(256) group_aggregate_i32_kernel(const uint32_t *__restrict__ src_row,
+                                                                  const uint64_t *__restrict__ group_off, uint64_t n_groups,
+                                                                  const uint8_t *payload, const uint8_t *ver_payload,
+                                                                  uint32_t payload_size, uint32_t col_off, int threshold,
+                                                                  GroupAggI32 *out) {
+    const int lane = threadIdx.x & 31;
+    const uint64_t warps = ((uint64_t) gridDim.x * blockDim.x) >> 5;
+    for (uint64_t g = ((uint64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5; g < n_groups; g += warps) {
+        const uint64_t lo = __ldg(group_off + g), hi = __ldg(group_off + g + 1);
+        unsigned found = 0, below = 0, mi = 0xFFFFFFFFu, lb = 0;      // lb: index + 1, 0 = none
+        int mn = 0x7FFFFFFF, mx = (int) 0x80000000;
+        for (uint64_t o = lo + lane; o < hi; o += 32) {
+            const uint32_t row = __ldg(src_row + o);
+            if (row == kNoRow) continue;
+            const uint8_t *base = (row & kVersionRowFlag) ? ver_payload : payload;
+            const uint8_t *p = base + (uint64_t) (row & ~kVersionRowFlag) * payload_size + col_off;
+            const int v = (int) ((uint32_t) __ldg(p) | ((uint32_t) __ldg(p + 1) << 8) | ((uint32_t) __ldg(p + 2) << 16) |
+                                 ((uint32_t) __ldg(p + 3) << 24));
+            ++found;
+            if (v < threshold) {
+                ++below;
+                lb = (unsigned) o + 1;                    // o ascends within a lane
+            }
+            if (v < mn) {                                 // strict: the first index wins within a lane
+                mn = v;
+                mi = (unsigned) o;
+            }
+            mx = max(mx, v);
+        }
+        found = __reduce_add_sync(0xFFFFFFFFu, found);
+        below = __reduce_add_sync(0xFFFFFFFFu, below);
+        const int wmn = __reduce_min_sync(0xFFFFFFFFu, mn);
+        mi = __reduce_min_sync(0xFFFFFFFFu, (found && mn == wmn) ? mi : 0xFFFFFFFFu);
+        mx = __reduce_max_sync(0xFFFFFFFFu, mx);
+        lb = __reduce_max_sync(0xFFFFFFFFu, lb);
+        if (lane == 0) out[g] = GroupAggI32{found, below, wmn, mi, mx, lb - 1u};
+    }
+}
+
 }  // namespace stage
 
 // ---- mid-size rows (TPC-C stock: 400 B) ---------------------------------------------------------------------------

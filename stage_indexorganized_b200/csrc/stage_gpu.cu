@@ -117,6 +117,7 @@ struct HostCtx {
     DevBuf tse, vise;                               // per-operation read ids / visibility flags (batching front-end)
     uint32_t *h_counts = nullptr;                   // pinned: row counts of the chunk in flight (per-scan copies)
     size_t h_counts_cap = 0;
+    uint8_t *h_small = nullptr, *d_small = nullptr; // pinned slab (and its device alias) of the small-call path
     bool busy = false;
     void release_all() {
         keys.release(); sizes.release(); srcrow.release();
@@ -127,6 +128,7 @@ struct HostCtx {
             if (drained[i]) cudaEventDestroy(drained[i]);
         }
         if (h_counts) cudaFreeHost(h_counts);
+        if (h_small) cudaFreeHost(h_small);
         if (st) cudaStreamDestroy(st);
         if (cp) cudaStreamDestroy(cp);
     }
@@ -2156,6 +2158,9 @@ static int probe_host_staged(stage_snapshot *s, HostCtx *c, const void *keys, ui
     return STAGE_OK;
 }
 
+static int probe_host_small(stage_snapshot *s, HostCtx *c, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
+                            uint32_t *ts, void *key_out, void *payload_out);          // "small host calls" below
+
 extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
                                      uint32_t *ts, void *key_out, void *payload_out, int flags) {
     if (!s || (n && !keys)) return STAGE_ERR_ARG;
@@ -2175,6 +2180,10 @@ extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint
     int rc = STAGE_OK;
     CtxGuard g{s, ctx_acquire(s, &rc)};
     if (!g.c) return rc;
+    if (host_path_mode() == kHostAuto) {
+        rc = probe_host_small(s, g.c, keys, n, read_ts, found, ts, key_out, payload_out);
+        if (rc != 1 /* kNotSmall */) return rc;
+    }
     if (host_path_mode() == kHostZeroCopy) {
         uint8_t *df = static_cast<uint8_t *>(mapped_alias(found)), *dk = static_cast<uint8_t *>(mapped_alias(key_out)),
                 *dp = static_cast<uint8_t *>(mapped_alias(payload_out));
@@ -2457,6 +2466,102 @@ static int scan_host_staged(stage_snapshot *s, HostCtx *c, const void *start_key
     return STAGE_OK;
 }
 
+// ---- small host calls -----------------------------------------------------------------------------------------
+// A call with a few operations (the reference's drivers issue ONE per executor) is all latency: the staged path costs
+// two H2D copies, two fills, two launches, four D2H copies and their events. Below kSmallHostBytes of inputs + results
+// the kernels instead read the keys from, and store the results into, a pinned slab of the call context through its
+// device alias: memcpy in, two launches, one stream synchronisation, memcpy out — any host memory, either layout.
+constexpr size_t kSmallHostBytes = 192u << 10;
+constexpr int kNotSmall = 1;                     // "does not fit": the caller takes the staged path
+
+static int ctx_small_slab(HostCtx *c) {
+    if (c->h_small) return c->d_small ? STAGE_OK : kNotSmall;
+    CUDA_TRY(cudaHostAlloc((void **) &c->h_small, kSmallHostBytes, cudaHostAllocDefault));
+    c->d_small = static_cast<uint8_t *>(mapped_alias(c->h_small));
+    return c->d_small ? STAGE_OK : kNotSmall;
+}
+
+struct SlabCarve {
+    size_t off = 0;
+    size_t take(size_t bytes) {
+        const size_t o = off;
+        off = (off + bytes + 15) & ~size_t(15);
+        return o;
+    }
+};
+
+static int probe_host_small(stage_snapshot *s, HostCtx *c, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
+                            uint32_t *ts, void *key_out, void *payload_out) {
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    if (n > kSmallHostBytes) return kNotSmall;
+    SlabCarve cv;
+    const size_t o_keys = cv.take(n * K), o_found = cv.take(n), o_ts = cv.take(n * 4), o_kout = cv.take(key_out ? n * K : 0),
+                 o_pay = cv.take(payload_out ? n * (size_t) P : 0);
+    if (cv.off > kSmallHostBytes) return kNotSmall;
+    int rc;
+    if ((rc = ctx_small_slab(c))) return rc;
+    uint8_t *h = c->h_small, *d = c->d_small;
+    memcpy(h + o_keys, keys, n * K);
+    ProbeArgs a{};
+    a.n = n;
+    a.read_ts = read_ts;
+    a.keys = d + o_keys;
+    a.found = d + o_found;
+    a.ts_out = reinterpret_cast<uint32_t *>(d + o_ts);
+    a.key_out = key_out ? d + o_kout : nullptr;
+    if ((rc = probe_device(s, Lane{c->st, &c->srcrow, false}, a, payload_out ? d + o_pay : nullptr))) return rc;
+    CUDA_TRY(cudaStreamSynchronize(c->st));
+    if (found) memcpy(found, h + o_found, n);
+    if (ts) memcpy(ts, h + o_ts, n * 4);
+    for (uint64_t i = 0; i < n; ++i) {               // rows of missed probes stay untouched
+        if (!h[o_found + i]) continue;
+        if (key_out) memcpy(static_cast<uint8_t *>(key_out) + i * K, h + o_kout + i * K, K);
+        if (payload_out) memcpy(static_cast<uint8_t *>(payload_out) + i * (size_t) P, h + o_pay + i * (size_t) P, P);
+    }
+    return STAGE_OK;
+}
+
+static int scan_host_small(stage_snapshot *s, HostCtx *c, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
+                           uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts, void *key_out,
+                           uint32_t *ts_out, void *payload_out, bool compact) {
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    if (n > kSmallHostBytes || (uint64_t) n * out_stride > kSmallHostBytes) return kNotSmall;
+    const size_t slots = (size_t) n * out_stride;
+    SlabCarve cv;
+    const size_t o_keys = cv.take(n * K), o_sizes = cv.take(n * 4), o_counts = cv.take(n * 4), o_ts = cv.take(ts_out ? slots * 4 : 0),
+                 o_kout = cv.take(key_out ? slots * K : 0), o_pay = cv.take(payload_out ? slots * P : 0);
+    if (cv.off > kSmallHostBytes) return kNotSmall;
+    int rc;
+    if ((rc = ctx_small_slab(c))) return rc;
+    uint8_t *h = c->h_small, *d = c->d_small;
+    memcpy(h + o_keys, start_keys, n * K);
+    memcpy(h + o_sizes, scan_sizes, n * 4);
+    ScanArgs a{};
+    a.n = n;
+    a.out_stride = out_stride;
+    a.read_ts = read_ts;
+    a.apply_visibility = apply_visibility;
+    a.start_keys = d + o_keys;
+    a.scan_sizes = reinterpret_cast<const uint32_t *>(d + o_sizes);
+    a.row_counts = reinterpret_cast<uint32_t *>(d + o_counts);
+    a.key_out = key_out ? d + o_kout : nullptr;
+    a.ts_out = ts_out ? reinterpret_cast<uint32_t *>(d + o_ts) : nullptr;
+    if ((rc = scan_device(s, Lane{c->st, &c->srcrow, false}, a, payload_out ? d + o_pay : nullptr))) return rc;
+    CUDA_TRY(cudaStreamSynchronize(c->st));
+    const uint32_t *cnt = reinterpret_cast<const uint32_t *>(h + o_counts);
+    memcpy(row_counts, cnt, n * 4);
+    size_t packed = 0;
+    for (uint64_t i = 0; i < n; ++i) {               // row slots beyond row_counts[i] stay untouched
+        const size_t src = (size_t) i * out_stride, dst = compact ? packed : src, m = cnt[i];
+        packed += m;
+        if (!m) continue;
+        if (ts_out) memcpy(ts_out + dst, h + o_ts + src * 4, m * 4);
+        if (key_out) memcpy(static_cast<uint8_t *>(key_out) + dst * K, h + o_kout + src * K, m * K);
+        if (payload_out) memcpy(static_cast<uint8_t *>(payload_out) + dst * P, h + o_pay + src * P, m * P);
+    }
+    return STAGE_OK;
+}
+
 extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys, const uint32_t *scan_sizes, uint64_t n,
                                     uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts,
                                     void *key_out, uint32_t *ts_out, void *payload_out, int flags) {
@@ -2485,6 +2590,11 @@ extern "C" int stage_gpu_scan_batch(stage_snapshot_t *s, const void *start_keys,
     CtxGuard g{s, ctx_acquire(s, &rc)};
     if (!g.c) return rc;
     const bool compact = (flags & STAGE_IO_COMPACT) != 0;
+    if (host_path_mode() == kHostAuto) {
+        rc = scan_host_small(s, g.c, start_keys, scan_sizes, n, out_stride, read_ts, apply_visibility, row_counts, key_out, ts_out,
+                             payload_out, compact);
+        if (rc != kNotSmall) return rc;
+    }
     if (host_path_mode() == kHostZeroCopy && !compact) {
         uint32_t *dc = static_cast<uint32_t *>(mapped_alias(row_counts)), *dt = static_cast<uint32_t *>(mapped_alias(ts_out));
         uint8_t *dk = static_cast<uint8_t *>(mapped_alias(key_out)), *dp = static_cast<uint8_t *>(mapped_alias(payload_out));
@@ -2602,6 +2712,55 @@ extern "C" int stage_gpu_probe_aggregate_i32(stage_snapshot_t *s, const void *ke
     }
     CUDA_TRY(cudaMemcpyAsync(out, d_out, sizeof(AggI32), cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_probe_group_aggregate_i32(stage_snapshot_t *s, const void *keys, uint64_t n, const uint64_t *group_offsets,
+                                                   uint64_t n_groups, uint32_t read_ts, uint32_t col_off, int32_t threshold,
+                                                   stage_group_agg_i32_t *out, int flags) {
+    if (!s || (n && !keys) || (n_groups && (!group_offsets || !out))) return STAGE_ERR_ARG;
+    if (!s->sealed) return STAGE_ERR_STATE;
+    const uint32_t K = s->schema.key_size, P = s->schema.payload_size;
+    if ((uint64_t) col_off + 4 > P || n > (1ull << 26) || n_groups > (1ull << 26)) return STAGE_ERR_ARG;
+    static_assert(sizeof(GroupAggI32) == sizeof(stage_group_agg_i32_t), "group aggregate record layout");
+    if (n_groups == 0) return STAGE_OK;
+    const bool dev = flags & STAGE_IO_DEVICE;
+    if (!dev) {
+        if (group_offsets[0] != 0 || group_offsets[n_groups] != n) return STAGE_ERR_ARG;
+        for (uint64_t g = 0; g < n_groups; ++g)
+            if (group_offsets[g] > group_offsets[g + 1]) return STAGE_ERR_ARG;
+    }
+    std::lock_guard<std::mutex> lock(s->mu);
+    CUDA_TRY(cudaSetDevice(s->device));
+    int rc;
+    if ((rc = s->sc_srcrow.ensure(std::max<uint64_t>(n, 1) * 4))) return rc;
+    const uint64_t *d_off = group_offsets;
+    GroupAggI32 *d_out = reinterpret_cast<GroupAggI32 *>(out);
+    ProbeArgs a{};
+    a.n = n;
+    a.read_ts = read_ts;
+    a.src_row = static_cast<uint32_t *>(s->sc_srcrow.p);
+    a.keys = static_cast<const uint8_t *>(keys);
+    if (!dev) {
+        // scratch: keys | offsets | records
+        const size_t o_off = (n * K + 15) & ~size_t(15), o_out = o_off + (n_groups + 1) * 8;
+        if ((rc = s->sc_keys.ensure(o_out + n_groups * sizeof(GroupAggI32)))) return rc;
+        uint8_t *base = static_cast<uint8_t *>(s->sc_keys.p);
+        if (n) CUDA_TRY(cudaMemcpyAsync(base, keys, n * K, cudaMemcpyHostToDevice, s->stream));
+        CUDA_TRY(cudaMemcpyAsync(base + o_off, group_offsets, (n_groups + 1) * 8, cudaMemcpyHostToDevice, s->stream));
+        a.keys = base;
+        d_off = reinterpret_cast<const uint64_t *>(base + o_off);
+        d_out = reinterpret_cast<GroupAggI32 *>(base + o_out);
+    }
+    if (n && (rc = launch_probe_nw(s, s->stream, a))) return rc;
+    const unsigned blocks = (unsigned) std::min<uint64_t>((n_groups + 7) / 8, (uint64_t) sm_count() * 8);
+    group_aggregate_i32_kernel<<<blocks, 256, 0, s->stream>>>(a.src_row, d_off, n_groups, s->d_payload, s->d_ver_payload, P, col_off,
+                                                              threshold, d_out);
+    LAUNCH_CHECK();
+    if (!dev) {
+        CUDA_TRY(cudaMemcpyAsync(out, d_out, n_groups * sizeof(GroupAggI32), cudaMemcpyDeviceToHost, s->stream));
+        CUDA_TRY(cudaStreamSynchronize(s->stream));
+    }
     return STAGE_OK;
 }
 

@@ -92,3 +92,16 @@ def q2_supplier_keys(warehouses, supplier, items=ITEMS):
     i = np.tile(np.arange(1, items + 1, dtype=np.int64), warehouses)
     m = (w * i) % 10000 == supplier
     return stock_key(w[m], i[m])
+
+
+def q2_all_supplier_keys(warehouses, items=ITEMS, suppliers=10000):
+    """supp_stock_map (benchmark/tpcc/tpcc_workload.cpp:581-585) as one probe batch: the (w, i) pairs grouped by
+    (w * i) mod 10000, within a supplier in the map's order (w ascending, then i ascending).
+    Returns (keys [warehouses * items, 16], group_offsets uint64 [suppliers + 1])."""
+    w = np.repeat(np.arange(1, warehouses + 1, dtype=np.int64), items)
+    i = np.tile(np.arange(1, items + 1, dtype=np.int64), warehouses)
+    sup = (w * i) % suppliers
+    order = np.argsort(sup, kind="stable")
+    off = np.zeros(suppliers + 1, np.uint64)
+    off[1:] = np.cumsum(np.bincount(sup, minlength=suppliers))
+    return stock_key(w[order], i[order]), off

@@ -150,6 +150,53 @@ def test_quantity_aggregate_pushdown(tables):
         s_snap.probe_aggregate_i32(keys, 1, tpcc.STOCK_PAYLOAD - 3, 15)                         # column runs past the row
 
 
+def test_q2_group_aggregate_per_supplier(tables):
+    """stage_gpu_probe_group_aggregate_i32: CH-Q2*'s loop over suppliers (tpcc_new_order.cpp:803-866) as ONE call — the
+    stock probes of a run of suppliers, one record per supplier — against the reference's loop restated on the checker's
+    rows: MIN(S_QUANTITY) with its first row, and the row the loop literally keeps (its running minimum is never
+    lowered, so the last row below INT16_MAX wins). Groups with misses, empty groups, host and device buffers."""
+    import torch
+    stock, _, s_snap, _, _, _ = tables
+    keys_all, off_all = tpcc.q2_all_supplier_keys(W)
+    assert len(keys_all) == W * tpcc.ITEMS and off_all[-1] == len(keys_all)
+    assert np.array_equal(keys_all[off_all[77]:off_all[78]], tpcc.q2_supplier_keys(W, 77))
+    g0, g1 = 4200, 4264                                       # 64 suppliers
+    lo, hi = int(off_all[g0]), int(off_all[g1])
+    keys = np.concatenate([keys_all[lo:hi], tpcc.stock_key([W + 3, 0, W + 9], [5, 1, 2])])      # + a group of misses
+    off = np.concatenate([off_all[g0:g1 + 1] - lo, [hi - lo, hi - lo + 3]]).astype(np.uint64)   # + an empty group
+    for read_ts in (1, 50000):
+        wf, _, _, wp = stock.probe(keys, read_ts)
+        q = np.ascontiguousarray(wp[:, 0:4]).view("<i4").ravel()
+        for thr in (32767, 40):
+            got = s_snap.probe_group_aggregate_i32(keys, off, read_ts, 0, thr)
+            assert len(got) == len(off) - 1
+            for g in range(len(off) - 1):
+                a, b = int(off[g]), int(off[g + 1])
+                hit = np.flatnonzero(wf[a:b] == 1) + a
+                r = got[g]
+                if len(hit) == 0:
+                    assert (r["found"], r["below"], r["min_value"], r["min_index"], r["max_value"], r["last_below_index"]) == \
+                        (0, 0, 2**31 - 1, 0xFFFFFFFF, -2**31, 0xFFFFFFFF), g
+                    continue
+                qq = q[hit]
+                below = hit[qq < thr]
+                keep = 0xFFFFFFFF                              # the reference's loop, literally
+                for j in hit:
+                    if thr > q[j]:
+                        keep = j
+                assert (r["found"], r["below"], r["min_value"], r["max_value"]) == (len(hit), len(below), qq.min(), qq.max()), g
+                assert r["min_index"] == hit[np.argmin(qq)] and r["last_below_index"] == keep, g
+        dk, do = torch.from_numpy(keys).cuda(), torch.from_numpy(off.astype(np.int64)).cuda()
+        dout = torch.zeros((len(off) - 1, 24), dtype=torch.uint8, device="cuda")
+        s_snap.probe_group_aggregate_i32(dk, do, read_ts, 0, 40, n=len(keys), out=dout)
+        torch.cuda.synchronize()
+        assert np.array_equal(dout.cpu().numpy().view(sg.GROUP_AGG_I32).ravel(), s_snap.probe_group_aggregate_i32(keys, off, read_ts, 0, 40))
+    with pytest.raises(sg.StageError):
+        s_snap.probe_group_aggregate_i32(keys, off[:-1], 1, 0, 40)                             # offsets do not cover the batch
+    with pytest.raises(sg.StageError):
+        s_snap.probe_group_aggregate_i32(keys, off[::-1].copy(), 1, 0, 40)                     # not ascending
+
+
 def _stock_level_by_the_three_steps(ol, stock, reqs, read_ts):
     """RunStockLevel's reads done the reference's way on the checker's tables (tpcc_stock_level.cpp:92-190): 20 scans of
     10 rows, first returned row of the order -> one stock probe -> S_QUANTITY < threshold -> distinct items."""

@@ -52,18 +52,37 @@ enum stage_status {
 enum stage_key_kind {
     STAGE_KEY_AUTO = 0,         /* key_size < 16 -> signed bytes, else memcmp */
     STAGE_KEY_SIGNED_BYTES = 1, /* my_memcmp: signed char difference, byte 0 first (b_tree.h:99-106) */
-    STAGE_KEY_MEMCMP = 2        /* libc memcmp: unsigned bytes */
+    STAGE_KEY_MEMCMP = 2,       /* libc memcmp: unsigned bytes */
+    STAGE_KEY_VARLEN = 0x100    /* flag, OR-ed in: keys of different lengths in one table (see stage_gpu_key_pack) */
 };
 
 /* Table schema = the part of ParameterSet (include/vstore/b_tree.h:23-40) and Catalog
  * (include/common/catalog.h:69) the read path depends on. Keys are fixed-length per table, as in
- * every driver table (YCSB int 4 B, YCSB string 16 B, TPC-C 8/16/32 B). */
+ * every driver table (YCSB int 4 B, YCSB string 16 B, TPC-C 8/16/32 B), unless key_kind carries
+ * STAGE_KEY_VARLEN (below). */
 typedef struct stage_schema {
     uint32_t key_size;       /* bytes of key actually passed to Read/Insert (YCSB int: 4); 1..32 */
     uint32_t payload_size;   /* ParameterSet.payload_size */
     uint32_t leaf_node_size; /* ParameterSet.leaf_node_size (64 KiB in both drivers) */
     uint32_t key_kind;       /* enum stage_key_kind */
 } stage_schema_t;
+
+/* Variable-length keys (key_kind | STAGE_KEY_VARLEN). BaseNode::KeyCompare orders two keys by their first
+ * min(l1, l2) bytes and then by length (include/vstore/b_tree.h:116-134) — the order test/testing_btree.cpp's
+ * std::to_string keys rely on. Such a table is described by key_size = SLOT size = longest key + 1 (<= 32), and every key
+ * crosses this interface (probe keys, scan start keys, separators, key_out) as a slot of key_size bytes:
+ *   bytes [0, len) the key, bytes [len, key_size - 1) padding that sorts lowest (0x80 for the signed-byte order, 0x00
+ *   for memcmp), last byte the length (XOR 0x80 for the signed-byte order)
+ * so that comparing two slots as fixed-length keys of the table's byte order IS KeyCompare on the keys (a proper prefix
+ * sorts first, keys that differ only by trailing minimum bytes are decided by the length byte). stage_gpu_key_pack /
+ * stage_gpu_key_unpack convert; the adapters in stage_gpu_executors.h do it for their callers. Because KeyCompare picks the
+ * byte order per pair (signed bytes when the shorter key has < 16 bytes), a table has ONE order only if its keys are
+ * all <= 15 bytes (signed; what STAGE_KEY_AUTO picks for key_size <= 16) or all >= 16 bytes (memcmp): other tables are
+ * rejected (schema: STAGE_ERR_ARG, a record outside the range: STAGE_ERR_LAYOUT). Quiesced trees without version
+ * chains only (from_tree, refresh_from_tree, begin / add_leaves / seal): the version store keeps [key][payload] slots of
+ * the catalog's fixed key length (version_store.h:445-481), no variable-length table goes through it. */
+int stage_gpu_key_pack(const stage_schema_t *schema, const void *key, uint32_t len, void *slot);
+int stage_gpu_key_unpack(const stage_schema_t *schema, const void *slot, void *key_out, uint32_t *len_out);
 
 /* One retired version = one TupleHeader (include/vstore/version_store.h:28-46) in index form. */
 typedef struct stage_version {

@@ -84,6 +84,19 @@ public:
     // BTree::Read shape. Returns the LATEST in-leaf version like the reference (visibility is the
     // executor's job); nullptr on a miss.
     std::unique_ptr<Record> Read(const char *key, uint16_t key_size, cid_t commit_id, bool /*is_for_update*/) {
+        if (varlen()) {          // keys of different lengths travel as slots (stage_gpu_key_pack)
+            char slot[32], slot_out[32];
+            if (stage_gpu_key_pack(&schema_, key, key_size, slot) != STAGE_OK) return nullptr;   // no such key in this table
+            auto rec = std::make_unique<Record>(key_size, schema_.payload_size);
+            uint8_t found = 0;
+            uint32_t ts = 0;
+            ReadBatch(slot, 1, 0xFFFFFFFFu, &found, &ts, slot_out, rec->GetPayload());
+            if (!found) return nullptr;
+            std::memcpy(rec->GetData(), key, key_size);
+            rec->commit_id = ts;
+            rec->SetCstamp(commit_id);
+            return rec;
+        }
         if (key_size != schema_.key_size) return nullptr;
         auto rec = std::make_unique<Record>(schema_.key_size, schema_.payload_size);
         uint8_t found = 0;
@@ -97,6 +110,7 @@ public:
     }
 
     std::unique_ptr<GpuIterator> RangeScanBySize(const char *key1, uint16_t size1, uint32_t scan_size);
+    bool varlen() const { return (schema_.key_kind & STAGE_KEY_VARLEN) != 0; }
 
     // Batched forms: the ones that reach HBM speed. Outputs are caller-allocated host buffers.
     void ReadBatch(const void *keys, uint64_t n, cid_t read_ts, uint8_t *found, uint32_t *ts, void *key_out,
@@ -194,7 +208,7 @@ private:
 class GpuIterator {
 public:
     GpuIterator(GpuTreeView *tree, const char *key1, uint32_t scan_size, cid_t read_ts, bool apply_visibility)
-        : K_(tree->schema().key_size), P_(tree->schema().payload_size), scan_size_(scan_size) {
+        : schema_(tree->schema()), K_(tree->schema().key_size), P_(tree->schema().payload_size), scan_size_(scan_size) {
         keys_.resize((size_t) scan_size * K_);
         ts_.resize(scan_size);
         pay_.resize((size_t) scan_size * P_);
@@ -206,8 +220,10 @@ public:
     // executor loop too, b_tree.h:900-902).
     std::unique_ptr<Record> GetNext() {
         if (next_ >= count_) return nullptr;
-        auto rec = std::make_unique<Record>(K_, P_);
-        std::memcpy(rec->GetData(), keys_.data() + (size_t) next_ * K_, K_);
+        uint32_t len = K_;
+        if (schema_.key_kind & STAGE_KEY_VARLEN) stage_gpu_key_unpack(&schema_, keys_.data() + (size_t) next_ * K_, nullptr, &len);
+        auto rec = std::make_unique<Record>(len, P_);
+        std::memcpy(rec->GetData(), keys_.data() + (size_t) next_ * K_, len);
         std::memcpy(rec->GetPayload(), pay_.data() + (size_t) next_ * P_, P_);
         rec->commit_id = ts_[next_];
         ++next_;
@@ -215,12 +231,18 @@ public:
     }
     uint32_t count() const { return count_; }
 private:
+    stage_schema_t schema_;
     uint32_t K_, P_, scan_size_, count_ = 0, next_ = 0;
     std::vector<char> keys_, pay_;
     std::vector<uint32_t> ts_;
 };
 
 inline std::unique_ptr<GpuIterator> GpuTreeView::RangeScanBySize(const char *key1, uint16_t size1, uint32_t scan_size) {
+    if (varlen()) {
+        char slot[32];
+        if (stage_gpu_key_pack(&schema_, key1, size1, slot) != STAGE_OK) return nullptr;
+        return std::make_unique<GpuIterator>(this, slot, scan_size, 0xFFFFFFFFu, false);
+    }
     if (size1 != schema_.key_size) return nullptr;
     return std::make_unique<GpuIterator>(this, key1, scan_size, 0xFFFFFFFFu, false);
 }

@@ -57,6 +57,8 @@ class _Table:
         self._root = self._fn("root", _vp, [_vp])
         self._probe = self._fn("probe", _i32, [_vp, _vp, _u32, _u64, _u32, _vp, _vp, _vp, _vp])
         self._scan = self._fn("scan", _i32, [_vp, _vp, _u32, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _vp, _vp])
+        self._probe_varlen = self._fn("probe_varlen", _i32, [_vp, _vp, _vp, _u64, _u32, _vp, _vp, _vp])
+        self._scan_varlen = self._fn("scan_varlen", _i32, [_vp, _vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _u32, _vp, _vp, _vp])
         self._time_probe = self._fn("time_probe", C.c_double, [_vp, _vp, _u32, _u64, _u32, _i32, _i32, _vp])
         self._time_scan = self._fn("time_scan", C.c_double,
                                    [_vp, _vp, _u32, _u32, _u64, _u32, _i32, _i32, _i32, _vp])
@@ -122,6 +124,39 @@ class _Table:
         self._scan(self.h, _ptr(start_keys), ks, _ptr(scan_sizes), n, stride, read_ts, int(apply_visibility),
                    _ptr(counts), _ptr(key_out), _ptr(ts), _ptr(pay))
         return counts, key_out, ts, pay
+
+    # -- the same reads for keys of different lengths (lists of bytes) --------------------------
+    @staticmethod
+    def _blob(key_list):
+        blob = np.frombuffer(b"".join(key_list) + b"\0", np.uint8).copy()
+        off = np.zeros(len(key_list) + 1, np.uint32)
+        off[1:] = np.cumsum([len(k) for k in key_list])
+        return blob, off
+
+    def probe_varlen(self, key_list, read_ts):
+        """-> (found u8[n], ts u32[n], payload u8[n, P])"""
+        blob, off = self._blob(key_list)
+        n = len(key_list)
+        found, ts = np.zeros(n, np.uint8), np.zeros(n, np.uint32)
+        pay = np.zeros((n, self.payload_size), np.uint8)
+        self._probe_varlen(self.h, _ptr(blob), _ptr(off), n, read_ts, _ptr(found), _ptr(ts), _ptr(pay))
+        return found, ts, pay
+
+    def scan_varlen(self, start_list, scan_sizes, read_ts, apply_visibility, key_stride=32):
+        """-> (row_counts u32[n], keys: list of lists of bytes, ts u32[n, S], payload u8[n, S, P])"""
+        blob, off = self._blob(start_list)
+        n = len(start_list)
+        scan_sizes = np.ascontiguousarray(np.broadcast_to(np.asarray(scan_sizes, np.uint32), (n,)))
+        stride = int(scan_sizes.max()) if n else 0
+        counts = np.zeros(n, np.uint32)
+        key_out = np.zeros((n, stride, key_stride), np.uint8)
+        lens = np.zeros((n, stride), np.uint32)
+        ts = np.zeros((n, stride), np.uint32)
+        pay = np.zeros((n, stride, self.payload_size), np.uint8)
+        self._scan_varlen(self.h, _ptr(blob), _ptr(off), _ptr(scan_sizes), n, stride, read_ts, int(apply_visibility),
+                          _ptr(counts), _ptr(key_out), key_stride, _ptr(lens), _ptr(ts), _ptr(pay))
+        keys = [[bytes(key_out[i, j, : lens[i, j]]) for j in range(counts[i])] for i in range(n)]
+        return counts, keys, ts, pay
 
     def time_probe(self, keys, read_ts, threads, pin=True):
         keys = np.ascontiguousarray(keys, np.uint8)
@@ -223,6 +258,17 @@ class Writer:
         self._stop.value = 1
         self._t.join()
         return int(self.tried), self.committed
+
+
+def key_compare(a, b):
+    """BaseNode::KeyCompare (b_tree.h:116-134) on two byte strings, as restated by the C oracle -> -1 / 0 / 1."""
+    if OracleTable._lib is None:
+        build_oracle()
+        OracleTable._lib = C.CDLL(ORACLE_SO)
+    f = OracleTable._lib.so_key_compare
+    f.restype, f.argtypes = C.c_int, [C.c_char_p, _u32, C.c_char_p, _u32]
+    r = f(bytes(a), len(a), bytes(b), len(b))
+    return (r > 0) - (r < 0)
 
 
 def walk_tree(root):

@@ -411,6 +411,55 @@ int ref_scan(ref_table *t, const void *start_keys, uint32_t key_size, const uint
     return 0;
 }
 
+// Tables whose keys differ in length (test/testing_btree.cpp's std::to_string keys): key i = keys[off[i] .. off[i+1]).
+// Tree-level calls only — BTree::Read and RangeScanBySize / Iterator::GetNext take the length per call
+// (b_tree.h:812-835); the executors are typed on a fixed-size key struct.
+int ref_probe_varlen(ref_table *t, const void *keys, const uint32_t *off, uint64_t n, uint32_t read_ts, uint8_t *found,
+                     uint32_t *ts, void *payload_out) {
+    const char *k = static_cast<const char *>(keys);
+    const uint32_t P = t->payload_size;
+    for (uint64_t i = 0; i < n; ++i) {
+        const uint32_t len = off[i + 1] - off[i];
+        std::unique_ptr<Record> rec = t->tree->Read(k + off[i], (uint16_t) len, read_ts, false);
+        int f = 0;
+        if (rec != nullptr) {
+            f = visible_version(rec.get(), len, P, read_ts, ts ? ts + i : nullptr, nullptr,
+                                payload_out ? static_cast<char *>(payload_out) + i * (uint64_t) P : nullptr);
+            delete[] reinterpret_cast<char *>(rec.release());
+        }
+        found[i] = (uint8_t) f;
+    }
+    return 0;
+}
+
+int ref_scan_varlen(ref_table *t, const void *keys, const uint32_t *off, const uint32_t *scan_sizes, uint64_t n,
+                    uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts, void *key_out,
+                    uint32_t key_stride, uint32_t *key_lens, uint32_t *ts_out, void *payload_out) {
+    const char *k = static_cast<const char *>(keys);
+    const uint32_t P = t->payload_size;
+    for (uint64_t i = 0; i < n; ++i) {
+        const uint64_t base = i * (uint64_t) out_stride;
+        auto iter = t->tree->RangeScanBySize(k + off[i], (uint16_t) (off[i + 1] - off[i]), scan_sizes[i]);
+        uint32_t cnt = 0;
+        for (uint32_t scanned = 0; scanned < scan_sizes[i]; ++scanned) {
+            std::unique_ptr<Record> rec = iter->GetNext();
+            if (rec == nullptr) continue;
+            const uint32_t cid = rec->meta.meta_data.GetTxnCommitId();
+            if (!apply_visibility || read_ts >= cid) {       // executor.h:469; the range branch never walks a chain
+                const uint32_t len = rec->meta.meta_data.GetKeyLength();
+                key_lens[base + cnt] = len;
+                if (ts_out) ts_out[base + cnt] = cid;
+                if (key_out) memcpy(static_cast<char *>(key_out) + (base + cnt) * key_stride, rec->GetKey(), len < key_stride ? len : key_stride);
+                if (payload_out) memcpy(static_cast<char *>(payload_out) + (base + cnt) * P, rec->GetPayload(), P);
+                ++cnt;
+            }
+            delete[] reinterpret_cast<char *>(rec.release());
+        }
+        row_counts[i] = cnt;
+    }
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 // timing legs (CPU baseline): T threads, each over its slice of the same key stream, results copied
 // into per-thread scratch (the reference allocates a Record per row; that cost is part of its path).

@@ -623,7 +623,8 @@ static void leaf_range_scan(const u8 *leaf, const void *key1, uint32_t size1, ui
 
 /* executor loop over Iterator::GetNext (executor.h:459-535 with visibility, :626-638 without) */
 static uint32_t scan_one(so_tree *t, scan_buf *buf, const u8 *start, uint32_t ks, uint32_t scan_size, uint32_t read_ts,
-                         int apply_visibility, uint32_t *ts_out, u8 *key_out, u8 *payload_out) {
+                         int apply_visibility, uint32_t *ts_out, u8 *key_out, u8 *payload_out, uint32_t kstride,
+                         uint32_t *lens_out) {
     uint32_t P = t->payload_size, remaining = scan_size, cnt = 0;
     u8 *leaf = traverse_to_leaf(t, NULL, start, ks, 1);      /* Iterator ctor, b_tree.h:885-891 */
     leaf_range_scan(leaf, start, ks, scan_size, buf);
@@ -651,7 +652,12 @@ static uint32_t scan_one(so_tree *t, scan_buf *buf, const u8 *start, uint32_t ks
         } else {
             uint64_t m = cur.mp[0];
             if (ts_out) ts_out[cnt] = m_cid(m);
-            if (key_out) memcpy(key_out + (uint64_t) cnt * ks, cur.key, ks);
+            if (lens_out) {                                  /* variable-length keys: key bytes + their length */
+                lens_out[cnt] = cur.len;
+                if (key_out) memcpy(key_out + (uint64_t) cnt * kstride, cur.key, cur.len < kstride ? cur.len : kstride);
+            } else if (key_out) {
+                memcpy(key_out + (uint64_t) cnt * ks, cur.key, ks);
+            }
             if (payload_out) memcpy(payload_out + (uint64_t) cnt * P, cur.leaf + m_offset(m) + m_padlen(m), P);
         }
         cnt += (uint32_t) f;
@@ -669,9 +675,40 @@ int so_scan(so_tree *t, const void *start_keys, uint32_t ks, const uint32_t *sca
         uint64_t base = i * (uint64_t) out_stride;
         row_counts[i] = scan_one(t, &buf, k + i * ks, ks, scan_sizes[i], read_ts, apply_visibility,
                                  ts_out ? ts_out + base : NULL, key_out ? (u8 *) key_out + base * ks : NULL,
-                                 payload_out ? (u8 *) payload_out + base * P : NULL);
+                                 payload_out ? (u8 *) payload_out + base * P : NULL, ks, NULL);
     }
     free(buf.v);
+    return 0;
+}
+
+/* the same loop for tables with keys of different lengths (test/testing_btree.cpp's std::to_string keys): start key i
+ * = keys[off[i] .. off[i+1]); returned keys go to key_out in slots of key_stride bytes, their lengths to key_lens */
+int so_scan_varlen(so_tree *t, const void *keys, const uint32_t *off, const uint32_t *scan_sizes, uint64_t n,
+                   uint32_t out_stride, uint32_t read_ts, int apply_visibility, uint32_t *row_counts, void *key_out,
+                   uint32_t key_stride, uint32_t *key_lens, uint32_t *ts_out, void *payload_out) {
+    const u8 *k = (const u8 *) keys;
+    uint32_t P = t->payload_size;
+    scan_buf buf = { 0 };
+    for (uint64_t i = 0; i < n; i++) {
+        uint64_t base = i * (uint64_t) out_stride;
+        row_counts[i] = scan_one(t, &buf, k + off[i], off[i + 1] - off[i], scan_sizes[i], read_ts, apply_visibility,
+                                 ts_out ? ts_out + base : NULL, key_out ? (u8 *) key_out + base * key_stride : NULL,
+                                 payload_out ? (u8 *) payload_out + base * P : NULL, key_stride, key_lens + base);
+    }
+    free(buf.v);
+    return 0;
+}
+
+/* BTree::Read for keys of different lengths: key i = keys[off[i] .. off[i+1]) */
+int so_probe_varlen(so_tree *t, const void *keys, const uint32_t *off, uint64_t n, uint32_t read_ts, uint8_t *found,
+                    uint32_t *ts, void *payload_out) {
+    const u8 *k = (const u8 *) keys;
+    uint32_t P = t->payload_size;
+    for (uint64_t i = 0; i < n; i++) {
+        int f = probe_one(t, k + off[i], off[i + 1] - off[i], read_ts, ts ? ts + i : NULL, NULL,
+                          payload_out ? (u8 *) payload_out + i * P : NULL);
+        found[i] = (uint8_t) f;
+    }
     return 0;
 }
 
@@ -726,7 +763,7 @@ static void *job_main(void *arg) {
         scan_buf buf = { 0 };
         pthread_barrier_wait(j->bar);
         for (uint64_t i = j->b; i < j->e; i++)
-            acc += scan_one(j->t, &buf, j->keys + i * j->ks, j->ks, j->scan_size, j->read_ts, j->vis, ts, key, pay);
+            acc += scan_one(j->t, &buf, j->keys + i * j->ks, j->ks, j->scan_size, j->read_ts, j->vis, ts, key, pay, j->ks, NULL);
         free(pay); free(key); free(ts); free(buf.v);
     }
     j->out = acc;

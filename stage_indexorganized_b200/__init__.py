@@ -23,6 +23,7 @@ IO_HOST, IO_DEVICE, IO_COMPACT = 0, 1, 2
 XCHG_DEVICE_SYNC = 1
 IPC_HANDLE_BYTES = 64
 KEY_AUTO, KEY_SIGNED_BYTES, KEY_MEMCMP = 0, 1, 2
+KEY_VARLEN = 0x100      # flag: keys of different lengths, passed as slots (pack_keys / unpack_keys)
 
 _vp, _u32, _u64, _i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int
 
@@ -65,6 +66,8 @@ class RefreshStats(C.Structure):
 # every symbol include/stage_gpu.h declares: (restype, argtypes)
 SYMBOLS = {
     "stage_gpu_init": (_i32, [_i32]),
+    "stage_gpu_key_pack": (_i32, [_vp, _vp, _u32, _vp]),
+    "stage_gpu_key_unpack": (_i32, [_vp, _vp, _vp, _vp]),
     "stage_gpu_snapshot_from_tree": (_i32, [_vp, C.POINTER(Schema), C.POINTER(_vp)]),
     "stage_gpu_snapshot_from_tree_live": (_i32, [_vp, C.POINTER(Schema), _vp, _vp, C.POINTER(_vp)]),
     "stage_gpu_snapshot_refresh_from_tree": (_i32, [_vp, _vp, C.POINTER(_vp), C.POINTER(RefreshStats)]),
@@ -175,6 +178,29 @@ def _ptr(a):
     if hasattr(a, "data_ptr"):          # torch tensor on the snapshot's device
         return _vp(a.data_ptr())
     return _vp(int(a))
+
+
+def pack_keys(keys, slot_size, key_kind=KEY_AUTO):
+    """Variable-length keys -> slots (stage_gpu_key_pack): list of bytes -> uint8 [n, slot_size]."""
+    sc = Schema(slot_size, 1, 65536, key_kind | KEY_VARLEN)
+    out = np.zeros((len(keys), slot_size), np.uint8)
+    for i, k in enumerate(keys):
+        kb = np.frombuffer(bytes(k), np.uint8)
+        _check(lib().stage_gpu_key_pack(C.byref(sc), _ptr(kb) if len(kb) else None, len(kb), _ptr(out[i])))
+    return out
+
+
+def unpack_keys(slots, key_kind=KEY_AUTO):
+    """Slots uint8 [n, slot_size] -> list of bytes (stage_gpu_key_unpack)."""
+    slots = np.ascontiguousarray(slots, np.uint8)
+    sc = Schema(slots.shape[1], 1, 65536, key_kind | KEY_VARLEN)
+    out = []
+    buf = np.zeros(slots.shape[1], np.uint8)
+    ln = C.c_uint32(0)
+    for i in range(slots.shape[0]):
+        _check(lib().stage_gpu_key_unpack(C.byref(sc), _ptr(slots[i]), _ptr(buf), C.byref(ln)))
+        out.append(bytes(buf[: ln.value]))
+    return out
 
 
 def init(device=0):

@@ -54,6 +54,30 @@ STAGE_HD SKey<NW> to_sortable(const uint8_t *key, uint32_t key_size, uint32_t xo
     return s;
 }
 
+// Variable-length keys (STAGE_KEY_VARLEN). KeyCompare orders two keys by their first min(l1, l2) bytes and then by
+// length (b_tree.h:116-134): "prefix first, shorter first". Sortable form of a key of `len` bytes in a table whose keys
+// have at most slot_size - 1 bytes: the transformed bytes, zero padding (below every transformed byte value or equal
+// to the smallest), and the length as the LAST byte — a key that is a proper prefix of another, or equals it up to
+// bytes of the minimum value, is decided by that byte exactly as the reference decides by length. Outside the library
+// such a key travels as a fixed slot of slot_size bytes, = from_sortable of this form (stage_gpu_key_pack in stage_gpu.h),
+// so every kernel treats the table as a fixed-length-key table; only the leaf transform sees real lengths.
+template <int NW>
+STAGE_HD SKey<NW> varlen_sortable(const uint8_t *key, uint32_t len, uint32_t slot_size, uint32_t xormask) {
+    SKey<NW> s;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) {
+        uint32_t v = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const uint32_t idx = (uint32_t) (i * 4 + b);
+            const uint32_t byte = idx < len ? ((uint32_t) key[idx] ^ (xormask & 0xFFu)) : (idx + 1 == slot_size ? len : 0u);
+            v = (v << 8) | byte;
+        }
+        s.w[i] = v;
+    }
+    return s;
+}
+
 // inverse: write the original key bytes
 template <int NW>
 STAGE_HD void from_sortable(const SKey<NW> &s, uint8_t *key, uint32_t key_size, uint32_t xormask) {

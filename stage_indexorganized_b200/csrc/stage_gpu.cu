@@ -12,6 +12,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <array>
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -230,10 +231,48 @@ static int schema_check(const stage_schema_t *sc, int *nw, uint32_t *xormask) {
         return STAGE_ERR_ARG;
     *nw = key_words(sc->key_size);
     if (*nw == 0) return STAGE_ERR_ARG;
-    uint32_t kind = sc->key_kind;
-    if (kind == STAGE_KEY_AUTO) kind = sc->key_size < 16 ? STAGE_KEY_SIGNED_BYTES : STAGE_KEY_MEMCMP;
+    const bool varlen = (sc->key_kind & STAGE_KEY_VARLEN) != 0;
+    uint32_t kind = sc->key_kind & ~(uint32_t) STAGE_KEY_VARLEN;
+    // variable-length keys: key_size is the slot size, the longest key has key_size - 1 bytes
+    const uint32_t longest = varlen ? sc->key_size - 1 : sc->key_size;
+    if (varlen && longest == 0) return STAGE_ERR_ARG;
+    if (kind == STAGE_KEY_AUTO) kind = longest < 16 ? STAGE_KEY_SIGNED_BYTES : STAGE_KEY_MEMCMP;
     if (kind != STAGE_KEY_SIGNED_BYTES && kind != STAGE_KEY_MEMCMP) return STAGE_ERR_ARG;
+    // KeyCompare picks the byte order per PAIR (min length < 16: signed bytes, b_tree.h:118-124): a table whose lengths
+    // straddle 16 has no single order. Signed tables hold keys of <= 15 bytes; memcmp tables keys of >= 16 (checked per
+    // record by the transform).
+    if (varlen && kind == STAGE_KEY_SIGNED_BYTES && longest > 15) return STAGE_ERR_ARG;
     *xormask = kind == STAGE_KEY_SIGNED_BYTES ? 0x80808080u : 0u;
+    return STAGE_OK;
+}
+static bool schema_varlen(const stage_schema_t *sc) { return (sc->key_kind & STAGE_KEY_VARLEN) != 0; }
+
+// stage_gpu_key_pack: key bytes, padding that sorts lowest, length byte — the inverse image of varlen_sortable (keys.cuh)
+static void pack_key_slot(const uint8_t *key, uint32_t len, uint32_t slot_size, uint32_t xormask, uint8_t *slot) {
+    const uint8_t mask = (uint8_t) (xormask & 0xFFu);
+    for (uint32_t i = 0; i + 1 < slot_size; ++i) slot[i] = i < len ? key[i] : mask;
+    slot[slot_size - 1] = (uint8_t) len ^ mask;
+}
+
+extern "C" int stage_gpu_key_pack(const stage_schema_t *schema, const void *key, uint32_t len, void *slot) {
+    int nw;
+    uint32_t xm;
+    if (!slot || (len && !key) || schema_check(schema, &nw, &xm) || !schema_varlen(schema) || len + 1 > schema->key_size ||
+        (xm == 0 && len < 16))
+        return STAGE_ERR_ARG;
+    pack_key_slot(static_cast<const uint8_t *>(key), len, schema->key_size, xm, static_cast<uint8_t *>(slot));
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_key_unpack(const stage_schema_t *schema, const void *slot, void *key_out, uint32_t *len_out) {
+    int nw;
+    uint32_t xm;
+    if (!slot || !len_out || schema_check(schema, &nw, &xm) || !schema_varlen(schema)) return STAGE_ERR_ARG;
+    const uint8_t *p = static_cast<const uint8_t *>(slot);
+    const uint32_t len = p[schema->key_size - 1] ^ (uint8_t) (xm & 0xFFu);
+    if (len + 1 > schema->key_size) return STAGE_ERR_ARG;
+    *len_out = len;
+    if (key_out && len) memcpy(key_out, p, len);
     return STAGE_OK;
 }
 
@@ -386,6 +425,7 @@ static int launch_transform(stage_snapshot *s, int buf, uint32_t n_chunk, uint64
     a.key_size = s->schema.key_size;
     a.payload_size = s->schema.payload_size;
     a.xormask = s->xormask;
+    a.varlen = schema_varlen(&s->schema) ? 1u : 0u;
     uint32_t cap = 32;
     while (cap < maxcount) cap <<= 1;
     a.sort_cap = cap;
@@ -792,6 +832,14 @@ struct WalkOut {
     std::vector<const uint8_t *> leaves;
     std::vector<const uint8_t *> fences;   // fence[i] = separator to the right of leaf i (nullptr for the last)
     uint64_t rows_upper = 0;
+    // variable-length keys: separators are packed into slots here (fences[] then points into this store)
+    bool varlen = false;
+    uint32_t xormask = 0;
+    std::deque<std::array<uint8_t, 32>> slots;
+    void key_form(const stage_schema_t *sc, uint32_t xm) {
+        varlen = schema_varlen(sc);
+        xormask = xm;
+    }
 };
 
 static int walk(const uint8_t *node, uint32_t key_size, WalkOut &w, int depth) {
@@ -812,8 +860,17 @@ static int walk(const uint8_t *node, uint32_t key_size, WalkOut &w, int depth) {
         const uint8_t *rec = node + meta_offset(m);
         if (i > 0) {
             // separator i sits between child i-1 and child i: upper fence of the last leaf emitted
-            if (meta_key_len(m) != key_size || w.leaves.empty()) return STAGE_ERR_LAYOUT;
-            w.fences.back() = rec;
+            if (w.leaves.empty()) return STAGE_ERR_LAYOUT;
+            if (w.varlen) {
+                const uint32_t len = meta_key_len(m);
+                if (len + 1 > key_size || (w.xormask == 0 && len < 16)) return STAGE_ERR_LAYOUT;
+                w.slots.emplace_back();
+                pack_key_slot(rec, len, key_size, w.xormask, w.slots.back().data());
+                w.fences.back() = w.slots.back().data();
+            } else {
+                if (meta_key_len(m) != key_size) return STAGE_ERR_LAYOUT;
+                w.fences.back() = rec;
+            }
         }
         uint64_t child;
         memcpy(&child, rec + pad_key_len(meta_key_len(m)), 8);      // GetChildByMetaIndex, b_tree.h:336-345
@@ -1121,6 +1178,10 @@ static int from_tree_impl(const void *root, const stage_schema_t *schema, stage_
     uint32_t xm;
     int rc = schema_check(schema, &nw, &xm);
     if (rc) return rc;
+    // variable-length keys: quiesced trees without version chains (the version store's slots are [key][payload] of the
+    // catalog's fixed key length, version_store.h:445-481; no variable-length table goes through it)
+    if (schema_varlen(schema) && resolve) return STAGE_ERR_ARG;
+    w.key_form(schema, xm);
     if ((rc = walk(static_cast<const uint8_t *>(root), schema->key_size, w, 0))) return rc;
 
     PHASE("walk");
@@ -1149,6 +1210,7 @@ static int from_tree_impl(const void *root, const stage_schema_t *schema, stage_
                           },
                           [&](uint64_t li) { return d.discover(li, w.leaves[li]); });
     PHASE("stage + transform");
+    if (!rc && !vers.empty() && schema_varlen(schema)) rc = STAGE_ERR_LAYOUT;
     if (!rc && !vers.empty()) rc = upload_versions_staged(s, cs);
     if (!rc) {       // fingerprints for a later stage_gpu_snapshot_refresh_from_tree
         s->h_leaf_addr.resize(w.leaves.size());
@@ -1194,7 +1256,9 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
     std::lock_guard<std::mutex> lock(old->mu);
     const stage_schema_t *schema = &old->schema;
     const uint32_t K = schema->key_size, P = schema->payload_size, ls = schema->leaf_node_size;
+    if (schema_varlen(schema) && resolve) return STAGE_ERR_ARG;
     WalkOut w;
+    w.key_form(schema, old->xormask);
     int rc;
     if ((rc = walk(static_cast<const uint8_t *>(root), K, w, 0))) return rc;
     const size_t L = w.leaves.size();

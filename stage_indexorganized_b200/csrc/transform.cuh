@@ -28,6 +28,7 @@ struct TransformArgs {
     const uint32_t *sep;        // [n_leaves] sortable upper fence of every leaf
     const uint8_t *has_sep;     // [n_leaves]
     uint32_t key_size, payload_size, xormask;
+    uint32_t varlen;            // STAGE_KEY_VARLEN: key_size is the slot size, records carry keys of 0..key_size-1 bytes
     uint32_t sort_cap;          // power of two >= max record_count in the chunk
     uint32_t *skey;
     uint16_t *slot;
@@ -86,7 +87,16 @@ __global__ void __launch_bounds__(128) leaf_transform_kernel(TransformArgs a) {
         if (m & kMetaControl) atomicExch(a.err, 1u);            // in-flight record: tree not quiesced
         const uint32_t pos = atomicAdd(&s_n, 1u);
         if (pos < a.sort_cap) {
-            SKey<NW> k = to_sortable<NW>(leaf + meta_offset(m), a.key_size, a.xormask);
+            SKey<NW> k;
+            if (a.varlen) {
+                const uint32_t len = meta_key_len(m);
+                // longer than the slot allows, or a short key in a table ordered by memcmp (KeyCompare would switch to
+                // the signed-byte order for that pair, b_tree.h:118-124): not representable
+                if (len + 1 > a.key_size || (a.xormask == 0 && len < 16)) atomicExch(a.err, 3u);
+                k = varlen_sortable<NW>(leaf + meta_offset(m), min(len, a.key_size - 1), a.key_size, a.xormask);
+            } else {
+                k = to_sortable<NW>(leaf + meta_offset(m), a.key_size, a.xormask);
+            }
 #pragma unroll
             for (int w = 0; w < NW; ++w) s_key[(size_t) pos * NW + w] = k.w[w];
             s_slot[pos] = (uint16_t) i;

@@ -387,6 +387,67 @@ static void run_driver_shape(Table &t, uint32_t n_rows, int threads, int ops_per
     printf("%-12s %s\n", "driver-shape", g_fail == fail0 ? "OK" : "FAILED");
 }
 
+// Keys of different lengths in one tree — the fixture of test/testing_btree.cpp (std::to_string keys, :393-440):
+// BTree::Read / RangeScanBySize / Iterator::GetNext against GpuTreeView built with STAGE_KEY_VARLEN (slot of 8 bytes).
+static void run_varlen(bool ref_only, uint32_t n_keys) {
+    Table t = make_table(8, 8, 16 * 1024, 4096);
+    auto insert = [&](const std::string &k, uint64_t v) {
+        RecordMeta meta;
+        ReturnCode rc = t.tree->Insert(k.data(), (uint16_t) k.size(), reinterpret_cast<const char *>(&v), &meta, INVALID_CID);
+        if (!rc.IsOk()) return;
+        auto *mp = reinterpret_cast<RecordMetadata *>(meta.GetMetaData().GetLocationPtr()->record_meta_ptr);
+        t.tree->FinalizeInsert(mp, INVALID_CID);
+    };
+    for (uint32_t i = 0; i < n_keys; ++i) insert(std::to_string((i * 7919u) % n_keys), (i * 7919u) % n_keys);   // shuffled order
+    if (ref_only) return;
+    stage_gpu::GpuTreeView view(t.tree->GetRootNodeSafe(), 8, 8, 65536, STAGE_KEY_VARLEN);
+    const int fail0 = g_fail;
+    std::vector<std::string> probes;
+    for (uint32_t i = 0; i < n_keys; i += 3) probes.push_back(std::to_string(i));
+    for (const char *k : {"", "abc", "00", "1x", "99999999", "-1"}) probes.push_back(k);     // misses ("99999999": too long for the slot)
+    probes.push_back(std::to_string(n_keys));
+    uint64_t hits = 0;
+    for (const std::string &k : probes) {
+        std::unique_ptr<Record> r = t.tree->Read(k.data(), (uint16_t) k.size(), 5, false);
+        std::unique_ptr<stage_gpu::Record> g = view.Read(k.data(), (uint16_t) k.size(), 5, false);
+        EXPECT((r == nullptr) == (g == nullptr), "varlen Read '%s': found mismatch", k.c_str());
+        if (r && g) {
+            ++hits;
+            EXPECT(r->GetKeyLength() == g->GetKeyLength() && r->GetKeyPaddedLength() == g->GetKeyPaddedLength(), "varlen Read: key length");
+            EXPECT(memcmp(r->GetKey(), g->GetKey(), k.size()) == 0, "varlen Read: key bytes");
+            EXPECT(memcmp(r->GetPayload(), g->GetPayload(), 8) == 0, "varlen Read '%s': payload", k.c_str());
+            EXPECT(r->GetCstamp() == g->GetCstamp(), "varlen Read: cstamp");
+        }
+        if (r) delete[] reinterpret_cast<char *>(r.release());
+    }
+    uint64_t rows = 0;
+    for (const char *start : {"9000", "", "1", "10", "5555", "99", "999999", ":"}) {
+        for (uint32_t size : {1u, 100u, 1000u}) {
+            const std::string k(start);
+            auto it_ref = t.tree->RangeScanBySize(k.data(), (uint16_t) k.size(), size);
+            auto it_gpu = view.RangeScanBySize(k.data(), (uint16_t) k.size(), size);
+            EXPECT(it_gpu != nullptr, "varlen scan: no iterator");
+            if (!it_gpu) continue;
+            for (uint32_t s = 0; s < size; ++s) {
+                std::unique_ptr<Record> r = it_ref->GetNext();
+                if (!r) continue;
+                std::unique_ptr<stage_gpu::Record> g = it_gpu->GetNext();
+                EXPECT(g != nullptr, "varlen iterator from '%s': gpu ran out at step %u", start, s);
+                if (g) {
+                    ++rows;
+                    EXPECT(r->GetKeyLength() == g->GetKeyLength(), "varlen iterator: key length %u vs %u", r->GetKeyLength(), g->GetKeyLength());
+                    EXPECT(memcmp(r->GetKey(), g->GetKey(), r->GetKeyLength()) == 0 && memcmp(r->GetPayload(), g->GetPayload(), 8) == 0,
+                           "varlen iterator from '%s': row %u differs", start, s);
+                }
+                delete[] reinterpret_cast<char *>(r.release());
+            }
+            EXPECT(it_gpu->GetNext() == nullptr, "varlen iterator from '%s': gpu has extra rows", start);
+        }
+    }
+    printf("variable-length keys: %zu reads (%lu hits), %lu iterator rows %s\n", probes.size(), (unsigned long) hits,
+           (unsigned long) rows, g_fail == fail0 ? "OK" : "MISMATCH");
+}
+
 int main(int argc, char **argv) {
     setvbuf(stdout, nullptr, _IOLBF, 0);      // a crash must not swallow the lines before it
     bool ref_only = false;
@@ -486,6 +547,7 @@ int main(int argc, char **argv) {
         run_checks<TupleStock>(t, probes, scans, 10, ref_only, "stock");       // stock-level scans 10 rows
     }
     run_mvcc_checks(ref_only, n_rows);
+    run_varlen(ref_only, 100000);
     printf("%s: %d failure(s)\n", ref_only ? "reference half only" : "drop-in parity", g_fail);
     return g_fail ? 1 : 0;
 }

@@ -169,6 +169,18 @@ int stage_gpu_snapshot_refresh_from_tree_live(stage_snapshot_t *old, const void 
                                               void *resolve_ctx, stage_snapshot_t **out,
                                               stage_refresh_stats_t *stats /* may be NULL */);
 
+/* The same refresh for a shard that fills its GPU (two copies of the table do not fit): *snap is REPLACED. The
+ * payload rows of the unchanged leaves are shifted inside the existing buffer to their new offsets (runs of leaves, a
+ * bounce buffer of 64 MiB where source and destination overlap), the rows of the changed leaves are transformed into
+ * the gaps; only the small columns (keys, slots, commit ids, chain heads: 14-42 B per row), the search levels and the
+ * directory are built anew, and the version table is kept as it is unless chains have to be appended. Needs room in
+ * the buffer for the new row count: stage_gpu_set_row_slack(fraction) BEFORE the snapshot is built keeps that fraction
+ * of its rows free (STAGE_ERR_NOMEM here otherwise, *snap untouched and still usable). No read may be in flight on
+ * *snap during the call and every handle derived from it (batcher) must be gone; on any other error after the rows
+ * started moving the snapshot is unusable (reads return STAGE_ERR_STATE) and must be destroyed. Quiesced trees. */
+int stage_gpu_snapshot_refresh_in_place(stage_snapshot_t **snap, const void *root, stage_refresh_stats_t *stats /* may be NULL */);
+int stage_gpu_set_row_slack(double fraction);
+
 /* Streaming construction for callers that own the walk (same result as from_tree):
  *   begin -> add_versions* -> add_leaves* -> seal.
  * leaf_images[i] points at leaf_node_size bytes of an unmodified LeafNode, leaves in tree order.

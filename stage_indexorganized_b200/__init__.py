@@ -71,6 +71,8 @@ SYMBOLS = {
     "stage_gpu_snapshot_from_tree": (_i32, [_vp, C.POINTER(Schema), C.POINTER(_vp)]),
     "stage_gpu_snapshot_from_tree_live": (_i32, [_vp, C.POINTER(Schema), _vp, _vp, C.POINTER(_vp)]),
     "stage_gpu_snapshot_refresh_from_tree": (_i32, [_vp, _vp, C.POINTER(_vp), C.POINTER(RefreshStats)]),
+    "stage_gpu_snapshot_refresh_in_place": (_i32, [_vp, _vp, _vp]),
+    "stage_gpu_set_row_slack": (_i32, [C.c_double]),
     "stage_gpu_snapshot_refresh_from_tree_live": (_i32, [_vp, _vp, _vp, _vp, C.POINTER(_vp), C.POINTER(RefreshStats)]),
     "stage_gpu_snapshot_begin": (_i32, [C.POINTER(Schema), _u64, _u64, C.POINTER(_vp)]),
     "stage_gpu_snapshot_add_versions": (_i32, [_vp, _vp, _vp, _u64]),
@@ -180,6 +182,11 @@ def _ptr(a):
     return _vp(int(a))
 
 
+def set_row_slack(fraction):
+    """Row capacity kept free in snapshots built from host trees from now on (for refresh_in_place)."""
+    _check(lib().stage_gpu_set_row_slack(float(fraction)))
+
+
 def pack_keys(keys, slot_size, key_kind=KEY_AUTO):
     """Variable-length keys -> slots (stage_gpu_key_pack): list of bytes -> uint8 [n, slot_size]."""
     sc = Schema(slot_size, 1, 65536, key_kind | KEY_VARLEN)
@@ -266,6 +273,15 @@ class Snapshot:
         else:
             _check(lib().stage_gpu_snapshot_refresh_from_tree(self.h, _vp(int(root)), C.byref(h), C.byref(st)))
         return type(self)(h, self.schema), st
+
+    def refresh_in_place(self, root):
+        """stage_gpu_snapshot_refresh_in_place: THIS snapshot becomes the refreshed one (payload rows shifted inside
+        their buffer; no second copy of the table). Returns RefreshStats. Needs row slack (set_row_slack before the
+        snapshot was built) when rows were inserted; no reads may be in flight."""
+        h, st = _vp(self.h.value if hasattr(self.h, "value") else self.h), RefreshStats()
+        _check(lib().stage_gpu_snapshot_refresh_in_place(C.byref(h), _vp(int(root)), C.byref(st)))
+        self.h = h
+        return st
 
     @classmethod
     def generate_ycsb(cls, n_rows_total, payload_size=1000, rows_per_leaf=61, first_rank=0, n_local=None,

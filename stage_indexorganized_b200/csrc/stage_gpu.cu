@@ -344,7 +344,7 @@ static int snapshot_new(const stage_schema_t *schema, stage_snapshot **out) {
     return STAGE_OK;
 }
 
-static int alloc_columns(stage_snapshot *s, uint64_t cap_leaves, uint64_t cap_rows) {
+static int alloc_columns(stage_snapshot *s, uint64_t cap_leaves, uint64_t cap_rows, uint8_t *adopt_payload = nullptr) {
     // source rows travel as u32 with bit 31 = "row of the version table" (gather.cuh kVersionRowFlag): a shard holds
     // fewer than 2^31 rows (include/stage_gpu.h, stage_schema_t)
     if (cap_rows >= (uint64_t) kVersionRowFlag) return STAGE_ERR_ARG;
@@ -363,7 +363,12 @@ static int alloc_columns(stage_snapshot *s, uint64_t cap_leaves, uint64_t cap_ro
     if ((rc = dev_alloc(s, &s->d_slot, cap_rows))) return rc;
     if ((rc = dev_alloc(s, &s->d_ts, cap_rows))) return rc;
     if ((rc = dev_alloc(s, &s->d_chain, cap_rows))) return rc;
-    if ((rc = dev_alloc(s, &s->d_payload, cap_rows * (uint64_t) s->schema.payload_size))) return rc;
+    if (adopt_payload) {                       // in-place refresh: the previous snapshot's payload buffer, same capacity
+        s->d_payload = adopt_payload;
+        s->device_bytes += cap_rows * (uint64_t) s->schema.payload_size + 256;
+    } else if ((rc = dev_alloc(s, &s->d_payload, cap_rows * (uint64_t) s->schema.payload_size))) {
+        return rc;
+    }
     if ((rc = dev_alloc(s, &s->d_leaf_off, cap_leaves + 1))) return rc;
     if ((rc = dev_alloc(s, &s->d_sep, (cap_leaves + 1) * s->nw))) return rc;
     if ((rc = dev_alloc(s, &s->d_cont, cap_leaves + 1))) return rc;
@@ -386,19 +391,38 @@ static int alloc_staging(stage_snapshot *s) {
     return STAGE_OK;
 }
 
-extern "C" int stage_gpu_snapshot_begin(const stage_schema_t *schema, uint64_t n_leaves_hint, uint64_t n_rows_hint,
-                                        stage_snapshot_t **out) {
+static int snapshot_begin_impl(const stage_schema_t *schema, uint64_t n_leaves_hint, uint64_t n_rows_hint, uint8_t *adopt_payload,
+                               stage_snapshot_t **out) {
     if (!out) return STAGE_ERR_ARG;
     stage_snapshot *s = nullptr;
     int rc = snapshot_new(schema, &s);
     if (rc) return rc;
-    if ((rc = alloc_columns(s, std::max<uint64_t>(n_leaves_hint, 1), n_rows_hint)) || (rc = alloc_staging(s))) {
+    if ((rc = alloc_columns(s, std::max<uint64_t>(n_leaves_hint, 1), n_rows_hint, adopt_payload)) || (rc = alloc_staging(s))) {
+        if (adopt_payload) s->d_payload = nullptr;       // still owned by the snapshot it came from
         snapshot_free(s);
         return rc;
     }
     s->h_leaf_off.push_back(0);
     *out = s;
     return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_begin(const stage_schema_t *schema, uint64_t n_leaves_hint, uint64_t n_rows_hint,
+                                        stage_snapshot_t **out) {
+    return snapshot_begin_impl(schema, n_leaves_hint, n_rows_hint, nullptr, out);
+}
+
+// Row capacity kept free in snapshots built from a host tree (fraction of the rows), so that a later
+// stage_gpu_snapshot_refresh_in_place has room for inserted rows. Process-wide, default 0.
+static std::atomic<uint32_t> g_row_slack_ppm{0};
+extern "C" int stage_gpu_set_row_slack(double fraction) {
+    if (!(fraction >= 0.0) || fraction > 4.0) return STAGE_ERR_ARG;
+    g_row_slack_ppm.store((uint32_t) (fraction * 1e6));
+    return STAGE_OK;
+}
+static uint64_t with_row_slack(uint64_t rows) {
+    const uint64_t extra = (uint64_t) ((double) rows * g_row_slack_ppm.load() * 1e-6);
+    return std::min<uint64_t>(rows + extra, (uint64_t) kVersionRowFlag - 1);
 }
 
 extern "C" int stage_gpu_snapshot_add_versions(stage_snapshot_t *s, const stage_version_t *versions,
@@ -1186,7 +1210,7 @@ static int from_tree_impl(const void *root, const stage_schema_t *schema, stage_
 
     PHASE("walk");
     stage_snapshot *s = nullptr;
-    if ((rc = stage_gpu_snapshot_begin(schema, w.leaves.size(), w.rows_upper, &s))) return rc;
+    if ((rc = stage_gpu_snapshot_begin(schema, w.leaves.size(), with_row_slack(w.rows_upper), &s))) return rc;
     PHASE("alloc");
 
     const uint32_t K = schema->key_size, P = schema->payload_size;
@@ -1248,8 +1272,55 @@ extern "C" int stage_gpu_snapshot_from_tree_live(const void *root, const stage_s
 // deletes and the leaf splits they caused. Unchanged leaves (same address, same fingerprint) are carried over on
 // the device; only changed and new leaves cross PCIe and go through the transform kernel again.
 // ------------------------------------------------------------------------------------------------
+// In-place refresh: rows of the carried leaves move inside the payload buffer. Consecutive carried leaves whose rows
+// shift by the same distance form a run; runs keep their order (a B-tree never reorders untouched leaves), so moving the
+// left-shifting runs in ascending order and then the right-shifting runs in descending order never overwrites a row
+// that has not been moved yet. A run whose source and destination overlap goes through a bounce buffer, chunk by chunk
+// in the direction of the shift.
+struct RowRun {
+    uint64_t src, dst, n;      // rows
+};
+static int shift_payload_runs(uint8_t *payload, uint32_t P, const std::vector<RowRun> &runs, cudaStream_t st) {
+    constexpr uint64_t kBounce = 64ull << 20;
+    uint8_t *tmp = nullptr;
+    auto move_run = [&](const RowRun &r) -> int {
+        const uint64_t sb = r.src * P, db = r.dst * P, len = r.n * P;
+        if (sb == db || len == 0) return STAGE_OK;
+        const uint64_t dist = sb > db ? sb - db : db - sb;
+        const bool left = db < sb;
+        if (dist >= len) {                                   // disjoint: one copy
+            CUDA_TRY(cudaMemcpyAsync(payload + db, payload + sb, len, cudaMemcpyDeviceToDevice, st));
+            return STAGE_OK;
+        }
+        const bool direct = dist >= kBounce;                 // a chunk never reaches into its own source
+        if (!direct && !tmp) CUDA_TRY(cudaMalloc((void **) &tmp, kBounce));
+        const uint64_t n_chunks = (len + kBounce - 1) / kBounce;
+        for (uint64_t k = 0; k < n_chunks; ++k) {
+            const uint64_t c = left ? k : n_chunks - 1 - k;  // ascending for a left shift, descending for a right shift
+            const uint64_t off = c * kBounce, m = std::min(kBounce, len - off);
+            if (direct) {
+                CUDA_TRY(cudaMemcpyAsync(payload + db + off, payload + sb + off, m, cudaMemcpyDeviceToDevice, st));
+            } else {
+                CUDA_TRY(cudaMemcpyAsync(tmp, payload + sb + off, m, cudaMemcpyDeviceToDevice, st));
+                CUDA_TRY(cudaMemcpyAsync(payload + db + off, tmp, m, cudaMemcpyDeviceToDevice, st));
+            }
+        }
+        return STAGE_OK;
+    };
+    int rc = STAGE_OK;
+    for (size_t i = 0; i < runs.size() && !rc; ++i)
+        if (runs[i].dst < runs[i].src) rc = move_run(runs[i]);
+    for (size_t i = runs.size(); i-- > 0 && !rc;)
+        if (runs[i].dst > runs[i].src) rc = move_run(runs[i]);
+    if (tmp) {
+        cudaStreamSynchronize(st);
+        cudaFree(tmp);
+    }
+    return rc;
+}
+
 static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_resolver_t resolve, void *resolve_ctx,
-                        stage_snapshot_t **out, stage_refresh_stats_t *stats) {
+                        stage_snapshot_t **out, stage_refresh_stats_t *stats, bool in_place = false) {
     if (!old || !root || !out) return STAGE_ERR_ARG;
     if (!old->sealed || old->h_leaf_addr.size() != old->n_leaves || old->h_leaf_off.size() != old->n_leaves + 1)
         return STAGE_ERR_STATE;                       // only snapshots that came from a host tree carry fingerprints
@@ -1315,12 +1386,36 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
     for (size_t j = 0; j < L; ++j) n_rows += vis[j];
 
     stage_snapshot *s = nullptr;
-    if ((rc = stage_gpu_snapshot_begin(schema, L, n_rows, &s))) return rc;
+    bool rows_moved = false, versions_adopted = false;
+    if (in_place) {
+        if (n_rows > old->cap_rows) {
+            g_last_error = "in-place refresh: the snapshot has no room for the new rows (stage_gpu_set_row_slack before it is built)";
+            return STAGE_ERR_NOMEM;
+        }
+        uint32_t prev = 0;
+        bool any = false;
+        for (size_t j = 0; j < L; ++j) {                    // carried leaves keep their order
+            if (src_leaf[j] == kNoLeaf) continue;
+            if (any && src_leaf[j] <= prev) return STAGE_ERR_STATE;
+            prev = src_leaf[j];
+            any = true;
+        }
+        CUDA_TRY(cudaStreamSynchronize(old->stream));
+        rc = snapshot_begin_impl(schema, L, old->cap_rows, old->d_payload, &s);
+    } else {
+        rc = stage_gpu_snapshot_begin(schema, L, with_row_slack(n_rows), &s);
+    }
+    if (rc) return rc;
     uint32_t *d_src_leaf = nullptr, *d_changed = nullptr;
     auto fail = [&](int code) {
         cudaStreamSynchronize(s->stream);
         if (d_src_leaf) cudaFree(d_src_leaf);
         if (d_changed) cudaFree(d_changed);
+        if (in_place) {
+            s->d_payload = nullptr;                         // belongs to `old`
+            if (versions_adopted) s->d_ver_begin = s->d_ver_commit = s->d_ver_next = nullptr, s->d_ver_payload = nullptr;
+            if (rows_moved) old->sealed = false;            // its rows are no longer where its columns say: unusable
+        }
         snapshot_free(s);
         return code;
     };
@@ -1356,12 +1451,23 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
         c.old_slot = old->d_slot; c.new_slot = s->d_slot;
         c.old_ts = old->d_ts; c.new_ts = s->d_ts;
         c.old_chain = old->d_chain; c.new_chain = s->d_chain;
-        c.old_payload = old->d_payload; c.new_payload = s->d_payload;
+        c.old_payload = old->d_payload; c.new_payload = in_place ? nullptr : s->d_payload;
         c.old_cont = old->d_cont; c.new_cont = s->d_cont;
         c.nw = (uint32_t) s->nw; c.payload_size = P;
         leaf_carry_kernel<<<(unsigned) std::min<uint64_t>(L, (uint64_t) sm_count() * 8), 256, 0, st>>>(c);
         if (cudaGetLastError() != cudaSuccess) return fail(STAGE_ERR_CUDA);
         g_launches.fetch_add(1);
+        if (in_place) {
+            std::vector<RowRun> runs;
+            for (size_t j = 0; j < L; ++j) {
+                if (src_leaf[j] == kNoLeaf || vis[j] == 0) continue;
+                const uint64_t src = old->h_leaf_off[src_leaf[j]], dst = s->h_leaf_off[j];
+                if (!runs.empty() && runs.back().src + runs.back().n == src && runs.back().dst + runs.back().n == dst) runs.back().n += vis[j];
+                else runs.push_back(RowRun{src, dst, vis[j]});
+            }
+            rows_moved = true;
+            if ((rc = shift_payload_runs(s->d_payload, P, runs, st))) return fail(rc);
+        }
     }
 
     // 3. changed leaves: images, transform
@@ -1421,7 +1527,13 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
     // 4. version table: the previous one (device copy) followed by the chains of the changed leaves
     const uint64_t V0 = old->n_versions, V1 = cs.vers.size(), V = V0 + V1;
     uint8_t *vbuf = nullptr;
-    if (!rc && V) {
+    if (!rc && in_place && V1 == 0 && V0) {           // nothing to append: the previous version table as it is
+        s->d_ver_begin = old->d_ver_begin; s->d_ver_commit = old->d_ver_commit; s->d_ver_next = old->d_ver_next;
+        s->d_ver_payload = old->d_ver_payload;
+        s->ver_cap = old->ver_cap;
+        s->n_versions = V0;
+        versions_adopted = true;
+    } else if (!rc && V) {
         if ((rc = dev_alloc(s, &s->d_ver_begin, V)) || (rc = dev_alloc(s, &s->d_ver_commit, V)) ||
             (rc = dev_alloc(s, &s->d_ver_next, V)) || (rc = dev_alloc(s, &s->d_ver_payload, V * (uint64_t) P))) {
         } else {
@@ -1473,7 +1585,22 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
         stats->versions_added = V1;
         stats->host_bytes_staged = (uint64_t) changed.size() * ls + V1 * (uint64_t) P;
     }
+    if (in_place) {                                     // the buffers now belong to the new snapshot
+        old->d_payload = nullptr;
+        if (versions_adopted) old->d_ver_begin = old->d_ver_commit = old->d_ver_next = nullptr, old->d_ver_payload = nullptr;
+        old->sealed = false;
+    }
     *out = s;
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_snapshot_refresh_in_place(stage_snapshot_t **snap, const void *root, stage_refresh_stats_t *stats) {
+    if (!snap || !*snap) return STAGE_ERR_ARG;
+    stage_snapshot *old = *snap, *next = nullptr;
+    const int rc = refresh_impl(old, root, nullptr, nullptr, &next, stats, true);
+    if (rc) return rc;
+    stage_gpu_snapshot_destroy(old);
+    *snap = next;
     return STAGE_OK;
 }
 

@@ -207,7 +207,8 @@ __global__ void __launch_bounds__(256) leaf_carry_kernel(LeafCarryArgs a) {
         cta_copy_bytes(reinterpret_cast<const uint8_t *>(a.old_slot + r0), reinterpret_cast<uint8_t *>(a.new_slot + d0), n * 2);
         cta_copy_bytes(reinterpret_cast<const uint8_t *>(a.old_ts + r0), reinterpret_cast<uint8_t *>(a.new_ts + d0), n * 4);
         cta_copy_bytes(reinterpret_cast<const uint8_t *>(a.old_chain + r0), reinterpret_cast<uint8_t *>(a.new_chain + d0), n * 4);
-        cta_copy_bytes(a.old_payload + r0 * a.payload_size, a.new_payload + d0 * a.payload_size, n * a.payload_size);
+        // in-place refresh: the payload column is the previous snapshot's buffer, its rows are shifted separately
+        if (a.new_payload) cta_copy_bytes(a.old_payload + r0 * a.payload_size, a.new_payload + d0 * a.payload_size, n * a.payload_size);
         if (threadIdx.x == 0) a.new_cont[j] = a.old_cont[o];
     }
 }

@@ -239,3 +239,127 @@ def test_snapshots_while_update_transactions_are_running():
         pk = u32_keys(rng.integers(0, N, 20000))
         for read_ts in (0, 50000, 0xFFFFFFFF):
             assert_probe_equal(q.probe(pk, read_ts), t.probe(pk, read_ts), f"quiesced ts={read_ts}")
+
+
+@pytest.mark.parametrize("cls", checker_classes(), ids=lambda c: c.__name__)
+def test_refresh_in_place_shifts_rows_inside_the_payload_buffer(cls):
+    """stage_gpu_snapshot_refresh_in_place: the same rounds (updates with new chains, inserts with leaf splits in the
+    middle of the key order -> rows to the right shift right; deletes -> rows shift left; nothing changed) with the
+    payload rows moved inside the existing buffer. Answers equal the tree's and a from-scratch snapshot's, the device
+    footprint does not grow beyond the small columns, and a snapshot without room refuses and stays usable."""
+    N, P = 40000, 200
+    t = ycsb_int_table(cls, N, P)
+    rng = np.random.default_rng(77)
+    assert t.commit_update_batch(u32_keys(rng.integers(0, N, 3000)), 10) == 3000
+    probes = u32_keys(np.concatenate([rng.integers(0, N + 50, 6000), 0x10000007 + 256 * rng.integers(0, 2600, 3000)]))
+    starts = np.concatenate([u32_keys(rng.integers(0, N, 96)), u32_keys(0x10000007 + 256 * rng.integers(0, 2500, 32))])
+    stamps = (0, 10, 1500, 3009, 5000, 5010, 5020, 6000, 6500, 9000)
+    ik = (0x10000007 + 256 * np.arange(2500)).astype(np.uint32)
+    rng.shuffle(ik)
+    ipay = np.repeat((ik >> 8).astype(np.uint8)[:, None], P, axis=1)
+
+    tight = sg.Snapshot.from_tree(t.root, 4, P)                       # no slack: inserts cannot be taken in place
+    sg.set_row_slack(0.10)
+    try:
+        snap = sg.Snapshot.from_tree(t.root, 4, P)
+    finally:
+        sg.set_row_slack(0.0)
+    try:
+        bytes0 = snap.info().device_bytes
+        L0 = snap.info().n_leaves
+        # round 1: committed updates (new chains are appended to the version table)
+        assert t.commit_update_batch(u32_keys(rng.integers(0, N, 12).astype(np.uint32)), 5000) == 12
+        st = snap.refresh_in_place(t.root)
+        assert st.leaves_total == L0 and 1 <= st.leaves_transformed <= 12 and st.versions_added >= 12
+        _check(snap, t, probes, starts, 150, stamps, "in place, after updates")
+        # round 2: inserts into one region -> splits; every row behind them shifts right
+        assert t.insert(u32_keys(ik), ipay, 5010) == 2500
+        with pytest.raises(sg.StageError):
+            tight.refresh_in_place(t.root)                            # no room: refused before anything moved
+        assert tight.info().n_rows == N and tight.probe(probes[:16], 0)[0].shape == (16,)     # untouched, still answers
+        st = snap.refresh_in_place(t.root)
+        assert st.leaves_total > L0 and st.rows == N + 2500
+        assert st.leaves_carried >= L0 - 8
+        _check(snap, t, probes, starts, 150, stamps, "in place, after inserts")
+        # round 3: deletes everywhere (rows shift left) + updates of inserted rows
+        dk = np.concatenate([rng.choice(N, 400, replace=False).astype(np.uint32), ik[:200]])
+        for key in u32_keys(dk):
+            t.delete(key)
+        assert t.commit_update_batch(u32_keys(ik[300:400]), 6000) == 100
+        st = snap.refresh_in_place(t.root)
+        assert st.rows == N + 2500 - 600
+        _check(snap, t, probes, starts, 150, stamps, "in place, after deletes")
+        # round 4: nothing changed -> nothing staged, the version table is kept as it is
+        st = snap.refresh_in_place(t.root)
+        assert st.leaves_transformed == 0 and st.host_bytes_staged == 0 and st.versions_added == 0
+        _check(snap, t, probes, starts, 150, (0, 5015, 9000), "in place, no-op")
+        with sg.Snapshot.from_tree(t.root, 4, P) as fresh:
+            a, b = snap.info(), fresh.info()
+            assert (a.n_rows, a.n_leaves, a.max_leaf_rows) == (b.n_rows, b.n_leaves, b.max_leaf_rows)
+            for read_ts in (0, 5005, 9000):
+                assert_probe_equal(snap.probe(probes, read_ts), fresh.probe(probes, read_ts), "vs fresh")
+                assert_scan_equal(snap.scan(starts, 150, read_ts, 1), fresh.scan(starts, 150, read_ts, 1), "vs fresh")
+        # the payload buffer was never duplicated: the footprint stays within the small columns + version growth
+        assert snap.info().device_bytes < bytes0 * 1.15
+        # and the ordinary refresh still works on a snapshot that went through in-place rounds
+        assert t.commit_update_batch(u32_keys(ik[500:520]), 7000) == 20
+        s2, st = snap.refresh_from_tree(t.root)
+        _check(s2, t, probes, starts, 150, (0, 6999, 7010, 9000), "two-table refresh after in-place rounds")
+        s2.close()
+    finally:
+        snap.close()
+        tight.close()
+
+
+def test_refresh_in_place_large_shifts():
+    """A 250 MB payload column whose rows shift by less than the 64 MiB bounce buffer (overlapping runs, several chunks,
+    right then left) and by more (chunks that never reach into their own source): keys with low byte 0x80 sort first in
+    the reference order, so inserting / deleting them moves nearly every row of the table."""
+    N, P = 250_000, 1000
+    t = ycsb_int_table(pyoracle.OracleTable, N, P)
+    rng = np.random.default_rng(5)
+    sg.set_row_slack(0.40)
+    try:
+        snap = sg.Snapshot.from_tree(t.root, 4, P)
+    finally:
+        sg.set_row_slack(0.0)
+
+    def front_keys(lo, n):
+        return (0x80 + 256 * (1000 + lo + np.arange(n))).astype(np.uint32)
+
+    def check(what, extra):
+        probes = u32_keys(np.concatenate([rng.integers(0, N, 20000).astype(np.uint32), extra]))
+        starts = u32_keys(np.concatenate([rng.integers(0, N, 48).astype(np.uint32), extra[:16]]))
+        for read_ts in (0, 50):
+            assert_probe_equal(snap.probe(probes, read_ts), t.probe(probes, read_ts), what)
+            assert_scan_equal(snap.scan(starts, 300, read_ts, 1), t.scan(starts, 300, read_ts, 1), what)
+
+    try:
+        bytes0 = snap.info().device_bytes
+        a = front_keys(0, 3000)
+        assert t.insert(u32_keys(a), np.repeat((a >> 8).astype(np.uint8)[:, None], P, axis=1), 20) == 3000
+        st = snap.refresh_in_place(t.root)                    # ~3 MB to the right, through the bounce buffer
+        assert st.rows == N + 3000 and st.leaves_carried > 0.9 * st.leaves_total
+        check("right shift, bounce", a)
+        for key in u32_keys(a[:2000]):
+            t.delete(key)
+        st = snap.refresh_in_place(t.root)                    # ~2 MB to the left
+        assert st.rows == N + 1000
+        check("left shift, bounce", a)
+        b = front_keys(3000, 70_000)
+        assert t.insert(u32_keys(b), np.repeat((b >> 8).astype(np.uint8)[:, None], P, axis=1), 30) == 70_000
+        st = snap.refresh_in_place(t.root)                    # 70 MB to the right: direct chunks
+        assert st.rows == N + 71_000
+        check("right shift, direct chunks", np.concatenate([a, b[:5000]]))
+        for key in u32_keys(b[:68_000]):
+            t.delete(key)
+        st = snap.refresh_in_place(t.root)                    # 68 MB to the left
+        assert st.rows == N + 3000
+        check("left shift, direct chunks", np.concatenate([a, b[-5000:]]))
+        with sg.Snapshot.from_tree(t.root, 4, P) as fresh:
+            probes = u32_keys(rng.integers(0, N, 50000).astype(np.uint32))
+            assert_probe_equal(snap.probe(probes, 99), fresh.probe(probes, 99), "vs fresh")
+        assert snap.info().device_bytes < bytes0 * 1.1
+    finally:
+        snap.close()
+        t.close()

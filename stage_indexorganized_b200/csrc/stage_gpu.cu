@@ -515,18 +515,6 @@ constexpr int kStageRetry = -100;              // internal: the leaf moved betwe
 
 // Copy one leaf image into its pinned staging slot, count its visible records and replace the host TupleHeader
 // pointers in RecordMetadata.next_ptr by version indices. Thread-safe: touches only `dst`.
-// hostcopy.cpp: streaming-store copy for leaf images (STAGE_STAGING_NT=0 falls back to memcpy)
-extern "C" int stage_host_has_avx2(void);
-extern "C" void stage_host_stream_copy(uint8_t *dst, const uint8_t *src, size_t n);
-static void copy_leaf_image(uint8_t *dst, const uint8_t *src, size_t n) {
-    static const bool nt = [] {
-        const char *e = getenv("STAGE_STAGING_NT");
-        return (!e || atoi(e) != 0) && stage_host_has_avx2();
-    }();
-    if (nt && (n & 127u) == 0 && ((uintptr_t) dst & 31u) == 0) stage_host_stream_copy(dst, src, n);
-    else memcpy(dst, src, n);
-}
-
 static int stage_copy_leaf(const stage_snapshot *s, uint8_t *dst, const uint8_t *leaf, const LeafExtras &ex,
                            uint32_t *vis_out, uint32_t *count_out) {
     const uint32_t ls = s->schema.leaf_node_size;
@@ -536,7 +524,7 @@ static int stage_copy_leaf(const stage_snapshot *s, uint8_t *dst, const uint8_t 
     if (status & kStatusFrozen) return STAGE_ERR_NOT_QUIESCED;
     const uint32_t count = status_record_count(status);
     if ((uint64_t) kOffMeta + (uint64_t) count * kMetaSize > ls) return STAGE_ERR_LAYOUT;
-    copy_leaf_image(dst, leaf, ls);
+    memcpy(dst, leaf, ls);
     if (ex.expect_fp) {
         // writers are running: what was copied (and what the leaf holds right after the copy) must still be what the
         // discovery pass saw — every begin / commit / abort of an update rewrites a metadata word or the chain pointer

@@ -1471,6 +1471,7 @@ static int refresh_impl(stage_snapshot_t *old, const void *root, stage_undo_reso
     }
 
     // 3. changed leaves: images, transform
+    if (in_place && !changed.empty()) rows_moved = true;        // the transform writes into the previous snapshot's buffer
     if (!rc && !changed.empty()) {
         if (cudaMalloc((void **) &d_changed, changed.size() * 4) != cudaSuccess) rc = STAGE_ERR_NOMEM;
         else if (cudaMemcpyAsync(d_changed, changed.data(), changed.size() * 4, cudaMemcpyHostToDevice, st) != cudaSuccess)

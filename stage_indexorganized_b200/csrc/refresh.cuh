@@ -106,4 +106,54 @@ __global__ void refresh_clear_unused_kernel(RefreshArgs a) {
     }
 }
 
+// ---- version-table compaction -----------------------------------------------------------------------------------
+// Every refresh that re-transforms a leaf stages the chains of its rows again (append-only), so the copies the previous
+// snapshot held for that leaf stay behind unreferenced. Mark what the chain column still reaches, renumber, move.
+__global__ void versions_mark_kernel(const uint32_t *__restrict__ chain, uint64_t n_rows, const uint32_t *__restrict__ ver_next,
+                                     uint64_t n_versions, uint32_t *__restrict__ live) {
+    for (uint64_t r = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += (uint64_t) gridDim.x * blockDim.x) {
+        uint32_t v = chain[r];                               // 1-based, 0 = no chain
+        uint32_t hops = 0;
+        while (v != 0 && v <= n_versions && hops++ < (1u << 20)) {
+            if (atomicExch(live + (v - 1), 1u)) break;       // somebody else walks the rest of this chain
+            v = ver_next[v - 1];
+        }
+    }
+}
+
+// new_index = exclusive prefix sum of live[]; copies the surviving versions to their new places (one warp per version)
+__global__ void versions_move_kernel(const uint32_t *__restrict__ live, const uint32_t *__restrict__ new_index, uint64_t n_versions,
+                                     const uint32_t *__restrict__ ob, const uint32_t *__restrict__ oc, const uint32_t *__restrict__ on,
+                                     const uint8_t *__restrict__ op, uint32_t *__restrict__ nb, uint32_t *__restrict__ nc,
+                                     uint32_t *__restrict__ nn, uint8_t *__restrict__ np, uint32_t payload_size) {
+    const int lane = threadIdx.x & 31;
+    const uint64_t warps = ((uint64_t) gridDim.x * blockDim.x) >> 5;
+    for (uint64_t v = ((uint64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5; v < n_versions; v += warps) {
+        if (!live[v]) continue;
+        const uint32_t d = new_index[v];
+        if (lane == 0) {
+            nb[d] = ob[v];
+            nc[d] = oc[v];
+            const uint32_t nx = on[v];
+            nn[d] = (nx != 0 && nx <= n_versions && live[nx - 1]) ? new_index[nx - 1] + 1 : 0;
+        }
+        const uint8_t *src = op + v * (uint64_t) payload_size;
+        uint8_t *dst = np + d * (uint64_t) payload_size;
+        if ((payload_size & 3u) == 0) {
+            for (uint32_t b = lane * 4; b < payload_size; b += 128)
+                *reinterpret_cast<uint32_t *>(dst + b) = *reinterpret_cast<const uint32_t *>(src + b);
+        } else {
+            for (uint32_t b = lane; b < payload_size; b += 32) dst[b] = src[b];
+        }
+    }
+}
+
+__global__ void versions_remap_chain_kernel(uint32_t *__restrict__ chain, uint64_t n_rows, const uint32_t *__restrict__ live,
+                                            const uint32_t *__restrict__ new_index, uint64_t n_versions) {
+    for (uint64_t r = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += (uint64_t) gridDim.x * blockDim.x) {
+        const uint32_t v = chain[r];
+        if (v != 0) chain[r] = (v <= n_versions && live[v - 1]) ? new_index[v - 1] + 1 : 0;
+    }
+}
+
 }  // namespace stage

@@ -181,6 +181,12 @@ int stage_gpu_snapshot_refresh_from_tree_live(stage_snapshot_t *old, const void 
 int stage_gpu_snapshot_refresh_in_place(stage_snapshot_t **snap, const void *root, stage_refresh_stats_t *stats /* may be NULL */);
 int stage_gpu_set_row_slack(double fraction);
 
+/* Both refresh forms stage the chains of every re-transformed leaf again (the version table is append-only), so the
+ * copies the previous snapshot held for those leaves stay behind unreferenced. This drops every version no chain head
+ * reaches any more and renumbers the rest (mark from the chain column, prefix sum, move); reads give the same answers
+ * before and after. No read may be in flight during the call. kept / dropped may be NULL. */
+int stage_gpu_snapshot_compact_versions(stage_snapshot_t *s, uint64_t *kept, uint64_t *dropped);
+
 /* Streaming construction for callers that own the walk (same result as from_tree):
  *   begin -> add_versions* -> add_leaves* -> seal.
  * leaf_images[i] points at leaf_node_size bytes of an unmodified LeafNode, leaves in tree order.

@@ -71,6 +71,7 @@ SYMBOLS = {
     "stage_gpu_snapshot_from_tree": (_i32, [_vp, C.POINTER(Schema), C.POINTER(_vp)]),
     "stage_gpu_snapshot_from_tree_live": (_i32, [_vp, C.POINTER(Schema), _vp, _vp, C.POINTER(_vp)]),
     "stage_gpu_snapshot_refresh_from_tree": (_i32, [_vp, _vp, C.POINTER(_vp), C.POINTER(RefreshStats)]),
+    "stage_gpu_snapshot_compact_versions": (_i32, [_vp, _vp, _vp]),
     "stage_gpu_snapshot_refresh_in_place": (_i32, [_vp, _vp, _vp]),
     "stage_gpu_set_row_slack": (_i32, [C.c_double]),
     "stage_gpu_snapshot_refresh_from_tree_live": (_i32, [_vp, _vp, _vp, _vp, C.POINTER(_vp), C.POINTER(RefreshStats)]),
@@ -273,6 +274,12 @@ class Snapshot:
         else:
             _check(lib().stage_gpu_snapshot_refresh_from_tree(self.h, _vp(int(root)), C.byref(h), C.byref(st)))
         return type(self)(h, self.schema), st
+
+    def compact_versions(self):
+        """Drop the versions no chain reaches any more (left behind by refreshes) -> (kept, dropped)."""
+        kept, dropped = _u64(0), _u64(0)
+        _check(lib().stage_gpu_snapshot_compact_versions(self.h, C.byref(kept), C.byref(dropped)))
+        return kept.value, dropped.value
 
     def refresh_in_place(self, root):
         """stage_gpu_snapshot_refresh_in_place: THIS snapshot becomes the refreshed one (payload rows shifted inside

@@ -1748,6 +1748,71 @@ static int grow_versions(stage_snapshot *s, uint64_t need) {
     return STAGE_OK;
 }
 
+// Version-table compaction: drops the versions no chain reaches any more (the copies left behind by refreshes that
+// re-transformed their leaves) and renumbers the rest. Exclusive like apply_updates: no read in flight.
+extern "C" int stage_gpu_snapshot_compact_versions(stage_snapshot_t *s, uint64_t *kept_out, uint64_t *dropped_out) {
+    if (!s) return STAGE_ERR_ARG;
+    if (!s->sealed) return STAGE_ERR_STATE;
+    std::lock_guard<std::mutex> lock(s->mu);
+    CUDA_TRY(cudaSetDevice(s->device));
+    const uint64_t V = s->n_versions, P = s->schema.payload_size;
+    if (kept_out) *kept_out = V;
+    if (dropped_out) *dropped_out = 0;
+    if (V == 0) return STAGE_OK;
+    cudaStream_t st = s->stream;
+    uint32_t *live = nullptr, *idx = nullptr, *nb = nullptr, *nc = nullptr, *nn = nullptr;
+    uint8_t *np_ = nullptr;
+    void *tmp = nullptr;
+    auto cleanup = [&](int code) {
+        cudaStreamSynchronize(st);
+        for (void *p : {(void *) live, (void *) idx, (void *) nb, (void *) nc, (void *) nn, (void *) np_, tmp})
+            if (p) cudaFree(p);
+        return code;
+    };
+#define CV_TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { g_last_error = cudaGetErrorString(e_); return cleanup(STAGE_ERR_CUDA); } } while (0)
+    CV_TRY(cudaMalloc((void **) &live, (V + 1) * 4));
+    CV_TRY(cudaMalloc((void **) &idx, (V + 1) * 4));
+    CV_TRY(cudaMemsetAsync(live, 0, (V + 1) * 4, st));
+    const unsigned rb = (unsigned) std::min<uint64_t>((s->n_rows + 255) / 256 + 1, (uint64_t) sm_count() * 16);
+    versions_mark_kernel<<<rb, 256, 0, st>>>(s->d_chain, s->n_rows, s->d_ver_next, V, live);
+    CV_TRY(cudaGetLastError());
+    size_t tmp_bytes = 0;
+    CV_TRY(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, live, idx, V + 1, st));
+    CV_TRY(cudaMalloc(&tmp, tmp_bytes));
+    CV_TRY(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, live, idx, V + 1, st));      // idx[V] = number of live versions
+    uint32_t kept32 = 0;
+    CV_TRY(cudaMemcpyAsync(&kept32, idx + V, 4, cudaMemcpyDeviceToHost, st));
+    CV_TRY(cudaStreamSynchronize(st));
+    const uint64_t kept = kept32;
+    if (kept == V) return cleanup(STAGE_OK);                 // nothing to drop
+    const uint64_t cap = std::max<uint64_t>(kept, 1);
+    CV_TRY(cudaMalloc((void **) &nb, cap * 4));
+    CV_TRY(cudaMalloc((void **) &nc, cap * 4));
+    CV_TRY(cudaMalloc((void **) &nn, cap * 4));
+    CV_TRY(cudaMalloc((void **) &np_, cap * P + 256));
+    const unsigned vb = (unsigned) std::min<uint64_t>((V + 7) / 8, (uint64_t) sm_count() * 16);
+    versions_move_kernel<<<vb, 256, 0, st>>>(live, idx, V, s->d_ver_begin, s->d_ver_commit, s->d_ver_next, s->d_ver_payload, nb, nc, nn,
+                                             np_, (uint32_t) P);
+    CV_TRY(cudaGetLastError());
+    versions_remap_chain_kernel<<<rb, 256, 0, st>>>(s->d_chain, s->n_rows, live, idx, V);
+    CV_TRY(cudaGetLastError());
+    CV_TRY(cudaStreamSynchronize(st));
+#undef CV_TRY
+    g_launches.fetch_add(3);
+    void *old[] = {s->d_ver_begin, s->d_ver_commit, s->d_ver_next, s->d_ver_payload};
+    for (void *p : old)
+        if (p) cudaFree(p);
+    s->d_ver_begin = nb; s->d_ver_commit = nc; s->d_ver_next = nn; s->d_ver_payload = np_;
+    nb = nc = nn = nullptr;
+    np_ = nullptr;
+    s->n_versions = kept;
+    s->ver_cap = cap;
+    fill_view(s);
+    if (kept_out) *kept_out = kept;
+    if (dropped_out) *dropped_out = V - kept;
+    return cleanup(STAGE_OK);
+}
+
 extern "C" int stage_gpu_snapshot_apply_updates(stage_snapshot_t *s, const void *keys, const void *patches,
                                                 uint32_t patch_off, uint32_t patch_len, const uint32_t *commit_ids,
                                                 uint64_t n, int flags, uint64_t *applied_out) {

@@ -363,3 +363,51 @@ def test_refresh_in_place_large_shifts():
     finally:
         snap.close()
         t.close()
+
+
+@pytest.mark.parametrize("cls", checker_classes(), ids=lambda c: c.__name__)
+def test_version_table_compaction_after_refreshes(cls):
+    """Every refresh stages the chains of the leaves it re-transforms again; the previous copies stay behind. After a
+    few rounds stage_gpu_snapshot_compact_versions must drop exactly the unreachable ones: answers at every read id are
+    the tree's before and after, the table shrinks to what a from-scratch snapshot holds, a second call drops nothing."""
+    N, P = 30000, 120
+    t = ycsb_int_table(cls, N, P)
+    rng = np.random.default_rng(41)
+    hot = rng.integers(0, N, 400).astype(np.uint32)                    # the same rows again and again: long chains
+    assert t.commit_update_batch(u32_keys(rng.integers(0, N, 4000)), 10) == 4000
+    snap = sg.Snapshot.from_tree(t.root, 4, P)
+    probes = u32_keys(np.concatenate([rng.integers(0, N + 20, 8000).astype(np.uint32), hot]))
+    starts = u32_keys(rng.integers(0, N, 64))
+    stamps = [0, 10, 2000, 4009]
+    try:
+        assert snap.compact_versions() == (snap.info().n_versions, 0)                  # fresh: everything is reachable
+        cid = 5000
+        for rnd in range(4):
+            ks = np.concatenate([hot[rng.integers(0, len(hot), 300)], rng.integers(0, N, 200).astype(np.uint32)])
+            assert t.commit_update_batch(u32_keys(ks), cid) == len(ks)
+            stamps += [cid, cid + 250, cid + 499]
+            cid += 1000
+            if rnd % 2:
+                snap.refresh_in_place(t.root)
+            else:
+                s2, _ = snap.refresh_from_tree(t.root)
+                snap.close()
+                snap = s2
+        stamps.append(cid + 5)
+        before = snap.info().n_versions
+        _check(snap, t, probes, starts, 120, stamps, "before compaction")
+        kept, dropped = snap.compact_versions()
+        with sg.Snapshot.from_tree(t.root, 4, P) as fresh:
+            assert kept == fresh.info().n_versions, "what a from-scratch snapshot stages is what stays"
+        assert dropped > 0 and kept + dropped == before and snap.info().n_versions == kept
+        _check(snap, t, probes, starts, 120, stamps, "after compaction")
+        assert snap.compact_versions() == (kept, 0)
+        # the compacted table keeps working as the base of further refreshes and device-side updates
+        assert t.commit_update_batch(u32_keys(hot[:50]), cid + 100) == 50
+        s2, st = snap.refresh_from_tree(t.root)
+        snap.close()
+        snap = s2
+        _check(snap, t, probes, starts, 120, stamps + [cid + 120, cid + 200], "refresh after compaction")
+    finally:
+        snap.close()
+        t.close()

@@ -310,6 +310,21 @@ typedef struct {
 int stage_gpu_probe_aggregate_i32(stage_snapshot_t *s, const void *keys, uint64_t n, uint32_t read_ts, uint32_t col_off,
                                   int32_t threshold, stage_agg_i32_t *out, int flags);
 
+/* stage_gpu_probe_aggregate_i32 for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it). No counterpart in the reference.
+ * The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine) and does not synchronise: its
+ * scratch — the source row of every probe — is a fixed device array inside the library (4 MiB per GPU that loads the
+ * library, held until exit), so n <= 1 048 576 probes per call (STAGE_ERR_ARG with a message in
+ * stage_gpu_last_error() beyond that). keys_dev (n x key_size) and out_dev (one record, 8-byte aligned) are DEVICE
+ * memory on the snapshot's GPU; the three kernels are enqueued on the snapshot's stream
+ * (stage_gpu_snapshot_set_stream) and out_dev holds the result once they have run — same record, same values as
+ * stage_gpu_probe_aggregate_i32. The array is shared by every call on that GPU and keeps the last call's contents
+ * (what a call reads it has written before; the record is initialised on the device): calls that overlap on the GPU
+ * — two snapshots, two streams — race; serialise them. The array's device address is looked up once per device on the
+ * first call there (cudaGetSymbolAddress): make one call before starting a graph capture. */
+int stage_gpu_probe_aggregate_i32_noalloc(stage_snapshot_t *s, const void *keys_dev, uint64_t n, uint32_t read_ts,
+                                          uint32_t col_off, int32_t threshold, stage_agg_i32_t *out_dev);
+
 /* The same reduction per GROUP of consecutive probes: CH-Q2* loops over the suppliers and reduces the ~300 stock rows
  * of each (benchmark/tpcc/tpcc_new_order.cpp:803-866; the (w, i) lists come from supp_stock_map,
  * benchmark/tpcc/tpcc_workload.cpp:581-585). Group g = probes [group_offsets[g], group_offsets[g+1]); group_offsets has

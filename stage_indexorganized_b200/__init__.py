@@ -97,6 +97,7 @@ SYMBOLS = {
     "stage_gpu_scan_batch": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _vp, _vp, _i32]),
     "stage_gpu_probe_project": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp, _u32, _u32, _vp, _i32]),
     "stage_gpu_probe_aggregate_i32": (_i32, [_vp, _vp, _u64, _u32, _u32, C.c_int32, C.POINTER(AggI32), _i32]),
+    "stage_gpu_probe_aggregate_i32_noalloc": (_i32, [_vp, _vp, _u64, _u32, _u32, C.c_int32, _vp]),
     "stage_gpu_probe_group_aggregate_i32": (_i32, [_vp, _vp, _u64, _vp, _u64, _u32, _u32, C.c_int32, _vp, _i32]),
     "stage_gpu_scan_project": (_i32, [_vp, _vp, _vp, _u64, _u32, _u32, _i32, _vp, _vp, _u32, _u32, _vp, _i32]),
     "stage_gpu_tpcc_stock_level": (_i32, [_vp, _vp, _vp, _u64, _u32, _vp, _i32]),

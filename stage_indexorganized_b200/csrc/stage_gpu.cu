@@ -2972,6 +2972,77 @@ extern "C" int stage_gpu_probe_aggregate_i32(stage_snapshot_t *s, const void *ke
     return STAGE_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of stage_gpu_probe_aggregate_i32 (no counterpart in the reference).
+// Callers that cannot call cudaMalloc — code under CUDA graph capture, tight serving loops, harnesses
+// that forbid it — need an entry point that allocates nothing. The ordinary call keeps the source row of every probe in
+// a scratch buffer it grows with cudaMalloc; here that scratch is a file-scope device array of a fixed maximum size
+// (kNoAllocMaxProbes source rows = 4 MiB, held by every GPU that loads the library until exit).
+// The array's name is a host-side stand-in in host code, not a device address: its address is taken once per device,
+// with that device current, through cudaGetSymbolAddress and cached. Every call shares the array (it keeps the last
+// call's contents; entries [0, n) are rewritten by the probe kernel before they are read, the caller's result record is
+// initialised by a kernel): calls that overlap on the GPU race.
+// ------------------------------------------------------------------------------------------------
+constexpr uint64_t kNoAllocMaxProbes = 1ull << 20;
+static __device__ __align__(256) uint32_t g_noalloc_src_row[kNoAllocMaxProbes];
+
+__global__ void noalloc_agg_init_kernel(AggI32 *out) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) *out = AggI32{0ull, 0ull, 0x7FFFFFFF, (int) 0x80000000};
+}
+
+constexpr int kNoAllocMaxDevices = 64;
+static std::mutex g_noalloc_mu;
+static uint32_t *g_noalloc_ptr[kNoAllocMaxDevices] = {nullptr};
+
+// device address of the scratch array on `device` (which must be current)
+static int noalloc_scratch(int device, uint32_t **out) {
+    if (device < 0 || device >= kNoAllocMaxDevices) return STAGE_ERR_ARG;
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        uint32_t *p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress((void **) &p, g_noalloc_src_row));
+        if (!p) {
+            g_last_error = "cudaGetSymbolAddress returned a null address for the no-alloc scratch array";
+            return STAGE_ERR_CUDA;
+        }
+        g_noalloc_ptr[device] = p;
+    }
+    *out = g_noalloc_ptr[device];
+    return STAGE_OK;
+}
+
+extern "C" int stage_gpu_probe_aggregate_i32_noalloc(stage_snapshot_t *s, const void *keys_dev, uint64_t n, uint32_t read_ts,
+                                                     uint32_t col_off, int32_t threshold, stage_agg_i32_t *out_dev) {
+    if (!s || !out_dev || (n && !keys_dev)) return STAGE_ERR_ARG;
+    if (!s->sealed) return STAGE_ERR_STATE;
+    if ((uint64_t) col_off + 4 > s->schema.payload_size) return STAGE_ERR_ARG;
+    if (n > kNoAllocMaxProbes) {
+        g_last_error = "stage_gpu_probe_aggregate_i32_noalloc: n = " + std::to_string(n) + " probes exceed the fixed scratch of " +
+                       std::to_string(kNoAllocMaxProbes) + " (split the batch or use stage_gpu_probe_aggregate_i32)";
+        return STAGE_ERR_ARG;
+    }
+    std::lock_guard<std::mutex> lock(s->mu);          // one enqueue at a time on the snapshot's stream
+    CUDA_TRY(cudaSetDevice(s->device));
+    uint32_t *src_row = nullptr;
+    int rc;
+    if ((rc = noalloc_scratch(s->device, &src_row))) return rc;
+    AggI32 *d_out = reinterpret_cast<AggI32 *>(out_dev);
+    noalloc_agg_init_kernel<<<1, 32, 0, s->stream>>>(d_out);
+    LAUNCH_CHECK();
+    if (n == 0) return STAGE_OK;
+    ProbeArgs a{};
+    a.n = n;
+    a.read_ts = read_ts;
+    a.src_row = src_row;
+    a.keys = static_cast<const uint8_t *>(keys_dev);
+    if ((rc = launch_probe_nw(s, s->stream, a))) return rc;
+    const unsigned blocks = (unsigned) std::min<uint64_t>((n + 255) / 256, (uint64_t) sm_count() * 8);
+    aggregate_i32_kernel<<<blocks, 256, 0, s->stream>>>(src_row, n, s->d_payload, s->d_ver_payload, s->schema.payload_size, col_off,
+                                                        threshold, d_out);
+    LAUNCH_CHECK();
+    return STAGE_OK;
+}
+
 extern "C" int stage_gpu_probe_group_aggregate_i32(stage_snapshot_t *s, const void *keys, uint64_t n, const uint64_t *group_offsets,
                                                    uint64_t n_groups, uint32_t read_ts, uint32_t col_off, int32_t threshold,
                                                    stage_group_agg_i32_t *out, int flags) {

@@ -2415,6 +2415,7 @@ static int probe_host_staged(stage_snapshot *s, HostCtx *c, const void *keys, ui
     return STAGE_OK;
 }
 
+constexpr int kNotSmall = 1;                     // small-call path: "does not fit", the caller takes the staged path
 static int probe_host_small(stage_snapshot *s, HostCtx *c, const void *keys, uint64_t n, uint32_t read_ts, uint8_t *found,
                             uint32_t *ts, void *key_out, void *payload_out);          // "small host calls" below
 
@@ -2439,7 +2440,7 @@ extern "C" int stage_gpu_probe_batch(stage_snapshot_t *s, const void *keys, uint
     if (!g.c) return rc;
     if (host_path_mode() == kHostAuto) {
         rc = probe_host_small(s, g.c, keys, n, read_ts, found, ts, key_out, payload_out);
-        if (rc != 1 /* kNotSmall */) return rc;
+        if (rc != kNotSmall) return rc;
     }
     if (host_path_mode() == kHostZeroCopy) {
         uint8_t *df = static_cast<uint8_t *>(mapped_alias(found)), *dk = static_cast<uint8_t *>(mapped_alias(key_out)),
@@ -2729,7 +2730,6 @@ static int scan_host_staged(stage_snapshot *s, HostCtx *c, const void *start_key
 // the kernels instead read the keys from, and store the results into, a pinned slab of the call context through its
 // device alias: memcpy in, two launches, one stream synchronisation, memcpy out — any host memory, either layout.
 constexpr size_t kSmallHostBytes = 192u << 10;
-constexpr int kNotSmall = 1;                     // "does not fit": the caller takes the staged path
 
 static int ctx_small_slab(HostCtx *c) {
     if (c->h_small) return c->d_small ? STAGE_OK : kNotSmall;

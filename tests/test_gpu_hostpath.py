@@ -280,3 +280,54 @@ def test_batching_front_end_coalesces_concurrent_single_operations(mvcc_table):
     b.close()
     assert not errors, errors[:3]
     assert ops == n_threads * per and batches < ops, (batches, ops)
+
+
+@pytest.mark.skipif(ZEROCOPY, reason="the small-call path belongs to the default host path")
+def test_small_call_path_and_its_size_boundary(mvcc_table):
+    """Calls whose keys + results fit the 192 KiB pinned slab of the call context run without staging copies
+    (probe_host_small / scan_host_small, csrc/stage_gpu.cu); one operation more and the staged path takes over. Both sides
+    of the boundary, both layouts, pageable buffers pre-filled with a pattern: same answers as the checker, rows of
+    missed probes and slots beyond row_counts untouched on the small path."""
+    t, snap = mvcc_table
+    K, P = 4, 1000
+    per_probe = K + 1 + 4 + K + P + 64                     # generous: carve-outs are 16-byte aligned
+    n_small = (192 << 10) // per_probe - 2
+    rng = np.random.default_rng(91)
+    for n in (1, 3, n_small, n_small + 8, 4 * n_small):
+        keys = u32_keys(rng.integers(0, 20050, n).astype(np.uint32))
+        keys[0] = u32_keys(np.array([20040], np.uint32))[0]                      # a miss in every batch
+        for read_ts in (0, 1500, 5000):
+            want = t.probe(keys, read_ts)
+            found = np.full(n, 7, np.uint8)
+            ts = np.zeros(n, np.uint32)
+            ko = np.full((n, K), 0xEE, np.uint8)
+            po = np.full((n, P), 0xEE, np.uint8)
+            sg._check(sg.lib().stage_gpu_probe_batch(snap.h, keys.ctypes.data, n, read_ts, found.ctypes.data, ts.ctypes.data,
+                                                     ko.ctypes.data, po.ctypes.data, sg.IO_HOST))
+            hit = want[0] == 1
+            assert np.array_equal(found, want[0]) and np.array_equal(ts[hit], want[1][hit])
+            assert np.array_equal(ko[hit], want[2][hit]) and np.array_equal(po[hit], want[3][hit]), (n, read_ts)
+            if n <= n_small:
+                assert (po[~hit] == 0xEE).all() and (ko[~hit] == 0xEE).all(), "small path leaves missed rows untouched"
+    # scans: 1 x 100 rows (102 KB of results: small), 2 x 100 rows (staged), 12 x 10 rows (small), strided and compact
+    for n, S in ((1, 100), (2, 100), (12, 10), (1, 1), (40, 10)):
+        sk = u32_keys(rng.integers(0, 20000, n).astype(np.uint32))
+        sizes = np.full(n, S, np.uint32)
+        for vis in (0, 1):
+            wc, wk, wt, wp = t.scan(sk, S, 1500, vis)
+            for compact in (False, True):
+                counts = np.zeros(n, np.uint32)
+                ko = np.full((n * S, K), 0xEE, np.uint8)
+                to = np.full(n * S, 0xEEEEEEEE, np.uint32)
+                po = np.full((n * S, P), 0xEE, np.uint8)
+                sg._check(sg.lib().stage_gpu_scan_batch(snap.h, sk.ctypes.data, sizes.ctypes.data, n, S, 1500, vis, counts.ctypes.data,
+                                                        ko.ctypes.data, to.ctypes.data, po.ctypes.data,
+                                                        sg.IO_HOST | (sg.IO_COMPACT if compact else 0)))
+                assert np.array_equal(counts, wc), (n, S, vis, compact)
+                base = 0
+                for i in range(n):
+                    c = int(wc[i])
+                    o = base if compact else i * S
+                    assert np.array_equal(ko[o:o + c], wk[i, :c]) and np.array_equal(to[o:o + c], wt[i, :c]) \
+                        and np.array_equal(po[o:o + c], wp[i, :c]), (n, S, vis, compact, i)
+                    base += c

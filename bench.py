@@ -877,6 +877,31 @@ def main():
     rows_all = float(r_sum.item())
     value = rows_all / (total_ms_max * 1e-3)
 
+    # ---- the same scans at the first / middle / latest read id, with and without visibility ----
+    sweep = None
+    if world == 1:
+        sweep = {}
+        for name, rts in (("first", FIRST_CID), ("mid", FIRST_CID + updates // 2), ("latest", FIRST_CID + updates)):
+            for v in (1, 0):
+                for b in range(2):
+                    snap.scan_device(d_sk[b], d_sizes, n_scans, S, rts, v, d_counts[b], d_keyout, d_tsout, d_payout)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                k = min(5, n_batches)
+                e0.record(stream)
+                for b in range(k):
+                    snap.scan_device(d_sk[b], d_sizes, n_scans, S, rts, v, d_counts[b], d_keyout, d_tsout, d_payout)
+                e1.record(stream)
+                torch.cuda.synchronize()
+                r = int(d_counts[:k].sum().item())
+                ms = e0.elapsed_time(e1) / k
+                sweep[f"{name}/{'IndexScanExecutor' if v else 'TableScanExecutor'}"] = {
+                    "rows_per_s": r / k / (ms * 1e-3), "ms_per_step": ms, "rows_per_step": r // k}
+        # leave d_counts as the timed steps wrote them
+        for b in range(min(5, n_batches)):
+            scan_step(b)
+        torch.cuda.synchronize()
+
     # ---- e2e: host buffers through the C ABI ----------------------------------------------------
     if world > 1:       # probe keys of this rank's own shard (the e2e probe call is shard-local)
         pk_e2e = rank_to_key(rows * world, rank * rows + np.random.default_rng(5000 + rank).integers(
@@ -978,6 +1003,7 @@ def main():
             "parity_check": parity,
             "transform": transform,
             "host_tree": host_tree,
+            "visibility_sweep": sweep,
             "e2e": e2e,
             "gpu_launches": int(launches),
             "clocks": clk.summary(),

@@ -177,14 +177,17 @@ int stage_gpu_snapshot_refresh_from_tree_live(stage_snapshot_t *old, const void 
  * the buffer for the new row count: stage_gpu_set_row_slack(fraction) BEFORE the snapshot is built keeps that fraction
  * of its rows free (STAGE_ERR_NOMEM here otherwise, *snap untouched and still usable). No read may be in flight on
  * *snap during the call and every handle derived from it (batcher) must be gone; on any other error after the rows
- * started moving the snapshot is unusable (reads return STAGE_ERR_STATE) and must be destroyed. Quiesced trees. */
+ * started moving the snapshot is unusable (reads return STAGE_ERR_STATE) and must be destroyed. Quiesced trees.
+ * No counterpart in the reference (its tree is updated in place by the writers, b_tree.cpp:1558-1690 for splits). */
 int stage_gpu_snapshot_refresh_in_place(stage_snapshot_t **snap, const void *root, stage_refresh_stats_t *stats /* may be NULL */);
 int stage_gpu_set_row_slack(double fraction);
 
 /* Both refresh forms stage the chains of every re-transformed leaf again (the version table is append-only), so the
  * copies the previous snapshot held for those leaves stay behind unreferenced. This drops every version no chain head
  * reaches any more and renumbers the rest (mark from the chain column, prefix sum, move); reads give the same answers
- * before and after. No read may be in flight during the call. kept / dropped may be NULL. */
+ * before and after. No read may be in flight during the call. kept / dropped may be NULL. (The reference reclaims
+ * retired versions through VersionStore::CollectRetiredVersionSet / CleanCandidateSlot, version_store.h:629-640; this
+ * is the same duty for the device-side copy of the chains.) */
 int stage_gpu_snapshot_compact_versions(stage_snapshot_t *s, uint64_t *kept, uint64_t *dropped);
 
 /* Streaming construction for callers that own the walk (same result as from_tree):

@@ -124,3 +124,39 @@ def test_tables_without_a_single_order_are_rejected():
     with pytest.raises(sg.StageError):                   # fixed-length schema on a mixed-length tree
         sg.Snapshot.from_tree(t.root, 4, P, leaf_node_size=4096)
     t.close()
+
+
+def test_refresh_of_a_variable_length_table():
+    """Structural refresh (two-table and in-place) on a table with keys of different lengths: the walker packs the new
+    separators, the transform the new records; answers equal the tree's and a from-scratch snapshot's."""
+    keys = [str(i).encode() for i in range(0, 60000, 2)]
+    t = _build(keys, 21)
+    sg.set_row_slack(0.6)
+    try:
+        snap = sg.Snapshot.from_tree(t.root, 8, P, leaf_node_size=4096, key_kind=sg.KEY_VARLEN)
+    finally:
+        sg.set_row_slack(0.0)
+    try:
+        more = [str(i).encode() for i in range(1, 20001, 2)]                  # odd numbers: inserts everywhere, splits
+        pay = (np.arange(len(more), dtype=np.uint64) * 2 + 1).view(np.uint8).reshape(-1, P)
+        assert t.insert_varlen(more, pay, 0) == len(more)
+        all_keys = keys + more
+        s2, st = snap.refresh_from_tree(t.root)
+        assert st.rows == len(all_keys) and st.leaves_transformed > 0
+        _check_reads(t, s2, 8, all_keys, [b"", b"60001", b"x"], [b"", b"1", b"19999", b"5"], 22)
+        s2.close()
+        st = snap.refresh_in_place(t.root)
+        assert st.rows == len(all_keys)
+        _check_reads(t, snap, 8, all_keys, [b"", b"60001", b"x"], [b"", b"1", b"19999", b"5"], 23)
+        for k in more[:3000]:
+            t.delete(np.frombuffer(k, np.uint8))
+        st = snap.refresh_in_place(t.root)
+        assert st.rows == len(all_keys) - 3000
+        _check_reads(t, snap, 8, keys + more[3000:], [more[0], more[2999], b""], [b"", more[10], b"2"], 24)
+        with sg.Snapshot.from_tree(t.root, 8, P, leaf_node_size=4096, key_kind=sg.KEY_VARLEN) as fresh:
+            slots = sg.pack_keys(all_keys[::7], 8)
+            a, b = snap.probe(slots, 9), fresh.probe(slots, 9)
+            assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    finally:
+        snap.close()
+        t.close()

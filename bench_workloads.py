@@ -64,10 +64,18 @@ def config0(args, sg, torch, dev, peak, cpu=True):
     pay = torch.empty((n, P_BYTES), dtype=torch.uint8, device=dev)
     ms = _time_steps(torch, lambda b: snap.probe_device(d_keys[b], n, 1, found, ts, kout, pay), warm, steps)
     hits = int(found.sum().item())
+    # SURVEY 8(d) config 1 names two key streams: (ii) zipf 0.2 above, (i) uniform 1 + x % N (key N misses)
+    u = ycsb.uniform_keys(n_rows, n * nb, seed=1).reshape(nb, n)
+    d_ukeys = torch.from_numpy(u.view(np.int32)).to(dev)
+    ms_u = _time_steps(torch, lambda b: snap.probe_device(d_ukeys[b], n, 1, found, ts, kout, pay), warm, steps)
+    hits_u = int(found.sum().item())
+    del d_ukeys
     algo = hits * (K_BYTES + 2 * (K_BYTES + P_BYTES + 4)) + (n - hits) * (K_BYTES + 1)
     ach = algo / (ms * 1e-3) / 1e9
     out = {"workload": "BASELINE configs[0]: ./ycsb -k 10000 -b 4 -o 10 -u 0 -z 0.2 (read-only point probes, 10 k-row int table)",
            "value": n / (ms * 1e-3), "unit": "probes/s", "ms_per_step": ms, "probes_per_step": n, "hit_rate": hits / n,
+           "uniform_keys": {"value": n / (ms_u * 1e-3), "unit": "probes/s", "ms_per_step": ms_u, "hit_rate": hits_u / n,
+                            "stream": "1 + FastRandom(1).next() % N (ycsb.cpp:99-103: key N is never loaded and misses)"},
            "roofline": {"bound": "l2", "achieved": ach, "unit": "GB/s", "peak": None, "frac": None,
                         "hbm_write_frac": hits * (K_BYTES + P_BYTES + 4) / (ms * 1e-3) / 1e9 / peak,
                         "note": "the 10 MB table is L2-resident: reads never reach HBM, only the result rows are written "
